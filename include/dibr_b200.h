@@ -1,0 +1,182 @@
+/*
+ * dibr_b200.h -- C ABI of libdibr_b200.so: the B200-native (sm_100a) DIB-R
+ * differentiable-rasterization hot path.
+ *
+ * Drop-in boundary.  These entry points replace the four functions the
+ * reference registers with pybind11 at kaolin/csrc/bindings.cpp:76-81
+ *   kaolin._C.render.mesh.packed_rasterize_forward_cuda   (csrc/render/mesh/rasterization.h:23-32)
+ *   kaolin._C.render.mesh.rasterize_backward_cuda         (csrc/render/mesh/rasterization.h:34-41)
+ *   kaolin._C.render.mesh.dibr_soft_mask_forward_cuda     (csrc/render/mesh/dibr_soft_mask.h:23-29)
+ *   kaolin._C.render.mesh.dibr_soft_mask_backward_cuda    (csrc/render/mesh/dibr_soft_mask.h:31-41)
+ * and the torch-side preparation around them in kaolin/render/mesh/rasterization.py:299-363
+ * and kaolin/render/mesh/dibr.py:31-39, which the kernels here fold in.
+ *
+ * Conventions
+ *  - plain C: raw DEVICE pointers, sizes and scalars; no ATen / torch types.
+ *  - every tensor is C-contiguous fp32 unless stated; int64 where the reference uses
+ *    int64 (selected_face_idx, close_face_idx); uint8 for bool masks / dist types.
+ *  - the library never allocates or frees device memory and keeps no state between
+ *    calls: outputs and the scratch workspace are allocated by the caller.
+ *  - all work is enqueued on `stream` (a cudaStream_t passed as void*); no host
+ *    synchronisation happens inside unless documented (needed_host == NULL).
+ *  - return value: DIBR_OK (0) or a negative DIBR_E_* code; dibr_last_error() returns
+ *    a thread-local message for the last failure.
+ *  - there is no CPU fallback: without a CUDA device every entry point fails.
+ *
+ * Workspace protocol.  The face-binning pass builds per-bin face lists whose total
+ * length is data dependent.  The caller passes `ws` of `ws_bytes` bytes laid out as
+ *    [ fixed part | raster list: raster_capacity int32 | soft list: soft_capacity int32 ]
+ * with ws_bytes >= dibr_workspace_bytes_for(..., raster_capacity, soft_capacity); a call
+ * that does not build a list ignores that list's capacity.  The number of list entries
+ * the call needed is written as int64[2] = {raster, soft} to `needed_host`:
+ *    needed_host != NULL : pinned host memory, written asynchronously on `stream`; the
+ *                          caller checks it after its own event/stream sync and, if a
+ *                          value exceeds the capacity it passed, grows `ws` and calls
+ *                          again (outputs of the overflowing call are invalid, but no
+ *                          out-of-bounds access happens).
+ *    needed_host == NULL : the call synchronises `stream` once internally and returns
+ *                          DIBR_E_WORKSPACE if a capacity was insufficient
+ *                          (dibr_last_error() then names the needed entry counts).
+ * The backward of the soft mask re-reads the soft list, so `ws` must be kept unchanged
+ * between dibr_softmask_fwd / dibr_render_fwd and dibr_softmask_bwd, which takes the
+ * same two capacities.
+ */
+#ifndef DIBR_B200_H_
+#define DIBR_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define DIBR_API __attribute__((visibility("default")))
+#else
+#define DIBR_API
+#endif
+
+#define DIBR_OK 0
+#define DIBR_E_INVALID (-1)   /* bad argument (shape, null pointer, unsupported size) */
+#define DIBR_E_WORKSPACE (-2) /* workspace too small (see protocol above)             */
+#define DIBR_E_CUDA (-3)      /* CUDA runtime error; message in dibr_last_error()      */
+
+DIBR_API const char* dibr_last_error(void);
+DIBR_API int dibr_version(void);
+
+/* Bytes of the fixed (data-independent) part of the workspace for a call over `batch`
+ * views of `num_faces` faces (for the packed mode: the total number of packed faces) at
+ * height x width.  Returns < 0 on invalid sizes. */
+DIBR_API int64_t dibr_workspace_fixed_bytes(int batch, int num_faces, int height, int width);
+/* fixed bytes + room for raster_capacity + soft_capacity list entries. */
+DIBR_API int64_t dibr_workspace_bytes_for(int batch, int num_faces, int height, int width,
+                                 int64_t raster_capacity, int64_t soft_capacity);
+
+/*
+ * rasterize forward.  Replaces RasterizeCuda.forward (rasterization.py:289-369) +
+ * packed_rasterize_forward_cuda (rasterization.cpp:49-104, rasterization_cuda.cu:43-192).
+ *
+ *   face_vertices_z      (B, F, 3)
+ *   face_vertices_image  (B, F, 3, 2)   NDC, NOT multiplied (the kernel multiplies)
+ *   face_features        (B, F, 3, D)
+ *   valid_faces          (B, F) uint8/bool or NULL
+ *   face_normals_z       (B, F) or NULL; when given, valid = (normal_z >= 0)
+ *                        (dibr.py:190-199); at most one of the two may be non-NULL
+ * Packed / pre-scaled mode (the raw _C op signature): `prescaled` != 0 means
+ *   face_vertices_image is already multiplied, `face_bboxes` (.,4) is given and
+ *   `first_idx_face_per_mesh` (B+1) int64 delimits each mesh's faces inside packed
+ *   arrays of `num_faces` faces in total; selected_face_idx is then relative to the mesh.
+ * Outputs (every element is written):
+ *   selected_face_idx      (B, H, W) int64, -1 = background
+ *   interpolated_features  (B, H, W, D)
+ *   output_weights         (B, H, W, 3) or NULL (the fast path recomputes them in backward)
+ */
+DIBR_API int dibr_rasterize_fwd(int batch, int num_faces, int height, int width, int feat_dim,
+                       const float* face_vertices_z, const float* face_vertices_image,
+                       const float* face_features, const uint8_t* valid_faces,
+                       const float* face_normals_z, int prescaled, const float* face_bboxes,
+                       const int64_t* first_idx_face_per_mesh, float multiplier, float eps,
+                       int64_t* selected_face_idx, float* interpolated_features,
+                       float* output_weights, void* ws, int64_t ws_bytes,
+                       int64_t raster_capacity, int64_t* needed_host, void* stream);
+
+/*
+ * rasterize backward.  Replaces rasterize_backward_cuda (rasterization.cpp:106-168,
+ * rasterization_cuda.cu:238-402).  face_vertices_image is UNscaled (B, F, 3, 2).
+ * output_weights may be NULL: the weights are then recomputed bit-identically from
+ * (face_vertices_image * multiplier, pixel centre, eps) as the forward did.
+ * grad_face_vertices_image (B,F,3,2) and grad_face_features (B,F,3,D) are ACCUMULATED
+ * into (the caller zero-fills them, as at::zeros_like does at rasterization.cpp:156-157).
+ * face_vertices_z receives no gradient (rasterization.py:387-388).
+ */
+DIBR_API int dibr_rasterize_bwd(int batch, int num_faces, int height, int width, int feat_dim,
+                       const float* grad_interpolated_features, const int64_t* selected_face_idx,
+                       const float* output_weights, const float* face_vertices_image,
+                       const float* face_features, float multiplier, float eps,
+                       float* grad_face_vertices_image, float* grad_face_features, void* stream);
+
+/*
+ * soft mask forward.  Replaces DibrSoftMaskCuda.forward (dibr.py:29-55) +
+ * dibr_soft_mask_forward_cuda (dibr_soft_mask.cpp:48-108, dibr_soft_mask_cuda.cu:27-184).
+ *   face_vertices_image (B, F, 3, 2): unscaled when prescaled == 0 (the kernel multiplies
+ *   and enlarges the boxes by box_margin = (float)(boxlen * multiplier), the product
+ *   taken in double by the caller exactly as dibr.py:37-38 does); when prescaled != 0 it is
+ *   already multiplied and face_large_bboxes (B, F, 4) is used as given (raw _C op).
+ * Outputs: soft_mask (B,H,W) always; the dense per-pixel state of the reference
+ *   close_face_prob (B,H,W,K) f32 / close_face_idx (B,H,W,K) int64 / close_face_dist_type
+ *   (B,H,W,K) uint8 only when all three are non-NULL (they must be pre-filled 0 / -1 / 0
+ *   as dibr_soft_mask.cpp:84-97 does; only used slots are written).
+ */
+DIBR_API int dibr_softmask_fwd(int batch, int num_faces, int height, int width,
+                      const float* face_vertices_image, int prescaled,
+                      const float* face_large_bboxes, const int64_t* selected_face_idx,
+                      float sigmainv, float box_margin, int knum, float multiplier,
+                      float* soft_mask, float* close_face_prob, int64_t* close_face_idx,
+                      uint8_t* close_face_dist_type, void* ws, int64_t ws_bytes,
+                      int64_t raster_capacity, int64_t soft_capacity, int64_t* needed_host,
+                      void* stream);
+
+/*
+ * soft mask backward, recompute form (fast path): re-walks the lists left in `ws` by
+ * dibr_softmask_fwd / dibr_render_fwd instead of reading 13*K bytes/pixel of saved state.
+ * Same arguments as the forward (they must be the SAME values) + grad_soft_mask, the
+ * forward's soft_mask, and grad_face_vertices_image (B,F,3,2), accumulated into, w.r.t.
+ * the UNscaled coordinates (every term is divided by multiplier, dibr_soft_mask_cuda.cu:298-346).
+ */
+DIBR_API int dibr_softmask_bwd(int batch, int num_faces, int height, int width,
+                      const float* face_vertices_image, int prescaled,
+                      const float* face_large_bboxes, const int64_t* selected_face_idx,
+                      float sigmainv, float box_margin, int knum, float multiplier,
+                      const float* grad_soft_mask, const float* soft_mask,
+                      float* grad_face_vertices_image, const void* ws, int64_t ws_bytes,
+                      int64_t raster_capacity, int64_t soft_capacity, void* stream);
+
+/*
+ * soft mask backward, dense-state form: the raw _C op dibr_soft_mask_backward_cuda
+ * (dibr_soft_mask.cpp:110-183, dibr_soft_mask_cuda.cu:230-353).  face_vertices_image is
+ * the SCALED tensor the reference saves (dibr.py:51-54).
+ */
+DIBR_API int dibr_softmask_bwd_dense(int batch, int num_faces, int height, int width, int knum,
+                            const float* grad_soft_mask, const float* soft_mask,
+                            const int64_t* selected_face_idx, const float* close_face_prob,
+                            const int64_t* close_face_idx, const uint8_t* close_face_dist_type,
+                            const float* face_vertices_image_scaled, float sigmainv,
+                            float multiplier, float* grad_face_vertices_image, void* stream);
+
+/*
+ * dibr_rasterization forward, fused (dibr.py:119-209): one binning pass builds both
+ * lists, then the rasterizer and the soft mask run back to back.  valid = normal_z >= 0
+ * for the rasterizer, ALL faces for the soft mask (dibr.py:201-203).
+ */
+DIBR_API int dibr_render_fwd(int batch, int num_faces, int height, int width, int feat_dim,
+                    const float* face_vertices_z, const float* face_vertices_image,
+                    const float* face_features, const float* face_normals_z, float sigmainv,
+                    float box_margin, int knum, float multiplier, float eps,
+                    int64_t* selected_face_idx, float* interpolated_features, float* soft_mask,
+                    void* ws, int64_t ws_bytes, int64_t raster_capacity, int64_t soft_capacity,
+                    int64_t* needed_host, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DIBR_B200_H_ */

@@ -1,0 +1,86 @@
+"""ctypes binding of libdibr_b200.so (C ABI declared in include/dibr_b200.h).
+
+The library is the product: there is no CPU or PyTorch fallback.  If it cannot be
+loaded (or built from csrc/ with nvcc) importing this module raises.
+"""
+import ctypes
+import os
+import subprocess
+import threading
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdibr_b200.so")
+HEADER = os.path.join(os.path.dirname(_HERE), "include", "dibr_b200.h")
+
+DIBR_OK, DIBR_E_INVALID, DIBR_E_WORKSPACE, DIBR_E_CUDA = 0, -1, -2, -3
+
+_c = ctypes
+_vp, _i, _f, _i64 = _c.c_void_p, _c.c_int, _c.c_float, _c.c_int64
+
+# name -> (restype, argtypes); mirrors include/dibr_b200.h declaration by declaration
+SIGNATURES = {
+    "dibr_last_error": (_c.c_char_p, []),
+    "dibr_version": (_i, []),
+    "dibr_workspace_fixed_bytes": (_i64, [_i, _i, _i, _i]),
+    "dibr_workspace_bytes_for": (_i64, [_i, _i, _i, _i, _i64, _i64]),
+    "dibr_rasterize_fwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _f, _f,
+                                _vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp]),
+    "dibr_rasterize_bwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp]),
+    "dibr_softmask_fwd": (_i, [_i, _i, _i, _i, _vp, _i, _vp, _vp, _f, _f, _i, _f, _vp, _vp, _vp, _vp,
+                               _vp, _i64, _i64, _i64, _vp, _vp]),
+    "dibr_softmask_bwd": (_i, [_i, _i, _i, _i, _vp, _i, _vp, _vp, _f, _f, _i, _f, _vp, _vp, _vp,
+                               _vp, _i64, _i64, _i64, _vp]),
+    "dibr_softmask_bwd_dense": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f, _f,
+                                     _vp, _vp]),
+    "dibr_render_fwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _f, _f, _i, _f, _f, _vp, _vp,
+                             _vp, _vp, _i64, _i64, _i64, _vp, _vp]),
+}
+
+_lock = threading.Lock()
+_lib = None
+
+
+def build(force=False):
+    """Compile csrc/*.cu for sm_100a into libdibr_b200.so (in-tree, next to this file)."""
+    srcs = [os.path.join(_HERE, "csrc", f) for f in os.listdir(os.path.join(_HERE, "csrc"))
+            if f.endswith((".cu", ".cuh"))] + [HEADER]
+    if (not force and os.path.exists(LIB_PATH)
+            and all(os.path.getmtime(LIB_PATH) >= os.path.getmtime(s) for s in srcs)):
+        return LIB_PATH
+    subprocess.check_call(["sh", os.path.join(_HERE, "csrc", "build.sh")])
+    return LIB_PATH
+
+
+def lib():
+    global _lib
+    with _lock:
+        if _lib is None:
+            if not os.path.exists(LIB_PATH):
+                try:
+                    build()
+                except Exception as e:  # no silent fallback: the CUDA library IS the product
+                    raise ImportError(
+                        "kaolin-windows_b200: libdibr_b200.so is missing and could not be built "
+                        "(run `python -c 'import __graft_entry__ as g; g.build()'`): %r" % (e,))
+            h = ctypes.CDLL(LIB_PATH)
+            for name, (res, args) in SIGNATURES.items():
+                fn = getattr(h, name)  # AttributeError if the library lacks a declared symbol
+                fn.restype = res
+                fn.argtypes = args
+            _lib = h
+    return _lib
+
+
+def last_error():
+    return lib().dibr_last_error().decode("utf-8", "replace")
+
+
+def check(rc, what):
+    """Maps C return codes to the exceptions the reference's C++ wrappers raise
+    (c10::Error -> RuntimeError, rasterization.cpp:70-85)."""
+    if rc == DIBR_OK:
+        return
+    msg = "%s: %s" % (what, last_error())
+    if rc == DIBR_E_INVALID:
+        raise ValueError(msg)
+    raise RuntimeError(msg)

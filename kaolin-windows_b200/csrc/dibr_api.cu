@@ -1,0 +1,343 @@
+// dibr_api.cu -- C ABI of libdibr_b200.so (see include/dibr_b200.h).
+// Plans the screen hierarchy, lays out the caller's workspace and sequences the
+// kernels of dibr_binning.cu / dibr_raster.cu / dibr_softmask.cu on the caller's stream.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+#include "../../include/dibr_b200.h"
+#include "dibr_common.cuh"
+
+namespace dibr {
+
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define DIBR_CUDA(expr)                                                              \
+  do {                                                                               \
+    cudaError_t e_ = (expr);                                                         \
+    if (e_ != cudaSuccess)                                                           \
+      return fail(DIBR_E_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e_));      \
+  } while (0)
+
+static inline int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+
+static int make_plan(int B, int F, int H, int W, Plan& p) {
+  if (B < 0 || F < 0 || H <= 0 || W <= 0)
+    return fail(DIBR_E_INVALID, "invalid sizes B=%d F=%d H=%d W=%d", B, F, H, W);
+  if (B > 65535) return fail(DIBR_E_INVALID, "batch %d > 65535 not supported", B);
+  if (H > 32768 || W > 32768) return fail(DIBR_E_INVALID, "image %dx%d too large", H, W);
+  memset(&p, 0, sizeof(p));
+  p.B = B; p.F = F; p.H = H; p.W = W;
+  int k = 5;
+  while ((int64_t)((W + (1 << k) - 1) >> k) * ((H + (1 << k) - 1) >> k) > 1024) k++;
+  p.bin_log2 = k;
+  p.nbx = (W + (1 << k) - 1) >> k;
+  p.nby = (H + (1 << k) - 1) >> k;
+  p.NB = p.nbx * p.nby;
+  p.blk_log2 = k < 6 ? k : 6;
+  p.nkx = (W + (1 << p.blk_log2) - 1) >> p.blk_log2;
+  p.nky = (H + (1 << p.blk_log2) - 1) >> p.blk_log2;
+  // one warp per chunk of S faces: aim at ~8k warps, keep the count matrix moderate
+  int64_t s = ((int64_t)B * F) / 8192;
+  if (s < 128) s = 128;
+  if (s > 4096) s = 4096;
+  p.S = (int)align_up(s, 32);
+  p.nchunks = F > 0 ? (F + p.S - 1) / p.S : 0;
+  int64_t off = 0;
+  p.off_total = off; off += 64;
+  p.off_flags = off; off = align_up(off + (int64_t)B * p.nkx * p.nky * 4, 256);
+  for (int l = 0; l < 2; l++) {
+    p.off_start[l] = off; off = align_up(off + (int64_t)B * p.NB * 4, 256);
+    p.off_count[l] = off; off = align_up(off + (int64_t)B * p.NB * 4, 256);
+    p.off_range[l] = off; off = align_up(off + (int64_t)B * p.nchunks * 8, 256);
+    p.off_mat[l] = off; off = align_up(off + (int64_t)B * p.NB * p.nchunks * 4, 256);
+  }
+  p.fixed_bytes = off;
+  return DIBR_OK;
+}
+
+struct Workspace {
+  char* base;
+  int64_t cap[2];
+  int* list[2];
+};
+
+static int bind_workspace(const Plan& p, const void* ws, int64_t ws_bytes, int64_t cap_r,
+                          int64_t cap_s, Workspace& w) {
+  if (cap_r < 0) cap_r = 0;
+  if (cap_s < 0) cap_s = 0;
+  if (cap_r > 0x7fffffff || cap_s > 0x7fffffff)
+    return fail(DIBR_E_INVALID, "list capacity above 2^31-1 entries");
+  const int64_t need = p.fixed_bytes + 4 * (cap_r + cap_s);
+  if (!ws || ws_bytes < need)
+    return fail(DIBR_E_WORKSPACE, "workspace of %lld bytes given, %lld needed",
+                (long long)ws_bytes, (long long)need);
+  if (((uintptr_t)ws & 255) != 0) return fail(DIBR_E_INVALID, "workspace must be 256-byte aligned");
+  w.base = (char*)ws;
+  w.cap[0] = cap_r;
+  w.cap[1] = cap_s;
+  w.list[0] = (int*)(w.base + p.fixed_bytes);
+  w.list[1] = w.list[0] + cap_r;
+  return DIBR_OK;
+}
+
+static void attach(BinJob& j, const Plan& p, const Workspace& w, int l) {
+  j.mat = (int*)(w.base + p.off_mat[l]);
+  j.range = (int2*)(w.base + p.off_range[l]);
+  j.start = (int*)(w.base + p.off_start[l]);
+  j.count = (int*)(w.base + p.off_count[l]);
+  j.list = w.list[l];
+  j.total = (unsigned long long*)(w.base + p.off_total) + l;
+  j.capacity = w.cap[l];
+}
+
+// memset + count + scan + (capacity check) + fill for the given jobs (kinds[i] = 0/1).
+static int run_binning(const Plan& p, const Workspace& w, BinJobs& jobs, const int* kinds,
+                       int njobs, int64_t* needed_host, cudaStream_t st) {
+  DIBR_CUDA(cudaMemsetAsync(w.base, 0, p.off_start[0], st));  // totals + block flags
+  for (int i = 0; i < njobs; i++) {
+    const int l = kinds[i];
+    DIBR_CUDA(cudaMemsetAsync(w.base + p.off_start[l], 0,
+                              (l == 0 ? p.off_start[1] : p.fixed_bytes) - p.off_start[l], st));
+  }
+  if (p.B > 0 && p.F > 0) DIBR_CUDA(launch_binning_count(jobs, njobs, p, st));
+  if (needed_host) {
+    DIBR_CUDA(cudaMemcpyAsync(needed_host, w.base + p.off_total, 16, cudaMemcpyDeviceToHost, st));
+  } else {
+    unsigned long long tot[2] = {0, 0};
+    DIBR_CUDA(cudaMemcpyAsync(tot, w.base + p.off_total, 16, cudaMemcpyDeviceToHost, st));
+    DIBR_CUDA(cudaStreamSynchronize(st));
+    if ((int64_t)tot[0] > w.cap[0] || (int64_t)tot[1] > w.cap[1])
+      return fail(DIBR_E_WORKSPACE, "face lists need %llu raster / %llu soft entries, "
+                  "capacity %lld / %lld", tot[0], tot[1], (long long)w.cap[0], (long long)w.cap[1]);
+  }
+  if (p.B > 0 && p.F > 0) DIBR_CUDA(launch_binning_fill(jobs, njobs, p, st));
+  return DIBR_OK;
+}
+
+static BinJob face_source(const float* img, const float* bbox, const uint8_t* valid,
+                          const float* normal_z, const int64_t* first, long long view_stride,
+                          float mult, float margin, int prescaled) {
+  BinJob j;
+  memset(&j, 0, sizeof(j));
+  j.img = img; j.bbox = bbox; j.valid = valid; j.normal_z = normal_z; j.first = first;
+  j.view_stride = view_stride; j.mult = mult; j.margin = margin; j.prescaled = prescaled;
+  return j;
+}
+
+}  // namespace dibr
+
+using namespace dibr;
+
+extern "C" const char* dibr_last_error(void) { return g_err; }
+extern "C" int dibr_version(void) { return 100; }
+
+extern "C" int64_t dibr_workspace_fixed_bytes(int B, int F, int H, int W) {
+  Plan p;
+  int rc = make_plan(B, F, H, W, p);
+  return rc ? rc : p.fixed_bytes;
+}
+
+extern "C" int64_t dibr_workspace_bytes_for(int B, int F, int H, int W, int64_t cap_r,
+                                            int64_t cap_s) {
+  Plan p;
+  int rc = make_plan(B, F, H, W, p);
+  if (rc) return rc;
+  return p.fixed_bytes + 4 * ((cap_r > 0 ? cap_r : 0) + (cap_s > 0 ? cap_s : 0));
+}
+
+static int check_common(float multiplier) {
+  if (!(multiplier > 0.f) || !isfinite(multiplier))
+    return fail(DIBR_E_INVALID, "multiplier must be a positive finite number");
+  return DIBR_OK;
+}
+
+extern "C" int dibr_rasterize_fwd(int B, int F, int H, int W, int D, const float* z,
+                                  const float* img, const float* feat, const uint8_t* valid,
+                                  const float* normal_z, int prescaled, const float* bboxes,
+                                  const int64_t* first, float multiplier, float eps,
+                                  int64_t* out_idx, float* out_feat, float* out_w, void* ws,
+                                  int64_t ws_bytes, int64_t cap_r, int64_t* needed_host,
+                                  void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  Plan p;
+  int rc = make_plan(B, F, H, W, p);
+  if (rc) return rc;
+  if ((rc = check_common(multiplier))) return rc;
+  if (D < 0) return fail(DIBR_E_INVALID, "feat_dim < 0");
+  if (B == 0) return DIBR_OK;
+  if (!out_idx || (!out_feat && D > 0)) return fail(DIBR_E_INVALID, "null output");
+  if (F > 0 && (!z || !img || (!feat && D > 0))) return fail(DIBR_E_INVALID, "null input");
+  if (valid && normal_z) return fail(DIBR_E_INVALID, "valid_faces and face_normals_z both given");
+  if (prescaled && (!bboxes || !first))
+    return fail(DIBR_E_INVALID, "prescaled mode needs face_bboxes and first_idx_face_per_mesh");
+  if (!prescaled && (bboxes || first))
+    return fail(DIBR_E_INVALID, "face_bboxes / first_idx only valid in prescaled mode");
+  Workspace w;
+  if ((rc = bind_workspace(p, ws, ws_bytes, cap_r, 0, w))) return rc;
+  BinJobs jobs;
+  jobs.j[0] = face_source(img, bboxes, valid, normal_z, first, prescaled ? 0 : F, multiplier,
+                          0.f, prescaled);
+  attach(jobs.j[0], p, w, 0);
+  jobs.j[1] = jobs.j[0];
+  const int kinds[1] = {0};
+  if ((rc = run_binning(p, w, jobs, kinds, 1, needed_host, st))) return rc;
+  RasterArgs a;
+  a.job = jobs.j[0]; a.z = z; a.feat = feat; a.D = D; a.eps_d = (double)eps;
+  a.out_idx = out_idx; a.out_feat = out_feat; a.out_w = out_w;
+  a.block_uncovered = (int*)(w.base + p.off_flags);
+  DIBR_CUDA(launch_raster_forward(a, p, st));
+  return DIBR_OK;
+}
+
+extern "C" int dibr_rasterize_bwd(int B, int F, int H, int W, int D, const float* grad,
+                                  const int64_t* idx, const float* weights, const float* img,
+                                  const float* feat, float multiplier, float eps, float* grad_img,
+                                  float* grad_feat, void* stream) {
+  if (B < 0 || F < 0 || H <= 0 || W <= 0 || D < 0) return fail(DIBR_E_INVALID, "invalid sizes");
+  int rc = check_common(multiplier);
+  if (rc) return rc;
+  if (B == 0 || F == 0 || D == 0) return DIBR_OK;
+  if (B > 65535) return fail(DIBR_E_INVALID, "batch %d > 65535 not supported", B);
+  if (!grad || !idx || !img || !feat || !grad_img || !grad_feat)
+    return fail(DIBR_E_INVALID, "null pointer");
+  RasterBwdArgs a;
+  a.grad = grad; a.idx = idx; a.weights = weights; a.img = img; a.feat = feat;
+  a.grad_img = grad_img; a.grad_feat = grad_feat;
+  a.B = B; a.F = F; a.H = H; a.W = W; a.D = D;
+  a.mult = multiplier; a.eps_f = eps; a.eps_d = (double)eps;
+  DIBR_CUDA(launch_raster_backward(a, (cudaStream_t)stream));
+  return DIBR_OK;
+}
+
+static int soft_common(int B, int F, int H, int W, const float* img, int prescaled,
+                       const float* bboxes, const int64_t* sel, int K, float multiplier,
+                       float box_margin, Plan& p, BinJob& job) {
+  int rc = make_plan(B, F, H, W, p);
+  if (rc) return rc;
+  if ((rc = check_common(multiplier))) return rc;
+  if (K < 0) return fail(DIBR_E_INVALID, "knum < 0");
+  if (B > 0 && !sel) return fail(DIBR_E_INVALID, "null selected_face_idx");
+  if (B > 0 && F > 0 && !img) return fail(DIBR_E_INVALID, "null face_vertices_image");
+  if (prescaled && !bboxes) return fail(DIBR_E_INVALID, "prescaled mode needs face_large_bboxes");
+  if (!prescaled && bboxes) return fail(DIBR_E_INVALID, "face_large_bboxes only in prescaled mode");
+  job = face_source(img, bboxes, nullptr, nullptr, nullptr, F, multiplier, box_margin, prescaled);
+  return DIBR_OK;
+}
+
+extern "C" int dibr_softmask_fwd(int B, int F, int H, int W, const float* img, int prescaled,
+                                 const float* bboxes, const int64_t* sel, float sigmainv,
+                                 float box_margin, int K, float multiplier, float* mask,
+                                 float* prob, int64_t* cidx, uint8_t* type, void* ws,
+                                 int64_t ws_bytes, int64_t cap_r, int64_t cap_s,
+                                 int64_t* needed_host, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  Plan p;
+  BinJobs jobs;
+  int rc = soft_common(B, F, H, W, img, prescaled, bboxes, sel, K, multiplier, box_margin, p,
+                       jobs.j[0]);
+  if (rc) return rc;
+  if (B == 0) return DIBR_OK;
+  if (!mask) return fail(DIBR_E_INVALID, "null soft_mask");
+  const bool dense = prob && cidx && type;
+  if (!dense && (prob || cidx || type))
+    return fail(DIBR_E_INVALID, "dense outputs must be given all three or none");
+  Workspace w;
+  if ((rc = bind_workspace(p, ws, ws_bytes, cap_r, cap_s, w))) return rc;
+  attach(jobs.j[0], p, w, 1);
+  jobs.j[1] = jobs.j[0];
+  const int kinds[1] = {1};
+  if ((rc = run_binning(p, w, jobs, kinds, 1, needed_host, st))) return rc;
+  SoftArgs a;
+  memset(&a, 0, sizeof(a));
+  a.job = jobs.j[0]; a.sel = sel; a.sigmainv = sigmainv; a.K = K; a.mask = mask;
+  a.prob = prob; a.cidx = cidx; a.type = type;
+  DIBR_CUDA(launch_softmask(a, dense ? SOFT_FWD_DENSE : SOFT_FWD, p, st));
+  return DIBR_OK;
+}
+
+extern "C" int dibr_softmask_bwd(int B, int F, int H, int W, const float* img, int prescaled,
+                                 const float* bboxes, const int64_t* sel, float sigmainv,
+                                 float box_margin, int K, float multiplier,
+                                 const float* grad_mask, const float* mask, float* grad_img,
+                                 const void* ws, int64_t ws_bytes, int64_t cap_r, int64_t cap_s,
+                                 void* stream) {
+  Plan p;
+  BinJob job;
+  int rc = soft_common(B, F, H, W, img, prescaled, bboxes, sel, K, multiplier, box_margin, p, job);
+  if (rc) return rc;
+  if (B == 0 || F == 0) return DIBR_OK;
+  if (!grad_mask || !mask || !grad_img) return fail(DIBR_E_INVALID, "null pointer");
+  Workspace w;
+  if ((rc = bind_workspace(p, ws, ws_bytes, cap_r, cap_s, w))) return rc;
+  attach(job, p, w, 1);
+  SoftArgs a;
+  memset(&a, 0, sizeof(a));
+  a.job = job; a.sel = sel; a.sigmainv = sigmainv; a.K = K;
+  a.grad_mask = grad_mask; a.mask_in = mask; a.grad_img = grad_img;
+  DIBR_CUDA(launch_softmask(a, SOFT_BWD, p, (cudaStream_t)stream));
+  return DIBR_OK;
+}
+
+extern "C" int dibr_softmask_bwd_dense(int B, int F, int H, int W, int K, const float* grad_mask,
+                                       const float* mask, const int64_t* sel, const float* prob,
+                                       const int64_t* cidx, const uint8_t* type,
+                                       const float* img_scaled, float sigmainv, float multiplier,
+                                       float* grad_img, void* stream) {
+  if (B < 0 || F < 0 || H <= 0 || W <= 0 || K < 0) return fail(DIBR_E_INVALID, "invalid sizes");
+  int rc = check_common(multiplier);
+  if (rc) return rc;
+  if (B == 0 || F == 0 || K == 0) return DIBR_OK;
+  if (!grad_mask || !mask || !sel || !prob || !cidx || !type || !img_scaled || !grad_img)
+    return fail(DIBR_E_INVALID, "null pointer");
+  SoftDenseBwdArgs a;
+  a.grad_mask = grad_mask; a.mask = mask; a.sel = sel; a.prob = prob; a.cidx = cidx;
+  a.type = type; a.img = img_scaled; a.grad_img = grad_img;
+  a.B = B; a.F = F; a.H = H; a.W = W; a.K = K; a.sigmainv = sigmainv; a.mult = multiplier;
+  DIBR_CUDA(launch_softmask_dense_backward(a, (cudaStream_t)stream));
+  return DIBR_OK;
+}
+
+extern "C" int dibr_render_fwd(int B, int F, int H, int W, int D, const float* z,
+                               const float* img, const float* feat, const float* normal_z,
+                               float sigmainv, float box_margin, int K, float multiplier,
+                               float eps, int64_t* out_idx, float* out_feat, float* mask,
+                               void* ws, int64_t ws_bytes, int64_t cap_r, int64_t cap_s,
+                               int64_t* needed_host, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  Plan p;
+  int rc = make_plan(B, F, H, W, p);
+  if (rc) return rc;
+  if ((rc = check_common(multiplier))) return rc;
+  if (D < 0 || K < 0) return fail(DIBR_E_INVALID, "feat_dim / knum < 0");
+  if (B == 0) return DIBR_OK;
+  if (!out_idx || (!out_feat && D > 0) || !mask) return fail(DIBR_E_INVALID, "null output");
+  if (F > 0 && (!z || !img || (!feat && D > 0))) return fail(DIBR_E_INVALID, "null input");
+  Workspace w;
+  if ((rc = bind_workspace(p, ws, ws_bytes, cap_r, cap_s, w))) return rc;
+  BinJobs jobs;
+  jobs.j[0] = face_source(img, nullptr, nullptr, normal_z, nullptr, F, multiplier, 0.f, 0);
+  jobs.j[1] = face_source(img, nullptr, nullptr, nullptr, nullptr, F, multiplier, box_margin, 0);
+  attach(jobs.j[0], p, w, 0);
+  attach(jobs.j[1], p, w, 1);
+  const int kinds[2] = {0, 1};
+  if ((rc = run_binning(p, w, jobs, kinds, 2, needed_host, st))) return rc;
+  RasterArgs a;
+  a.job = jobs.j[0]; a.z = z; a.feat = feat; a.D = D; a.eps_d = (double)eps;
+  a.out_idx = out_idx; a.out_feat = out_feat; a.out_w = nullptr;
+  a.block_uncovered = (int*)(w.base + p.off_flags);
+  DIBR_CUDA(launch_raster_forward(a, p, st));
+  SoftArgs s;
+  memset(&s, 0, sizeof(s));
+  s.job = jobs.j[1]; s.sel = out_idx; s.sigmainv = sigmainv; s.K = K; s.mask = mask;
+  DIBR_CUDA(launch_softmask(s, SOFT_FWD, p, st));
+  return DIBR_OK;
+}

@@ -1,0 +1,179 @@
+// dibr_binning.cu -- per-view face binning (north_star subsystem (a)).
+//
+// Builds, for every (view, screen bin), the compacted list of faces whose box touches
+// the bin, IN ASCENDING FACE ORDER (the soft mask's "first knum faces" rule,
+// dibr_soft_mask_cuda.cu:80,165-171, depends on that order; the rasterizer does not).
+// It is a stable multi-bin partition done in three launches, without any global atomics
+// on the data path and without a sort:
+//
+//   bin_count  one WARP per chunk of S consecutive faces of one view.  Per step the warp
+//              loads 32 faces, derives each face's bin rectangle, and walks the distinct
+//              bins touched in ascending bin id (warp min-reduce); the faces touching the
+//              current bin are found with __ballot_sync and counted with __popc into the
+//              warp's private shared-memory histogram.  Non-zero counts go to
+//              mat[view][bin][chunk].
+//   bin_scan   one warp per (view, bin): exclusive scan of mat[view][bin][:] over chunks
+//              (coalesced, shuffle scan), then one list segment per bin is reserved from
+//              a global cursor (one atomic per CTA of 8 bins).
+//   bin_fill   same walk as bin_count; the rank of a face inside its bin is
+//              segment start + chunk offset + running count + popc(ballot & lanemask_lt),
+//              so every bin's list comes out sorted by face index.
+//
+// All three kernels take up to two jobs (raster list, soft-mask list) via blockIdx.z so
+// that the fused forward bins both in the same launches.
+#include "dibr_common.cuh"
+
+namespace dibr {
+
+
+constexpr int kBinWarps = 4;  // warps (= chunks) per CTA of bin_count / bin_fill
+
+// Bin rectangle of a face box; false if it touches no pixel.
+__device__ __forceinline__ bool bin_rect(const Grid& g, const Face2D& f, int bin_log2, int& bx0,
+                                         int& bx1, int& by0, int& by1) {
+  int x_lo, x_hi, y_lo, y_hi;
+  if (!pixel_range(g, f.xmin, f.ymin, f.xmax, f.ymax, x_lo, x_hi, y_lo, y_hi)) return false;
+  bx0 = x_lo >> bin_log2;
+  bx1 = x_hi >> bin_log2;
+  by0 = y_lo >> bin_log2;
+  by1 = y_hi >> bin_log2;
+  return true;
+}
+
+template <bool FILL>
+__global__ void __launch_bounds__(kBinWarps * 32)
+bin_walk_kernel(const BinJobs jobs, const Plan p) {
+  extern __shared__ int s_hist[];  // [kBinWarps][NB]
+  const BinJob& job = jobs.j[blockIdx.z];
+  const int warp = threadIdx.x >> 5, lane = lane_id();
+  const int b = blockIdx.y;
+  const int chunk = blockIdx.x * kBinWarps + warp;
+  if (chunk >= p.nchunks) return;  // whole warp leaves; no block-wide barrier below
+  int* hist = s_hist + warp * p.NB;
+  const Grid g = make_grid(job.mult, p.W, p.H);
+  const long long row = (long long)b * p.NB;  // first bin row of this view in mat/start
+
+  int lo_bin = p.NB, hi_bin = -1;
+  if (FILL) {
+    const int2 r = job.range[(long long)b * p.nchunks + chunk];
+    lo_bin = r.x;
+    hi_bin = r.y;
+    for (int i = lo_bin + lane; i <= hi_bin; i += 32)
+      hist[i] = job.start[row + i] + job.mat[(row + i) * p.nchunks + chunk];
+  } else {
+    for (int i = lane; i < p.NB; i += 32) hist[i] = 0;
+  }
+  __syncwarp();
+
+  const int f_begin = chunk * p.S;
+  const int f_end = min(f_begin + p.S, p.F);
+  for (int f0 = f_begin; f0 < f_end; f0 += 32) {
+    const int f = f0 + lane;
+    int bx0 = 0, bx1 = -1, by0 = 0, by1 = -1;
+    bool act = false;
+    if (f < f_end) {
+      Face2D fc;
+      if (load_face2d(job, b, f, fc)) act = bin_rect(g, fc, p.bin_log2, bx0, bx1, by0, by1);
+    }
+    int cx = bx0, cy = by0;
+    // Ordered emission: each lane walks its rectangle row-major (ascending bin id); the
+    // warp repeatedly takes the smallest pending bin id, so all faces touching that bin
+    // are handled together, in lane (= face) order.
+    while (true) {
+      const int cur = act ? cy * p.nbx + cx : 0x7fffffff;
+      const int m = __reduce_min_sync(DIBR_FULL_MASK, cur);
+      if (m == 0x7fffffff) break;
+      const bool hit = (cur == m);
+      const unsigned mask = __ballot_sync(DIBR_FULL_MASK, hit);
+      const int base = hist[m];
+      __syncwarp();
+      if (lane == 0) hist[m] = base + __popc(mask);
+      if (FILL) {
+        if (hit) {
+          const long long slot = (long long)base + __popc(mask & lanemask_lt());
+          if (slot < job.capacity) job.list[slot] = f;
+        }
+      } else {
+        lo_bin = min(lo_bin, m);
+        hi_bin = max(hi_bin, m);
+      }
+      if (hit) {
+        if (++cx > bx1) {
+          cx = bx0;
+          if (++cy > by1) act = false;
+        }
+      }
+      __syncwarp();
+    }
+  }
+  if (!FILL) {
+    __syncwarp();
+    for (int i = lo_bin + lane; i <= hi_bin; i += 32) {
+      const int c = hist[i];
+      if (c) job.mat[(row + i) * p.nchunks + chunk] = c;
+    }
+    if (lane == 0) job.range[(long long)b * p.nchunks + chunk] = make_int2(lo_bin, hi_bin);
+  }
+}
+
+// One warp per (view, bin); 8 warps per CTA share one cursor atomic.
+__global__ void __launch_bounds__(256) bin_scan_kernel(const BinJobs jobs, const Plan p) {
+  __shared__ int s_tot[8];
+  __shared__ long long s_base;
+  const BinJob& job = jobs.j[blockIdx.z];
+  const int warp = threadIdx.x >> 5, lane = lane_id();
+  const long long nrows = (long long)p.B * p.NB;
+  const long long rowi = (long long)blockIdx.x * 8 + warp;
+  int carry = 0;
+  if (rowi < nrows) {
+    int* m = job.mat + rowi * p.nchunks;
+    for (int i = 0; i < p.nchunks; i += 32) {
+      const int idx = i + lane;
+      const int v = idx < p.nchunks ? m[idx] : 0;
+      int incl = v;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int t = __shfl_up_sync(DIBR_FULL_MASK, incl, d);
+        if (lane >= d) incl += t;
+      }
+      if (idx < p.nchunks) m[idx] = carry + incl - v;
+      carry += __shfl_sync(DIBR_FULL_MASK, incl, 31);
+    }
+  }
+  if (lane == 0) s_tot[warp] = carry;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+    for (int i = 0; i < 8; i++) t += s_tot[i];
+    s_base = t ? (long long)atomicAdd(job.total, (unsigned long long)t) : 0ll;
+  }
+  __syncthreads();
+  if (rowi < nrows && lane == 0) {
+    long long st = s_base;
+    for (int i = 0; i < warp; i++) st += s_tot[i];
+    // Segments beyond the capacity are clamped by the consumers (start + count <= capacity
+    // is re-checked there); the host sees the overflow through job.total.
+    job.start[rowi] = (int)min(st, (long long)0x7fffffff);
+    job.count[rowi] = carry;
+  }
+}
+
+// ---------------------------------------------------------------------------- host
+cudaError_t launch_binning_count(const BinJobs& jobs, int njobs, const Plan& p, cudaStream_t st) {
+  const size_t smem = (size_t)kBinWarps * p.NB * sizeof(int);
+  dim3 grid((p.nchunks + kBinWarps - 1) / kBinWarps, p.B, njobs);
+  bin_walk_kernel<false><<<grid, kBinWarps * 32, smem, st>>>(jobs, p);
+  const long long nrows = (long long)p.B * p.NB;
+  dim3 grid2((unsigned)((nrows + 7) / 8), 1, njobs);
+  bin_scan_kernel<<<grid2, 256, 0, st>>>(jobs, p);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_binning_fill(const BinJobs& jobs, int njobs, const Plan& p, cudaStream_t st) {
+  const size_t smem = (size_t)kBinWarps * p.NB * sizeof(int);
+  dim3 grid((p.nchunks + kBinWarps - 1) / kBinWarps, p.B, njobs);
+  bin_walk_kernel<true><<<grid, kBinWarps * 32, smem, st>>>(jobs, p);
+  return cudaGetLastError();
+}
+
+}  // namespace dibr

@@ -1,0 +1,282 @@
+// dibr_common.cuh -- shared device code of libdibr_b200 (sm_100a).
+//
+// Exact arithmetic.  selected_face_idx has to be bit-exact against the reference, so the
+// per-(pixel, face) test is written with explicit round-to-nearest intrinsics in the
+// very shapes nvcc 12.9 contracts the reference source into for sm_100a (decoded from
+// the SASS of the reference build, see DESIGN.md "Numerics"):
+//   rasterization_cuda.cu:85-86   x0 = fl(fl(mult / W) * float(2*ix + 1 - W))
+//   rasterization_cuda.cu:137-139 w = fma(p, q, -fl(r * s))
+//   rasterization_cuda.cu:140-142 norm = (w0 + w1) + w2; += copysign(eps) in double
+//   rasterization_cuda.cu:143-145 three IEEE divisions
+//   rasterization_cuda.cu:159     z0 = fma(w2, cz, fma(w0, az, fl(w1 * bz)))
+//   rasterization_cuda.cu:187     feat = fma(w2, r2, fma(w0, r0, fl(w1 * r1)))
+// Using intrinsics (never a*b+c) keeps nvcc from re-contracting them differently here.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <math.h>
+
+#define DIBR_FULL_MASK 0xffffffffu
+
+namespace dibr {
+
+// ------------------------------------------------------------------ plan / workspace
+// Screen hierarchy: bin (bin_px = 32 << k, <= 1024 bins per view, the binning
+// granularity) >= block (min(bin_px, 64): one CTA of the rasterizer / soft mask)
+// >= tile 16x16 (one warp of the soft mask) >= region 8x4 (one pixel per lane).
+struct Plan {
+  int B, F, H, W;
+  int bin_log2, nbx, nby, NB;  // bins
+  int blk_log2, nkx, nky;      // blocks (CTA footprint)
+  int S, nchunks;              // faces per binning chunk (one warp), chunks per view
+  int lists;
+  // byte offsets inside the workspace (per list kind l = 0 raster, 1 soft)
+  int64_t off_mat[2];     // int [B][NB][nchunks]  chunk counts -> exclusive offsets
+  int64_t off_range[2];   // int2 [B][nchunks]     touched bin range of each chunk
+  int64_t off_start[2];   // int [B][NB]           list segment start of each bin
+  int64_t off_count[2];   // int [B][NB]           list segment length
+  int64_t off_total;      // unsigned long long [2] entries needed per list kind
+  int64_t off_flags;      // int [B][nkx*nky]      uncovered-pixel count per block
+  int64_t fixed_bytes;    // everything above
+};
+
+// One binning job = one list kind.  Passed by value to the kernels.
+struct BinJob {
+  const float* img;        // (B or 1, F, 3, 2)
+  const float* bbox;       // explicit boxes (., F, 4) or nullptr (computed)
+  const uint8_t* valid;    // (B, F) or nullptr
+  const float* normal_z;   // (B, F) or nullptr (valid = nz >= 0)
+  const int64_t* first;    // (B + 1) packed ranges or nullptr
+  long long view_stride;   // faces between consecutive views in img/bbox (F, or 0 if packed)
+  float mult;              // multiplier (applied unless prescaled)
+  float margin;            // box enlargement, 0 for the raster list
+  int prescaled;
+  int* mat;
+  int2* range;
+  int* start;
+  int* count;
+  int* list;
+  unsigned long long* total;
+  long long capacity;      // entries available in `list`
+};
+
+
+// ------------------------------------------------------------- kernel argument packs
+struct BinJobs {
+  BinJob j[2];
+};
+
+struct RasterArgs {
+  BinJob job;              // raster list + how to read faces
+  const float* z;          // (., F, 3)
+  const float* feat;       // (., F, 3, D)
+  int D;
+  double eps_d;
+  int64_t* out_idx;        // (B, H, W)
+  float* out_feat;         // (B, H, W, D)
+  float* out_w;            // (B, H, W, 3) or nullptr
+  int* block_uncovered;    // (B, nkx*nky) or nullptr
+};
+
+struct RasterBwdArgs {
+  const float* grad;       // (B, H, W, D)
+  const int64_t* idx;      // (B, H, W)
+  const float* weights;    // (B, H, W, 3) or nullptr -> recompute
+  const float* img;        // (B, F, 3, 2) unscaled
+  const float* feat;       // (B, F, 3, D)
+  float* grad_img;         // (B, F, 3, 2)
+  float* grad_feat;        // (B, F, 3, D)
+  int B, F, H, W, D;
+  float mult;
+  float eps_f;
+  double eps_d;
+};
+
+struct SoftArgs {
+  BinJob job;              // soft list + how to read faces (mult, margin, prescaled, boxes)
+  const int64_t* sel;      // (B, H, W)
+  float sigmainv;
+  int K;
+  float* mask;             // (B, H, W) forward output
+  float* prob;             // dense (B, H, W, K) or nullptr
+  int64_t* cidx;
+  uint8_t* type;
+  const float* grad_mask;  // backward inputs
+  const float* mask_in;
+  float* grad_img;         // (B, F, 3, 2) accumulated, unscaled coordinates
+};
+
+struct SoftDenseBwdArgs {
+  const float* grad_mask;
+  const float* mask;
+  const int64_t* sel;
+  const float* prob;
+  const int64_t* cidx;
+  const uint8_t* type;
+  const float* img;  // (B, F, 3, 2) scaled
+  float* grad_img;
+  int B, F, H, W, K;
+  float sigmainv, mult;
+};
+
+enum { SOFT_FWD = 0, SOFT_FWD_DENSE = 1, SOFT_BWD = 2 };
+
+cudaError_t launch_binning_count(const BinJobs&, int njobs, const Plan&, cudaStream_t);
+cudaError_t launch_binning_fill(const BinJobs&, int njobs, const Plan&, cudaStream_t);
+cudaError_t launch_raster_forward(const RasterArgs&, const Plan&, cudaStream_t);
+cudaError_t launch_raster_backward(const RasterBwdArgs&, cudaStream_t);
+cudaError_t launch_softmask(const SoftArgs&, int mode, const Plan&, cudaStream_t);
+cudaError_t launch_softmask_dense_backward(const SoftDenseBwdArgs&, cudaStream_t);
+
+// ------------------------------------------------------------------------ pixel grid
+struct Grid {
+  float xs, ys;        // fl(mult / W), fl(mult / H)       (rasterization_cuda.cu:85-86)
+  float inv_xs, inv_ys;
+  int W, H;
+};
+
+__host__ __device__ inline Grid make_grid(float mult, int W, int H) {
+  Grid g;
+  g.W = W;
+  g.H = H;
+#ifdef __CUDA_ARCH__
+  g.xs = __fdiv_rn(mult, (float)W);
+  g.ys = __fdiv_rn(mult, (float)H);
+#else
+  g.xs = mult / (float)W;
+  g.ys = mult / (float)H;
+#endif
+  g.inv_xs = 1.0f / g.xs;
+  g.inv_ys = 1.0f / g.ys;
+  return g;
+}
+
+__device__ __forceinline__ float pix_x(const Grid& g, int ix) {
+  return __fmul_rn(g.xs, (float)(2 * ix + 1 - g.W));
+}
+__device__ __forceinline__ float pix_y(const Grid& g, int iy) {
+  return __fmul_rn(g.ys, (float)(g.H - 2 * iy - 1));
+}
+
+// Conservative pixel range [x_lo, x_hi] x [y_lo, y_hi] (clamped to the image) of the
+// pixel centres that can satisfy  xmin <= x0 < xmax && ymin <= y0 < ymax  (the
+// reference's half-open test, rasterization_cuda.cu:115).  One pixel of slack on every
+// side absorbs the rounding of this estimate; the exact float test is redone per pixel.
+// Returns false when the range is empty.
+__device__ __forceinline__ bool pixel_range(const Grid& g, float xmin, float ymin, float xmax,
+                                            float ymax, int& x_lo, int& x_hi, int& y_lo,
+                                            int& y_hi) {
+  if (!(xmin < xmax) || !(ymin < ymax)) return false;  // also rejects NaN boxes
+  const float Wf = (float)(g.W - 1), Hf = (float)(g.H - 1);
+  float fx_lo = (xmin * g.inv_xs + Wf) * 0.5f;
+  float fx_hi = (xmax * g.inv_xs + Wf) * 0.5f;
+  float fy_lo = (Hf - ymax * g.inv_ys) * 0.5f;  // y grows downwards in pixel rows
+  float fy_hi = (Hf - ymin * g.inv_ys) * 0.5f;
+  fx_lo = fminf(fmaxf(fx_lo, -4.f), Wf + 4.f);
+  fx_hi = fminf(fmaxf(fx_hi, -4.f), Wf + 4.f);
+  fy_lo = fminf(fmaxf(fy_lo, -4.f), Hf + 4.f);
+  fy_hi = fminf(fmaxf(fy_hi, -4.f), Hf + 4.f);
+  x_lo = max((int)floorf(fx_lo) - 1, 0);
+  x_hi = min((int)ceilf(fx_hi) + 1, g.W - 1);
+  y_lo = max((int)floorf(fy_lo) - 1, 0);
+  y_hi = min((int)ceilf(fy_hi) + 1, g.H - 1);
+  return x_lo <= x_hi && y_lo <= y_hi;
+}
+
+// ----------------------------------------------------------------------- face records
+struct Face2D {
+  float ax, ay, bx, by, cx, cy;     // scaled image coordinates
+  float xmin, ymin, xmax, ymax;     // (possibly enlarged) box
+};
+
+// Loads face `f` of view `b` for a binning job / consumer: scales (fl(v * mult) as torch
+// does at rasterization.py:337 / dibr.py:32) and builds the box (rasterization.py:342-344,
+// dibr.py:34-39) unless explicit boxes were given.  Returns false for faces that are not
+// part of the list (invalid, outside the packed range, or non-finite coordinates).
+__device__ __forceinline__ bool load_face2d(const BinJob& j, int b, int f, Face2D& o) {
+  if (j.first) {
+    if (f < (int)j.first[b] || f >= (int)j.first[b + 1]) return false;
+  }
+  const long long gi = (long long)b * j.view_stride + f;
+  if (j.valid && !j.valid[(long long)b * j.view_stride + f]) return false;
+  if (j.normal_z && !(j.normal_z[gi] >= 0.f)) return false;
+  const float2* p = reinterpret_cast<const float2*>(j.img + gi * 6);
+  float2 a = __ldg(p), bb = __ldg(p + 1), c = __ldg(p + 2);
+  if (!j.prescaled) {
+    a.x = __fmul_rn(a.x, j.mult); a.y = __fmul_rn(a.y, j.mult);
+    bb.x = __fmul_rn(bb.x, j.mult); bb.y = __fmul_rn(bb.y, j.mult);
+    c.x = __fmul_rn(c.x, j.mult); c.y = __fmul_rn(c.y, j.mult);
+  }
+  o.ax = a.x; o.ay = a.y; o.bx = bb.x; o.by = bb.y; o.cx = c.x; o.cy = c.y;
+  if (j.bbox) {
+    const float4 q = __ldg(reinterpret_cast<const float4*>(j.bbox + gi * 4));
+    o.xmin = q.x; o.ymin = q.y; o.xmax = q.z; o.ymax = q.w;
+  } else {
+    o.xmin = __fsub_rn(fminf(fminf(a.x, bb.x), c.x), j.margin);
+    o.ymin = __fsub_rn(fminf(fminf(a.y, bb.y), c.y), j.margin);
+    o.xmax = __fadd_rn(fmaxf(fmaxf(a.x, bb.x), c.x), j.margin);
+    o.ymax = __fadd_rn(fmaxf(fmaxf(a.y, bb.y), c.y), j.margin);
+  }
+  const float s = a.x + a.y + bb.x + bb.y + c.x + c.y;
+  return isfinite(s);
+}
+
+// -------------------------------------------------- exact rasterizer test (see header)
+// Returns true when pixel (x0, y0) is inside the face by the reference's rule
+// (none of the three normalised weights < 0, rasterization_cuda.cu:148).
+__device__ __forceinline__ bool raster_weights(float x0, float y0, float ax, float ay, float bx,
+                                               float by, float cx, float cy, double eps_d,
+                                               float& w0, float& w1, float& w2) {
+  const float a_ex = __fsub_rn(ax, x0), a_ey = __fsub_rn(ay, y0);
+  const float b_ex = __fsub_rn(bx, x0), b_ey = __fsub_rn(by, y0);
+  const float c_ex = __fsub_rn(cx, x0), c_ey = __fsub_rn(cy, y0);
+  w0 = __fmaf_rn(b_ex, c_ey, -__fmul_rn(b_ey, c_ex));
+  w1 = __fmaf_rn(c_ex, a_ey, -__fmul_rn(c_ey, a_ex));
+  w2 = __fmaf_rn(a_ex, b_ey, -__fmul_rn(a_ey, b_ex));
+  float norm = __fadd_rn(__fadd_rn(w0, w1), w2);
+  norm = __double2float_rn(__dadd_rn((double)norm, copysign(eps_d, (double)norm)));
+  w0 = __fdiv_rn(w0, norm);
+  w1 = __fdiv_rn(w1, norm);
+  w2 = __fdiv_rn(w2, norm);
+  return !(w0 < 0.f || w1 < 0.f || w2 < 0.f);
+}
+
+__device__ __forceinline__ float raster_depth(float w0, float w1, float w2, float az, float bz,
+                                              float cz) {
+  return __fmaf_rn(w2, cz, __fmaf_rn(w0, az, __fmul_rn(w1, bz)));
+}
+
+// Depth key: larger wins.  High word = order-preserving map of z0 (after -0 -> +0), low
+// word = ~face index, so that on equal depth the LOWEST face index wins exactly as the
+// reference's ascending scan with a strict '>' does (rasterization_cuda.cu:162).
+// z0 = -inf can never beat the initial max_z0 = -inf there, and NaN depths are not
+// supported: both yield key 0 (= empty).
+__device__ __forceinline__ unsigned long long depth_key(float z0, int face) {
+  if (!(z0 > -INFINITY)) return 0ull;
+  z0 = __fadd_rn(z0, 0.0f);  // -0.0 -> +0.0
+  const unsigned u = __float_as_uint(z0);
+  const unsigned ord = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+  return ((unsigned long long)ord << 32) | (unsigned)(~(unsigned)face);
+}
+__device__ __forceinline__ int key_face(unsigned long long key) {
+  return (int)(~(unsigned)(key & 0xffffffffull));
+}
+
+__device__ __forceinline__ void smem_max64(unsigned long long* addr, unsigned long long key) {
+  unsigned long long old = *addr;
+  while (key > old) {
+    const unsigned long long assumed = old;
+    old = atomicCAS(addr, assumed, key);
+    if (old == assumed) break;
+  }
+}
+
+// ------------------------------------------------------------------------------ misc
+__device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
+__device__ __forceinline__ unsigned lanemask_lt() {
+  unsigned m;
+  asm("mov.u32 %0, %%lanemask_lt;" : "=r"(m));
+  return m;
+}
+
+}  // namespace dibr

@@ -1,0 +1,193 @@
+"""kaolin.render.mesh.dibr_soft_mask / dibr_rasterization on B200.
+
+Same public signatures and defaults as kaolin/render/mesh/dibr.py:75-209.  The fast path
+keeps no per-pixel face lists between forward and backward (the reference saves
+13*knum bytes per pixel, dibr.py:51-54): the backward re-walks the binned face lists left
+in the workspace by the forward.
+"""
+import numpy as np
+import torch
+from torch.autograd import Function
+
+from ... import _lib, _workspace
+from .rasterization import _prep, _ptr, _stream, rasterize
+
+__all__ = ["dibr_soft_mask", "dibr_rasterization"]
+
+
+def _margin(boxlen, multiplier):
+    # dibr.py:37-38: the Python product boxlen * multiplier (double) becomes a float32
+    # scalar when subtracted from / added to the float32 box corners
+    return float(np.float32(boxlen * multiplier))
+
+
+class DibrSoftMaskB200(Function):
+    """Drop-in for DibrSoftMaskCuda (dibr.py:27-73)."""
+
+    @staticmethod
+    def forward(ctx, face_vertices_image, selected_face_idx, sigmainv, boxlen, knum, multiplier):
+        img = _prep(face_vertices_image, "face_vertices_image")
+        sel = _prep(selected_face_idx, "selected_face_idx", torch.long)
+        B, F = img.shape[:2]
+        if img.shape != (B, F, 3, 2) or sel.dim() != 3 or sel.shape[0] != B:
+            raise RuntimeError("dibr_soft_mask: expected face_vertices_image (B,F,3,2) and "
+                               "selected_face_idx (B,H,W)")
+        if sel.device != img.device:
+            raise RuntimeError("dibr_soft_mask: all tensors must be on the same GPU")
+        H, W = sel.shape[1:]
+        dev = img.device
+        mask = torch.empty((B, H, W), dtype=torch.float32, device=dev)
+        margin = _margin(boxlen, multiplier)
+        lib = _lib.lib()
+        with torch.cuda.device(dev):
+            st = _stream(dev)
+
+            def call(ws, ws_bytes, cap_r, cap_s, needed):
+                return lib.dibr_softmask_fwd(
+                    B, F, H, W, _ptr(img), 0, None, _ptr(sel), float(sigmainv), margin, int(knum),
+                    float(multiplier), _ptr(mask), None, None, None, ws, ws_bytes, cap_r, cap_s,
+                    needed, st)
+
+            ws, cap_r, cap_s = _workspace.run("soft", dev, B, F, H, W, False, True, call)
+        ctx.save_for_backward(img, sel, mask, ws)
+        ctx.args = (float(sigmainv), margin, int(knum), float(multiplier), cap_r, cap_s)
+        return mask
+
+    @staticmethod
+    def backward(ctx, grad_soft_mask):
+        img, sel, mask, ws = ctx.saved_tensors
+        sigmainv, margin, knum, multiplier, cap_r, cap_s = ctx.args
+        B, F = img.shape[:2]
+        H, W = sel.shape[1:]
+        grad = _prep(grad_soft_mask, "grad_soft_mask")
+        grad_img = torch.zeros_like(img)
+        with torch.cuda.device(img.device):
+            rc = _lib.lib().dibr_softmask_bwd(
+                B, F, H, W, _ptr(img), 0, None, _ptr(sel), sigmainv, margin, knum, multiplier,
+                _ptr(grad), _ptr(mask), _ptr(grad_img), _ptr(ws), ws.numel(), cap_r, cap_s,
+                _stream(img.device))
+        _lib.check(rc, "dibr_softmask_bwd")
+        return grad_img, None, None, None, None, None
+
+
+def dibr_soft_mask(face_vertices_image, selected_face_idx,
+                   sigmainv=7000, boxlen=0.02, knum=30, multiplier=1000.):
+    r"""Soft silhouette mask of DIB-R (see kaolin/render/mesh/dibr.py:77-115).
+
+    Args:
+        face_vertices_image (torch.Tensor): (batch_size, num_faces, 3, 2), in [-1, 1].
+        selected_face_idx (torch.LongTensor): (batch_size, height, width), from rasterize.
+        sigmainv (float): smoothness term, the higher the sharper. Default: 7000.
+        boxlen (float): margin over the face bounding boxes. Default: 0.02.
+        knum (int): maximum number of faces that can influence one pixel. Default: 30.
+        multiplier (float): internal coordinate multiplier. Default: 1000.
+
+    Returns:
+        (torch.FloatTensor): the soft mask, of shape (batch_size, height, width).
+    """
+    return DibrSoftMaskB200.apply(face_vertices_image, selected_face_idx, sigmainv, boxlen,
+                                  knum, multiplier)
+
+
+class DibrRasterizationB200(Function):
+    """rasterize(valid = normal_z >= 0) + dibr_soft_mask fused: one binning pass feeds both
+    kernels, and one backward accumulates both gradient paths into the same buffer."""
+
+    @staticmethod
+    def forward(ctx, height, width, face_vertices_z, face_vertices_image, face_features,
+                face_normals_z, sigmainv, boxlen, knum, multiplier, eps):
+        z = _prep(face_vertices_z, "face_vertices_z")
+        img = _prep(face_vertices_image, "face_vertices_image")
+        feat = _prep(face_features, "face_features")
+        nz = _prep(face_normals_z, "face_normals_z")
+        B, F = z.shape[:2]
+        D = feat.shape[-1]
+        if (img.shape != (B, F, 3, 2) or z.shape != (B, F, 3) or feat.shape != (B, F, 3, D)
+                or nz.shape != (B, F)):
+            raise RuntimeError("dibr_rasterization: inconsistent input shapes")
+        dev = z.device
+        if any(t.device != dev for t in (img, feat, nz)):
+            raise RuntimeError("dibr_rasterization: all tensors must be on the same GPU")
+        H, W = int(height), int(width)
+        idx = torch.empty((B, H, W), dtype=torch.long, device=dev)
+        out = torch.empty((B, H, W, D), dtype=torch.float32, device=dev)
+        mask = torch.empty((B, H, W), dtype=torch.float32, device=dev)
+        margin = _margin(boxlen, multiplier)
+        lib = _lib.lib()
+        with torch.cuda.device(dev):
+            st = _stream(dev)
+
+            def call(ws, ws_bytes, cap_r, cap_s, needed):
+                return lib.dibr_render_fwd(
+                    B, F, H, W, D, _ptr(z), _ptr(img), _ptr(feat), _ptr(nz), float(sigmainv),
+                    margin, int(knum), float(multiplier), float(eps), _ptr(idx), _ptr(out),
+                    _ptr(mask), ws, ws_bytes, cap_r, cap_s, needed, st)
+
+            ws, cap_r, cap_s = _workspace.run("render", dev, B, F, H, W, True, True, call)
+        ctx.save_for_backward(idx, img, feat, mask, ws)
+        ctx.mark_non_differentiable(idx)
+        ctx.args = (float(sigmainv), margin, int(knum), float(multiplier), float(eps), cap_r, cap_s)
+        return out, mask, idx
+
+    @staticmethod
+    def backward(ctx, grad_features, grad_soft_mask, grad_face_idx):
+        idx, img, feat, mask, ws = ctx.saved_tensors
+        sigmainv, margin, knum, multiplier, eps, cap_r, cap_s = ctx.args
+        B, F = img.shape[:2]
+        H, W = idx.shape[1:]
+        D = feat.shape[-1]
+        lib = _lib.lib()
+        grad_img = torch.zeros_like(img)
+        grad_feat = torch.zeros_like(feat)
+        with torch.cuda.device(img.device):
+            st = _stream(img.device)
+            if grad_features is not None:
+                g = _prep(grad_features, "grad_interpolated_features")
+                rc = lib.dibr_rasterize_bwd(B, F, H, W, D, _ptr(g), _ptr(idx), None, _ptr(img),
+                                            _ptr(feat), multiplier, eps, _ptr(grad_img),
+                                            _ptr(grad_feat), st)
+                _lib.check(rc, "dibr_rasterize_bwd")
+            if grad_soft_mask is not None:
+                gm = _prep(grad_soft_mask, "grad_soft_mask")
+                rc = lib.dibr_softmask_bwd(B, F, H, W, _ptr(img), 0, None, _ptr(idx), sigmainv,
+                                           margin, knum, multiplier, _ptr(gm), _ptr(mask),
+                                           _ptr(grad_img), _ptr(ws), ws.numel(), cap_r, cap_s, st)
+                _lib.check(rc, "dibr_softmask_bwd")
+        return (None, None, None, grad_img, grad_feat, None, None, None, None, None, None)
+
+
+def dibr_rasterization(height, width, face_vertices_z, face_vertices_image,
+                       face_features, face_normals_z, sigmainv=7000,
+                       boxlen=0.02, knum=30, multiplier=None, eps=None,
+                       rast_backend='cuda'):
+    r"""Fully differentiable DIB-R renderer (see kaolin/render/mesh/dibr.py:123-188).
+
+    Renders per-vertex per-face features to feature images, a soft foreground mask and a
+    face index map.  Only faces with ``face_normals_z >= 0`` are rasterized; the soft mask
+    uses all faces (dibr.py:190-208).
+
+    Returns:
+        (torch.Tensor or tuple, torch.Tensor, torch.LongTensor): features
+        (batch_size, height, width, num_features), soft mask (batch_size, height, width),
+        face index (batch_size, height, width), -1 is None.
+    """
+    if rast_backend != 'cuda':
+        # same dispatch (and the same errors) as rasterize()
+        interpolated_features, face_idx = rasterize(
+            height, width, face_vertices_z, face_vertices_image, face_features,
+            face_normals_z >= 0., multiplier, eps, rast_backend)
+    _multiplier = 1000. if multiplier is None else multiplier
+    _eps = 1e-8 if eps is None else eps
+    _face_features = torch.cat(face_features, dim=-1) \
+        if isinstance(face_features, (list, tuple)) else face_features
+    image_features, soft_mask, face_idx = DibrRasterizationB200.apply(
+        height, width, face_vertices_z, face_vertices_image, _face_features, face_normals_z,
+        sigmainv, boxlen, knum, _multiplier, _eps)
+    if isinstance(face_features, (list, tuple)):
+        _image_features = []
+        cur_idx = 0
+        for face_feature in face_features:
+            _image_features.append(image_features[..., cur_idx:cur_idx + face_feature.shape[-1]])
+            cur_idx += face_feature.shape[-1]
+        image_features = tuple(_image_features)
+    return image_features, soft_mask, face_idx

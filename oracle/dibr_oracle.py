@@ -157,8 +157,29 @@ def dibr_soft_mask_backward(grad_soft_mask, soft_mask, selected_face_idx, close_
 
 
 # ------------------------------------------------------------------ python-level ops
+class _CpuOps:
+    """The CPU oracle under the raw-op names of kaolin._C.render.mesh."""
+    packed_rasterize_forward_cuda = staticmethod(packed_rasterize_forward)
+    rasterize_backward_cuda = staticmethod(rasterize_backward)
+    dibr_soft_mask_forward_cuda = staticmethod(dibr_soft_mask_forward)
+    dibr_soft_mask_backward_cuda = staticmethod(dibr_soft_mask_backward)
+
+
+def load_ref_ops():
+    """The reference's own CUDA kernels (oracle/_ref/kaolin_ref_C.so, built by
+    oracle/build_ref.py from /root/reference): same four raw ops, GPU tensors only."""
+    import importlib.util
+    from . import build_ref
+    so = build_ref.build()
+    spec = importlib.util.spec_from_file_location("kaolin_ref_C", so)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
 def rasterize_forward(height, width, face_vertices_z, face_vertices_image, face_features,
-                      valid_faces=None, multiplier=None, eps=None, return_pair_count=False):
+                      valid_faces=None, multiplier=None, eps=None, return_pair_count=False,
+                      ops=_CpuOps):
     """RasterizeCuda.forward (rasterization.py:289-369) + the list handling and defaults
     of rasterize() (:469-481).  Returns (features, face_idx, ctx) with ctx the saved
     tensors the backward needs."""
@@ -172,29 +193,32 @@ def rasterize_forward(height, width, face_vertices_z, face_vertices_image, face_
     feat_dim = face_features.shape[-1]
     face_features = face_features.contiguous()
     face_vertices_image = face_vertices_image.contiguous()
+    device = face_vertices_z.device
     if valid_faces is None:
         valid_faces_idx = (
-            torch.arange(batch_size).reshape(-1, 1).repeat(1, num_faces).reshape(-1),
-            torch.arange(num_faces).reshape(1, -1).repeat(batch_size, 1).reshape(-1))
+            torch.arange(batch_size, device=device).reshape(-1, 1).repeat(1, num_faces).reshape(-1),
+            torch.arange(num_faces, device=device).reshape(1, -1).repeat(batch_size, 1).reshape(-1))
         v_img = face_vertices_image.reshape(batch_size * num_faces, 3, 2)
         v_z = face_vertices_z.reshape(batch_size * num_faces, 3)
         v_feat = face_features.reshape(batch_size * num_faces, 3, feat_dim)
-        num_faces_per_mesh = torch.full((batch_size,), num_faces, dtype=torch.long)
+        num_faces_per_mesh = torch.full((batch_size,), num_faces, dtype=torch.long,
+                                        device=device)
     else:
         valid_faces_idx = torch.where(valid_faces)
         v_img = face_vertices_image[valid_faces_idx[0], valid_faces_idx[1]]
         v_z = face_vertices_z[valid_faces_idx[0], valid_faces_idx[1]]
         v_feat = face_features[valid_faces_idx[0], valid_faces_idx[1]]
         num_faces_per_mesh = torch.sum(valid_faces.reshape(batch_size, -1), dim=1)
-    first_idx = torch.zeros(batch_size + 1, dtype=torch.long)
+    first_idx = torch.zeros(batch_size + 1, dtype=torch.long, device=device)
     torch.cumsum(num_faces_per_mesh, dim=0, out=first_idx[1:])
     v_img = v_img * multiplier                     # :337
     points_min = torch.min(v_img, dim=1)[0]
     points_max = torch.max(v_img, dim=1)[0]
     v_bbox = torch.cat((points_min, points_max), dim=1)
-    out = packed_rasterize_forward(height, width, v_z.contiguous(), v_img.contiguous(),
-                                   v_bbox.contiguous(), v_feat.contiguous(), first_idx,
-                                   multiplier, eps, return_pair_count=return_pair_count)
+    kw = {"return_pair_count": True} if return_pair_count else {}
+    out = ops.packed_rasterize_forward_cuda(
+        height, width, v_z.contiguous(), v_img.contiguous(), v_bbox.contiguous(),
+        v_feat.contiguous(), first_idx, multiplier, eps, **kw)
     interp, sel, weights = out[:3]
     if valid_faces_idx[1].numel() > 0:
         face_idx = valid_faces_idx[1][
@@ -210,16 +234,16 @@ def rasterize_forward(height, width, face_vertices_z, face_vertices_image, face_
     return interp, face_idx, ctx
 
 
-def rasterize_backward_from_ctx(ctx, grad_interpolated_features):
+def rasterize_backward_from_ctx(ctx, grad_interpolated_features, ops=_CpuOps):
     """RasterizeCuda.backward (rasterization.py:371-388): grads for image coords and
     features only; face_vertices_z gets None."""
-    return rasterize_backward(grad_interpolated_features.contiguous(), ctx["interp"],
-                              ctx["face_idx"], ctx["weights"], ctx["face_vertices_image"],
-                              ctx["face_features"], ctx["eps"])
+    return ops.rasterize_backward_cuda(
+        grad_interpolated_features.contiguous(), ctx["interp"], ctx["face_idx"],
+        ctx["weights"], ctx["face_vertices_image"], ctx["face_features"], ctx["eps"])
 
 
 def dibr_soft_mask_forward_py(face_vertices_image, selected_face_idx, sigmainv=7000,
-                              boxlen=0.02, knum=30, multiplier=1000.):
+                              boxlen=0.02, knum=30, multiplier=1000., ops=_CpuOps):
     """DibrSoftMaskCuda.forward (dibr.py:29-55).  Returns (soft_mask, ctx)."""
     img = face_vertices_image.contiguous() * multiplier
     sel = selected_face_idx.contiguous()
@@ -227,39 +251,39 @@ def dibr_soft_mask_forward_py(face_vertices_image, selected_face_idx, sigmainv=7
     points_max = torch.max(img, dim=-2)[0]
     bbox = torch.cat([points_min - boxlen * multiplier,
                       points_max + boxlen * multiplier], dim=-1)
-    mask, prob, cidx, typ = dibr_soft_mask_forward(img, bbox.contiguous(), sel, sigmainv,
-                                                   knum, multiplier)
+    mask, prob, cidx, typ = ops.dibr_soft_mask_forward_cuda(img, bbox.contiguous(), sel,
+                                                            sigmainv, knum, multiplier)
     ctx = dict(soft_mask=mask, img=img, sel=sel, prob=prob, cidx=cidx, typ=typ,
                sigmainv=sigmainv, multiplier=multiplier)
     return mask, ctx
 
 
-def dibr_soft_mask_backward_from_ctx(ctx, grad_soft_mask):
+def dibr_soft_mask_backward_from_ctx(ctx, grad_soft_mask, ops=_CpuOps):
     """DibrSoftMaskCuda.backward (dibr.py:57-73)."""
-    return dibr_soft_mask_backward(grad_soft_mask.contiguous(), ctx["soft_mask"], ctx["sel"],
-                                   ctx["prob"], ctx["cidx"], ctx["typ"], ctx["img"],
-                                   ctx["sigmainv"], ctx["multiplier"])
+    return ops.dibr_soft_mask_backward_cuda(
+        grad_soft_mask.contiguous(), ctx["soft_mask"], ctx["sel"], ctx["prob"], ctx["cidx"],
+        ctx["typ"], ctx["img"], ctx["sigmainv"], ctx["multiplier"])
 
 
 def dibr_rasterization_forward(height, width, face_vertices_z, face_vertices_image,
                                face_features, face_normals_z, sigmainv=7000, boxlen=0.02,
-                               knum=30, multiplier=None, eps=None):
+                               knum=30, multiplier=None, eps=None, ops=_CpuOps):
     """dibr_rasterization (dibr.py:119-209).  Returns (features, soft_mask, face_idx, ctxs)."""
     interp, face_idx, rctx = rasterize_forward(height, width, face_vertices_z,
                                                face_vertices_image, face_features,
-                                               face_normals_z >= 0., multiplier, eps)
+                                               face_normals_z >= 0., multiplier, eps, ops=ops)
     _multiplier = 1000. if multiplier is None else multiplier
     mask, sctx = dibr_soft_mask_forward_py(face_vertices_image, face_idx, sigmainv, boxlen,
-                                           knum, _multiplier)
+                                           knum, _multiplier, ops=ops)
     return interp, mask, face_idx, (rctx, sctx)
 
 
-def dibr_rasterization_backward(ctxs, grad_features, grad_soft_mask):
+def dibr_rasterization_backward(ctxs, grad_features, grad_soft_mask, ops=_CpuOps):
     """Sum of the two autograd branches: returns (grad_face_vertices_image,
     grad_face_features)."""
     rctx, sctx = ctxs
-    gi, gf = rasterize_backward_from_ctx(rctx, grad_features)
-    gi2 = dibr_soft_mask_backward_from_ctx(sctx, grad_soft_mask)
+    gi, gf = rasterize_backward_from_ctx(rctx, grad_features, ops=ops)
+    gi2 = dibr_soft_mask_backward_from_ctx(sctx, grad_soft_mask, ops=ops)
     return gi + gi2, gf
 
 
