@@ -46,6 +46,10 @@ inline float fma_(float a, float b, float c) { return std::fmaf(a, b, c); }
 inline double fma_(double a, double b, double c) { return std::fma(a, b, c); }
 
 static int g_threads = 0;  // 0 = OpenMP default (all cores)
+// bench.py's bounded CPU sample: only pixel rows [g_row_lo, g_row_hi) are processed (the
+// per-pixel work is independent, so throughput in pixels/s is unaffected by the band).
+static int g_row_lo = 0, g_row_hi = 0x7fffffff;
+inline bool row_skipped(int heiidx) { return heiidx < g_row_lo || heiidx >= g_row_hi; }
 
 inline int nthreads() {
 #ifdef _OPENMP
@@ -76,6 +80,7 @@ void packed_rasterize_forward(
 #pragma omp parallel for collapse(2) schedule(dynamic, 4) num_threads(nthreads()) reduction(+ : pairs)
   for (int bidx = 0; bidx < batch_size; bidx++) {
     for (int heiidx = 0; heiidx < height; heiidx++) {
+      if (row_skipped(heiidx)) continue;
       const int first_id_faces = (int)first_idx_face_per_mesh[bidx];
       const int last_id_faces = (int)first_idx_face_per_mesh[bidx + 1];
       for (int wididx = 0; wididx < width; wididx++) {
@@ -197,6 +202,7 @@ void rasterize_backward(
       gf.assign(n_feat, 0.0);
 #pragma omp for schedule(static)
       for (int64_t pixel_idx = 0; pixel_idx < num_pixels; pixel_idx++) {
+        if (row_skipped((int)(pixel_idx / width))) continue;
         const int64_t true_pixel_idx = batch_idx * num_pixels + pixel_idx;
         const int64_t start_weight_idx = true_pixel_idx * 3;
         const int64_t start_feat_idx = true_pixel_idx * feat_dim;
@@ -328,6 +334,7 @@ void dibr_soft_mask_forward(
 #pragma omp parallel for collapse(2) schedule(dynamic, 4) num_threads(nthreads())
   for (int bidx = 0; bidx < batch_size; bidx++) {
     for (int heiidx = 0; heiidx < height; heiidx++) {
+      if (row_skipped(heiidx)) continue;
       for (int wididx = 0; wididx < width; wididx++) {
         const int64_t totalidx1 = ((int64_t)bidx * height + heiidx) * width + wididx;
         const int64_t totalidxk = totalidx1 * knum;
@@ -448,6 +455,7 @@ void dibr_soft_mask_backward(
       g.assign(n_img, 0.0);
 #pragma omp for schedule(dynamic, 4)
       for (int heiidx = 0; heiidx < height; heiidx++) {
+        if (row_skipped(heiidx)) continue;
         for (int wididx = 0; wididx < width; wididx++) {
           const int64_t totalidx1 = ((int64_t)bidx * height + heiidx) * width + wididx;
           const int64_t totalidxk = totalidx1 * knum;
@@ -554,4 +562,5 @@ ORACLE_EXPORT(f32, float)
 ORACLE_EXPORT(f64, double)
 
 extern "C" void oracle_set_threads(int n) { g_threads = n; }
+extern "C" void oracle_set_row_band(int lo, int hi) { g_row_lo = lo; g_row_hi = hi; }
 extern "C" int oracle_get_threads() { return nthreads(); }

@@ -61,6 +61,11 @@ def set_threads(n):
     lib().oracle_set_threads(int(n))
 
 
+def set_row_band(lo=0, hi=0x7fffffff):
+    """Restrict all four kernels to pixel rows [lo, hi) (bench.py's bounded CPU sample)."""
+    lib().oracle_set_row_band(int(lo), int(hi))
+
+
 def get_threads():
     return int(lib().oracle_get_threads())
 
