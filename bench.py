@@ -1,0 +1,377 @@
+#!/usr/bin/env python
+"""bench.py -- DIB-R fwd+bwd Mpixels/s (views x H x W) on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    torchrun --nproc-per-node N ... bench.py --gpus N ...
+
+A step = one pass of the hot path over one batch: dibr_rasterization forward, then the
+backward driven by fixed random cotangents on both outputs
+(loss = (features*G1).sum() + (soft_mask*G2).sum()).
+
+Workload at every N: BASELINE.json configs[1] per GPU (synthetic 69,938-face sphere with
+radial noise, 8 views, 512x512, D=3 vertex colours, sigmainv=7000 boxlen=0.02 knum=30).
+Weak scaling: rank r renders views [8r, 8r+8) of an 8N-view job over the shared mesh; for
+N > 1 the step adds the path's only exchange, a NCCL SUM all-reduce of the shared mesh's
+vertex-position/feature gradients (after the local face->vertex scatter-add).
+
+Prints ONE JSON line (rank 0).  `value` = device-resident throughput (CUDA events, max
+over ranks, L2 flushed between steps outside the timed spans); `e2e` = the same metric
+through the public API from pinned HOST buffers (H2D of the step's inputs and D2H of its
+loss inside the timed region); `roofline` = dominant kernel vs the measured HBM peak;
+`cpu_baseline` = the CPU oracle (a port of the reference kernels; the reference has no CPU
+implementation of this path) on a bounded sample, rank 0, N = 1 only.
+
+--impl reference: times that CPU port with all host threads on the same config
+(each step = a 64-row band of one view; throughput in pixels/s is band-independent).
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+CFG = "cfg2_70k_8x512"
+SIGMAINV, BOXLEN, KNUM = 7000, 0.02, 30
+KERNELS = ["bin_count", "bin_scan", "bin_fill", "raster_fwd", "softmask_fwd", "raster_bwd",
+           "softmask_bwd", "softmask_bwd_dense"]
+METRIC = "DIB-R fwd+bwd Mpixels/s (views x H x W)"
+
+
+def algorithmic_bytes(kernel, B, F, P, D):
+    """API-level compulsory bytes each kernel touches (SURVEY 8(d) per-unit figures split
+    by kernel; DESIGN.md "Algorithmic bytes")."""
+    fv, px = B * F, B * P
+    return {
+        "bin_count": fv * (28 + 24), "bin_fill": fv * (28 + 24), "bin_scan": 0,
+        "raster_fwd": fv * (40 + 12 * D) + px * (8 + 4 * D),
+        "softmask_fwd": fv * 24 + px * 12,
+        "raster_bwd": fv * (48 + 24 * D) + px * (8 + 4 * D),
+        "softmask_bwd": fv * 48 + px * 16,
+    }.get(kernel, 0)
+
+
+def total_algorithmic_bytes(B, F, P, D):
+    return B * P * (32 + 8 * D) + B * F * (88 + 36 * D)
+
+
+def hbm_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.reasons, self.stop_flag = index, [], set(), False
+        self.max_mhz = None
+
+    def run(self):
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(
+                    ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.FIELDS,
+                     "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5)
+                p = [x.strip() for x in out.stdout.strip().split(",")]
+                self.samples.append(float(p[0]))
+                self.max_mhz = float(p[1])
+                for n, v in zip(names, p[2:]):
+                    if v.lower().startswith("active"):
+                        self.reasons.add(n)
+            except Exception:
+                pass
+            time.sleep(0.1)
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+def reference_arm(args, rank, world):
+    """The reference's path on host cores: the CPU port (the reference has no CPU code for
+    this path: rasterization.cpp:100-102)."""
+    if rank != 0:
+        return
+    import torch
+    import workloads as wl
+    from oracle import dibr_oracle as orc
+    inp = wl.make_config(CFG, views=1)
+    H, W = inp["H"], inp["W"]
+    z, img, feat, nz = (inp[k] for k in ("face_vertices_z", "face_vertices_image",
+                                         "face_features", "face_normals_z"))
+    rows = 64
+    lo = (H - rows) // 2
+    orc.set_row_band(lo, lo + rows)
+    g1 = torch.rand(1, H, W, feat.shape[-1])
+    g2 = torch.rand(1, H, W)
+
+    def step():
+        _, _, _, ctxs = orc.dibr_rasterization_forward(H, W, z, img, feat, nz, SIGMAINV, BOXLEN,
+                                                       KNUM)
+        orc.dibr_rasterization_backward(ctxs, g1, g2)
+
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = (time.perf_counter() - t0) / args.steps
+    orc.set_row_band()
+    val = rows * W / dt / 1e6
+    sample = "rows %d-%d of 1 view per step (%d px), extrapolated linearly in pixels" % (
+        lo, lo + rows, rows * W)
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": "Mpixels/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": CFG, "views_per_gpu": 8, "faces": int(z.shape[1]), "H": H, "W": W,
+                   "D": int(feat.shape[-1]), "sigmainv": SIGMAINV, "boxlen": BOXLEN, "knum": KNUM},
+        "cpu_baseline": {"value": val, "unit": "Mpixels/s", "cores": orc.get_threads(),
+                         "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "Mpixels/s", "h2d_bytes_per_step": 0,
+                "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-ref-gpu", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        return reference_arm(args, rank, world)
+
+    import torch
+    import torch.distributed as dist
+    import workloads as wl
+    import kaolin_windows_b200 as kal
+    from kaolin_windows_b200 import _lib
+
+    if args.warmup < 3:
+        args.warmup = 3
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    # ---- workload: this rank's 8 views of the 8N-view job over the shared mesh
+    views_per_gpu = wl.CONFIGS[CFG]["views"]
+    lo, hi = kal.parallel.shard_range(views_per_gpu * world, rank, world)
+    inp = wl.make_config(CFG, device=dev, views=views_per_gpu * world, view_slice=(lo, hi))
+    H, W = inp["H"], inp["W"]
+    z, img, feat, nz = (inp[k] for k in ("face_vertices_z", "face_vertices_image",
+                                         "face_features", "face_normals_z"))
+    faces = inp["faces"]
+    B, F, D = z.shape[0], z.shape[1], feat.shape[-1]
+    V = inp["vertices"].shape[1]
+    P = H * W
+    gen = torch.Generator(device=dev).manual_seed(1234 + rank)
+    g1 = torch.rand((B, H, W, D), device=dev, generator=gen)
+    g2 = torch.rand((B, H, W), device=dev, generator=gen)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def step(img_in, feat_in, z_in=z, nz_in=nz):
+        img_l = img_in.detach().requires_grad_(True)
+        feat_l = feat_in.detach().requires_grad_(True)
+        out, mask, idx = kal.render.mesh.dibr_rasterization(H, W, z_in, img_l, feat_l, nz_in,
+                                                            SIGMAINV, BOXLEN, KNUM)
+        loss = (out * g1).sum() + (mask * g2).sum()
+        loss.backward()
+        if world > 1:
+            # local face -> vertex scatter-add, then ONE flat all-reduce of the shared
+            # mesh's gradients (vertex image-plane positions per view stay local; what is
+            # shared is the per-vertex feature and the summed positional signal)
+            gv = torch.zeros((V, 2 + D), device=dev)
+            gv.index_add_(0, faces.reshape(-1),
+                          torch.cat([img_l.grad, feat_l.grad], dim=-1).sum(0).reshape(-1, 2 + D))
+            kal.parallel.allreduce_mesh_grads([gv])
+        return loss
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    for _ in range(args.warmup):
+        step(img, feat)
+    barrier()
+
+    # ---- timed: exactly K steps, one CUDA-event pair per step, L2 flushed in between
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+           for _ in range(args.steps)]
+    barrier()
+    for e0, e1 in evs:
+        flush.zero_()
+        e0.record()
+        step(img, feat)
+        e1.record()
+    barrier()
+    sampler.stop_flag = True
+    step_ms = [e0.elapsed_time(e1) for e0, e1 in evs]
+    total_ms = torch.tensor([sum(step_ms)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+    ms_per_step = float(total_ms.item()) / args.steps
+    value = world * B * P / (ms_per_step * 1e-3) / 1e6
+
+    # ---- e2e: public API from pinned host buffers, H2D of inputs + D2H of the loss per step
+    h_in = [t.detach().cpu().pin_memory() for t in (z, img, feat, nz)]
+    d_in = [torch.empty_like(t, device=dev) for t in h_in]
+    h2d = sum(t.numel() * t.element_size() for t in h_in)
+
+    def e2e_step():
+        for d, h in zip(d_in, h_in):
+            d.copy_(h, non_blocking=True)
+        return float(step(d_in[1], d_in[2], d_in[0], d_in[3]).item())   # D2H read of the loss
+
+    for _ in range(3):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        flush.zero_()
+        e2e_step()
+    torch.cuda.synchronize(dev)
+    e2e_t = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    # the flush memset runs inside this wall-clock span; measure and subtract it
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        flush.zero_()
+    torch.cuda.synchronize(dev)
+    flush_s = time.perf_counter() - t0
+    e2e_s = max(float(e2e_t.item()) - flush_s, 1e-9) / args.steps
+    e2e_val = world * B * P / e2e_s / 1e6
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- per-kernel times (CUDA events on the launching stream, a separate pass of K steps)
+    lib = _lib.lib()
+    lib.dibr_profile_begin()
+    for _ in range(args.steps):
+        flush.zero_()
+        step(img, feat)
+    cap = 64 * args.steps
+    ids = (ctypes.c_int * cap)()
+    ms = (ctypes.c_float * cap)()
+    n = lib.dibr_profile_end(ids, ms, cap)
+    per_kernel = {}
+    for i in range(n):
+        per_kernel.setdefault(KERNELS[ids[i]], []).append(ms[i])
+    kernel_ms = {k: sum(v) / len(v) for k, v in per_kernel.items()}
+    launches_per_step = n // max(args.steps, 1)
+    top = max(kernel_ms, key=kernel_ms.get)
+    peak, peak_kind = hbm_peak()
+    achieved = algorithmic_bytes(top, B, F, P, D) / (kernel_ms[top] * 1e-3) / 1e9
+    roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak,
+                "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "kernel_ms": {k: round(v, 4) for k, v in kernel_ms.items()},
+                "kernel_share_of_step": kernel_ms[top] / ms_per_step,
+                "path_achieved_gbs": total_algorithmic_bytes(B, F, P, D) / (ms_per_step * 1e-3) / 1e9,
+                "path_frac": total_algorithmic_bytes(B, F, P, D) / (ms_per_step * 1e-3) / 1e9 / peak}
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
+            roofline["traffic"] = json.load(fh).get(top)
+    except Exception:
+        pass
+
+    line = {
+        "metric": METRIC, "value": value, "unit": "Mpixels/s", "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": CFG, "views_per_gpu": B, "faces": F, "H": H, "W": W, "D": D,
+                   "sigmainv": SIGMAINV, "boxlen": BOXLEN, "knum": KNUM,
+                   "l2": "flushed between steps (256 MiB memset outside the per-step event spans)",
+                   "parallelism": "views sharded, %d per GPU" % B},
+        "clocks": sampler.summary(),
+        "e2e": {"value": e2e_val, "unit": "Mpixels/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": 8, "ms_per_step": e2e_s * 1e3},
+        "gpu_launches": launches_per_step * args.steps,
+        "roofline": roofline,
+    }
+
+    # ---- the reference's own CUDA kernels on this B200 (context, not the baseline arm)
+    if not args.no_ref_gpu and world == 1:
+        try:
+            from oracle import dibr_oracle as orc
+            ref = orc.load_ref_ops()
+            torch.cuda.synchronize(dev)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            reps = 2
+            for i in range(reps + 1):
+                if i == 1:
+                    e0.record()
+                _, _, _, ctxs = orc.dibr_rasterization_forward(H, W, z, img, feat, nz, SIGMAINV,
+                                                               BOXLEN, KNUM, ops=ref)
+                orc.dibr_rasterization_backward(ctxs, g1, g2, ops=ref)
+            e1.record()
+            torch.cuda.synchronize(dev)
+            rms = e0.elapsed_time(e1) / reps
+            line["reference_kernels_on_this_gpu"] = {
+                "ms_per_step": rms, "value": B * P / (rms * 1e-3) / 1e6, "unit": "Mpixels/s",
+                "what": "reference's unmodified CUDA kernels + torch prep, same inputs"}
+        except Exception as e:  # the strengthened checker is optional
+            line["reference_kernels_on_this_gpu"] = {"unavailable": repr(e)[:200]}
+
+    # ---- CPU baseline: the oracle port on the host cores, bounded sample
+    if not args.no_cpu_baseline and world == 1:
+        from oracle import dibr_oracle as orc
+        rows = 128
+        lo_r = (H - rows) // 2
+        orc.set_row_band(lo_r, lo_r + rows)
+        cz, cimg, cfeat, cnz = (t[:1].cpu() for t in (z, img, feat, nz))
+        cg1, cg2 = g1[:1].cpu(), g2[:1].cpu()
+        t0 = time.perf_counter()
+        reps = 0
+        while reps < 2 or (time.perf_counter() - t0 < 10.0 and reps < 50):
+            _, _, _, ctxs = orc.dibr_rasterization_forward(H, W, cz, cimg, cfeat, cnz, SIGMAINV,
+                                                           BOXLEN, KNUM)
+            orc.dibr_rasterization_backward(ctxs, cg1, cg2)
+            reps += 1
+        dt = (time.perf_counter() - t0) / reps
+        orc.set_row_band()
+        line["cpu_baseline"] = {
+            "value": rows * W / dt / 1e6, "unit": "Mpixels/s", "cores": orc.get_threads(),
+            "kind": "port",
+            "sample": "rows %d-%d of view 0 (%d px) x %d repeats, extrapolated linearly in pixels"
+                      % (lo_r, lo_r + rows, rows * W, reps)}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -64,6 +64,14 @@ extern "C" {
 DIBR_API const char* dibr_last_error(void);
 DIBR_API int dibr_version(void);
 
+/* Measurement aid (used by bench.py only): between dibr_profile_begin() and
+ * dibr_profile_end() every kernel launch of this library is bracketed by CUDA events on
+ * its launching stream.  dibr_profile_end synchronises those events and returns the number
+ * of records written: kernel_ids[i] in {0 bin_count, 1 bin_scan, 2 bin_fill, 3 raster_fwd,
+ * 4 softmask_fwd, 5 raster_bwd, 6 softmask_bwd, 7 softmask_bwd_dense}, ms[i] its duration. */
+DIBR_API int dibr_profile_begin(void);
+DIBR_API int dibr_profile_end(int* kernel_ids, float* ms, int capacity);
+
 /* Bytes of the fixed (data-independent) part of the workspace for a call over `batch`
  * views of `num_faces` faces (for the packed mode: the total number of packed faces) at
  * height x width.  Returns < 0 on invalid sizes. */

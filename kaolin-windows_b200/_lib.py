@@ -21,6 +21,8 @@ _vp, _i, _f, _i64 = _c.c_void_p, _c.c_int, _c.c_float, _c.c_int64
 SIGNATURES = {
     "dibr_last_error": (_c.c_char_p, []),
     "dibr_version": (_i, []),
+    "dibr_profile_begin": (_i, []),
+    "dibr_profile_end": (_i, [_vp, _vp, _i]),
     "dibr_workspace_fixed_bytes": (_i64, [_i, _i, _i, _i]),
     "dibr_workspace_bytes_for": (_i64, [_i, _i, _i, _i, _i64, _i64]),
     "dibr_rasterize_fwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _f, _f,

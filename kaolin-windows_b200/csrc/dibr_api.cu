@@ -4,6 +4,8 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
+#include <vector>
 
 #include "../../include/dibr_b200.h"
 #include "dibr_common.cuh"
@@ -26,6 +28,27 @@ static int fail(int code, const char* fmt, ...) {
     if (e_ != cudaSuccess)                                                           \
       return fail(DIBR_E_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e_));      \
   } while (0)
+
+// ------------------------------------------------------------- per-kernel profiling
+struct ProfRec { int id; cudaEvent_t e0, e1; };
+static bool g_prof_on = false;
+static std::vector<ProfRec> g_prof;
+static std::mutex g_prof_mu;
+
+void prof_begin(int id, cudaStream_t st) {
+  if (!g_prof_on) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  ProfRec r;
+  r.id = id;
+  if (cudaEventCreate(&r.e0) != cudaSuccess || cudaEventCreate(&r.e1) != cudaSuccess) return;
+  cudaEventRecord(r.e0, st);
+  g_prof.push_back(r);
+}
+void prof_end(cudaStream_t st) {
+  if (!g_prof_on) return;
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  if (!g_prof.empty()) cudaEventRecord(g_prof.back().e1, st);
+}
 
 static inline int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
 
@@ -139,6 +162,33 @@ using namespace dibr;
 
 extern "C" const char* dibr_last_error(void) { return g_err; }
 extern "C" int dibr_version(void) { return 100; }
+
+extern "C" int dibr_profile_begin(void) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  for (auto& r : g_prof) { cudaEventDestroy(r.e0); cudaEventDestroy(r.e1); }
+  g_prof.clear();
+  g_prof_on = true;
+  return DIBR_OK;
+}
+
+extern "C" int dibr_profile_end(int* kernel_ids, float* ms, int capacity) {
+  std::lock_guard<std::mutex> lk(g_prof_mu);
+  g_prof_on = false;
+  int n = 0;
+  for (auto& r : g_prof) {
+    float t = 0.f;
+    if (cudaEventSynchronize(r.e1) == cudaSuccess &&
+        cudaEventElapsedTime(&t, r.e0, r.e1) == cudaSuccess && n < capacity) {
+      if (kernel_ids) kernel_ids[n] = r.id;
+      if (ms) ms[n] = t;
+      n++;
+    }
+    cudaEventDestroy(r.e0);
+    cudaEventDestroy(r.e1);
+  }
+  g_prof.clear();
+  return n;
+}
 
 extern "C" int64_t dibr_workspace_fixed_bytes(int B, int F, int H, int W) {
   Plan p;

@@ -162,17 +162,23 @@ __global__ void __launch_bounds__(256) bin_scan_kernel(const BinJobs jobs, const
 cudaError_t launch_binning_count(const BinJobs& jobs, int njobs, const Plan& p, cudaStream_t st) {
   const size_t smem = (size_t)kBinWarps * p.NB * sizeof(int);
   dim3 grid((p.nchunks + kBinWarps - 1) / kBinWarps, p.B, njobs);
+  prof_begin(K_BIN_COUNT, st);
   bin_walk_kernel<false><<<grid, kBinWarps * 32, smem, st>>>(jobs, p);
+  prof_end(st);
   const long long nrows = (long long)p.B * p.NB;
   dim3 grid2((unsigned)((nrows + 7) / 8), 1, njobs);
+  prof_begin(K_BIN_SCAN, st);
   bin_scan_kernel<<<grid2, 256, 0, st>>>(jobs, p);
+  prof_end(st);
   return cudaGetLastError();
 }
 
 cudaError_t launch_binning_fill(const BinJobs& jobs, int njobs, const Plan& p, cudaStream_t st) {
   const size_t smem = (size_t)kBinWarps * p.NB * sizeof(int);
   dim3 grid((p.nchunks + kBinWarps - 1) / kBinWarps, p.B, njobs);
+  prof_begin(K_BIN_FILL, st);
   bin_walk_kernel<true><<<grid, kBinWarps * 32, smem, st>>>(jobs, p);
+  prof_end(st);
   return cudaGetLastError();
 }
 

@@ -121,6 +121,13 @@ struct SoftDenseBwdArgs {
 
 enum { SOFT_FWD = 0, SOFT_FWD_DENSE = 1, SOFT_BWD = 2 };
 
+// Optional per-kernel timing (dibr_profile_begin/end in the C ABI): CUDA events recorded on
+// the launching stream right before and after a kernel.  No-ops unless enabled.
+enum { K_BIN_COUNT = 0, K_BIN_SCAN, K_BIN_FILL, K_RASTER_FWD, K_SOFT_FWD, K_RASTER_BWD,
+       K_SOFT_BWD, K_SOFT_BWD_DENSE, K_NUM };
+void prof_begin(int kernel_id, cudaStream_t st);
+void prof_end(cudaStream_t st);
+
 cudaError_t launch_binning_count(const BinJobs&, int njobs, const Plan&, cudaStream_t);
 cudaError_t launch_binning_fill(const BinJobs&, int njobs, const Plan&, cudaStream_t);
 cudaError_t launch_raster_forward(const RasterArgs&, const Plan&, cudaStream_t);

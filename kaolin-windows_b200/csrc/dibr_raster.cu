@@ -161,6 +161,7 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
 cudaError_t launch_raster_forward(const RasterArgs& a, const Plan& p, cudaStream_t st) {
   dim3 grid(p.nkx, p.nky, p.B);
   const size_t big = sizeof(BigFace) * kRasterThreads;
+  prof_begin(K_RASTER_FWD, st);
   if (p.blk_log2 == 5) {
     raster_forward_kernel<5><<<grid, kRasterThreads, 8 * 32 * 32 + big, st>>>(a, p);
   } else {
@@ -174,6 +175,7 @@ cudaError_t launch_raster_forward(const RasterArgs& a, const Plan& p, cudaStream
     }
     raster_forward_kernel<6><<<grid, kRasterThreads, smem, st>>>(a, p);
   }
+  prof_end(st);
   return cudaGetLastError();
 }
 
@@ -307,12 +309,14 @@ __global__ void __launch_bounds__(256) raster_backward_kernel(const RasterBwdArg
 
 cudaError_t launch_raster_backward(const RasterBwdArgs& a, cudaStream_t st) {
   dim3 grid((a.W + 15) / 16, (a.H + 15) / 16, a.B);
+  prof_begin(K_RASTER_BWD, st);
   switch (a.D >= 4 ? 4 : a.D) {
     case 1: raster_backward_kernel<1><<<grid, 256, 0, st>>>(a); break;
     case 2: raster_backward_kernel<2><<<grid, 256, 0, st>>>(a); break;
     case 3: raster_backward_kernel<3><<<grid, 256, 0, st>>>(a); break;
     default: raster_backward_kernel<4><<<grid, 256, 0, st>>>(a); break;
   }
+  prof_end(st);
   return cudaGetLastError();
 }
 

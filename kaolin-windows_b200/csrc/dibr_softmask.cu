@@ -333,10 +333,12 @@ __global__ void __launch_bounds__(256) softmask_dense_backward_kernel(const Soft
 template <int MODE>
 static cudaError_t launch_soft_mode(const SoftArgs& a, const Plan& p, cudaStream_t st) {
   dim3 grid(p.nkx, p.nky, p.B);
+  prof_begin(MODE == SOFT_BWD ? K_SOFT_BWD : K_SOFT_FWD, st);
   if (p.blk_log2 == 5)
     softmask_kernel<5, MODE><<<grid, 128, 0, st>>>(a, p);
   else
     softmask_kernel<6, MODE><<<grid, 512, 0, st>>>(a, p);
+  prof_end(st);
   return cudaGetLastError();
 }
 
@@ -352,7 +354,9 @@ cudaError_t launch_softmask_dense_backward(const SoftDenseBwdArgs& a, cudaStream
   const long long npix = (long long)a.B * a.H * a.W;
   if (npix == 0) return cudaSuccess;
   const int blocks = (int)min((npix + 255) / 256, (long long)148 * 16);
+  prof_begin(K_SOFT_BWD_DENSE, st);
   softmask_dense_backward_kernel<<<blocks, 256, 0, st>>>(a);
+  prof_end(st);
   return cudaGetLastError();
 }
 
