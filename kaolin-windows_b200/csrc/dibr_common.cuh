@@ -167,14 +167,18 @@ __device__ __forceinline__ float pix_y(const Grid& g, int iy) {
 
 // Conservative pixel range [x_lo, x_hi] x [y_lo, y_hi] (clamped to the image) of the
 // pixel centres that can satisfy  xmin <= x0 < xmax && ymin <= y0 < ymax  (the
-// reference's half-open test, rasterization_cuda.cu:115).  One pixel of slack on every
-// side absorbs the rounding of this estimate; the exact float test is redone per pixel.
+// reference's half-open test, rasterization_cuda.cu:115).  In real arithmetic
+// x0(ix) >= xmin  <=>  ix >= fx_lo = (xmin / xs + W - 1) / 2   and   x0(ix) < xmax  <=>
+// ix < fx_hi; the float evaluation of fx is off by < W * 4e-7 pixels for on-screen boxes
+// (three roundings of magnitudes <= 2W), so a slack of W * 1e-6 + 1e-3 pixels makes the
+// range a superset.  The exact float test is redone per pixel by the consumers.
 // Returns false when the range is empty.
 __device__ __forceinline__ bool pixel_range(const Grid& g, float xmin, float ymin, float xmax,
                                             float ymax, int& x_lo, int& x_hi, int& y_lo,
                                             int& y_hi) {
   if (!(xmin < xmax) || !(ymin < ymax)) return false;  // also rejects NaN boxes
   const float Wf = (float)(g.W - 1), Hf = (float)(g.H - 1);
+  const float dx = (float)g.W * 1e-6f + 1e-3f, dy = (float)g.H * 1e-6f + 1e-3f;
   float fx_lo = (xmin * g.inv_xs + Wf) * 0.5f;
   float fx_hi = (xmax * g.inv_xs + Wf) * 0.5f;
   float fy_lo = (Hf - ymax * g.inv_ys) * 0.5f;  // y grows downwards in pixel rows
@@ -183,10 +187,13 @@ __device__ __forceinline__ bool pixel_range(const Grid& g, float xmin, float ymi
   fx_hi = fminf(fmaxf(fx_hi, -4.f), Wf + 4.f);
   fy_lo = fminf(fmaxf(fy_lo, -4.f), Hf + 4.f);
   fy_hi = fminf(fmaxf(fy_hi, -4.f), Hf + 4.f);
-  x_lo = max((int)floorf(fx_lo) - 1, 0);
-  x_hi = min((int)ceilf(fx_hi) + 1, g.W - 1);
-  y_lo = max((int)floorf(fy_lo) - 1, 0);
-  y_hi = min((int)ceilf(fy_hi) + 1, g.H - 1);
+  // x: xmin <= x0 < xmax  ->  ix in [ceil(fx_lo), ceil(fx_hi) - 1]
+  x_lo = max((int)ceilf(fx_lo - dx), 0);
+  x_hi = min((int)ceilf(fx_hi + dx) - 1, g.W - 1);
+  // y: y0 = ys * (H - 2 iy - 1) decreases with iy:  y0 < ymax <=> iy > fy_lo,
+  //    y0 >= ymin <=> iy <= fy_hi  ->  iy in [floor(fy_lo) + 1, floor(fy_hi)]
+  y_lo = max((int)floorf(fy_lo - dy) + 1, 0);
+  y_hi = min((int)floorf(fy_hi + dy), g.H - 1);
   return x_lo <= x_hi && y_lo <= y_hi;
 }
 

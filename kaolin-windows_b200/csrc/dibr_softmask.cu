@@ -32,9 +32,21 @@ namespace dibr {
 
 constexpr int kSoftChunk = 256;
 
-// prob and nearest-feature id (0-2 edge, 3-5 vertex) of one (pixel, face) pair.
-__device__ __forceinline__ void soft_eval(float x0, float y0, const float (&X)[6], float four_mm,
-                                          float sigmainv, float mult, float& prob, int& edgeid) {
+// Correctly rounded double quotient a / b from the correctly rounded reciprocal
+// inv = RN(1 / b) (Markstein): q0 = RN(a * inv), r = a - b * q0 (exact, FMA),
+// q = RN(q0 + r * inv).  Three FP64 ops instead of a ~25-instruction division; the
+// reciprocal is taken once per face edge when the face is staged.
+__device__ __forceinline__ double div_by(double a, double b, double inv) {
+  const double q0 = __dmul_rn(a, inv);
+  const double r = __fma_rn(-b, q0, a);
+  return __fma_rn(r, inv, q0);
+}
+
+// prob and nearest-feature id (0-2 edge, 3-5 vertex) of one (pixel, face) pair
+// (dibr_soft_mask_cuda.cu:103-163).  inv[i] = RN(1 / ((double)down_i + EPS)).
+__device__ __forceinline__ void soft_eval(float x0, float y0, const float (&X)[6],
+                                          const double (&inv)[3], float four_mm, float sigmainv,
+                                          float mult, float& prob, int& edgeid) {
   float pdis[6];
 #pragma unroll
   for (int i = 0; i < 3; i++) {
@@ -48,14 +60,14 @@ __device__ __forceinline__ void soft_eval(float x0, float y0, const float (&X)[6
     const float x3n = __fmaf_rn(-A, C, __fmaf_rn(BB, x0, -__fmul_rn(AB, y0)));
     const float y3n = __fmaf_rn(-B, C, __fmaf_rn(AA, y0, -__fmul_rn(AB, x0)));
     const double dd = __dadd_rn((double)down, DIBR_SOFT_EPS);
-    const float x3 = __double2float_rn(__ddiv_rn((double)x3n, dd));
-    const float y3 = __double2float_rn(__ddiv_rn((double)y3n, dd));
+    const float x3 = __double2float_rn(div_by((double)x3n, dd, inv[i]));
+    const float y3 = __double2float_rn(div_by((double)y3n, dd, inv[i]));
     const float direct = __fmaf_rn(__fsub_rn(x3, x1), __fsub_rn(x3, x2),
                                    __fmul_rn(__fsub_rn(y3, y1), __fsub_rn(y3, y2)));
     if (direct > 0.f)
       pdis[i] = four_mm;
     else
-      pdis[i] = __double2float_rn(__ddiv_rn((double)__fmul_rn(up, up), dd));
+      pdis[i] = __double2float_rn(div_by((double)__fmul_rn(up, up), dd, inv[i]));
     const float dx = __fsub_rn(x0, x1), dy = __fsub_rn(y0, y1);
     pdis[i + 3] = __fmaf_rn(dx, dx, __fmul_rn(dy, dy));
   }
@@ -68,6 +80,13 @@ __device__ __forceinline__ void soft_eval(float x0, float y0, const float (&X)[6
   prob = expf(-z);
 }
 
+// RN(1 / ((double)(A*A + B*B) + EPS)) of edge i of a staged face.
+__device__ __forceinline__ double edge_inv(float x1, float y1, float x2, float y2) {
+  const float A = __fsub_rn(y2, y1), B = __fsub_rn(x1, x2);
+  const float down = __fadd_rn(__fmul_rn(A, A), __fmul_rn(B, B));
+  return __drcp_rn(__dadd_rn((double)down, DIBR_SOFT_EPS));
+}
+
 __device__ __forceinline__ float pick3(int v, float a, float b, float c) {
   return v == 0 ? a : (v == 1 ? b : c);
 }
@@ -76,7 +95,7 @@ __device__ __forceinline__ float pick3(int v, float a, float b, float c) {
 // six UNscaled coordinates, added into g[6] (register array: static indices only).
 __device__ __forceinline__ void soft_grad(float x0, float y0, const float (&X)[6], int edgeid,
                                           float prob, float allprob, float dLdp, float sigmainv,
-                                          float mult, float (&g)[6]) {
+                                          float mult, double inv_e, float (&g)[6]) {
   const float dLdz = (float)(-1.0 * sigmainv * dLdp * (1.0 - allprob) /
                              (1.0 - prob + DIBR_SOFT_EPS) * prob);
   int v1, v2 = -1;
@@ -96,10 +115,11 @@ __device__ __forceinline__ void soft_grad(float x0, float y0, const float (&X)[6
     const float A = y2 - y1, B = x1 - x2, C = x2 * y1 - x1 * y2;
     const float up = A * x0 + B * y0 + C;
     const float down = A * A + B * B;
-    const float dissquare = up * up / (down + DIBR_SOFT_EPS);
-    const float dzdA = 2 * (x0 * up - dissquare * A) / (down + DIBR_SOFT_EPS);
-    const float dzdB = 2 * (y0 * up - dissquare * B) / (down + DIBR_SOFT_EPS);
-    const float dzdC = 2 * up / (down + DIBR_SOFT_EPS);
+    const double dd = (double)down + DIBR_SOFT_EPS;   // the four "/ (down + EPS)" below
+    const float dissquare = (float)div_by((double)(up * up), dd, inv_e);
+    const float dzdA = (float)div_by((double)(2 * (x0 * up - dissquare * A)), dd, inv_e);
+    const float dzdB = (float)div_by((double)(2 * (y0 * up - dissquare * B)), dd, inv_e);
+    const float dzdC = (float)div_by((double)(2 * up), dd, inv_e);
     const float dLdx1 = dLdz * (dzdB - y2 * dzdC);
     const float dLdy1 = dLdz * (x2 * dzdC - dzdA);
     const float dLdx2 = dLdz * (y1 * dzdC - dzdB);
@@ -116,19 +136,51 @@ __device__ __forceinline__ void soft_grad(float x0, float y0, const float (&X)[6
   }
 }
 
+// ---------------------------------------------------------------------------
+// Block kernel.  8 warps per CTA; the block's 8x4 regions are handed to warps through a
+// shared-memory queue, so warps stay busy whatever part of the block is uncovered.
+// Per (chunk of staged faces, region) a warp works in two phases:
+//   1. gather: walk the chunk in face order; 32 faces per instruction are tested against
+//      the region rectangle (__ballot_sync), survivors are tested per pixel with the
+//      reference's half-open box test and recorded in the pixel's hit segment until the
+//      pixel holds knum faces (order = ascending face index, the reference's rule);
+//   2. evaluate: the (pixel, face) pairs gathered by the whole region are dealt out
+//      evenly over the 32 lanes, whatever pixel they belong to, so the expensive
+//      distance/exp (or gradient) arithmetic runs with every lane busy; each pixel then
+//      folds its probabilities in order.
+// ---------------------------------------------------------------------------
+constexpr int kSoftWarps = 8;
+constexpr int kSoftThreads = kSoftWarps * 32;
+constexpr int kSeg = 16;  // hit-segment length per pixel between two evaluate phases
+
 template <int BLK_LOG2, int MODE>
-__global__ void __launch_bounds__((1 << (2 * (BLK_LOG2 - 4))) * 32)
+struct SoftSmem {
+  static constexpr int BLK = 1 << BLK_LOG2;
+  static constexpr int NPX = BLK * BLK;
+  static constexpr int NR = NPX / 32;
+  double inv[3][kSoftChunk];
+  float x[6][kSoftChunk];
+  float bb[4][kSoftChunk];
+  int face[kSoftChunk];
+  float ap[NPX];
+  unsigned short cnt[NPX];       // faces held; 0xffff = covered / outside the image
+  float pr[kSoftWarps][kSeg][32];
+  unsigned short hit[kSoftWarps][kSeg][32];
+  unsigned char ty[kSoftWarps][kSeg][32];
+  int off[kSoftWarps][33];
+  unsigned char ropen[NR];
+  int next;
+  float acc[MODE == SOFT_BWD ? kSoftChunk : 1][6];
+};
+
+template <int BLK_LOG2, int MODE>
+__global__ void __launch_bounds__(kSoftThreads)
 softmask_kernel(const SoftArgs a, const Plan p) {
-  constexpr int BLK = 1 << BLK_LOG2;
-  constexpr int TPB = BLK / 16;          // tiles per block row
-  constexpr int NW = TPB * TPB;          // warps = tiles
-  constexpr int NT = NW * 32;
+  using Smem = SoftSmem<BLK_LOG2, MODE>;
+  constexpr int BLK = Smem::BLK, NPX = Smem::NPX, NR = Smem::NR, RX = BLK / 8;
   constexpr int CH = kSoftChunk;
-  __shared__ float s_x[6][CH];           // scaled coordinates ax ay bx by cx cy
-  __shared__ float s_bb[4][CH];          // enlarged box
-  __shared__ int s_face[CH];
-  __shared__ unsigned short s_tl[NW][CH];  // per-warp compacted tile list (chunk slots)
-  __shared__ float s_acc[MODE == SOFT_BWD ? CH : 1][6];
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  Smem& sm = *reinterpret_cast<Smem*>(s_raw);
 
   const int tid = threadIdx.x, lane = lane_id(), warp = tid >> 5;
   const int b = blockIdx.z;
@@ -136,29 +188,24 @@ softmask_kernel(const SoftArgs a, const Plan p) {
   const Grid g = make_grid(a.job.mult, p.W, p.H);
   const float mult = a.job.mult;
   const float four_mm = __fmul_rn(__fmul_rn(mult, 4.f), mult);
-
-  // this warp's tile and this lane's pixel in each of the 8 regions
-  const int tx0 = bx0 + (warp % TPB) * 16, ty0 = by0 + (warp / TPB) * 16;
+  const int K = min(a.K, 0xfffe);
   const int lx = lane & 7, ly = lane >> 3;
-  unsigned open_bits = 0;                // bit r: pixel of region r still collects faces
-  int cnt[8];
-  float ap[8];
-#pragma unroll
-  for (int r = 0; r < 8; r++) {
-    const int ix = tx0 + (r & 1) * 8 + lx, iy = ty0 + (r >> 1) * 4 + ly;
-    cnt[r] = 0;
-    ap[r] = 1.0f;
-    if (ix < p.W && iy < p.H) {
-      const long long pix = ((long long)b * p.H + iy) * p.W + ix;
-      if (a.sel[pix] < 0) open_bits |= 1u << r;
-    }
-  }
-  const unsigned uncov_bits = open_bits;
-  if (a.K <= 0) open_bits = 0;
 
-  // tile rectangle in pixel-centre coordinates (x grows with ix, y shrinks with iy)
-  const float t_xlo = pix_x(g, tx0), t_xhi = pix_x(g, min(tx0 + 15, p.W - 1));
-  const float t_yhi = pix_y(g, ty0), t_ylo = pix_y(g, min(ty0 + 15, p.H - 1));
+  // ---- pixel state
+  for (int i = tid; i < NPX; i += kSoftThreads) {
+    const int ix = bx0 + (i & (BLK - 1)), iy = by0 + (i >> BLK_LOG2);
+    bool uncovered = false;
+    if (ix < p.W && iy < p.H) uncovered = a.sel[((long long)b * p.H + iy) * p.W + ix] < 0;
+    sm.cnt[i] = uncovered ? 0 : 0xffff;
+    sm.ap[i] = 1.0f;
+  }
+  __syncthreads();
+  for (int r = warp; r < NR; r += kSoftWarps) {
+    const int pl = (((r / RX) * 4 + ly) << BLK_LOG2) + (r % RX) * 8 + lx;
+    const bool open = (int)sm.cnt[pl] < K;
+    const unsigned m = __ballot_sync(DIBR_FULL_MASK, open);
+    if (lane == 0) sm.ropen[r] = m != 0;
+  }
 
   const int shift = p.bin_log2 - BLK_LOG2;
   const int bin = (blockIdx.y >> shift) * p.nbx + (blockIdx.x >> shift);
@@ -168,132 +215,151 @@ softmask_kernel(const SoftArgs a, const Plan p) {
   if (start + n > a.job.capacity) n = max(0ll, a.job.capacity - start);
 
   for (long long base = 0; base < n; base += CH) {
-    if (!__syncthreads_or(open_bits != 0)) break;
+    __syncthreads();
+    bool mine = false;
+    for (int r = tid; r < NR; r += kSoftThreads) mine |= sm.ropen[r] != 0;
+    if (tid == 0) sm.next = 0;
+    if (!__syncthreads_or(mine)) break;
     const int nc = (int)min((long long)CH, n - base);
-    // ---- stage the chunk (scaled coordinates + enlarged box), zero the accumulators
-    for (int t = tid; t < nc; t += NT) {
+    // ---- stage the chunk: scaled coordinates, enlarged box, edge reciprocals
+    for (int t = tid; t < nc; t += kSoftThreads) {
       const int f = a.job.list[start + base + t];
       Face2D fc;
       load_face2d(a.job, b, f, fc);
-      s_x[0][t] = fc.ax; s_x[1][t] = fc.ay; s_x[2][t] = fc.bx;
-      s_x[3][t] = fc.by; s_x[4][t] = fc.cx; s_x[5][t] = fc.cy;
-      s_bb[0][t] = fc.xmin; s_bb[1][t] = fc.ymin; s_bb[2][t] = fc.xmax; s_bb[3][t] = fc.ymax;
-      s_face[t] = f;
+      sm.x[0][t] = fc.ax; sm.x[1][t] = fc.ay; sm.x[2][t] = fc.bx;
+      sm.x[3][t] = fc.by; sm.x[4][t] = fc.cx; sm.x[5][t] = fc.cy;
+      sm.bb[0][t] = fc.xmin; sm.bb[1][t] = fc.ymin; sm.bb[2][t] = fc.xmax; sm.bb[3][t] = fc.ymax;
+      sm.inv[0][t] = edge_inv(fc.ax, fc.ay, fc.bx, fc.by);
+      sm.inv[1][t] = edge_inv(fc.bx, fc.by, fc.cx, fc.cy);
+      sm.inv[2][t] = edge_inv(fc.cx, fc.cy, fc.ax, fc.ay);
+      sm.face[t] = f;
       if (MODE == SOFT_BWD) {
 #pragma unroll
-        for (int i = 0; i < 6; i++) s_acc[t][i] = 0.f;
+        for (int i = 0; i < 6; i++) sm.acc[t][i] = 0.f;
       }
     }
     __syncthreads();
 
-    if (__any_sync(DIBR_FULL_MASK, open_bits != 0)) {
-      // ---- compact the chunk to this warp's tile, keeping the order
-      int ntl = 0;
-      for (int t0 = 0; t0 < nc; t0 += 32) {
-        const int t = t0 + lane;
-        bool hit = false;
-        if (t < nc)
-          hit = s_bb[0][t] <= t_xhi && s_bb[2][t] > t_xlo && s_bb[1][t] <= t_yhi &&
-                s_bb[3][t] > t_ylo;
-        const unsigned m = __ballot_sync(DIBR_FULL_MASK, hit);
-        if (hit) s_tl[warp][ntl + __popc(m & lanemask_lt())] = (unsigned short)t;
-        ntl += __popc(m);
-      }
-      __syncwarp();
+    while (true) {
+      int r = 0;
+      if (lane == 0) r = atomicAdd(&sm.next, 1);
+      r = __shfl_sync(DIBR_FULL_MASK, r, 0);
+      if (r >= NR) break;
+      if (!sm.ropen[r]) continue;
+      const int rx0 = bx0 + (r % RX) * 8, ry0 = by0 + (r / RX) * 4;
+      const int ix = rx0 + lx, iy = ry0 + ly;
+      const int pl = ((iy - by0) << BLK_LOG2) + (ix - bx0);
+      const float r_xlo = pix_x(g, rx0), r_xhi = pix_x(g, min(rx0 + 7, p.W - 1));
+      const float r_yhi = pix_y(g, ry0), r_ylo = pix_y(g, min(ry0 + 3, p.H - 1));
+      const float x0 = pix_x(g, ix), y0 = pix_y(g, iy);
+      const long long pix = ((long long)b * p.H + min(iy, p.H - 1)) * p.W + min(ix, p.W - 1);
+      int cnt = sm.cnt[pl];
+      float ap = sm.ap[pl];
+      bool open = cnt < K;
+      int nbuf = 0;
 
-      // ---- regions
-      for (int r = 0; r < 8; r++) {
-        if (!__any_sync(DIBR_FULL_MASK, (open_bits >> r) & 1)) continue;
-        const int ix = tx0 + (r & 1) * 8 + lx, iy = ty0 + (r >> 1) * 4 + ly;
-        const int rx0 = tx0 + (r & 1) * 8, ry0 = ty0 + (r >> 1) * 4;
-        const float r_xlo = pix_x(g, rx0), r_xhi = pix_x(g, min(rx0 + 7, p.W - 1));
-        const float r_yhi = pix_y(g, ry0), r_ylo = pix_y(g, min(ry0 + 3, p.H - 1));
-        const float x0 = pix_x(g, ix), y0 = pix_y(g, iy);
-        const long long pix = ((long long)b * p.H + min(iy, p.H - 1)) * p.W + min(ix, p.W - 1);
-        bool open = (open_bits >> r) & 1;
-        int my_cnt = 0;
-        float my_ap = 1.f;
+      // evaluate everything gathered so far for this region (all lanes call it together)
+      auto flush = [&]() {
+        int incl = nbuf;
 #pragma unroll
-        for (int rr = 0; rr < 8; rr++)
-          if (rr == r) { my_cnt = cnt[rr]; my_ap = ap[rr]; }
-        float dLdp = 0.f, apf = 0.f;
-        if (MODE == SOFT_BWD && open) { dLdp = a.grad_mask[pix]; apf = a.mask_in[pix]; }
-
-        for (int j0 = 0; j0 < ntl; j0 += 32) {
-          int slot = 0;
-          bool cand = false;
-          if (j0 + lane < ntl) {
-            slot = s_tl[warp][j0 + lane];
-            cand = s_bb[0][slot] <= r_xhi && s_bb[2][slot] > r_xlo && s_bb[1][slot] <= r_yhi &&
-                   s_bb[3][slot] > r_ylo;
-          }
-          unsigned m = __ballot_sync(DIBR_FULL_MASK, cand);
-          while (m) {
-            const int k = __ffs(m) - 1;
-            m &= m - 1;
-            const int s = __shfl_sync(DIBR_FULL_MASK, slot, k);
-            const bool in = open && !(x0 < s_bb[0][s] || x0 >= s_bb[2][s] || y0 < s_bb[1][s] ||
-                                      y0 >= s_bb[3][s]);  // :95-97
-            float gacc[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-            if (in) {
-              const float X[6] = {s_x[0][s], s_x[1][s], s_x[2][s], s_x[3][s], s_x[4][s], s_x[5][s]};
-              float prob;
-              int edgeid;
-              soft_eval(x0, y0, X, four_mm, a.sigmainv, mult, prob, edgeid);
-              if (MODE == SOFT_FWD_DENSE) {
-                const long long o = pix * a.K + my_cnt;
-                a.prob[o] = prob;
-                a.cidx[o] = s_face[s];
-                a.type[o] = (uint8_t)(edgeid + 1);
-              }
-              if (MODE == SOFT_BWD) {
-                soft_grad(x0, y0, X, edgeid, prob, apf, dLdp, a.sigmainv, mult, gacc);
-              } else {
-                my_ap = __double2float_rn(__dmul_rn((double)my_ap, __dsub_rn(1.0, (double)prob)));
-              }
-              if (++my_cnt >= a.K) open = false;  // :170-171
-            }
-            if (MODE == SOFT_BWD) {
-              if (__any_sync(DIBR_FULL_MASK, in)) {
+        for (int d = 1; d < 32; d <<= 1) {
+          const int t = __shfl_up_sync(DIBR_FULL_MASK, incl, d);
+          if (lane >= d) incl += t;
+        }
+        const int total = __shfl_sync(DIBR_FULL_MASK, incl, 31);
+        sm.off[warp][lane] = incl - nbuf;
+        if (lane == 31) sm.off[warp][32] = total;
+        __syncwarp();
+        for (int i = lane; i < total; i += 32) {
+          int l = 0;  // owner pixel: the largest l with off[l] <= i
 #pragma unroll
-                for (int i = 0; i < 6; i++) {
-                  float v = gacc[i];
+          for (int st = 16; st > 0; st >>= 1)
+            if (sm.off[warp][l + st] <= i) l += st;
+          const int j = i - sm.off[warp][l];
+          const int s = sm.hit[warp][j][l];
+          const int pix_x_i = rx0 + (l & 7), pix_y_i = ry0 + (l >> 3);
+          const float px = pix_x(g, pix_x_i), py = pix_y(g, pix_y_i);
+          const float X[6] = {sm.x[0][s], sm.x[1][s], sm.x[2][s], sm.x[3][s], sm.x[4][s], sm.x[5][s]};
+          const double inv[3] = {sm.inv[0][s], sm.inv[1][s], sm.inv[2][s]};
+          float prob;
+          int edgeid;
+          soft_eval(px, py, X, inv, four_mm, a.sigmainv, mult, prob, edgeid);
+          if (MODE == SOFT_BWD) {
+            const long long q = ((long long)b * p.H + pix_y_i) * p.W + pix_x_i;
+            float gv[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            soft_grad(px, py, X, edgeid, prob, a.mask_in[q], a.grad_mask[q], a.sigmainv, mult,
+                      edgeid < 3 ? (edgeid == 0 ? inv[0] : (edgeid == 1 ? inv[1] : inv[2])) : 0.0,
+                      gv);
 #pragma unroll
-                  for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(DIBR_FULL_MASK, v, d);
-                  if (lane == i && v != 0.f) atomicAdd(&s_acc[s][i], v);
-                }
-              }
-            }
-            if (!__any_sync(DIBR_FULL_MASK, open)) { m = 0; j0 = ntl; }
+            for (int k = 0; k < 6; k++)
+              if (gv[k] != 0.f) atomicAdd(&sm.acc[s][k], gv[k]);
+          } else {
+            sm.pr[warp][j][l] = prob;
+            sm.ty[warp][j][l] = (unsigned char)(edgeid + 1);
           }
         }
-#pragma unroll
-        for (int rr = 0; rr < 8; rr++)
-          if (rr == r) { cnt[rr] = my_cnt; ap[rr] = my_ap; }
-        if (!open) open_bits &= ~(1u << r);
+        __syncwarp();
+        if (MODE != SOFT_BWD) {
+          for (int j = 0; j < nbuf; j++) {
+            const float prob = sm.pr[warp][j][lane];
+            ap = __double2float_rn(__dmul_rn((double)ap, __dsub_rn(1.0, (double)prob)));  // :176-177
+            if (MODE == SOFT_FWD_DENSE) {
+              const long long o = pix * a.K + (cnt - nbuf + j);
+              a.prob[o] = prob;
+              a.cidx[o] = sm.face[sm.hit[warp][j][lane]];
+              a.type[o] = sm.ty[warp][j][lane];
+            }
+          }
+        }
+        nbuf = 0;
+        __syncwarp();
+      };
+
+      for (int j0 = 0; j0 < nc; j0 += 32) {
+        const int t = j0 + lane;
+        bool cand = false;
+        if (t < nc)
+          cand = sm.bb[0][t] <= r_xhi && sm.bb[2][t] > r_xlo && sm.bb[1][t] <= r_yhi &&
+                 sm.bb[3][t] > r_ylo;
+        unsigned m = __ballot_sync(DIBR_FULL_MASK, cand);
+        while (m) {
+          const int s = j0 + __ffs(m) - 1;
+          m &= m - 1;
+          const bool in = open && !(x0 < sm.bb[0][s] || x0 >= sm.bb[2][s] || y0 < sm.bb[1][s] ||
+                                    y0 >= sm.bb[3][s]);  // :95-97
+          if (in) {
+            sm.hit[warp][nbuf][lane] = (unsigned short)s;
+            nbuf++;
+            if (++cnt >= K) open = false;  // :170-171
+          }
+          if (__any_sync(DIBR_FULL_MASK, nbuf == kSeg)) flush();
+          if (!__any_sync(DIBR_FULL_MASK, open)) { m = 0; j0 = nc; }
+        }
       }
+      if (__any_sync(DIBR_FULL_MASK, nbuf > 0)) flush();
+      sm.cnt[pl] = (unsigned short)cnt;
+      sm.ap[pl] = ap;
+      const unsigned still = __ballot_sync(DIBR_FULL_MASK, open);
+      if (lane == 0) sm.ropen[r] = still != 0;
     }
-    __syncthreads();
     if (MODE == SOFT_BWD) {
-      for (int t = tid; t < nc * 6; t += NT) {
-        const float v = s_acc[t / 6][t % 6];
-        if (v != 0.f)
-          atomicAdd(a.grad_img + ((long long)b * a.job.view_stride + s_face[t / 6]) * 6 + t % 6, v);
-      }
       __syncthreads();
+      for (int t = tid; t < nc * 6; t += kSoftThreads) {
+        const float v = sm.acc[t / 6][t % 6];
+        if (v != 0.f)
+          atomicAdd(a.grad_img + ((long long)b * a.job.view_stride + sm.face[t / 6]) * 6 + t % 6, v);
+      }
     }
   }
 
   if (MODE != SOFT_BWD) {
-#pragma unroll
-    for (int r = 0; r < 8; r++) {
-      const int ix = tx0 + (r & 1) * 8 + lx, iy = ty0 + (r >> 1) * 4 + ly;
-      if (ix < p.W && iy < p.H) {
-        const long long pix = ((long long)b * p.H + iy) * p.W + ix;
-        a.mask[pix] = ((uncov_bits >> r) & 1)
-                          ? __double2float_rn(__dsub_rn(1.0, (double)ap[r]))  // :181-182
-                          : 1.0f;                                             // :68-70
-      }
+    __syncthreads();
+    for (int i = tid; i < NPX; i += kSoftThreads) {
+      const int ix = bx0 + (i & (BLK - 1)), iy = by0 + (i >> BLK_LOG2);
+      if (ix < p.W && iy < p.H)
+        a.mask[((long long)b * p.H + iy) * p.W + ix] =
+            sm.cnt[i] == 0xffff ? 1.0f                                            // :68-70
+                                : __double2float_rn(__dsub_rn(1.0, (double)sm.ap[i]));  // :181-182
     }
   }
 }
@@ -320,7 +386,14 @@ __global__ void __launch_bounds__(256) softmask_dense_backward_kernel(const Soft
       const float* ip = a.img + ((long long)b * a.F + f) * 6;
       const float X[6] = {ip[0], ip[1], ip[2], ip[3], ip[4], ip[5]};
       float gv[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      soft_grad(x0, y0, X, (int)a.type[o] - 1, a.prob[o], allprob, dLdp, a.sigmainv, a.mult, gv);
+      const int eid = (int)a.type[o] - 1;
+      double inv_e = 0.0;
+      if (eid < 3) {
+        const int v2 = (eid + 1) % 3;
+        inv_e = edge_inv(pick3(eid, X[0], X[2], X[4]), pick3(eid, X[1], X[3], X[5]),
+                         pick3(v2, X[0], X[2], X[4]), pick3(v2, X[1], X[3], X[5]));
+      }
+      soft_grad(x0, y0, X, eid, a.prob[o], allprob, dLdp, a.sigmainv, a.mult, inv_e, gv);
       float* gp = a.grad_img + ((long long)b * a.F + f) * 6;
 #pragma unroll
       for (int i = 0; i < 6; i++)
@@ -333,11 +406,29 @@ __global__ void __launch_bounds__(256) softmask_dense_backward_kernel(const Soft
 template <int MODE>
 static cudaError_t launch_soft_mode(const SoftArgs& a, const Plan& p, cudaStream_t st) {
   dim3 grid(p.nkx, p.nky, p.B);
-  prof_begin(MODE == SOFT_BWD ? K_SOFT_BWD : K_SOFT_FWD, st);
-  if (p.blk_log2 == 5)
-    softmask_kernel<5, MODE><<<grid, 128, 0, st>>>(a, p);
-  else
-    softmask_kernel<6, MODE><<<grid, 512, 0, st>>>(a, p);
+  static bool attr5 = false, attr6 = false;
+  cudaError_t e = cudaSuccess;
+  if (p.blk_log2 == 5) {
+    const int smem = (int)sizeof(SoftSmem<5, MODE>);
+    if (!attr5) {
+      e = cudaFuncSetAttribute(softmask_kernel<5, MODE>,
+                               cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      if (e != cudaSuccess) return e;
+      attr5 = true;
+    }
+    prof_begin(MODE == SOFT_BWD ? K_SOFT_BWD : K_SOFT_FWD, st);
+    softmask_kernel<5, MODE><<<grid, kSoftThreads, smem, st>>>(a, p);
+  } else {
+    const int smem = (int)sizeof(SoftSmem<6, MODE>);
+    if (!attr6) {
+      e = cudaFuncSetAttribute(softmask_kernel<6, MODE>,
+                               cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      if (e != cudaSuccess) return e;
+      attr6 = true;
+    }
+    prof_begin(MODE == SOFT_BWD ? K_SOFT_BWD : K_SOFT_FWD, st);
+    softmask_kernel<6, MODE><<<grid, kSoftThreads, smem, st>>>(a, p);
+  }
   prof_end(st);
   return cudaGetLastError();
 }
