@@ -18,25 +18,35 @@ namespace dibr {
 
 
 constexpr int kRasterThreads = 256;
-constexpr int kSmallBox = 24;  // boxes with more candidate pixels go to the warp queue
+constexpr int kRasterWarps = kRasterThreads / 32;
+constexpr int kQueue = 64;  // survivor queue entries per warp (drained 32 at a time)
 
-struct BigFace {
-  float ax, ay, bx, by, cx, cy, xmin, ymin, xmax, ymax, az, bz, cz;
-  int face, x_lo, y_lo, w, n;
+template <int BLK_LOG2>
+struct RasterSmem {
+  static constexpr int BLK = 1 << BLK_LOG2;
+  unsigned long long zbuf[BLK * BLK];
+  float x[6][kRasterThreads];   // staged faces of the current chunk (scaled coordinates)
+  float z[3][kRasterThreads];
+  int rect[kRasterThreads];     // x_lo | y_lo << 8 | (w - 1) << 16 | (h - 1) << 24, block-relative
+  int face[kRasterThreads];
+  int pre[kRasterThreads + 1];  // exclusive prefix of the candidate counts w * h
+  int wsum[kRasterWarps];
+  unsigned queue[kRasterWarps][kQueue];
+  int uncovered;
 };
 
-__device__ __forceinline__ void raster_pixel(const Grid& g, int ix, int iy, float ax, float ay,
-                                             float bx, float by, float cx, float cy, float xmin,
-                                             float ymin, float xmax, float ymax, float az,
-                                             float bz, float cz, double eps_d, int face,
-                                             unsigned long long* zbuf, int bx0, int by0,
-                                             int blk_log2) {
-  const float x0 = pix_x(g, ix), y0 = pix_y(g, iy);
-  if (x0 < xmin || x0 >= xmax || y0 < ymin || y0 >= ymax) return;  // :115
-  float w0, w1, w2;
-  if (!raster_weights(x0, y0, ax, ay, bx, by, cx, cy, eps_d, w0, w1, w2)) return;
-  const unsigned long long key = depth_key(raster_depth(w0, w1, w2, az, bz, cz), face);
-  if (key) smem_max64(&zbuf[((iy - by0) << blk_log2) + (ix - bx0)], key);
+// Sign-only rejection of a candidate before the normalisation (exactness argument in
+// DESIGN.md "Numerics"): the reference rejects when RN(w_k / norm) < 0.  norm has the sign
+// bit of n32 = (w0 + w1) + w2 and |n32| <= |norm| <= 2^100 when |n32| <= 2^99 and
+// |eps| <= 2^90, so for |w_k| >= 2^-20 with the opposite sign bit the quotient is a
+// negative NORMAL number whatever its rounding: rejected.  Everything else (zeros, tiny
+// values, NaN/Inf, huge norms) goes through the full division path.
+__device__ __forceinline__ bool surely_outside(float w0, float w1, float w2, float n32) {
+  const int sn = __float_as_int(n32);
+  const bool o0 = ((__float_as_int(w0) ^ sn) < 0) && fabsf(w0) >= 0x1p-20f;
+  const bool o1 = ((__float_as_int(w1) ^ sn) < 0) && fabsf(w1) >= 0x1p-20f;
+  const bool o2 = ((__float_as_int(w2) ^ sn) < 0) && fabsf(w2) >= 0x1p-20f;
+  return (o0 || o1 || o2) && fabsf(n32) <= 0x1p99f;
 }
 
 template <int BLK_LOG2>
@@ -44,19 +54,18 @@ __global__ void __launch_bounds__(kRasterThreads)
 raster_forward_kernel(const RasterArgs a, const Plan p) {
   constexpr int BLK = 1 << BLK_LOG2;
   extern __shared__ __align__(16) unsigned char s_raw[];
-  unsigned long long* zbuf = reinterpret_cast<unsigned long long*>(s_raw);        // BLK*BLK
-  BigFace* s_big = reinterpret_cast<BigFace*>(s_raw + sizeof(unsigned long long) * BLK * BLK);
-  __shared__ int s_nbig;
-  __shared__ int s_uncovered;
+  RasterSmem<BLK_LOG2>& sm = *reinterpret_cast<RasterSmem<BLK_LOG2>*>(s_raw);
+  unsigned long long* zbuf = sm.zbuf;
 
   const int b = blockIdx.z;
   const int bx0 = blockIdx.x << BLK_LOG2, by0 = blockIdx.y << BLK_LOG2;
   const int bx1 = min(bx0 + BLK, p.W) - 1, by1 = min(by0 + BLK, p.H) - 1;
   const Grid g = make_grid(a.job.mult, p.W, p.H);
   const int tid = threadIdx.x, lane = lane_id(), warp = tid >> 5;
+  const bool fast_ok = fabs(a.eps_d) <= 0x1p90;
 
   for (int i = tid; i < BLK * BLK; i += kRasterThreads) zbuf[i] = 0ull;
-  if (tid == 0) { s_nbig = 0; s_uncovered = 0; }
+  if (tid == 0) sm.uncovered = 0;
 
   // parent bin of this block
   const int shift = p.bin_log2 - BLK_LOG2;
@@ -65,59 +74,152 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
   long long start = a.job.start[row];
   long long n = a.job.count[row];
   if (start + n > a.job.capacity) n = max(0ll, a.job.capacity - start);  // overflowed call
-  __syncthreads();
+
+  unsigned* queue = sm.queue[warp];
+
+  // Exact test + depth + publish of 32 (or `cnt` < 32) queued candidates, one per lane.
+  auto drain = [&](int first, int cnt) {
+    if (lane < cnt) {
+      const unsigned e = queue[(first + lane) & (kQueue - 1)];
+      const int s = e & 0xff, rx = (e >> 8) & 0xff, ry = (e >> 16) & 0xff;
+      const float x0 = pix_x(g, bx0 + rx), y0 = pix_y(g, by0 + ry);
+      float w0, w1, w2;
+      if (raster_weights(x0, y0, sm.x[0][s], sm.x[1][s], sm.x[2][s], sm.x[3][s], sm.x[4][s],
+                         sm.x[5][s], a.eps_d, w0, w1, w2)) {
+        const unsigned long long key =
+            depth_key(raster_depth(w0, w1, w2, sm.z[0][s], sm.z[1][s], sm.z[2][s]), sm.face[s]);
+        if (key) smem_max64(&zbuf[(ry << BLK_LOG2) + rx], key);
+      }
+    }
+  };
 
   for (long long base = 0; base < n; base += kRasterThreads) {
-    const long long li = base + tid;
-    if (li < n) {
-      const int f = a.job.list[start + li];
-      Face2D fc;
-      // list entries were accepted by load_face2d during binning; redo it for the data
-      if (load_face2d(a.job, b, f, fc)) {
-        int x_lo, x_hi, y_lo, y_hi;
-        if (pixel_range(g, fc.xmin, fc.ymin, fc.xmax, fc.ymax, x_lo, x_hi, y_lo, y_hi)) {
-          x_lo = max(x_lo, bx0); x_hi = min(x_hi, bx1);
-          y_lo = max(y_lo, by0); y_hi = min(y_hi, by1);
-          const int w = x_hi - x_lo + 1, h = y_hi - y_lo + 1;
-          if (w > 0 && h > 0) {
-            const long long gi = (long long)b * a.job.view_stride + f;
-            const float az = __ldg(a.z + gi * 3), bz = __ldg(a.z + gi * 3 + 1),
-                        cz = __ldg(a.z + gi * 3 + 2);
-            const int face = a.job.first ? f - (int)a.job.first[b] : f;
-            if (w * h <= kSmallBox) {
-              for (int iy = y_lo; iy <= y_hi; iy++)
-                for (int ix = x_lo; ix <= x_hi; ix++)
-                  raster_pixel(g, ix, iy, fc.ax, fc.ay, fc.bx, fc.by, fc.cx, fc.cy, fc.xmin,
-                               fc.ymin, fc.xmax, fc.ymax, az, bz, cz, a.eps_d, face, zbuf, bx0,
-                               by0, BLK_LOG2);
-            } else {
-              const int s = atomicAdd(&s_nbig, 1);
-              BigFace& q = s_big[s];
-              q.ax = fc.ax; q.ay = fc.ay; q.bx = fc.bx; q.by = fc.by; q.cx = fc.cx; q.cy = fc.cy;
-              q.xmin = fc.xmin; q.ymin = fc.ymin; q.xmax = fc.xmax; q.ymax = fc.ymax;
-              q.az = az; q.bz = bz; q.cz = cz;
-              q.face = face; q.x_lo = x_lo; q.y_lo = y_lo; q.w = w; q.n = w * h;
+    __syncthreads();  // previous chunk fully consumed (and zbuf initialised)
+    // ---- phase A: one face per thread -> exact pixel rectangle inside this block
+    int cand = 0;
+    {
+      const long long li = base + tid;
+      int rect = 0;
+      if (li < n) {
+        const int f = a.job.list[start + li];
+        Face2D fc;
+        if (load_face2d(a.job, b, f, fc)) {
+          int x_lo, x_hi, y_lo, y_hi;
+          if (pixel_range(g, fc.xmin, fc.ymin, fc.xmax, fc.ymax, x_lo, x_hi, y_lo, y_hi)) {
+            x_lo = max(x_lo, bx0); x_hi = min(x_hi, bx1);
+            y_lo = max(y_lo, by0); y_hi = min(y_hi, by1);
+            // trim the conservative range to the reference's half-open test
+            // (rasterization_cuda.cu:115); pix_x / pix_y are monotone in ix / iy
+            while (x_lo <= x_hi && pix_x(g, x_lo) < fc.xmin) x_lo++;
+            while (x_lo <= x_hi && pix_x(g, x_hi) >= fc.xmax) x_hi--;
+            while (y_lo <= y_hi && pix_y(g, y_lo) >= fc.ymax) y_lo++;
+            while (y_lo <= y_hi && pix_y(g, y_hi) < fc.ymin) y_hi--;
+            const int w = x_hi - x_lo + 1, h = y_hi - y_lo + 1;
+            if (w > 0 && h > 0) {
+              cand = w * h;
+              rect = (x_lo - bx0) | ((y_lo - by0) << 8) | ((w - 1) << 16) | ((h - 1) << 24);
+              const long long gi = (long long)b * a.job.view_stride + f;
+              sm.x[0][tid] = fc.ax; sm.x[1][tid] = fc.ay; sm.x[2][tid] = fc.bx;
+              sm.x[3][tid] = fc.by; sm.x[4][tid] = fc.cx; sm.x[5][tid] = fc.cy;
+              sm.z[0][tid] = __ldg(a.z + gi * 3);
+              sm.z[1][tid] = __ldg(a.z + gi * 3 + 1);
+              sm.z[2][tid] = __ldg(a.z + gi * 3 + 2);
+              sm.face[tid] = a.job.first ? f - (int)a.job.first[b] : f;
             }
           }
         }
       }
+      sm.rect[tid] = rect;
     }
+    // block-wide exclusive scan of the candidate counts
+    int incl = cand;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int t = __shfl_up_sync(DIBR_FULL_MASK, incl, d);
+      if (lane >= d) incl += t;
+    }
+    if (lane == 31) sm.wsum[warp] = incl;
     __syncthreads();
-    const int nbig = s_nbig;
-    for (int qi = warp; qi < nbig; qi += kRasterThreads / 32) {
-      const BigFace& q = s_big[qi];
-      for (int k = lane; k < q.n; k += 32) {
-        const int iy = q.y_lo + k / q.w, ix = q.x_lo + k % q.w;
-        raster_pixel(g, ix, iy, q.ax, q.ay, q.bx, q.by, q.cx, q.cy, q.xmin, q.ymin, q.xmax,
-                     q.ymax, q.az, q.bz, q.cz, a.eps_d, q.face, zbuf, bx0, by0, BLK_LOG2);
+    int woff = 0, total = 0;
+#pragma unroll
+    for (int i = 0; i < kRasterWarps; i++) {
+      const int v = sm.wsum[i];
+      if (i < warp) woff += v;
+      total += v;
+    }
+    sm.pre[tid] = woff + incl - cand;
+    if (tid == 0) sm.pre[kRasterThreads] = total;
+    __syncthreads();
+    if (total == 0) continue;
+
+    // ---- phase B: the chunk's (face, pixel) candidates dealt out evenly, a contiguous
+    // run per thread; cheap sign test for all, survivors compacted into the warp's queue
+    const int per = (total + kRasterThreads - 1) / kRasterThreads;
+    int k = tid * per;
+    const int k_end = min(k + per, total);
+    int s = 0, rx0 = 0, rw = 1, rx = 0, ry = 0, left = 0;
+    float ax = 0.f, ay = 0.f, bx = 0.f, by = 0.f, cx = 0.f, cy = 0.f, y0 = 0.f;
+    if (k < k_end) {
+#pragma unroll
+      for (int st = kRasterThreads / 2; st > 0; st >>= 1)
+        if (sm.pre[s + st] <= k) s += st;
+      const int r = sm.rect[s];
+      rx0 = r & 0xff; rw = ((r >> 16) & 0xff) + 1;
+      const int off = k - sm.pre[s];
+      ry = (r >> 8 & 0xff) + off / rw;
+      rx = rx0 + off % rw;
+      left = sm.pre[s + 1] - k;  // candidates left in this face, this one included
+      ax = sm.x[0][s]; ay = sm.x[1][s]; bx = sm.x[2][s];
+      by = sm.x[3][s]; cx = sm.x[4][s]; cy = sm.x[5][s];
+      y0 = pix_y(g, by0 + ry);
+    }
+    int qhead = 0, qn = 0;  // warp-uniform
+    for (int it = 0; it < per; it++) {
+      bool keep = false;
+      if (k < k_end) {
+        const float x0 = pix_x(g, bx0 + rx);
+        const float a_ex = __fsub_rn(ax, x0), a_ey = __fsub_rn(ay, y0);
+        const float b_ex = __fsub_rn(bx, x0), b_ey = __fsub_rn(by, y0);
+        const float c_ex = __fsub_rn(cx, x0), c_ey = __fsub_rn(cy, y0);
+        const float w0 = __fmaf_rn(b_ex, c_ey, -__fmul_rn(b_ey, c_ex));
+        const float w1 = __fmaf_rn(c_ex, a_ey, -__fmul_rn(c_ey, a_ex));
+        const float w2 = __fmaf_rn(a_ex, b_ey, -__fmul_rn(a_ey, b_ex));
+        const float n32 = __fadd_rn(__fadd_rn(w0, w1), w2);
+        keep = !(fast_ok && surely_outside(w0, w1, w2, n32));
+      }
+      const unsigned m = __ballot_sync(DIBR_FULL_MASK, keep);
+      if (keep)
+        queue[(qhead + qn + __popc(m & lanemask_lt())) & (kQueue - 1)] =
+            (unsigned)s | ((unsigned)rx << 8) | ((unsigned)ry << 16);
+      qn += __popc(m);
+      __syncwarp();
+      if (qn >= 32) {
+        drain(qhead, 32);
+        qhead = (qhead + 32) & (kQueue - 1);
+        qn -= 32;
+        __syncwarp();
+      }
+      // advance to the next candidate of this thread's run
+      if (++k < k_end) {
+        if (--left == 0) {
+          do { s++; } while (sm.pre[s + 1] == sm.pre[s]);
+          const int r = sm.rect[s];
+          rx0 = r & 0xff; rw = ((r >> 16) & 0xff) + 1;
+          rx = rx0; ry = (r >> 8) & 0xff;
+          left = sm.pre[s + 1] - sm.pre[s];
+          ax = sm.x[0][s]; ay = sm.x[1][s]; bx = sm.x[2][s];
+          by = sm.x[3][s]; cx = sm.x[4][s]; cy = sm.x[5][s];
+          y0 = pix_y(g, by0 + ry);
+        } else if (++rx == rx0 + rw) {
+          rx = rx0;
+          ry++;
+          y0 = pix_y(g, by0 + ry);
+        }
       }
     }
-    __syncthreads();
-    if (tid == 0) s_nbig = 0;
-    // (the next iteration's atomicAdd on s_nbig happens after its own loads; the barrier
-    //  at the end of that iteration orders it against this reset through the next sync)
-    __syncthreads();
+    if (qn > 0) drain(qhead, qn);
   }
+  __syncthreads();
 
   // ---- resolve: one pixel per thread-iteration, rows of the block are contiguous in x
   int uncovered = 0;
@@ -150,22 +252,21 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
   }
   if (a.block_uncovered) {
     uncovered = __reduce_add_sync(DIBR_FULL_MASK, uncovered);
-    if (lane == 0 && uncovered) atomicAdd(&s_uncovered, uncovered);
+    if (lane == 0 && uncovered) atomicAdd(&sm.uncovered, uncovered);
     __syncthreads();
     if (tid == 0)
       a.block_uncovered[(long long)b * p.nkx * p.nky + blockIdx.y * p.nkx + blockIdx.x] =
-          s_uncovered;
+          sm.uncovered;
   }
 }
 
 cudaError_t launch_raster_forward(const RasterArgs& a, const Plan& p, cudaStream_t st) {
   dim3 grid(p.nkx, p.nky, p.B);
-  const size_t big = sizeof(BigFace) * kRasterThreads;
   prof_begin(K_RASTER_FWD, st);
   if (p.blk_log2 == 5) {
-    raster_forward_kernel<5><<<grid, kRasterThreads, 8 * 32 * 32 + big, st>>>(a, p);
+    raster_forward_kernel<5><<<grid, kRasterThreads, sizeof(RasterSmem<5>), st>>>(a, p);
   } else {
-    const size_t smem = 8 * 64 * 64 + big;  // 50 KB: above the 48 KB default, opt in
+    const size_t smem = sizeof(RasterSmem<6>);  // above the 48 KB default: opt in
     static bool once = false;
     if (!once) {
       cudaError_t e = cudaFuncSetAttribute(raster_forward_kernel<6>,
