@@ -39,7 +39,8 @@ sys.path.insert(0, ROOT)
 CFG = "cfg2_70k_8x512"
 SIGMAINV, BOXLEN, KNUM = 7000, 0.02, 30
 KERNELS = ["bin_count", "bin_scan", "bin_fill", "raster_fwd", "softmask_fwd", "raster_bwd",
-           "softmask_bwd", "softmask_bwd_dense"]
+           "softmask_bwd", "softmask_bwd_dense", "softmask_gather", "softmask_eval",
+           "softmask_grad"]
 METRIC = "DIB-R fwd+bwd Mpixels/s (views x H x W)"
 
 
@@ -50,9 +51,10 @@ def algorithmic_bytes(kernel, B, F, P, D):
     return {
         "bin_count": fv * (28 + 24), "bin_fill": fv * (28 + 24), "bin_scan": 0,
         "raster_fwd": fv * (40 + 12 * D) + px * (8 + 4 * D),
-        "softmask_fwd": fv * 24 + px * 12,
+        "softmask_fwd": fv * 24 + px * 12, "softmask_gather": fv * 24 + px * 12,
+        "softmask_eval": fv * 24 + px * 4,
         "raster_bwd": fv * (48 + 24 * D) + px * (8 + 4 * D),
-        "softmask_bwd": fv * 48 + px * 16,
+        "softmask_bwd": fv * 48 + px * 16, "softmask_grad": fv * 48 + px * 16,
     }.get(kernel, 0)
 
 

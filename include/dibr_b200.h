@@ -39,7 +39,18 @@
  *                          (dibr_last_error() then names the needed entry counts).
  * The backward of the soft mask re-reads the soft list, so `ws` must be kept unchanged
  * between dibr_softmask_fwd / dibr_render_fwd and dibr_softmask_bwd, which takes the
- * same two capacities.
+ * same capacities.
+ *
+ * Pair buffer (optional, pair_capacity > 0 and 0 < knum <= 1024).  The soft-mask forward
+ * then also leaves in `ws`, after the two lists, the compact per-pixel face lists it found
+ * ("pairs": face id, probability, nearest-feature type per (pixel, face)), allocated in
+ * segments of 8 hits x 32 pixels; pair_capacity is the number of such segments (and the
+ * maximum number of 8x4-pixel regions holding any hit).  The backward then runs over the
+ * saved pairs instead of re-walking the lists.  If the buffer is too small nothing breaks:
+ * both directions fall back, decided on the device, to the self-contained kernels.  The
+ * segments / regions the call wanted are reported as needed_host[2], needed_host[3]
+ * (needed_host is int64[4]; entries 2-3 are written when the gather kernel has finished, so
+ * a caller reads them later, e.g. before its next call, to size the buffer).
  */
 #ifndef DIBR_B200_H_
 #define DIBR_B200_H_
@@ -76,9 +87,11 @@ DIBR_API int dibr_profile_end(int* kernel_ids, float* ms, int capacity);
  * views of `num_faces` faces (for the packed mode: the total number of packed faces) at
  * height x width.  Returns < 0 on invalid sizes. */
 DIBR_API int64_t dibr_workspace_fixed_bytes(int batch, int num_faces, int height, int width);
-/* fixed bytes + room for raster_capacity + soft_capacity list entries. */
+/* fixed bytes + room for raster_capacity + soft_capacity list entries + a pair buffer of
+ * pair_capacity segments for `knum` (0 / 0 for calls that use none). */
 DIBR_API int64_t dibr_workspace_bytes_for(int batch, int num_faces, int height, int width,
-                                 int64_t raster_capacity, int64_t soft_capacity);
+                                 int64_t raster_capacity, int64_t soft_capacity,
+                                 int64_t pair_capacity, int knum);
 
 /*
  * rasterize forward.  Replaces RasterizeCuda.forward (rasterization.py:289-369) +
@@ -141,12 +154,13 @@ DIBR_API int dibr_softmask_fwd(int batch, int num_faces, int height, int width,
                       float sigmainv, float box_margin, int knum, float multiplier,
                       float* soft_mask, float* close_face_prob, int64_t* close_face_idx,
                       uint8_t* close_face_dist_type, void* ws, int64_t ws_bytes,
-                      int64_t raster_capacity, int64_t soft_capacity, int64_t* needed_host,
-                      void* stream);
+                      int64_t raster_capacity, int64_t soft_capacity, int64_t pair_capacity,
+                      int64_t* needed_host, void* stream);
 
 /*
- * soft mask backward, recompute form (fast path): re-walks the lists left in `ws` by
- * dibr_softmask_fwd / dibr_render_fwd instead of reading 13*K bytes/pixel of saved state.
+ * soft mask backward (fast path): runs over the pairs left in `ws` by dibr_softmask_fwd /
+ * dibr_render_fwd or, without a (large enough) pair buffer, re-walks the face lists left
+ * there -- instead of reading the reference's 13*K bytes/pixel of saved state.
  * Same arguments as the forward (they must be the SAME values) + grad_soft_mask, the
  * forward's soft_mask, and grad_face_vertices_image (B,F,3,2), accumulated into, w.r.t.
  * the UNscaled coordinates (every term is divided by multiplier, dibr_soft_mask_cuda.cu:298-346).
@@ -157,7 +171,8 @@ DIBR_API int dibr_softmask_bwd(int batch, int num_faces, int height, int width,
                       float sigmainv, float box_margin, int knum, float multiplier,
                       const float* grad_soft_mask, const float* soft_mask,
                       float* grad_face_vertices_image, const void* ws, int64_t ws_bytes,
-                      int64_t raster_capacity, int64_t soft_capacity, void* stream);
+                      int64_t raster_capacity, int64_t soft_capacity, int64_t pair_capacity,
+                      void* stream);
 
 /*
  * soft mask backward, dense-state form: the raw _C op dibr_soft_mask_backward_cuda
@@ -182,7 +197,7 @@ DIBR_API int dibr_render_fwd(int batch, int num_faces, int height, int width, in
                     float box_margin, int knum, float multiplier, float eps,
                     int64_t* selected_face_idx, float* interpolated_features, float* soft_mask,
                     void* ws, int64_t ws_bytes, int64_t raster_capacity, int64_t soft_capacity,
-                    int64_t* needed_host, void* stream);
+                    int64_t pair_capacity, int64_t* needed_host, void* stream);
 
 #ifdef __cplusplus
 }

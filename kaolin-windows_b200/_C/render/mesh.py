@@ -71,7 +71,7 @@ def packed_rasterize_forward_cuda(height, width, face_vertices_z, face_vertices_
     with torch.cuda.device(dev):
         st = _stream(dev)
 
-        def call(ws, ws_bytes, cap_r, cap_s, needed):
+        def call(ws, ws_bytes, cap_r, cap_s, cap_p, needed):
             return lib.dibr_rasterize_fwd(
                 batch_size, num_faces, int(height), int(width), feat_dim, _ptr(z), _ptr(img),
                 _ptr(feat), None, None, 1, _ptr(bbox), _ptr(first), float(multiplier), float(eps),
@@ -135,11 +135,11 @@ def dibr_soft_mask_forward_cuda(face_vertices_image, face_large_bboxes, selected
     with torch.cuda.device(dev):
         st = _stream(dev)
 
-        def call(ws, ws_bytes, cap_r, cap_s, needed):
+        def call(ws, ws_bytes, cap_r, cap_s, cap_p, needed):
             return lib.dibr_softmask_fwd(
                 B, F, H, W, _ptr(img), 1, _ptr(bbox), _ptr(selected_face_idx), float(sigmainv),
                 0.0, knum, float(multiplier), _ptr(mask), _ptr(prob), _ptr(cidx), _ptr(typ),
-                ws, ws_bytes, cap_r, cap_s, needed, st)
+                ws, ws_bytes, cap_r, cap_s, 0, needed, st)
 
         _workspace.run("soft_dense", dev, B, F, H, W, False, True, call)
     return [mask, prob, cidx, typ]

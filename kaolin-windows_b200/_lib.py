@@ -24,18 +24,18 @@ SIGNATURES = {
     "dibr_profile_begin": (_i, []),
     "dibr_profile_end": (_i, [_vp, _vp, _i]),
     "dibr_workspace_fixed_bytes": (_i64, [_i, _i, _i, _i]),
-    "dibr_workspace_bytes_for": (_i64, [_i, _i, _i, _i, _i64, _i64]),
+    "dibr_workspace_bytes_for": (_i64, [_i, _i, _i, _i, _i64, _i64, _i64, _i]),
     "dibr_rasterize_fwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _f, _f,
                                 _vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp]),
     "dibr_rasterize_bwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp]),
     "dibr_softmask_fwd": (_i, [_i, _i, _i, _i, _vp, _i, _vp, _vp, _f, _f, _i, _f, _vp, _vp, _vp, _vp,
-                               _vp, _i64, _i64, _i64, _vp, _vp]),
+                               _vp, _i64, _i64, _i64, _i64, _vp, _vp]),
     "dibr_softmask_bwd": (_i, [_i, _i, _i, _i, _vp, _i, _vp, _vp, _f, _f, _i, _f, _vp, _vp, _vp,
-                               _vp, _i64, _i64, _i64, _vp]),
+                               _vp, _i64, _i64, _i64, _i64, _vp]),
     "dibr_softmask_bwd_dense": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _f, _f,
                                      _vp, _vp]),
     "dibr_render_fwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _f, _f, _i, _f, _f, _vp, _vp,
-                             _vp, _vp, _i64, _i64, _i64, _vp, _vp]),
+                             _vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp]),
 }
 
 _lock = threading.Lock()

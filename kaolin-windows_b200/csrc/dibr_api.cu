@@ -91,15 +91,28 @@ struct Workspace {
   char* base;
   int64_t cap[2];
   int* list[2];
+  PairBuf pairs;
 };
 
+// Pair area (compact soft-mask face lists kept for the backward) for `cap` segments.
+static int pair_nseg(int K) { return (K + kPairSegHits - 1) / kPairSegHits; }
+static bool pair_usable(int64_t cap, int K) { return cap > 0 && K > 0 && K <= kPairMaxK; }
+static int64_t pair_bytes(int64_t cap, int K) {
+  if (!pair_usable(cap, K)) return 0;
+  const int64_t n = cap * kPairSegSlots;
+  return align_up(cap * 4, 256) + align_up(cap * 64, 256) + align_up(cap * pair_nseg(K) * 4, 256) +
+         2 * align_up(n * 4, 256) + align_up(n, 256);
+}
+
 static int bind_workspace(const Plan& p, const void* ws, int64_t ws_bytes, int64_t cap_r,
-                          int64_t cap_s, Workspace& w) {
+                          int64_t cap_s, Workspace& w, int64_t cap_p = 0, int K = 0) {
   if (cap_r < 0) cap_r = 0;
   if (cap_s < 0) cap_s = 0;
   if (cap_r > 0x7fffffff || cap_s > 0x7fffffff)
     return fail(DIBR_E_INVALID, "list capacity above 2^31-1 entries");
-  const int64_t need = p.fixed_bytes + 4 * (cap_r + cap_s);
+  if (cap_p > (1 << 23)) return fail(DIBR_E_INVALID, "pair capacity above 2^23 segments");
+  const int64_t lists_end = align_up(p.fixed_bytes + 4 * (cap_r + cap_s), 256);
+  const int64_t need = lists_end + pair_bytes(cap_p, K);
   if (!ws || ws_bytes < need)
     return fail(DIBR_E_WORKSPACE, "workspace of %lld bytes given, %lld needed",
                 (long long)ws_bytes, (long long)need);
@@ -109,6 +122,21 @@ static int bind_workspace(const Plan& p, const void* ws, int64_t ws_bytes, int64
   w.cap[1] = cap_s;
   w.list[0] = (int*)(w.base + p.fixed_bytes);
   w.list[1] = w.list[0] + cap_r;
+  memset(&w.pairs, 0, sizeof(w.pairs));
+  if (pair_usable(cap_p, K)) {
+    PairBuf& pb = w.pairs;
+    const int64_t n = cap_p * kPairSegSlots;
+    char* q = w.base + lists_end;
+    pb.cap = (int)cap_p;
+    pb.nseg = pair_nseg(K);
+    pb.cursor = (unsigned long long*)(w.base + p.off_total) + 2;
+    pb.act_region = (int*)q; q += align_up(cap_p * 4, 256);
+    pb.act_cnt = (unsigned short*)q; q += align_up(cap_p * 64, 256);
+    pb.act_seg = (int*)q; q += align_up(cap_p * pb.nseg * 4, 256);
+    pb.face = (int*)q; q += align_up(n * 4, 256);
+    pb.prob = (float*)q; q += align_up(n * 4, 256);
+    pb.type = (unsigned char*)q;
+  }
   return DIBR_OK;
 }
 
@@ -197,11 +225,12 @@ extern "C" int64_t dibr_workspace_fixed_bytes(int B, int F, int H, int W) {
 }
 
 extern "C" int64_t dibr_workspace_bytes_for(int B, int F, int H, int W, int64_t cap_r,
-                                            int64_t cap_s) {
+                                            int64_t cap_s, int64_t cap_p, int K) {
   Plan p;
   int rc = make_plan(B, F, H, W, p);
   if (rc) return rc;
-  return p.fixed_bytes + 4 * ((cap_r > 0 ? cap_r : 0) + (cap_s > 0 ? cap_s : 0));
+  return align_up(p.fixed_bytes + 4 * ((cap_r > 0 ? cap_r : 0) + (cap_s > 0 ? cap_s : 0)), 256) +
+         pair_bytes(cap_p, K);
 }
 
 static int check_common(float multiplier) {
@@ -268,6 +297,20 @@ extern "C" int dibr_rasterize_bwd(int B, int F, int H, int W, int D, const float
   return DIBR_OK;
 }
 
+// Soft-mask forward: with a pair buffer, gather -> pair evaluation, and the self-contained
+// kernel as the (device-side decided) fallback when the buffer overflowed.
+static int run_soft_forward(const SoftArgs& a, const Plan& p, int64_t* needed_host,
+                            cudaStream_t st) {
+  if (a.pairs.cap > 0) {
+    DIBR_CUDA(launch_softmask(a, SOFT_GATHER, p, st));
+    if (needed_host)
+      DIBR_CUDA(cudaMemcpyAsync(needed_host + 2, a.pairs.cursor, 16, cudaMemcpyDeviceToHost, st));
+    DIBR_CUDA(launch_softmask_pairs_eval(a, p, st));
+  }
+  DIBR_CUDA(launch_softmask(a, SOFT_FWD, p, st));
+  return DIBR_OK;
+}
+
 static int soft_common(int B, int F, int H, int W, const float* img, int prescaled,
                        const float* bboxes, const int64_t* sel, int K, float multiplier,
                        float box_margin, Plan& p, BinJob& job) {
@@ -287,7 +330,7 @@ extern "C" int dibr_softmask_fwd(int B, int F, int H, int W, const float* img, i
                                  const float* bboxes, const int64_t* sel, float sigmainv,
                                  float box_margin, int K, float multiplier, float* mask,
                                  float* prob, int64_t* cidx, uint8_t* type, void* ws,
-                                 int64_t ws_bytes, int64_t cap_r, int64_t cap_s,
+                                 int64_t ws_bytes, int64_t cap_r, int64_t cap_s, int64_t cap_p,
                                  int64_t* needed_host, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   Plan p;
@@ -301,7 +344,8 @@ extern "C" int dibr_softmask_fwd(int B, int F, int H, int W, const float* img, i
   if (!dense && (prob || cidx || type))
     return fail(DIBR_E_INVALID, "dense outputs must be given all three or none");
   Workspace w;
-  if ((rc = bind_workspace(p, ws, ws_bytes, cap_r, cap_s, w))) return rc;
+  if (dense) cap_p = 0;
+  if ((rc = bind_workspace(p, ws, ws_bytes, cap_r, cap_s, w, cap_p, K))) return rc;
   attach(jobs.j[0], p, w, 1);
   jobs.j[1] = jobs.j[0];
   const int kinds[1] = {1};
@@ -310,8 +354,12 @@ extern "C" int dibr_softmask_fwd(int B, int F, int H, int W, const float* img, i
   memset(&a, 0, sizeof(a));
   a.job = jobs.j[0]; a.sel = sel; a.sigmainv = sigmainv; a.K = K; a.mask = mask;
   a.prob = prob; a.cidx = cidx; a.type = type;
-  DIBR_CUDA(launch_softmask(a, dense ? SOFT_FWD_DENSE : SOFT_FWD, p, st));
-  return DIBR_OK;
+  a.pairs = w.pairs;
+  if (dense) {
+    DIBR_CUDA(launch_softmask(a, SOFT_FWD_DENSE, p, st));
+    return DIBR_OK;
+  }
+  return run_soft_forward(a, p, needed_host, st);
 }
 
 extern "C" int dibr_softmask_bwd(int B, int F, int H, int W, const float* img, int prescaled,
@@ -319,7 +367,7 @@ extern "C" int dibr_softmask_bwd(int B, int F, int H, int W, const float* img, i
                                  float box_margin, int K, float multiplier,
                                  const float* grad_mask, const float* mask, float* grad_img,
                                  const void* ws, int64_t ws_bytes, int64_t cap_r, int64_t cap_s,
-                                 void* stream) {
+                                 int64_t cap_p, void* stream) {
   Plan p;
   BinJob job;
   int rc = soft_common(B, F, H, W, img, prescaled, bboxes, sel, K, multiplier, box_margin, p, job);
@@ -327,12 +375,14 @@ extern "C" int dibr_softmask_bwd(int B, int F, int H, int W, const float* img, i
   if (B == 0 || F == 0) return DIBR_OK;
   if (!grad_mask || !mask || !grad_img) return fail(DIBR_E_INVALID, "null pointer");
   Workspace w;
-  if ((rc = bind_workspace(p, ws, ws_bytes, cap_r, cap_s, w))) return rc;
+  if ((rc = bind_workspace(p, ws, ws_bytes, cap_r, cap_s, w, cap_p, K))) return rc;
   attach(job, p, w, 1);
   SoftArgs a;
   memset(&a, 0, sizeof(a));
   a.job = job; a.sel = sel; a.sigmainv = sigmainv; a.K = K;
   a.grad_mask = grad_mask; a.mask_in = mask; a.grad_img = grad_img;
+  a.pairs = w.pairs;
+  DIBR_CUDA(launch_softmask_pairs_grad(a, p, (cudaStream_t)stream));
   DIBR_CUDA(launch_softmask(a, SOFT_BWD, p, (cudaStream_t)stream));
   return DIBR_OK;
 }
@@ -361,7 +411,7 @@ extern "C" int dibr_render_fwd(int B, int F, int H, int W, int D, const float* z
                                float sigmainv, float box_margin, int K, float multiplier,
                                float eps, int64_t* out_idx, float* out_feat, float* mask,
                                void* ws, int64_t ws_bytes, int64_t cap_r, int64_t cap_s,
-                               int64_t* needed_host, void* stream) {
+                               int64_t cap_p, int64_t* needed_host, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   Plan p;
   int rc = make_plan(B, F, H, W, p);
@@ -372,7 +422,7 @@ extern "C" int dibr_render_fwd(int B, int F, int H, int W, int D, const float* z
   if (!out_idx || (!out_feat && D > 0) || !mask) return fail(DIBR_E_INVALID, "null output");
   if (F > 0 && (!z || !img || (!feat && D > 0))) return fail(DIBR_E_INVALID, "null input");
   Workspace w;
-  if ((rc = bind_workspace(p, ws, ws_bytes, cap_r, cap_s, w))) return rc;
+  if ((rc = bind_workspace(p, ws, ws_bytes, cap_r, cap_s, w, cap_p, K))) return rc;
   BinJobs jobs;
   jobs.j[0] = face_source(img, nullptr, nullptr, normal_z, nullptr, F, multiplier, 0.f, 0);
   jobs.j[1] = face_source(img, nullptr, nullptr, nullptr, nullptr, F, multiplier, box_margin, 0);
@@ -388,6 +438,6 @@ extern "C" int dibr_render_fwd(int B, int F, int H, int W, int D, const float* z
   SoftArgs s;
   memset(&s, 0, sizeof(s));
   s.job = jobs.j[1]; s.sel = out_idx; s.sigmainv = sigmainv; s.K = K; s.mask = mask;
-  DIBR_CUDA(launch_softmask(s, SOFT_FWD, p, st));
-  return DIBR_OK;
+  s.pairs = w.pairs;
+  return run_soft_forward(s, p, needed_host, st);
 }

@@ -92,6 +92,29 @@ struct RasterBwdArgs {
   double eps_d;
 };
 
+// Compact per-pixel face lists of the soft mask ("pairs"), kept between forward and
+// backward.  A region (8x4 pixels, one per lane) that holds at least one hit becomes
+// "active" and owns segments of 8 hits x 32 lanes: slot (hit h of lane l) lives at
+// seg[h / 8] * 256 + (h % 8) * 32 + l.  Everything is sized by `cap` segments.
+constexpr int kPairSegHits = 8;
+constexpr int kPairSegSlots = kPairSegHits * 32;
+constexpr int kPairMaxK = 1024;  // above this knum the pair path is not used
+struct PairBuf {
+  int cap;                    // segments (and active regions) available; 0 = pair path off
+  int nseg;                   // segments per region = ceil(knum / 8)
+  unsigned long long* cursor; // [0] segments requested, [1] active regions requested
+  int* act_region;            // [cap]        global region id
+  unsigned short* act_cnt;    // [cap][32]    hits held by each pixel of the region
+  int* act_seg;               // [cap][nseg]  segment ids
+  int* face;                  // [cap * 256]
+  float* prob;                // [cap * 256]
+  unsigned char* type;        // [cap * 256]  1-3 edge, 4-6 vertex (reference numbering)
+};
+
+__device__ __forceinline__ bool pairs_overflowed(const PairBuf& pb) {
+  return pb.cursor[0] > (unsigned long long)pb.cap || pb.cursor[1] > (unsigned long long)pb.cap;
+}
+
 struct SoftArgs {
   BinJob job;              // soft list + how to read faces (mult, margin, prescaled, boxes)
   const int64_t* sel;      // (B, H, W)
@@ -104,6 +127,7 @@ struct SoftArgs {
   const float* grad_mask;  // backward inputs
   const float* mask_in;
   float* grad_img;         // (B, F, 3, 2) accumulated, unscaled coordinates
+  PairBuf pairs;
 };
 
 struct SoftDenseBwdArgs {
@@ -119,12 +143,15 @@ struct SoftDenseBwdArgs {
   float sigmainv, mult;
 };
 
-enum { SOFT_FWD = 0, SOFT_FWD_DENSE = 1, SOFT_BWD = 2 };
+// SOFT_FWD / SOFT_BWD: self-contained kernels (gather + evaluate per block); when a pair
+// buffer is attached they only run if it overflowed.  SOFT_GATHER: gather only, fills the
+// pair buffer for launch_softmask_pairs_{eval,grad}.
+enum { SOFT_FWD = 0, SOFT_FWD_DENSE = 1, SOFT_BWD = 2, SOFT_GATHER = 3 };
 
 // Optional per-kernel timing (dibr_profile_begin/end in the C ABI): CUDA events recorded on
 // the launching stream right before and after a kernel.  No-ops unless enabled.
 enum { K_BIN_COUNT = 0, K_BIN_SCAN, K_BIN_FILL, K_RASTER_FWD, K_SOFT_FWD, K_RASTER_BWD,
-       K_SOFT_BWD, K_SOFT_BWD_DENSE, K_NUM };
+       K_SOFT_BWD, K_SOFT_BWD_DENSE, K_SOFT_GATHER, K_SOFT_EVAL, K_SOFT_GRAD, K_NUM };
 void prof_begin(int kernel_id, cudaStream_t st);
 void prof_end(cudaStream_t st);
 
@@ -134,6 +161,8 @@ cudaError_t launch_raster_forward(const RasterArgs&, const Plan&, cudaStream_t);
 cudaError_t launch_raster_backward(const RasterBwdArgs&, cudaStream_t);
 cudaError_t launch_softmask(const SoftArgs&, int mode, const Plan&, cudaStream_t);
 cudaError_t launch_softmask_dense_backward(const SoftDenseBwdArgs&, cudaStream_t);
+cudaError_t launch_softmask_pairs_eval(const SoftArgs&, const Plan&, cudaStream_t);
+cudaError_t launch_softmask_pairs_grad(const SoftArgs&, const Plan&, cudaStream_t);
 
 // ------------------------------------------------------------------------ pixel grid
 struct Grid {

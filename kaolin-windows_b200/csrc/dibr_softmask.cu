@@ -169,6 +169,8 @@ struct SoftSmem {
   unsigned char ty[kSoftWarps][kSeg][32];
   int off[kSoftWarps][33];
   unsigned char ropen[NR];
+  unsigned char rseg[NR];        // SOFT_GATHER: pair segments the region owns so far
+  int ract[NR];                  // SOFT_GATHER: active-region slot, -1 = none yet
   int next;
   float acc[MODE == SOFT_BWD ? kSoftChunk : 1][6];
 };
@@ -183,6 +185,11 @@ softmask_kernel(const SoftArgs a, const Plan p) {
   Smem& sm = *reinterpret_cast<Smem*>(s_raw);
 
   const int tid = threadIdx.x, lane = lane_id(), warp = tid >> 5;
+  // with a pair buffer attached the self-contained kernels are only the overflow fallback
+  if ((MODE == SOFT_FWD || MODE == SOFT_BWD) && a.pairs.cap > 0 && !pairs_overflowed(a.pairs))
+    return;
+  const PairBuf& pb = a.pairs;
+  const int nrx = (p.W + 7) >> 3, nry = (p.H + 3) >> 2;  // regions of a view
   const int b = blockIdx.z;
   const int bx0 = blockIdx.x << BLK_LOG2, by0 = blockIdx.y << BLK_LOG2;
   const Grid g = make_grid(a.job.mult, p.W, p.H);
@@ -204,7 +211,11 @@ softmask_kernel(const SoftArgs a, const Plan p) {
     const int pl = (((r / RX) * 4 + ly) << BLK_LOG2) + (r % RX) * 8 + lx;
     const bool open = (int)sm.cnt[pl] < K;
     const unsigned m = __ballot_sync(DIBR_FULL_MASK, open);
-    if (lane == 0) sm.ropen[r] = m != 0;
+    if (lane == 0) {
+      sm.ropen[r] = m != 0;
+      sm.rseg[r] = 0;
+      sm.ract[r] = -1;
+    }
   }
 
   const int shift = p.bin_log2 - BLK_LOG2;
@@ -229,9 +240,11 @@ softmask_kernel(const SoftArgs a, const Plan p) {
       sm.x[0][t] = fc.ax; sm.x[1][t] = fc.ay; sm.x[2][t] = fc.bx;
       sm.x[3][t] = fc.by; sm.x[4][t] = fc.cx; sm.x[5][t] = fc.cy;
       sm.bb[0][t] = fc.xmin; sm.bb[1][t] = fc.ymin; sm.bb[2][t] = fc.xmax; sm.bb[3][t] = fc.ymax;
-      sm.inv[0][t] = edge_inv(fc.ax, fc.ay, fc.bx, fc.by);
-      sm.inv[1][t] = edge_inv(fc.bx, fc.by, fc.cx, fc.cy);
-      sm.inv[2][t] = edge_inv(fc.cx, fc.cy, fc.ax, fc.ay);
+      if (MODE != SOFT_GATHER) {
+        sm.inv[0][t] = edge_inv(fc.ax, fc.ay, fc.bx, fc.by);
+        sm.inv[1][t] = edge_inv(fc.bx, fc.by, fc.cx, fc.cy);
+        sm.inv[2][t] = edge_inv(fc.cx, fc.cy, fc.ax, fc.ay);
+      }
       sm.face[t] = f;
       if (MODE == SOFT_BWD) {
 #pragma unroll
@@ -260,6 +273,48 @@ softmask_kernel(const SoftArgs a, const Plan p) {
 
       // evaluate everything gathered so far for this region (all lanes call it together)
       auto flush = [&]() {
+        if (MODE == SOFT_GATHER) {
+          // append this round's hits to the region's pair segments (allocating them on
+          // demand: one cursor atomic per region per growth step)
+          const int mx = __reduce_max_sync(DIBR_FULL_MASK, cnt == 0xffff ? 0 : cnt);
+          const int need = (mx + kPairSegHits - 1) / kPairSegHits;
+          int aidx = sm.ract[r];
+          const int have = sm.rseg[r];
+          if (need > have) {
+            long long base = 0;
+            if (lane == 0) {
+              if (aidx < 0) {
+                const unsigned long long v = atomicAdd(pb.cursor + 1, 1ull);
+                aidx = v < (unsigned long long)pb.cap ? (int)v : 0x7fffffff;
+                if (aidx < pb.cap)
+                  pb.act_region[aidx] =
+                      (b * nry + (by0 >> 2) + r / RX) * nrx + (bx0 >> 3) + r % RX;
+              }
+              base = (long long)atomicAdd(pb.cursor, (unsigned long long)(need - have));
+            }
+            aidx = __shfl_sync(DIBR_FULL_MASK, aidx, 0);
+            base = __shfl_sync(DIBR_FULL_MASK, base, 0);
+            if (aidx < pb.cap)
+              for (int q = have + lane; q < need; q += 32) {
+                const long long sg = base + (q - have);
+                pb.act_seg[(long long)aidx * pb.nseg + q] = sg < pb.cap ? (int)sg : -1;
+              }
+            if (lane == 0) { sm.ract[r] = aidx; sm.rseg[r] = (unsigned char)need; }
+            __syncwarp();
+          }
+          if (aidx < pb.cap) {
+            for (int j = 0; j < nbuf; j++) {
+              const int hp = cnt - nbuf + j;
+              const int sg = pb.act_seg[(long long)aidx * pb.nseg + hp / kPairSegHits];
+              if (sg >= 0)
+                pb.face[(long long)sg * kPairSegSlots + (hp % kPairSegHits) * 32 + lane] =
+                    sm.face[sm.hit[warp][j][lane]];
+            }
+          }
+          nbuf = 0;
+          __syncwarp();
+          return;
+        }
         int incl = nbuf;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
@@ -354,12 +409,134 @@ softmask_kernel(const SoftArgs a, const Plan p) {
 
   if (MODE != SOFT_BWD) {
     __syncthreads();
+    // (SOFT_GATHER: ap is still 1, i.e. 0 for every uncovered pixel; the pixels of active
+    //  regions are overwritten by the pair evaluation kernel)
     for (int i = tid; i < NPX; i += kSoftThreads) {
       const int ix = bx0 + (i & (BLK - 1)), iy = by0 + (i >> BLK_LOG2);
       if (ix < p.W && iy < p.H)
         a.mask[((long long)b * p.H + iy) * p.W + ix] =
             sm.cnt[i] == 0xffff ? 1.0f                                            // :68-70
                                 : __double2float_rn(__dsub_rn(1.0, (double)sm.ap[i]));  // :181-182
+    }
+    if (MODE == SOFT_GATHER) {
+      for (int r = warp; r < NR; r += kSoftWarps) {
+        const int aidx = sm.ract[r];
+        if (aidx >= 0 && aidx < pb.cap) {
+          const int c = sm.cnt[(((r / RX) * 4 + ly) << BLK_LOG2) + (r % RX) * 8 + lx];
+          pb.act_cnt[(long long)aidx * 32 + lane] = (unsigned short)(c == 0xffff ? 0 : c);
+        }
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Pair kernels.  SOFT_GATHER left, for every active region, the first-knum face ids of
+// each pixel in the pair buffer.  Evaluation and gradient then run with ONE WARP PER
+// ACTIVE REGION (lane = pixel, hits walked in order), i.e. spread over the whole GPU
+// however unevenly the silhouette is distributed over the screen blocks.
+// ---------------------------------------------------------------------------
+constexpr int kPairWarps = 8;
+
+__device__ __forceinline__ void load_scaled_coords(const BinJob& j, int b, int f, float (&X)[6]) {
+  const long long gi = (long long)b * j.view_stride + f;
+  const float2* q = reinterpret_cast<const float2*>(j.img + gi * 6);
+  float2 v0 = __ldg(q), v1 = __ldg(q + 1), v2 = __ldg(q + 2);
+  if (!j.prescaled) {  // fl(v * mult), as torch does at dibr.py:32
+    v0.x = __fmul_rn(v0.x, j.mult); v0.y = __fmul_rn(v0.y, j.mult);
+    v1.x = __fmul_rn(v1.x, j.mult); v1.y = __fmul_rn(v1.y, j.mult);
+    v2.x = __fmul_rn(v2.x, j.mult); v2.y = __fmul_rn(v2.y, j.mult);
+  }
+  X[0] = v0.x; X[1] = v0.y; X[2] = v1.x; X[3] = v1.y; X[4] = v2.x; X[5] = v2.y;
+}
+
+// Decodes the active region `act` of the pair buffer for this lane.  Returns false (for
+// the whole warp) when there is nothing to do.
+__device__ __forceinline__ bool pair_region(const PairBuf& pb, const Plan& p, long long act,
+                                            int lane, int& b, int& ix, int& iy, int& cnt) {
+  if (pairs_overflowed(pb)) return false;
+  if (act >= (long long)pb.cursor[1]) return false;
+  const int nrx = (p.W + 7) >> 3, nry = (p.H + 3) >> 2;
+  const int rid = pb.act_region[act];
+  b = rid / (nrx * nry);
+  const int rr = rid - b * nrx * nry;
+  ix = (rr % nrx) * 8 + (lane & 7);
+  iy = (rr / nrx) * 4 + (lane >> 3);
+  cnt = pb.act_cnt[act * 32 + lane];
+  return true;
+}
+
+__global__ void __launch_bounds__(kPairWarps * 32)
+softmask_pairs_eval_kernel(const SoftArgs a, const Plan p) {
+  const PairBuf& pb = a.pairs;
+  const int lane = lane_id();
+  const long long act = (long long)blockIdx.x * kPairWarps + (threadIdx.x >> 5);
+  int b, ix, iy, cnt;
+  if (!pair_region(pb, p, act, lane, b, ix, iy, cnt)) return;
+  const Grid g = make_grid(a.job.mult, p.W, p.H);
+  const float mult = a.job.mult;
+  const float four_mm = __fmul_rn(__fmul_rn(mult, 4.f), mult);
+  const float x0 = pix_x(g, ix), y0 = pix_y(g, iy);
+  const int mx = __reduce_max_sync(DIBR_FULL_MASK, cnt);
+  float ap = 1.0f;
+  for (int h = 0; h < mx; h++) {
+    const int sg = pb.act_seg[act * pb.nseg + h / kPairSegHits];  // warp-uniform
+    if (h < cnt) {
+      const long long slot = (long long)sg * kPairSegSlots + (h % kPairSegHits) * 32 + lane;
+      float X[6];
+      load_scaled_coords(a.job, b, pb.face[slot], X);
+      const double inv[3] = {edge_inv(X[0], X[1], X[2], X[3]), edge_inv(X[2], X[3], X[4], X[5]),
+                             edge_inv(X[4], X[5], X[0], X[1])};
+      float prob;
+      int edgeid;
+      soft_eval(x0, y0, X, inv, four_mm, a.sigmainv, mult, prob, edgeid);
+      pb.prob[slot] = prob;
+      pb.type[slot] = (unsigned char)(edgeid + 1);
+      ap = __double2float_rn(__dmul_rn((double)ap, __dsub_rn(1.0, (double)prob)));  // :176-177
+    }
+  }
+  if (cnt > 0)
+    a.mask[((long long)b * p.H + iy) * p.W + ix] =
+        __double2float_rn(__dsub_rn(1.0, (double)ap));  // :181-182
+}
+
+__global__ void __launch_bounds__(kPairWarps * 32)
+softmask_pairs_grad_kernel(const SoftArgs a, const Plan p) {
+  const PairBuf& pb = a.pairs;
+  const int lane = lane_id();
+  const long long act = (long long)blockIdx.x * kPairWarps + (threadIdx.x >> 5);
+  int b, ix, iy, cnt;
+  if (!pair_region(pb, p, act, lane, b, ix, iy, cnt)) return;
+  const Grid g = make_grid(a.job.mult, p.W, p.H);
+  const float mult = a.job.mult;
+  const float x0 = pix_x(g, ix), y0 = pix_y(g, iy);
+  float dLdp = 0.f, allprob = 0.f;
+  if (cnt > 0) {
+    const long long pix = ((long long)b * p.H + iy) * p.W + ix;
+    dLdp = a.grad_mask[pix];
+    allprob = a.mask_in[pix];
+  }
+  const int mx = __reduce_max_sync(DIBR_FULL_MASK, cnt);
+  for (int h = 0; h < mx; h++) {
+    const int sg = pb.act_seg[act * pb.nseg + h / kPairSegHits];
+    if (h < cnt) {
+      const long long slot = (long long)sg * kPairSegSlots + (h % kPairSegHits) * 32 + lane;
+      const int f = pb.face[slot];
+      float X[6];
+      load_scaled_coords(a.job, b, f, X);
+      const int eid = (int)pb.type[slot] - 1;
+      double inv_e = 0.0;
+      if (eid < 3) {
+        const int v2 = (eid + 1) % 3;
+        inv_e = edge_inv(pick3(eid, X[0], X[2], X[4]), pick3(eid, X[1], X[3], X[5]),
+                         pick3(v2, X[0], X[2], X[4]), pick3(v2, X[1], X[3], X[5]));
+      }
+      float gv[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      soft_grad(x0, y0, X, eid, pb.prob[slot], allprob, dLdp, a.sigmainv, mult, inv_e, gv);
+      float* gp = a.grad_img + ((long long)b * a.job.view_stride + f) * 6;
+#pragma unroll
+      for (int i = 0; i < 6; i++)
+        if (gv[i] != 0.f) atomicAdd(gp + i, gv[i]);
     }
   }
 }
@@ -416,7 +593,8 @@ static cudaError_t launch_soft_mode(const SoftArgs& a, const Plan& p, cudaStream
       if (e != cudaSuccess) return e;
       attr5 = true;
     }
-    prof_begin(MODE == SOFT_BWD ? K_SOFT_BWD : K_SOFT_FWD, st);
+    prof_begin(MODE == SOFT_BWD ? K_SOFT_BWD : (MODE == SOFT_GATHER ? K_SOFT_GATHER : K_SOFT_FWD),
+               st);
     softmask_kernel<5, MODE><<<grid, kSoftThreads, smem, st>>>(a, p);
   } else {
     const int smem = (int)sizeof(SoftSmem<6, MODE>);
@@ -426,15 +604,35 @@ static cudaError_t launch_soft_mode(const SoftArgs& a, const Plan& p, cudaStream
       if (e != cudaSuccess) return e;
       attr6 = true;
     }
-    prof_begin(MODE == SOFT_BWD ? K_SOFT_BWD : K_SOFT_FWD, st);
+    prof_begin(MODE == SOFT_BWD ? K_SOFT_BWD : (MODE == SOFT_GATHER ? K_SOFT_GATHER : K_SOFT_FWD),
+               st);
     softmask_kernel<6, MODE><<<grid, kSoftThreads, smem, st>>>(a, p);
   }
   prof_end(st);
   return cudaGetLastError();
 }
 
+cudaError_t launch_softmask_pairs_eval(const SoftArgs& a, const Plan& p, cudaStream_t st) {
+  if (a.pairs.cap <= 0) return cudaSuccess;
+  prof_begin(K_SOFT_EVAL, st);
+  softmask_pairs_eval_kernel<<<(a.pairs.cap + kPairWarps - 1) / kPairWarps, kPairWarps * 32, 0,
+                               st>>>(a, p);
+  prof_end(st);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_softmask_pairs_grad(const SoftArgs& a, const Plan& p, cudaStream_t st) {
+  if (a.pairs.cap <= 0) return cudaSuccess;
+  prof_begin(K_SOFT_GRAD, st);
+  softmask_pairs_grad_kernel<<<(a.pairs.cap + kPairWarps - 1) / kPairWarps, kPairWarps * 32, 0,
+                               st>>>(a, p);
+  prof_end(st);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_softmask(const SoftArgs& a, int mode, const Plan& p, cudaStream_t st) {
   switch (mode) {
+    case SOFT_GATHER: return launch_soft_mode<SOFT_GATHER>(a, p, st);
     case SOFT_FWD: return launch_soft_mode<SOFT_FWD>(a, p, st);
     case SOFT_FWD_DENSE: return launch_soft_mode<SOFT_FWD_DENSE>(a, p, st);
     default: return launch_soft_mode<SOFT_BWD>(a, p, st);

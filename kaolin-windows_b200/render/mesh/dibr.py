@@ -42,21 +42,22 @@ class DibrSoftMaskB200(Function):
         with torch.cuda.device(dev):
             st = _stream(dev)
 
-            def call(ws, ws_bytes, cap_r, cap_s, needed):
+            def call(ws, ws_bytes, cap_r, cap_s, cap_p, needed):
                 return lib.dibr_softmask_fwd(
                     B, F, H, W, _ptr(img), 0, None, _ptr(sel), float(sigmainv), margin, int(knum),
                     float(multiplier), _ptr(mask), None, None, None, ws, ws_bytes, cap_r, cap_s,
-                    needed, st)
+                    cap_p, needed, st)
 
-            ws, cap_r, cap_s = _workspace.run("soft", dev, B, F, H, W, False, True, call)
+            ws, cap_r, cap_s, cap_p = _workspace.run("soft", dev, B, F, H, W, False, True, call,
+                                                     int(knum))
         ctx.save_for_backward(img, sel, mask, ws)
-        ctx.args = (float(sigmainv), margin, int(knum), float(multiplier), cap_r, cap_s)
+        ctx.args = (float(sigmainv), margin, int(knum), float(multiplier), cap_r, cap_s, cap_p)
         return mask
 
     @staticmethod
     def backward(ctx, grad_soft_mask):
         img, sel, mask, ws = ctx.saved_tensors
-        sigmainv, margin, knum, multiplier, cap_r, cap_s = ctx.args
+        sigmainv, margin, knum, multiplier, cap_r, cap_s, cap_p = ctx.args
         B, F = img.shape[:2]
         H, W = sel.shape[1:]
         grad = _prep(grad_soft_mask, "grad_soft_mask")
@@ -65,7 +66,7 @@ class DibrSoftMaskB200(Function):
             rc = _lib.lib().dibr_softmask_bwd(
                 B, F, H, W, _ptr(img), 0, None, _ptr(sel), sigmainv, margin, knum, multiplier,
                 _ptr(grad), _ptr(mask), _ptr(grad_img), _ptr(ws), ws.numel(), cap_r, cap_s,
-                _stream(img.device))
+                cap_p, _stream(img.device))
         _lib.check(rc, "dibr_softmask_bwd")
         return grad_img, None, None, None, None, None
 
@@ -117,22 +118,24 @@ class DibrRasterizationB200(Function):
         with torch.cuda.device(dev):
             st = _stream(dev)
 
-            def call(ws, ws_bytes, cap_r, cap_s, needed):
+            def call(ws, ws_bytes, cap_r, cap_s, cap_p, needed):
                 return lib.dibr_render_fwd(
                     B, F, H, W, D, _ptr(z), _ptr(img), _ptr(feat), _ptr(nz), float(sigmainv),
                     margin, int(knum), float(multiplier), float(eps), _ptr(idx), _ptr(out),
-                    _ptr(mask), ws, ws_bytes, cap_r, cap_s, needed, st)
+                    _ptr(mask), ws, ws_bytes, cap_r, cap_s, cap_p, needed, st)
 
-            ws, cap_r, cap_s = _workspace.run("render", dev, B, F, H, W, True, True, call)
+            ws, cap_r, cap_s, cap_p = _workspace.run("render", dev, B, F, H, W, True, True, call,
+                                                     int(knum))
         ctx.save_for_backward(idx, img, feat, mask, ws)
         ctx.mark_non_differentiable(idx)
-        ctx.args = (float(sigmainv), margin, int(knum), float(multiplier), float(eps), cap_r, cap_s)
+        ctx.args = (float(sigmainv), margin, int(knum), float(multiplier), float(eps), cap_r, cap_s,
+                    cap_p)
         return out, mask, idx
 
     @staticmethod
     def backward(ctx, grad_features, grad_soft_mask, grad_face_idx):
         idx, img, feat, mask, ws = ctx.saved_tensors
-        sigmainv, margin, knum, multiplier, eps, cap_r, cap_s = ctx.args
+        sigmainv, margin, knum, multiplier, eps, cap_r, cap_s, cap_p = ctx.args
         B, F = img.shape[:2]
         H, W = idx.shape[1:]
         D = feat.shape[-1]
@@ -151,7 +154,8 @@ class DibrRasterizationB200(Function):
                 gm = _prep(grad_soft_mask, "grad_soft_mask")
                 rc = lib.dibr_softmask_bwd(B, F, H, W, _ptr(img), 0, None, _ptr(idx), sigmainv,
                                            margin, knum, multiplier, _ptr(gm), _ptr(mask),
-                                           _ptr(grad_img), _ptr(ws), ws.numel(), cap_r, cap_s, st)
+                                           _ptr(grad_img), _ptr(ws), ws.numel(), cap_r, cap_s,
+                                           cap_p, st)
                 _lib.check(rc, "dibr_softmask_bwd")
         return (None, None, None, grad_img, grad_feat, None, None, None, None, None, None)
 

@@ -68,7 +68,7 @@ class RasterizeB200(Function):
         with torch.cuda.device(dev):
             st = _stream(dev)
 
-            def call(ws, ws_bytes, cap_r, cap_s, needed):
+            def call(ws, ws_bytes, cap_r, cap_s, cap_p, needed):
                 return lib.dibr_rasterize_fwd(
                     B, F, height, width, D, _ptr(z), _ptr(img), _ptr(feat), _ptr(valid), None,
                     0, None, None, float(multiplier), float(eps), _ptr(idx), _ptr(out), None,

@@ -44,7 +44,7 @@ def test_workspace_planning_without_gpu():
     h = _lib.lib()
     fixed = h.dibr_workspace_fixed_bytes(8, 70000, 512, 512)
     assert fixed > 0 and fixed % 256 == 0
-    assert h.dibr_workspace_bytes_for(8, 70000, 512, 512, 10, 20) == fixed + 4 * 30
+    assert h.dibr_workspace_bytes_for(8, 70000, 512, 512, 10, 20, 0, 0) == (fixed + 4 * 30 + 255) // 256 * 256
     assert h.dibr_workspace_fixed_bytes(1, 10, 0, 16) == _lib.DIBR_E_INVALID
     assert "invalid sizes" in _lib.last_error()
     # larger images use larger bins, never more than 1024 per view

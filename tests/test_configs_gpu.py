@@ -178,3 +178,37 @@ def test_full_size_properties(kal):
     px = 1000.0 / W * (2 * x + 1 - W).float()
     fx = img[b, sel][..., 0] * 1000
     assert ((px >= fx.min(dim=1)[0]) & (px < fx.max(dim=1)[0])).all()
+
+
+@pytest.mark.parametrize("mode", ["tiny_pair_buffer", "pairs_off"])
+def test_soft_mask_fallback_paths_match_pair_path(kal, mode):
+    """The pair path (gather -> evaluate -> gradient over saved pairs) and the
+    self-contained kernels it falls back to when the pair buffer overflows (decided on the
+    device) or is switched off compute the same forward bit for bit and the same gradient
+    up to the order of the float atomics."""
+    from kaolin_windows_b200 import _workspace
+    inp = wl.make_config("cfg5_256x2k_128", device=DEV, views=6)
+    z, img, feat, nz = (inp[k] for k in ("face_vertices_z", "face_vertices_image",
+                                         "face_features", "face_normals_z"))
+    g2 = torch.rand((6, 128, 128), device=DEV, generator=torch.Generator(device=DEV).manual_seed(5))
+
+    def run():
+        img_l = img.clone().requires_grad_(True)
+        out, mask, idx = kal.render.mesh.dibr_rasterization(128, 128, z, img_l, feat, nz)
+        (mask * g2).sum().backward()
+        m2 = kal.render.mesh.dibr_soft_mask(img, idx)
+        return mask.detach(), img_l.grad, m2
+
+    m_ref, g_ref, m2_ref = run()
+    assert ((m_ref > 0) & (m_ref < 1)).sum() > 500
+    old = (_workspace.USE_PAIRS, _workspace.PAIR_CAP_OVERRIDE)
+    try:
+        if mode == "pairs_off":
+            _workspace.USE_PAIRS = False
+        else:
+            _workspace.PAIR_CAP_OVERRIDE = 3
+        m, g, m2 = run()
+    finally:
+        _workspace.USE_PAIRS, _workspace.PAIR_CAP_OVERRIDE = old
+    assert torch.equal(m, m_ref) and torch.equal(m2, m2_ref) and torch.equal(m2, m)
+    assert rel_err(g, g_ref) < 1e-5
