@@ -161,6 +161,7 @@ cudaError_t launch_raster_forward(const RasterArgs&, const Plan&, cudaStream_t);
 cudaError_t launch_raster_backward(const RasterBwdArgs&, cudaStream_t);
 cudaError_t launch_softmask(const SoftArgs&, int mode, const Plan&, cudaStream_t);
 cudaError_t launch_softmask_dense_backward(const SoftDenseBwdArgs&, cudaStream_t);
+cudaError_t launch_softmask_gather(const SoftArgs&, const Plan&, cudaStream_t);
 cudaError_t launch_softmask_pairs_eval(const SoftArgs&, const Plan&, cudaStream_t);
 cudaError_t launch_softmask_pairs_grad(const SoftArgs&, const Plan&, cudaStream_t);
 

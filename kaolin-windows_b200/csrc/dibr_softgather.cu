@@ -1,0 +1,280 @@
+// dibr_softgather.cu -- soft mask, step 1: which faces influence which pixel.
+//
+// For every pixel NOT covered by the rasterizer the reference keeps the first `knum` faces,
+// in ascending face order, whose enlarged box contains the pixel centre
+// (dibr_soft_mask_cuda.cu:80-97,165-171).  This kernel finds exactly those (pixel, face)
+// pairs and appends them to the pair buffer (PairBuf, dibr_common.cuh); the arithmetic of
+// the mask itself runs afterwards, pair-parallel, in softmask_pairs_eval_kernel.
+//
+// One CTA per screen block.  Per chunk of the bin's (ascending) face list:
+//   stage      one face per thread: the EXACT pixel rectangle of its enlarged box inside
+//              the block (conservative range trimmed with the reference's half-open float
+//              test; pix_x/pix_y are monotone), and from it the set of 8x4-pixel regions
+//              the face touches as a bit mask;
+//   transpose  32 faces x 32 regions bit matrices are transposed with __ballot_sync, so
+//              every region gets, per 32 staged faces, one word of candidate faces -- the
+//              faces x regions pre-test costs one ballot per (face, 32 regions) instead of
+//              a compare per (face, region);
+//   gather     warps pull regions from a shared queue; lane = pixel; the region's candidate
+//              words are walked in face order with an integer rectangle test per pixel,
+//              hits are appended until the pixel holds knum faces.
+// A region closes when all its uncovered pixels hold knum faces; the CTA stops when every
+// region is closed.
+#include "dibr_common.cuh"
+
+namespace dibr {
+
+constexpr int kGWarps = 8;
+constexpr int kGThreads = kGWarps * 32;
+constexpr int kGChunk = 512;            // staged faces per chunk
+constexpr int kGWords = kGChunk / 32;   // candidate words per region and chunk
+constexpr int kGSeg = 32;               // candidates processed between two flushes
+
+template <int BLK_LOG2>
+struct GatherSmem {
+  static constexpr int BLK = 1 << BLK_LOG2;
+  static constexpr int NPX = BLK * BLK;
+  static constexpr int NR = NPX / 32;   // regions (8 wide, 4 high)
+  static constexpr int RX = BLK / 8;    // regions per row
+  static constexpr int NW = NR / 32;    // 32-region words per face
+  unsigned short cnt[NPX];              // faces held; 0xffff = covered / outside the image
+  int ract[NR];                         // active-region slot in the pair buffer, -1 = none
+  unsigned char rseg[NR];               // pair segments owned
+  unsigned char ropen[NR];
+  int face[kGChunk];
+  unsigned rect[kGChunk];               // x_lo | x_hi << 8 | y_lo << 16 | y_hi << 24, block-relative
+  unsigned cand[NR][kGWords];
+  unsigned short hit[kGWarps][kGSeg][32];
+  int next;
+};
+
+template <int BLK_LOG2>
+__global__ void __launch_bounds__(kGThreads)
+softmask_gather_kernel(const SoftArgs a, const Plan p) {
+  using Smem = GatherSmem<BLK_LOG2>;
+  constexpr int BLK = Smem::BLK, NPX = Smem::NPX, NR = Smem::NR, RX = Smem::RX, NW = Smem::NW;
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  Smem& sm = *reinterpret_cast<Smem*>(s_raw);
+  const PairBuf& pb = a.pairs;
+
+  const int tid = threadIdx.x, lane = lane_id(), warp = tid >> 5;
+  const int b = blockIdx.z;
+  const int bx0 = blockIdx.x << BLK_LOG2, by0 = blockIdx.y << BLK_LOG2;
+  const int bx1 = min(bx0 + BLK, p.W) - 1, by1 = min(by0 + BLK, p.H) - 1;
+  const Grid g = make_grid(a.job.mult, p.W, p.H);
+  const int K = min(a.K, 0xfffe);
+  const int lx = lane & 7, ly = lane >> 3;
+  const int nrx = (p.W + 7) >> 3, nry = (p.H + 3) >> 2;  // regions of a view
+
+  // ---- pixel state; covered pixels get their final value right away
+  for (int i = tid; i < NPX; i += kGThreads) {
+    const int ix = bx0 + (i & (BLK - 1)), iy = by0 + (i >> BLK_LOG2);
+    bool uncovered = false;
+    if (ix < p.W && iy < p.H) {
+      const long long pix = ((long long)b * p.H + iy) * p.W + ix;
+      uncovered = a.sel[pix] < 0;
+      // 1 for covered pixels (:68-70); 1 - 1 = 0 for uncovered ones until the pair
+      // evaluation overwrites those that hold faces
+      a.mask[pix] = uncovered ? 0.0f : 1.0f;
+    }
+    sm.cnt[i] = uncovered ? 0 : 0xffff;
+  }
+  __syncthreads();
+  bool any_open = false;
+  for (int r = warp; r < NR; r += kGWarps) {
+    const int pl = (((r / RX) * 4 + ly) << BLK_LOG2) + (r % RX) * 8 + lx;
+    const unsigned m = __ballot_sync(DIBR_FULL_MASK, (int)sm.cnt[pl] < K);
+    if (lane == 0) {
+      sm.ropen[r] = m != 0;
+      sm.rseg[r] = 0;
+      sm.ract[r] = -1;
+    }
+    any_open |= m != 0;
+  }
+  if (!__syncthreads_or(any_open)) return;
+
+  const int shift = p.bin_log2 - BLK_LOG2;
+  const int bin = (blockIdx.y >> shift) * p.nbx + (blockIdx.x >> shift);
+  const long long row = (long long)b * p.NB + bin;
+  const long long start = a.job.start[row];
+  long long n = a.job.count[row];
+  if (start + n > a.job.capacity) n = max(0ll, a.job.capacity - start);
+
+  for (long long base = 0; base < n; base += kGChunk) {
+    __syncthreads();
+    bool mine = false;
+    for (int r = tid; r < NR; r += kGThreads) mine |= sm.ropen[r] != 0;
+    if (tid == 0) sm.next = 0;
+    if (!__syncthreads_or(mine)) break;
+    const int nc = (int)min((long long)kGChunk, n - base);
+
+    // ---- stage + transpose (t / 32 is warp-uniform)
+    for (int t = tid; t < kGChunk; t += kGThreads) {
+      unsigned rmask[NW];
+#pragma unroll
+      for (int w = 0; w < NW; w++) rmask[w] = 0u;
+      if (t < nc) {
+        const int f = a.job.list[start + base + t];
+        Face2D fc;
+        int x_lo, x_hi, y_lo, y_hi;
+        if (load_face2d(a.job, b, f, fc) &&
+            pixel_range(g, fc.xmin, fc.ymin, fc.xmax, fc.ymax, x_lo, x_hi, y_lo, y_hi)) {
+          x_lo = max(x_lo, bx0); x_hi = min(x_hi, bx1);
+          y_lo = max(y_lo, by0); y_hi = min(y_hi, by1);
+          // exact half-open test of the reference (:89-97) on the range ends
+          while (x_lo <= x_hi && pix_x(g, x_lo) < fc.xmin) x_lo++;
+          while (x_lo <= x_hi && pix_x(g, x_hi) >= fc.xmax) x_hi--;
+          while (y_lo <= y_hi && pix_y(g, y_lo) >= fc.ymax) y_lo++;
+          while (y_lo <= y_hi && pix_y(g, y_hi) < fc.ymin) y_hi--;
+          if (x_lo <= x_hi && y_lo <= y_hi) {
+            const int xl = x_lo - bx0, xh = x_hi - bx0, yl = y_lo - by0, yh = y_hi - by0;
+            sm.rect[t] = (unsigned)xl | ((unsigned)xh << 8) | ((unsigned)yl << 16) |
+                         ((unsigned)yh << 24);
+            sm.face[t] = f;
+            const unsigned cols = (2u << (xh >> 3)) - (1u << (xl >> 3));  // RX bits
+            for (int ry = yl >> 2; ry <= (yh >> 2); ry++) {
+              const int bit = ry * RX;  // RX divides 32: a row of regions never straddles words
+#pragma unroll
+              for (int w = 0; w < NW; w++)
+                if ((bit >> 5) == w) rmask[w] |= cols << (bit & 31);
+            }
+          }
+        }
+      }
+      const int grp = t >> 5;
+#pragma unroll
+      for (int w = 0; w < NW; w++) {
+        unsigned keep = 0u;
+        if (__any_sync(DIBR_FULL_MASK, rmask[w] != 0u)) {
+#pragma unroll
+          for (int r = 0; r < 32; r++) {
+            const unsigned v = __ballot_sync(DIBR_FULL_MASK, (rmask[w] >> r) & 1u);
+            if (lane == r) keep = v;
+          }
+        }
+        sm.cand[w * 32 + lane][grp] = keep;
+      }
+    }
+    __syncthreads();
+
+    // ---- gather
+    while (true) {
+      int r = 0;
+      if (lane == 0) r = atomicAdd(&sm.next, 1);
+      r = __shfl_sync(DIBR_FULL_MASK, r, 0);
+      if (r >= NR) break;
+      if (!sm.ropen[r]) continue;
+      const unsigned myw = lane < kGWords ? sm.cand[r][lane] : 0u;
+      const unsigned gmask = __ballot_sync(DIBR_FULL_MASK, myw != 0u);
+      if (!gmask) continue;
+      const int px = (r % RX) * 8 + lx, py = (r / RX) * 4 + ly;  // block-relative
+      const int pl = (py << BLK_LOG2) + px;
+      int cnt = sm.cnt[pl];
+      bool open = cnt < K;
+      int nbuf = 0, proc = 0;
+
+      auto flush = [&]() {
+        // append the hits gathered since the last flush to the region's pair segments
+        // (allocated on demand: one cursor atomic per region per growth step)
+        const int mx = __reduce_max_sync(DIBR_FULL_MASK, cnt == 0xffff ? 0 : cnt);
+        const int need = (mx + kPairSegHits - 1) / kPairSegHits;
+        int aidx = sm.ract[r];
+        const int have = sm.rseg[r];
+        if (need > have) {
+          long long sbase = 0;
+          if (lane == 0) {
+            if (aidx < 0) {
+              const unsigned long long v = atomicAdd(pb.cursor + 1, 1ull);
+              aidx = v < (unsigned long long)pb.cap ? (int)v : 0x7fffffff;
+              if (aidx < pb.cap)
+                pb.act_region[aidx] = (b * nry + (by0 >> 2) + r / RX) * nrx + (bx0 >> 3) + r % RX;
+            }
+            sbase = (long long)atomicAdd(pb.cursor, (unsigned long long)(need - have));
+          }
+          aidx = __shfl_sync(DIBR_FULL_MASK, aidx, 0);
+          sbase = __shfl_sync(DIBR_FULL_MASK, sbase, 0);
+          if (aidx < pb.cap)
+            for (int q = have + lane; q < need; q += 32) {
+              const long long sg = sbase + (q - have);
+              pb.act_seg[(long long)aidx * pb.nseg + q] = sg < pb.cap ? (int)sg : -1;
+            }
+          if (lane == 0) { sm.ract[r] = aidx; sm.rseg[r] = (unsigned char)need; }
+          __syncwarp();
+        }
+        if (aidx < pb.cap) {
+          for (int j = 0; j < nbuf; j++) {
+            const int hp = cnt - nbuf + j;
+            const int sg = pb.act_seg[(long long)aidx * pb.nseg + hp / kPairSegHits];
+            if (sg >= 0)
+              pb.face[(long long)sg * kPairSegSlots + (hp % kPairSegHits) * 32 + lane] =
+                  sm.face[sm.hit[warp][j][lane]];
+          }
+        }
+        nbuf = 0;
+        proc = 0;
+      };
+
+      unsigned gm = gmask;
+      bool done = false;
+      while (gm && !done) {
+        const int grp = __ffs(gm) - 1;
+        gm &= gm - 1;
+        unsigned m = __shfl_sync(DIBR_FULL_MASK, myw, grp);
+        while (m) {
+          const int s = (grp << 5) + __ffs(m) - 1;
+          m &= m - 1;
+          const unsigned rc = sm.rect[s];
+          const bool in = open && px >= (int)(rc & 0xff) && px <= (int)((rc >> 8) & 0xff) &&
+                          py >= (int)((rc >> 16) & 0xff) && py <= (int)(rc >> 24);
+          if (in) {
+            sm.hit[warp][nbuf][lane] = (unsigned short)s;
+            nbuf++;
+            if (++cnt >= K) open = false;  // :170-171
+          }
+          if (++proc == kGSeg) {
+            const bool any_hit = __any_sync(DIBR_FULL_MASK, nbuf > 0);
+            if (any_hit) flush();
+            proc = 0;
+            if (!__any_sync(DIBR_FULL_MASK, open)) { m = 0; done = true; }
+          }
+        }
+      }
+      if (__any_sync(DIBR_FULL_MASK, nbuf > 0)) flush();
+      sm.cnt[pl] = (unsigned short)cnt;
+      const unsigned still = __ballot_sync(DIBR_FULL_MASK, open);
+      if (lane == 0) sm.ropen[r] = still != 0;
+    }
+  }
+
+  // ---- per-pixel hit counts of the regions that became active
+  __syncthreads();
+  for (int r = warp; r < NR; r += kGWarps) {
+    const int aidx = sm.ract[r];
+    if (aidx >= 0 && aidx < pb.cap) {
+      const int c = sm.cnt[(((r / RX) * 4 + ly) << BLK_LOG2) + (r % RX) * 8 + lx];
+      pb.act_cnt[(long long)aidx * 32 + lane] = (unsigned short)(c == 0xffff ? 0 : c);
+    }
+  }
+}
+
+cudaError_t launch_softmask_gather(const SoftArgs& a, const Plan& p, cudaStream_t st) {
+  dim3 grid(p.nkx, p.nky, p.B);
+  prof_begin(K_SOFT_GATHER, st);
+  if (p.blk_log2 == 5) {
+    softmask_gather_kernel<5><<<grid, kGThreads, sizeof(GatherSmem<5>), st>>>(a, p);
+  } else {
+    static bool once = false;
+    if (!once) {
+      cudaError_t e = cudaFuncSetAttribute(softmask_gather_kernel<6>,
+                                           cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           (int)sizeof(GatherSmem<6>));
+      if (e != cudaSuccess) return e;
+      once = true;
+    }
+    softmask_gather_kernel<6><<<grid, kGThreads, sizeof(GatherSmem<6>), st>>>(a, p);
+  }
+  prof_end(st);
+  return cudaGetLastError();
+}
+
+}  // namespace dibr

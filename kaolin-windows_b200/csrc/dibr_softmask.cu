@@ -169,8 +169,6 @@ struct SoftSmem {
   unsigned char ty[kSoftWarps][kSeg][32];
   int off[kSoftWarps][33];
   unsigned char ropen[NR];
-  unsigned char rseg[NR];        // SOFT_GATHER: pair segments the region owns so far
-  int ract[NR];                  // SOFT_GATHER: active-region slot, -1 = none yet
   int next;
   float acc[MODE == SOFT_BWD ? kSoftChunk : 1][6];
 };
@@ -188,8 +186,6 @@ softmask_kernel(const SoftArgs a, const Plan p) {
   // with a pair buffer attached the self-contained kernels are only the overflow fallback
   if ((MODE == SOFT_FWD || MODE == SOFT_BWD) && a.pairs.cap > 0 && !pairs_overflowed(a.pairs))
     return;
-  const PairBuf& pb = a.pairs;
-  const int nrx = (p.W + 7) >> 3, nry = (p.H + 3) >> 2;  // regions of a view
   const int b = blockIdx.z;
   const int bx0 = blockIdx.x << BLK_LOG2, by0 = blockIdx.y << BLK_LOG2;
   const Grid g = make_grid(a.job.mult, p.W, p.H);
@@ -211,11 +207,7 @@ softmask_kernel(const SoftArgs a, const Plan p) {
     const int pl = (((r / RX) * 4 + ly) << BLK_LOG2) + (r % RX) * 8 + lx;
     const bool open = (int)sm.cnt[pl] < K;
     const unsigned m = __ballot_sync(DIBR_FULL_MASK, open);
-    if (lane == 0) {
-      sm.ropen[r] = m != 0;
-      sm.rseg[r] = 0;
-      sm.ract[r] = -1;
-    }
+    if (lane == 0) sm.ropen[r] = m != 0;
   }
 
   const int shift = p.bin_log2 - BLK_LOG2;
@@ -240,11 +232,9 @@ softmask_kernel(const SoftArgs a, const Plan p) {
       sm.x[0][t] = fc.ax; sm.x[1][t] = fc.ay; sm.x[2][t] = fc.bx;
       sm.x[3][t] = fc.by; sm.x[4][t] = fc.cx; sm.x[5][t] = fc.cy;
       sm.bb[0][t] = fc.xmin; sm.bb[1][t] = fc.ymin; sm.bb[2][t] = fc.xmax; sm.bb[3][t] = fc.ymax;
-      if (MODE != SOFT_GATHER) {
-        sm.inv[0][t] = edge_inv(fc.ax, fc.ay, fc.bx, fc.by);
-        sm.inv[1][t] = edge_inv(fc.bx, fc.by, fc.cx, fc.cy);
-        sm.inv[2][t] = edge_inv(fc.cx, fc.cy, fc.ax, fc.ay);
-      }
+      sm.inv[0][t] = edge_inv(fc.ax, fc.ay, fc.bx, fc.by);
+      sm.inv[1][t] = edge_inv(fc.bx, fc.by, fc.cx, fc.cy);
+      sm.inv[2][t] = edge_inv(fc.cx, fc.cy, fc.ax, fc.ay);
       sm.face[t] = f;
       if (MODE == SOFT_BWD) {
 #pragma unroll
@@ -273,48 +263,6 @@ softmask_kernel(const SoftArgs a, const Plan p) {
 
       // evaluate everything gathered so far for this region (all lanes call it together)
       auto flush = [&]() {
-        if (MODE == SOFT_GATHER) {
-          // append this round's hits to the region's pair segments (allocating them on
-          // demand: one cursor atomic per region per growth step)
-          const int mx = __reduce_max_sync(DIBR_FULL_MASK, cnt == 0xffff ? 0 : cnt);
-          const int need = (mx + kPairSegHits - 1) / kPairSegHits;
-          int aidx = sm.ract[r];
-          const int have = sm.rseg[r];
-          if (need > have) {
-            long long base = 0;
-            if (lane == 0) {
-              if (aidx < 0) {
-                const unsigned long long v = atomicAdd(pb.cursor + 1, 1ull);
-                aidx = v < (unsigned long long)pb.cap ? (int)v : 0x7fffffff;
-                if (aidx < pb.cap)
-                  pb.act_region[aidx] =
-                      (b * nry + (by0 >> 2) + r / RX) * nrx + (bx0 >> 3) + r % RX;
-              }
-              base = (long long)atomicAdd(pb.cursor, (unsigned long long)(need - have));
-            }
-            aidx = __shfl_sync(DIBR_FULL_MASK, aidx, 0);
-            base = __shfl_sync(DIBR_FULL_MASK, base, 0);
-            if (aidx < pb.cap)
-              for (int q = have + lane; q < need; q += 32) {
-                const long long sg = base + (q - have);
-                pb.act_seg[(long long)aidx * pb.nseg + q] = sg < pb.cap ? (int)sg : -1;
-              }
-            if (lane == 0) { sm.ract[r] = aidx; sm.rseg[r] = (unsigned char)need; }
-            __syncwarp();
-          }
-          if (aidx < pb.cap) {
-            for (int j = 0; j < nbuf; j++) {
-              const int hp = cnt - nbuf + j;
-              const int sg = pb.act_seg[(long long)aidx * pb.nseg + hp / kPairSegHits];
-              if (sg >= 0)
-                pb.face[(long long)sg * kPairSegSlots + (hp % kPairSegHits) * 32 + lane] =
-                    sm.face[sm.hit[warp][j][lane]];
-            }
-          }
-          nbuf = 0;
-          __syncwarp();
-          return;
-        }
         int incl = nbuf;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
@@ -409,23 +357,12 @@ softmask_kernel(const SoftArgs a, const Plan p) {
 
   if (MODE != SOFT_BWD) {
     __syncthreads();
-    // (SOFT_GATHER: ap is still 1, i.e. 0 for every uncovered pixel; the pixels of active
-    //  regions are overwritten by the pair evaluation kernel)
     for (int i = tid; i < NPX; i += kSoftThreads) {
       const int ix = bx0 + (i & (BLK - 1)), iy = by0 + (i >> BLK_LOG2);
       if (ix < p.W && iy < p.H)
         a.mask[((long long)b * p.H + iy) * p.W + ix] =
             sm.cnt[i] == 0xffff ? 1.0f                                            // :68-70
                                 : __double2float_rn(__dsub_rn(1.0, (double)sm.ap[i]));  // :181-182
-    }
-    if (MODE == SOFT_GATHER) {
-      for (int r = warp; r < NR; r += kSoftWarps) {
-        const int aidx = sm.ract[r];
-        if (aidx >= 0 && aidx < pb.cap) {
-          const int c = sm.cnt[(((r / RX) * 4 + ly) << BLK_LOG2) + (r % RX) * 8 + lx];
-          pb.act_cnt[(long long)aidx * 32 + lane] = (unsigned short)(c == 0xffff ? 0 : c);
-        }
-      }
     }
   }
 }
@@ -593,8 +530,7 @@ static cudaError_t launch_soft_mode(const SoftArgs& a, const Plan& p, cudaStream
       if (e != cudaSuccess) return e;
       attr5 = true;
     }
-    prof_begin(MODE == SOFT_BWD ? K_SOFT_BWD : (MODE == SOFT_GATHER ? K_SOFT_GATHER : K_SOFT_FWD),
-               st);
+    prof_begin(MODE == SOFT_BWD ? K_SOFT_BWD : K_SOFT_FWD, st);
     softmask_kernel<5, MODE><<<grid, kSoftThreads, smem, st>>>(a, p);
   } else {
     const int smem = (int)sizeof(SoftSmem<6, MODE>);
@@ -604,8 +540,7 @@ static cudaError_t launch_soft_mode(const SoftArgs& a, const Plan& p, cudaStream
       if (e != cudaSuccess) return e;
       attr6 = true;
     }
-    prof_begin(MODE == SOFT_BWD ? K_SOFT_BWD : (MODE == SOFT_GATHER ? K_SOFT_GATHER : K_SOFT_FWD),
-               st);
+    prof_begin(MODE == SOFT_BWD ? K_SOFT_BWD : K_SOFT_FWD, st);
     softmask_kernel<6, MODE><<<grid, kSoftThreads, smem, st>>>(a, p);
   }
   prof_end(st);
@@ -632,7 +567,7 @@ cudaError_t launch_softmask_pairs_grad(const SoftArgs& a, const Plan& p, cudaStr
 
 cudaError_t launch_softmask(const SoftArgs& a, int mode, const Plan& p, cudaStream_t st) {
   switch (mode) {
-    case SOFT_GATHER: return launch_soft_mode<SOFT_GATHER>(a, p, st);
+    case SOFT_GATHER: return launch_softmask_gather(a, p, st);
     case SOFT_FWD: return launch_soft_mode<SOFT_FWD>(a, p, st);
     case SOFT_FWD_DENSE: return launch_soft_mode<SOFT_FWD_DENSE>(a, p, st);
     default: return launch_soft_mode<SOFT_BWD>(a, p, st);
