@@ -50,6 +50,10 @@ void prof_end(cudaStream_t st) {
   if (!g_prof.empty()) cudaEventRecord(g_prof.back().e1, st);
 }
 
+#ifdef DIBR_TRACE
+static unsigned long long* g_trace_ptr = nullptr;
+#endif
+
 static inline int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
 
 static int make_plan(int B, int F, int H, int W, Plan& p) {
@@ -84,6 +88,9 @@ static int make_plan(int B, int F, int H, int W, Plan& p) {
     p.off_mat[l] = off; off = align_up(off + (int64_t)B * p.NB * p.nchunks * 4, 256);
   }
   p.fixed_bytes = off;
+#ifdef DIBR_TRACE
+  p.trace = g_trace_ptr;
+#endif
   return DIBR_OK;
 }
 
@@ -187,6 +194,14 @@ static BinJob face_source(const float* img, const float* bbox, const uint8_t* va
 }  // namespace dibr
 
 using namespace dibr;
+
+
+#ifdef DIBR_TRACE
+extern "C" __attribute__((visibility("default"))) int dibr_trace_set(void* ptr) {
+  dibr::g_trace_ptr = (unsigned long long*)ptr;
+  return 0;
+}
+#endif
 
 extern "C" const char* dibr_last_error(void) { return g_err; }
 extern "C" int dibr_version(void) { return 100; }

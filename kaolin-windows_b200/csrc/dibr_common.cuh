@@ -38,6 +38,7 @@ struct Plan {
   int64_t off_total;      // unsigned long long [2] entries needed per list kind
   int64_t off_flags;      // int [B][nkx*nky]      uncovered-pixel count per block
   int64_t fixed_bytes;    // everything above
+  unsigned long long* trace;  // -DDIBR_TRACE builds only, else null
 };
 
 // One binning job = one list kind.  Passed by value to the kernels.
@@ -314,6 +315,33 @@ __device__ __forceinline__ void smem_max64(unsigned long long* addr, unsigned lo
     if (old == assumed) break;
   }
 }
+
+// ----------------------------------------------------------------------- CTA tracing
+// Development aid, compiled in only with -DDIBR_TRACE: every CTA of an instrumented kernel
+// records {start ns, end ns, SM id, user value} at plan.trace[4 * linear block id]
+// (a kernel argument, set through dibr_trace_set; `p` must be the kernel's Plan).
+#ifdef DIBR_TRACE
+__device__ __forceinline__ unsigned long long trace_now() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+#define DIBR_TRACE_BEGIN() const unsigned long long trace_t0_ = trace_now()
+#define DIBR_TRACE_END(user)                                                               \
+  do {                                                                                     \
+    __syncthreads();                                                                       \
+    if (p.trace && threadIdx.x == 0) {                                                        \
+      unsigned smid_;                                                                      \
+      asm volatile("mov.u32 %0, %%smid;" : "=r"(smid_));                                   \
+      unsigned long long* o_ =                                                             \
+          p.trace + 4ull * ((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x); \
+      o_[0] = trace_t0_; o_[1] = trace_now(); o_[2] = smid_; o_[3] = (unsigned long long)(user); \
+    }                                                                                      \
+  } while (0)
+#else
+#define DIBR_TRACE_BEGIN()
+#define DIBR_TRACE_END(user)
+#endif
 
 // ------------------------------------------------------------------------------ misc
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }

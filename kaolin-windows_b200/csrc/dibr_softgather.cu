@@ -15,9 +15,12 @@
 //              every region gets, per 32 staged faces, one word of candidate faces -- the
 //              faces x regions pre-test costs one ballot per (face, 32 regions) instead of
 //              a compare per (face, region);
-//   gather     warps pull regions from a shared queue; lane = pixel; the region's candidate
-//              words are walked in face order with an integer rectangle test per pixel,
-//              hits are appended until the pixel holds knum faces.
+//   gather     warps pull regions from a shared queue; the region's candidates are compacted
+//              and handled 32 at a time, bit-parallel: each candidate lane turns its
+//              rectangle into a mask over the region's 32 pixels, 32 ballots transpose these
+//              into per-pixel candidate masks (bit order = face order), of which each pixel
+//              keeps the first knum - held; hits are staged in shared memory and leave as
+//              whole 128-byte rows.
 // A region closes when all its uncovered pixels hold knum faces; the CTA stops when every
 // region is closed.
 #include "dibr_common.cuh"
@@ -28,7 +31,7 @@ constexpr int kGWarps = 8;
 constexpr int kGThreads = kGWarps * 32;
 constexpr int kGChunk = 512;            // staged faces per chunk
 constexpr int kGWords = kGChunk / 32;   // candidate words per region and chunk
-constexpr int kGSeg = 32;               // candidates processed between two flushes
+constexpr int kGTileK = 32;             // knum up to which a region's hits are staged in smem
 
 template <int BLK_LOG2>
 struct GatherSmem {
@@ -36,7 +39,8 @@ struct GatherSmem {
   static constexpr int NPX = BLK * BLK;
   static constexpr int NR = NPX / 32;   // regions (8 wide, 4 high)
   static constexpr int RX = BLK / 8;    // regions per row
-  static constexpr int NW = NR / 32;    // 32-region words per face
+  static constexpr int NW = NR >= 32 ? NR / 32 : 1;  // 32-region words per face
+  static constexpr int NRW = NR >= 32 ? 32 : NR;     // regions per word
   unsigned short cnt[NPX];              // faces held; 0xffff = covered / outside the image
   int ract[NR];                         // active-region slot in the pair buffer, -1 = none
   unsigned char rseg[NR];               // pair segments owned
@@ -44,7 +48,8 @@ struct GatherSmem {
   int face[kGChunk];
   unsigned rect[kGChunk];               // x_lo | x_hi << 8 | y_lo << 16 | y_hi << 24, block-relative
   unsigned cand[NR][kGWords];
-  unsigned short hit[kGWarps][kGSeg][32];
+  int tile[kGWarps][kGTileK][32];       // hits of the region a warp works on: [hit][pixel]
+  unsigned short clist[kGWarps][kGChunk];  // the region's candidates of the chunk, compacted
   int next;
 };
 
@@ -53,11 +58,13 @@ __global__ void __launch_bounds__(kGThreads)
 softmask_gather_kernel(const SoftArgs a, const Plan p) {
   using Smem = GatherSmem<BLK_LOG2>;
   constexpr int BLK = Smem::BLK, NPX = Smem::NPX, NR = Smem::NR, RX = Smem::RX, NW = Smem::NW;
+  constexpr int NRW = Smem::NRW;
   extern __shared__ __align__(16) unsigned char s_raw[];
   Smem& sm = *reinterpret_cast<Smem*>(s_raw);
   const PairBuf& pb = a.pairs;
 
   const int tid = threadIdx.x, lane = lane_id(), warp = tid >> 5;
+  DIBR_TRACE_BEGIN();
   const int b = blockIdx.z;
   const int bx0 = blockIdx.x << BLK_LOG2, by0 = blockIdx.y << BLK_LOG2;
   const int bx1 = min(bx0 + BLK, p.W) - 1, by1 = min(by0 + BLK, p.H) - 1;
@@ -91,10 +98,14 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
     }
     any_open |= m != 0;
   }
-  if (!__syncthreads_or(any_open)) return;
+  if (!__syncthreads_or(any_open)) {
+    DIBR_TRACE_END(0);
+    return;
+  }
 
-  const int shift = p.bin_log2 - BLK_LOG2;
-  const int bin = (blockIdx.y >> shift) * p.nbx + (blockIdx.x >> shift);
+  // the gather CTA covers a quarter (or less) of a raster block: more, shorter CTAs over
+  // the few blocks the silhouette crosses; each re-stages its parent bin's list
+  const int bin = (by0 >> p.bin_log2) * p.nbx + (bx0 >> p.bin_log2);
   const long long row = (long long)b * p.NB + bin;
   const long long start = a.job.start[row];
   long long n = a.job.count[row];
@@ -147,12 +158,12 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
         unsigned keep = 0u;
         if (__any_sync(DIBR_FULL_MASK, rmask[w] != 0u)) {
 #pragma unroll
-          for (int r = 0; r < 32; r++) {
+          for (int r = 0; r < NRW; r++) {
             const unsigned v = __ballot_sync(DIBR_FULL_MASK, (rmask[w] >> r) & 1u);
             if (lane == r) keep = v;
           }
         }
-        sm.cand[w * 32 + lane][grp] = keep;
+        if (lane < NRW) sm.cand[w * 32 + lane][grp] = keep;
       }
     }
     __syncthreads();
@@ -171,75 +182,136 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
       const int pl = (py << BLK_LOG2) + px;
       int cnt = sm.cnt[pl];
       bool open = cnt < K;
-      int nbuf = 0, proc = 0;
+      // Hits are staged in the warp's shared-memory tile (bank = lane: conflict-free) and
+      // written out row by row when the item ends -- one 128-byte line per row instead of a
+      // 32-line scatter per candidate face, which made the kernel LSU-bound.
+      const bool staged = K <= kGTileK;
+      const int cnt0 = cnt;
+      int (*tile)[32] = sm.tile[warp];
+      // segment ids the region owns: lane q holds segment q (regions with more than 32
+      // segments, knum > 256, read the rest from the table in global memory)
+      int aidx = sm.ract[r];
+      int have = sm.rseg[r];
+      int segreg = -1;
+      if (aidx >= 0 && aidx < pb.cap && lane < have)
+        segreg = pb.act_seg[(long long)aidx * pb.nseg + lane];
 
-      auto flush = [&]() {
-        // append the hits gathered since the last flush to the region's pair segments
-        // (allocated on demand: one cursor atomic per region per growth step)
-        const int mx = __reduce_max_sync(DIBR_FULL_MASK, cnt == 0xffff ? 0 : cnt);
-        const int need = (mx + kPairSegHits - 1) / kPairSegHits;
-        int aidx = sm.ract[r];
-        const int have = sm.rseg[r];
-        if (need > have) {
-          long long sbase = 0;
-          if (lane == 0) {
-            if (aidx < 0) {
-              const unsigned long long v = atomicAdd(pb.cursor + 1, 1ull);
-              aidx = v < (unsigned long long)pb.cap ? (int)v : 0x7fffffff;
-              if (aidx < pb.cap)
-                pb.act_region[aidx] = (b * nry + (by0 >> 2) + r / RX) * nrx + (bx0 >> 3) + r % RX;
-            }
-            sbase = (long long)atomicAdd(pb.cursor, (unsigned long long)(need - have));
+      // Makes sure the region owns segments for `upto` hits per pixel (allocated on demand;
+      // small knum takes all its segments with the first hit, so a region pays the cursor
+      // round trip once).
+      auto ensure = [&](int upto) {
+        int need = (min(upto, K) + kPairSegHits - 1) / kPairSegHits;
+        if (need <= have) return;
+        need = pb.nseg <= 4 ? pb.nseg : min(pb.nseg, max(need, 2 * have));
+        long long sbase = 0;
+        if (lane == 0) {
+          if (aidx < 0) {
+            const unsigned long long v = atomicAdd(pb.cursor + 1, 1ull);
+            aidx = v < (unsigned long long)pb.cap ? (int)v : 0x7fffffff;
+            if (aidx < pb.cap)
+              pb.act_region[aidx] = (b * nry + (by0 >> 2) + r / RX) * nrx + (bx0 >> 3) + r % RX;
           }
-          aidx = __shfl_sync(DIBR_FULL_MASK, aidx, 0);
-          sbase = __shfl_sync(DIBR_FULL_MASK, sbase, 0);
-          if (aidx < pb.cap)
-            for (int q = have + lane; q < need; q += 32) {
-              const long long sg = sbase + (q - have);
-              pb.act_seg[(long long)aidx * pb.nseg + q] = sg < pb.cap ? (int)sg : -1;
-            }
-          if (lane == 0) { sm.ract[r] = aidx; sm.rseg[r] = (unsigned char)need; }
-          __syncwarp();
+          sbase = (long long)atomicAdd(pb.cursor, (unsigned long long)(need - have));
         }
-        if (aidx < pb.cap) {
-          for (int j = 0; j < nbuf; j++) {
-            const int hp = cnt - nbuf + j;
-            const int sg = pb.act_seg[(long long)aidx * pb.nseg + hp / kPairSegHits];
-            if (sg >= 0)
-              pb.face[(long long)sg * kPairSegSlots + (hp % kPairSegHits) * 32 + lane] =
-                  sm.face[sm.hit[warp][j][lane]];
-          }
+        aidx = __shfl_sync(DIBR_FULL_MASK, aidx, 0);
+        sbase = __shfl_sync(DIBR_FULL_MASK, sbase, 0);
+        for (int q = have + lane; q < need; q += 32) {
+          const long long sg = sbase + (q - have);
+          if (aidx < pb.cap) pb.act_seg[(long long)aidx * pb.nseg + q] = sg < pb.cap ? (int)sg : -1;
         }
-        nbuf = 0;
-        proc = 0;
+        if (lane >= have && lane < need) {
+          const long long sg = sbase + (lane - have);
+          segreg = sg < pb.cap ? (int)sg : -1;
+        }
+        if (lane == 0) { sm.ract[r] = aidx; sm.rseg[r] = (unsigned char)need; }
+        have = need;
       };
 
-      unsigned gm = gmask;
-      bool done = false;
-      while (gm && !done) {
-        const int grp = __ffs(gm) - 1;
-        gm &= gm - 1;
-        unsigned m = __shfl_sync(DIBR_FULL_MASK, myw, grp);
-        while (m) {
-          const int s = (grp << 5) + __ffs(m) - 1;
-          m &= m - 1;
-          const unsigned rc = sm.rect[s];
-          const bool in = open && px >= (int)(rc & 0xff) && px <= (int)((rc >> 8) & 0xff) &&
-                          py >= (int)((rc >> 16) & 0xff) && py <= (int)(rc >> 24);
-          if (in) {
-            sm.hit[warp][nbuf][lane] = (unsigned short)s;
-            nbuf++;
-            if (++cnt >= K) open = false;  // :170-171
-          }
-          if (++proc == kGSeg) {
-            const bool any_hit = __any_sync(DIBR_FULL_MASK, nbuf > 0);
-            if (any_hit) flush();
-            proc = 0;
-            if (!__any_sync(DIBR_FULL_MASK, open)) { m = 0; done = true; }
-          }
+      // ---- compact the region's candidates of this chunk (ascending face order)
+      const int pc = __popc(myw);
+      int incl = pc;
+#pragma unroll
+      for (int d = 1; d < kGWords; d <<= 1) {
+        const int t = __shfl_up_sync(DIBR_FULL_MASK, incl, d);
+        if (lane >= d) incl += t;
+      }
+      const int T = __shfl_sync(DIBR_FULL_MASK, incl, kGWords - 1);
+      unsigned short* cl = sm.clist[warp];
+      {
+        unsigned w = myw;
+        int o = incl - pc;
+        while (w) {
+          cl[o++] = (unsigned short)((lane << 5) + __ffs(w) - 1);
+          w &= w - 1;
         }
       }
-      if (__any_sync(DIBR_FULL_MASK, nbuf > 0)) flush();
+      __syncwarp();
+
+      // ---- 32 candidates per step, bit-parallel: every candidate lane builds the mask of
+      // the region's pixels inside its rectangle; 32 ballots transpose that into, per pixel
+      // lane, the mask of candidates containing it (bit order = face order)
+      const int rx0 = (r % RX) * 8, ry0 = (r / RX) * 4;
+      for (int cb = 0; cb < T; cb += 32) {
+        if (!__any_sync(DIBR_FULL_MASK, open)) break;
+        const bool cv = cb + lane < T;
+        const int s = cv ? cl[cb + lane] : 0;
+        const unsigned rc = sm.rect[s];
+        const int fid = sm.face[s];
+        unsigned pixmask = 0u;
+        if (cv) {
+          const int c0 = max((int)(rc & 0xff) - rx0, 0), c1 = min((int)((rc >> 8) & 0xff) - rx0, 7);
+          const int r0 = max((int)((rc >> 16) & 0xff) - ry0, 0), r1 = min((int)(rc >> 24) - ry0, 3);
+          if (c0 <= c1 && r0 <= r1) {
+            const unsigned cols = ((2u << c1) - (1u << c0)) & 0xffu;
+            const unsigned rows = ((2u << r1) - (1u << r0)) & 0xfu;
+            pixmask = (cols * 0x01010101u) & ((((rows * 0x00204081u) & 0x01010101u)) * 0xffu);
+          }
+        }
+        unsigned inmask = 0u;
+#pragma unroll
+        for (int q = 0; q < 32; q++) {
+          const unsigned v = __ballot_sync(DIBR_FULL_MASK, (pixmask >> q) & 1u);
+          if (lane == q) inmask = v;
+        }
+        if (!open) inmask = 0u;
+        const int room = K - cnt;           // > 0 for open pixels
+        for (int drop = open ? __popc(inmask) - room : 0; drop > 0; drop--)  // first `room` (:170-171)
+          inmask &= ~(0x80000000u >> __clz(inmask));
+        const int nh = __popc(inmask);
+        const int mxh = __reduce_max_sync(DIBR_FULL_MASK, nh);
+        if (mxh == 0) continue;
+        ensure(__reduce_max_sync(DIBR_FULL_MASK, open ? cnt + nh : 0));
+        for (int k = 0; k < mxh; k++) {
+          const bool has = inmask != 0u;
+          const int c = has ? __ffs(inmask) - 1 : 0;
+          inmask &= inmask - 1u;
+          const int f = __shfl_sync(DIBR_FULL_MASK, fid, c);
+          const int q = cnt / kPairSegHits;
+          int sg = __shfl_sync(DIBR_FULL_MASK, segreg, q & 31);
+          if (has) {
+            if (staged) {
+              tile[cnt][lane] = f;
+            } else {
+              if (q >= 32 && aidx < pb.cap) sg = pb.act_seg[(long long)aidx * pb.nseg + q];
+              if (aidx < pb.cap && sg >= 0)
+                pb.face[(long long)sg * kPairSegSlots + (cnt % kPairSegHits) * 32 + lane] = f;
+            }
+            cnt++;
+          }
+        }
+        open = cnt < K;
+      }
+      __syncwarp();
+      if (staged && aidx >= 0 && aidx < pb.cap) {
+        const bool got = cnt != 0xffff && cnt > cnt0;
+        const int h0 = __reduce_min_sync(DIBR_FULL_MASK, got ? cnt0 : 0x7fff);
+        const int h1 = __reduce_max_sync(DIBR_FULL_MASK, got ? cnt : 0);
+        for (int h = h0; h < h1; h++) {
+          const int sg = __shfl_sync(DIBR_FULL_MASK, segreg, h / kPairSegHits);
+          if (got && h >= cnt0 && h < cnt && sg >= 0)
+            pb.face[(long long)sg * kPairSegSlots + (h % kPairSegHits) * 32 + lane] = tile[h][lane];
+        }
+      }
       sm.cnt[pl] = (unsigned short)cnt;
       const unsigned still = __ballot_sync(DIBR_FULL_MASK, open);
       if (lane == 0) sm.ropen[r] = still != 0;
@@ -255,23 +327,17 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
       pb.act_cnt[(long long)aidx * 32 + lane] = (unsigned short)(c == 0xffff ? 0 : c);
     }
   }
+  DIBR_TRACE_END(n);
 }
 
 cudaError_t launch_softmask_gather(const SoftArgs& a, const Plan& p, cudaStream_t st) {
-  dim3 grid(p.nkx, p.nky, p.B);
   prof_begin(K_SOFT_GATHER, st);
   if (p.blk_log2 == 5) {
-    softmask_gather_kernel<5><<<grid, kGThreads, sizeof(GatherSmem<5>), st>>>(a, p);
+    dim3 grid((p.W + 15) >> 4, (p.H + 15) >> 4, p.B);
+    softmask_gather_kernel<4><<<grid, kGThreads, sizeof(GatherSmem<4>), st>>>(a, p);
   } else {
-    static bool once = false;
-    if (!once) {
-      cudaError_t e = cudaFuncSetAttribute(softmask_gather_kernel<6>,
-                                           cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                           (int)sizeof(GatherSmem<6>));
-      if (e != cudaSuccess) return e;
-      once = true;
-    }
-    softmask_gather_kernel<6><<<grid, kGThreads, sizeof(GatherSmem<6>), st>>>(a, p);
+    dim3 grid((p.W + 31) >> 5, (p.H + 31) >> 5, p.B);
+    softmask_gather_kernel<5><<<grid, kGThreads, sizeof(GatherSmem<5>), st>>>(a, p);
   }
   prof_end(st);
   return cudaGetLastError();

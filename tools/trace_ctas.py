@@ -1,0 +1,68 @@
+#!/usr/bin/env python
+"""Development aid: per-CTA start/end/SM trace of one instrumented kernel on cfg2.
+
+Build with  NVCC_EXTRA=-DDIBR_TRACE sh kaolin-windows_b200/csrc/build.sh  first; the
+kernel named on the command line must contain DIBR_TRACE_BEGIN/END.  Usage:
+    python tools/trace_ctas.py fwd|bwd
+(all instrumented kernels of that pass write the same buffer: instrument one at a time).
+"""
+import ctypes
+import sys
+
+import numpy as np
+import torch
+
+sys.path.insert(0, __file__.rsplit("/", 2)[0])
+import workloads as wl                      # noqa: E402
+import kaolin_windows_b200 as kal           # noqa: E402
+from kaolin_windows_b200 import _lib        # noqa: E402
+
+which = sys.argv[1] if len(sys.argv) > 1 else "fwd"
+dev = torch.device("cuda:0")
+inp = wl.make_config("cfg2_70k_8x512", device=dev)
+z, img, feat, nz = (inp[k] for k in ("face_vertices_z", "face_vertices_image", "face_features",
+                                     "face_normals_z"))
+H = W = 512
+lib = ctypes.CDLL(_lib.LIB_PATH)
+lib.dibr_trace_set.argtypes = [ctypes.c_void_p]
+NCTA = 1 << 16
+buf = torch.zeros(NCTA * 4, dtype=torch.int64, device=dev)
+
+
+def run(trace):
+    img_l = img.clone().requires_grad_(True)
+    feat_l = feat.clone().requires_grad_(True)
+    if trace and which == "fwd":
+        lib.dibr_trace_set(buf.data_ptr())
+    out, mask, idx = kal.render.mesh.dibr_rasterization(H, W, z, img_l, feat_l, nz)
+    lib.dibr_trace_set(None)
+    loss = out.sum() + mask.sum()
+    if trace and which == "bwd":
+        lib.dibr_trace_set(buf.data_ptr())
+    loss.backward()
+    torch.cuda.synchronize()
+    lib.dibr_trace_set(None)
+
+
+for _ in range(3):
+    run(False)
+run(True)
+d = buf.cpu().numpy().reshape(-1, 4)
+d = d[d[:, 1] > 0]
+t0 = d[:, 0].min()
+dur = (d[:, 1] - d[:, 0]) / 1e3
+print("CTAs traced %d; kernel span %.1f us; CTA dur mean %.2f max %.1f sum %.0f us" % (
+    len(d), (d[:, 1].max() - t0) / 1e3, dur.mean(), dur.max(), dur.sum()))
+print("duration histogram (us):", np.histogram(dur, bins=[0, 2, 5, 10, 20, 40, 80, 160, 1000]))
+order = np.argsort(-dur)[:12]
+for i in order:
+    print("  dur %.1f start %.1f user %d sm %d" % (dur[i], (d[i, 0] - t0) / 1e3, d[i, 3], d[i, 2]),
+          "n", d[i, 3] >> 40, "stage kcyc %.1f" % (((d[i, 3] >> 20) & 0xfffff) / 10), "init kcyc %.1f" % ((d[i, 3] & 0xfffff) / 10))
+busy = np.zeros(148)
+last = np.zeros(148)
+for s, e, smid, _ in d:
+    busy[smid] += (e - s) / 1e3
+    last[smid] = max(last[smid], (e - t0) / 1e3)
+print("per-SM sum of CTA durations: min %.0f mean %.0f max %.0f; last end min %.0f max %.0f" % (
+    busy.min(), busy.mean(), busy.max(), last.min(), last.max()))
+print("corr(user, dur) = %.2f" % np.corrcoef(d[:, 3], dur)[0, 1])
