@@ -93,13 +93,17 @@ __device__ __forceinline__ float pick3(int v, float a, float b, float c) {
 
 // dibr_soft_mask_cuda.cu:283-347: gradient of one (pixel, face) pair w.r.t. the face's
 // six UNscaled coordinates, added into g[6] (register array: static indices only).
-__device__ __forceinline__ void soft_grad(float x0, float y0, const float (&X)[6], int edgeid,
-                                          float prob, float allprob, float dLdp, float sigmainv,
-                                          float mult, double inv_e, float (&g)[6]) {
+// Core: the gradient lands on vertex v1 (always) and v2 (edge case, else -1).
+__device__ __forceinline__ void soft_grad_core(float x0, float y0, const float (&X)[6], int edgeid,
+                                               float prob, float allprob, float dLdp,
+                                               float sigmainv, float mult, double inv_e, int& v1,
+                                               float& g1x, float& g1y, int& v2, float& g2x,
+                                               float& g2y) {
   const float dLdz = (float)(-1.0 * sigmainv * dLdp * (1.0 - allprob) /
                              (1.0 - prob + DIBR_SOFT_EPS) * prob);
-  int v1, v2 = -1;
-  float g1x, g1y, g2x = 0.f, g2y = 0.f;
+  v2 = -1;
+  g2x = 0.f;
+  g2y = 0.f;
   if (edgeid >= 3) {
     v1 = edgeid - 3;
     const float x1 = pick3(v1, X[0], X[2], X[4]), y1 = pick3(v1, X[1], X[3], X[5]);
@@ -129,6 +133,15 @@ __device__ __forceinline__ void soft_grad(float x0, float y0, const float (&X)[6
     g2x = dLdx2 / mult;
     g2y = dLdy2 / mult;
   }
+}
+
+__device__ __forceinline__ void soft_grad(float x0, float y0, const float (&X)[6], int edgeid,
+                                          float prob, float allprob, float dLdp, float sigmainv,
+                                          float mult, double inv_e, float (&g)[6]) {
+  int v1, v2;
+  float g1x, g1y, g2x, g2y;
+  soft_grad_core(x0, y0, X, edgeid, prob, allprob, dLdp, sigmainv, mult, inv_e, v1, g1x, g1y, v2,
+                 g2x, g2y);
 #pragma unroll
   for (int v = 0; v < 3; v++) {
     if (v == v1) { g[2 * v] += g1x; g[2 * v + 1] += g1y; }
@@ -403,6 +416,46 @@ __device__ __forceinline__ bool pair_region(const PairBuf& pb, const Plan& p, lo
   return true;
 }
 
+// The (pixel, hit) pairs of a region are dealt out evenly over the 32 lanes whatever
+// pixel they belong to (partially covered regions would otherwise leave most lanes idle):
+// pair i belongs to the pixel lane l with off[l] <= i < off[l + 1], off = exclusive scan of
+// the per-pixel hit counts, and is that pixel's hit h = i - off[l].
+struct PairDeal {
+  int off;     // exclusive prefix of cnt over lanes (this lane's first pair)
+  int total;   // pairs of the region
+  int segreg;  // lane q holds the region's segment q (q < 32)
+};
+
+__device__ __forceinline__ PairDeal pair_deal(const PairBuf& pb, long long act, int cnt, int lane) {
+  int incl = cnt;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int t = __shfl_up_sync(DIBR_FULL_MASK, incl, d);
+    if (lane >= d) incl += t;
+  }
+  PairDeal pd;
+  pd.off = incl - cnt;
+  pd.total = __shfl_sync(DIBR_FULL_MASK, incl, 31);
+  pd.segreg = lane < pb.nseg ? pb.act_seg[act * pb.nseg + lane] : -1;
+  return pd;
+}
+
+// (owner lane, hit index, slot) of pair i; all lanes call it, i may differ per lane
+__device__ __forceinline__ long long pair_locate(const PairBuf& pb, long long act,
+                                                 const PairDeal& pd, int i, int& l, int& h) {
+  l = 0;
+#pragma unroll
+  for (int st = 16; st > 0; st >>= 1) {
+    const int o = __shfl_sync(DIBR_FULL_MASK, pd.off, l + st);
+    if (o <= i) l += st;
+  }
+  h = i - __shfl_sync(DIBR_FULL_MASK, pd.off, l);
+  const int q = h / kPairSegHits;
+  int sg = __shfl_sync(DIBR_FULL_MASK, pd.segreg, q & 31);
+  if (q >= 32) sg = pb.act_seg[act * pb.nseg + q];
+  return (long long)sg * kPairSegSlots + (h % kPairSegHits) * 32 + l;
+}
+
 __global__ void __launch_bounds__(kPairWarps * 32)
 softmask_pairs_eval_kernel(const SoftArgs a, const Plan p) {
   const PairBuf& pb = a.pairs;
@@ -413,13 +466,15 @@ softmask_pairs_eval_kernel(const SoftArgs a, const Plan p) {
   const Grid g = make_grid(a.job.mult, p.W, p.H);
   const float mult = a.job.mult;
   const float four_mm = __fmul_rn(__fmul_rn(mult, 4.f), mult);
-  const float x0 = pix_x(g, ix), y0 = pix_y(g, iy);
-  const int mx = __reduce_max_sync(DIBR_FULL_MASK, cnt);
-  float ap = 1.0f;
-  for (int h = 0; h < mx; h++) {
-    const int sg = pb.act_seg[act * pb.nseg + h / kPairSegHits];  // warp-uniform
-    if (h < cnt) {
-      const long long slot = (long long)sg * kPairSegSlots + (h % kPairSegHits) * 32 + lane;
+  const int rx0 = ix - (lane & 7), ry0 = iy - (lane >> 3);
+  const PairDeal pd = pair_deal(pb, act, cnt, lane);
+  // ---- evaluate, all lanes busy
+  for (int i0 = 0; i0 < pd.total; i0 += 32) {
+    const bool valid = i0 + lane < pd.total;
+    int l, h;
+    const long long slot = pair_locate(pb, act, pd, valid ? i0 + lane : pd.total - 1, l, h);
+    if (valid) {
+      const float x0 = pix_x(g, rx0 + (l & 7)), y0 = pix_y(g, ry0 + (l >> 3));
       float X[6];
       load_scaled_coords(a.job, b, pb.face[slot], X);
       const double inv[3] = {edge_inv(X[0], X[1], X[2], X[3]), edge_inv(X[2], X[3], X[4], X[5]),
@@ -429,6 +484,18 @@ softmask_pairs_eval_kernel(const SoftArgs a, const Plan p) {
       soft_eval(x0, y0, X, inv, four_mm, a.sigmainv, mult, prob, edgeid);
       pb.prob[slot] = prob;
       pb.type[slot] = (unsigned char)(edgeid + 1);
+    }
+  }
+  __syncwarp();
+  // ---- fold each pixel's probabilities in face order (:174-182); rows are coalesced
+  const int mx = __reduce_max_sync(DIBR_FULL_MASK, cnt);
+  float ap = 1.0f;
+  for (int h = 0; h < mx; h++) {
+    const int q = h / kPairSegHits;
+    int sg = __shfl_sync(DIBR_FULL_MASK, pd.segreg, q & 31);
+    if (q >= 32) sg = pb.act_seg[act * pb.nseg + q];
+    if (h < cnt) {
+      const float prob = __ldcg(pb.prob + (long long)sg * kPairSegSlots + (h % kPairSegHits) * 32 + lane);
       ap = __double2float_rn(__dmul_rn((double)ap, __dsub_rn(1.0, (double)prob)));  // :176-177
     }
   }
@@ -446,34 +513,41 @@ softmask_pairs_grad_kernel(const SoftArgs a, const Plan p) {
   if (!pair_region(pb, p, act, lane, b, ix, iy, cnt)) return;
   const Grid g = make_grid(a.job.mult, p.W, p.H);
   const float mult = a.job.mult;
-  const float x0 = pix_x(g, ix), y0 = pix_y(g, iy);
-  float dLdp = 0.f, allprob = 0.f;
+  const int rx0 = ix - (lane & 7), ry0 = iy - (lane >> 3);
+  float my_dLdp = 0.f, my_allprob = 0.f;
   if (cnt > 0) {
     const long long pix = ((long long)b * p.H + iy) * p.W + ix;
-    dLdp = a.grad_mask[pix];
-    allprob = a.mask_in[pix];
+    my_dLdp = a.grad_mask[pix];
+    my_allprob = a.mask_in[pix];
   }
-  const int mx = __reduce_max_sync(DIBR_FULL_MASK, cnt);
-  for (int h = 0; h < mx; h++) {
-    const int sg = pb.act_seg[act * pb.nseg + h / kPairSegHits];
-    if (h < cnt) {
-      const long long slot = (long long)sg * kPairSegSlots + (h % kPairSegHits) * 32 + lane;
+  const PairDeal pd = pair_deal(pb, act, cnt, lane);
+  for (int i0 = 0; i0 < pd.total; i0 += 32) {
+    const bool valid = i0 + lane < pd.total;
+    int l, h;
+    const long long slot = pair_locate(pb, act, pd, valid ? i0 + lane : pd.total - 1, l, h);
+    const float dLdp = __shfl_sync(DIBR_FULL_MASK, my_dLdp, l);
+    const float allprob = __shfl_sync(DIBR_FULL_MASK, my_allprob, l);
+    if (valid) {
+      const float x0 = pix_x(g, rx0 + (l & 7)), y0 = pix_y(g, ry0 + (l >> 3));
       const int f = pb.face[slot];
       float X[6];
       load_scaled_coords(a.job, b, f, X);
       const int eid = (int)pb.type[slot] - 1;
       double inv_e = 0.0;
       if (eid < 3) {
-        const int v2 = (eid + 1) % 3;
+        const int w2 = (eid + 1) % 3;
         inv_e = edge_inv(pick3(eid, X[0], X[2], X[4]), pick3(eid, X[1], X[3], X[5]),
-                         pick3(v2, X[0], X[2], X[4]), pick3(v2, X[1], X[3], X[5]));
+                         pick3(w2, X[0], X[2], X[4]), pick3(w2, X[1], X[3], X[5]));
       }
-      float gv[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      soft_grad(x0, y0, X, eid, pb.prob[slot], allprob, dLdp, a.sigmainv, mult, inv_e, gv);
-      float* gp = a.grad_img + ((long long)b * a.job.view_stride + f) * 6;
-#pragma unroll
-      for (int i = 0; i < 6; i++)
-        if (gv[i] != 0.f) atomicAdd(gp + i, gv[i]);
+      int v1, v2;
+      float g1x, g1y, g2x, g2y;
+      soft_grad_core(x0, y0, X, eid, pb.prob[slot], allprob, dLdp, a.sigmainv, mult, inv_e, v1,
+                     g1x, g1y, v2, g2x, g2y);
+      // one 8-byte vector reduction per touched vertex ((x, y) of a vertex are adjacent and
+      // 8-byte aligned in grad_face_vertices_image) instead of up to four scalar ones
+      float2* gp = reinterpret_cast<float2*>(a.grad_img + ((long long)b * a.job.view_stride + f) * 6);
+      if (g1x != 0.f || g1y != 0.f) atomicAdd(gp + v1, make_float2(g1x, g1y));
+      if (v2 >= 0 && (g2x != 0.f || g2y != 0.f)) atomicAdd(gp + v2, make_float2(g2x, g2y));
     }
   }
 }
