@@ -155,6 +155,7 @@ static void attach(BinJob& j, const Plan& p, const Workspace& w, int l) {
   j.list = w.list[l];
   j.total = (unsigned long long*)(w.base + p.off_total) + l;
   j.capacity = w.cap[l];
+  j.ordered = l == 1;
 }
 
 // memset + count + scan + (capacity check) + fill for the given jobs (kinds[i] = 0/1).

@@ -7,17 +7,18 @@
 // on the data path and without a sort:
 //
 //   bin_count  one WARP per chunk of S consecutive faces of one view.  Per step the warp
-//              loads 32 faces, derives each face's bin rectangle, and walks the distinct
-//              bins touched in ascending bin id (warp min-reduce); the faces touching the
-//              current bin are found with __ballot_sync and counted with __popc into the
-//              warp's private shared-memory histogram.  Non-zero counts go to
-//              mat[view][bin][chunk].
+//              loads 32 faces, derives each face's bin rectangle and bumps the warp's
+//              private shared-memory histogram (native integer shared atomics; the order
+//              is irrelevant for counting).  Non-zero counts go to mat[view][bin][chunk].
 //   bin_scan   one warp per (view, bin): exclusive scan of mat[view][bin][:] over chunks
 //              (coalesced, shuffle scan), then one list segment per bin is reserved from
 //              a global cursor (one atomic per CTA of 8 bins).
-//   bin_fill   same walk as bin_count; the rank of a face inside its bin is
-//              segment start + chunk offset + running count + popc(ballot & lanemask_lt),
+//   bin_fill   soft-mask list (ordered): the warp walks the distinct bins its 32 faces
+//              touch in ascending bin id (warp min-reduce); the faces touching the current
+//              bin are found with __ballot_sync and ranked with __popc(mask & lanemask_lt),
 //              so every bin's list comes out sorted by face index.
+//              rasterizer list (order free, its depth test is order independent): slots
+//              are taken with shared-memory atomics on the same per-warp counters.
 //
 // All three kernels take up to two jobs (raster list, soft-mask list) via blockIdx.z so
 // that the fused forward bins both in the same launches.
@@ -75,8 +76,25 @@ bin_walk_kernel(const BinJobs jobs, const Plan p) {
       Face2D fc;
       if (load_face2d(job, b, f, fc)) act = bin_rect(g, fc, p.bin_log2, bx0, bx1, by0, by1);
     }
+    // Where the order inside a bin's list does not matter -- the counting pass, and the
+    // fill of the rasterizer's list (its depth test is order independent) -- every lane
+    // simply bumps the shared-memory counters of the bins of its rectangle.
+    if (!FILL || !job.ordered) {
+      for (int cy = by0; cy <= by1; cy++)
+        for (int cx = bx0; cx <= bx1; cx++) {
+          const int bin = cy * p.nbx + cx;
+          const int slot = atomicAdd(&hist[bin], 1);
+          if (FILL) {
+            if (slot < job.capacity) job.list[slot] = f;
+          } else {
+            lo_bin = min(lo_bin, bin);
+            hi_bin = max(hi_bin, bin);
+          }
+        }
+      continue;
+    }
     int cx = bx0, cy = by0;
-    // Ordered emission: each lane walks its rectangle row-major (ascending bin id); the
+    // Ordered emission (soft-mask list): each lane walks its rectangle row-major (ascending bin id); the
     // warp repeatedly takes the smallest pending bin id, so all faces touching that bin
     // are handled together, in lane (= face) order.
     while (true) {
@@ -93,9 +111,6 @@ bin_walk_kernel(const BinJobs jobs, const Plan p) {
           const long long slot = (long long)base + __popc(mask & lanemask_lt());
           if (slot < job.capacity) job.list[slot] = f;
         }
-      } else {
-        lo_bin = min(lo_bin, m);
-        hi_bin = max(hi_bin, m);
       }
       if (hit) {
         if (++cx > bx1) {
@@ -107,6 +122,8 @@ bin_walk_kernel(const BinJobs jobs, const Plan p) {
     }
   }
   if (!FILL) {
+    lo_bin = __reduce_min_sync(DIBR_FULL_MASK, lo_bin);
+    hi_bin = __reduce_max_sync(DIBR_FULL_MASK, hi_bin);
     __syncwarp();
     for (int i = lo_bin + lane; i <= hi_bin; i += 32) {
       const int c = hist[i];

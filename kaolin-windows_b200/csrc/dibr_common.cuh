@@ -52,6 +52,7 @@ struct BinJob {
   float mult;              // multiplier (applied unless prescaled)
   float margin;            // box enlargement, 0 for the raster list
   int prescaled;
+  int ordered;             // list must come out in ascending face order (soft mask: yes)
   int* mat;
   int2* range;
   int* start;

@@ -187,20 +187,14 @@ struct SoftSmem {
 };
 
 template <int BLK_LOG2, int MODE>
-__global__ void __launch_bounds__(kSoftThreads)
-softmask_kernel(const SoftArgs a, const Plan p) {
+__device__ __forceinline__ void soft_block(const SoftArgs& a, const Plan& p,
+                                           SoftSmem<BLK_LOG2, MODE>& sm, const int bxi,
+                                           const int byi, const int b) {
   using Smem = SoftSmem<BLK_LOG2, MODE>;
   constexpr int BLK = Smem::BLK, NPX = Smem::NPX, NR = Smem::NR, RX = BLK / 8;
   constexpr int CH = kSoftChunk;
-  extern __shared__ __align__(16) unsigned char s_raw[];
-  Smem& sm = *reinterpret_cast<Smem*>(s_raw);
-
   const int tid = threadIdx.x, lane = lane_id(), warp = tid >> 5;
-  // with a pair buffer attached the self-contained kernels are only the overflow fallback
-  if ((MODE == SOFT_FWD || MODE == SOFT_BWD) && a.pairs.cap > 0 && !pairs_overflowed(a.pairs))
-    return;
-  const int b = blockIdx.z;
-  const int bx0 = blockIdx.x << BLK_LOG2, by0 = blockIdx.y << BLK_LOG2;
+  const int bx0 = bxi << BLK_LOG2, by0 = byi << BLK_LOG2;
   const Grid g = make_grid(a.job.mult, p.W, p.H);
   const float mult = a.job.mult;
   const float four_mm = __fmul_rn(__fmul_rn(mult, 4.f), mult);
@@ -224,7 +218,7 @@ softmask_kernel(const SoftArgs a, const Plan p) {
   }
 
   const int shift = p.bin_log2 - BLK_LOG2;
-  const int bin = (blockIdx.y >> shift) * p.nbx + (blockIdx.x >> shift);
+  const int bin = (byi >> shift) * p.nbx + (bxi >> shift);
   const long long row = (long long)b * p.NB + bin;
   const long long start = a.job.start[row];
   long long n = a.job.count[row];
@@ -377,6 +371,25 @@ softmask_kernel(const SoftArgs a, const Plan p) {
             sm.cnt[i] == 0xffff ? 1.0f                                            // :68-70
                                 : __double2float_rn(__dsub_rn(1.0, (double)sm.ap[i]));  // :181-182
     }
+  }
+}
+
+// Screen blocks are taken from a 1-D grid with a stride loop: when the kernel is only the
+// overflow fallback of the pair path (the usual case: nothing to do) it is launched with a
+// few CTAs per SM that read the pair cursors and leave.
+template <int BLK_LOG2, int MODE>
+__global__ void __launch_bounds__(kSoftThreads)
+softmask_kernel(const SoftArgs a, const Plan p) {
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  SoftSmem<BLK_LOG2, MODE>& sm = *reinterpret_cast<SoftSmem<BLK_LOG2, MODE>*>(s_raw);
+  if ((MODE == SOFT_FWD || MODE == SOFT_BWD) && a.pairs.cap > 0 && !pairs_overflowed(a.pairs))
+    return;
+  const int per_view = p.nkx * p.nky;
+  const long long nblk = (long long)per_view * p.B;
+  for (long long blk = blockIdx.x; blk < nblk; blk += gridDim.x) {
+    const int b = (int)(blk / per_view), rr = (int)(blk - (long long)b * per_view);
+    soft_block<BLK_LOG2, MODE>(a, p, sm, rr % p.nkx, rr / p.nkx, b);
+    __syncthreads();
   }
 }
 
@@ -593,7 +606,9 @@ __global__ void __launch_bounds__(256) softmask_dense_backward_kernel(const Soft
 // ---------------------------------------------------------------------------- host
 template <int MODE>
 static cudaError_t launch_soft_mode(const SoftArgs& a, const Plan& p, cudaStream_t st) {
-  dim3 grid(p.nkx, p.nky, p.B);
+  const long long nblk = (long long)p.nkx * p.nky * p.B;
+  const bool fallback = MODE != SOFT_FWD_DENSE && a.pairs.cap > 0;
+  dim3 grid((unsigned)(fallback ? min(nblk, (long long)148 * 3) : nblk));
   static bool attr5 = false, attr6 = false;
   cudaError_t e = cudaSuccess;
   if (p.blk_log2 == 5) {
