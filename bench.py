@@ -178,7 +178,8 @@ def main():
     dev = torch.device("cuda", local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=120))
 
     # ---- workload: this rank's 8 views of the 8N-view job over the shared mesh
     views_per_gpu = wl.CONFIGS[CFG]["views"]
@@ -196,21 +197,23 @@ def main():
     g2 = torch.rand((B, H, W), device=dev, generator=gen)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
 
-    def step(img_in, feat_in, z_in=z, nz_in=nz):
+    def step(img_in, feat_in, z_in=z, nz_in=nz, exchange=True):
         img_l = img_in.detach().requires_grad_(True)
         feat_l = feat_in.detach().requires_grad_(True)
         out, mask, idx = kal.render.mesh.dibr_rasterization(H, W, z_in, img_l, feat_l, nz_in,
                                                             SIGMAINV, BOXLEN, KNUM)
         loss = (out * g1).sum() + (mask * g2).sum()
         loss.backward()
-        if world > 1:
+        if world > 1 and exchange:
             # local face -> vertex scatter-add, then ONE flat all-reduce of the shared
             # mesh's gradients (vertex image-plane positions per view stay local; what is
             # shared is the per-vertex feature and the summed positional signal)
-            gv = torch.zeros((V, 2 + D), device=dev)
-            gv.index_add_(0, faces.reshape(-1),
-                          torch.cat([img_l.grad, feat_l.grad], dim=-1).sum(0).reshape(-1, 2 + D))
-            kal.parallel.allreduce_mesh_grads([gv])
+            fidx = faces.reshape(-1)
+            gvi = torch.zeros((V, 2), device=dev)
+            gvf = torch.zeros((V, D), device=dev)
+            gvi.index_add_(0, fidx, img_l.grad.sum(0).reshape(-1, 2))
+            gvf.index_add_(0, fidx, feat_l.grad.sum(0).reshape(-1, D))
+            kal.parallel.allreduce_mesh_grads([gvi, gvf])
         return loss
 
     def barrier():
@@ -284,7 +287,7 @@ def main():
     lib.dibr_profile_begin()
     for _ in range(args.steps):
         flush.zero_()
-        step(img, feat)
+        step(img, feat, exchange=False)   # rank 0 only: no collective in this pass
     cap = 64 * args.steps
     ids = (ctypes.c_int * cap)()
     ms = (ctypes.c_float * cap)()

@@ -79,13 +79,16 @@ static int make_plan(int B, int F, int H, int W, Plan& p) {
   p.S = (int)align_up(s, 32);
   p.nchunks = F > 0 ? (F + p.S - 1) / p.S : 0;
   int64_t off = 0;
-  p.off_total = off; off += 64;
+  p.off_total = off; off += 256;
   p.off_flags = off; off = align_up(off + (int64_t)B * p.nkx * p.nky * 4, 256);
   for (int l = 0; l < 2; l++) {
     p.off_start[l] = off; off = align_up(off + (int64_t)B * p.NB * 4, 256);
     p.off_count[l] = off; off = align_up(off + (int64_t)B * p.NB * 4, 256);
     p.off_range[l] = off; off = align_up(off + (int64_t)B * p.nchunks * 8, 256);
     p.off_mat[l] = off; off = align_up(off + (int64_t)B * p.NB * p.nchunks * 4, 256);
+  }
+  for (int l = 0; l < 2; l++) {  // not memset: only the bucket sizes in the header are
+    p.off_order[l] = off; off = align_up(off + (int64_t)kOrderBuckets * B * p.NB * 4, 256);
   }
   p.fixed_bytes = off;
 #ifdef DIBR_TRACE
@@ -153,6 +156,8 @@ static void attach(BinJob& j, const Plan& p, const Workspace& w, int l) {
   j.start = (int*)(w.base + p.off_start[l]);
   j.count = (int*)(w.base + p.off_count[l]);
   j.list = w.list[l];
+  j.order = (int*)(w.base + p.off_order[l]);
+  j.bucket = (int*)(w.base + p.off_total + 64) + l * kOrderBuckets;
   j.total = (unsigned long long*)(w.base + p.off_total) + l;
   j.capacity = w.cap[l];
   j.ordered = l == 1;
@@ -165,9 +170,9 @@ static int run_binning(const Plan& p, const Workspace& w, BinJobs& jobs, const i
   for (int i = 0; i < njobs; i++) {
     const int l = kinds[i];
     DIBR_CUDA(cudaMemsetAsync(w.base + p.off_start[l], 0,
-                              (l == 0 ? p.off_start[1] : p.fixed_bytes) - p.off_start[l], st));
+                              (l == 0 ? p.off_start[1] : p.off_order[0]) - p.off_start[l], st));
   }
-  if (p.B > 0 && p.F > 0) DIBR_CUDA(launch_binning_count(jobs, njobs, p, st));
+  if (p.B > 0) DIBR_CUDA(launch_binning_count(jobs, njobs, p, st));
   if (needed_host) {
     DIBR_CUDA(cudaMemcpyAsync(needed_host, w.base + p.off_total, 16, cudaMemcpyDeviceToHost, st));
   } else {

@@ -172,16 +172,21 @@ __global__ void __launch_bounds__(256) bin_scan_kernel(const BinJobs jobs, const
     // is re-checked there); the host sees the overflow through job.total.
     job.start[rowi] = (int)min(st, (long long)0x7fffffff);
     job.count[rowi] = carry;
+    // heaviest-first order (lpt_row in dibr_common.cuh)
+    const int bk = carry > 0 ? min(kOrderBuckets - 1, 32 - __clz(carry)) : 0;
+    job.order[(long long)bk * nrows + atomicAdd(job.bucket + bk, 1)] = (int)rowi;
   }
 }
 
 // ---------------------------------------------------------------------------- host
 cudaError_t launch_binning_count(const BinJobs& jobs, int njobs, const Plan& p, cudaStream_t st) {
   const size_t smem = (size_t)kBinWarps * p.NB * sizeof(int);
-  dim3 grid((p.nchunks + kBinWarps - 1) / kBinWarps, p.B, njobs);
-  prof_begin(K_BIN_COUNT, st);
-  bin_walk_kernel<false><<<grid, kBinWarps * 32, smem, st>>>(jobs, p);
-  prof_end(st);
+  if (p.nchunks > 0) {
+    dim3 grid((p.nchunks + kBinWarps - 1) / kBinWarps, p.B, njobs);
+    prof_begin(K_BIN_COUNT, st);
+    bin_walk_kernel<false><<<grid, kBinWarps * 32, smem, st>>>(jobs, p);
+    prof_end(st);
+  }
   const long long nrows = (long long)p.B * p.NB;
   dim3 grid2((unsigned)((nrows + 7) / 8), 1, njobs);
   prof_begin(K_BIN_SCAN, st);

@@ -35,7 +35,9 @@ struct Plan {
   int64_t off_range[2];   // int2 [B][nchunks]     touched bin range of each chunk
   int64_t off_start[2];   // int [B][NB]           list segment start of each bin
   int64_t off_count[2];   // int [B][NB]           list segment length
-  int64_t off_total;      // unsigned long long [2] entries needed per list kind
+  int64_t off_total;      // header: u64 [2] entries needed per list kind, [2] pair cursors;
+                          // then int [2][16] bucket sizes of the heaviest-first order
+  int64_t off_order[2];   // int [16][B * NB]    (view, bin) rows bucketed by list length
   int64_t off_flags;      // int [B][nkx*nky]      uncovered-pixel count per block
   int64_t fixed_bytes;    // everything above
   unsigned long long* trace;  // -DDIBR_TRACE builds only, else null
@@ -58,6 +60,8 @@ struct BinJob {
   int* start;
   int* count;
   int* list;
+  int* order;              // [16][B * NB] rows of each length bucket (filled by bin_scan)
+  int* bucket;             // [16] rows per bucket
   unsigned long long* total;
   long long capacity;      // entries available in `list`
 };
@@ -166,6 +170,39 @@ cudaError_t launch_softmask_dense_backward(const SoftDenseBwdArgs&, cudaStream_t
 cudaError_t launch_softmask_gather(const SoftArgs&, const Plan&, cudaStream_t);
 cudaError_t launch_softmask_pairs_eval(const SoftArgs&, const Plan&, cudaStream_t);
 cudaError_t launch_softmask_pairs_grad(const SoftArgs&, const Plan&, cudaStream_t);
+
+// ------------------------------------------------- heaviest-first block scheduling
+// bin_scan buckets the (view, bin) rows by floor(log2(list length)) + 1.  Consumers whose
+// CTA cost grows with the list length take their block through this order, longest lists
+// first, so the long CTAs start early and the short ones fill the tail (LPT scheduling).
+constexpr int kOrderBuckets = 16;
+__device__ __forceinline__ long long lpt_row(const BinJob& j, long long nrows, long long i) {
+  int c[kOrderBuckets];
+#pragma unroll
+  for (int k = 0; k < kOrderBuckets; k++) c[k] = j.bucket[k];
+  long long acc = 0;
+#pragma unroll
+  for (int k = kOrderBuckets - 1; k >= 0; k--) {
+    if (i < acc + c[k]) return j.order[(long long)k * nrows + (i - acc)];
+    acc += c[k];
+  }
+  return -1;
+}
+
+// CTA `id` of a 1-D grid of B * NB * 4^(bin_log2 - sub_log2) CTAs -> (view, block x, block y)
+// in units of 2^sub_log2 pixels.  Returns false for blocks outside the image.
+__device__ __forceinline__ bool lpt_block(const BinJob& j, const Plan& p, int sub_log2,
+                                          long long id, int& b, int& bxi, int& byi) {
+  const int shift = p.bin_log2 - sub_log2;
+  const long long row = lpt_row(j, (long long)p.B * p.NB, id >> (2 * shift));
+  if (row < 0) return false;
+  const int sub = (int)(id & ((1ll << (2 * shift)) - 1));
+  b = (int)(row / p.NB);
+  const int bin = (int)(row - (long long)b * p.NB);
+  bxi = ((bin % p.nbx) << shift) + (sub & ((1 << shift) - 1));
+  byi = ((bin / p.nbx) << shift) + (sub >> shift);
+  return (bxi << sub_log2) < p.W && (byi << sub_log2) < p.H;
+}
 
 // ------------------------------------------------------------------------ pixel grid
 struct Grid {

@@ -57,8 +57,11 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
   RasterSmem<BLK_LOG2>& sm = *reinterpret_cast<RasterSmem<BLK_LOG2>*>(s_raw);
   unsigned long long* zbuf = sm.zbuf;
 
-  const int b = blockIdx.z;
-  const int bx0 = blockIdx.x << BLK_LOG2, by0 = blockIdx.y << BLK_LOG2;
+  DIBR_TRACE_BEGIN();
+  // blocks are taken longest face list first (lpt_block)
+  int b, bxi, byi;
+  if (!lpt_block(a.job, p, BLK_LOG2, blockIdx.x, b, bxi, byi)) return;
+  const int bx0 = bxi << BLK_LOG2, by0 = byi << BLK_LOG2;
   const int bx1 = min(bx0 + BLK, p.W) - 1, by1 = min(by0 + BLK, p.H) - 1;
   const Grid g = make_grid(a.job.mult, p.W, p.H);
   const int tid = threadIdx.x, lane = lane_id(), warp = tid >> 5;
@@ -69,7 +72,7 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
 
   // parent bin of this block
   const int shift = p.bin_log2 - BLK_LOG2;
-  const int bin = (blockIdx.y >> shift) * p.nbx + (blockIdx.x >> shift);
+  const int bin = (byi >> shift) * p.nbx + (bxi >> shift);
   const long long row = (long long)b * p.NB + bin;
   long long start = a.job.start[row];
   long long n = a.job.count[row];
@@ -255,13 +258,15 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
     if (lane == 0 && uncovered) atomicAdd(&sm.uncovered, uncovered);
     __syncthreads();
     if (tid == 0)
-      a.block_uncovered[(long long)b * p.nkx * p.nky + blockIdx.y * p.nkx + blockIdx.x] =
+      a.block_uncovered[(long long)b * p.nkx * p.nky + byi * p.nkx + bxi] =
           sm.uncovered;
   }
+  DIBR_TRACE_END(n);
 }
 
 cudaError_t launch_raster_forward(const RasterArgs& a, const Plan& p, cudaStream_t st) {
-  dim3 grid(p.nkx, p.nky, p.B);
+  const int shift = p.bin_log2 - p.blk_log2;
+  dim3 grid((unsigned)(((long long)p.B * p.NB) << (2 * shift)));
   prof_begin(K_RASTER_FWD, st);
   if (p.blk_log2 == 5) {
     raster_forward_kernel<5><<<grid, kRasterThreads, sizeof(RasterSmem<5>), st>>>(a, p);

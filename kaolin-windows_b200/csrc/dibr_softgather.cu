@@ -64,7 +64,9 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
   const PairBuf& pb = a.pairs;
 
   const int tid = threadIdx.x, lane = lane_id(), warp = tid >> 5;
+#ifdef DIBR_TRACE_GATHER
   DIBR_TRACE_BEGIN();
+#endif
   const int b = blockIdx.z;
   const int bx0 = blockIdx.x << BLK_LOG2, by0 = blockIdx.y << BLK_LOG2;
   const int bx1 = min(bx0 + BLK, p.W) - 1, by1 = min(by0 + BLK, p.H) - 1;
@@ -99,7 +101,9 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
     any_open |= m != 0;
   }
   if (!__syncthreads_or(any_open)) {
+#ifdef DIBR_TRACE_GATHER
     DIBR_TRACE_END(0);
+#endif
     return;
   }
 
@@ -327,7 +331,9 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
       pb.act_cnt[(long long)aidx * 32 + lane] = (unsigned short)(c == 0xffff ? 0 : c);
     }
   }
+#ifdef DIBR_TRACE_GATHER
   DIBR_TRACE_END(n);
+#endif
 }
 
 cudaError_t launch_softmask_gather(const SoftArgs& a, const Plan& p, cudaStream_t st) {
