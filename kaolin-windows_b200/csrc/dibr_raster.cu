@@ -1,17 +1,21 @@
 // dibr_raster.cu -- block rasterizer forward (north_star (b)) and its backward ((d)).
 //
-// Forward: one CTA per screen block (32x32 or 64x64 pixels) of one view.  The block's
-// depth buffer lives in shared memory as 64-bit keys (order-preserving depth | ~face).
-// The bin's face list is consumed FACE-PARALLEL: each thread takes one face, scales it,
-// finds the handful of pixel centres inside its box and runs the reference's exact
-// edge/barycentric test only on those, publishing hits with a shared-memory 64-bit max.
-// With meshes whose faces cover a few pixels this does ~10x less arithmetic than
-// testing every pixel of the block against every face.  Faces whose box covers many
-// pixels are queued in shared memory and rasterized by a whole warp each, lanes striding
-// over the box.  A final pixel-parallel pass decodes the winner of every pixel,
-// recomputes its weights with the same instruction sequence (bit-identical) and writes
-// selected_face_idx / interpolated_features (/ output_weights) with coalesced stores;
-// background pixels are written too, so the caller needs no memset.
+// Forward: one CTA per screen block (32x32 or 64x64 pixels) of one view, blocks taken
+// longest face list first.  The block's depth buffer lives in shared memory as 64-bit keys
+// (order-preserving depth | ~face).  The bin's face list is consumed in chunks of 256:
+//   A   one face per thread: the EXACT pixel rectangle of its box inside the block (the
+//       reference's half-open float test on the range ends) and, per rectangle row, a
+//       CONSERVATIVE span [xa, xb] outside of which the face cannot cover a pixel centre
+//       (edge functions in a block-local frame, widened by one full pixel in x and y);
+//   B   the (face, row, x) candidates inside the spans are dealt out evenly over the
+//       threads, a contiguous run each, and every candidate takes the reference's exact
+//       edge / barycentric / depth arithmetic; hits are published with a shared-memory
+//       64-bit max.
+// Candidates are thus ~the covered pixels plus a rim, instead of whole bounding boxes, and
+// every lane is busy whatever the face sizes are.  A final pixel-parallel pass decodes the
+// winner of every pixel, recomputes its weights with the same instruction sequence
+// (bit-identical) and writes selected_face_idx / interpolated_features (/ output_weights)
+// with coalesced stores; background pixels are written too, so the caller needs no memset.
 #include "dibr_common.cuh"
 
 namespace dibr {
@@ -19,38 +23,49 @@ namespace dibr {
 
 constexpr int kRasterThreads = 256;
 constexpr int kRasterWarps = kRasterThreads / 32;
-constexpr int kQueue = 64;  // survivor queue entries per warp (drained 32 at a time)
+constexpr int kRowBatch = 2048;  // row spans expanded per pass (+ one face's rows of slack)
 
 template <int BLK_LOG2>
 struct RasterSmem {
   static constexpr int BLK = 1 << BLK_LOG2;
+  static constexpr int ROWS = kRowBatch + BLK;
   unsigned long long zbuf[BLK * BLK];
   float x[6][kRasterThreads];   // staged faces of the current chunk (scaled coordinates)
   float z[3][kRasterThreads];
-  int rect[kRasterThreads];     // x_lo | y_lo << 8 | (w - 1) << 16 | (h - 1) << 24, block-relative
   int face[kRasterThreads];
-  int pre[kRasterThreads + 1];  // exclusive prefix of the candidate counts w * h
+  int rpre[kRasterThreads + 1]; // exclusive prefix of the faces' row counts
+  int cpre[kRasterThreads];     // candidates before the face's first row (within the batch)
   int wsum[kRasterWarps];
-  unsigned queue[kRasterWarps][kQueue];
+  unsigned span[ROWS];          // slot | ry << 8 | xa << 16 | len << 24 (len <= 64 -> 7 bits)
+  int spre[ROWS + 1];           // exclusive prefix of the span lengths within the batch
   int uncovered;
 };
 
-// Sign-only rejection of a candidate before the normalisation (exactness argument in
-// DESIGN.md "Numerics"): the reference rejects when RN(w_k / norm) < 0.  norm has the sign
-// bit of n32 = (w0 + w1) + w2 and |n32| <= |norm| <= 2^100 when |n32| <= 2^99 and
-// |eps| <= 2^90, so for |w_k| >= 2^-20 with the opposite sign bit the quotient is a
-// negative NORMAL number whatever its rounding: rejected.  Everything else (zeros, tiny
-// values, NaN/Inf, huge norms) goes through the full division path.
-__device__ __forceinline__ bool surely_outside(float w0, float w1, float w2, float n32) {
-  const int sn = __float_as_int(n32);
-  const bool o0 = ((__float_as_int(w0) ^ sn) < 0) && fabsf(w0) >= 0x1p-20f;
-  const bool o1 = ((__float_as_int(w1) ^ sn) < 0) && fabsf(w1) >= 0x1p-20f;
-  const bool o2 = ((__float_as_int(w2) ^ sn) < 0) && fabsf(w2) >= 0x1p-20f;
-  return (o0 || o1 || o2) && fabsf(n32) <= 0x1p99f;
+// block-wide exclusive scan of one int per thread; returns the exclusive prefix, total in
+// `total`.  Two barriers.
+__device__ __forceinline__ int block_scan(int v, int* wsum, int lane, int warp, int& total) {
+  int incl = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int t = __shfl_up_sync(DIBR_FULL_MASK, incl, d);
+    if (lane >= d) incl += t;
+  }
+  __syncthreads();  // wsum free to overwrite
+  if (lane == 31) wsum[warp] = incl;
+  __syncthreads();
+  int woff = 0;
+  total = 0;
+#pragma unroll
+  for (int i = 0; i < kRasterWarps; i++) {
+    const int t = wsum[i];
+    if (i < warp) woff += t;
+    total += t;
+  }
+  return woff + incl - v;
 }
 
 template <int BLK_LOG2>
-__global__ void __launch_bounds__(kRasterThreads)
+__global__ void __launch_bounds__(kRasterThreads, 4)
 raster_forward_kernel(const RasterArgs a, const Plan p) {
   constexpr int BLK = 1 << BLK_LOG2;
   extern __shared__ __align__(16) unsigned char s_raw[];
@@ -65,7 +80,10 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
   const int bx1 = min(bx0 + BLK, p.W) - 1, by1 = min(by0 + BLK, p.H) - 1;
   const Grid g = make_grid(a.job.mult, p.W, p.H);
   const int tid = threadIdx.x, lane = lane_id(), warp = tid >> 5;
-  const bool fast_ok = fabs(a.eps_d) <= 0x1p90;
+  // local frame of the conservative span culling: origin = centre of the block's first
+  // pixel, pixel (rx, ry) at (rx * pitch_x, -ry * pitch_y)
+  const float X0 = pix_x(g, bx0), Y0 = pix_y(g, by0);
+  const float pitch_x = 2.f * g.xs, pitch_y = 2.f * g.ys;
 
   for (int i = tid; i < BLK * BLK; i += kRasterThreads) zbuf[i] = 0ull;
   if (tid == 0) sm.uncovered = 0;
@@ -78,149 +96,178 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
   long long n = a.job.count[row];
   if (start + n > a.job.capacity) n = max(0ll, a.job.capacity - start);  // overflowed call
 
-  unsigned* queue = sm.queue[warp];
-
-  // Exact test + depth + publish of 32 (or `cnt` < 32) queued candidates, one per lane.
-  auto drain = [&](int first, int cnt) {
-    if (lane < cnt) {
-      const unsigned e = queue[(first + lane) & (kQueue - 1)];
-      const int s = e & 0xff, rx = (e >> 8) & 0xff, ry = (e >> 16) & 0xff;
-      const float x0 = pix_x(g, bx0 + rx), y0 = pix_y(g, by0 + ry);
-      float w0, w1, w2;
-      if (raster_weights(x0, y0, sm.x[0][s], sm.x[1][s], sm.x[2][s], sm.x[3][s], sm.x[4][s],
-                         sm.x[5][s], a.eps_d, w0, w1, w2)) {
-        const unsigned long long key =
-            depth_key(raster_depth(w0, w1, w2, sm.z[0][s], sm.z[1][s], sm.z[2][s]), sm.face[s]);
-        if (key) smem_max64(&zbuf[(ry << BLK_LOG2) + rx], key);
-      }
-    }
-  };
-
   for (long long base = 0; base < n; base += kRasterThreads) {
-    __syncthreads();  // previous chunk fully consumed (and zbuf initialised)
-    // ---- phase A: one face per thread -> exact pixel rectangle inside this block
-    int cand = 0;
+    // ---- phase A: one face per thread -> exact pixel rectangle inside this block and the
+    // coefficients of a CONSERVATIVE per-row span test (see DESIGN.md "Span culling")
+    int x_lo = 0, x_hi = -1, y_lo = 0, y_hi = -1;
+    float ia[3], sb[3], scm[3];
+    bool cull = false;
     {
       const long long li = base + tid;
-      int rect = 0;
       if (li < n) {
         const int f = a.job.list[start + li];
         Face2D fc;
-        if (load_face2d(a.job, b, f, fc)) {
-          int x_lo, x_hi, y_lo, y_hi;
-          if (pixel_range(g, fc.xmin, fc.ymin, fc.xmax, fc.ymax, x_lo, x_hi, y_lo, y_hi)) {
-            x_lo = max(x_lo, bx0); x_hi = min(x_hi, bx1);
-            y_lo = max(y_lo, by0); y_hi = min(y_hi, by1);
-            // trim the conservative range to the reference's half-open test
-            // (rasterization_cuda.cu:115); pix_x / pix_y are monotone in ix / iy
-            while (x_lo <= x_hi && pix_x(g, x_lo) < fc.xmin) x_lo++;
-            while (x_lo <= x_hi && pix_x(g, x_hi) >= fc.xmax) x_hi--;
-            while (y_lo <= y_hi && pix_y(g, y_lo) >= fc.ymax) y_lo++;
-            while (y_lo <= y_hi && pix_y(g, y_hi) < fc.ymin) y_hi--;
-            const int w = x_hi - x_lo + 1, h = y_hi - y_lo + 1;
-            if (w > 0 && h > 0) {
-              cand = w * h;
-              rect = (x_lo - bx0) | ((y_lo - by0) << 8) | ((w - 1) << 16) | ((h - 1) << 24);
-              const long long gi = (long long)b * a.job.view_stride + f;
-              sm.x[0][tid] = fc.ax; sm.x[1][tid] = fc.ay; sm.x[2][tid] = fc.bx;
-              sm.x[3][tid] = fc.by; sm.x[4][tid] = fc.cx; sm.x[5][tid] = fc.cy;
-              sm.z[0][tid] = __ldg(a.z + gi * 3);
-              sm.z[1][tid] = __ldg(a.z + gi * 3 + 1);
-              sm.z[2][tid] = __ldg(a.z + gi * 3 + 2);
-              sm.face[tid] = a.job.first ? f - (int)a.job.first[b] : f;
+        if (load_face2d(a.job, b, f, fc) &&
+            pixel_range(g, fc.xmin, fc.ymin, fc.xmax, fc.ymax, x_lo, x_hi, y_lo, y_hi)) {
+          x_lo = max(x_lo, bx0); x_hi = min(x_hi, bx1);
+          y_lo = max(y_lo, by0); y_hi = min(y_hi, by1);
+          // trim the conservative range to the reference's half-open test
+          // (rasterization_cuda.cu:115); pix_x / pix_y are monotone in ix / iy
+          while (x_lo <= x_hi && pix_x(g, x_lo) < fc.xmin) x_lo++;
+          while (x_lo <= x_hi && pix_x(g, x_hi) >= fc.xmax) x_hi--;
+          while (y_lo <= y_hi && pix_y(g, y_lo) >= fc.ymax) y_lo++;
+          while (y_lo <= y_hi && pix_y(g, y_hi) < fc.ymin) y_hi--;
+          if (x_lo <= x_hi && y_lo <= y_hi) {
+            const long long gi = (long long)b * a.job.view_stride + f;
+            sm.x[0][tid] = fc.ax; sm.x[1][tid] = fc.ay; sm.x[2][tid] = fc.bx;
+            sm.x[3][tid] = fc.by; sm.x[4][tid] = fc.cx; sm.x[5][tid] = fc.cy;
+            sm.z[0][tid] = __ldg(a.z + gi * 3);
+            sm.z[1][tid] = __ldg(a.z + gi * 3 + 1);
+            sm.z[2][tid] = __ldg(a.z + gi * 3 + 2);
+            sm.face[tid] = a.job.first ? f - (int)a.job.first[b] : f;
+            // edge functions E_k(x, y) = A_k x + B_k y + C_k in the local frame; inside
+            // <=> s E_k >= 0 for all k with s = sign(E_0 + E_1 + E_2) (twice the area)
+            const float ax = fc.ax - X0, ay = fc.ay - Y0, bx = fc.bx - X0, by = fc.by - Y0;
+            const float cx = fc.cx - X0, cy = fc.cy - Y0;
+            const float A[3] = {by - cy, cy - ay, ay - by};
+            const float Bc[3] = {cx - bx, ax - cx, bx - ax};
+            const float C[3] = {bx * cy - by * cx, cx * ay - cy * ax, ax * by - ay * bx};
+            const float area2 = (bx - ax) * (cy - ay) - (by - ay) * (cx - ax);
+            const float sA = fabsf(A[0]) + fabsf(A[1]) + fabsf(A[2]);
+            const float sB = fabsf(Bc[0]) + fabsf(Bc[1]) + fabsf(Bc[2]);
+            const float R = fmaxf(fmaxf(fmaxf(fabsf(ax), fabsf(bx)), fabsf(cx)),
+                                  fmaxf(fmaxf(fabsf(ay), fabsf(by)), fabsf(cy))) +
+                            (float)BLK * fmaxf(pitch_x, pitch_y);
+            // cull only where the arithmetic below is far inside its error bounds: a clear
+            // orientation, coordinates of moderate size
+            cull = fabsf(area2) > 0x1p-10f * sA * sB + 0x1p-6f &&
+                   R < 4096.f * fminf(pitch_x, pitch_y);
+            const float s = area2 < 0.f ? -1.f : 1.f;
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+              // keep a pixel unless s E_k < -m_k: m_k = an eighth of a pixel step of E_k in x
+              // and in y, plus 64 ulp of R^2, which bounds (with a factor > 8 to spare) both
+              // the rounding of the reference's own w_k and of this evaluation
+              const float m = 0.125f * (fabsf(A[k]) * pitch_x + fabsf(Bc[k]) * pitch_y) +
+                              0x1p-18f * R * R + 0x1p-10f;
+              ia[k] = 1.0f / (s * A[k] * pitch_x);
+              sb[k] = s * Bc[k];
+              scm[k] = s * C[k] + m;
+            }
+          } else {
+            x_hi = x_lo - 1;  // empty
+          }
+        } else {
+          x_lo = 0; x_hi = -1; y_lo = 0; y_hi = -1;
+        }
+      }
+    }
+    const int h = (x_lo <= x_hi && y_lo <= y_hi) ? y_hi - y_lo + 1 : 0;
+    int rtotal;
+    const int rbase = block_scan(h, sm.wsum, lane, warp, rtotal);
+    sm.rpre[tid] = rbase;
+    if (tid == 0) sm.rpre[kRasterThreads] = rtotal;
+    __syncthreads();
+    if (rtotal == 0) continue;  // uniform
+
+    // ---- row batches: the faces whose first row falls into [bi, bi + 1) * kRowBatch
+    for (int rb = 0; rb < rtotal; rb += kRowBatch) {
+      // first / one-past-last face of the batch (binary search in the row prefix)
+      int f_lo = 0, f_hi = 0;
+#pragma unroll
+      for (int st = kRasterThreads / 2; st > 0; st >>= 1) {
+        if (sm.rpre[f_lo + st] < rb) f_lo += st;
+        if (sm.rpre[f_hi + st] < rb + kRowBatch) f_hi += st;
+      }
+      if (sm.rpre[f_lo] < rb) f_lo++;
+      if (sm.rpre[f_hi] < rb + kRowBatch) f_hi++;
+      const int row0 = sm.rpre[f_lo];
+      const int nrows = sm.rpre[f_hi] - row0;  // <= kRowBatch + BLK
+      // ---- phase A2: the owning thread turns each of its rows into a span [xa, xa + len)
+      const bool mine = tid >= f_lo && tid < f_hi && h > 0;
+      int cand = 0;
+      if (mine) {
+        const int rxl = x_lo - bx0, rxh = x_hi - bx0;
+        for (int i = 0; i < h; i++) {
+          const int ry = y_lo - by0 + i;
+          int xa = rxl, xb = rxh;
+          if (cull) {
+            const float yl = -(float)ry * pitch_y;
+            float L = (float)rxl, U = (float)rxh;
+#pragma unroll
+            for (int k = 0; k < 3; k++) {
+              const float t = -(sb[k] * yl + scm[k]) * ia[k];  // s E_k = -m_k crossing [pixels]
+              if (ia[k] > 0.f) L = fmaxf(L, t); else U = fminf(U, t);
+            }
+            L = fminf(L, 1e6f);
+            U = fmaxf(U, -1e6f);
+            xa = max(rxl, (int)ceilf(L - 0.01f));
+            xb = min(rxh, (int)floorf(U + 0.01f));
+          }
+          const int len = max(xb - xa + 1, 0);
+          sm.span[rbase - row0 + i] = (unsigned)tid | ((unsigned)ry << 8) | ((unsigned)xa << 16) |
+                                      ((unsigned)len << 24);
+          cand += len;
+        }
+      }
+      int ctotal;
+      int crun = block_scan(cand, sm.wsum, lane, warp, ctotal);
+      if (mine) {
+        for (int i = 0; i < h; i++) {
+          sm.spre[rbase - row0 + i] = crun;
+          crun += (int)(sm.span[rbase - row0 + i] >> 24);
+        }
+      }
+      if (tid == 0) sm.spre[nrows] = ctotal;
+      __syncthreads();
+
+      // ---- phase B: the batch's candidates dealt out evenly, a contiguous run per thread;
+      // every candidate takes the reference's exact test (the spans hold few misses)
+      if (ctotal > 0) {
+        const int per = (ctotal + kRasterThreads - 1) / kRasterThreads;
+        int k = tid * per;
+        const int k_end = min(k + per, ctotal);
+        if (k < k_end) {
+          int r = 0;
+          for (int st = 2048; st > 0; st >>= 1)  // nrows < 4096
+            if (r + st <= nrows && sm.spre[r + st] <= k) r += st;
+          unsigned sp = sm.span[r];
+          int slot = sp & 0xff, ry = (sp >> 8) & 0xff;
+          int rx = ((sp >> 16) & 0xff) + (k - sm.spre[r]);
+          int left = sm.spre[r + 1] - k;  // candidates left in this row, this one included
+          float ax = sm.x[0][slot], ay = sm.x[1][slot], bx = sm.x[2][slot];
+          float by = sm.x[3][slot], cx = sm.x[4][slot], cy = sm.x[5][slot];
+          float y0 = pix_y(g, by0 + ry);
+          while (true) {
+            const float x0 = pix_x(g, bx0 + rx);
+            float w0, w1, w2;
+            if (raster_weights(x0, y0, ax, ay, bx, by, cx, cy, a.eps_d, w0, w1, w2)) {
+              const unsigned long long key = depth_key(
+                  raster_depth(w0, w1, w2, sm.z[0][slot], sm.z[1][slot], sm.z[2][slot]),
+                  sm.face[slot]);
+              if (key) smem_max64(&zbuf[(ry << BLK_LOG2) + rx], key);
+            }
+            if (++k >= k_end) break;
+            rx++;
+            if (--left == 0) {
+              do { r++; } while (sm.spre[r + 1] == sm.spre[r]);
+              sp = sm.span[r];
+              const int ns = sp & 0xff;
+              ry = (sp >> 8) & 0xff;
+              rx = (sp >> 16) & 0xff;
+              left = sp >> 24;
+              y0 = pix_y(g, by0 + ry);
+              if (ns != slot) {
+                slot = ns;
+                ax = sm.x[0][slot]; ay = sm.x[1][slot]; bx = sm.x[2][slot];
+                by = sm.x[3][slot]; cx = sm.x[4][slot]; cy = sm.x[5][slot];
+              }
             }
           }
         }
       }
-      sm.rect[tid] = rect;
+      __syncthreads();  // spans / staged faces free for the next batch / chunk
     }
-    // block-wide exclusive scan of the candidate counts
-    int incl = cand;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-      const int t = __shfl_up_sync(DIBR_FULL_MASK, incl, d);
-      if (lane >= d) incl += t;
-    }
-    if (lane == 31) sm.wsum[warp] = incl;
-    __syncthreads();
-    int woff = 0, total = 0;
-#pragma unroll
-    for (int i = 0; i < kRasterWarps; i++) {
-      const int v = sm.wsum[i];
-      if (i < warp) woff += v;
-      total += v;
-    }
-    sm.pre[tid] = woff + incl - cand;
-    if (tid == 0) sm.pre[kRasterThreads] = total;
-    __syncthreads();
-    if (total == 0) continue;
-
-    // ---- phase B: the chunk's (face, pixel) candidates dealt out evenly, a contiguous
-    // run per thread; cheap sign test for all, survivors compacted into the warp's queue
-    const int per = (total + kRasterThreads - 1) / kRasterThreads;
-    int k = tid * per;
-    const int k_end = min(k + per, total);
-    int s = 0, rx0 = 0, rw = 1, rx = 0, ry = 0, left = 0;
-    float ax = 0.f, ay = 0.f, bx = 0.f, by = 0.f, cx = 0.f, cy = 0.f, y0 = 0.f;
-    if (k < k_end) {
-#pragma unroll
-      for (int st = kRasterThreads / 2; st > 0; st >>= 1)
-        if (sm.pre[s + st] <= k) s += st;
-      const int r = sm.rect[s];
-      rx0 = r & 0xff; rw = ((r >> 16) & 0xff) + 1;
-      const int off = k - sm.pre[s];
-      ry = (r >> 8 & 0xff) + off / rw;
-      rx = rx0 + off % rw;
-      left = sm.pre[s + 1] - k;  // candidates left in this face, this one included
-      ax = sm.x[0][s]; ay = sm.x[1][s]; bx = sm.x[2][s];
-      by = sm.x[3][s]; cx = sm.x[4][s]; cy = sm.x[5][s];
-      y0 = pix_y(g, by0 + ry);
-    }
-    int qhead = 0, qn = 0;  // warp-uniform
-    for (int it = 0; it < per; it++) {
-      bool keep = false;
-      if (k < k_end) {
-        const float x0 = pix_x(g, bx0 + rx);
-        const float a_ex = __fsub_rn(ax, x0), a_ey = __fsub_rn(ay, y0);
-        const float b_ex = __fsub_rn(bx, x0), b_ey = __fsub_rn(by, y0);
-        const float c_ex = __fsub_rn(cx, x0), c_ey = __fsub_rn(cy, y0);
-        const float w0 = __fmaf_rn(b_ex, c_ey, -__fmul_rn(b_ey, c_ex));
-        const float w1 = __fmaf_rn(c_ex, a_ey, -__fmul_rn(c_ey, a_ex));
-        const float w2 = __fmaf_rn(a_ex, b_ey, -__fmul_rn(a_ey, b_ex));
-        const float n32 = __fadd_rn(__fadd_rn(w0, w1), w2);
-        keep = !(fast_ok && surely_outside(w0, w1, w2, n32));
-      }
-      const unsigned m = __ballot_sync(DIBR_FULL_MASK, keep);
-      if (keep)
-        queue[(qhead + qn + __popc(m & lanemask_lt())) & (kQueue - 1)] =
-            (unsigned)s | ((unsigned)rx << 8) | ((unsigned)ry << 16);
-      qn += __popc(m);
-      __syncwarp();
-      if (qn >= 32) {
-        drain(qhead, 32);
-        qhead = (qhead + 32) & (kQueue - 1);
-        qn -= 32;
-        __syncwarp();
-      }
-      // advance to the next candidate of this thread's run
-      if (++k < k_end) {
-        if (--left == 0) {
-          do { s++; } while (sm.pre[s + 1] == sm.pre[s]);
-          const int r = sm.rect[s];
-          rx0 = r & 0xff; rw = ((r >> 16) & 0xff) + 1;
-          rx = rx0; ry = (r >> 8) & 0xff;
-          left = sm.pre[s + 1] - sm.pre[s];
-          ax = sm.x[0][s]; ay = sm.x[1][s]; bx = sm.x[2][s];
-          by = sm.x[3][s]; cx = sm.x[4][s]; cy = sm.x[5][s];
-          y0 = pix_y(g, by0 + ry);
-        } else if (++rx == rx0 + rw) {
-          rx = rx0;
-          ry++;
-          y0 = pix_y(g, by0 + ry);
-        }
-      }
-    }
-    if (qn > 0) drain(qhead, qn);
   }
   __syncthreads();
 
