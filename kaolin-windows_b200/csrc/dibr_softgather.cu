@@ -336,17 +336,27 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
 #endif
 }
 
+template <int G_LOG2>
+static cudaError_t launch_gather(const SoftArgs& a, const Plan& p, cudaStream_t st) {
+  static bool once = false;
+  const int smem = (int)sizeof(GatherSmem<G_LOG2>);
+  if (!once) {
+    cudaError_t e = cudaFuncSetAttribute(softmask_gather_kernel<G_LOG2>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    once = true;
+  }
+  dim3 grid((p.W + (1 << G_LOG2) - 1) >> G_LOG2, (p.H + (1 << G_LOG2) - 1) >> G_LOG2, p.B);
+  softmask_gather_kernel<G_LOG2><<<grid, kGThreads, smem, st>>>(a, p);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_softmask_gather(const SoftArgs& a, const Plan& p, cudaStream_t st) {
   prof_begin(K_SOFT_GATHER, st);
-  if (p.blk_log2 == 5) {
-    dim3 grid((p.W + 15) >> 4, (p.H + 15) >> 4, p.B);
-    softmask_gather_kernel<4><<<grid, kGThreads, sizeof(GatherSmem<4>), st>>>(a, p);
-  } else {
-    dim3 grid((p.W + 31) >> 5, (p.H + 31) >> 5, p.B);
-    softmask_gather_kernel<5><<<grid, kGThreads, sizeof(GatherSmem<5>), st>>>(a, p);
-  }
+  // a quarter (or less) of a raster block per CTA
+  cudaError_t e = p.blk_log2 == 5 ? launch_gather<4>(a, p, st) : launch_gather<5>(a, p, st);
   prof_end(st);
-  return cudaGetLastError();
+  return e;
 }
 
 }  // namespace dibr

@@ -128,6 +128,7 @@ class DibrRasterizationB200(Function):
                                                      int(knum))
         ctx.save_for_backward(idx, img, feat, mask, ws)
         ctx.mark_non_differentiable(idx)
+        ctx.set_materialize_grads(False)
         ctx.args = (float(sigmainv), margin, int(knum), float(multiplier), float(eps), cap_r, cap_s,
                     cap_p)
         return out, mask, idx

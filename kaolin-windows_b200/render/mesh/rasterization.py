@@ -77,12 +77,15 @@ class RasterizeB200(Function):
             _workspace.run("raster", dev, B, F, height, width, True, False, call)
         ctx.save_for_backward(idx, img, feat)
         ctx.mark_non_differentiable(idx)
+        ctx.set_materialize_grads(False)
         ctx.eps = float(eps)
         ctx.multiplier = float(multiplier)
         return out, idx
 
     @staticmethod
     def backward(ctx, grad_interpolated_features, grad_face_idx):
+        if grad_interpolated_features is None:
+            return (None,) * 8
         idx, img, feat = ctx.saved_tensors
         B, F = img.shape[:2]
         H, W = idx.shape[1:]

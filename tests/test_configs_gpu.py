@@ -99,6 +99,17 @@ def test_odd_image_sizes(kal, ref, H, W):
     full_compare(kal, ref, inp, H, W, grads=(H * W >= 512))   # ref bwd needs >= 512 px
 
 
+def test_large_image_64px_blocks(kal, ref):
+    """More than 1024 bins of 32 px -> 64-px bins and blocks (the BLK = 64 kernel variants,
+    four gather CTAs per bin)."""
+    g = wl.fixture_geometry(batch_size=2)
+    inp = dict(face_vertices_z=g["face_vertices_z"].to(DEV),
+               face_vertices_image=g["face_vertices_image"].to(DEV),
+               face_features=g["face_uvs"].to(DEV), face_normals_z=g["face_normals_z"].to(DEV))
+    s = full_compare(kal, ref, inp, 1100, 1090)
+    assert s["covered"] > 100000 and s["soft"] > 1000
+
+
 @pytest.mark.parametrize("knum,boxlen,sigmainv,multiplier,eps",
                          [(5, 0.05, 7000, 1000, 1e-8), (100, 0.2, 70, 100, 1e-6),
                           (1, 0.02, 7000, 1, 1e-8), (30, 0.0, 7000, 1000, 1e-8)])
