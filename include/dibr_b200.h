@@ -126,8 +126,10 @@ DIBR_API int dibr_rasterize_fwd(int batch, int num_faces, int height, int width,
  * rasterization_cuda.cu:238-402).  face_vertices_image is UNscaled (B, F, 3, 2).
  * output_weights may be NULL: the weights are then recomputed bit-identically from
  * (face_vertices_image * multiplier, pixel centre, eps) as the forward did.
- * grad_face_vertices_image (B,F,3,2) and grad_face_features (B,F,3,D) are ACCUMULATED
- * into (the caller zero-fills them, as at::zeros_like does at rasterization.cpp:156-157).
+ * grad_face_vertices_image (B,F,3,2) is ACCUMULATED into; grad_face_features (B,F,3,D)
+ * MUST be zero-filled by the caller (at::zeros_like at rasterization.cpp:156-157): it
+ * doubles as the per-face moment accumulator of the two-pass backward and is rewritten
+ * in place.
  * face_vertices_z receives no gradient (rasterization.py:387-388).
  */
 DIBR_API int dibr_rasterize_bwd(int batch, int num_faces, int height, int width, int feat_dim,

@@ -333,14 +333,45 @@ cudaError_t launch_raster_forward(const RasterArgs& a, const Plan& p, cudaStream
 }
 
 // ===========================================================================
-// Backward (rasterization_cuda.cu:238-402), pixel-parallel.
+// Backward (rasterization_cuda.cu:238-402).
 //
-// The reference issues 9*D global atomics per covered pixel.  Here a warp owns an
-// 8x4 pixel region; lanes that selected the same face are grouped with
-// __match_any_sync and their contributions are summed with shuffles first, so one
-// red.global.add per (face, component) leaves the warp, and the 6 image-coordinate
-// terms are summed over the feature dimension in registers before that.
+// The reference issues 9*D global atomics per covered pixel and ~200 flops.  Its
+// per-pixel terms are, however, affine in the pixel position: with (s, t) = pixel - vertex
+// a (unscaled coordinates) and the face constants m, p, n, q, k3 (:305-322),
+//     w1 = (s q - n t) / k3,  w2 = (m t - s p) / k3,  w0 = 1 - w1 - w2,
+// and every d(w1|w2)/d(vertex) (:324-374) is (const + const s + const t) / k3^2.  So all a
+// face needs from its pixels are the 3*D MOMENTS  M0_d = sum g_d, Ms_d = sum g_d s,
+// Mt_d = sum g_d t  of the incoming gradient g over the pixels that selected it:
+//   pass 1 (pixel-parallel): a warp owns an 8x4 region; lanes with the same face are
+//     grouped with __match_any_sync, their moments summed with shuffles, and ONE
+//     red.global.add per (face, moment) leaves the warp -- into grad_face_features, whose
+//     (3, D) slot per face is used as the moment accumulator;
+//   pass 2 (face-parallel): turns the moments of every touched face into grad_face_features
+//     (in place) and grad_face_vertices_image (added) with plain stores.
+// Faces for which the moment form would not stay within a few ulp of the per-pixel form
+// keep the reference's per-pixel arithmetic in pass 1 and are skipped by pass 2: slivers
+// and zero-area faces (|k3| < 1% of |m q| + |n p|) and faces smaller than two pixels
+// (|k3| < 4 pixel areas) -- the latter own one or two pixels, have the largest gradients
+// (~ 1 / k3^2) and gain nothing from the moments anyway.
 // ===========================================================================
+
+// face constants of the backward (unscaled coordinates); regular = moment form applies
+struct BwdFace {
+  float ax, ay, m, p, n, q, k3raw;
+  bool regular;
+};
+__device__ __forceinline__ BwdFace bwd_face(const float* img, long long fbase, float min_k3) {
+  const float2* ip = reinterpret_cast<const float2*>(img + fbase * 6);
+  const float2 A = __ldg(ip), Bv = __ldg(ip + 1), C = __ldg(ip + 2);
+  BwdFace f;
+  f.ax = A.x; f.ay = A.y;
+  f.m = Bv.x - A.x; f.p = Bv.y - A.y; f.n = C.x - A.x; f.q = C.y - A.y;
+  f.k3raw = f.m * f.q - f.n * f.p;
+  // (false for NaN / Inf coordinates as well)
+  f.regular = fabsf(f.k3raw) >= 0.01f * (fabsf(f.m * f.q) + fabsf(f.n * f.p)) &&
+              fabsf(f.k3raw) >= min_k3 && fabsf(f.k3raw) < 3e38f;
+  return f;
+}
 
 template <int N>
 __device__ __forceinline__ void reduce_peers(unsigned peers, float (&v)[N], int lane) {
@@ -374,18 +405,56 @@ __global__ void __launch_bounds__(256) raster_backward_kernel(const RasterBwdArg
   const unsigned peers = __match_any_sync(DIBR_FULL_MASK, face);
   const bool leader = (peers & lanemask_lt()) == 0;
 
-  float gimg[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-  float w[3] = {0.f, 0.f, 0.f};
-  float dw1[6], dw2[6];  // dw*: d(w1|w2 * k3^2)/d(ax,ay,bx,by,cx,cy)
-  float inv_k3sq = 0.f;
-#pragma unroll
-  for (int i = 0; i < 6; i++) dw1[i] = dw2[i] = 0.f;
   long long fbase = 0;
+  float s = 0.f, t = 0.f;
+  bool regular = false;
+  BwdFace fc;
   if (face >= 0) {
     fbase = (long long)b * a.F + face;
+    fc = bwd_face(a.img, fbase, 16.f / ((float)a.W * (float)a.H));
+    regular = fc.regular;
+    // pixel centre (what :302-303 reconstruct from the weights) minus vertex a, unscaled.
+    // The difference is taken in double: for faces much smaller than the image the float
+    // rounding of the centre itself (~6e-8) would be a visible fraction of (s, t).
+    s = (float)((double)(2 * ix + 1 - a.W) / (double)a.W - (double)fc.ax);
+    t = (float)((double)(a.H - 2 * iy - 1) / (double)a.H - (double)fc.ay);
+  }
+  for (int d0 = 0; d0 < a.D; d0 += DC) {
+    float mom[3 * DC];
+#pragma unroll
+    for (int i = 0; i < 3 * DC; i++) mom[i] = 0.f;
+    if (regular) {
+#pragma unroll
+      for (int dd = 0; dd < DC; dd++) {
+        if (d0 + dd < a.D) {
+          const float gd = a.grad[pix * a.D + d0 + dd];
+          mom[dd] = gd;
+          mom[DC + dd] = gd * s;
+          mom[2 * DC + dd] = gd * t;
+        }
+      }
+    }
+    reduce_peers<3 * DC>(peers, mom, lane);
+    if (leader && regular) {
+      float* gp = a.grad_feat + fbase * 3 * a.D;
+#pragma unroll
+      for (int dd = 0; dd < DC; dd++) {
+        const int d = d0 + dd;
+        if (d < a.D) {
+          atomicAdd(gp + d, mom[dd]);
+          atomicAdd(gp + a.D + d, mom[DC + dd]);
+          atomicAdd(gp + 2 * a.D + d, mom[2 * DC + dd]);
+        }
+      }
+    }
+  }
+
+  // ---- thin faces: the reference's per-pixel arithmetic (:273-399), straight atomics
+  if (face >= 0 && !regular) {
     const float2* ip = reinterpret_cast<const float2*>(a.img + fbase * 6);
     const float2 A = __ldg(ip), Bv = __ldg(ip + 1), C = __ldg(ip + 2);
     const float ax = A.x, ay = A.y, bx = Bv.x, by = Bv.y, cx = C.x, cy = C.y;
+    float w[3];
     if (a.weights) {
       w[0] = a.weights[pix * 3]; w[1] = a.weights[pix * 3 + 1]; w[2] = a.weights[pix * 3 + 2];
     } else {
@@ -394,70 +463,87 @@ __global__ void __launch_bounds__(256) raster_backward_kernel(const RasterBwdArg
                      __fmul_rn(bx, a.mult), __fmul_rn(by, a.mult), __fmul_rn(cx, a.mult),
                      __fmul_rn(cy, a.mult), a.eps_d, w[0], w[1], w[2]);
     }
-    // rasterization_cuda.cu:302-374
     const float x0 = w[0] * ax + w[1] * bx + w[2] * cx;
     const float y0 = w[0] * ay + w[1] * by + w[2] * cy;
-    const float m = bx - ax, pp = by - ay, n = cx - ax, q = cy - ay, s = x0 - ax, t = y0 - ay;
-    const float k1 = s * q - n * t;
-    const float k2 = m * t - s * pp;
+    const float m = bx - ax, pp = by - ay, n = cx - ax, q = cy - ay, ss = x0 - ax, tt = y0 - ay;
+    const float k1 = ss * q - n * tt;
+    const float k2 = m * tt - ss * pp;
     float k3 = m * q - n * pp;
     k3 = (float)((double)k3 + copysign(a.eps_d, (double)k3));
-    const float dw1dm = 0.f * k3 - q * k1, dw1dn = (-t) * k3 - (-pp) * k1;
-    const float dw1dp = 0.f * k3 - (-n) * k1, dw1dq = s * k3 - m * k1;
+    float dw1[6], dw2[6];
+    const float dw1dm = 0.f * k3 - q * k1, dw1dn = (-tt) * k3 - (-pp) * k1;
+    const float dw1dp = 0.f * k3 - (-n) * k1, dw1dq = ss * k3 - m * k1;
     const float dw1ds = q * k3 - 0.f * k1, dw1dt = (-n) * k3 - 0.f * k1;
-    const float dw2dm = t * k3 - q * k2, dw2dn = 0.f * k3 - (-pp) * k2;
-    const float dw2dp = (-s) * k3 - (-n) * k2, dw2dq = 0.f * k3 - m * k2;
+    const float dw2dm = tt * k3 - q * k2, dw2dn = 0.f * k3 - (-pp) * k2;
+    const float dw2dp = (-ss) * k3 - (-n) * k2, dw2dq = 0.f * k3 - m * k2;
     const float dw2ds = (-pp) * k3 - 0.f * k2, dw2dt = m * k3 - 0.f * k2;
     dw1[0] = -(dw1dm + dw1dn + dw1ds); dw1[1] = -(dw1dp + dw1dq + dw1dt);
     dw1[2] = dw1dm; dw1[3] = dw1dp; dw1[4] = dw1dn; dw1[5] = dw1dq;
     dw2[0] = -(dw2dm + dw2dn + dw2ds); dw2[1] = -(dw2dp + dw2dq + dw2dt);
     dw2[2] = dw2dm; dw2[3] = dw2dp; dw2[4] = dw2dn; dw2[5] = dw2dq;
-    inv_k3sq = 1.0f / (k3 * k3);
+    const float* fp = a.feat + fbase * 3 * a.D;
+    float* gf = a.grad_feat + fbase * 3 * a.D;
+    float* gi = a.grad_img + fbase * 6;
+    for (int d = 0; d < a.D; d++) {
+      const float gd = a.grad[pix * a.D + d];
+      atomicAdd(gf + d, gd * w[0]);
+      atomicAdd(gf + a.D + d, gd * w[1]);
+      atomicAdd(gf + 2 * a.D + d, gd * w[2]);
+      const float c0 = __ldg(fp + d), c1 = __ldg(fp + a.D + d), c2 = __ldg(fp + 2 * a.D + d);
+      const float dldI = gd / (k3 * k3);
+#pragma unroll
+      for (int i = 0; i < 6; i++) atomicAdd(gi + i, dldI * ((c1 - c0) * dw1[i] + (c2 - c0) * dw2[i]));
+    }
   }
+}
 
-  for (int d0 = 0; d0 < a.D; d0 += DC) {
-    float gf[3 * DC];
-#pragma unroll
-    for (int i = 0; i < 3 * DC; i++) gf[i] = 0.f;
-    if (face >= 0) {
-      const float* fp = a.feat + fbase * 3 * a.D;
-#pragma unroll
-      for (int dd = 0; dd < DC; dd++) {
-        const int d = d0 + dd;
-        if (d < a.D) {
-          const float gd = a.grad[pix * a.D + d];
-          gf[dd] = gd * w[0];            // :273-285
-          gf[DC + dd] = gd * w[1];
-          gf[2 * DC + dd] = gd * w[2];
-          const float c0 = __ldg(fp + d), c1 = __ldg(fp + a.D + d), c2 = __ldg(fp + 2 * a.D + d);
-          const float dldI = gd * inv_k3sq;  // :389 (gd / k3^2; one reciprocal per pixel)
-          const float e1 = c1 - c0, e2 = c2 - c0;
-#pragma unroll
-          for (int i = 0; i < 6; i++) gimg[i] += dldI * (e1 * dw1[i] + e2 * dw2[i]);
-        }
-      }
-    }
-    reduce_peers<3 * DC>(peers, gf, lane);
-    if (leader && face >= 0) {
-      float* gp = a.grad_feat + fbase * 3 * a.D;
-#pragma unroll
-      for (int dd = 0; dd < DC; dd++) {
-        const int d = d0 + dd;
-        if (d < a.D) {
-          atomicAdd(gp + d, gf[dd]);
-          atomicAdd(gp + a.D + d, gf[DC + dd]);
-          atomicAdd(gp + 2 * a.D + d, gf[2 * DC + dd]);
-        }
-      }
-    }
+// pass 2: moments -> gradients, one thread per (view, face)
+__global__ void __launch_bounds__(256) raster_backward_finish_kernel(const RasterBwdArgs a) {
+  const long long fbase = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (fbase >= (long long)a.B * a.F) return;
+  float* gf = a.grad_feat + fbase * 3 * a.D;
+  // untouched faces (most of them: back faces, hidden faces) hold zeros and keep them
+  bool any = false;
+  for (int i = 0; i < 3 * a.D; i++) any |= gf[i] != 0.f;
+  if (!any) return;
+  const BwdFace fc = bwd_face(a.img, fbase, 16.f / ((float)a.W * (float)a.H));
+  if (!fc.regular) return;  // thin / tiny face: pass 1 wrote its gradients directly
+  const float m = fc.m, p = fc.p, n = fc.n, q = fc.q;
+  const float k3 = (float)((double)fc.k3raw + copysign(a.eps_d, (double)fc.k3raw));  // :321-322
+  const float inv_k3 = 1.0f / k3;
+  // the forward's weights carry eps only on the SCALED normalisation (negligible); the
+  // eps on the unscaled k3 belongs to the coordinate gradient alone (:321-322)
+  const float inv_k3raw = 1.0f / fc.k3raw;
+  const float* fp = a.feat + fbase * 3 * a.D;
+  float P0 = 0.f, Ps = 0.f, Pt = 0.f, Q0 = 0.f, Qs = 0.f, Qt = 0.f;
+  for (int d = 0; d < a.D; d++) {
+    const float M0 = gf[d], Ms = gf[a.D + d], Mt = gf[2 * a.D + d];
+    const float c0 = __ldg(fp + d), c1 = __ldg(fp + a.D + d), c2 = __ldg(fp + 2 * a.D + d);
+    const float e1 = c1 - c0, e2 = c2 - c0;
+    P0 += e1 * M0; Ps += e1 * Ms; Pt += e1 * Mt;
+    Q0 += e2 * M0; Qs += e2 * Ms; Qt += e2 * Mt;
+    // grad_face_features: sum g w_k with w1 = k1 / k3, w2 = k2 / k3, w0 = 1 - w1 - w2
+    const float g1 = (Ms * q - n * Mt) * inv_k3raw;
+    const float g2 = (m * Mt - Ms * p) * inv_k3raw;
+    gf[d] = M0 - g1 - g2;
+    gf[a.D + d] = g1;
+    gf[2 * a.D + d] = g2;
   }
-  reduce_peers<6>(peers, gimg, lane);
-  if (leader && face >= 0) {
-    // (x, y) of a vertex are adjacent and 8-byte aligned: three vector reductions
-    float2* gp = reinterpret_cast<float2*>(a.grad_img + fbase * 6);
-#pragma unroll
-    for (int i = 0; i < 3; i++) atomicAdd(gp + i, make_float2(gimg[2 * i], gimg[2 * i + 1]));
-  }
+  // :324-374 with (1, s, t) replaced by their e1- / e2-weighted sums over the pixels
+  const float K1 = Ps * q - n * Pt, K2 = m * Qt - Qs * p;
+  const float dm = -q * K1 + (Qt * k3 - q * K2);
+  const float dn = (-Pt * k3 + p * K1) + p * K2;
+  const float dp = n * K1 + (-Qs * k3 + n * K2);
+  const float dq = (Ps * k3 - m * K1) - m * K2;
+  const float ds = q * k3 * P0 - p * k3 * Q0;
+  const float dt = -n * k3 * P0 + m * k3 * Q0;
+  const float r = inv_k3 * inv_k3;
+  float2* gi = reinterpret_cast<float2*>(a.grad_img + fbase * 6);
+  float2 ga = gi[0], gb = gi[1], gc = gi[2];
+  ga.x += -(dm + dn + ds) * r; ga.y += -(dp + dq + dt) * r;
+  gb.x += dm * r; gb.y += dp * r;
+  gc.x += dn * r; gc.y += dq * r;
+  gi[0] = ga; gi[1] = gb; gi[2] = gc;
 }
 
 cudaError_t launch_raster_backward(const RasterBwdArgs& a, cudaStream_t st) {
@@ -469,6 +555,8 @@ cudaError_t launch_raster_backward(const RasterBwdArgs& a, cudaStream_t st) {
     case 3: raster_backward_kernel<3><<<grid, 256, 0, st>>>(a); break;
     default: raster_backward_kernel<4><<<grid, 256, 0, st>>>(a); break;
   }
+  const long long nf = (long long)a.B * a.F;
+  raster_backward_finish_kernel<<<(unsigned)((nf + 255) / 256), 256, 0, st>>>(a);
   prof_end(st);
   return cudaGetLastError();
 }

@@ -292,6 +292,16 @@ def dibr_rasterization_backward(ctxs, grad_features, grad_soft_mask, ops=_CpuOps
     return gi + gi2, gf
 
 
+def ctxs_to_double(ctxs):
+    """The saved forward state with every floating tensor cast to float64 and every
+    discrete choice (face indices, nearest-feature types) kept: running the backward on it
+    gives a low-noise reference for the SAME discrete decisions the fp32 forward took."""
+    def lift(ctx):
+        return {k: (v.double() if torch.is_tensor(v) and v.is_floating_point() else v)
+                for k, v in ctx.items()}
+    return tuple(lift(c) for c in ctxs)
+
+
 def mask_iou(lhs_mask, rhs_mask):
     """kaolin/metrics/render.py:18-40 (used by the reference's golden-gradient tests)."""
     batch_size = lhs_mask.shape[0]
