@@ -314,6 +314,7 @@ extern "C" int dibr_rasterize_bwd(int B, int F, int H, int W, int D, const float
   a.grad_img = grad_img; a.grad_feat = grad_feat;
   a.B = B; a.F = F; a.H = H; a.W = W; a.D = D;
   a.mult = multiplier; a.eps_f = eps; a.eps_d = (double)eps;
+  a.inv_w = 1.0 / (double)W; a.inv_h = 1.0 / (double)H;
   DIBR_CUDA(launch_raster_backward(a, (cudaStream_t)stream));
   return DIBR_OK;
 }

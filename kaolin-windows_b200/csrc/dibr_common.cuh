@@ -96,6 +96,7 @@ struct RasterBwdArgs {
   float mult;
   float eps_f;
   double eps_d;
+  double inv_w, inv_h;     // 1 / W, 1 / H
 };
 
 // Compact per-pixel face lists of the soft mask ("pairs"), kept between forward and

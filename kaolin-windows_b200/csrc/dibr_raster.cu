@@ -392,7 +392,7 @@ __device__ __forceinline__ void reduce_peers(unsigned peers, float (&v)[N], int 
 }
 
 template <int DC>  // features handled per pass (D <= 4: one pass)
-__global__ void __launch_bounds__(256) raster_backward_kernel(const RasterBwdArgs a) {
+__global__ void __launch_bounds__(256, 6) raster_backward_kernel(const RasterBwdArgs a) {
   const int lane = lane_id(), warp = threadIdx.x >> 5;
   const int ix = (blockIdx.x << 4) + ((warp & 1) << 3) + (lane & 7);
   const int iy = (blockIdx.y << 4) + ((warp >> 1) << 2) + (lane >> 3);
@@ -416,8 +416,8 @@ __global__ void __launch_bounds__(256) raster_backward_kernel(const RasterBwdArg
     // pixel centre (what :302-303 reconstruct from the weights) minus vertex a, unscaled.
     // The difference is taken in double: for faces much smaller than the image the float
     // rounding of the centre itself (~6e-8) would be a visible fraction of (s, t).
-    s = (float)((double)(2 * ix + 1 - a.W) / (double)a.W - (double)fc.ax);
-    t = (float)((double)(a.H - 2 * iy - 1) / (double)a.H - (double)fc.ay);
+    s = (float)((double)(2 * ix + 1 - a.W) * a.inv_w - (double)fc.ax);
+    t = (float)((double)(a.H - 2 * iy - 1) * a.inv_h - (double)fc.ay);
   }
   for (int d0 = 0; d0 < a.D; d0 += DC) {
     float mom[3 * DC];
