@@ -1,0 +1,74 @@
+#!/usr/bin/env python
+"""Summarise an `ncu --set full` report: the metrics that matter per path kernel, and
+`profiles/traffic.json` (DRAM bytes per launch per kernel, read by bench.py's roofline).
+
+    python profiles/summarize_full.py gpurun_out/x.ncu-rep "header text" > profiles/<name>.txt
+"""
+import collections
+import csv
+import json
+import os
+import subprocess
+import sys
+
+METRICS = [
+    "gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum",
+    "launch__registers_per_thread", "launch__grid_size", "launch__block_size",
+    "sm__warps_active.avg.pct_of_peak_sustained_active",
+    "sm__throughput.avg.pct_of_peak_sustained_elapsed",
+    "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+    "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+    "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active",
+    "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active",
+    "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
+    "smsp__thread_inst_executed_per_inst_executed.ratio",
+    "sm__cycles_active.avg", "sm__cycles_active.max", "sm__cycles_elapsed.max",
+    "lts__t_sector_hit_rate.pct",
+]
+# bench.py's kernel names by substring of the ncu kernel name (first match wins)
+BENCH_NAMES = [
+    ("bin_walk_kernel<0>", "bin_count"), ("bin_walk_kernel<false>", "bin_count"),
+    ("bin_scan", "bin_scan"), ("bin_walk_kernel", "bin_fill"),
+    ("raster_forward", "raster_fwd"), ("raster_backward_finish", None),
+    ("raster_backward", "raster_bwd"), ("softmask_gather", "softmask_gather"),
+    ("softmask_pairs_eval", "softmask_eval"), ("softmask_pairs_grad", "softmask_grad"),
+]
+SCALE = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+
+
+def main():
+    rep = sys.argv[1]
+    out = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True,
+                         text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hdr, units = rows[0], rows[1]
+    ki = hdr.index("Kernel Name")
+    print("# %s; per launch" % (sys.argv[2] if len(sys.argv) > 2 else rep))
+    seen = collections.Counter()
+    traffic = {}
+    for r in rows[2:]:
+        name = r[ki]
+        seen[name] += 1
+        if seen[name] > 1:          # one launch per kernel is enough here
+            continue
+        print("----\nKernel Name = %s" % name)
+        dram = 0.0
+        for m in METRICS:
+            if m not in hdr:
+                continue
+            j = hdr.index(m)
+            print("%s = %s %s" % (m, r[j], units[j]))
+            if m.startswith("dram__bytes"):
+                dram += float(r[j].replace(",", "")) * SCALE.get(units[j], 1)
+        for sub, bname in BENCH_NAMES:
+            if sub in name:
+                if bname:
+                    traffic[bname] = traffic.get(bname, 0) + dram
+                break
+    here = os.path.dirname(os.path.abspath(__file__))
+    with open(os.path.join(here, "traffic.json"), "w") as fh:
+        json.dump({k: int(v) for k, v in traffic.items()}, fh, indent=1)
+
+
+if __name__ == "__main__":
+    main()
