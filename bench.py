@@ -197,13 +197,19 @@ def main():
     g2 = torch.rand((B, H, W), device=dev, generator=gen)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
 
-    def step(img_in, feat_in, z_in=z, nz_in=nz, exchange=True):
+    def step(img_in, feat_in, z_in=z, nz_in=nz, exchange=True, with_loss=False):
         img_l = img_in.detach().requires_grad_(True)
         feat_l = feat_in.detach().requires_grad_(True)
         out, mask, idx = kal.render.mesh.dibr_rasterization(H, W, z_in, img_l, feat_l, nz_in,
                                                             SIGMAINV, BOXLEN, KNUM)
-        loss = (out * g1).sum() + (mask * g2).sum()
-        loss.backward()
+        if with_loss:
+            loss = (out * g1).sum() + (mask * g2).sum()
+            loss.backward()
+        else:
+            # d loss / d out = g1, d loss / d mask = g2: the same backward without timing
+            # torch's multiply/reduce kernels, which are not part of the path
+            loss = None
+            torch.autograd.backward((out, mask), (g1, g2))
         if world > 1 and exchange:
             # local face -> vertex scatter-add, then ONE flat all-reduce of the shared
             # mesh's gradients (vertex image-plane positions per view stay local; what is
@@ -254,7 +260,7 @@ def main():
     def e2e_step():
         for d, h in zip(d_in, h_in):
             d.copy_(h, non_blocking=True)
-        return float(step(d_in[1], d_in[2], d_in[0], d_in[3]).item())   # D2H read of the loss
+        return float(step(d_in[1], d_in[2], d_in[0], d_in[3], with_loss=True).item())  # D2H of the loss
 
     for _ in range(3):
         e2e_step()
@@ -312,6 +318,18 @@ def main():
     except Exception:
         pass
 
+    # ---- forward only (SURVEY 8(d) asks for it beside fwd+bwd)
+    fe = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+          for _ in range(args.steps)]
+    with torch.no_grad():
+        for e0, e1 in fe:
+            flush.zero_()
+            e0.record()
+            kal.render.mesh.dibr_rasterization(H, W, z, img, feat, nz, SIGMAINV, BOXLEN, KNUM)
+            e1.record()
+    torch.cuda.synchronize(dev)
+    fwd_ms = sum(e0.elapsed_time(e1) for e0, e1 in fe) / args.steps
+
     line = {
         "metric": METRIC, "value": value, "unit": "Mpixels/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
@@ -320,11 +338,15 @@ def main():
         "config": {"workload": CFG, "views_per_gpu": B, "faces": F, "H": H, "W": W, "D": D,
                    "sigmainv": SIGMAINV, "boxlen": BOXLEN, "knum": KNUM,
                    "l2": "flushed between steps (256 MiB memset outside the per-step event spans)",
+                   "cotangents": "fixed random G1, G2 fed to autograd directly (= backward of "
+                                 "(features*G1).sum() + (soft_mask*G2).sum()); e2e computes "
+                                 "and reads back that loss",
                    "parallelism": "views sharded, %d per GPU" % B},
         "clocks": sampler.summary(),
         "e2e": {"value": e2e_val, "unit": "Mpixels/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 8, "ms_per_step": e2e_s * 1e3},
         "gpu_launches": launches_per_step * args.steps,
+        "fwd_only_ms_per_step": fwd_ms,
         "roofline": roofline,
     }
 
