@@ -211,15 +211,9 @@ def main():
             loss = None
             torch.autograd.backward((out, mask), (g1, g2))
         if world > 1 and exchange:
-            # local face -> vertex scatter-add, then ONE flat all-reduce of the shared
-            # mesh's gradients (vertex image-plane positions per view stay local; what is
-            # shared is the per-vertex feature and the summed positional signal)
-            fidx = faces.reshape(-1)
-            gvi = torch.zeros((V, 2), device=dev)
-            gvf = torch.zeros((V, D), device=dev)
-            gvi.index_add_(0, fidx, img_l.grad.sum(0).reshape(-1, 2))
-            gvf.index_add_(0, fidx, feat_l.grad.sum(0).reshape(-1, D))
-            kal.parallel.allreduce_mesh_grads([gvi, gvf])
+            # local face -> vertex scatter-add (one kernel per gradient into one flat
+            # (V, 2+D) buffer), then ONE all-reduce of the shared mesh's gradients
+            kal.parallel.exchange_mesh_grads(faces, V, img_l.grad, feat_l.grad)
         return loss
 
     def barrier():

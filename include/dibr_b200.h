@@ -201,6 +201,48 @@ DIBR_API int dibr_render_fwd(int batch, int num_faces, int height, int width, in
                     void* ws, int64_t ws_bytes, int64_t raster_capacity, int64_t soft_capacity,
                     int64_t pair_capacity, int64_t* needed_host, void* stream);
 
+/* ---------------------------------------------------------------------------------------
+ * Next to the path: the (views x faces)-sized steps of
+ * kaolin.render.mesh.prepare_vertices (kaolin/render/mesh/utils.py:128-175) and of
+ * kaolin.ops.mesh.index_vertices_by_faces (kaolin/ops/mesh/mesh.py:25-47), and their
+ * backward.  V-sized work (camera transform, projection) stays with the caller.
+ * faces: int64 (F, 3).  Out-of-range vertex indices read as 0 / are skipped (the
+ * reference's torch.gather raises a device assert there).
+ * ------------------------------------------------------------------------------------- */
+
+/* face_features (B,F,3,C)[b,f,c,:] = vertex_features[b, faces[f,c], :]; vertex_features is
+ * (B,V,C), or (1,V,C) broadcast over the views when shared != 0. */
+DIBR_API int dibr_index_vertices_by_faces(int batch, int num_vertices, int num_faces, int dim,
+                                 int shared, const float* vertex_features, const int64_t* faces,
+                                 float* face_features, void* stream);
+
+/* Backward of the gather: grad_vertex_features[b, faces[f,c], out_col + k] +=
+ * grad_face_features[b,f,c,k].  The destination has rows of out_stride floats (so several
+ * gradients can share one flat (V, out_stride) buffer) and is ACCUMULATED into.  With
+ * shared != 0 the B views are summed first and the destination is (V, out_stride): the
+ * vertex-level message of the multi-GPU all-reduce. */
+DIBR_API int dibr_scatter_face_grads(int batch, int num_vertices, int num_faces, int dim,
+                            int shared, const float* grad_face_features, const int64_t* faces,
+                            float* grad_vertex_features, int out_stride, int out_col,
+                            void* stream);
+
+/* prepare_vertices after the camera: vertices_camera (B,V,3), vertices_image (B,V,2) ->
+ * face_vertices_camera (B,F,3,3), face_vertices_image (B,F,3,2), unit face_normals (B,F,3)
+ * (cross of the edges from corner 0 divided by length + 1e-10, trianglemesh.py:328-335).
+ * Any output may be NULL. */
+DIBR_API int dibr_face_setup_fwd(int batch, int num_vertices, int num_faces,
+                        const float* vertices_camera, const float* vertices_image,
+                        const int64_t* faces, float* face_vertices_camera,
+                        float* face_vertices_image, float* face_normals, void* stream);
+
+/* Its backward: cotangents of the three outputs (any may be NULL) are ACCUMULATED into
+ * grad_vertices_camera (B,V,3) and grad_vertices_image (B,V,2). */
+DIBR_API int dibr_face_setup_bwd(int batch, int num_vertices, int num_faces,
+                        const float* vertices_camera, const int64_t* faces,
+                        const float* grad_face_vertices_camera,
+                        const float* grad_face_vertices_image, const float* grad_face_normals,
+                        float* grad_vertices_camera, float* grad_vertices_image, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,269 @@
+// dibr_mesh.cu -- the steps either side of the DIB-R path that touch (views x faces)-sized
+// data: vertex -> face-corner gathers, unit face normals, and their
+// backward scatter-adds (optionally summed over the views of a shared mesh, which is the
+// message of the multi-GPU all-reduce).  Everything V-sized (camera transform, projection)
+// stays with the caller.
+//
+//   index_vertices_by_faces          kaolin/ops/mesh/mesh.py:25-47
+//   face_normals(unit=True)          kaolin/ops/mesh/trianglemesh.py:313-337
+//   prepare_vertices (gather part)   kaolin/render/mesh/utils.py:171-174
+#include "../../include/dibr_b200.h"
+#include "dibr_common.cuh"
+
+namespace dibr {
+
+int fail(int code, const char* fmt, ...);
+
+namespace {
+
+constexpr int kThreads = 256;
+
+// out[b, f, c, k] = feat[b (or 0 when shared), faces[f, c], k]; one thread per output float
+// (coalesced stores; the index and feature reads hit L1/L2).
+__global__ void __launch_bounds__(kThreads)
+gather_corners_kernel(const float* __restrict__ feat, const int64_t* __restrict__ faces,
+                      float* __restrict__ out, int V, int F, int C, long long feat_view_stride,
+                      long long per_view) {
+  const int b = blockIdx.y;
+  for (long long e = (long long)blockIdx.x * kThreads + threadIdx.x; e < per_view;
+       e += (long long)gridDim.x * kThreads) {
+    const long long fc = e / C;
+    const int k = (int)(e - fc * C);
+    const long long v = __ldg(faces + fc);
+    float val = 0.f;
+    if (v >= 0 && v < V) val = __ldg(feat + b * feat_view_stride + v * C + k);
+    out[b * per_view + e] = val;
+  }
+}
+
+// grad_vertex[b or 0, faces[f, c], col + k] += sum over views (when shared) of
+// grad_face[b, f, c, k]; one thread per (corner, k), one atomic per thread and view group.
+__global__ void __launch_bounds__(kThreads)
+scatter_corners_kernel(const float* __restrict__ grad_face, const int64_t* __restrict__ faces,
+                       float* __restrict__ grad_vertex, int B, int V, int F, int C, int shared,
+                       int out_stride, int out_col, long long per_view) {
+  const int b0 = shared ? 0 : blockIdx.y, b1 = shared ? B : blockIdx.y + 1;
+  for (long long e = (long long)blockIdx.x * kThreads + threadIdx.x; e < per_view;
+       e += (long long)gridDim.x * kThreads) {
+    const long long fc = e / C;
+    const int k = (int)(e - fc * C);
+    const long long v = __ldg(faces + fc);
+    if (v < 0 || v >= V) continue;
+    float s = 0.f;
+    for (int b = b0; b < b1; b++) s += __ldg(grad_face + b * per_view + e);
+    if (s != 0.f)
+      atomicAdd(grad_vertex + ((long long)(shared ? 0 : b0) * V + v) * out_stride + out_col + k, s);
+  }
+}
+
+struct Vec3 { float x, y, z; };
+__device__ __forceinline__ Vec3 sub(Vec3 a, Vec3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+__device__ __forceinline__ Vec3 cross(Vec3 a, Vec3 b) {
+  return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x};
+}
+__device__ __forceinline__ float dot(Vec3 a, Vec3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ Vec3 load3(const float* p) { return {__ldg(p), __ldg(p + 1), __ldg(p + 2)}; }
+
+constexpr int kSetupFaces = 128;   // faces per CTA; the tile is written out coalesced
+
+// One thread per (view, face): gather the three corners from the per-view vertex arrays,
+// unit normal as the reference computes it (cross of the two edges from corner 0, divided by
+// length + 1e-10).  Results go through shared memory so that each of the three outputs
+// is stored as one contiguous, fully coalesced range per CTA.
+__global__ void __launch_bounds__(kSetupFaces)
+face_setup_forward_kernel(const float* __restrict__ vcam, const float* __restrict__ vimg,
+                          const int64_t* __restrict__ faces, float* __restrict__ fvc,
+                          float* __restrict__ fvi, float* __restrict__ fn, int V, int F) {
+  __shared__ float s_cam[kSetupFaces * 9], s_img[kSetupFaces * 6], s_n[kSetupFaces * 3];
+  const int b = blockIdx.y, f0 = blockIdx.x * kSetupFaces, t = threadIdx.x;
+  const int nf = min(kSetupFaces, F - f0);
+  if (t < nf) {
+    Vec3 p[3];
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+      long long v = __ldg(faces + (long long)(f0 + t) * 3 + c);
+      const bool ok = v >= 0 && v < V;
+      v = ok ? v : 0;
+      p[c] = ok ? load3(vcam + ((long long)b * V + v) * 3) : Vec3{0.f, 0.f, 0.f};
+      s_cam[t * 9 + c * 3 + 0] = p[c].x;
+      s_cam[t * 9 + c * 3 + 1] = p[c].y;
+      s_cam[t * 9 + c * 3 + 2] = p[c].z;
+      if (vimg) {
+        s_img[t * 6 + c * 2 + 0] = ok ? __ldg(vimg + ((long long)b * V + v) * 2) : 0.f;
+        s_img[t * 6 + c * 2 + 1] = ok ? __ldg(vimg + ((long long)b * V + v) * 2 + 1) : 0.f;
+      }
+    }
+    const Vec3 n = cross(sub(p[1], p[0]), sub(p[2], p[0]));
+    const float len = sqrtf(dot(n, n)) + 1e-10f;
+    s_n[t * 3 + 0] = n.x / len;
+    s_n[t * 3 + 1] = n.y / len;
+    s_n[t * 3 + 2] = n.z / len;
+  }
+  __syncthreads();
+  const long long base = (long long)b * F + f0;
+  if (fvc) for (int i = t; i < nf * 9; i += kSetupFaces) fvc[base * 9 + i] = s_cam[i];
+  if (fvi) for (int i = t; i < nf * 6; i += kSetupFaces) fvi[base * 6 + i] = s_img[i];
+  if (fn) for (int i = t; i < nf * 3; i += kSetupFaces) fn[base * 3 + i] = s_n[i];
+}
+
+// Backward of the above: cotangents of the three outputs (any may be null) scattered into
+// the per-view vertex gradients.  n = c / (|c| + eps), c = e0 x e1:
+//   dc = g / (L + eps) - c (g . c) / (L (L + eps)^2)   (second term 0 at L = 0, as torch's norm)
+//   de0 = e1 x dc, de1 = dc x e0; corner 1 += de0, corner 2 += de1, corner 0 -= de0 + de1.
+__global__ void __launch_bounds__(kThreads)
+face_setup_backward_kernel(const float* __restrict__ vcam, const int64_t* __restrict__ faces,
+                           const float* __restrict__ g_fvc, const float* __restrict__ g_fvi,
+                           const float* __restrict__ g_fn, float* __restrict__ g_vcam,
+                           float* __restrict__ g_vimg, int V, int F) {
+  const int b = blockIdx.y;
+  const int f = blockIdx.x * kThreads + threadIdx.x;
+  if (f >= F) return;
+  long long v[3];
+  bool ok = true;
+#pragma unroll
+  for (int c = 0; c < 3; c++) {
+    v[c] = __ldg(faces + (long long)f * 3 + c);
+    ok = ok && v[c] >= 0 && v[c] < V;
+  }
+  if (!ok) return;
+  const long long bf = (long long)b * F + f;
+  Vec3 g[3] = {{0, 0, 0}, {0, 0, 0}, {0, 0, 0}};
+  if (g_fvc) {
+#pragma unroll
+    for (int c = 0; c < 3; c++) g[c] = load3(g_fvc + bf * 9 + c * 3);
+  }
+  if (g_fn) {
+    const Vec3 gn = load3(g_fn + bf * 3);
+    if (gn.x != 0.f || gn.y != 0.f || gn.z != 0.f) {
+      Vec3 p[3];
+#pragma unroll
+      for (int c = 0; c < 3; c++) p[c] = load3(vcam + ((long long)b * V + v[c]) * 3);
+      const Vec3 e0 = sub(p[1], p[0]), e1 = sub(p[2], p[0]);
+      const Vec3 c = cross(e0, e1);
+      const float L = sqrtf(dot(c, c)), Le = L + 1e-10f;
+      const float k = L > 0.f ? dot(gn, c) / (L * Le * Le) : 0.f;
+      const Vec3 dc = {gn.x / Le - c.x * k, gn.y / Le - c.y * k, gn.z / Le - c.z * k};
+      const Vec3 de0 = cross(e1, dc), de1 = cross(dc, e0);
+      g[1].x += de0.x; g[1].y += de0.y; g[1].z += de0.z;
+      g[2].x += de1.x; g[2].y += de1.y; g[2].z += de1.z;
+      g[0].x -= de0.x + de1.x; g[0].y -= de0.y + de1.y; g[0].z -= de0.z + de1.z;
+    }
+  }
+  if (g_vcam && (g_fvc || g_fn)) {
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+      float* dst = g_vcam + ((long long)b * V + v[c]) * 3;
+      if (g[c].x != 0.f) atomicAdd(dst, g[c].x);
+      if (g[c].y != 0.f) atomicAdd(dst + 1, g[c].y);
+      if (g[c].z != 0.f) atomicAdd(dst + 2, g[c].z);
+    }
+  }
+  if (g_vimg && g_fvi) {
+#pragma unroll
+    for (int c = 0; c < 3; c++) {
+      const float gx = __ldg(g_fvi + bf * 6 + c * 2), gy = __ldg(g_fvi + bf * 6 + c * 2 + 1);
+      if (gx != 0.f || gy != 0.f)      // 8-byte aligned: (b V + v) * 2 floats
+        atomicAdd(reinterpret_cast<float2*>(g_vimg + ((long long)b * V + v[c]) * 2),
+                  make_float2(gx, gy));
+    }
+  }
+}
+
+inline int grid_for(long long n, int threads) {
+  long long g = (n + threads - 1) / threads;
+  return (int)(g < 1 ? 1 : (g > 148 * 64 ? 148 * 64 : g));
+}
+
+}  // namespace
+}  // namespace dibr
+
+using namespace dibr;
+
+#define MESH_CUDA(expr)                                                              \
+  do {                                                                               \
+    cudaError_t e_ = (expr);                                                         \
+    if (e_ != cudaSuccess)                                                           \
+      return fail(DIBR_E_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e_));      \
+  } while (0)
+
+extern "C" {
+
+DIBR_API int dibr_index_vertices_by_faces(int batch, int num_vertices, int num_faces, int dim,
+                                          int shared, const float* vertex_features,
+                                          const int64_t* faces, float* face_features,
+                                          void* stream) {
+  if (batch < 0 || num_vertices < 0 || num_faces < 0 || dim < 0)
+    return fail(DIBR_E_INVALID, "invalid sizes");
+  if (batch > 65535) return fail(DIBR_E_INVALID, "batch %d > 65535 not supported", batch);
+  const long long per_view = (long long)num_faces * 3 * dim;
+  if (batch == 0 || per_view == 0) return DIBR_OK;
+  if (!vertex_features || !faces || !face_features) return fail(DIBR_E_INVALID, "null pointer");
+  gather_corners_kernel<<<dim3(grid_for(per_view, kThreads), batch), kThreads, 0,
+                          (cudaStream_t)stream>>>(
+      vertex_features, faces, face_features, num_vertices, num_faces, dim,
+      shared ? 0 : (long long)num_vertices * dim, per_view);
+  MESH_CUDA(cudaGetLastError());
+  return DIBR_OK;
+}
+
+DIBR_API int dibr_scatter_face_grads(int batch, int num_vertices, int num_faces, int dim,
+                                     int shared, const float* grad_face_features,
+                                     const int64_t* faces, float* grad_vertex_features,
+                                     int out_stride, int out_col, void* stream) {
+  if (batch < 0 || num_vertices < 0 || num_faces < 0 || dim < 0 || out_col < 0 ||
+      out_stride < out_col + dim)
+    return fail(DIBR_E_INVALID, "invalid sizes");
+  if (batch > 65535) return fail(DIBR_E_INVALID, "batch %d > 65535 not supported", batch);
+  const long long per_view = (long long)num_faces * 3 * dim;
+  if (batch == 0 || per_view == 0) return DIBR_OK;
+  if (!grad_face_features || !faces || !grad_vertex_features)
+    return fail(DIBR_E_INVALID, "null pointer");
+  scatter_corners_kernel<<<dim3(grid_for(per_view, kThreads), shared ? 1 : batch), kThreads, 0,
+                           (cudaStream_t)stream>>>(
+      grad_face_features, faces, grad_vertex_features, batch, num_vertices, num_faces, dim,
+      shared, out_stride, out_col, per_view);
+  MESH_CUDA(cudaGetLastError());
+  return DIBR_OK;
+}
+
+DIBR_API int dibr_face_setup_fwd(int batch, int num_vertices, int num_faces,
+                                 const float* vertices_camera, const float* vertices_image,
+                                 const int64_t* faces, float* face_vertices_camera,
+                                 float* face_vertices_image, float* face_normals, void* stream) {
+  if (batch < 0 || num_vertices < 0 || num_faces < 0) return fail(DIBR_E_INVALID, "invalid sizes");
+  if (batch > 65535) return fail(DIBR_E_INVALID, "batch %d > 65535 not supported", batch);
+  if (batch == 0 || num_faces == 0) return DIBR_OK;
+  if (!vertices_camera || !faces) return fail(DIBR_E_INVALID, "null pointer");
+  if (face_vertices_image && !vertices_image)
+    return fail(DIBR_E_INVALID, "face_vertices_image wanted without vertices_image");
+  face_setup_forward_kernel<<<dim3((num_faces + kSetupFaces - 1) / kSetupFaces, batch),
+                              kSetupFaces, 0, (cudaStream_t)stream>>>(
+      vertices_camera, face_vertices_image ? vertices_image : nullptr, faces,
+      face_vertices_camera, face_vertices_image, face_normals, num_vertices, num_faces);
+  MESH_CUDA(cudaGetLastError());
+  return DIBR_OK;
+}
+
+DIBR_API int dibr_face_setup_bwd(int batch, int num_vertices, int num_faces,
+                                 const float* vertices_camera, const int64_t* faces,
+                                 const float* grad_face_vertices_camera,
+                                 const float* grad_face_vertices_image,
+                                 const float* grad_face_normals, float* grad_vertices_camera,
+                                 float* grad_vertices_image, void* stream) {
+  if (batch < 0 || num_vertices < 0 || num_faces < 0) return fail(DIBR_E_INVALID, "invalid sizes");
+  if (batch > 65535) return fail(DIBR_E_INVALID, "batch %d > 65535 not supported", batch);
+  if (batch == 0 || num_faces == 0) return DIBR_OK;
+  if (!vertices_camera || !faces) return fail(DIBR_E_INVALID, "null pointer");
+  if ((grad_face_vertices_camera || grad_face_normals) && !grad_vertices_camera)
+    return fail(DIBR_E_INVALID, "null grad_vertices_camera");
+  if (grad_face_vertices_image && !grad_vertices_image)
+    return fail(DIBR_E_INVALID, "null grad_vertices_image");
+  face_setup_backward_kernel<<<dim3((num_faces + kThreads - 1) / kThreads, batch), kThreads, 0,
+                               (cudaStream_t)stream>>>(
+      vertices_camera, faces, grad_face_vertices_camera, grad_face_vertices_image,
+      grad_face_normals, grad_vertices_camera, grad_vertices_image, num_vertices, num_faces);
+  MESH_CUDA(cudaGetLastError());
+  return DIBR_OK;
+}
+
+}  // extern "C"

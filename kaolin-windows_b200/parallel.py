@@ -34,3 +34,40 @@ def allreduce_mesh_grads(grads, group=None):
         g.copy_(flat[off:off + n].view_as(g))
         off += n
     return grads
+
+
+def scatter_mesh_grads(faces, num_vertices, *face_grads):
+    """Local face -> vertex scatter-add of this rank's views onto the shared mesh: each
+    (views, faces, 3, C_i) face-level gradient is summed over views and corners into the
+    columns of ONE flat (num_vertices, sum C_i) buffer (csrc/dibr_mesh.cu, one kernel per
+    gradient, no intermediate).  The buffer is the message of `allreduce_mesh_grads`."""
+    import ctypes
+    from . import _lib
+    face_grads = [g.contiguous() for g in face_grads]
+    dev = face_grads[0].device
+    if not face_grads[0].is_cuda:
+        raise RuntimeError("scatter_mesh_grads needs CUDA tensors (there is no CPU path)")
+    faces = faces.contiguous()
+    width = sum(g.shape[-1] for g in face_grads)
+    flat = torch.zeros((num_vertices, width), dtype=torch.float32, device=dev)
+    lib = _lib.lib()
+    col = 0
+    with torch.cuda.device(dev):
+        st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        for g in face_grads:
+            B, F, _, C = g.shape
+            _lib.check(lib.dibr_scatter_face_grads(
+                B, num_vertices, F, C, 1, ctypes.c_void_p(g.data_ptr()),
+                ctypes.c_void_p(faces.data_ptr()), ctypes.c_void_p(flat.data_ptr()),
+                width, col, st), "scatter_mesh_grads")
+            col += C
+    return flat
+
+
+def exchange_mesh_grads(faces, num_vertices, *face_grads, group=None):
+    """scatter_mesh_grads + the path's only collective: one NCCL SUM all-reduce of the
+    flat vertex-level buffer.  Returns the (num_vertices, sum C_i) total over all ranks."""
+    flat = scatter_mesh_grads(faces, num_vertices, *face_grads)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    return flat

@@ -1,4 +1,5 @@
 # mirrors kaolin/render/mesh/__init__.py:1-4 for the hot path only
 from .rasterization import *
 from .dibr import *
-from . import rasterization, dibr
+from .utils import *
+from . import rasterization, dibr, utils

@@ -14,6 +14,11 @@ What it writes (all small, compressed .npz):
 * model_obj.npz -- tests/samples/model.obj (960 triangles), the mesh every hot-path test
   of the reference renders (test_rasterization.py:38-41, test_dibr.py:203-206).
 * pizza_obj.npz -- sample_data/meshes/pizza.obj, BASELINE.json config 1.
+* prepare_vertices.npz -- outputs and gradients of the reference's own (pure torch)
+  ``prepare_vertices`` (kaolin/render/mesh/utils.py:128-175, with
+  camera/legacy.py:22-37,120-139, ops/mesh/mesh.py:25-47, ops/mesh/trianglemesh.py:313-337),
+  functions extracted from /root/reference and run here on CPU on model.obj with 2 random
+  look-at cameras, both camera parametrisations, fixed random cotangents.
 * rasterize_naive.npz -- outputs of the reference's pure-torch oracle
   ``_naive_deftet_sparse_render`` (kaolin/render/mesh/deftet.py:25-267), imported from
   /root/reference and run here on CPU on the fixture geometry of
@@ -125,11 +130,87 @@ def naive_golden():
     np.savez_compressed(os.path.join(HERE, "rasterize_naive.npz"), **out)
 
 
+def load_ref_functions(relpath, names, globs):
+    """exec the named top-level functions of a reference source file (pure torch code whose
+    package cannot be imported without the compiled kaolin._C) in `globs`."""
+    import ast
+    src = open(os.path.join(REF, relpath)).read()
+    tree = ast.parse(src)
+    for node in tree.body:
+        if isinstance(node, ast.FunctionDef) and node.name in names:
+            code = compile(ast.Module(body=[node], type_ignores=[]), relpath, "exec")
+            exec(code, globs)
+    return [globs[n] for n in names]
+
+
+def prepare_vertices_golden():
+    cam = types.SimpleNamespace()
+    g_cam = {"torch": torch, "tan": math.tan}
+    (cam.rotate_translate_points, cam.perspective_camera, gen_rt, gen_proj, gen_tf) = \
+        load_ref_functions("kaolin/render/camera/legacy.py",
+                           ["rotate_translate_points", "perspective_camera",
+                            "generate_rotate_translate_matrices",
+                            "generate_perspective_projection",
+                            "generate_transformation_matrix"], g_cam)
+    mesh = types.SimpleNamespace()
+    (mesh.index_vertices_by_faces,) = load_ref_functions(
+        "kaolin/ops/mesh/mesh.py", ["index_vertices_by_faces"], {"torch": torch})
+    (mesh.face_normals,) = load_ref_functions(
+        "kaolin/ops/mesh/trianglemesh.py", ["face_normals"], {"torch": torch})
+    (prepare_vertices,) = load_ref_functions(
+        "kaolin/render/mesh/utils.py", ["prepare_vertices"],
+        {"torch": torch, "camera": cam, "ops": types.SimpleNamespace(mesh=mesh)})
+    d = np.load(os.path.join(HERE, "model_obj.npz"))
+    g = torch.Generator().manual_seed(11)
+    B = 2
+    verts = torch.from_numpy(d["vertices"]).float()
+    verts = (verts - verts.mean(0)) / verts.abs().max()
+    vertices = verts.unsqueeze(0).repeat(B, 1, 1)
+    vertices = vertices + 0.01 * torch.randn(vertices.shape, generator=g)
+    faces = torch.from_numpy(d["faces"]).long()
+    pos = torch.tensor([[0.3, 0.5, 2.5], [-1.8, 0.2, 1.9]])
+    look = torch.zeros(B, 3)
+    up = torch.tensor([[0., 1., 0.]]).repeat(B, 1)
+    rot, trans = gen_rt(pos, look, up)
+    transform = gen_tf(pos, look, up)
+    proj = gen_proj(math.pi / 4, 1.0)
+    out = dict(vertices=vertices.numpy(), faces=faces.numpy().astype(np.int32),
+               camera_rot=rot.numpy(), camera_trans=trans.numpy(),
+               camera_transform=transform.numpy(), camera_proj=proj.numpy())
+    F = faces.shape[0]
+    cot = [torch.randn((B, F, 3, 3), generator=g), torch.randn((B, F, 3, 2), generator=g),
+           torch.randn((B, F, 3), generator=g)]
+    for i, c in enumerate(cot):
+        out["cot%d" % i] = c.numpy()
+    for mode in ("rot_trans", "transform"):
+        v = vertices.clone().requires_grad_(True)
+        pj = proj.clone().requires_grad_(True)
+        if mode == "rot_trans":
+            r, t = rot.clone().requires_grad_(True), trans.clone().requires_grad_(True)
+            res = prepare_vertices(v, faces, pj, camera_rot=r, camera_trans=t)
+            leaves = {"vertices": v, "camera_proj": pj, "camera_rot": r, "camera_trans": t}
+        else:
+            tf = transform.clone().requires_grad_(True)
+            res = prepare_vertices(v, faces, pj, camera_transform=tf)
+            leaves = {"vertices": v, "camera_proj": pj, "camera_transform": tf}
+        sum((o * c).sum() for o, c in zip(res, cot)).backward()
+        for name, o in zip(("fvc", "fvi", "fn"), res):
+            out["%s_%s" % (mode, name)] = o.detach().numpy()
+        for name, leaf in leaves.items():
+            out["%s_grad_%s" % (mode, name)] = leaf.grad.numpy()
+    np.savez_compressed(os.path.join(HERE, "prepare_vertices.npz"), **out)
+    print("prepare_vertices", {k: v.shape for k, v in out.items() if k.startswith("rot_trans")})
+
+
 if __name__ == "__main__":
+    if sys.argv[1:] == ["prepare_vertices"]:
+        prepare_vertices_golden()
+        sys.exit(0)
     pack_obj(os.path.join(REF, "tests/samples/model.obj"), "model_obj.npz")
     pack_obj(os.path.join(REF, "sample_data/meshes/pizza.obj"), "pizza_obj.npz")
     pack_dibr("simple")
     pack_dibr("sphere")
     naive_golden()
+    prepare_vertices_golden()
     for f in sorted(glob.glob(os.path.join(HERE, "*.npz"))):
         print(os.path.basename(f), os.path.getsize(f) // 1024, "KiB")
