@@ -40,7 +40,7 @@ CFG = "cfg2_70k_8x512"
 SIGMAINV, BOXLEN, KNUM = 7000, 0.02, 30
 KERNELS = ["bin_count", "bin_scan", "bin_fill", "raster_fwd", "softmask_fwd", "raster_bwd",
            "softmask_bwd", "softmask_bwd_dense", "softmask_gather", "softmask_eval",
-           "softmask_grad"]
+           "softmask_grad", "softmask_fold"]
 METRIC = "DIB-R fwd+bwd Mpixels/s (views x H x W)"
 
 
@@ -52,7 +52,7 @@ def algorithmic_bytes(kernel, B, F, P, D):
         "bin_count": fv * (28 + 24), "bin_fill": fv * (28 + 24), "bin_scan": 0,
         "raster_fwd": fv * (40 + 12 * D) + px * (8 + 4 * D),
         "softmask_fwd": fv * 24 + px * 12, "softmask_gather": fv * 24 + px * 12,
-        "softmask_eval": fv * 24 + px * 4,
+        "softmask_eval": fv * 24, "softmask_fold": px * 4,
         "raster_bwd": fv * (48 + 24 * D) + px * (8 + 4 * D),
         "softmask_bwd": fv * 48 + px * 16, "softmask_grad": fv * 48 + px * 16,
     }.get(kernel, 0)

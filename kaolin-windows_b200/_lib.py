@@ -9,7 +9,8 @@ import subprocess
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdibr_b200.so")
+# DIBR_B200_LIB: an alternative build of the same library (kernel tuning experiments)
+LIB_PATH = os.environ.get("DIBR_B200_LIB") or os.path.join(_HERE, "libdibr_b200.so")
 HEADER = os.path.join(os.path.dirname(_HERE), "include", "dibr_b200.h")
 
 DIBR_OK, DIBR_E_INVALID, DIBR_E_WORKSPACE, DIBR_E_CUDA = 0, -1, -2, -3

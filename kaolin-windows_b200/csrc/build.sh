@@ -2,7 +2,7 @@
 # Builds libdibr_b200.so (sm_100a only) next to the Python package.
 set -e
 cd "$(dirname "$0")"
-OUT=../libdibr_b200.so
+OUT=${DIBR_OUT:-../libdibr_b200.so}
 FLAGS="-std=c++17 -O3 -gencode arch=compute_100a,code=sm_100a -lineinfo -Xcompiler -fPIC,-fvisibility=hidden"
 pids=""
 for f in dibr_api dibr_binning dibr_raster dibr_softmask dibr_softgather dibr_mesh; do

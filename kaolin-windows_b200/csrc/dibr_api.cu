@@ -111,7 +111,7 @@ static int64_t pair_bytes(int64_t cap, int K) {
   if (!pair_usable(cap, K)) return 0;
   const int64_t n = cap * kPairSegSlots;
   return align_up(cap * 4, 256) + align_up(cap * 64, 256) + align_up(cap * pair_nseg(K) * 4, 256) +
-         2 * align_up(n * 4, 256) + align_up(n, 256);
+         2 * align_up(n * 4, 256) + align_up(n, 256) + align_up(cap * 12, 256);
 }
 
 static int bind_workspace(const Plan& p, const void* ws, int64_t ws_bytes, int64_t cap_r,
@@ -145,7 +145,9 @@ static int bind_workspace(const Plan& p, const void* ws, int64_t ws_bytes, int64
     pb.act_seg = (int*)q; q += align_up(cap_p * pb.nseg * 4, 256);
     pb.face = (int*)q; q += align_up(n * 4, 256);
     pb.prob = (float*)q; q += align_up(n * 4, 256);
-    pb.type = (unsigned char*)q;
+    pb.type = (unsigned char*)q; q += align_up(n, 256);
+    pb.chunk = (int*)q;
+    pb.nchunk = (unsigned int*)(w.base + p.off_total + 192);
   }
   return DIBR_OK;
 }

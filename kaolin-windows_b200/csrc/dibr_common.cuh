@@ -116,7 +116,12 @@ struct PairBuf {
   int* face;                  // [cap * 256]
   float* prob;                // [cap * 256]
   unsigned char* type;        // [cap * 256]  1-3 edge, 4-6 vertex (reference numbering)
+  // work items of the evaluation / gradient kernels: a region's pairs in chunks of
+  // kPairChunk, so that the silhouette's few thousand heavy regions spread over all SMs
+  unsigned int* nchunk;       // chunks written (header)
+  int* chunk;                 // [3 * cap]    act * 256 + chunk index within the region
 };
+constexpr int kPairChunk = 128;
 
 __device__ __forceinline__ bool pairs_overflowed(const PairBuf& pb) {
   return pb.cursor[0] > (unsigned long long)pb.cap || pb.cursor[1] > (unsigned long long)pb.cap;
@@ -158,7 +163,7 @@ enum { SOFT_FWD = 0, SOFT_FWD_DENSE = 1, SOFT_BWD = 2, SOFT_GATHER = 3 };
 // Optional per-kernel timing (dibr_profile_begin/end in the C ABI): CUDA events recorded on
 // the launching stream right before and after a kernel.  No-ops unless enabled.
 enum { K_BIN_COUNT = 0, K_BIN_SCAN, K_BIN_FILL, K_RASTER_FWD, K_SOFT_FWD, K_RASTER_BWD,
-       K_SOFT_BWD, K_SOFT_BWD_DENSE, K_SOFT_GATHER, K_SOFT_EVAL, K_SOFT_GRAD, K_NUM };
+       K_SOFT_BWD, K_SOFT_BWD_DENSE, K_SOFT_GATHER, K_SOFT_EVAL, K_SOFT_GRAD, K_SOFT_FOLD, K_NUM };
 void prof_begin(int kernel_id, cudaStream_t st);
 void prof_end(cudaStream_t st);
 

@@ -328,7 +328,16 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
     const int aidx = sm.ract[r];
     if (aidx >= 0 && aidx < pb.cap) {
       const int c = sm.cnt[(((r / RX) * 4 + ly) << BLK_LOG2) + (r % RX) * 8 + lx];
-      pb.act_cnt[(long long)aidx * 32 + lane] = (unsigned short)(c == 0xffff ? 0 : c);
+      const int held = c == 0xffff ? 0 : c;
+      pb.act_cnt[(long long)aidx * 32 + lane] = (unsigned short)held;
+      // work items of the evaluation / gradient kernels: the region's pairs in chunks
+      const int total = __reduce_add_sync(DIBR_FULL_MASK, held);
+      const int nch = (total + kPairChunk - 1) / kPairChunk;
+      unsigned base = 0;
+      if (lane == 0) base = atomicAdd(pb.nchunk, (unsigned)nch);
+      base = __shfl_sync(DIBR_FULL_MASK, base, 0);
+      for (int i = lane; i < nch; i += 32)
+        if (base + i < 3u * (unsigned)pb.cap) pb.chunk[base + i] = aidx * 256 + i;
     }
   }
 #ifdef DIBR_TRACE_GATHER

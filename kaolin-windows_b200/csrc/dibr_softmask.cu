@@ -395,11 +395,15 @@ softmask_kernel(const SoftArgs a, const Plan p) {
 
 // ---------------------------------------------------------------------------
 // Pair kernels.  SOFT_GATHER left, for every active region, the first-knum face ids of
-// each pixel in the pair buffer.  Evaluation and gradient then run with ONE WARP PER
-// ACTIVE REGION (lane = pixel, hits walked in order), i.e. spread over the whole GPU
-// however unevenly the silhouette is distributed over the screen blocks.
+// each pixel in the pair buffer, and cut every region's pairs into chunks of kPairChunk.
+// Evaluation and gradient run with ONE WARP PER CHUNK, i.e. spread over the whole GPU
+// however unevenly the silhouette is distributed over the screen (the pairs live in a
+// few thousand regions of very different weight).
 // ---------------------------------------------------------------------------
-constexpr int kPairWarps = 8;
+#ifndef DIBR_PAIR_WARPS
+#define DIBR_PAIR_WARPS 8
+#endif
+constexpr int kPairWarps = DIBR_PAIR_WARPS;
 
 __device__ __forceinline__ void load_scaled_coords(const BinJob& j, int b, int f, float (&X)[6]) {
   const long long gi = (long long)b * j.view_stride + f;
@@ -469,83 +473,179 @@ __device__ __forceinline__ long long pair_locate(const PairBuf& pb, long long ac
   return (long long)sg * kPairSegSlots + (h % kPairSegHits) * 32 + l;
 }
 
-__global__ void __launch_bounds__(kPairWarps * 32)
+// Work item of both kernels: one chunk (kPairChunk pairs, dealt order) of one active region,
+// taken by one warp of a persistent grid.  Returns false when the chunk list is exhausted.
+struct PairWork {
+  long long act;
+  int b, ix, iy, cnt, i_begin, i_end;
+  PairDeal pd;
+};
+
+__device__ __forceinline__ bool pair_work(const PairBuf& pb, const Plan& p, unsigned w, int lane,
+                                          PairWork& k) {
+  const int code = pb.chunk[w];
+  k.act = code >> 8;
+  if (!pair_region(pb, p, k.act, lane, k.b, k.ix, k.iy, k.cnt)) return false;
+  k.pd = pair_deal(pb, k.act, k.cnt, lane);
+  k.i_begin = (code & 255) * kPairChunk;
+  k.i_end = min(k.pd.total, k.i_begin + kPairChunk);
+  return true;
+}
+
+#ifndef DIBR_EVAL_MINB
+#define DIBR_EVAL_MINB 4
+#endif
+__global__ void __launch_bounds__(kPairWarps * 32, DIBR_EVAL_MINB)
 softmask_pairs_eval_kernel(const SoftArgs a, const Plan p) {
+  __shared__ float sX[kPairWarps][6][kPairChunk];
   const PairBuf& pb = a.pairs;
+  if (pairs_overflowed(pb)) return;
   const int lane = lane_id();
-  const long long act = (long long)blockIdx.x * kPairWarps + (threadIdx.x >> 5);
-  int b, ix, iy, cnt;
-  if (!pair_region(pb, p, act, lane, b, ix, iy, cnt)) return;
+  const unsigned nchunk = min(*pb.nchunk, 3u * (unsigned)pb.cap);
   const Grid g = make_grid(a.job.mult, p.W, p.H);
   const float mult = a.job.mult;
   const float four_mm = __fmul_rn(__fmul_rn(mult, 4.f), mult);
-  const int rx0 = ix - (lane & 7), ry0 = iy - (lane >> 3);
-  const PairDeal pd = pair_deal(pb, act, cnt, lane);
-  // ---- evaluate, all lanes busy
-  for (int i0 = 0; i0 < pd.total; i0 += 32) {
-    const bool valid = i0 + lane < pd.total;
-    int l, h;
-    const long long slot = pair_locate(pb, act, pd, valid ? i0 + lane : pd.total - 1, l, h);
-    if (valid) {
-      const float x0 = pix_x(g, rx0 + (l & 7)), y0 = pix_y(g, ry0 + (l >> 3));
+  for (unsigned w = blockIdx.x * kPairWarps + (threadIdx.x >> 5); w < nchunk;
+       w += gridDim.x * kPairWarps) {
+    PairWork k;
+    if (!pair_work(pb, p, w, lane, k)) continue;
+    const int rx0 = k.ix - (lane & 7), ry0 = k.iy - (lane >> 3);
+    // ---- evaluate, all lanes busy.  The kernel is bound by the latency of its dependent
+    // loads (face id -> coordinates), so all of the chunk's loads are issued back to back
+    // and parked in shared memory (each lane reads back only what it wrote) before any
+    // arithmetic; lanes past the end redo the chunk's last pair and skip the stores.
+    constexpr int U = kPairChunk / 32;
+    unsigned slot[U];
+    int lpack = 0;
+    {
+      int f[U];
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        const int i = k.i_begin + 32 * u + lane;
+        int l, h;
+        slot[u] = (unsigned)pair_locate(pb, k.act, k.pd, min(i, k.i_end - 1), l, h);
+        lpack |= l << (8 * u);
+        f[u] = __ldcg(pb.face + slot[u]);
+      }
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        float X[6];
+        load_scaled_coords(a.job, k.b, f[u], X);
+#pragma unroll
+        for (int c = 0; c < 6; c++) sX[threadIdx.x >> 5][c][32 * u + lane] = X[c];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      if (k.i_begin + 32 * u >= k.i_end) break;
+      const int l = (lpack >> (8 * u)) & 31;
       float X[6];
-      load_scaled_coords(a.job, b, pb.face[slot], X);
+#pragma unroll
+      for (int c = 0; c < 6; c++) X[c] = sX[threadIdx.x >> 5][c][32 * u + lane];
+      const float x0 = pix_x(g, rx0 + (l & 7)), y0 = pix_y(g, ry0 + (l >> 3));
       const double inv[3] = {edge_inv(X[0], X[1], X[2], X[3]), edge_inv(X[2], X[3], X[4], X[5]),
                              edge_inv(X[4], X[5], X[0], X[1])};
       float prob;
       int edgeid;
       soft_eval(x0, y0, X, inv, four_mm, a.sigmainv, mult, prob, edgeid);
-      pb.prob[slot] = prob;
-      pb.type[slot] = (unsigned char)(edgeid + 1);
+      if (k.i_begin + 32 * u + lane < k.i_end) {
+        pb.prob[slot[u]] = prob;
+        pb.type[slot[u]] = (unsigned char)(edgeid + 1);
+      }
     }
   }
-  __syncwarp();
-  // ---- fold each pixel's probabilities in face order (:174-182); rows are coalesced
-  const int mx = __reduce_max_sync(DIBR_FULL_MASK, cnt);
-  float ap = 1.0f;
-  for (int h = 0; h < mx; h++) {
-    const int q = h / kPairSegHits;
-    int sg = __shfl_sync(DIBR_FULL_MASK, pd.segreg, q & 31);
-    if (q >= 32) sg = pb.act_seg[act * pb.nseg + q];
-    if (h < cnt) {
-      const float prob = __ldcg(pb.prob + (long long)sg * kPairSegSlots + (h % kPairSegHits) * 32 + lane);
-      ap = __double2float_rn(__dmul_rn((double)ap, __dsub_rn(1.0, (double)prob)));  // :176-177
-    }
-  }
-  if (cnt > 0)
-    a.mask[((long long)b * p.H + iy) * p.W + ix] =
-        __double2float_rn(__dsub_rn(1.0, (double)ap));  // :181-182
 }
 
-__global__ void __launch_bounds__(kPairWarps * 32)
-softmask_pairs_grad_kernel(const SoftArgs a, const Plan p) {
+// Fold of each pixel's probabilities in face order (:174-182), one warp per active region
+// (lane = pixel) once every chunk is evaluated: a chain of dependent FP64 multiplies per
+// pixel that only many resident warps can hide, hence its own small-footprint kernel.
+// Rows are coalesced, eight independent loads at a time (a missing hit multiplies by
+// exactly 1).
+__global__ void __launch_bounds__(256) softmask_pairs_fold_kernel(const SoftArgs a, const Plan p) {
   const PairBuf& pb = a.pairs;
+  if (pairs_overflowed(pb)) return;
   const int lane = lane_id();
-  const long long act = (long long)blockIdx.x * kPairWarps + (threadIdx.x >> 5);
-  int b, ix, iy, cnt;
-  if (!pair_region(pb, p, act, lane, b, ix, iy, cnt)) return;
+  const long long nact = (long long)pb.cursor[1];
+  for (long long act = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); act < nact;
+       act += (long long)gridDim.x * 8) {
+    int b, ix, iy, cnt;
+    pair_region(pb, p, act, lane, b, ix, iy, cnt);
+    const int segreg = lane < pb.nseg ? pb.act_seg[act * pb.nseg + lane] : -1;
+    const int mx = __reduce_max_sync(DIBR_FULL_MASK, cnt);
+    float ap = 1.0f;
+    for (int q = 0; q * kPairSegHits < mx; q++) {
+      int sg = __shfl_sync(DIBR_FULL_MASK, segreg, q & 31);
+      if (q >= 32) sg = pb.act_seg[act * pb.nseg + q];
+      const float* row = pb.prob + (long long)sg * kPairSegSlots + lane;
+      float pr[kPairSegHits];
+#pragma unroll
+      for (int j = 0; j < kPairSegHits; j++)
+        pr[j] = q * kPairSegHits + j < cnt ? __ldcg(row + j * 32) : 0.f;
+#pragma unroll
+      for (int j = 0; j < kPairSegHits; j++)
+        ap = __double2float_rn(__dmul_rn((double)ap, __dsub_rn(1.0, (double)pr[j])));  // :176-177
+    }
+    if (cnt > 0)
+      a.mask[((long long)b * p.H + iy) * p.W + ix] =
+          __double2float_rn(__dsub_rn(1.0, (double)ap));  // :181-182
+  }
+}
+
+#ifndef DIBR_GRAD_MINB
+#define DIBR_GRAD_MINB 4
+#endif
+__global__ void __launch_bounds__(kPairWarps * 32, DIBR_GRAD_MINB)
+softmask_pairs_grad_kernel(const SoftArgs a, const Plan p) {
+  __shared__ float sX[kPairWarps][6][kPairChunk];
+  const PairBuf& pb = a.pairs;
+  if (pairs_overflowed(pb)) return;
+  const int lane = lane_id();
+  const unsigned nchunk = min(*pb.nchunk, 3u * (unsigned)pb.cap);
   const Grid g = make_grid(a.job.mult, p.W, p.H);
   const float mult = a.job.mult;
-  const int rx0 = ix - (lane & 7), ry0 = iy - (lane >> 3);
-  float my_dLdp = 0.f, my_allprob = 0.f;
-  if (cnt > 0) {
-    const long long pix = ((long long)b * p.H + iy) * p.W + ix;
-    my_dLdp = a.grad_mask[pix];
-    my_allprob = a.mask_in[pix];
-  }
-  const PairDeal pd = pair_deal(pb, act, cnt, lane);
-  for (int i0 = 0; i0 < pd.total; i0 += 32) {
-    const bool valid = i0 + lane < pd.total;
-    int l, h;
-    const long long slot = pair_locate(pb, act, pd, valid ? i0 + lane : pd.total - 1, l, h);
-    const float dLdp = __shfl_sync(DIBR_FULL_MASK, my_dLdp, l);
-    const float allprob = __shfl_sync(DIBR_FULL_MASK, my_allprob, l);
-    if (valid) {
-      const float x0 = pix_x(g, rx0 + (l & 7)), y0 = pix_y(g, ry0 + (l >> 3));
-      const int f = pb.face[slot];
+  for (unsigned w = blockIdx.x * kPairWarps + (threadIdx.x >> 5); w < nchunk;
+       w += gridDim.x * kPairWarps) {
+    PairWork k;
+    if (!pair_work(pb, p, w, lane, k)) continue;
+    const int rx0 = k.ix - (lane & 7), ry0 = k.iy - (lane >> 3);
+    float my_dLdp = 0.f, my_allprob = 0.f;
+    if (k.cnt > 0) {
+      const long long pix = ((long long)k.b * p.H + k.iy) * p.W + k.ix;
+      my_dLdp = a.grad_mask[pix];
+      my_allprob = a.mask_in[pix];
+    }
+    constexpr int U = kPairChunk / 32;
+    int f[U], lpack = 0, epack = 0;
+    float pr[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {      // all loads of the chunk first (see the eval kernel)
+      const int i = k.i_begin + 32 * u + lane;
+      int l, h;
+      const long long slot = pair_locate(pb, k.act, k.pd, min(i, k.i_end - 1), l, h);
+      lpack |= l << (8 * u);
+      f[u] = __ldcg(pb.face + slot);
+      epack |= (int)__ldcg(pb.type + slot) << (8 * u);
+      pr[u] = __ldcg(pb.prob + slot);
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
       float X[6];
-      load_scaled_coords(a.job, b, f, X);
-      const int eid = (int)pb.type[slot] - 1;
+      load_scaled_coords(a.job, k.b, f[u], X);
+#pragma unroll
+      for (int c = 0; c < 6; c++) sX[threadIdx.x >> 5][c][32 * u + lane] = X[c];
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      if (k.i_begin + 32 * u >= k.i_end) break;
+      const int l = (lpack >> (8 * u)) & 31;
+      const int eid = ((epack >> (8 * u)) & 255) - 1;
+      const float dLdp = __shfl_sync(DIBR_FULL_MASK, my_dLdp, l);
+      const float allprob = __shfl_sync(DIBR_FULL_MASK, my_allprob, l);
+      if (k.i_begin + 32 * u + lane >= k.i_end) continue;
+      float X[6];
+#pragma unroll
+      for (int c = 0; c < 6; c++) X[c] = sX[threadIdx.x >> 5][c][32 * u + lane];
+      const float x0 = pix_x(g, rx0 + (l & 7)), y0 = pix_y(g, ry0 + (l >> 3));
       double inv_e = 0.0;
       if (eid < 3) {
         const int w2 = (eid + 1) % 3;
@@ -554,11 +654,12 @@ softmask_pairs_grad_kernel(const SoftArgs a, const Plan p) {
       }
       int v1, v2;
       float g1x, g1y, g2x, g2y;
-      soft_grad_core(x0, y0, X, eid, pb.prob[slot], allprob, dLdp, a.sigmainv, mult, inv_e, v1,
-                     g1x, g1y, v2, g2x, g2y);
-      // one 8-byte vector reduction per touched vertex ((x, y) of a vertex are adjacent and
-      // 8-byte aligned in grad_face_vertices_image) instead of up to four scalar ones
-      float2* gp = reinterpret_cast<float2*>(a.grad_img + ((long long)b * a.job.view_stride + f) * 6);
+      soft_grad_core(x0, y0, X, eid, pr[u], allprob, dLdp, a.sigmainv, mult, inv_e, v1, g1x, g1y,
+                     v2, g2x, g2y);
+      // one 8-byte vector reduction per touched vertex ((x, y) of a vertex are adjacent
+      // and 8-byte aligned in grad_face_vertices_image) instead of up to four scalar ones
+      float2* gp = reinterpret_cast<float2*>(
+          a.grad_img + ((long long)k.b * a.job.view_stride + f[u]) * 6);
       if (g1x != 0.f || g1y != 0.f) atomicAdd(gp + v1, make_float2(g1x, g1y));
       if (v2 >= 0 && (g2x != 0.f || g2y != 0.f)) atomicAdd(gp + v2, make_float2(g2x, g2y));
     }
@@ -636,11 +737,22 @@ static cudaError_t launch_soft_mode(const SoftArgs& a, const Plan& p, cudaStream
   return cudaGetLastError();
 }
 
+// persistent grid: every warp strides over the chunk list (its length is only known on the
+// device); enough CTAs to fill the GPU, never more warps than there can be chunks
+static int pair_grid(const PairBuf& pb) {
+  const long long most = (3LL * pb.cap + kPairWarps - 1) / kPairWarps;
+  const long long fill = 148LL * (2048 / (kPairWarps * 32));
+  return (int)(most < fill ? most : fill);
+}
+
 cudaError_t launch_softmask_pairs_eval(const SoftArgs& a, const Plan& p, cudaStream_t st) {
   if (a.pairs.cap <= 0) return cudaSuccess;
   prof_begin(K_SOFT_EVAL, st);
-  softmask_pairs_eval_kernel<<<(a.pairs.cap + kPairWarps - 1) / kPairWarps, kPairWarps * 32, 0,
-                               st>>>(a, p);
+  softmask_pairs_eval_kernel<<<pair_grid(a.pairs), kPairWarps * 32, 0, st>>>(a, p);
+  prof_end(st);
+  prof_begin(K_SOFT_FOLD, st);
+  const long long regions = (a.pairs.cap + 7) / 8;
+  softmask_pairs_fold_kernel<<<(int)(regions < 148 * 8 ? regions : 148 * 8), 256, 0, st>>>(a, p);
   prof_end(st);
   return cudaGetLastError();
 }
@@ -648,8 +760,7 @@ cudaError_t launch_softmask_pairs_eval(const SoftArgs& a, const Plan& p, cudaStr
 cudaError_t launch_softmask_pairs_grad(const SoftArgs& a, const Plan& p, cudaStream_t st) {
   if (a.pairs.cap <= 0) return cudaSuccess;
   prof_begin(K_SOFT_GRAD, st);
-  softmask_pairs_grad_kernel<<<(a.pairs.cap + kPairWarps - 1) / kPairWarps, kPairWarps * 32, 0,
-                               st>>>(a, p);
+  softmask_pairs_grad_kernel<<<pair_grid(a.pairs), kPairWarps * 32, 0, st>>>(a, p);
   prof_end(st);
   return cudaGetLastError();
 }
