@@ -40,7 +40,7 @@ CFG = "cfg2_70k_8x512"
 SIGMAINV, BOXLEN, KNUM = 7000, 0.02, 30
 KERNELS = ["bin_count", "bin_scan", "bin_fill", "raster_fwd", "softmask_fwd", "raster_bwd",
            "softmask_bwd", "softmask_bwd_dense", "softmask_gather", "softmask_eval",
-           "softmask_grad", "softmask_fold"]
+           "softmask_grad", "softmask_fold", "raster_bwd_finish"]
 METRIC = "DIB-R fwd+bwd Mpixels/s (views x H x W)"
 
 
@@ -157,6 +157,10 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--e2e-chunks", type=int, default=4,
+                    help="view chunks the e2e loop overlaps H2D copies and rendering with")
+    ap.add_argument("--no-cuda-graph", action="store_true",
+                    help="eager launches instead of dibr_rasterization(cuda_graph=True)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-gpu", action="store_true")
     args = ap.parse_args()
@@ -197,11 +201,14 @@ def main():
     g2 = torch.rand((B, H, W), device=dev, generator=gen)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
 
-    def step(img_in, feat_in, z_in=z, nz_in=nz, exchange=True, with_loss=False):
+    GRAPH = not args.no_cuda_graph
+
+    def step(img_in, feat_in, z_in=z, nz_in=nz, exchange=True, with_loss=False, graph=GRAPH):
         img_l = img_in.detach().requires_grad_(True)
         feat_l = feat_in.detach().requires_grad_(True)
         out, mask, idx = kal.render.mesh.dibr_rasterization(H, W, z_in, img_l, feat_l, nz_in,
-                                                            SIGMAINV, BOXLEN, KNUM)
+                                                            SIGMAINV, BOXLEN, KNUM,
+                                                            cuda_graph=graph)
         if with_loss:
             loss = (out * g1).sum() + (mask * g2).sum()
             loss.backward()
@@ -251,10 +258,44 @@ def main():
     d_in = [torch.empty_like(t, device=dev) for t in h_in]
     h2d = sum(t.numel() * t.element_size() for t in h_in)
 
+    # The user-level loop a host-fed renderer runs: the batch goes over in view chunks on a
+    # copy stream while the previous chunk renders (fwd + bwd of the chunk's share of the
+    # loss -- the loss is a sum over views, so gradients are those of the whole batch);
+    # one D2H read of the total loss at the end.
+    n_chunks = max(1, min(args.e2e_chunks, B))
+    bounds = [kal.parallel.shard_range(B, c, n_chunks) for c in range(n_chunks)]
+    copy_stream = torch.cuda.Stream(dev)
+    gi_out, gf_out = torch.empty_like(d_in[1]), torch.empty_like(d_in[2])
+
     def e2e_step():
-        for d, h in zip(d_in, h_in):
-            d.copy_(h, non_blocking=True)
-        return float(step(d_in[1], d_in[2], d_in[0], d_in[3], with_loss=True).item())  # D2H of the loss
+        main = torch.cuda.current_stream(dev)
+        copy_stream.wait_stream(main)          # previous step's readers of d_in are done
+        ready = []
+        with torch.cuda.stream(copy_stream):
+            for lo, hi in bounds:
+                for d, h in zip(d_in, h_in):
+                    d[lo:hi].copy_(h[lo:hi], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(copy_stream)
+                ready.append(ev)
+        total = None
+        for (lo, hi), ev in zip(bounds, ready):
+            main.wait_event(ev)
+            img_l = d_in[1][lo:hi].requires_grad_(True)
+            feat_l = d_in[2][lo:hi].requires_grad_(True)
+            out, mask, idx = kal.render.mesh.dibr_rasterization(
+                H, W, d_in[0][lo:hi], img_l, feat_l, d_in[3][lo:hi], SIGMAINV, BOXLEN, KNUM,
+                cuda_graph=GRAPH)
+            # backward of the chunk's loss terms (d loss / d out = G1, d loss / d mask = G2)
+            torch.autograd.backward((out, mask), (g1[lo:hi], g2[lo:hi]))
+            with torch.no_grad():
+                loss = (out * g1[lo:hi]).sum() + (mask * g2[lo:hi]).sum()
+                total = loss if total is None else total + loss
+            gi_out[lo:hi] = img_l.grad
+            gf_out[lo:hi] = feat_l.grad
+        if world > 1:
+            kal.parallel.exchange_mesh_grads(faces, V, gi_out, gf_out)
+        return float(total.item())             # D2H read of the loss
 
     for _ in range(3):
         e2e_step()
@@ -287,7 +328,9 @@ def main():
     lib.dibr_profile_begin()
     for _ in range(args.steps):
         flush.zero_()
-        step(img, feat, exchange=False)   # rank 0 only: no collective in this pass
+        # rank 0 only: no collective in this pass; eager launches so that the library's
+        # per-kernel CUDA events bracket each kernel (a graph replay has none)
+        step(img, feat, exchange=False, graph=False)
     cap = 64 * args.steps
     ids = (ctypes.c_int * cap)()
     ms = (ctypes.c_float * cap)()
@@ -319,7 +362,8 @@ def main():
         for e0, e1 in fe:
             flush.zero_()
             e0.record()
-            kal.render.mesh.dibr_rasterization(H, W, z, img, feat, nz, SIGMAINV, BOXLEN, KNUM)
+            kal.render.mesh.dibr_rasterization(H, W, z, img, feat, nz, SIGMAINV, BOXLEN, KNUM,
+                                               cuda_graph=GRAPH)
             e1.record()
     torch.cuda.synchronize(dev)
     fwd_ms = sum(e0.elapsed_time(e1) for e0, e1 in fe) / args.steps
@@ -335,10 +379,13 @@ def main():
                    "cotangents": "fixed random G1, G2 fed to autograd directly (= backward of "
                                  "(features*G1).sum() + (soft_mask*G2).sum()); e2e computes "
                                  "and reads back that loss",
+                   "launch": "CUDA graphs (dibr_rasterization(cuda_graph=True))" if GRAPH
+                             else "eager",
                    "parallelism": "views sharded, %d per GPU" % B},
         "clocks": sampler.summary(),
         "e2e": {"value": e2e_val, "unit": "Mpixels/s", "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": 8, "ms_per_step": e2e_s * 1e3},
+                "d2h_bytes_per_step": 8, "ms_per_step": e2e_s * 1e3,
+                "view_chunks": n_chunks},
         "gpu_launches": launches_per_step * args.steps,
         "fwd_only_ms_per_step": fwd_ms,
         "roofline": roofline,

@@ -201,6 +201,20 @@ DIBR_API int dibr_render_fwd(int batch, int num_faces, int height, int width, in
                     void* ws, int64_t ws_bytes, int64_t raster_capacity, int64_t soft_capacity,
                     int64_t pair_capacity, int64_t* needed_host, void* stream);
 
+/* Backward of dibr_render_fwd in one call: zero-fills both gradients, then runs the
+ * rasterizer backward (cotangent grad_interpolated_features, may be NULL) and the soft-mask
+ * backward (cotangent grad_soft_mask, may be NULL), which both add into the gradients.
+ * Same workspace and capacities as the forward call.  Replaces the two backward halves of DibrRasterization's autograd graph
+ * (kaolin/render/mesh/rasterization.py:371-388, dibr.py:56-73). */
+DIBR_API int dibr_render_bwd(int batch, int num_faces, int height, int width, int feat_dim,
+                    const float* grad_interpolated_features, const float* grad_soft_mask,
+                    const int64_t* selected_face_idx, const float* face_vertices_image,
+                    const float* face_features, const float* soft_mask, float sigmainv,
+                    float box_margin, int knum, float multiplier, float eps,
+                    float* grad_face_vertices_image, float* grad_face_features, const void* ws,
+                    int64_t ws_bytes, int64_t raster_capacity, int64_t soft_capacity,
+                    int64_t pair_capacity, void* stream);
+
 /* ---------------------------------------------------------------------------------------
  * Next to the path: the (views x faces)-sized steps of
  * kaolin.render.mesh.prepare_vertices (kaolin/render/mesh/utils.py:128-175) and of

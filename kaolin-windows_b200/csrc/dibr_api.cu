@@ -411,6 +411,47 @@ extern "C" int dibr_softmask_bwd(int B, int F, int H, int W, const float* img, i
   return DIBR_OK;
 }
 
+extern "C" int dibr_render_bwd(int B, int F, int H, int W, int D, const float* grad_feat_img,
+                               const float* grad_mask, const int64_t* idx, const float* img,
+                               const float* feat, const float* mask, float sigmainv,
+                               float box_margin, int K, float multiplier, float eps,
+                               float* grad_img, float* grad_feat, const void* ws,
+                               int64_t ws_bytes, int64_t cap_r, int64_t cap_s, int64_t cap_p,
+                               void* stream) {
+  if (B < 0 || F < 0 || H <= 0 || W <= 0 || D < 0 || K < 0)
+    return fail(DIBR_E_INVALID, "invalid sizes");
+  int rc = check_common(multiplier);
+  if (rc) return rc;
+  if (B > 65535) return fail(DIBR_E_INVALID, "batch %d > 65535 not supported", B);
+  if (B == 0 || F == 0) return DIBR_OK;
+  if (!idx || !img || !grad_img || (D > 0 && (!feat || !grad_feat)))
+    return fail(DIBR_E_INVALID, "null pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t nfv = (size_t)B * F * 3;
+  DIBR_CUDA(cudaMemsetAsync(grad_img, 0, nfv * 2 * sizeof(float), st));
+  if (D > 0) DIBR_CUDA(cudaMemsetAsync(grad_feat, 0, nfv * D * sizeof(float), st));
+  const bool do_raster = grad_feat_img && D > 0, do_soft = grad_mask && K > 0;
+  if (do_soft && !mask) return fail(DIBR_E_INVALID, "null soft_mask");
+  RasterBwdArgs ra;
+  if (do_raster) {
+    ra.grad = grad_feat_img; ra.idx = idx; ra.weights = nullptr; ra.img = img; ra.feat = feat;
+    ra.grad_img = grad_img; ra.grad_feat = grad_feat;
+    ra.B = B; ra.F = F; ra.H = H; ra.W = W; ra.D = D;
+    ra.mult = multiplier; ra.eps_f = eps; ra.eps_d = (double)eps;
+    ra.inv_w = 1.0 / (double)W; ra.inv_h = 1.0 / (double)H;
+    DIBR_CUDA(launch_raster_backward_moments(ra, st));
+  }
+  if (do_soft) {
+    // (running this on a second stream beside the moments pass was measured: both kernels
+    // fill the SMs, the overlap gained nothing)
+    rc = dibr_softmask_bwd(B, F, H, W, img, 0, nullptr, idx, sigmainv, box_margin, K, multiplier,
+                           grad_mask, mask, grad_img, ws, ws_bytes, cap_r, cap_s, cap_p, st);
+    if (rc) return rc;
+  }
+  if (do_raster) DIBR_CUDA(launch_raster_backward_finish(ra, st));
+  return DIBR_OK;
+}
+
 extern "C" int dibr_softmask_bwd_dense(int B, int F, int H, int W, int K, const float* grad_mask,
                                        const float* mask, const int64_t* sel, const float* prob,
                                        const int64_t* cidx, const uint8_t* type,

@@ -163,7 +163,7 @@ enum { SOFT_FWD = 0, SOFT_FWD_DENSE = 1, SOFT_BWD = 2, SOFT_GATHER = 3 };
 // Optional per-kernel timing (dibr_profile_begin/end in the C ABI): CUDA events recorded on
 // the launching stream right before and after a kernel.  No-ops unless enabled.
 enum { K_BIN_COUNT = 0, K_BIN_SCAN, K_BIN_FILL, K_RASTER_FWD, K_SOFT_FWD, K_RASTER_BWD,
-       K_SOFT_BWD, K_SOFT_BWD_DENSE, K_SOFT_GATHER, K_SOFT_EVAL, K_SOFT_GRAD, K_SOFT_FOLD, K_NUM };
+       K_SOFT_BWD, K_SOFT_BWD_DENSE, K_SOFT_GATHER, K_SOFT_EVAL, K_SOFT_GRAD, K_SOFT_FOLD, K_RASTER_BWD_FINISH, K_NUM };
 void prof_begin(int kernel_id, cudaStream_t st);
 void prof_end(cudaStream_t st);
 
@@ -171,6 +171,8 @@ cudaError_t launch_binning_count(const BinJobs&, int njobs, const Plan&, cudaStr
 cudaError_t launch_binning_fill(const BinJobs&, int njobs, const Plan&, cudaStream_t);
 cudaError_t launch_raster_forward(const RasterArgs&, const Plan&, cudaStream_t);
 cudaError_t launch_raster_backward(const RasterBwdArgs&, cudaStream_t);
+cudaError_t launch_raster_backward_moments(const RasterBwdArgs&, cudaStream_t);
+cudaError_t launch_raster_backward_finish(const RasterBwdArgs&, cudaStream_t);
 cudaError_t launch_softmask(const SoftArgs&, int mode, const Plan&, cudaStream_t);
 cudaError_t launch_softmask_dense_backward(const SoftDenseBwdArgs&, cudaStream_t);
 cudaError_t launch_softmask_gather(const SoftArgs&, const Plan&, cudaStream_t);

@@ -546,7 +546,9 @@ __global__ void __launch_bounds__(256) raster_backward_finish_kernel(const Raste
   gi[0] = ga; gi[1] = gb; gi[2] = gc;
 }
 
-cudaError_t launch_raster_backward(const RasterBwdArgs& a, cudaStream_t st) {
+// Pass 1 (pixel-parallel moments).  The finish pass adds into grad_img with plain
+// read-modify-writes, so it must not overlap another writer of grad_img.
+cudaError_t launch_raster_backward_moments(const RasterBwdArgs& a, cudaStream_t st) {
   dim3 grid((a.W + 15) / 16, (a.H + 15) / 16, a.B);
   prof_begin(K_RASTER_BWD, st);
   switch (a.D >= 4 ? 4 : a.D) {
@@ -555,10 +557,21 @@ cudaError_t launch_raster_backward(const RasterBwdArgs& a, cudaStream_t st) {
     case 3: raster_backward_kernel<3><<<grid, 256, 0, st>>>(a); break;
     default: raster_backward_kernel<4><<<grid, 256, 0, st>>>(a); break;
   }
+  prof_end(st);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_raster_backward_finish(const RasterBwdArgs& a, cudaStream_t st) {
   const long long nf = (long long)a.B * a.F;
+  prof_begin(K_RASTER_BWD_FINISH, st);
   raster_backward_finish_kernel<<<(unsigned)((nf + 255) / 256), 256, 0, st>>>(a);
   prof_end(st);
   return cudaGetLastError();
+}
+
+cudaError_t launch_raster_backward(const RasterBwdArgs& a, cudaStream_t st) {
+  cudaError_t e = launch_raster_backward_moments(a, st);
+  return e != cudaSuccess ? e : launch_raster_backward_finish(a, st);
 }
 
 }  // namespace dibr

@@ -140,36 +140,36 @@ class DibrRasterizationB200(Function):
         B, F = img.shape[:2]
         H, W = idx.shape[1:]
         D = feat.shape[-1]
-        lib = _lib.lib()
-        grad_img = torch.zeros_like(img)
-        grad_feat = torch.zeros_like(feat)
+        if grad_features is None and grad_soft_mask is None:
+            return (None,) * 11
+        grad_img = torch.empty_like(img)      # zero-filled by the call
+        grad_feat = torch.empty_like(feat)
+        g = None if grad_features is None else _prep(grad_features, "grad_interpolated_features")
+        gm = None if grad_soft_mask is None else _prep(grad_soft_mask, "grad_soft_mask")
         with torch.cuda.device(img.device):
-            st = _stream(img.device)
-            if grad_features is not None:
-                g = _prep(grad_features, "grad_interpolated_features")
-                rc = lib.dibr_rasterize_bwd(B, F, H, W, D, _ptr(g), _ptr(idx), None, _ptr(img),
-                                            _ptr(feat), multiplier, eps, _ptr(grad_img),
-                                            _ptr(grad_feat), st)
-                _lib.check(rc, "dibr_rasterize_bwd")
-            if grad_soft_mask is not None:
-                gm = _prep(grad_soft_mask, "grad_soft_mask")
-                rc = lib.dibr_softmask_bwd(B, F, H, W, _ptr(img), 0, None, _ptr(idx), sigmainv,
-                                           margin, knum, multiplier, _ptr(gm), _ptr(mask),
-                                           _ptr(grad_img), _ptr(ws), ws.numel(), cap_r, cap_s,
-                                           cap_p, st)
-                _lib.check(rc, "dibr_softmask_bwd")
+            # both backward halves (and the zero-fill of the gradients) in one call
+            rc = _lib.lib().dibr_render_bwd(
+                B, F, H, W, D, _ptr(g), _ptr(gm), _ptr(idx), _ptr(img), _ptr(feat), _ptr(mask),
+                sigmainv, margin, knum, multiplier, eps, _ptr(grad_img), _ptr(grad_feat),
+                _ptr(ws), ws.numel(), cap_r, cap_s, cap_p, _stream(img.device))
+        _lib.check(rc, "dibr_render_bwd")
         return (None, None, None, grad_img, grad_feat, None, None, None, None, None, None)
 
 
 def dibr_rasterization(height, width, face_vertices_z, face_vertices_image,
                        face_features, face_normals_z, sigmainv=7000,
                        boxlen=0.02, knum=30, multiplier=None, eps=None,
-                       rast_backend='cuda'):
+                       rast_backend='cuda', cuda_graph=False):
     r"""Fully differentiable DIB-R renderer (see kaolin/render/mesh/dibr.py:123-188).
 
     Renders per-vertex per-face features to feature images, a soft foreground mask and a
     face index map.  Only faces with ``face_normals_z >= 0`` are rasterized; the soft mask
     uses all faces (dibr.py:190-208).
+
+    ``cuda_graph=True`` (not in the reference; see dibr_graph.py) replays the forward and
+    the backward from CUDA graphs once the same problem (shapes, parameters and input
+    addresses) is seen a second time; the results then live in static buffers that the
+    next such call overwrites.
 
     Returns:
         (torch.Tensor or tuple, torch.Tensor, torch.LongTensor): features
@@ -185,9 +185,18 @@ def dibr_rasterization(height, width, face_vertices_z, face_vertices_image,
     _eps = 1e-8 if eps is None else eps
     _face_features = torch.cat(face_features, dim=-1) \
         if isinstance(face_features, (list, tuple)) else face_features
-    image_features, soft_mask, face_idx = DibrRasterizationB200.apply(
-        height, width, face_vertices_z, face_vertices_image, _face_features, face_normals_z,
-        sigmainv, boxlen, knum, _multiplier, _eps)
+    res = None
+    if cuda_graph and rast_backend == 'cuda':
+        from .dibr_graph import graphed_dibr_rasterization
+        res = graphed_dibr_rasterization(
+            height, width, face_vertices_z, face_vertices_image, _face_features, face_normals_z,
+            (float(sigmainv), _margin(boxlen, _multiplier), int(knum), float(_multiplier),
+             float(_eps)))
+    if res is None:
+        res = DibrRasterizationB200.apply(
+            height, width, face_vertices_z, face_vertices_image, _face_features, face_normals_z,
+            sigmainv, boxlen, knum, _multiplier, _eps)
+    image_features, soft_mask, face_idx = res
     if isinstance(face_features, (list, tuple)):
         _image_features = []
         cur_idx = 0

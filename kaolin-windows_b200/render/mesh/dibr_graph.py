@@ -1,0 +1,241 @@
+"""CUDA-graph replay of dibr_rasterization (opt-in: ``dibr_rasterization(..., cuda_graph=True)``).
+
+The eager call costs ~25 CUDA launches and ~0.25 ms of host time per forward + backward,
+as much as the kernels themselves take on a B200, so small batches (and slow hosts) are
+launch-bound.  Here the forward (memsets, binning, rasterizer, soft mask, the 16-byte size
+report) and the backward (gradient memsets, both backward kernels) are each captured once
+per problem -- same shapes, parameters AND input addresses -- into a CUDA graph working on
+buffers owned by a cache entry, and replayed afterwards: one launch each way.
+
+Semantics that differ from the eager call (hence opt-in):
+  * the returned tensors are views of the entry's static buffers: the next graphed call on
+    the same inputs overwrites them (as with torch.cuda.make_graphed_callables);
+  * backward must run before the next forward of the same entry (checked: raises);
+  * gradients come back as views of static buffers (autograd copies them into ``.grad``).
+Correctness is kept as in the eager path: the list-size report of every replay is checked
+before the call returns; an overflow grows the workspace, re-issues the call eagerly and
+re-captures.  A first sighting of a problem runs eagerly; it is captured when seen again.
+"""
+import collections
+import time
+
+import torch
+from torch.autograd import Function
+
+from ... import _lib, _workspace
+from .rasterization import _prep, _ptr, _stream
+
+MAX_ENTRIES = 8          # problems kept (each owns outputs, gradients and a workspace)
+MAX_BWD_GRAPHS = 4       # cotangent address pairs captured per entry
+
+_entries = collections.OrderedDict()
+_sightings = collections.OrderedDict()
+
+
+def clear():
+    """Drop every captured graph and its buffers."""
+    _entries.clear()
+    _sightings.clear()
+
+
+class _Entry:
+    def __init__(self, H, W, z, img, feat, nz, params):
+        self.H, self.W = H, W
+        # input ADDRESSES only: holding the tensors would keep the allocator from handing
+        # the same blocks to the next iteration's inputs, i.e. from ever hitting this entry
+        # again.  The graph is replayed only for a call whose inputs live at these addresses.
+        self.zp, self.imgp, self.featp, self.nzp = (t.data_ptr() for t in (z, img, feat, nz))
+        self.params = params                      # sigmainv, margin, knum, multiplier, eps
+        self.B, self.F = z.shape[:2]
+        self.D = feat.shape[-1]
+        dev = self.dev = z.device
+        B, D = self.B, self.D
+        self.idx = torch.empty((B, H, W), dtype=torch.long, device=dev)
+        self.out = torch.empty((B, H, W, D), dtype=torch.float32, device=dev)
+        self.mask = torch.empty((B, H, W), dtype=torch.float32, device=dev)
+        self.grad_img = torch.empty(tuple(img.shape), dtype=torch.float32, device=dev)
+        self.grad_feat = torch.empty(tuple(feat.shape), dtype=torch.float32, device=dev)
+        self.caps = _workspace.initial_caps(B, self.F, H, W, params[2])
+        if not (_workspace.USE_PAIRS and 0 < params[2] <= _workspace.PAIR_MAX_K):
+            self.caps[2] = 0
+        self.slot = torch.full((4,), -1, dtype=torch.int64).pin_memory()
+        self.ws = None
+        self.graph = None
+        self.bwd_graphs = collections.OrderedDict()
+        self.bwd_seen = set()
+        self.generation = 0
+        self._alloc_ws()
+
+    # ------------------------------------------------------------------ workspace
+    def _alloc_ws(self):
+        lib = _lib.lib()
+        cap_r, cap_s, cap_p = self.caps
+        n = lib.dibr_workspace_bytes_for(self.B, self.F, self.H, self.W, cap_r, cap_s, cap_p,
+                                         self.params[2])
+        if n < 0:
+            _lib.check(int(n), "dibr_workspace_bytes_for")
+        self.ws_bytes = int(n)
+        self.ws = torch.empty(self.ws_bytes, dtype=torch.uint8, device=self.dev)
+        self.graph = None                 # captured graphs point into the old workspace
+        self.bwd_graphs.clear()
+
+    # ------------------------------------------------------------------ forward
+    def _issue_forward(self):
+        sigmainv, margin, knum, multiplier, eps = self.params
+        cap_r, cap_s, cap_p = self.caps
+        rc = _lib.lib().dibr_render_fwd(
+            self.B, self.F, self.H, self.W, self.D, self.zp, self.imgp, self.featp, self.nzp,
+            sigmainv, margin, knum, multiplier, eps,
+            _ptr(self.idx), _ptr(self.out), _ptr(self.mask), self.ws.data_ptr(), self.ws_bytes,
+            cap_r, cap_s, cap_p, self.slot.data_ptr(), _stream(self.dev))
+        _lib.check(rc, "dibr_render_fwd")
+
+    def _poll(self):
+        slot = self.slot
+        t0 = time.perf_counter()
+        while True:
+            nr, ns = int(slot[0]), int(slot[1])
+            if nr >= 0 and ns >= 0:
+                return nr, ns
+            if time.perf_counter() - t0 > 120.0:
+                torch.cuda.synchronize(self.dev)
+                nr, ns = int(slot[0]), int(slot[1])
+                if nr < 0 or ns < 0:
+                    raise RuntimeError("libdibr_b200: list-size report never arrived")
+                return nr, ns
+
+    def forward(self, capture_ok):
+        # pair buffer: what the previous call of this entry wanted (long arrived)
+        want = max(int(self.slot[2]), int(self.slot[3]))
+        if self.caps[2] > 0 and want > self.caps[2]:
+            self.caps[2] = min(int(want * 1.25) + 1024, 1 << 23)
+            self._alloc_ws()
+        with torch.cuda.device(self.dev):
+            for _attempt in range(4):
+                self.slot.fill_(-1)
+                if self.graph is not None:
+                    self.graph.replay()
+                else:
+                    self._issue_forward()
+                nr, ns = self._poll()
+                if nr <= self.caps[0] and ns <= self.caps[1]:
+                    break
+                if nr > self.caps[0]:
+                    self.caps[0] = int(nr * 1.25) + 4096
+                if ns > self.caps[1]:
+                    self.caps[1] = int(ns * 1.25) + 4096
+                self._alloc_ws()
+            else:
+                raise RuntimeError("libdibr_b200: workspace kept overflowing")
+            if self.graph is None and capture_ok:
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, capture_error_mode="thread_local"):
+                    self._issue_forward()
+                self.graph = g
+        self.generation += 1
+
+    # ------------------------------------------------------------------ backward
+    def _issue_backward(self, g_out, g_mask):
+        sigmainv, margin, knum, multiplier, eps = self.params
+        cap_r, cap_s, cap_p = self.caps
+        rc = _lib.lib().dibr_render_bwd(
+            self.B, self.F, self.H, self.W, self.D, _ptr(g_out), _ptr(g_mask), _ptr(self.idx),
+            self.imgp, self.featp, _ptr(self.mask), sigmainv, margin, knum, multiplier, eps,
+            _ptr(self.grad_img), _ptr(self.grad_feat), self.ws.data_ptr(), self.ws_bytes,
+            cap_r, cap_s, cap_p, _stream(self.dev))
+        _lib.check(rc, "dibr_render_bwd")
+
+    def backward(self, g_out, g_mask):
+        key = (None if g_out is None else g_out.data_ptr(),
+               None if g_mask is None else g_mask.data_ptr())
+        with torch.cuda.device(self.dev):
+            g = self.bwd_graphs.get(key)
+            if g is not None:
+                g.replay()
+                return
+            self._issue_backward(g_out, g_mask)
+            if key in self.bwd_seen:      # same cotangent buffers again: worth a graph
+                if len(self.bwd_graphs) >= MAX_BWD_GRAPHS:
+                    self.bwd_graphs.popitem(last=False)
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph, capture_error_mode="thread_local"):
+                    self._issue_backward(g_out, g_mask)
+                self.bwd_graphs[key] = graph     # addresses only, as for the inputs
+            else:
+                self.bwd_seen.add(key)
+                if len(self.bwd_seen) > 64:
+                    self.bwd_seen.clear()
+
+
+def _entry_for(H, W, z, img, feat, nz, params):
+    key = (z.device.index, H, W, tuple(z.shape), feat.shape[-1], params,
+           z.data_ptr(), img.data_ptr(), feat.data_ptr(), nz.data_ptr())
+    e = _entries.get(key)
+    if e is not None:
+        _entries.move_to_end(key)
+        return e, True
+    n = _sightings.get(key, 0) + 1
+    _sightings[key] = n
+    _sightings.move_to_end(key)
+    while len(_sightings) > 64:
+        _sightings.popitem(last=False)
+    if n < 2:
+        return None, False               # first sighting: the caller runs eagerly
+    while len(_entries) >= MAX_ENTRIES:
+        _entries.popitem(last=False)
+    e = _entries[key] = _Entry(H, W, z, img, feat, nz, params)
+    del _sightings[key]
+    return e, True
+
+
+class DibrRasterizationGraphed(Function):
+    """DibrRasterizationB200 (dibr.py) replayed from CUDA graphs; see the module docstring."""
+
+    @staticmethod
+    def forward(ctx, entry, img, feat, face_vertices_image, face_features):
+        entry.forward(capture_ok=True)
+        ctx.entry = entry
+        ctx.save_for_backward(img, feat)   # the backward reads them: keep them alive
+        ctx.generation = entry.generation
+        ctx.set_materialize_grads(False)
+        idx = entry.idx.view_as(entry.idx)
+        ctx.mark_non_differentiable(idx)
+        return entry.out.view_as(entry.out), entry.mask.view_as(entry.mask), idx
+
+    @staticmethod
+    def backward(ctx, grad_features, grad_soft_mask, grad_face_idx):
+        entry = ctx.entry
+        if ctx.generation != entry.generation:
+            raise RuntimeError("dibr_rasterization(cuda_graph=True): backward of a call whose "
+                               "static buffers were overwritten by a later forward")
+        if grad_features is None and grad_soft_mask is None:
+            return None, None, None, None, None
+        g = None if grad_features is None else _prep(grad_features, "grad_interpolated_features")
+        gm = None if grad_soft_mask is None else _prep(grad_soft_mask, "grad_soft_mask")
+        entry.backward(g, gm)
+        return (None, None, None, entry.grad_img.view_as(entry.grad_img),
+                entry.grad_feat.view_as(entry.grad_feat))
+
+
+def graphed_dibr_rasterization(H, W, face_vertices_z, face_vertices_image, face_features,
+                               face_normals_z, params):
+    """Returns (features, soft_mask, face_idx) from a graph entry, or None when this problem
+    is seen for the first time (the caller then takes the eager path)."""
+    z = _prep(face_vertices_z, "face_vertices_z")
+    img = _prep(face_vertices_image, "face_vertices_image")
+    feat = _prep(face_features, "face_features")
+    nz = _prep(face_normals_z, "face_normals_z")
+    B, F = z.shape[:2]
+    D = feat.shape[-1]
+    if (img.shape != (B, F, 3, 2) or z.shape != (B, F, 3) or feat.shape != (B, F, 3, D)
+            or nz.shape != (B, F)):
+        raise RuntimeError("dibr_rasterization: inconsistent input shapes")
+    if any(t.device != z.device for t in (img, feat, nz)):
+        raise RuntimeError("dibr_rasterization: all tensors must be on the same GPU")
+    if B == 0 or F == 0:
+        return None
+    entry, ok = _entry_for(int(H), int(W), z, img, feat, nz, params)
+    if not ok:
+        return None
+    return DibrRasterizationGraphed.apply(entry, img.detach(), feat.detach(),
+                                          face_vertices_image, face_features)

@@ -22,7 +22,7 @@ def _declared_symbols():
 
 def test_library_exports_every_declared_symbol():
     names = _declared_symbols()
-    assert len(names) == 16 and "dibr_render_fwd" in names and "dibr_face_setup_fwd" in names
+    assert len(names) == 17 and "dibr_render_fwd" in names and "dibr_face_setup_fwd" in names
     h = _lib.lib()
     for n in names:
         assert hasattr(h, n), n
@@ -66,7 +66,9 @@ def test_public_signatures_match_reference():
     sig = inspect.signature(m.dibr_rasterization)
     assert list(sig.parameters) == ["height", "width", "face_vertices_z", "face_vertices_image",
                                     "face_features", "face_normals_z", "sigmainv", "boxlen", "knum",
-                                    "multiplier", "eps", "rast_backend"]
+                                    "multiplier", "eps", "rast_backend",
+                                    "cuda_graph"]      # extension, keyword, default off
+    assert sig.parameters["cuda_graph"].default is False
     for n in ("packed_rasterize_forward_cuda", "rasterize_backward_cuda",
               "dibr_soft_mask_forward_cuda", "dibr_soft_mask_backward_cuda"):
         assert callable(getattr(kal._C.render.mesh, n))      # bindings.cpp:76-81

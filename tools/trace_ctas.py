@@ -56,13 +56,12 @@ print("CTAs traced %d; kernel span %.1f us; CTA dur mean %.2f max %.1f sum %.0f 
 print("duration histogram (us):", np.histogram(dur, bins=[0, 2, 5, 10, 20, 40, 80, 160, 1000]))
 order = np.argsort(-dur)[:12]
 for i in order:
-    print("  dur %.1f start %.1f user %d sm %d" % (dur[i], (d[i, 0] - t0) / 1e3, d[i, 3], d[i, 2]),
-          "n", d[i, 3] >> 40, "stage kcyc %.1f" % (((d[i, 3] >> 20) & 0xfffff) / 10), "init kcyc %.1f" % ((d[i, 3] & 0xfffff) / 10))
-busy = np.zeros(148)
-last = np.zeros(148)
-for s, e, smid, _ in d:
-    busy[smid] += (e - s) / 1e3
-    last[smid] = max(last[smid], (e - t0) / 1e3)
-print("per-SM sum of CTA durations: min %.0f mean %.0f max %.0f; last end min %.0f max %.0f" % (
-    busy.min(), busy.mean(), busy.max(), last.min(), last.max()))
-print("corr(user, dur) = %.2f" % np.corrcoef(d[:, 3], dur)[0, 1])
+    print("  dur %.1f us, start %.1f us, sm %d, user value %d" % (dur[i], (d[i, 0] - t0) / 1e3, d[i, 2], d[i, 3]))
+span = (d[:, 1].max() - t0) / 1e3
+busy = np.zeros(int(d[:, 2].max()) + 1)
+np.add.at(busy, d[:, 2], dur)
+print("per-SM summed CTA time / span: mean %.2f max %.2f (resident CTAs per SM on average)" % (
+    (busy / span).mean(), (busy / span).max()))
+# time by which X% of the CTA work is done
+end = np.sort((d[:, 1] - t0) / 1e3)
+print("CTA end-time percentiles 50/90/99/100: ", np.percentile(end, [50, 90, 99, 100]))
