@@ -157,7 +157,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--e2e-chunks", type=int, default=4,
+    ap.add_argument("--e2e-chunks", type=int, default=2,
                     help="view chunks the e2e loop overlaps H2D copies and rendering with")
     ap.add_argument("--no-cuda-graph", action="store_true",
                     help="eager launches instead of dibr_rasterization(cuda_graph=True)")

@@ -32,14 +32,15 @@ for spec in (sys.argv[1:] or DEFAULT):
     g1 = torch.rand((B, H, W, D), device=dev)
     g2 = torch.rand((B, H, W), device=dev)
 
-    def step():
+    def step(graph=True):
         img_l = img.detach().requires_grad_(True)
         feat_l = feat.detach().requires_grad_(True)
-        out, mask, idx = kal.render.mesh.dibr_rasterization(H, W, z, img_l, feat_l, nz)
-        ((out * g1).sum() + (mask * g2).sum()).backward()
+        out, mask, idx = kal.render.mesh.dibr_rasterization(H, W, z, img_l, feat_l, nz,
+                                                            cuda_graph=graph)
+        torch.autograd.backward((out, mask), (g1, g2))
         return idx, mask
 
-    for _ in range(3):
+    for _ in range(4):
         idx, mask = step()
     torch.cuda.synchronize()
     n = 10
@@ -52,7 +53,7 @@ for spec in (sys.argv[1:] or DEFAULT):
     ms = e0.elapsed_time(e1) / n
     lib.dibr_profile_begin()
     for _ in range(3):
-        step()
+        step(False)
     cap = 256
     ids, t = (ctypes.c_int * cap)(), (ctypes.c_float * cap)()
     k = lib.dibr_profile_end(ids, t, cap)
@@ -66,5 +67,7 @@ for spec in (sys.argv[1:] or DEFAULT):
                       "algorithmic_GB_s": round(gb / (ms * 1e-3), 1),
                       "covered": int((idx >= 0).sum()), "soft": int(((mask > 0) & (mask < 1)).sum()),
                       "kernel_ms": per}), flush=True)
+    from kaolin_windows_b200.render.mesh import dibr_graph
+    dibr_graph.clear()
     del inp, z, img, feat, nz, g1, g2
     torch.cuda.empty_cache()
