@@ -65,7 +65,10 @@ __device__ __forceinline__ int block_scan(int v, int* wsum, int lane, int warp, 
 }
 
 template <int BLK_LOG2>
-__global__ void __launch_bounds__(kRasterThreads, 4)
+#ifndef DIBR_RASTER_MINB
+#define DIBR_RASTER_MINB 4
+#endif
+__global__ void __launch_bounds__(kRasterThreads, DIBR_RASTER_MINB)
 raster_forward_kernel(const RasterArgs a, const Plan p) {
   constexpr int BLK = 1 << BLK_LOG2;
   extern __shared__ __align__(16) unsigned char s_raw[];
