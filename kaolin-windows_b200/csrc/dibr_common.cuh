@@ -284,13 +284,18 @@ struct Face2D {
 // does at rasterization.py:337 / dibr.py:32) and builds the box (rasterization.py:342-344,
 // dibr.py:34-39) unless explicit boxes were given.  Returns false for faces that are not
 // part of the list (invalid, outside the packed range, or non-finite coordinates).
+// LISTED: `f` comes out of the job's own face list, which binning only fills with faces
+// that passed these checks -- consumers skip the (dependent) validity loads.
+template <bool LISTED = false>
 __device__ __forceinline__ bool load_face2d(const BinJob& j, int b, int f, Face2D& o) {
-  if (j.first) {
-    if (f < (int)j.first[b] || f >= (int)j.first[b + 1]) return false;
-  }
   const long long gi = (long long)b * j.view_stride + f;
-  if (j.valid && !j.valid[(long long)b * j.view_stride + f]) return false;
-  if (j.normal_z && !(j.normal_z[gi] >= 0.f)) return false;
+  if (!LISTED) {
+    if (j.first) {
+      if (f < (int)j.first[b] || f >= (int)j.first[b + 1]) return false;
+    }
+    if (j.valid && !j.valid[gi]) return false;
+    if (j.normal_z && !(j.normal_z[gi] >= 0.f)) return false;
+  }
   const float2* p = reinterpret_cast<const float2*>(j.img + gi * 6);
   float2 a = __ldg(p), bb = __ldg(p + 1), c = __ldg(p + 2);
   if (!j.prescaled) {
@@ -388,6 +393,10 @@ __device__ __forceinline__ unsigned long long trace_now() {
 #define DIBR_TRACE_BEGIN()
 #define DIBR_TRACE_END(user)
 #endif
+
+__device__ __forceinline__ void prefetch_l1(const void* p) {
+  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+}
 
 // ------------------------------------------------------------------------------ misc
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }

@@ -99,6 +99,12 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
   long long n = a.job.count[row];
   if (start + n > a.job.capacity) n = max(0ll, a.job.capacity - start);  // overflowed call
 
+#ifdef DIBR_TRACE_PHASES
+  long long ph_a = 0, ph_a2 = 0, ph_b = 0, ph_t = clock64();
+#define PH_MARK(acc) do { const long long t_ = clock64(); acc += t_ - ph_t; ph_t = t_; } while (0)
+#else
+#define PH_MARK(acc)
+#endif
   for (long long base = 0; base < n; base += kRasterThreads) {
     // ---- phase A: one face per thread -> exact pixel rectangle inside this block and the
     // coefficients of a CONSERVATIVE per-row span test (see DESIGN.md "Span culling")
@@ -109,8 +115,19 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
       const long long li = base + tid;
       if (li < n) {
         const int f = a.job.list[start + li];
+        // the next chunk's entry now, its face record into L1 while this chunk is worked on
+        if (li + kRasterThreads < n) {
+          const long long gn = (long long)b * a.job.view_stride +
+                               a.job.list[start + li + kRasterThreads];
+          prefetch_l1(a.job.img + gn * 6);
+          prefetch_l1(a.z + gn * 3);
+        }
+        const long long gi = (long long)b * a.job.view_stride + f;
+        // depths requested together with the coordinates (one round trip, not two)
+        const float z_a = __ldg(a.z + gi * 3), z_b = __ldg(a.z + gi * 3 + 1);
+        const float z_c = __ldg(a.z + gi * 3 + 2);
         Face2D fc;
-        if (load_face2d(a.job, b, f, fc) &&
+        if (load_face2d<true>(a.job, b, f, fc) &&
             pixel_range(g, fc.xmin, fc.ymin, fc.xmax, fc.ymax, x_lo, x_hi, y_lo, y_hi)) {
           x_lo = max(x_lo, bx0); x_hi = min(x_hi, bx1);
           y_lo = max(y_lo, by0); y_hi = min(y_hi, by1);
@@ -121,12 +138,11 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
           while (y_lo <= y_hi && pix_y(g, y_lo) >= fc.ymax) y_lo++;
           while (y_lo <= y_hi && pix_y(g, y_hi) < fc.ymin) y_hi--;
           if (x_lo <= x_hi && y_lo <= y_hi) {
-            const long long gi = (long long)b * a.job.view_stride + f;
             sm.x[0][tid] = fc.ax; sm.x[1][tid] = fc.ay; sm.x[2][tid] = fc.bx;
             sm.x[3][tid] = fc.by; sm.x[4][tid] = fc.cx; sm.x[5][tid] = fc.cy;
-            sm.z[0][tid] = __ldg(a.z + gi * 3);
-            sm.z[1][tid] = __ldg(a.z + gi * 3 + 1);
-            sm.z[2][tid] = __ldg(a.z + gi * 3 + 2);
+            sm.z[0][tid] = z_a;
+            sm.z[1][tid] = z_b;
+            sm.z[2][tid] = z_c;
             sm.face[tid] = a.job.first ? f - (int)a.job.first[b] : f;
             // edge functions E_k(x, y) = A_k x + B_k y + C_k in the local frame; inside
             // <=> s E_k >= 0 for all k with s = sign(E_0 + E_1 + E_2) (twice the area)
@@ -171,6 +187,7 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
     sm.rpre[tid] = rbase;
     if (tid == 0) sm.rpre[kRasterThreads] = rtotal;
     __syncthreads();
+    PH_MARK(ph_a);
     if (rtotal == 0) continue;  // uniform
 
     // ---- row batches: the faces whose first row falls into [bi, bi + 1) * kRowBatch
@@ -223,6 +240,7 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
       }
       if (tid == 0) sm.spre[nrows] = ctotal;
       __syncthreads();
+      PH_MARK(ph_a2);
 
       // ---- phase B: the batch's candidates dealt out evenly, a contiguous run per thread;
       // every candidate takes the reference's exact test (the spans hold few misses)
@@ -270,11 +288,27 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
         }
       }
       __syncthreads();  // spans / staged faces free for the next batch / chunk
+      PH_MARK(ph_b);
     }
   }
   __syncthreads();
 
-  // ---- resolve: one pixel per thread-iteration, rows of the block are contiguous in x
+  // ---- resolve: one pixel per thread-iteration, rows of the block are contiguous in x.
+  // Everything a pixel needs hangs off its winner's id: the records of all of a thread's
+  // pixels are requested into L1 first, so that the pass pays one memory round trip and
+  // not one per pixel and tensor.
+  for (int i = tid; i < BLK * BLK; i += kRasterThreads) {
+    const unsigned long long key = zbuf[i];
+    if (key) {
+      const int face = key_face(key);
+      const long long gi = (long long)b * a.job.view_stride +
+                           (a.job.first ? face + (int)a.job.first[b] : face);
+      prefetch_l1(a.job.img + gi * 6);
+      const float* fp = a.feat + gi * 3 * a.D;
+      prefetch_l1(fp);
+      if (a.D > 2) prefetch_l1(fp + 3 * a.D - 1);
+    }
+  }
   int uncovered = 0;
   for (int i = tid; i < BLK * BLK; i += kRasterThreads) {
     const int ix = bx0 + (i & (BLK - 1)), iy = by0 + (i >> BLK_LOG2);
@@ -290,15 +324,29 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
     }
     const int face = key_face(key);
     const int f = a.job.first ? face + (int)a.job.first[b] : face;
+    const float* fp = a.feat + ((long long)b * a.job.view_stride + f) * 3 * a.D;
+    // features before any store (the stores may alias them as far as the compiler knows)
+    float r[3][4];
+    const int dn = a.D < 4 ? a.D : 4;
+#pragma unroll
+    for (int d = 0; d < 4; d++) {
+      if (d < dn) {
+        r[0][d] = __ldg(fp + d); r[1][d] = __ldg(fp + a.D + d); r[2][d] = __ldg(fp + 2 * a.D + d);
+      }
+    }
     Face2D fc;
-    load_face2d(a.job, b, f, fc);
+    load_face2d<true>(a.job, b, f, fc);
     float w0, w1, w2;
     raster_weights(pix_x(g, ix), pix_y(g, iy), fc.ax, fc.ay, fc.bx, fc.by, fc.cx, fc.cy, a.eps_d,
                    w0, w1, w2);
     a.out_idx[pix] = face;
     if (a.out_w) { a.out_w[pix * 3] = w0; a.out_w[pix * 3 + 1] = w1; a.out_w[pix * 3 + 2] = w2; }
-    const float* fp = a.feat + ((long long)b * a.job.view_stride + f) * 3 * a.D;
-    for (int d = 0; d < a.D; d++) {
+#pragma unroll
+    for (int d = 0; d < 4; d++)
+      if (d < dn)
+        a.out_feat[pix * a.D + d] =
+            __fmaf_rn(w2, r[2][d], __fmaf_rn(w0, r[0][d], __fmul_rn(w1, r[1][d])));
+    for (int d = 4; d < a.D; d++) {
       const float r0 = __ldg(fp + d), r1 = __ldg(fp + a.D + d), r2 = __ldg(fp + 2 * a.D + d);
       a.out_feat[pix * a.D + d] = __fmaf_rn(w2, r2, __fmaf_rn(w0, r0, __fmul_rn(w1, r1)));
     }
@@ -311,7 +359,19 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
       a.block_uncovered[(long long)b * p.nkx * p.nky + byi * p.nkx + bxi] =
           sm.uncovered;
   }
+#ifdef DIBR_TRACE_PHASES
+  {
+    __syncthreads();
+    const long long ph_r = clock64() - ph_t;
+    const unsigned long long u = ((unsigned long long)min(ph_a >> 6, 16383ll) << 42) |
+                                 ((unsigned long long)min(ph_a2 >> 6, 16383ll) << 28) |
+                                 ((unsigned long long)min(ph_b >> 6, 16383ll) << 14) |
+                                 (unsigned long long)min(ph_r >> 6, 16383ll);
+    DIBR_TRACE_END(u);
+  }
+#else
   DIBR_TRACE_END(n);
+#endif
 }
 
 cudaError_t launch_raster_forward(const RasterArgs& a, const Plan& p, cudaStream_t st) {

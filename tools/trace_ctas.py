@@ -57,6 +57,15 @@ print("duration histogram (us):", np.histogram(dur, bins=[0, 2, 5, 10, 20, 40, 8
 order = np.argsort(-dur)[:12]
 for i in order:
     print("  dur %.1f us, start %.1f us, sm %d, user value %d" % (dur[i], (d[i, 0] - t0) / 1e3, d[i, 2], d[i, 3]))
+if len(sys.argv) > 2 and sys.argv[2] == "phases":   # -DDIBR_TRACE_PHASES build of raster_forward
+    u = d[:, 3].astype(np.uint64)
+    ph = np.stack([(u >> np.uint64(42)) & np.uint64(16383), (u >> np.uint64(28)) & np.uint64(16383),
+                   (u >> np.uint64(14)) & np.uint64(16383), u & np.uint64(16383)], 1).astype(np.float64) * 64 / 1.965e3
+    tot = dur.sum()
+    print("phase time summed over CTAs (us): A %.0f  A2 %.0f  B %.0f  resolve(+tail) %.0f  | all %.0f" % (
+        ph[:, 0].sum(), ph[:, 1].sum(), ph[:, 2].sum(), ph[:, 3].sum(), tot))
+    print("  shares: A %.2f A2 %.2f B %.2f resolve %.2f other %.2f" % tuple(
+        list(ph.sum(0) / tot) + [1 - ph.sum() / tot]))
 span = (d[:, 1].max() - t0) / 1e3
 busy = np.zeros(int(d[:, 2].max()) + 1)
 np.add.at(busy, d[:, 2], dur)
