@@ -44,6 +44,19 @@ KERNELS = ["bin_count", "bin_scan", "bin_fill", "raster_fwd", "softmask_fwd", "r
 METRIC = "DIB-R fwd+bwd Mpixels/s (views x H x W)"
 
 
+def _teardown(dist):
+    """destroy_process_group with a watchdog: the measurement is printed by now, a stuck
+    communicator teardown must not keep the job alive."""
+    import threading
+    t = threading.Timer(20.0, lambda: os._exit(0))
+    t.daemon = True
+    t.start()
+    try:
+        dist.destroy_process_group()
+    finally:
+        t.cancel()
+
+
 def algorithmic_bytes(kernel, B, F, P, D):
     """API-level compulsory bytes each kernel touches (SURVEY 8(d) per-unit figures split
     by kernel; DESIGN.md "Algorithmic bytes")."""
@@ -182,6 +195,7 @@ def main():
     dev = torch.device("cuda", local_rank)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries the JSON line only
         import datetime
         dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=120))
 
@@ -202,6 +216,8 @@ def main():
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
 
     GRAPH = not args.no_cuda_graph
+    exchanger = kal.parallel.MeshGradExchange(inp["faces"], inp["vertices"].shape[1],
+                                              capture_collective=True) if GRAPH else None
 
     def step(img_in, feat_in, z_in=z, nz_in=nz, exchange=True, with_loss=False, graph=GRAPH):
         img_l = img_in.detach().requires_grad_(True)
@@ -220,7 +236,10 @@ def main():
         if world > 1 and exchange:
             # local face -> vertex scatter-add (one kernel per gradient into one flat
             # (V, 2+D) buffer), then ONE all-reduce of the shared mesh's gradients
-            kal.parallel.exchange_mesh_grads(faces, V, img_l.grad, feat_l.grad)
+            if exchanger is not None:
+                exchanger(img_l.grad, feat_l.grad)
+            else:
+                kal.parallel.exchange_mesh_grads(faces, V, img_l.grad, feat_l.grad)
         return loss
 
     def barrier():
@@ -294,7 +313,10 @@ def main():
             gi_out[lo:hi] = img_l.grad
             gf_out[lo:hi] = feat_l.grad
         if world > 1:
-            kal.parallel.exchange_mesh_grads(faces, V, gi_out, gf_out)
+            if exchanger is not None:
+                exchanger(gi_out, gf_out)
+            else:
+                kal.parallel.exchange_mesh_grads(faces, V, gi_out, gf_out)
         return float(total.item())             # D2H read of the loss
 
     for _ in range(3):
@@ -320,7 +342,10 @@ def main():
 
     if rank != 0:
         if world > 1:
-            dist.destroy_process_group()
+            if exchanger is not None:
+                exchanger.release()
+            torch.cuda.synchronize(dev)
+            _teardown(dist)
         return
 
     # ---- per-kernel times (CUDA events on the launching stream, a separate pass of K steps)
@@ -436,9 +461,12 @@ def main():
             "kind": "port",
             "sample": "rows %d-%d of view 0 (%d px) x %d repeats, extrapolated linearly in pixels"
                       % (lo_r, lo_r + rows, rows * W, reps)}
-    print(json.dumps(line))
+    print(json.dumps(line), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        if exchanger is not None:
+            exchanger.release()
+        torch.cuda.synchronize(dev)
+        _teardown(dist)
 
 
 if __name__ == "__main__":

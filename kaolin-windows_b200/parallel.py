@@ -71,3 +71,85 @@ def exchange_mesh_grads(faces, num_vertices, *face_grads, group=None):
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
     return flat
+
+
+class MeshGradExchange:
+    """exchange_mesh_grads with its local part -- the buffer memset and the scatter kernels
+    -- as ONE CUDA-graph launch, captured once per set of gradient addresses (a training
+    loop hands back the same blocks every iteration) and replayed; the NCCL all-reduce
+    follows as a normal call (kept out of the graph: a process group torn down while
+    graphs still hold its kernels hangs).  The result is a static (num_vertices, sum C_i)
+    buffer, overwritten by the next call.  Addresses seen for the first time run eagerly."""
+
+    MAX_GRAPHS = 4
+
+    def __init__(self, faces, num_vertices, group=None, capture_collective=False):
+        # capture_collective: put the all-reduce into the graph as well (one launch for the
+        # whole exchange).  The owner must then call release() before the process group is
+        # destroyed -- tearing a communicator down under live graphs hangs.
+        self.capture_collective = bool(capture_collective)
+        self.faces = faces.contiguous()
+        self.num_vertices = int(num_vertices)
+        self.group = group
+        self.flat = None
+        self.graphs = {}
+        self.seen = set()
+
+    def _issue(self, face_grads):
+        import ctypes
+        from . import _lib
+        lib = _lib.lib()
+        dev = self.flat.device
+        self.flat.zero_()
+        width = self.flat.shape[1]
+        col = 0
+        st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        for g in face_grads:
+            B, F, _, C = g.shape
+            _lib.check(lib.dibr_scatter_face_grads(
+                B, self.num_vertices, F, C, 1, ctypes.c_void_p(g.data_ptr()),
+                ctypes.c_void_p(self.faces.data_ptr()), ctypes.c_void_p(self.flat.data_ptr()),
+                width, col, st), "scatter_mesh_grads")
+            col += C
+
+    def release(self):
+        """Drop the captured graphs (required before destroy_process_group when the
+        collective is captured)."""
+        self.graphs.clear()
+        self.seen.clear()
+
+    def _reduce(self):
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group)
+        return self.flat
+
+    def __call__(self, *face_grads):
+        face_grads = [g.contiguous() for g in face_grads]
+        dev = face_grads[0].device
+        if not face_grads[0].is_cuda:
+            raise RuntimeError("MeshGradExchange needs CUDA tensors (there is no CPU path)")
+        width = sum(g.shape[-1] for g in face_grads)
+        if self.flat is None or self.flat.shape[1] != width:
+            self.flat = torch.empty((self.num_vertices, width), dtype=torch.float32, device=dev)
+            self.graphs.clear()
+        key = tuple((g.data_ptr(), tuple(g.shape)) for g in face_grads)
+        with torch.cuda.device(dev):
+            graph = self.graphs.get(key)
+            if graph is not None:
+                graph.replay()
+                return self.flat if self.capture_collective else self._reduce()
+            self._issue(face_grads)
+            if key in self.seen and len(self.graphs) < self.MAX_GRAPHS:
+                graph = torch.cuda.CUDAGraph()
+                self._reduce()            # this call's result, eagerly
+                with torch.cuda.graph(graph, capture_error_mode="thread_local"):
+                    self._issue(face_grads)
+                    if self.capture_collective:
+                        self._reduce()
+                self.graphs[key] = graph
+                return self.flat
+            else:
+                self.seen.add(key)
+                if len(self.seen) > 64:
+                    self.seen.clear()
+            return self._reduce()

@@ -142,3 +142,19 @@ def test_prepare_vertices_feeds_the_path():
     assert torch.equal(grads[0][2], grads[1][2])
     for a, b in zip(grads[0][:2], grads[1][:2]):
         assert float((a - b).abs().max()) <= 1e-4 * float(b.abs().max())
+
+
+def test_mesh_grad_exchange_graph_matches_eager():
+    B, V, F, D = 3, 400, 2500, 3
+    g = torch.Generator(device=DEV).manual_seed(9)
+    faces = torch.randint(0, V, (F, 3), device=DEV, generator=g)
+    gi = torch.randn((B, F, 3, 2), device=DEV, generator=g)
+    gf = torch.randn((B, F, 3, D), device=DEV, generator=g)
+    ex = kal.parallel.MeshGradExchange(faces, V)
+    for it in range(4):                      # eager, capture, replay, replay on new data
+        if it == 3:
+            gi.mul_(-0.5)
+        want = kal.parallel.scatter_mesh_grads(faces, V, gi, gf)
+        got = ex(gi, gf)
+        assert torch.allclose(got, want, rtol=1e-5, atol=1e-5)
+    assert len(ex.graphs) == 1
