@@ -257,6 +257,50 @@ DIBR_API int dibr_face_setup_bwd(int batch, int num_vertices, int num_faces,
                         const float* grad_face_vertices_image, const float* grad_face_normals,
                         float* grad_vertices_camera, float* grad_vertices_image, void* stream);
 
+/* ---------------------------------------------------------------------------------------
+ * Double precision: the reference dispatches float and double (rasterization_cuda.cu:30-39,
+ * dibr_soft_mask_cuda.cu:211,382) and tests both.  These are its four raw ops
+ * (bindings.cpp:76-81) for double, in its own layouts: packed faces + boxes + first index
+ * for the rasterizer (rasterization.cpp:49-104), scaled coordinates + enlarged boxes +
+ * dense per-pixel state for the soft mask (dibr_soft_mask.cpp:48-183).  `*32` arguments are
+ * float copies of the same arrays, used only to bin the faces; the double arrays decide.
+ * The soft-mask outputs prob / cidx / type must be pre-filled with 0 / -1 / 0.
+ * ------------------------------------------------------------------------------------- */
+DIBR_API int dibr_packed_rasterize_fwd_f64(
+    int batch, int num_packed_faces, int height, int width, int feat_dim,
+    const double* face_vertices_z, const double* face_vertices_image_scaled,
+    const double* face_bboxes, const double* face_features,
+    const float* face_vertices_image_scaled32, const float* face_bboxes32,
+    const int64_t* first_idx_face_per_mesh, float multiplier, float eps,
+    int64_t* selected_face_idx, double* interpolated_features, double* output_weights, void* ws,
+    int64_t ws_bytes, int64_t raster_capacity, int64_t* needed_host, void* stream);
+
+DIBR_API int dibr_rasterize_bwd_f64(int batch, int num_faces, int height, int width, int feat_dim,
+                           const double* grad_interpolated_features,
+                           const int64_t* selected_face_idx, const double* output_weights,
+                           const double* face_vertices_image, const double* face_features,
+                           float eps, double* grad_face_vertices_image,
+                           double* grad_face_features, void* stream);
+
+DIBR_API int dibr_softmask_fwd_f64(int batch, int num_faces, int height, int width,
+                          const double* face_vertices_image_scaled,
+                          const double* face_large_bboxes,
+                          const float* face_vertices_image_scaled32,
+                          const float* face_large_bboxes32, const int64_t* selected_face_idx,
+                          float sigmainv, int knum, float multiplier, double* soft_mask,
+                          double* close_face_prob, int64_t* close_face_idx,
+                          uint8_t* close_face_dist_type, void* ws, int64_t ws_bytes,
+                          int64_t soft_capacity, int64_t* needed_host, void* stream);
+
+DIBR_API int dibr_softmask_bwd_dense_f64(int batch, int num_faces, int height, int width, int knum,
+                                const double* grad_soft_mask, const double* soft_mask,
+                                const int64_t* selected_face_idx, const double* close_face_prob,
+                                const int64_t* close_face_idx,
+                                const uint8_t* close_face_dist_type,
+                                const double* face_vertices_image_scaled, float sigmainv,
+                                float multiplier, double* grad_face_vertices_image,
+                                void* stream);
+
 #ifdef __cplusplus
 }
 #endif

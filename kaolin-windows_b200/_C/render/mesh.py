@@ -34,10 +34,16 @@ def _check_size(fn, name, t, size):
 
 
 def _check_float(fn, *ts):
+    """AT_DISPATCH_FLOATING_TYPES (rasterization_cuda.cu:30-39): float or double, all alike.
+    Returns True for double."""
+    dt = ts[0].dtype
     for t in ts:
-        if t.dtype != torch.float32:
-            raise RuntimeError("%s not implemented for '%s' (float32 only in kaolin-windows_b200)"
-                               % (fn, t.dtype))
+        if t.dtype not in (torch.float32, torch.float64):
+            raise RuntimeError("%s not implemented for '%s'" % (fn, t.dtype))
+        if t.dtype != dt:
+            raise RuntimeError("%s: expected all floating tensors of dtype %s, got %s"
+                               % (fn, dt, t.dtype))
+    return dt == torch.float64
 
 
 def _aligned(t):
@@ -52,7 +58,7 @@ def packed_rasterize_forward_cuda(height, width, face_vertices_z, face_vertices_
                           ("face_vertices_image", face_vertices_image),
                           ("face_bboxes", face_bboxes), ("face_features", face_features),
                           ("first_idx_face_per_mesh", first_idx_face_per_mesh)])
-    _check_float(fn, face_vertices_z, face_vertices_image, face_bboxes, face_features)
+    f64 = _check_float(fn, face_vertices_z, face_vertices_image, face_bboxes, face_features)
     num_faces = face_vertices_z.shape[0]
     batch_size = first_idx_face_per_mesh.shape[0] - 1
     feat_dim = face_features.shape[2]
@@ -65,11 +71,24 @@ def packed_rasterize_forward_cuda(height, width, face_vertices_z, face_vertices_
     z, img, bbox, feat = (_aligned(t) for t in (face_vertices_z, face_vertices_image,
                                                   face_bboxes, face_features))
     idx = torch.empty((batch_size, height, width), dtype=torch.long, device=dev)
-    weights = torch.empty((batch_size, height, width, 3), dtype=torch.float32, device=dev)
-    interp = torch.empty((batch_size, height, width, feat_dim), dtype=torch.float32, device=dev)
+    weights = torch.empty((batch_size, height, width, 3), dtype=z.dtype, device=dev)
+    interp = torch.empty((batch_size, height, width, feat_dim), dtype=z.dtype, device=dev)
     lib = _lib.lib()
     with torch.cuda.device(dev):
         st = _stream(dev)
+        if f64:
+            img32, bbox32 = img.float(), bbox.float()    # binning only; the doubles decide
+
+            def call64(ws, ws_bytes, cap_r, cap_s, cap_p, needed):
+                return lib.dibr_packed_rasterize_fwd_f64(
+                    batch_size, num_faces, int(height), int(width), feat_dim, _ptr(z), _ptr(img),
+                    _ptr(bbox), _ptr(feat), _ptr(img32), _ptr(bbox32), _ptr(first),
+                    float(multiplier), float(eps), _ptr(idx), _ptr(interp), _ptr(weights),
+                    ws, ws_bytes, cap_r, needed, st)
+
+            _workspace.run("packed64", dev, batch_size, num_faces, int(height), int(width), True,
+                           False, call64)
+            return [interp, idx, weights]
 
         def call(ws, ws_bytes, cap_r, cap_s, cap_p, needed):
             return lib.dibr_rasterize_fwd(
@@ -92,8 +111,8 @@ def rasterize_backward_cuda(grad_interpolated_features, interpolated_features,
                           ("output_weights", output_weights),
                           ("face_vertices_image", face_vertices_image),
                           ("face_features", face_features)])
-    _check_float(fn, grad_interpolated_features, output_weights, face_vertices_image,
-                 face_features)
+    f64 = _check_float(fn, grad_interpolated_features, output_weights, face_vertices_image,
+                       face_features)
     B, H, W, D = grad_interpolated_features.shape
     F = face_vertices_image.shape[1]
     _check_size(fn, "interpolated_features", interpolated_features, (B, H, W, D))
@@ -105,6 +124,13 @@ def rasterize_backward_cuda(grad_interpolated_features, interpolated_features,
     grad_img = torch.zeros_like(img)
     grad_feat = torch.zeros_like(face_features)
     with torch.cuda.device(dev):
+        if f64:
+            rc = _lib.lib().dibr_rasterize_bwd_f64(
+                B, F, H, W, D, _ptr(grad_interpolated_features), _ptr(selected_face_idx),
+                _ptr(output_weights), _ptr(img), _ptr(face_features), float(eps),
+                _ptr(grad_img), _ptr(grad_feat), _stream(dev))
+            _lib.check(rc, fn)
+            return [grad_img, grad_feat]
         rc = _lib.lib().dibr_rasterize_bwd(
             B, F, H, W, D, _ptr(grad_interpolated_features), _ptr(selected_face_idx),
             _ptr(output_weights), _ptr(img), _ptr(face_features), 1.0, float(eps),
@@ -119,7 +145,7 @@ def dibr_soft_mask_forward_cuda(face_vertices_image, face_large_bboxes, selected
     dev = _check_all(fn, [("face_vertices_image", face_vertices_image),
                           ("face_bboxes", face_large_bboxes),
                           ("selected_face_idx", selected_face_idx)])
-    _check_float(fn, face_vertices_image, face_large_bboxes)
+    f64 = _check_float(fn, face_vertices_image, face_large_bboxes)
     B, F = face_vertices_image.shape[:2]
     H, W = selected_face_idx.shape[1:3]
     _check_size(fn, "face_vertices_image", face_vertices_image, (B, F, 3, 2))
@@ -128,12 +154,23 @@ def dibr_soft_mask_forward_cuda(face_vertices_image, face_large_bboxes, selected
     img, bbox = _aligned(face_vertices_image), _aligned(face_large_bboxes)
     knum = int(knum)
     cidx = torch.full((B, H, W, knum), -1, dtype=torch.long, device=dev)
-    prob = torch.zeros((B, H, W, knum), dtype=torch.float32, device=dev)
+    prob = torch.zeros((B, H, W, knum), dtype=img.dtype, device=dev)
     typ = torch.zeros((B, H, W, knum), dtype=torch.uint8, device=dev)
-    mask = torch.empty((B, H, W), dtype=torch.float32, device=dev)
+    mask = torch.zeros((B, H, W), dtype=img.dtype, device=dev)
     lib = _lib.lib()
     with torch.cuda.device(dev):
         st = _stream(dev)
+        if f64:
+            img32, bbox32 = img.float(), bbox.float()    # binning only; the doubles decide
+
+            def call64(ws, ws_bytes, cap_r, cap_s, cap_p, needed):
+                return lib.dibr_softmask_fwd_f64(
+                    B, F, H, W, _ptr(img), _ptr(bbox), _ptr(img32), _ptr(bbox32),
+                    _ptr(selected_face_idx), float(sigmainv), knum, float(multiplier), _ptr(mask),
+                    _ptr(prob), _ptr(cidx), _ptr(typ), ws, ws_bytes, cap_s, needed, st)
+
+            _workspace.run("soft64", dev, B, F, H, W, False, True, call64)
+            return [mask, prob, cidx, typ]
 
         def call(ws, ws_bytes, cap_r, cap_s, cap_p, needed):
             return lib.dibr_softmask_fwd(
@@ -155,7 +192,7 @@ def dibr_soft_mask_backward_cuda(grad_soft_mask, soft_mask, selected_face_idx, c
                           ("close_face_idx", close_face_idx),
                           ("close_face_dist_type", close_face_dist_type),
                           ("face_vertices_image", face_vertices_image)])
-    _check_float(fn, grad_soft_mask, soft_mask, close_face_prob, face_vertices_image)
+    f64 = _check_float(fn, grad_soft_mask, soft_mask, close_face_prob, face_vertices_image)
     B, F = face_vertices_image.shape[:2]
     H, W = selected_face_idx.shape[1:3]
     K = close_face_idx.shape[-1]
@@ -168,7 +205,8 @@ def dibr_soft_mask_backward_cuda(grad_soft_mask, soft_mask, selected_face_idx, c
     _check_size(fn, "face_vertices_image", face_vertices_image, (B, F, 3, 2))
     grad_img = torch.zeros_like(face_vertices_image)
     with torch.cuda.device(dev):
-        rc = _lib.lib().dibr_softmask_bwd_dense(
+        fnc = _lib.lib().dibr_softmask_bwd_dense_f64 if f64 else _lib.lib().dibr_softmask_bwd_dense
+        rc = fnc(
             B, F, H, W, K, _ptr(grad_soft_mask), _ptr(soft_mask), _ptr(selected_face_idx),
             _ptr(close_face_prob), _ptr(close_face_idx), _ptr(close_face_dist_type),
             _ptr(face_vertices_image), float(sigmainv), float(multiplier), _ptr(grad_img),

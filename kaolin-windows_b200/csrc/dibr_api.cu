@@ -506,3 +506,99 @@ extern "C" int dibr_render_fwd(int B, int F, int H, int W, int D, const float* z
   s.pairs = w.pairs;
   return run_soft_forward(s, p, needed_host, st);
 }
+
+// ---------------------------------------------------------------- double precision
+// The reference's four raw ops for scalar_t = double (dibr_f64.cu).  Binning runs on the
+// float copies the caller passes beside the double arrays.
+extern "C" int dibr_packed_rasterize_fwd_f64(
+    int B, int F, int H, int W, int D, const double* z, const double* img, const double* bbox,
+    const double* feat, const float* img32, const float* bbox32, const int64_t* first,
+    float multiplier, float eps, int64_t* out_idx, double* out_feat, double* out_w, void* ws,
+    int64_t ws_bytes, int64_t cap_r, int64_t* needed_host, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  Plan p;
+  int rc = make_plan(B, F, H, W, p);
+  if (rc) return rc;
+  if ((rc = check_common(multiplier))) return rc;
+  if (D < 0) return fail(DIBR_E_INVALID, "feat_dim < 0");
+  if (B == 0) return DIBR_OK;
+  if (!out_idx || (!out_feat && D > 0) || !first) return fail(DIBR_E_INVALID, "null pointer");
+  if (F > 0 && (!z || !img || !bbox || !img32 || !bbox32 || (!feat && D > 0)))
+    return fail(DIBR_E_INVALID, "null input");
+  Workspace w;
+  if ((rc = bind_workspace(p, ws, ws_bytes, cap_r, 0, w))) return rc;
+  BinJobs jobs;
+  jobs.j[0] = face_source(img32, bbox32, nullptr, nullptr, first, 0, multiplier, 0.f, 1);
+  attach(jobs.j[0], p, w, 0);
+  jobs.j[1] = jobs.j[0];
+  const int kinds[1] = {0};
+  if ((rc = run_binning(p, w, jobs, kinds, 1, needed_host, st))) return rc;
+  RasterF64Args a;
+  a.job = jobs.j[0]; a.z = z; a.img = img; a.bbox = bbox; a.feat = feat;
+  a.eps_d = (double)eps; a.D = D; a.out_idx = out_idx; a.out_feat = out_feat; a.out_w = out_w;
+  DIBR_CUDA(launch_raster_forward_f64(a, p, st));
+  return DIBR_OK;
+}
+
+extern "C" int dibr_rasterize_bwd_f64(int B, int F, int H, int W, int D, const double* grad,
+                                      const int64_t* idx, const double* weights,
+                                      const double* img, const double* feat, float eps,
+                                      double* grad_img, double* grad_feat, void* stream) {
+  if (B < 0 || F < 0 || H <= 0 || W <= 0 || D < 0) return fail(DIBR_E_INVALID, "invalid sizes");
+  if (B == 0 || F == 0 || D == 0) return DIBR_OK;
+  if (!grad || !idx || !weights || !img || !feat || !grad_img || !grad_feat)
+    return fail(DIBR_E_INVALID, "null pointer");
+  RasterBwdF64Args a;
+  a.grad = grad; a.idx = idx; a.weights = weights; a.img = img; a.feat = feat;
+  a.grad_img = grad_img; a.grad_feat = grad_feat;
+  a.B = B; a.F = F; a.H = H; a.W = W; a.D = D; a.eps_d = (double)eps;
+  DIBR_CUDA(launch_raster_backward_f64(a, (cudaStream_t)stream));
+  return DIBR_OK;
+}
+
+extern "C" int dibr_softmask_fwd_f64(int B, int F, int H, int W, const double* img,
+                                     const double* bbox, const float* img32, const float* bbox32,
+                                     const int64_t* sel, float sigmainv, int K, float multiplier,
+                                     double* mask, double* prob, int64_t* cidx, uint8_t* type,
+                                     void* ws, int64_t ws_bytes, int64_t cap_s,
+                                     int64_t* needed_host, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  Plan p;
+  BinJobs jobs;
+  int rc = soft_common(B, F, H, W, img32, 1, bbox32, sel, K, multiplier, 0.f, p, jobs.j[0]);
+  if (rc) return rc;
+  if (B == 0) return DIBR_OK;
+  if (!mask || !prob || !cidx || !type) return fail(DIBR_E_INVALID, "null output");
+  if (F > 0 && (!img || !bbox)) return fail(DIBR_E_INVALID, "null input");
+  Workspace w;
+  if ((rc = bind_workspace(p, ws, ws_bytes, 0, cap_s, w))) return rc;
+  attach(jobs.j[0], p, w, 1);
+  jobs.j[1] = jobs.j[0];
+  const int kinds[1] = {1};
+  if ((rc = run_binning(p, w, jobs, kinds, 1, needed_host, st))) return rc;
+  SoftF64Args a;
+  a.job = jobs.j[0]; a.img = img; a.bbox = bbox; a.sel = sel; a.sigmainv = sigmainv; a.K = K;
+  a.mask = mask; a.prob = prob; a.cidx = cidx; a.type = type;
+  DIBR_CUDA(launch_softmask_forward_f64(a, p, st));
+  return DIBR_OK;
+}
+
+extern "C" int dibr_softmask_bwd_dense_f64(int B, int F, int H, int W, int K,
+                                           const double* grad_mask, const double* mask,
+                                           const int64_t* sel, const double* prob,
+                                           const int64_t* cidx, const uint8_t* type,
+                                           const double* img_scaled, float sigmainv,
+                                           float multiplier, double* grad_img, void* stream) {
+  if (B < 0 || F < 0 || H <= 0 || W <= 0 || K < 0) return fail(DIBR_E_INVALID, "invalid sizes");
+  int rc = check_common(multiplier);
+  if (rc) return rc;
+  if (B == 0 || F == 0 || K == 0) return DIBR_OK;
+  if (!grad_mask || !mask || !sel || !prob || !cidx || !type || !img_scaled || !grad_img)
+    return fail(DIBR_E_INVALID, "null pointer");
+  SoftBwdF64Args a;
+  a.grad_mask = grad_mask; a.mask = mask; a.sel = sel; a.prob = prob; a.cidx = cidx;
+  a.type = type; a.img = img_scaled; a.grad_img = grad_img;
+  a.B = B; a.F = F; a.H = H; a.W = W; a.K = K; a.sigmainv = sigmainv; a.mult = multiplier;
+  DIBR_CUDA(launch_softmask_backward_f64(a, (cudaStream_t)stream));
+  return DIBR_OK;
+}

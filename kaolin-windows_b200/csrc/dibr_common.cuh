@@ -155,6 +155,43 @@ struct SoftDenseBwdArgs {
   float sigmainv, mult;
 };
 
+// ---- double-precision instantiation (dibr_f64.cu): the reference's raw-op layouts --
+// packed faces + boxes + first index for the rasterizer, scaled coordinates + enlarged boxes
+// + dense per-pixel state for the soft mask.  `job` is a float binning job over float copies.
+struct RasterF64Args {
+  BinJob job;
+  const double *z, *img, *bbox, *feat;   // (Fv,3) (Fv,3,2) scaled (Fv,4) (Fv,3,D)
+  double eps_d;
+  int D;
+  int64_t* out_idx;
+  double *out_feat, *out_w;
+};
+struct RasterBwdF64Args {
+  const double *grad, *weights, *img, *feat;
+  const int64_t* idx;
+  double *grad_img, *grad_feat;
+  int B, F, H, W, D;
+  double eps_d;
+};
+struct SoftF64Args {
+  BinJob job;
+  const double *img, *bbox;              // (B,F,3,2) scaled, (B,F,4) enlarged
+  const int64_t* sel;
+  float sigmainv;
+  int K;
+  double *mask, *prob;
+  int64_t* cidx;
+  uint8_t* type;
+};
+struct SoftBwdF64Args {
+  const double *grad_mask, *mask, *prob, *img;
+  const int64_t *sel, *cidx;
+  const uint8_t* type;
+  double* grad_img;
+  int B, F, H, W, K;
+  float sigmainv, mult;
+};
+
 // SOFT_FWD / SOFT_BWD: self-contained kernels (gather + evaluate per block); when a pair
 // buffer is attached they only run if it overflowed.  SOFT_GATHER: gather only, fills the
 // pair buffer for launch_softmask_pairs_{eval,grad}.
@@ -178,6 +215,10 @@ cudaError_t launch_softmask_dense_backward(const SoftDenseBwdArgs&, cudaStream_t
 cudaError_t launch_softmask_gather(const SoftArgs&, const Plan&, cudaStream_t);
 cudaError_t launch_softmask_pairs_eval(const SoftArgs&, const Plan&, cudaStream_t);
 cudaError_t launch_softmask_pairs_grad(const SoftArgs&, const Plan&, cudaStream_t);
+cudaError_t launch_raster_forward_f64(const RasterF64Args&, const Plan&, cudaStream_t);
+cudaError_t launch_raster_backward_f64(const RasterBwdF64Args&, cudaStream_t);
+cudaError_t launch_softmask_forward_f64(const SoftF64Args&, const Plan&, cudaStream_t);
+cudaError_t launch_softmask_backward_f64(const SoftBwdF64Args&, cudaStream_t);
 
 // ------------------------------------------------- heaviest-first block scheduling
 // bin_scan buckets the (view, bin) rows by floor(log2(list length)) + 1.  Consumers whose

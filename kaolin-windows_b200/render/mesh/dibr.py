@@ -86,8 +86,10 @@ def dibr_soft_mask(face_vertices_image, selected_face_idx,
     Returns:
         (torch.FloatTensor): the soft mask, of shape (batch_size, height, width).
     """
-    return DibrSoftMaskB200.apply(face_vertices_image, selected_face_idx, sigmainv, boxlen,
-                                  knum, multiplier)
+    fn = DibrSoftMaskB200
+    if face_vertices_image.dtype == torch.float64:     # the reference dispatches both dtypes
+        from ._f64 import DibrSoftMaskF64 as fn
+    return fn.apply(face_vertices_image, selected_face_idx, sigmainv, boxlen, knum, multiplier)
 
 
 class DibrRasterizationB200(Function):
@@ -181,6 +183,14 @@ def dibr_rasterization(height, width, face_vertices_z, face_vertices_image,
         interpolated_features, face_idx = rasterize(
             height, width, face_vertices_z, face_vertices_image, face_features,
             face_normals_z >= 0., multiplier, eps, rast_backend)
+    if face_vertices_z.dtype == torch.float64 and rast_backend == 'cuda':
+        # double: the reference's own composition of its two ops (dibr.py:190-208)
+        interpolated_features, face_idx = rasterize(
+            height, width, face_vertices_z, face_vertices_image, face_features,
+            face_normals_z >= 0., multiplier, eps, rast_backend)
+        soft_mask = dibr_soft_mask(face_vertices_image, face_idx, sigmainv, boxlen, knum,
+                                   1000. if multiplier is None else multiplier)
+        return interpolated_features, soft_mask, face_idx
     _multiplier = 1000. if multiplier is None else multiplier
     _eps = 1e-8 if eps is None else eps
     _face_features = torch.cat(face_features, dim=-1) \

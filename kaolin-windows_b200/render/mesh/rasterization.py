@@ -25,8 +25,8 @@ def _prep(t, name, dtype=torch.float32):
         raise RuntimeError("%s must be a CUDA tensor (there is no CPU path)" % name)
     if t.dtype != dtype:
         if t.dtype == torch.float64 and dtype == torch.float32:
-            raise TypeError("%s: float64 is not implemented yet in kaolin-windows_b200 "
-                            "(float32 only)" % name)
+            raise TypeError("%s is float64 while face_vertices_z is float32: all floating "
+                            "inputs must share one dtype" % name)
         raise TypeError("%s must be %s, got %s" % (name, dtype, t.dtype))
     t = t.contiguous()
     if t.data_ptr() % 16:
@@ -130,7 +130,10 @@ def rasterize(height, width, face_vertices_z, face_vertices_image, face_features
     _face_features = torch.cat(face_features, dim=-1) \
         if isinstance(face_features, (list, tuple)) else face_features
     if backend == 'cuda':
-        image_features, face_idx = RasterizeB200.apply(
+        fn = RasterizeB200
+        if face_vertices_z.dtype == torch.float64:     # the reference dispatches both dtypes
+            from ._f64 import RasterizeF64 as fn
+        image_features, face_idx = fn.apply(
             height, width, face_vertices_z, face_vertices_image, _face_features, valid_faces,
             multiplier, eps)
     elif backend in ('nvdiffrast', 'nvdiffrast_fwd'):
