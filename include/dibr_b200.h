@@ -301,6 +301,30 @@ DIBR_API int dibr_softmask_bwd_dense_f64(int batch, int num_faces, int height, i
                                 float multiplier, double* grad_face_vertices_image,
                                 void* stream);
 
+/* ---------------------------------------------------------------------------------------
+ * After the path: the consumer step of the DIB-R loop.
+ * texture_mapping (kaolin/render/mesh/utils.py:23-76): coordinates (B,N,2) in [0,1], y up,
+ * clamped; textures (B,C,Ht,Wt); out (B,N,C) channels-last; mode 0 = nearest, 1 = bilinear
+ * (grid_sample, align_corners=False, padding 'border').  The backward ACCUMULATES into
+ * grad_texture_maps (may be NULL) and WRITES grad_texture_coordinates (may be NULL).
+ * mask_iou (kaolin/metrics/render.py:18-40): sums (B,2) = per view {sum lhs*rhs,
+ * sum lhs+rhs-lhs*rhs}; loss = 1 - mean(sums[:,0] / (sums[:,1] + 1e-10)) is left to the
+ * caller (B numbers); the backward takes d loss (one float on the device).
+ * ------------------------------------------------------------------------------------- */
+DIBR_API int dibr_texture_mapping_fwd(int batch, int64_t num_points, int channels, int tex_height,
+                             int tex_width, int mode, const float* texture_coordinates,
+                             const float* texture_maps, float* out, void* stream);
+DIBR_API int dibr_texture_mapping_bwd(int batch, int64_t num_points, int channels, int tex_height,
+                             int tex_width, int mode, const float* texture_coordinates,
+                             const float* texture_maps, const float* grad_out,
+                             float* grad_texture_maps, float* grad_texture_coordinates,
+                             void* stream);
+DIBR_API int dibr_mask_iou_sums(int batch, int64_t num_pixels, const float* lhs_mask,
+                       const float* rhs_mask, float* sums, void* stream);
+DIBR_API int dibr_mask_iou_bwd(int batch, int64_t num_pixels, const float* lhs_mask,
+                      const float* rhs_mask, const float* sums, const float* grad_loss,
+                      float* grad_lhs, float* grad_rhs, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -13,7 +13,7 @@ from torch.autograd import Function
 from ... import _lib
 from ...ops.mesh import _check_faces, _check_float, _ptr, _stream
 
-__all__ = ["prepare_vertices"]
+__all__ = ["prepare_vertices", "texture_mapping"]
 
 
 def _rotate_translate_points(points, camera_rot, camera_trans):
@@ -99,3 +99,63 @@ def prepare_vertices(vertices, faces, camera_proj, camera_rot=None, camera_trans
         vertices_camera = padded_vertices @ camera_transform
     vertices_image = _perspective_camera(vertices_camera, camera_proj)
     return _FaceSetup.apply(vertices_camera, vertices_image, faces)
+
+
+class _TextureMapping(Function):
+    @staticmethod
+    def forward(ctx, texture_coordinates, texture_maps, mode):
+        coords = _check_float(texture_coordinates, "texture_coordinates")
+        tex = _check_float(texture_maps, "texture_maps")
+        if tex.device != coords.device:
+            raise RuntimeError("texture_mapping: all tensors must be on the same GPU")
+        B = coords.shape[0]
+        C, Ht, Wt = tex.shape[1:]
+        N = coords.numel() // (2 * B) if B > 0 else 0
+        out = torch.empty((B, N, C), dtype=torch.float32, device=coords.device)
+        with torch.cuda.device(coords.device):
+            _lib.check(_lib.lib().dibr_texture_mapping_fwd(
+                B, N, C, Ht, Wt, mode, _ptr(coords), _ptr(tex), _ptr(out),
+                _stream(coords.device)), "texture_mapping")
+        ctx.save_for_backward(coords, tex)
+        ctx.mode = mode
+        return out
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        coords, tex = ctx.saved_tensors
+        B = coords.shape[0]
+        C, Ht, Wt = tex.shape[1:]
+        N = coords.numel() // (2 * B) if B > 0 else 0
+        g = _check_float(grad_out, "grad")
+        g_tex = torch.zeros_like(tex) if ctx.needs_input_grad[1] else None
+        g_coords = torch.empty_like(coords) if ctx.needs_input_grad[0] else None
+        with torch.cuda.device(coords.device):
+            _lib.check(_lib.lib().dibr_texture_mapping_bwd(
+                B, N, C, Ht, Wt, ctx.mode, _ptr(coords), _ptr(tex), _ptr(g), _ptr(g_tex),
+                _ptr(g_coords), _stream(coords.device)), "texture_mapping backward")
+        return g_coords, g_tex, None
+
+
+def texture_mapping(texture_coordinates, texture_maps, mode='nearest'):
+    r"""Interpolates texture_maps by dense or sparse texture_coordinates
+    (kaolin/render/mesh/utils.py:23-76): one kernel each way instead of
+    clamp / scale / flip / grid_sample / permute / reshape.
+
+    Args:
+        texture_coordinates (torch.FloatTensor): (batch_size, h, w, 2) or
+            (batch_size, num_points, 2), normalized to [0, 1] (clamped), y bottom to top.
+        texture_maps (torch.FloatTensor): (batch_size, num_channels, h', w').
+        mode (str): 'nearest' or 'bilinear' as torch.nn.functional.grid_sample.
+
+    Returns:
+        (torch.FloatTensor): (batch_size, h, w, num_channels) or
+        (batch_size, num_points, num_channels).
+    """
+    if mode not in ('nearest', 'bilinear'):
+        raise ValueError("texture_mapping: mode must be 'nearest' or 'bilinear', got %r" % (mode,))
+    if texture_coordinates.shape[-1] != 2 or texture_maps.dim() != 4 \
+            or texture_maps.shape[0] != texture_coordinates.shape[0]:
+        raise RuntimeError("texture_mapping: expected coordinates (B, ..., 2) and maps (B, C, h', w')")
+    out = _TextureMapping.apply(texture_coordinates, texture_maps, 1 if mode == 'bilinear' else 0)
+    return out.reshape(texture_coordinates.shape[0], *texture_coordinates.shape[1:-1],
+                       texture_maps.shape[1])

@@ -50,3 +50,26 @@ def prepare_vertices(vertices, faces, camera_proj, camera_rot=None, camera_trans
     fvc = index_vertices_by_faces(vertices_camera, faces)
     fvi = index_vertices_by_faces(vertices_image, faces)
     return fvc, fvi, face_normals(fvc, unit=True)
+
+
+def texture_mapping(texture_coordinates, texture_maps, mode='nearest'):
+    """kaolin/render/mesh/utils.py:23-76 (any device, any float dtype)."""
+    batch_size = texture_coordinates.shape[0]
+    num_channels = texture_maps.shape[1]
+    c = texture_coordinates.reshape(batch_size, -1, 1, 2)
+    c = torch.clamp(c, 0., 1.) * 2 - 1                       # [0, 1] -> [-1, 1]
+    c = torch.stack([c[..., 0], -c[..., 1]], dim=-1)         # y axis bottom-to-top -> top-to-bottom
+    out = torch.nn.functional.grid_sample(texture_maps, c, mode=mode, align_corners=False,
+                                          padding_mode='border')
+    out = out.permute(0, 2, 3, 1)
+    return out.reshape(batch_size, *texture_coordinates.shape[1:-1], num_channels)
+
+
+def mask_iou(lhs_mask, rhs_mask):
+    """kaolin/metrics/render.py:18-40."""
+    batch_size = lhs_mask.shape[0]
+    sil_mul = lhs_mask * rhs_mask
+    sil_add = lhs_mask + rhs_mask
+    iou_up = torch.sum(sil_mul.reshape(batch_size, -1), dim=1)
+    iou_down = torch.sum((sil_add - sil_mul).reshape(batch_size, -1), dim=1)
+    return 1.0 - torch.mean(iou_up / (iou_down + 1e-10))
