@@ -18,21 +18,20 @@ namespace {
 
 constexpr int kThreads = 256;
 
-// out[b, f, c, k] = feat[b (or 0 when shared), faces[f, c], k]; one thread per output float
-// (coalesced stores; the index and feature reads hit L1/L2).
+// out[b, f, c, k] = feat[b (or 0 when shared), faces[f, c], k].  One thread per output float
+// (coalesced stores; the index and feature reads hit L1/L2); 32-bit index arithmetic inside
+// a view (the launcher refuses views of 2^31 or more floats).
 __global__ void __launch_bounds__(kThreads)
 gather_corners_kernel(const float* __restrict__ feat, const int64_t* __restrict__ faces,
                       float* __restrict__ out, int V, int F, int C, long long feat_view_stride,
-                      long long per_view) {
+                      unsigned per_view) {
   const int b = blockIdx.y;
-  for (long long e = (long long)blockIdx.x * kThreads + threadIdx.x; e < per_view;
-       e += (long long)gridDim.x * kThreads) {
-    const long long fc = e / C;
-    const int k = (int)(e - fc * C);
+  const float* src = feat + b * feat_view_stride;
+  float* dst = out + (long long)b * per_view;
+  for (unsigned e = blockIdx.x * kThreads + threadIdx.x; e < per_view; e += gridDim.x * kThreads) {
+    const unsigned fc = e / (unsigned)C, k = e - fc * (unsigned)C;
     const long long v = __ldg(faces + fc);
-    float val = 0.f;
-    if (v >= 0 && v < V) val = __ldg(feat + b * feat_view_stride + v * C + k);
-    out[b * per_view + e] = val;
+    dst[e] = (v >= 0 && v < V) ? __ldg(src + v * C + k) : 0.f;
   }
 }
 
@@ -41,16 +40,14 @@ gather_corners_kernel(const float* __restrict__ feat, const int64_t* __restrict_
 __global__ void __launch_bounds__(kThreads)
 scatter_corners_kernel(const float* __restrict__ grad_face, const int64_t* __restrict__ faces,
                        float* __restrict__ grad_vertex, int B, int V, int F, int C, int shared,
-                       int out_stride, int out_col, long long per_view) {
+                       int out_stride, int out_col, unsigned per_view) {
   const int b0 = shared ? 0 : blockIdx.y, b1 = shared ? B : blockIdx.y + 1;
-  for (long long e = (long long)blockIdx.x * kThreads + threadIdx.x; e < per_view;
-       e += (long long)gridDim.x * kThreads) {
-    const long long fc = e / C;
-    const int k = (int)(e - fc * C);
+  for (unsigned e = blockIdx.x * kThreads + threadIdx.x; e < per_view; e += gridDim.x * kThreads) {
+    const unsigned fc = e / (unsigned)C, k = e - fc * (unsigned)C;
     const long long v = __ldg(faces + fc);
     if (v < 0 || v >= V) continue;
     float s = 0.f;
-    for (int b = b0; b < b1; b++) s += __ldg(grad_face + b * per_view + e);
+    for (int b = b0; b < b1; b++) s += __ldg(grad_face + (long long)b * per_view + e);
     if (s != 0.f)
       atomicAdd(grad_vertex + ((long long)(shared ? 0 : b0) * V + v) * out_stride + out_col + k, s);
   }
@@ -197,11 +194,12 @@ DIBR_API int dibr_index_vertices_by_faces(int batch, int num_vertices, int num_f
   if (batch > 65535) return fail(DIBR_E_INVALID, "batch %d > 65535 not supported", batch);
   const long long per_view = (long long)num_faces * 3 * dim;
   if (batch == 0 || per_view == 0) return DIBR_OK;
+  if (per_view >= (1ll << 31)) return fail(DIBR_E_INVALID, "more than 2^31 values per view");
   if (!vertex_features || !faces || !face_features) return fail(DIBR_E_INVALID, "null pointer");
   gather_corners_kernel<<<dim3(grid_for(per_view, kThreads), batch), kThreads, 0,
                           (cudaStream_t)stream>>>(
       vertex_features, faces, face_features, num_vertices, num_faces, dim,
-      shared ? 0 : (long long)num_vertices * dim, per_view);
+      shared ? 0 : (long long)num_vertices * dim, (unsigned)per_view);
   MESH_CUDA(cudaGetLastError());
   return DIBR_OK;
 }
@@ -216,12 +214,13 @@ DIBR_API int dibr_scatter_face_grads(int batch, int num_vertices, int num_faces,
   if (batch > 65535) return fail(DIBR_E_INVALID, "batch %d > 65535 not supported", batch);
   const long long per_view = (long long)num_faces * 3 * dim;
   if (batch == 0 || per_view == 0) return DIBR_OK;
+  if (per_view >= (1ll << 31)) return fail(DIBR_E_INVALID, "more than 2^31 values per view");
   if (!grad_face_features || !faces || !grad_vertex_features)
     return fail(DIBR_E_INVALID, "null pointer");
   scatter_corners_kernel<<<dim3(grid_for(per_view, kThreads), shared ? 1 : batch), kThreads, 0,
                            (cudaStream_t)stream>>>(
       grad_face_features, faces, grad_vertex_features, batch, num_vertices, num_faces, dim,
-      shared, out_stride, out_col, per_view);
+      shared, out_stride, out_col, (unsigned)per_view);
   MESH_CUDA(cudaGetLastError());
   return DIBR_OK;
 }

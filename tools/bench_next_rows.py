@@ -42,26 +42,34 @@ colors = torch.rand((B, V, 3), device=dev)
 res = {}
 
 
-def prep(mod_prepare, mod_gather):
-    v = verts.clone().requires_grad_(True)
-    c = colors.clone().requires_grad_(True)
+F = faces.shape[0]
+cots = [torch.randn(s, device=dev) for s in ((B, F, 3, 3), (B, F, 3, 2), (B, F, 3), (B, F, 3, 3))]
+
+
+def prep(mod_prepare, mod_gather, backward=True):
+    v = verts.detach().requires_grad_(True)
+    c = colors.detach().requires_grad_(True)
     fvc, fvi, fn = mod_prepare(v, faces, proj, camera_rot=rot, camera_trans=trans)
     ff = mod_gather(c, faces)
-    (fvc.sum() + fvi.sum() + fn.sum() + ff.sum()).backward()
+    if backward:
+        torch.autograd.backward((fvc, fvi, fn, ff), cots)
 
 
-res["prepare_vertices+index_vertices_by_faces fwd+bwd (us)"] = {
-    "b200": timed(lambda: prep(kal.render.mesh.prepare_vertices, kal.ops.mesh.index_vertices_by_faces)),
-    "torch": timed(lambda: prep(mo.prepare_vertices, mo.index_vertices_by_faces))}
+for bw in (False, True):
+    res["prepare_vertices+index_vertices_by_faces %s (us)" % ("fwd+bwd" if bw else "fwd")] = {
+        "b200": timed(lambda: prep(kal.render.mesh.prepare_vertices,
+                                   kal.ops.mesh.index_vertices_by_faces, bw)),
+        "torch": timed(lambda: prep(mo.prepare_vertices, mo.index_vertices_by_faces, bw))}
 
 H = W = 512
 uv = torch.rand((B, H, W, 2), device=dev)
 tex = torch.rand((B, 3, 512, 512), device=dev)
+cot_tex = torch.randn((B, H, W, 3), device=dev)
 for mode in ("nearest", "bilinear"):
     def tm(fn):
-        u = uv.clone().requires_grad_(True)
-        t = tex.clone().requires_grad_(True)
-        fn(u, t, mode).sum().backward()
+        u = uv.detach().requires_grad_(True)
+        t = tex.detach().requires_grad_(True)
+        fn(u, t, mode).backward(cot_tex)
     res["texture_mapping %s fwd+bwd (us)" % mode] = {
         "b200": timed(lambda: tm(kal.render.mesh.texture_mapping)),
         "torch": timed(lambda: tm(mo.texture_mapping))}
@@ -71,7 +79,7 @@ m2 = (torch.rand((B, H, W), device=dev) > 0.5).float()
 
 
 def iou(fn):
-    a = m1.clone().requires_grad_(True)
+    a = m1.detach().requires_grad_(True)
     fn(a, m2).backward()
 
 
