@@ -325,6 +325,47 @@ DIBR_API int dibr_mask_iou_bwd(int batch, int64_t num_pixels, const float* lhs_m
                       const float* rhs_mask, const float* sums, const float* grad_loss,
                       float* grad_lhs, float* grad_rhs, void* stream);
 
+/* ---------------------------------------------------------------------------------------
+ * Sibling op: deftet_sparse_render, kaolin/render/mesh/deftet.py:269-417,
+ * replacing kaolin/csrc/render/mesh/deftet.h:25-44 (deftet_sparse_render_forward_cuda /
+ * deftet_sparse_render_backward_cuda, bound at bindings.cpp:82-83).  dtype = DIBR_F32 or
+ * DIBR_F64 selects the element type behind every `void*` tensor.
+ *   pixel_coords, render_ranges (B, P, 2); face_vertices_z (B, F, 3);
+ *   face_vertices_image (B, F, 3, 2); face_features (B, F, 3, D).
+ * dibr_deftet_fwd does the whole forward of DeftetSparseRenderer (deftet.py:273-323): the
+ * first knum faces hit per point in ascending face order, ordered by depth (descending, ties
+ * by face index), face_idx (B, P, K) int64 with -1 = void, weights (B, P, K, 3) with
+ * w2 = valid - (w0 + w1), interpolated_features (B, P, K, D).  Every output element is written.
+ * dibr_deftet_fwd_raw is the reference's raw op (deftet.cpp:47-107): unsorted slots in
+ * ascending face order, fills -1 / -inf / 0 / 0; face_bboxes (B, F, 4) as passed by the
+ * caller (may be NULL = computed from the vertices).
+ * dibr_deftet_bwd zero-fills and accumulates grad_face_vertices_image (B, F, 3, 2) and
+ * grad_face_features (B, F, 3, D) (deftet.cpp:109-165).
+ * The workspace (dibr_deftet_workspace_bytes, 256-byte aligned) holds the per-view cell grid
+ * and face lists; its size is a bound, there is no capacity protocol and no host sync.
+ * knum is limited by shared memory: knum * (4 + 3 * sizeof(T)) + 4 * pow2ceil(knum) <= 200 KiB.
+ * ------------------------------------------------------------------------------------- */
+#define DIBR_F32 0
+#define DIBR_F64 1
+DIBR_API int64_t dibr_deftet_workspace_bytes(int batch, int num_faces, int num_points);
+DIBR_API int dibr_deftet_fwd(int dtype, int batch, int num_faces, int num_points, int knum,
+                    int feat_dim, const void* face_vertices_z, const void* face_vertices_image,
+                    const void* face_features, const void* pixel_coords,
+                    const void* render_ranges, float eps, int64_t* face_idx,
+                    void* interpolated_features, void* weights, void* ws, int64_t ws_bytes,
+                    void* stream);
+DIBR_API int dibr_deftet_fwd_raw(int dtype, int batch, int num_faces, int num_points, int knum,
+                        const void* face_vertices_z, const void* face_vertices_image,
+                        const void* face_bboxes, const void* pixel_coords,
+                        const void* render_ranges, float eps, int64_t* face_idx,
+                        void* pixel_depths, void* w0, void* w1, void* ws, int64_t ws_bytes,
+                        void* stream);
+DIBR_API int dibr_deftet_bwd(int dtype, int batch, int num_faces, int num_points, int knum,
+                    int feat_dim, const void* grad_interpolated_features,
+                    const int64_t* face_idx, const void* weights,
+                    const void* face_vertices_image, const void* face_features, float eps,
+                    void* grad_face_vertices_image, void* grad_face_features, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

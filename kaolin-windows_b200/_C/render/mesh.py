@@ -8,7 +8,8 @@ from ... import _lib, _workspace
 from ...render.mesh.rasterization import _ptr, _stream
 
 __all__ = ["packed_rasterize_forward_cuda", "rasterize_backward_cuda",
-           "dibr_soft_mask_forward_cuda", "dibr_soft_mask_backward_cuda"]
+           "dibr_soft_mask_forward_cuda", "dibr_soft_mask_backward_cuda",
+           "deftet_sparse_render_forward_cuda", "deftet_sparse_render_backward_cuda"]
 
 
 def _check_all(fn, named, dtype=None):
@@ -213,3 +214,67 @@ def dibr_soft_mask_backward_cuda(grad_soft_mask, soft_mask, selected_face_idx, c
             _stream(dev))
     _lib.check(rc, fn)
     return grad_img
+
+
+def deftet_sparse_render_forward_cuda(face_vertices_z, face_vertices_image, face_bboxes,
+                                      pixel_coords, pixel_depth_ranges, knum, eps):
+    """deftet.cpp:47-107: the raw op -- unsorted slots in ascending face order."""
+    fn = "deftet_sparse_render_forward_cuda"
+    dev = _check_all(fn, [("face_vertices_z", face_vertices_z),
+                          ("face_vertices_image", face_vertices_image),
+                          ("face_bboxes", face_bboxes), ("pixel_coords", pixel_coords),
+                          ("pixel_depth_ranges", pixel_depth_ranges)])
+    f64 = _check_float(fn, face_vertices_z, face_vertices_image, face_bboxes, pixel_coords,
+                       pixel_depth_ranges)
+    B, F = face_vertices_z.shape[:2]
+    P = pixel_coords.shape[1]
+    knum = int(knum)
+    _check_size(fn, "face_vertices_z", face_vertices_z, (B, F, 3))
+    _check_size(fn, "face_vertices_image", face_vertices_image, (B, F, 3, 2))
+    _check_size(fn, "face_bboxes", face_bboxes, (B, F, 4))
+    _check_size(fn, "pixel_coords", pixel_coords, (B, P, 2))
+    _check_size(fn, "pixel_depth_ranges", pixel_depth_ranges, (B, P, 2))
+    z, img, bbox, pix, rng = (_aligned(t) for t in (face_vertices_z, face_vertices_image,
+                                                     face_bboxes, pixel_coords,
+                                                     pixel_depth_ranges))
+    idx = torch.empty((B, P, knum), dtype=torch.long, device=dev)
+    depth = torch.empty((B, P, knum), dtype=z.dtype, device=dev)
+    w0 = torch.empty((B, P, knum), dtype=z.dtype, device=dev)
+    w1 = torch.empty((B, P, knum), dtype=z.dtype, device=dev)
+    from ...render.mesh.deftet import workspace
+    with torch.cuda.device(dev):
+        ws, ws_bytes = workspace(dev, B, F, P)
+        rc = _lib.lib().dibr_deftet_fwd_raw(
+            1 if f64 else 0, B, F, P, knum, _ptr(z), _ptr(img), _ptr(bbox), _ptr(pix), _ptr(rng),
+            float(eps), _ptr(idx), _ptr(depth), _ptr(w0), _ptr(w1), _ptr(ws), ws_bytes,
+            _stream(dev))
+    _lib.check(rc, fn)
+    return [idx, depth, w0, w1]
+
+
+def deftet_sparse_render_backward_cuda(grad_interpolated_features, face_idx, weights,
+                                       face_vertices_image, face_features, eps):
+    """deftet.cpp:109-165."""
+    fn = "deftet_sparse_render_backward_cuda"
+    dev = _check_all(fn, [("grad_interpolated_features", grad_interpolated_features),
+                          ("face_idx", face_idx), ("weights", weights),
+                          ("face_vertices_image", face_vertices_image),
+                          ("face_features", face_features)])
+    f64 = _check_float(fn, grad_interpolated_features, weights, face_vertices_image,
+                       face_features)
+    B, P, K, D = grad_interpolated_features.shape
+    F = face_vertices_image.shape[1]
+    _check_size(fn, "face_idx", face_idx, (B, P, K))
+    _check_size(fn, "weights", weights, (B, P, K, 3))
+    _check_size(fn, "face_vertices_image", face_vertices_image, (B, F, 3, 2))
+    _check_size(fn, "face_features", face_features, (B, F, 3, D))
+    img = _aligned(face_vertices_image)
+    grad_img = torch.empty_like(img)
+    grad_feat = torch.empty_like(face_features)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().dibr_deftet_bwd(
+            1 if f64 else 0, B, F, P, K, D, _ptr(grad_interpolated_features), _ptr(face_idx),
+            _ptr(weights), _ptr(img), _ptr(face_features), float(eps), _ptr(grad_img),
+            _ptr(grad_feat), _stream(dev))
+    _lib.check(rc, fn)
+    return [grad_img, grad_feat]

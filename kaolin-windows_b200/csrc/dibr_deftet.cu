@@ -1,0 +1,778 @@
+// dibr_deftet.cu -- deftet_sparse_render: the k-layer sibling of the
+// rasterizer for ARBITRARY sample points instead of a pixel grid.
+//   kaolin/render/mesh/deftet.py:269-417          DeftetSparseRenderer (torch side)
+//   kaolin/csrc/render/mesh/deftet_cuda.cu:31-193 forward kernel, :239-401 backward kernel
+//
+// Semantics kept from the reference: per sample point the FIRST knum faces in ascending
+// face index that (a) contain the point in their half-open bounding box, (b) have all three
+// normalised edge functions >= 0 and (c) whose interpolated depth lies in
+// [range_min, range_max) are kept (deftet_cuda.cu:120-168), then ordered by depth,
+// nearest (largest z) first (deftet.py:303-306), w2 := valid - (w0 + w1) (:307) and the
+// features interpolated (:308-317).  Arithmetic of the test in the shapes nvcc contracts
+// the reference into for sm_100a (read from cuobjdump -sass of oracle/_ref):
+//   _w0 = fma(bex, cey, -fl(bey * cex)), _w1 = fma(cex, aey, -fl(cey * aex)),
+//   _w2 = fma(aex, bey, -fl(aey * bex)), norm = (_w0 + _w1) + _w2,
+//   den = norm + copysign(eps_float, norm), w_k = _w_k / den (IEEE),
+//   depth = fma(w2, cz, fma(w0, az, fl(w1 * bz))).
+//
+// B200 design.  The reference tests every face against every point (one warp per point,
+// F / 32 steps).  Here the faces of a view are dealt into a uniform grid laid over the
+// bounding box of the view's sample points, cell size ~1.5 mean face extent (measured on
+// the device, no host round trip); faces spanning more than kWideCells cells go to one
+// per-view "wide" list instead.  A point only tests its cell's list plus the wide list.
+// Lists are filled with atomics (unordered): the kept set is order independent (all hits,
+// or the knum smallest face ids among them) and so is the final order (depth descending,
+// ties by face id = the reference's insertion order under a stable sort).
+// float and double are both instantiated (the reference dispatches both).
+#include <algorithm>
+
+#include "../../include/dibr_b200.h"
+#include "dibr_common.cuh"
+
+namespace dibr {
+
+int fail(int code, const char* fmt, ...);
+
+namespace {
+
+constexpr int kGridMax = 512;     // cells per axis at most
+constexpr int kWideCells = 12;    // a face spanning more cells goes to the wide list
+
+// ------------------------------------------------------------------ exact arithmetic
+__device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
+__device__ __forceinline__ double mul_rn(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ float add_rn(float a, float b) { return __fadd_rn(a, b); }
+__device__ __forceinline__ double add_rn(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ float sub_rn(float a, float b) { return __fsub_rn(a, b); }
+__device__ __forceinline__ double sub_rn(double a, double b) { return __dsub_rn(a, b); }
+__device__ __forceinline__ float fma_rn(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+__device__ __forceinline__ double fma_rn(double a, double b, double c) { return __fma_rn(a, b, c); }
+__device__ __forceinline__ float div_rn(float a, float b) { return __fdiv_rn(a, b); }
+__device__ __forceinline__ double div_rn(double a, double b) { return __ddiv_rn(a, b); }
+__device__ __forceinline__ float to_f(float a) { return a; }
+__device__ __forceinline__ float to_f(double a) { return __double2float_rn(a); }  // monotone
+__device__ __forceinline__ bool sign_of(float a) { return (__float_as_uint(a) >> 31) != 0; }
+__device__ __forceinline__ bool sign_of(double a) { return (__double2hiint(a) >> 31) != 0; }
+
+template <typename T> struct Vec2;
+template <> struct Vec2<float> { typedef float2 type; };
+template <> struct Vec2<double> { typedef double2 type; };
+
+// float <-> unsigned with the order of the floats; every non-NaN value encodes to >= 1
+__device__ __forceinline__ unsigned enc_f(float f) {
+  const unsigned u = __float_as_uint(f);
+  return (u >> 31) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float dec_f(unsigned e) {
+  return __uint_as_float((e >> 31) ? (e & 0x7fffffffu) : ~e);
+}
+
+// per-view statistics the grid is derived from (zero-initialised by a memset)
+struct ViewStats {
+  unsigned nlo_x, nlo_y;          // ~enc(min sample coordinate)  (atomicMax)
+  unsigned hi_x, hi_y;            // enc(max sample coordinate)   (atomicMax); 0 = no sample
+  unsigned long long extent_sum;  // sum over faces of (clipped extent / domain) * 65536
+  unsigned faces;                 // faces meeting the samples' bounding box
+  unsigned wide;                  // entries of the wide list
+};
+
+struct CellGrid {
+  float lox, loy, hix, hiy, invx, invy;
+  int gx, gy;
+  bool empty;
+};
+
+// Every thread derives the same grid from the same statistics (pure function, ~30 instr.).
+__device__ __forceinline__ CellGrid make_grid(const ViewStats& s, int cells_cap) {
+  CellGrid g;
+  g.empty = (s.hi_x == 0u);
+  g.gx = g.gy = 1;
+  g.invx = g.invy = 0.f;
+  g.lox = g.loy = g.hix = g.hiy = 0.f;
+  if (g.empty) return g;
+  g.lox = dec_f(~s.nlo_x); g.loy = dec_f(~s.nlo_y);
+  g.hix = dec_f(s.hi_x); g.hiy = dec_f(s.hi_y);
+  const float dx = g.hix - g.lox, dy = g.hiy - g.loy;
+  const float dmax = fmaxf(dx, dy);
+  if (!(dmax > 0.f) || !(dmax < 3.0e38f) || s.faces == 0u) return g;
+  // mean clipped face extent as a fraction of the domain, times 1.5
+  float frac = 1.5f * ((float)s.extent_sum / (float)s.faces) * (1.f / 65536.f);
+  frac = fmaxf(frac, 1.f / (float)kGridMax);
+  int gx = (int)(dx / dmax / frac) + 1, gy = (int)(dy / dmax / frac) + 1;
+  gx = min(max(gx, 1), kGridMax);
+  gy = min(max(gy, 1), kGridMax);
+  while ((long long)gx * gy > cells_cap) { gx = (gx + 1) >> 1; gy = (gy + 1) >> 1; }
+  g.gx = gx; g.gy = gy;
+  g.invx = dx > 0.f ? (float)gx / dx : 0.f;
+  g.invy = dy > 0.f ? (float)gy / dy : 0.f;
+  if (!(g.invx < 3.0e38f)) { g.invx = 0.f; g.gx = 1; }
+  if (!(g.invy < 3.0e38f)) { g.invy = 0.f; g.gy = 1; }
+  return g;
+}
+
+// monotone non-decreasing in v (sub, mul by >= 0, truncation and clamp all are), so a
+// point inside [lo, hi) of a box falls in a cell between cell(lo) and cell(hi).
+__device__ __forceinline__ int cell_of(float v, float lo, float inv, int n) {
+  const float t = (v - lo) * inv;
+  return (t >= 0.f) ? ((t < (float)n) ? (int)t : n - 1) : 0;
+}
+
+template <typename T>
+struct DeftetArgs {
+  const T* z;          // (B, F, 3)
+  const T* img;        // (B, F, 3, 2)
+  const T* bbox;       // (B, F, 4) or nullptr (computed from img)
+  const T* feat;       // (B, F, 3, D)
+  const T* pix;        // (B, P, 2)
+  const T* range;      // (B, P, 2)
+  int64_t* out_idx;    // (B, P, K)
+  T* out_feat;         // (B, P, K, D)        sorted mode
+  T* out_w;            // (B, P, K, 3)        sorted mode
+  T* out_depth;        // (B, P, K)           raw mode
+  T* out_w0;           // (B, P, K)           raw mode
+  T* out_w1;           // (B, P, K)           raw mode
+  ViewStats* stats;    // [B]
+  int* cell_start;     // [B][cells_cap]
+  int* cell_count;     // [B][cells_cap]
+  int* wide;           // [B][F]
+  int* list;           // [B][kWideCells * F]
+  int B, F, P, K, D, cells_cap, n2;
+  float eps;
+};
+
+template <typename T>
+__device__ __forceinline__ bool any_nan6(const T (&v)[6]) {
+  return v[0] != v[0] || v[1] != v[1] || v[2] != v[2] || v[3] != v[3] || v[4] != v[4] ||
+         v[5] != v[5];
+}
+
+template <typename T>
+__device__ __forceinline__ void load_img6(const T* img, long long bf, T (&v)[6]) {
+  typedef typename Vec2<T>::type V2;
+  const V2* p = reinterpret_cast<const V2*>(img) + bf * 3;
+  const V2 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
+  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y;
+}
+
+// box of a face as torch.min / torch.max over the three vertices give it (deftet.py:290-292;
+// a NaN coordinate makes the box NaN, i.e. the face can never be hit) or the caller's box
+template <typename T>
+__device__ __forceinline__ bool face_box(const DeftetArgs<T>& a, long long bf, const T (&v)[6],
+                                         T& xmin, T& ymin, T& xmax, T& ymax) {
+  if (a.bbox) {
+    const T* q = a.bbox + bf * 4;
+    xmin = __ldg(q); ymin = __ldg(q + 1); xmax = __ldg(q + 2); ymax = __ldg(q + 3);
+    return !(xmin != xmin || ymin != ymin || xmax != xmax || ymax != ymax);
+  }
+  if (any_nan6(v)) return false;
+  xmin = v[0] < v[2] ? v[0] : v[2]; xmin = xmin < v[4] ? xmin : v[4];
+  xmax = v[0] > v[2] ? v[0] : v[2]; xmax = xmax > v[4] ? xmax : v[4];
+  ymin = v[1] < v[3] ? v[1] : v[3]; ymin = ymin < v[5] ? ymin : v[5];
+  ymax = v[1] > v[3] ? v[1] : v[3]; ymax = ymax > v[5] ? ymax : v[5];
+  return true;
+}
+
+// cell rectangle of a face; false if it cannot contain any sample of the view
+template <typename T>
+__device__ __forceinline__ bool face_cells(const DeftetArgs<T>& a, const CellGrid& g, int b,
+                                           int f, int& cx0, int& cy0, int& cx1, int& cy1,
+                                           float& ext) {
+  if (g.empty) return false;
+  const long long bf = (long long)b * a.F + f;
+  T v[6];
+  if (!a.bbox) load_img6(a.img, bf, v);
+  T xmin, ymin, xmax, ymax;
+  if (!face_box(a, bf, v, xmin, ymin, xmax, ymax)) return false;
+  const float fx0 = to_f(xmin), fy0 = to_f(ymin), fx1 = to_f(xmax), fy1 = to_f(ymax);
+  // a hit needs xmin <= x < xmax with lox <= x <= hix (to_f is monotone, so the float
+  // images keep the non-strict forms of these inequalities)
+  if (!(fx1 >= g.lox && fx0 <= g.hix && fy1 >= g.loy && fy0 <= g.hiy)) return false;
+  cx0 = cell_of(fx0, g.lox, g.invx, g.gx); cx1 = cell_of(fx1, g.lox, g.invx, g.gx);
+  cy0 = cell_of(fy0, g.loy, g.invy, g.gy); cy1 = cell_of(fy1, g.loy, g.invy, g.gy);
+  ext = fmaxf(fminf(fx1, g.hix) - fmaxf(fx0, g.lox), fminf(fy1, g.hiy) - fmaxf(fy0, g.loy));
+  return true;
+}
+
+// ------------------------------------------------------------------ grid construction
+template <typename T>
+__global__ void __launch_bounds__(256) deftet_bounds_kernel(const DeftetArgs<T> a) {
+  typedef typename Vec2<T>::type V2;
+  const int b = blockIdx.y;
+  unsigned nlx = 0, nly = 0, hx = 0, hy = 0;
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < a.P; p += gridDim.x * blockDim.x) {
+    const V2 c = __ldg(reinterpret_cast<const V2*>(a.pix) + (long long)b * a.P + p);
+    if (c.x != c.x || c.y != c.y) continue;   // such a sample hits nothing
+    const unsigned ex = enc_f(to_f(c.x)), ey = enc_f(to_f(c.y));
+    nlx = max(nlx, ~ex); nly = max(nly, ~ey); hx = max(hx, ex); hy = max(hy, ey);
+  }
+  nlx = __reduce_max_sync(DIBR_FULL_MASK, nlx); nly = __reduce_max_sync(DIBR_FULL_MASK, nly);
+  hx = __reduce_max_sync(DIBR_FULL_MASK, hx); hy = __reduce_max_sync(DIBR_FULL_MASK, hy);
+  if ((threadIdx.x & 31) == 0 && hx != 0u) {
+    ViewStats* s = a.stats + b;
+    atomicMax(&s->nlo_x, nlx); atomicMax(&s->nlo_y, nly);
+    atomicMax(&s->hi_x, hx); atomicMax(&s->hi_y, hy);
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) deftet_extent_kernel(const DeftetArgs<T> a) {
+  const int b = blockIdx.y;
+  ViewStats s = a.stats[b];
+  s.faces = 0; s.extent_sum = 0;   // this kernel writes them; the grid below ignores them
+  CellGrid g = make_grid(s, 1);
+  const float dmax = fmaxf(g.hix - g.lox, g.hiy - g.loy);
+  unsigned cnt = 0, sum = 0;
+  for (int f = blockIdx.x * blockDim.x + threadIdx.x; f < a.F; f += gridDim.x * blockDim.x) {
+    int cx0, cy0, cx1, cy1; float ext;
+    if (!face_cells(a, g, b, f, cx0, cy0, cx1, cy1, ext)) continue;
+    cnt++;
+    float q = dmax > 0.f ? ext / dmax : 0.f;
+    q = fminf(fmaxf(q, 0.f), 1.f);             // NaN -> 0
+    sum += (unsigned)(q * 65536.f);
+  }
+  cnt = __reduce_add_sync(DIBR_FULL_MASK, cnt);
+  // a warp's 32 summands of <= 65536 fit 32 bits
+  sum = __reduce_add_sync(DIBR_FULL_MASK, sum);
+  if ((threadIdx.x & 31) == 0 && cnt) {
+    atomicAdd(&a.stats[b].faces, cnt);
+    atomicAdd(&a.stats[b].extent_sum, (unsigned long long)sum);
+  }
+}
+
+// FILL = false: count entries per cell, wide faces go straight to the wide list;
+// FILL = true : write the face ids (cell_count doubles as the cursor, rebuilt to the count)
+template <typename T, bool FILL>
+__global__ void __launch_bounds__(256) deftet_bin_kernel(const DeftetArgs<T> a) {
+  const int b = blockIdx.y;
+  const CellGrid g = make_grid(a.stats[b], a.cells_cap);
+  int* cnt = a.cell_count + (long long)b * a.cells_cap;
+  const int* start = a.cell_start + (long long)b * a.cells_cap;
+  int* list = a.list + (long long)b * kWideCells * a.F;
+  for (int f = blockIdx.x * blockDim.x + threadIdx.x; f < a.F; f += gridDim.x * blockDim.x) {
+    int cx0, cy0, cx1, cy1; float ext;
+    if (!face_cells(a, g, b, f, cx0, cy0, cx1, cy1, ext)) continue;
+    if ((cx1 - cx0 + 1) * (cy1 - cy0 + 1) > kWideCells) {
+      if (!FILL) a.wide[(long long)b * a.F + atomicAdd(&a.stats[b].wide, 1u)] = f;
+      continue;
+    }
+    for (int cy = cy0; cy <= cy1; cy++)
+      for (int cx = cx0; cx <= cx1; cx++) {
+        const int c = cy * g.gx + cx;
+        if (FILL) list[start[c] + atomicAdd(cnt + c, 1)] = f;
+        else atomicAdd(cnt + c, 1);
+      }
+  }
+}
+
+// one CTA per view: exclusive scan of the cell counts, counts reset for the fill's cursors
+__global__ void __launch_bounds__(1024) deftet_scan_kernel(const ViewStats* stats, int* cell_start,
+                                                           int* cell_count, int cells_cap) {
+  __shared__ int warp_sum[32];
+  __shared__ int carry;
+  const int b = blockIdx.x;
+  const CellGrid g = make_grid(stats[b], cells_cap);
+  const int n = g.gx * g.gy;
+  int* cnt = cell_count + (long long)b * cells_cap;
+  int* start = cell_start + (long long)b * cells_cap;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int base = 0; base < n; base += 1024) {
+    const int i = base + threadIdx.x;
+    const int v = i < n ? cnt[i] : 0;
+    int s = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(DIBR_FULL_MASK, s, o);
+      if (lane >= o) s += t;
+    }
+    if (lane == 31) warp_sum[warp] = s;
+    __syncthreads();
+    if (warp == 0) {
+      int w = warp_sum[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int t = __shfl_up_sync(DIBR_FULL_MASK, w, o);
+        if (lane >= o) w += t;
+      }
+      warp_sum[lane] = w;
+    }
+    __syncthreads();
+    const int prefix = carry + (warp ? warp_sum[warp - 1] : 0) + s - v;
+    if (i < n) { start[i] = prefix; cnt[i] = 0; }
+    __syncthreads();
+    if (threadIdx.x == 1023) carry = prefix + v;
+    __syncthreads();
+  }
+}
+
+// ------------------------------------------------------------------ per-sample work
+// shared-memory staging of one warp's hits
+template <typename T>
+struct HitBuf {
+  T* depth; T* w0; T* w1; int* face; int* perm;
+};
+
+template <typename T>
+__device__ __forceinline__ HitBuf<T> carve(unsigned char* base, int warp, int K, int n2) {
+  const size_t per_warp = (size_t)K * (3 * sizeof(T) + sizeof(int)) + (size_t)n2 * sizeof(int);
+  unsigned char* p = base + (size_t)warp * ((per_warp + 15) & ~(size_t)15);
+  HitBuf<T> h;
+  h.depth = reinterpret_cast<T*>(p);
+  h.w0 = h.depth + K;
+  h.w1 = h.w0 + K;
+  h.face = reinterpret_cast<int*>(h.w1 + K);
+  h.perm = h.face + K;
+  return h;
+}
+
+// the reference's test of one face against one sample (deftet_cuda.cu:120-163)
+template <typename T>
+__device__ __forceinline__ bool deftet_test(const DeftetArgs<T>& a, int b, int f, T x0, T y0,
+                                            T dmin, T dmax, T eps_t, T& w0, T& w1, T& depth) {
+  const long long bf = (long long)b * a.F + f;
+  T v[6];
+  load_img6(a.img, bf, v);
+  T xmin, ymin, xmax, ymax;
+  if (!face_box(a, bf, v, xmin, ymin, xmax, ymax)) return false;
+  if (!(x0 >= xmin && x0 < xmax && y0 >= ymin && y0 < ymax)) return false;
+  const T aex = sub_rn(v[0], x0), aey = sub_rn(v[1], y0);
+  const T bex = sub_rn(v[2], x0), bey = sub_rn(v[3], y0);
+  const T cex = sub_rn(v[4], x0), cey = sub_rn(v[5], y0);
+  const T r0 = fma_rn(bex, cey, -mul_rn(bey, cex));
+  const T r1 = fma_rn(cex, aey, -mul_rn(cey, aex));
+  const T r2 = fma_rn(aex, bey, -mul_rn(aey, bex));
+  const T norm = add_rn(add_rn(r0, r1), r2);
+  const T den = add_rn(norm, sign_of(norm) ? -eps_t : eps_t);
+  w0 = div_rn(r0, den);
+  w1 = div_rn(r1, den);
+  const T w2 = div_rn(r2, den);
+  if (!(w0 >= (T)0 && w1 >= (T)0 && w2 >= (T)0)) return false;
+  const T* zp = a.z + bf * 3;
+  const T az = __ldg(zp), bz = __ldg(zp + 1), cz = __ldg(zp + 2);
+  depth = fma_rn(w2, cz, fma_rn(w0, az, mul_rn(w1, bz)));
+  return depth < dmax && depth >= dmin;
+}
+
+// order of the output slots: RAW = the reference kernel's insertion order (ascending face),
+// else depth descending, ties by ascending face (a stable sort of the insertion order)
+template <typename T, bool RAW>
+__device__ __forceinline__ bool slot_before(const HitBuf<T>& h, int i, int j) {
+  if (j < 0) return i >= 0;
+  if (i < 0) return false;
+  if (RAW) return h.face[i] < h.face[j];
+  const T di = h.depth[i], dj = h.depth[j];
+  return di > dj || (di == dj && h.face[i] < h.face[j]);
+}
+
+template <typename T, bool RAW>
+__global__ void __launch_bounds__(256) deftet_render_kernel(const DeftetArgs<T> a) {
+  typedef typename Vec2<T>::type V2;
+  extern __shared__ __align__(16) unsigned char smem[];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const long long gp = (long long)blockIdx.x * (blockDim.x >> 5) + warp;
+  if (gp >= (long long)a.B * a.P) return;
+  const int b = (int)(gp / a.P);
+  const int K = a.K;
+  HitBuf<T> h = carve<T>(smem, warp, K, a.n2);
+  const V2 c = __ldg(reinterpret_cast<const V2*>(a.pix) + gp);
+  const V2 r = __ldg(reinterpret_cast<const V2*>(a.range) + gp);
+  const T x0 = c.x, y0 = c.y, dmin = r.x, dmax = r.y;
+  const T eps_t = (T)a.eps;
+  const ViewStats st = a.stats[b];
+  const CellGrid g = make_grid(st, a.cells_cap);
+
+  int n = 0;            // hits held (warp uniform)
+  int maxf = -1, maxs = -1;   // largest held face id and its slot, valid once the buffer is full
+  const bool live = !g.empty && !(x0 != x0) && !(y0 != y0);
+  for (int pass = 0; pass < 2 && live; pass++) {
+    const int* lst;
+    int len;
+    if (pass == 0) {
+      const int cell = cell_of(to_f(y0), g.loy, g.invy, g.gy) * g.gx +
+                       cell_of(to_f(x0), g.lox, g.invx, g.gx);
+      lst = a.list + (long long)b * kWideCells * a.F + a.cell_start[(long long)b * a.cells_cap + cell];
+      len = a.cell_count[(long long)b * a.cells_cap + cell];
+    } else {
+      lst = a.wide + (long long)b * a.F;
+      len = (int)st.wide;
+    }
+    for (int base = 0; base < len; base += 32) {
+      const int i = base + lane;
+      int f = -1;
+      T w0 = 0, w1 = 0, depth = 0;
+      bool hit = false;
+      if (i < len) {
+        f = __ldg(lst + i);
+        hit = deftet_test(a, b, f, x0, y0, dmin, dmax, eps_t, w0, w1, depth);
+      }
+      unsigned m = __ballot_sync(DIBR_FULL_MASK, hit);
+      if (m == 0u) continue;
+      const int cnt = __popc(m);
+      if (n + cnt <= K) {
+        if (hit) {
+          const int s = n + __popc(m & lanemask_lt());
+          h.face[s] = f; h.depth[s] = depth; h.w0[s] = w0; h.w1[s] = w1;
+        }
+        n += cnt;
+        continue;
+      }
+      // more hits than slots: keep the K smallest face ids (the reference keeps the first
+      // K in ascending face order)
+      while (m) {
+        const int src = __ffs(m) - 1;
+        m &= m - 1;
+        const int bf_ = __shfl_sync(DIBR_FULL_MASK, f, src);
+        const T bd = __shfl_sync(DIBR_FULL_MASK, depth, src);
+        const T b0 = __shfl_sync(DIBR_FULL_MASK, w0, src);
+        const T b1 = __shfl_sync(DIBR_FULL_MASK, w1, src);
+        int s = -1;
+        if (n < K) {
+          s = n++;
+          maxs = -1;
+        } else {
+          if (K == 0) continue;
+          if (maxs < 0) {
+            __syncwarp();
+            int mf = -1, ms = -1;
+            for (int k = lane; k < K; k += 32) {
+              const int t = h.face[k];
+              if (t > mf) { mf = t; ms = k; }
+            }
+            const int top = __reduce_max_sync(DIBR_FULL_MASK, mf);
+            const unsigned who = __ballot_sync(DIBR_FULL_MASK, mf == top);
+            maxs = __shfl_sync(DIBR_FULL_MASK, ms, __ffs(who) - 1);
+            maxf = top;
+          }
+          if (bf_ < maxf) { s = maxs; maxs = -1; }
+        }
+        if (s >= 0 && lane == 0) { h.face[s] = bf_; h.depth[s] = bd; h.w0[s] = b0; h.w1[s] = b1; }
+        __syncwarp();
+      }
+    }
+  }
+  __syncwarp();
+
+  // order the held hits: bitonic network over slot numbers (padding = -1 goes last)
+  int n2 = 1;
+  while (n2 < n) n2 <<= 1;
+  for (int k = lane; k < n2; k += 32) h.perm[k] = k < n ? k : -1;
+  __syncwarp();
+  for (int k = 2; k <= n2; k <<= 1)
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int t = lane; t < (n2 >> 1); t += 32) {
+        const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+        const int l = i | j;
+        const int pi = h.perm[i], pl = h.perm[l];
+        const bool up = (i & k) == 0;
+        if (up ? slot_before<T, RAW>(h, pl, pi) : slot_before<T, RAW>(h, pi, pl)) {
+          h.perm[i] = pl; h.perm[l] = pi;
+        }
+      }
+      __syncwarp();
+    }
+
+  // write every slot of the sample (fills included: the library writes all outputs)
+  const long long row = gp * K;
+  for (int k = lane; k < K; k += 32) {
+    const int s = k < n ? h.perm[k] : -1;
+    a.out_idx[row + k] = s >= 0 ? (int64_t)h.face[s] : (int64_t)-1;
+    if (RAW) {
+      a.out_depth[row + k] = s >= 0 ? h.depth[s] : -(T)INFINITY;
+      a.out_w0[row + k] = s >= 0 ? h.w0[s] : (T)0;
+      a.out_w1[row + k] = s >= 0 ? h.w1[s] : (T)0;
+    }
+  }
+  if constexpr (!RAW) {
+  for (int j = lane; j < 3 * K; j += 32) {
+    const int k = j / 3, comp = j - 3 * k;
+    const int s = k < n ? h.perm[k] : -1;
+    T v = (T)0;
+    if (s >= 0) {
+      const T w0 = h.w0[s], w1 = h.w1[s];
+      // deftet.py:307  w2 = (face_idx != -1) - (w0 + w1)
+      v = comp == 0 ? w0 : (comp == 1 ? w1 : sub_rn((T)1, add_rn(w0, w1)));
+    }
+    a.out_w[row * 3 + j] = v;
+  }
+  const int D = a.D;
+  for (int j = lane; j < K * D; j += 32) {
+    const int k = j / D, d = j - k * D;
+    const int s = k < n ? h.perm[k] : -1;
+    T v = (T)0;
+    if (s >= 0) {
+      const T w0 = h.w0[s], w1 = h.w1[s], w2 = sub_rn((T)1, add_rn(w0, w1));
+      const T* fp = a.feat + ((long long)b * a.F + h.face[s]) * 3 * D + d;
+      // deftet.py:315-317  sum over the three vertices of weight * feature
+      v = add_rn(add_rn(mul_rn(w0, __ldg(fp)), mul_rn(w1, __ldg(fp + D))),
+                 mul_rn(w2, __ldg(fp + 2 * D)));
+    }
+    a.out_feat[row * D + j] = v;
+  }
+  }  // !RAW
+}
+
+// ------------------------------------------------------------------ backward
+// deftet_cuda.cu:239-401: one thread per (sample, layer) slot; the six image-coordinate
+// terms are summed over the features before the atomics (the reference issues 6 per feature).
+template <typename T>
+struct DeftetBwdArgs {
+  const T* grad;         // (B, P, K, D)
+  const int64_t* idx;    // (B, P, K)
+  const T* weights;      // (B, P, K, 3)
+  const T* img;          // (B, F, 3, 2)
+  const T* feat;         // (B, F, 3, D)
+  T* grad_img;           // (B, F, 3, 2)  accumulated
+  T* grad_feat;          // (B, F, 3, D)  accumulated
+  long long slots;       // B * P * K
+  long long per_view;    // P * K
+  int F, D;
+  float eps;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256) deftet_backward_kernel(const DeftetBwdArgs<T> a) {
+  for (long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x; s < a.slots;
+       s += (long long)gridDim.x * blockDim.x) {
+    const long long f = a.idx[s];
+    if (f < 0) continue;
+    const long long bf = (s / a.per_view) * a.F + f;
+    const int D = a.D;
+    const T* g = a.grad + s * D;
+    const T aw = __ldg(a.weights + s * 3), bw = __ldg(a.weights + s * 3 + 1),
+            cw = __ldg(a.weights + s * 3 + 2);
+    T* gf = a.grad_feat + bf * 3 * D;
+    for (int d = 0; d < D; d++) {
+      const T gd = __ldg(g + d);
+      atomicAdd(gf + d, gd * aw);
+      atomicAdd(gf + D + d, gd * bw);
+      atomicAdd(gf + 2 * D + d, gd * cw);
+    }
+    T v[6];
+    load_img6(a.img, bf, v);
+    const T ax = v[0], ay = v[1], bx = v[2], by = v[3], cx = v[4], cy = v[5];
+    const T x0 = aw * ax + bw * bx + cw * cx;
+    const T y0 = aw * ay + bw * by + cw * cy;
+    const T m = bx - ax, p = by - ay, n = cx - ax, q = cy - ay, sx = x0 - ax, t = y0 - ay;
+    const T k1 = sx * q - n * t;
+    const T k2 = m * t - sx * p;
+    T k3 = m * q - n * p;
+    k3 = (T)((double)k3 + copysign((double)a.eps, (double)k3));   // :321
+    // d(w1 k3^2), d(w2 k3^2) with respect to m, n, p, q, s, t (:324-349)
+    const T dw1dm = -q * k1, dw1dn = -t * k3 + p * k1, dw1dp = n * k1, dw1dq = sx * k3 - m * k1;
+    const T dw1ds = q * k3, dw1dt = -n * k3;
+    const T dw2dm = t * k3 - q * k2, dw2dn = p * k2, dw2dp = -sx * k3 + n * k2, dw2dq = -m * k2;
+    const T dw2ds = -p * k3, dw2dt = m * k3;
+    const T dw1dax = -(dw1dm + dw1dn + dw1ds), dw1day = -(dw1dp + dw1dq + dw1dt);
+    const T dw2dax = -(dw2dm + dw2dn + dw2ds), dw2day = -(dw2dp + dw2dq + dw2dt);
+    const T inv = (T)1 / (k3 * k3);
+    const T* fp = a.feat + bf * 3 * D;
+    T s_ax = 0, s_ay = 0, s_bx = 0, s_by = 0, s_cx = 0, s_cy = 0;
+    for (int d = 0; d < D; d++) {
+      const T c0 = __ldg(fp + d), c1 = __ldg(fp + D + d), c2 = __ldg(fp + 2 * D + d);
+      const T e1 = c1 - c0, e2 = c2 - c0;
+      const T dl = __ldg(g + d) * inv;
+      s_ax += dl * (e1 * dw1dax + e2 * dw2dax);
+      s_ay += dl * (e1 * dw1day + e2 * dw2day);
+      s_bx += dl * (e1 * dw1dm + e2 * dw2dm);
+      s_by += dl * (e1 * dw1dp + e2 * dw2dp);
+      s_cx += dl * (e1 * dw1dn + e2 * dw2dn);
+      s_cy += dl * (e1 * dw1dq + e2 * dw2dq);
+    }
+    T* gi = a.grad_img + bf * 6;
+    atomicAdd(gi + 0, s_ax); atomicAdd(gi + 1, s_ay);
+    atomicAdd(gi + 2, s_bx); atomicAdd(gi + 3, s_by);
+    atomicAdd(gi + 4, s_cx); atomicAdd(gi + 5, s_cy);
+  }
+}
+
+inline int64_t up256(int64_t v) { return (v + 255) / 256 * 256; }
+
+struct DeftetLayout {
+  int cells_cap;
+  int64_t off_stats, off_start, off_count, off_wide, off_list, bytes, zero_bytes;
+};
+
+DeftetLayout deftet_layout(int B, int F, int P) {
+  DeftetLayout L;
+  int64_t cap = 4 * (int64_t)P + 16;
+  if (cap > (int64_t)kGridMax * kGridMax) cap = (int64_t)kGridMax * kGridMax;
+  L.cells_cap = (int)cap;
+  int64_t off = 0;
+  L.off_stats = off; off = up256(off + (int64_t)B * sizeof(ViewStats));
+  L.off_count = off; off = up256(off + (int64_t)B * cap * 4);
+  L.zero_bytes = off;                       // stats and counts are memset, the rest written
+  L.off_start = off; off = up256(off + (int64_t)B * cap * 4);
+  L.off_wide = off; off = up256(off + (int64_t)B * F * 4);
+  L.off_list = off; off = up256(off + (int64_t)B * F * 4 * kWideCells);
+  L.bytes = off;
+  return L;
+}
+
+#define DEF_CUDA(expr)                                                               \
+  do {                                                                               \
+    cudaError_t e_ = (expr);                                                         \
+    if (e_ != cudaSuccess)                                                           \
+      return fail(DIBR_E_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e_));      \
+  } while (0)
+
+template <typename T>
+int deftet_forward(bool raw, int B, int F, int P, int K, int D, const void* z, const void* img,
+                   const void* bbox, const void* feat, const void* pix, const void* range,
+                   float eps, int64_t* out_idx, void* o1, void* o2, void* o3, void* ws,
+                   int64_t ws_bytes, cudaStream_t st) {
+  if (B < 0 || F < 0 || P < 0 || K < 0 || D < 0) return fail(DIBR_E_INVALID, "invalid sizes");
+  if (B > 65535) return fail(DIBR_E_INVALID, "batch %d > 65535 not supported", B);
+  if ((int64_t)F * kWideCells > 0x7fffffff) return fail(DIBR_E_INVALID, "too many faces");
+  if (B == 0 || P == 0 || K == 0) return DIBR_OK;
+  if (!pix || !range || !out_idx) return fail(DIBR_E_INVALID, "null pointer");
+  if (F > 0 && (!z || !img)) return fail(DIBR_E_INVALID, "null input");
+  if (raw ? (!o1 || !o2 || !o3) : (!o2 || (D > 0 && (!o1 || (F > 0 && !feat)))))
+    return fail(DIBR_E_INVALID, "null output");
+  const DeftetLayout L = deftet_layout(B, F, P);
+  if (!ws || ws_bytes < L.bytes)
+    return fail(DIBR_E_WORKSPACE, "workspace of %lld bytes given, %lld needed",
+                (long long)ws_bytes, (long long)L.bytes);
+  if (((uintptr_t)ws & 255) != 0) return fail(DIBR_E_INVALID, "workspace must be 256-byte aligned");
+  DeftetArgs<T> a = {};
+  a.z = (const T*)z; a.img = (const T*)img; a.bbox = (const T*)bbox; a.feat = (const T*)feat;
+  a.pix = (const T*)pix; a.range = (const T*)range;
+  a.out_idx = out_idx;
+  if (raw) { a.out_depth = (T*)o1; a.out_w0 = (T*)o2; a.out_w1 = (T*)o3; }
+  else { a.out_feat = (T*)o1; a.out_w = (T*)o2; }
+  char* base = (char*)ws;
+  a.stats = (ViewStats*)(base + L.off_stats);
+  a.cell_count = (int*)(base + L.off_count);
+  a.cell_start = (int*)(base + L.off_start);
+  a.wide = (int*)(base + L.off_wide);
+  a.list = (int*)(base + L.off_list);
+  a.B = B; a.F = F; a.P = P; a.K = K; a.D = D; a.cells_cap = L.cells_cap; a.eps = eps;
+  int n2 = 1;
+  while (n2 < K) n2 <<= 1;
+  a.n2 = n2;
+
+  DEF_CUDA(cudaMemsetAsync(base, 0, (size_t)L.zero_bytes, st));
+  if (F > 0) {
+    const int pb = (int)std::min<int64_t>((P + 255) / 256, 64);
+    deftet_bounds_kernel<T><<<dim3(pb, B), 256, 0, st>>>(a);
+    const int fb = (int)std::max<int64_t>(1, std::min<int64_t>((F + 255) / 256, (148 * 8 + B - 1) / B));
+    deftet_extent_kernel<T><<<dim3(fb, B), 256, 0, st>>>(a);
+    deftet_bin_kernel<T, false><<<dim3(fb, B), 256, 0, st>>>(a);
+    deftet_scan_kernel<<<B, 1024, 0, st>>>(a.stats, a.cell_start, a.cell_count, a.cells_cap);
+    deftet_bin_kernel<T, true><<<dim3(fb, B), 256, 0, st>>>(a);
+    DEF_CUDA(cudaGetLastError());
+  }
+  // one warp per sample; warps per CTA limited by the staging of K hits per warp
+  size_t per_warp = (size_t)K * (3 * sizeof(T) + sizeof(int)) + (size_t)n2 * sizeof(int);
+  per_warp = (per_warp + 15) & ~(size_t)15;
+  int warps = (int)std::min<size_t>(8, (200 * 1024) / per_warp);
+  if (warps < 1) return fail(DIBR_E_INVALID, "knum %d needs %zu bytes of shared memory per sample, "
+                             "more than an SM has", K, per_warp);
+  const size_t smem = per_warp * warps;
+  auto kern = raw ? deftet_render_kernel<T, true> : deftet_render_kernel<T, false>;
+  if (smem > 48 * 1024)
+    DEF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int64_t blocks = ((int64_t)B * P + warps - 1) / warps;
+  if (blocks > 0x7fffffff) return fail(DIBR_E_INVALID, "too many sample points");
+  kern<<<(unsigned)blocks, warps * 32, smem, st>>>(a);
+  DEF_CUDA(cudaGetLastError());
+  return DIBR_OK;
+}
+
+template <typename T>
+int deftet_backward(int B, int F, int P, int K, int D, const void* grad, const int64_t* idx,
+                    const void* weights, const void* img, const void* feat, float eps,
+                    void* grad_img, void* grad_feat, cudaStream_t st) {
+  if (B < 0 || F < 0 || P < 0 || K < 0 || D < 0) return fail(DIBR_E_INVALID, "invalid sizes");
+  if (B == 0 || F == 0) return DIBR_OK;
+  if (!grad_img || (D > 0 && !grad_feat)) return fail(DIBR_E_INVALID, "null output");
+  DEF_CUDA(cudaMemsetAsync(grad_img, 0, (size_t)B * F * 6 * sizeof(T), st));
+  if (D > 0) DEF_CUDA(cudaMemsetAsync(grad_feat, 0, (size_t)B * F * 3 * D * sizeof(T), st));
+  const long long slots = (long long)B * P * K;
+  if (slots == 0 || D == 0) return DIBR_OK;
+  if (!grad || !idx || !weights || !img || !feat) return fail(DIBR_E_INVALID, "null input");
+  DeftetBwdArgs<T> a = {};
+  a.grad = (const T*)grad; a.idx = idx; a.weights = (const T*)weights; a.img = (const T*)img;
+  a.feat = (const T*)feat; a.grad_img = (T*)grad_img; a.grad_feat = (T*)grad_feat;
+  a.slots = slots; a.per_view = (long long)P * K; a.F = F; a.D = D; a.eps = eps;
+  const long long blocks = std::min<long long>((slots + 255) / 256, 148 * 32);
+  deftet_backward_kernel<T><<<(unsigned)blocks, 256, 0, st>>>(a);
+  DEF_CUDA(cudaGetLastError());
+  return DIBR_OK;
+}
+
+}  // namespace
+}  // namespace dibr
+
+using namespace dibr;
+
+extern "C" {
+
+DIBR_API int64_t dibr_deftet_workspace_bytes(int batch, int num_faces, int num_points) {
+  if (batch < 0 || num_faces < 0 || num_points < 0)
+    return fail(DIBR_E_INVALID, "invalid sizes");
+  return deftet_layout(batch, num_faces, num_points).bytes;
+}
+
+DIBR_API int dibr_deftet_fwd(int dtype, int batch, int num_faces, int num_points, int knum,
+                             int feat_dim, const void* face_vertices_z,
+                             const void* face_vertices_image, const void* face_features,
+                             const void* pixel_coords, const void* render_ranges, float eps,
+                             int64_t* face_idx, void* interpolated_features, void* weights,
+                             void* ws, int64_t ws_bytes, void* stream) {
+  if (dtype == DIBR_F32)
+    return deftet_forward<float>(false, batch, num_faces, num_points, knum, feat_dim,
+                                 face_vertices_z, face_vertices_image, nullptr, face_features,
+                                 pixel_coords, render_ranges, eps, face_idx,
+                                 interpolated_features, weights, nullptr, ws, ws_bytes,
+                                 (cudaStream_t)stream);
+  if (dtype == DIBR_F64)
+    return deftet_forward<double>(false, batch, num_faces, num_points, knum, feat_dim,
+                                  face_vertices_z, face_vertices_image, nullptr, face_features,
+                                  pixel_coords, render_ranges, eps, face_idx,
+                                  interpolated_features, weights, nullptr, ws, ws_bytes,
+                                  (cudaStream_t)stream);
+  return fail(DIBR_E_INVALID, "dtype must be DIBR_F32 or DIBR_F64");
+}
+
+DIBR_API int dibr_deftet_fwd_raw(int dtype, int batch, int num_faces, int num_points, int knum,
+                                 const void* face_vertices_z, const void* face_vertices_image,
+                                 const void* face_bboxes, const void* pixel_coords,
+                                 const void* render_ranges, float eps, int64_t* face_idx,
+                                 void* pixel_depths, void* w0, void* w1, void* ws,
+                                 int64_t ws_bytes, void* stream) {
+  if (dtype == DIBR_F32)
+    return deftet_forward<float>(true, batch, num_faces, num_points, knum, 0, face_vertices_z,
+                                 face_vertices_image, face_bboxes, nullptr, pixel_coords,
+                                 render_ranges, eps, face_idx, pixel_depths, w0, w1, ws, ws_bytes,
+                                 (cudaStream_t)stream);
+  if (dtype == DIBR_F64)
+    return deftet_forward<double>(true, batch, num_faces, num_points, knum, 0, face_vertices_z,
+                                  face_vertices_image, face_bboxes, nullptr, pixel_coords,
+                                  render_ranges, eps, face_idx, pixel_depths, w0, w1, ws,
+                                  ws_bytes, (cudaStream_t)stream);
+  return fail(DIBR_E_INVALID, "dtype must be DIBR_F32 or DIBR_F64");
+}
+
+DIBR_API int dibr_deftet_bwd(int dtype, int batch, int num_faces, int num_points, int knum,
+                             int feat_dim, const void* grad_interpolated_features,
+                             const int64_t* face_idx, const void* weights,
+                             const void* face_vertices_image, const void* face_features,
+                             float eps, void* grad_face_vertices_image,
+                             void* grad_face_features, void* stream) {
+  if (dtype == DIBR_F32)
+    return deftet_backward<float>(batch, num_faces, num_points, knum, feat_dim,
+                                  grad_interpolated_features, face_idx, weights,
+                                  face_vertices_image, face_features, eps,
+                                  grad_face_vertices_image, grad_face_features,
+                                  (cudaStream_t)stream);
+  if (dtype == DIBR_F64)
+    return deftet_backward<double>(batch, num_faces, num_points, knum, feat_dim,
+                                   grad_interpolated_features, face_idx, weights,
+                                   face_vertices_image, face_features, eps,
+                                   grad_face_vertices_image, grad_face_features,
+                                   (cudaStream_t)stream);
+  return fail(DIBR_E_INVALID, "dtype must be DIBR_F32 or DIBR_F64");
+}
+
+}  // extern "C"

@@ -2,4 +2,5 @@
 from .rasterization import *
 from .dibr import *
 from .utils import *
-from . import rasterization, dibr, utils
+from .deftet import *
+from . import rasterization, dibr, utils, deftet

@@ -1,12 +1,14 @@
 """TEST INFRASTRUCTURE ONLY -- builds oracle/_ref/kaolin_ref_C.so.
 
-Compiles the reference's own four DIB-R source files, unmodified and from where
+Compiles the reference's own DIB-R source files, unmodified and from where
 they lie under /root/reference (nothing is copied into this repo):
 
     kaolin/csrc/render/mesh/rasterization.cpp
     kaolin/csrc/render/mesh/rasterization_cuda.cu
     kaolin/csrc/render/mesh/dibr_soft_mask.cpp
     kaolin/csrc/render/mesh/dibr_soft_mask_cuda.cu
+    kaolin/csrc/render/mesh/deftet.cpp          (next row 8(f).3)
+    kaolin/csrc/render/mesh/deftet_cuda.cu
 
 with the reference's own nvcc flags (setup.py:207-211: -O3 -DWITH_CUDA, no
 fast-math, default -fmad=true) for sm_100a, plus oracle/ref_binding.cpp, into a
@@ -27,11 +29,16 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 REF = os.environ.get("KAOLIN_REFERENCE", "/root/reference")
 OUT = os.path.join(HERE, "_ref")
 SO = os.path.join(OUT, "kaolin_ref_C.so")
+# keep the kernels' objects (cuobjdump -sass shows the contraction nvcc chose)
+KEEP_OBJS = bool(os.environ.get("KAOLIN_REF_KEEP_OBJS"))
 SRC = [
     "kaolin/csrc/render/mesh/rasterization.cpp",
     "kaolin/csrc/render/mesh/dibr_soft_mask.cpp",
     "kaolin/csrc/render/mesh/rasterization_cuda.cu",
     "kaolin/csrc/render/mesh/dibr_soft_mask_cuda.cu",
+    # the sibling op on the same math
+    "kaolin/csrc/render/mesh/deftet.cpp",
+    "kaolin/csrc/render/mesh/deftet_cuda.cu",
 ]
 
 
@@ -82,7 +89,8 @@ def build(force=False):
         "-lc10", "-ltorch_cpu", "-ltorch", "-ltorch_python", "-lc10_cuda",
         "-ltorch_cuda", "-lcudart"])
     for o in objs:
-        os.remove(o)
+        if not (KEEP_OBJS and o.endswith(".cu.o")):
+            os.remove(o)
     return SO
 
 

@@ -25,6 +25,8 @@ What it writes (all small, compressed .npz):
   test_rasterization.py:50-134, forward (face_idx, features) and backward (grads of
   image coordinates and features for a fixed cotangent) -- the same function the
   reference's tests use as ground truth for rasterize (test_rasterization.py:148-152,216-236).
+* deftet_naive.npz -- the same function as the reference's deftet tests use it
+  (test_deftet.py:340-437), see deftet_golden().
 """
 import glob
 import math
@@ -130,6 +132,49 @@ def naive_golden():
     np.savez_compressed(os.path.join(HERE, "rasterize_naive.npz"), **out)
 
 
+def deftet_golden():
+    """deftet_naive.npz: the reference's pure-torch _naive_deftet_sparse_render run as the
+    reference's own test does (test_deftet.py:340-437): model.obj, the three look-at cameras,
+    uniform random sample points in [-1, 1]^2, ranges up to the centre / the far end,
+    knum 20 (never exceeded: beyond knum hits the naive function keeps the NEAREST while the
+    CUDA op keeps the FIRST in face order -- the reference's tests never compare them there),
+    forward and backward."""
+    naive = load_naive_oracle()
+    out = {}
+    g = torch.Generator().manual_seed(5)
+    P = 257
+    for dtype in (torch.float32, torch.float64):
+        geo = fixture_geometry(os.path.join(HERE, "model_obj.npz"), batch_size=3, dtype=dtype)
+        z, img, uvs = geo["face_vertices_z"], geo["face_vertices_image"], geo["face_uvs"]
+        vc = geo["vertices_camera"]
+        B = z.shape[0]
+        pix = torch.rand((B, P, 2), generator=g, dtype=dtype) * 2. - 1.
+        tag = str(dtype)[-7:]
+        out[tag + "_pixel_coords"] = pix.numpy()
+        min_z = vc[:, :, -1].min(dim=1)[0]
+        max_z = vc[:, :, -1].max(dim=1)[0]
+        for centre in (False, True):
+            lo = (min_z + max_z) / 2. if centre else min_z
+            rr = torch.nn.functional.pad(lo.unsqueeze(-1), (0, 1), value=0.)
+            rr = rr.unsqueeze(1).repeat(1, P, 1)
+            for knum in (20,):
+                img2 = img.detach().clone().requires_grad_(True)
+                f2 = uvs.detach().clone().requires_grad_(True)
+                feat, idx = naive(pix, rr, z, img2, f2, knum)
+                grad_out = torch.rand(feat.shape, generator=g, dtype=dtype)
+                feat.backward(grad_out)
+                key = "%s_centre%d_k%d" % (tag, centre, knum)
+                out[key + "_ranges"] = rr.numpy()
+                out[key + "_idx"] = idx.numpy().astype(np.int16)
+                out[key + "_feat"] = feat.detach().numpy()
+                out[key + "_grad_out"] = grad_out.numpy()
+                out[key + "_grad_img"] = img2.grad.numpy()
+                out[key + "_grad_feat"] = f2.grad.numpy()
+                print(key, "hits:", int((idx >= 0).sum()),
+                      "max per point:", int((idx >= 0).sum(-1).max()))
+    np.savez_compressed(os.path.join(HERE, "deftet_naive.npz"), **out)
+
+
 def load_ref_functions(relpath, names, globs):
     """exec the named top-level functions of a reference source file (pure torch code whose
     package cannot be imported without the compiled kaolin._C) in `globs`."""
@@ -206,11 +251,15 @@ if __name__ == "__main__":
     if sys.argv[1:] == ["prepare_vertices"]:
         prepare_vertices_golden()
         sys.exit(0)
+    if sys.argv[1:] == ["deftet"]:
+        deftet_golden()
+        sys.exit(0)
     pack_obj(os.path.join(REF, "tests/samples/model.obj"), "model_obj.npz")
     pack_obj(os.path.join(REF, "sample_data/meshes/pizza.obj"), "pizza_obj.npz")
     pack_dibr("simple")
     pack_dibr("sphere")
     naive_golden()
     prepare_vertices_golden()
+    deftet_golden()
     for f in sorted(glob.glob(os.path.join(HERE, "*.npz"))):
         print(os.path.basename(f), os.path.getsize(f) // 1024, "KiB")
