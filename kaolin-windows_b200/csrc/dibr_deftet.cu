@@ -9,7 +9,7 @@
 // [range_min, range_max) are kept (deftet_cuda.cu:120-168), then ordered by depth,
 // nearest (largest z) first (deftet.py:303-306), w2 := valid - (w0 + w1) (:307) and the
 // features interpolated (:308-317).  Arithmetic of the test in the shapes nvcc contracts
-// the reference into for sm_100a (read from cuobjdump -sass of oracle/_ref):
+// the reference into for sm_100a (read from cuobjdump -sass of the reference build):
 //   _w0 = fma(bex, cey, -fl(bey * cex)), _w1 = fma(cex, aey, -fl(cey * aex)),
 //   _w2 = fma(aex, bey, -fl(aey * bex)), norm = (_w0 + _w1) + _w2,
 //   den = norm + copysign(eps_float, norm), w_k = _w_k / den (IEEE),
