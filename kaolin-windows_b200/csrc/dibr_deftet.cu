@@ -16,10 +16,14 @@
 //   depth = fma(w2, cz, fma(w0, az, fl(w1 * bz))).
 //
 // B200 design.  The reference tests every face against every point (one warp per point,
-// F / 32 steps).  Here the faces of a view are dealt into a uniform grid laid over the
-// bounding box of the view's sample points, cell size ~1.5 mean face extent (measured on
-// the device, no host round trip); faces spanning more than kWideCells cells go to one
-// per-view "wide" list instead.  A point only tests its cell's list plus the wide list.
+// F / 32 steps).  Here the faces of a view are dealt into a uniform G x G grid laid over the
+// bounding box of the view's sample points; faces spanning more than kWideCells cells go to
+// one per-view "wide" list instead.  A point only tests its cell's list plus the wide list.
+// G is chosen ON THE DEVICE (no host round trip): one pass counts, for every G = 1, 2, 4 ..
+// 512 at once, the list entries E_G and wide faces W_G the mesh would produce, and a
+// one-thread-per-view kernel takes the G minimising
+//     E_G * (c_build + c_test * P / G^2) + c_test * P * W_G
+// (E_G / G^2 is exactly the expected list length under a uniformly placed sample).
 // Lists are filled with atomics (unordered): the kept set is order independent (all hits,
 // or the knum smallest face ids among them) and so is the final order (depth descending,
 // ties by face id = the reference's insertion order under a stable sort).
@@ -35,8 +39,9 @@ int fail(int code, const char* fmt, ...);
 
 namespace {
 
-constexpr int kGridMax = 512;     // cells per axis at most
-constexpr int kWideCells = 12;    // a face spanning more cells goes to the wide list
+constexpr int kLevels = 10;       // G = 1 << level, level 0..9
+constexpr int kWideCells = 16;    // a face spanning more cells goes to the wide list
+constexpr float kCostBuild = 30.f, kCostTest = 40.f;   // thread-instructions per entry / test
 
 // ------------------------------------------------------------------ exact arithmetic
 __device__ __forceinline__ float mul_rn(float a, float b) { return __fmul_rn(a, b); }
@@ -53,6 +58,13 @@ __device__ __forceinline__ float to_f(float a) { return a; }
 __device__ __forceinline__ float to_f(double a) { return __double2float_rn(a); }  // monotone
 __device__ __forceinline__ bool sign_of(float a) { return (__float_as_uint(a) >> 31) != 0; }
 __device__ __forceinline__ bool sign_of(double a) { return (__double2hiint(a) >> 31) != 0; }
+// min / max that drop a NaN operand: a box computed with them is a superset of the
+// reference's torch.min / torch.max box, and a face with a NaN coordinate fails the
+// edge test on its own (every weight becomes NaN), so results do not change.
+__device__ __forceinline__ float min3(float a, float b, float c) { return fminf(fminf(a, b), c); }
+__device__ __forceinline__ float max3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }
+__device__ __forceinline__ double min3(double a, double b, double c) { return fmin(fmin(a, b), c); }
+__device__ __forceinline__ double max3(double a, double b, double c) { return fmax(fmax(a, b), c); }
 
 template <typename T> struct Vec2;
 template <> struct Vec2<float> { typedef float2 type; };
@@ -67,51 +79,45 @@ __device__ __forceinline__ float dec_f(unsigned e) {
   return __uint_as_float((e >> 31) ? (e & 0x7fffffffu) : ~e);
 }
 
-// per-view statistics the grid is derived from (zero-initialised by a memset)
+// per-view statistics (zero-initialised by a memset)
 struct ViewStats {
   unsigned nlo_x, nlo_y;          // ~enc(min sample coordinate)  (atomicMax)
   unsigned hi_x, hi_y;            // enc(max sample coordinate)   (atomicMax); 0 = no sample
-  unsigned long long extent_sum;  // sum over faces of (clipped extent / domain) * 65536
-  unsigned faces;                 // faces meeting the samples' bounding box
-  unsigned wide;                  // entries of the wide list
+  unsigned wide;                  // entries of the wide list (fill cursor)
+  unsigned pad[3];
+  unsigned long long entries[kLevels];  // list entries a G = 1 << l grid would hold
+  unsigned wides[kLevels];              // faces that grid would send to the wide list
+  unsigned pad2[2];
 };
 
+// the chosen grid of a view (written by deftet_choose_kernel, read by everything after)
 struct CellGrid {
   float lox, loy, hix, hiy, invx, invy;
-  int gx, gy;
-  bool empty;
+  int g;          // cells per axis
+  int empty;      // no sample point (or none that can be hit)
 };
 
-// Every thread derives the same grid from the same statistics (pure function, ~30 instr.).
-__device__ __forceinline__ CellGrid make_grid(const ViewStats& s, int cells_cap) {
+// sample domain of a view and 1 / extent (0 where the extent is 0 or not finite)
+__device__ __forceinline__ CellGrid domain_of(const ViewStats& s) {
   CellGrid g;
   g.empty = (s.hi_x == 0u);
-  g.gx = g.gy = 1;
+  g.g = 1;
   g.invx = g.invy = 0.f;
   g.lox = g.loy = g.hix = g.hiy = 0.f;
   if (g.empty) return g;
   g.lox = dec_f(~s.nlo_x); g.loy = dec_f(~s.nlo_y);
   g.hix = dec_f(s.hi_x); g.hiy = dec_f(s.hi_y);
   const float dx = g.hix - g.lox, dy = g.hiy - g.loy;
-  const float dmax = fmaxf(dx, dy);
-  if (!(dmax > 0.f) || !(dmax < 3.0e38f) || s.faces == 0u) return g;
-  // mean clipped face extent as a fraction of the domain, times 1.5
-  float frac = 1.5f * ((float)s.extent_sum / (float)s.faces) * (1.f / 65536.f);
-  frac = fmaxf(frac, 1.f / (float)kGridMax);
-  int gx = (int)(dx / dmax / frac) + 1, gy = (int)(dy / dmax / frac) + 1;
-  gx = min(max(gx, 1), kGridMax);
-  gy = min(max(gy, 1), kGridMax);
-  while ((long long)gx * gy > cells_cap) { gx = (gx + 1) >> 1; gy = (gy + 1) >> 1; }
-  g.gx = gx; g.gy = gy;
-  g.invx = dx > 0.f ? (float)gx / dx : 0.f;
-  g.invy = dy > 0.f ? (float)gy / dy : 0.f;
-  if (!(g.invx < 3.0e38f)) { g.invx = 0.f; g.gx = 1; }
-  if (!(g.invy < 3.0e38f)) { g.invy = 0.f; g.gy = 1; }
+  g.invx = (dx > 0.f && dx < 3.0e38f) ? 1.f / dx : 0.f;
+  g.invy = (dy > 0.f && dy < 3.0e38f) ? 1.f / dy : 0.f;
+  if (!(g.invx < 1.0e30f)) g.invx = 0.f;
+  if (!(g.invy < 1.0e30f)) g.invy = 0.f;
   return g;
 }
 
 // monotone non-decreasing in v (sub, mul by >= 0, truncation and clamp all are), so a
 // point inside [lo, hi) of a box falls in a cell between cell(lo) and cell(hi).
+// inv = (1 / extent) * G with G a power of two: exact, the same value wherever formed.
 __device__ __forceinline__ int cell_of(float v, float lo, float inv, int n) {
   const float t = (v - lo) * inv;
   return (t >= 0.f) ? ((t < (float)n) ? (int)t : n - 1) : 0;
@@ -132,6 +138,7 @@ struct DeftetArgs {
   T* out_w0;           // (B, P, K)           raw mode
   T* out_w1;           // (B, P, K)           raw mode
   ViewStats* stats;    // [B]
+  CellGrid* grids;     // [B]
   int* cell_start;     // [B][cells_cap]
   int* cell_count;     // [B][cells_cap]
   int* wide;           // [B][F]
@@ -141,12 +148,6 @@ struct DeftetArgs {
 };
 
 template <typename T>
-__device__ __forceinline__ bool any_nan6(const T (&v)[6]) {
-  return v[0] != v[0] || v[1] != v[1] || v[2] != v[2] || v[3] != v[3] || v[4] != v[4] ||
-         v[5] != v[5];
-}
-
-template <typename T>
 __device__ __forceinline__ void load_img6(const T* img, long long bf, T (&v)[6]) {
   typedef typename Vec2<T>::type V2;
   const V2* p = reinterpret_cast<const V2*>(img) + bf * 3;
@@ -154,43 +155,25 @@ __device__ __forceinline__ void load_img6(const T* img, long long bf, T (&v)[6])
   v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y;
 }
 
-// box of a face as torch.min / torch.max over the three vertices give it (deftet.py:290-292;
-// a NaN coordinate makes the box NaN, i.e. the face can never be hit) or the caller's box
+// float image of a face's box for the binning; false if it cannot contain any sample
 template <typename T>
-__device__ __forceinline__ bool face_box(const DeftetArgs<T>& a, long long bf, const T (&v)[6],
-                                         T& xmin, T& ymin, T& xmax, T& ymax) {
+__device__ __forceinline__ bool face_box_f(const DeftetArgs<T>& a, const CellGrid& g, int b,
+                                           int f, float& fx0, float& fy0, float& fx1,
+                                           float& fy1) {
+  const long long bf = (long long)b * a.F + f;
   if (a.bbox) {
     const T* q = a.bbox + bf * 4;
-    xmin = __ldg(q); ymin = __ldg(q + 1); xmax = __ldg(q + 2); ymax = __ldg(q + 3);
-    return !(xmin != xmin || ymin != ymin || xmax != xmax || ymax != ymax);
+    fx0 = to_f(__ldg(q)); fy0 = to_f(__ldg(q + 1));
+    fx1 = to_f(__ldg(q + 2)); fy1 = to_f(__ldg(q + 3));
+  } else {
+    T v[6];
+    load_img6(a.img, bf, v);
+    fx0 = to_f(min3(v[0], v[2], v[4])); fx1 = to_f(max3(v[0], v[2], v[4]));
+    fy0 = to_f(min3(v[1], v[3], v[5])); fy1 = to_f(max3(v[1], v[3], v[5]));
   }
-  if (any_nan6(v)) return false;
-  xmin = v[0] < v[2] ? v[0] : v[2]; xmin = xmin < v[4] ? xmin : v[4];
-  xmax = v[0] > v[2] ? v[0] : v[2]; xmax = xmax > v[4] ? xmax : v[4];
-  ymin = v[1] < v[3] ? v[1] : v[3]; ymin = ymin < v[5] ? ymin : v[5];
-  ymax = v[1] > v[3] ? v[1] : v[3]; ymax = ymax > v[5] ? ymax : v[5];
-  return true;
-}
-
-// cell rectangle of a face; false if it cannot contain any sample of the view
-template <typename T>
-__device__ __forceinline__ bool face_cells(const DeftetArgs<T>& a, const CellGrid& g, int b,
-                                           int f, int& cx0, int& cy0, int& cx1, int& cy1,
-                                           float& ext) {
-  if (g.empty) return false;
-  const long long bf = (long long)b * a.F + f;
-  T v[6];
-  if (!a.bbox) load_img6(a.img, bf, v);
-  T xmin, ymin, xmax, ymax;
-  if (!face_box(a, bf, v, xmin, ymin, xmax, ymax)) return false;
-  const float fx0 = to_f(xmin), fy0 = to_f(ymin), fx1 = to_f(xmax), fy1 = to_f(ymax);
   // a hit needs xmin <= x < xmax with lox <= x <= hix (to_f is monotone, so the float
-  // images keep the non-strict forms of these inequalities)
-  if (!(fx1 >= g.lox && fx0 <= g.hix && fy1 >= g.loy && fy0 <= g.hiy)) return false;
-  cx0 = cell_of(fx0, g.lox, g.invx, g.gx); cx1 = cell_of(fx1, g.lox, g.invx, g.gx);
-  cy0 = cell_of(fy0, g.loy, g.invy, g.gy); cy1 = cell_of(fy1, g.loy, g.invy, g.gy);
-  ext = fmaxf(fminf(fx1, g.hix) - fmaxf(fx0, g.lox), fminf(fy1, g.hiy) - fmaxf(fy0, g.loy));
-  return true;
+  // images keep the non-strict forms of these inequalities); NaN fails
+  return fx1 >= g.lox && fx0 <= g.hix && fy1 >= g.loy && fy0 <= g.hiy;
 }
 
 // ------------------------------------------------------------------ grid construction
@@ -214,29 +197,69 @@ __global__ void __launch_bounds__(256) deftet_bounds_kernel(const DeftetArgs<T> 
   }
 }
 
+// what every grid resolution would cost: entries and wide faces per level
 template <typename T>
-__global__ void __launch_bounds__(256) deftet_extent_kernel(const DeftetArgs<T> a) {
+__global__ void __launch_bounds__(256) deftet_levels_kernel(const DeftetArgs<T> a) {
   const int b = blockIdx.y;
-  ViewStats s = a.stats[b];
-  s.faces = 0; s.extent_sum = 0;   // this kernel writes them; the grid below ignores them
-  CellGrid g = make_grid(s, 1);
-  const float dmax = fmaxf(g.hix - g.lox, g.hiy - g.loy);
-  unsigned cnt = 0, sum = 0;
+  const CellGrid g = domain_of(a.stats[b]);
+  if (g.empty) return;
+  unsigned ent[kLevels], wid[kLevels];
+#pragma unroll
+  for (int l = 0; l < kLevels; l++) ent[l] = wid[l] = 0;
   for (int f = blockIdx.x * blockDim.x + threadIdx.x; f < a.F; f += gridDim.x * blockDim.x) {
-    int cx0, cy0, cx1, cy1; float ext;
-    if (!face_cells(a, g, b, f, cx0, cy0, cx1, cy1, ext)) continue;
-    cnt++;
-    float q = dmax > 0.f ? ext / dmax : 0.f;
-    q = fminf(fmaxf(q, 0.f), 1.f);             // NaN -> 0
-    sum += (unsigned)(q * 65536.f);
+    float fx0, fy0, fx1, fy1;
+    if (!face_box_f(a, g, b, f, fx0, fy0, fx1, fy1)) continue;
+#pragma unroll
+    for (int l = 0; l < kLevels; l++) {
+      const int G = 1 << l;
+      const float ix = g.invx * (float)G, iy = g.invy * (float)G;
+      const int nx = cell_of(fx1, g.lox, ix, G) - cell_of(fx0, g.lox, ix, G) + 1;
+      const int ny = cell_of(fy1, g.loy, iy, G) - cell_of(fy0, g.loy, iy, G) + 1;
+      const int n = nx * ny;
+      if (n > kWideCells) wid[l]++; else ent[l] += n;
+    }
   }
-  cnt = __reduce_add_sync(DIBR_FULL_MASK, cnt);
-  // a warp's 32 summands of <= 65536 fit 32 bits
-  sum = __reduce_add_sync(DIBR_FULL_MASK, sum);
-  if ((threadIdx.x & 31) == 0 && cnt) {
-    atomicAdd(&a.stats[b].faces, cnt);
-    atomicAdd(&a.stats[b].extent_sum, (unsigned long long)sum);
+  // warp sums -> shared atomics -> one global atomic per level and CTA
+  __shared__ unsigned sh[2 * kLevels];
+  if (threadIdx.x < 2 * kLevels) sh[threadIdx.x] = 0;
+  __syncthreads();
+#pragma unroll
+  for (int l = 0; l < kLevels; l++) {
+    const unsigned e = __reduce_add_sync(DIBR_FULL_MASK, ent[l]);
+    const unsigned w = __reduce_add_sync(DIBR_FULL_MASK, wid[l]);
+    if ((threadIdx.x & 31) == 0) {
+      if (e) atomicAdd(&sh[l], e);
+      if (w) atomicAdd(&sh[kLevels + l], w);
+    }
   }
+  __syncthreads();
+  if (threadIdx.x < kLevels) {
+    if (sh[threadIdx.x]) atomicAdd(&a.stats[b].entries[threadIdx.x], (unsigned long long)sh[threadIdx.x]);
+  } else if (threadIdx.x < 2 * kLevels) {
+    if (sh[threadIdx.x]) atomicAdd(&a.stats[b].wides[threadIdx.x - kLevels], sh[threadIdx.x]);
+  }
+}
+
+// one thread per view: the cheapest level (see the header), grid parameters stored
+__global__ void deftet_choose_kernel(const ViewStats* stats, CellGrid* grids, int B, int P,
+                                     int cells_cap) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const ViewStats s = stats[b];
+  CellGrid g = domain_of(s);
+  int best = 0;
+  float best_cost = 3.4e38f;
+  for (int l = 0; l < kLevels; l++) {
+    const long long cells = 1ll << (2 * l);
+    if (cells > cells_cap) break;
+    const float cost = (float)s.entries[l] * (kCostBuild + kCostTest * (float)P / (float)cells) +
+                       kCostTest * (float)P * (float)s.wides[l];
+    if (cost < best_cost) { best_cost = cost; best = l; }
+  }
+  g.g = 1 << best;
+  g.invx *= (float)g.g;
+  g.invy *= (float)g.g;
+  grids[b] = g;
 }
 
 // FILL = false: count entries per cell, wide faces go straight to the wide list;
@@ -244,20 +267,23 @@ __global__ void __launch_bounds__(256) deftet_extent_kernel(const DeftetArgs<T> 
 template <typename T, bool FILL>
 __global__ void __launch_bounds__(256) deftet_bin_kernel(const DeftetArgs<T> a) {
   const int b = blockIdx.y;
-  const CellGrid g = make_grid(a.stats[b], a.cells_cap);
+  const CellGrid g = a.grids[b];
+  if (g.empty) return;
   int* cnt = a.cell_count + (long long)b * a.cells_cap;
   const int* start = a.cell_start + (long long)b * a.cells_cap;
   int* list = a.list + (long long)b * kWideCells * a.F;
   for (int f = blockIdx.x * blockDim.x + threadIdx.x; f < a.F; f += gridDim.x * blockDim.x) {
-    int cx0, cy0, cx1, cy1; float ext;
-    if (!face_cells(a, g, b, f, cx0, cy0, cx1, cy1, ext)) continue;
+    float fx0, fy0, fx1, fy1;
+    if (!face_box_f(a, g, b, f, fx0, fy0, fx1, fy1)) continue;
+    const int cx0 = cell_of(fx0, g.lox, g.invx, g.g), cx1 = cell_of(fx1, g.lox, g.invx, g.g);
+    const int cy0 = cell_of(fy0, g.loy, g.invy, g.g), cy1 = cell_of(fy1, g.loy, g.invy, g.g);
     if ((cx1 - cx0 + 1) * (cy1 - cy0 + 1) > kWideCells) {
       if (!FILL) a.wide[(long long)b * a.F + atomicAdd(&a.stats[b].wide, 1u)] = f;
       continue;
     }
     for (int cy = cy0; cy <= cy1; cy++)
       for (int cx = cx0; cx <= cx1; cx++) {
-        const int c = cy * g.gx + cx;
+        const int c = cy * g.g + cx;
         if (FILL) list[start[c] + atomicAdd(cnt + c, 1)] = f;
         else atomicAdd(cnt + c, 1);
       }
@@ -265,13 +291,12 @@ __global__ void __launch_bounds__(256) deftet_bin_kernel(const DeftetArgs<T> a) 
 }
 
 // one CTA per view: exclusive scan of the cell counts, counts reset for the fill's cursors
-__global__ void __launch_bounds__(1024) deftet_scan_kernel(const ViewStats* stats, int* cell_start,
+__global__ void __launch_bounds__(1024) deftet_scan_kernel(const CellGrid* grids, int* cell_start,
                                                            int* cell_count, int cells_cap) {
   __shared__ int warp_sum[32];
   __shared__ int carry;
   const int b = blockIdx.x;
-  const CellGrid g = make_grid(stats[b], cells_cap);
-  const int n = g.gx * g.gy;
+  const int n = grids[b].g * grids[b].g;
   int* cnt = cell_count + (long long)b * cells_cap;
   int* start = cell_start + (long long)b * cells_cap;
   if (threadIdx.x == 0) carry = 0;
@@ -328,14 +353,21 @@ __device__ __forceinline__ HitBuf<T> carve(unsigned char* base, int warp, int K,
 
 // the reference's test of one face against one sample (deftet_cuda.cu:120-163)
 template <typename T>
-__device__ __forceinline__ bool deftet_test(const DeftetArgs<T>& a, int b, int f, T x0, T y0,
+__device__ __forceinline__ bool deftet_test(const DeftetArgs<T>& a, long long bf, T x0, T y0,
                                             T dmin, T dmax, T eps_t, T& w0, T& w1, T& depth) {
-  const long long bf = (long long)b * a.F + f;
   T v[6];
   load_img6(a.img, bf, v);
-  T xmin, ymin, xmax, ymax;
-  if (!face_box(a, bf, v, xmin, ymin, xmax, ymax)) return false;
-  if (!(x0 >= xmin && x0 < xmax && y0 >= ymin && y0 < ymax)) return false;
+  if (a.bbox) {
+    const T* q = a.bbox + bf * 4;
+    if (!(x0 >= __ldg(q) && x0 < __ldg(q + 2) && y0 >= __ldg(q + 1) && y0 < __ldg(q + 3)))
+      return false;
+  } else {
+    // min3 / max3 drop NaN where torch.min / torch.max keep it: a face with a NaN
+    // coordinate that slips through here gets NaN weights below and is rejected there
+    if (!(x0 >= min3(v[0], v[2], v[4]) && x0 < max3(v[0], v[2], v[4]) &&
+          y0 >= min3(v[1], v[3], v[5]) && y0 < max3(v[1], v[3], v[5])))
+      return false;
+  }
   const T aex = sub_rn(v[0], x0), aey = sub_rn(v[1], y0);
   const T bex = sub_rn(v[2], x0), bey = sub_rn(v[3], y0);
   const T cex = sub_rn(v[4], x0), cey = sub_rn(v[5], y0);
@@ -365,22 +397,24 @@ __device__ __forceinline__ bool slot_before(const HitBuf<T>& h, int i, int j) {
   return di > dj || (di == dj && h.face[i] < h.face[j]);
 }
 
+// one warp per sample point; blockIdx.y = view
 template <typename T, bool RAW>
 __global__ void __launch_bounds__(256) deftet_render_kernel(const DeftetArgs<T> a) {
   typedef typename Vec2<T>::type V2;
   extern __shared__ __align__(16) unsigned char smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const long long gp = (long long)blockIdx.x * (blockDim.x >> 5) + warp;
-  if (gp >= (long long)a.B * a.P) return;
-  const int b = (int)(gp / a.P);
+  const int p = blockIdx.x * (blockDim.x >> 5) + warp;
+  if (p >= a.P) return;
+  const int b = blockIdx.y;
+  const long long gp = (long long)b * a.P + p;
   const int K = a.K;
   HitBuf<T> h = carve<T>(smem, warp, K, a.n2);
   const V2 c = __ldg(reinterpret_cast<const V2*>(a.pix) + gp);
   const V2 r = __ldg(reinterpret_cast<const V2*>(a.range) + gp);
   const T x0 = c.x, y0 = c.y, dmin = r.x, dmax = r.y;
   const T eps_t = (T)a.eps;
-  const ViewStats st = a.stats[b];
-  const CellGrid g = make_grid(st, a.cells_cap);
+  const CellGrid g = a.grids[b];
+  const long long face0 = (long long)b * a.F;
 
   int n = 0;            // hits held (warp uniform)
   int maxf = -1, maxs = -1;   // largest held face id and its slot, valid once the buffer is full
@@ -389,13 +423,13 @@ __global__ void __launch_bounds__(256) deftet_render_kernel(const DeftetArgs<T> 
     const int* lst;
     int len;
     if (pass == 0) {
-      const int cell = cell_of(to_f(y0), g.loy, g.invy, g.gy) * g.gx +
-                       cell_of(to_f(x0), g.lox, g.invx, g.gx);
-      lst = a.list + (long long)b * kWideCells * a.F + a.cell_start[(long long)b * a.cells_cap + cell];
+      const int cell = cell_of(to_f(y0), g.loy, g.invy, g.g) * g.g +
+                       cell_of(to_f(x0), g.lox, g.invx, g.g);
+      lst = a.list + face0 * kWideCells + a.cell_start[(long long)b * a.cells_cap + cell];
       len = a.cell_count[(long long)b * a.cells_cap + cell];
     } else {
-      lst = a.wide + (long long)b * a.F;
-      len = (int)st.wide;
+      lst = a.wide + face0;
+      len = (int)a.stats[b].wide;
     }
     for (int base = 0; base < len; base += 32) {
       const int i = base + lane;
@@ -404,7 +438,7 @@ __global__ void __launch_bounds__(256) deftet_render_kernel(const DeftetArgs<T> 
       bool hit = false;
       if (i < len) {
         f = __ldg(lst + i);
-        hit = deftet_test(a, b, f, x0, y0, dmin, dmax, eps_t, w0, w1, depth);
+        hit = deftet_test(a, face0 + f, x0, y0, dmin, dmax, eps_t, w0, w1, depth);
       }
       unsigned m = __ballot_sync(DIBR_FULL_MASK, hit);
       if (m == 0u) continue;
@@ -431,7 +465,6 @@ __global__ void __launch_bounds__(256) deftet_render_kernel(const DeftetArgs<T> 
           s = n++;
           maxs = -1;
         } else {
-          if (K == 0) continue;
           if (maxs < 0) {
             __syncwarp();
             int mf = -1, ms = -1;
@@ -454,62 +487,59 @@ __global__ void __launch_bounds__(256) deftet_render_kernel(const DeftetArgs<T> 
   __syncwarp();
 
   // order the held hits: bitonic network over slot numbers (padding = -1 goes last)
-  int n2 = 1;
-  while (n2 < n) n2 <<= 1;
-  for (int k = lane; k < n2; k += 32) h.perm[k] = k < n ? k : -1;
-  __syncwarp();
-  for (int k = 2; k <= n2; k <<= 1)
-    for (int j = k >> 1; j > 0; j >>= 1) {
-      for (int t = lane; t < (n2 >> 1); t += 32) {
-        const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
-        const int l = i | j;
-        const int pi = h.perm[i], pl = h.perm[l];
-        const bool up = (i & k) == 0;
-        if (up ? slot_before<T, RAW>(h, pl, pi) : slot_before<T, RAW>(h, pi, pl)) {
-          h.perm[i] = pl; h.perm[l] = pi;
+  if (n > 1) {
+    int n2 = 2;
+    while (n2 < n) n2 <<= 1;
+    for (int k = lane; k < n2; k += 32) h.perm[k] = k < n ? k : -1;
+    __syncwarp();
+    for (int k = 2; k <= n2; k <<= 1)
+      for (int j = k >> 1; j > 0; j >>= 1) {
+        for (int t = lane; t < (n2 >> 1); t += 32) {
+          const int i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+          const int l = i | j;
+          const int pi = h.perm[i], pl = h.perm[l];
+          const bool up = (i & k) == 0;
+          if (up ? slot_before<T, RAW>(h, pl, pi) : slot_before<T, RAW>(h, pi, pl)) {
+            h.perm[i] = pl; h.perm[l] = pi;
+          }
         }
+        __syncwarp();
       }
-      __syncwarp();
-    }
+  }
 
-  // write every slot of the sample (fills included: the library writes all outputs)
+  // write every slot of the sample (fills included: the library writes all outputs);
+  // one slot per lane
   const long long row = gp * K;
-  for (int k = lane; k < K; k += 32) {
-    const int s = k < n ? h.perm[k] : -1;
-    a.out_idx[row + k] = s >= 0 ? (int64_t)h.face[s] : (int64_t)-1;
-    if (RAW) {
-      a.out_depth[row + k] = s >= 0 ? h.depth[s] : -(T)INFINITY;
-      a.out_w0[row + k] = s >= 0 ? h.w0[s] : (T)0;
-      a.out_w1[row + k] = s >= 0 ? h.w1[s] : (T)0;
-    }
-  }
-  if constexpr (!RAW) {
-  for (int j = lane; j < 3 * K; j += 32) {
-    const int k = j / 3, comp = j - 3 * k;
-    const int s = k < n ? h.perm[k] : -1;
-    T v = (T)0;
-    if (s >= 0) {
-      const T w0 = h.w0[s], w1 = h.w1[s];
-      // deftet.py:307  w2 = (face_idx != -1) - (w0 + w1)
-      v = comp == 0 ? w0 : (comp == 1 ? w1 : sub_rn((T)1, add_rn(w0, w1)));
-    }
-    a.out_w[row * 3 + j] = v;
-  }
   const int D = a.D;
-  for (int j = lane; j < K * D; j += 32) {
-    const int k = j / D, d = j - k * D;
-    const int s = k < n ? h.perm[k] : -1;
-    T v = (T)0;
-    if (s >= 0) {
-      const T w0 = h.w0[s], w1 = h.w1[s], w2 = sub_rn((T)1, add_rn(w0, w1));
-      const T* fp = a.feat + ((long long)b * a.F + h.face[s]) * 3 * D + d;
-      // deftet.py:315-317  sum over the three vertices of weight * feature
-      v = add_rn(add_rn(mul_rn(w0, __ldg(fp)), mul_rn(w1, __ldg(fp + D))),
-                 mul_rn(w2, __ldg(fp + 2 * D)));
+  for (int k = lane; k < K; k += 32) {
+    const int s = k < n ? (n > 1 ? h.perm[k] : 0) : -1;
+    const long long o = row + k;
+    if (s < 0) {
+      a.out_idx[o] = -1;
+      if (RAW) {
+        a.out_depth[o] = -(T)INFINITY; a.out_w0[o] = (T)0; a.out_w1[o] = (T)0;
+      } else {
+        a.out_w[o * 3] = (T)0; a.out_w[o * 3 + 1] = (T)0; a.out_w[o * 3 + 2] = (T)0;
+        for (int d = 0; d < D; d++) a.out_feat[o * D + d] = (T)0;
+      }
+      continue;
     }
-    a.out_feat[row * D + j] = v;
+    const int f = h.face[s];
+    const T w0 = h.w0[s], w1 = h.w1[s];
+    a.out_idx[o] = f;
+    if (RAW) {
+      a.out_depth[o] = h.depth[s]; a.out_w0[o] = w0; a.out_w1[o] = w1;
+      continue;
+    }
+    // deftet.py:307  w2 = (face_idx != -1) - (w0 + w1)
+    const T w2 = sub_rn((T)1, add_rn(w0, w1));
+    a.out_w[o * 3] = w0; a.out_w[o * 3 + 1] = w1; a.out_w[o * 3 + 2] = w2;
+    const T* fp = a.feat + (face0 + f) * 3 * D;
+    // deftet.py:315-317  sum over the three vertices of weight * feature
+    for (int d = 0; d < D; d++)
+      a.out_feat[o * D + d] = add_rn(add_rn(mul_rn(w0, __ldg(fp + d)), mul_rn(w1, __ldg(fp + D + d))),
+                                     mul_rn(w2, __ldg(fp + 2 * D + d)));
   }
-  }  // !RAW
 }
 
 // ------------------------------------------------------------------ backward
@@ -590,18 +620,19 @@ inline int64_t up256(int64_t v) { return (v + 255) / 256 * 256; }
 
 struct DeftetLayout {
   int cells_cap;
-  int64_t off_stats, off_start, off_count, off_wide, off_list, bytes, zero_bytes;
+  int64_t off_stats, off_grids, off_start, off_count, off_wide, off_list, bytes, zero_bytes;
 };
 
 DeftetLayout deftet_layout(int B, int F, int P) {
   DeftetLayout L;
-  int64_t cap = 4 * (int64_t)P + 16;
-  if (cap > (int64_t)kGridMax * kGridMax) cap = (int64_t)kGridMax * kGridMax;
+  int64_t cap = 4 * (int64_t)P + 16;      // no point in many more cells than samples
+  if (cap > (1ll << (2 * (kLevels - 1)))) cap = 1ll << (2 * (kLevels - 1));
   L.cells_cap = (int)cap;
   int64_t off = 0;
   L.off_stats = off; off = up256(off + (int64_t)B * sizeof(ViewStats));
   L.off_count = off; off = up256(off + (int64_t)B * cap * 4);
   L.zero_bytes = off;                       // stats and counts are memset, the rest written
+  L.off_grids = off; off = up256(off + (int64_t)B * sizeof(CellGrid));
   L.off_start = off; off = up256(off + (int64_t)B * cap * 4);
   L.off_wide = off; off = up256(off + (int64_t)B * F * 4);
   L.off_list = off; off = up256(off + (int64_t)B * F * 4 * kWideCells);
@@ -642,6 +673,7 @@ int deftet_forward(bool raw, int B, int F, int P, int K, int D, const void* z, c
   else { a.out_feat = (T*)o1; a.out_w = (T*)o2; }
   char* base = (char*)ws;
   a.stats = (ViewStats*)(base + L.off_stats);
+  a.grids = (CellGrid*)(base + L.off_grids);
   a.cell_count = (int*)(base + L.off_count);
   a.cell_start = (int*)(base + L.off_start);
   a.wide = (int*)(base + L.off_wide);
@@ -652,14 +684,20 @@ int deftet_forward(bool raw, int B, int F, int P, int K, int D, const void* z, c
   a.n2 = n2;
 
   DEF_CUDA(cudaMemsetAsync(base, 0, (size_t)L.zero_bytes, st));
-  if (F > 0) {
+  {
     const int pb = (int)std::min<int64_t>((P + 255) / 256, 64);
-    deftet_bounds_kernel<T><<<dim3(pb, B), 256, 0, st>>>(a);
     const int fb = (int)std::max<int64_t>(1, std::min<int64_t>((F + 255) / 256, (148 * 8 + B - 1) / B));
-    deftet_extent_kernel<T><<<dim3(fb, B), 256, 0, st>>>(a);
-    deftet_bin_kernel<T, false><<<dim3(fb, B), 256, 0, st>>>(a);
-    deftet_scan_kernel<<<B, 1024, 0, st>>>(a.stats, a.cell_start, a.cell_count, a.cells_cap);
-    deftet_bin_kernel<T, true><<<dim3(fb, B), 256, 0, st>>>(a);
+    if (F > 0) {
+      deftet_bounds_kernel<T><<<dim3(pb, B), 256, 0, st>>>(a);
+      const int lb = (int)std::max<int64_t>(1, std::min<int64_t>((F + 1023) / 1024, (148 * 4 + B - 1) / B));
+      deftet_levels_kernel<T><<<dim3(lb, B), 256, 0, st>>>(a);
+    }
+    deftet_choose_kernel<<<(B + 127) / 128, 128, 0, st>>>(a.stats, a.grids, B, P, a.cells_cap);
+    if (F > 0) {
+      deftet_bin_kernel<T, false><<<dim3(fb, B), 256, 0, st>>>(a);
+      deftet_scan_kernel<<<B, 1024, 0, st>>>(a.grids, a.cell_start, a.cell_count, a.cells_cap);
+      deftet_bin_kernel<T, true><<<dim3(fb, B), 256, 0, st>>>(a);
+    }
     DEF_CUDA(cudaGetLastError());
   }
   // one warp per sample; warps per CTA limited by the staging of K hits per warp
@@ -672,9 +710,8 @@ int deftet_forward(bool raw, int B, int F, int P, int K, int D, const void* z, c
   auto kern = raw ? deftet_render_kernel<T, true> : deftet_render_kernel<T, false>;
   if (smem > 48 * 1024)
     DEF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int64_t blocks = ((int64_t)B * P + warps - 1) / warps;
-  if (blocks > 0x7fffffff) return fail(DIBR_E_INVALID, "too many sample points");
-  kern<<<(unsigned)blocks, warps * 32, smem, st>>>(a);
+  const int blocks = (P + warps - 1) / warps;
+  kern<<<dim3(blocks, B), warps * 32, smem, st>>>(a);
   DEF_CUDA(cudaGetLastError());
   return DIBR_OK;
 }
