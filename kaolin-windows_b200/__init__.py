@@ -5,7 +5,8 @@ backward, over hand-written CUDA kernels behind a C ABI (include/dibr_b200.h).
 
 Next to the path: ``render.mesh.prepare_vertices`` and ``ops.mesh.index_vertices_by_faces``
 (the step that feeds it), ``render.mesh.texture_mapping`` and ``metrics.render.mask_iou``
-(the step that consumes it).  Nothing else of Kaolin is provided.  The directory name is not a Python identifier; import
+(the step that consumes it), and the sibling op ``render.mesh.deftet_sparse_render``.
+Nothing else of Kaolin is provided.  The directory name is not a Python identifier; import
 it as ``kaolin_windows_b200`` (a small alias package at the repository root) or with
 ``importlib.import_module("kaolin-windows_b200")``.
 """

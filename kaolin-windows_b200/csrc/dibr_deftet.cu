@@ -40,7 +40,8 @@ int fail(int code, const char* fmt, ...);
 namespace {
 
 constexpr int kLevels = 10;       // G = 1 << level, level 0..9
-constexpr int kWideCells = 16;    // a face spanning more cells goes to the wide list
+constexpr int kWideCells = 64;    // a face spanning more cells goes to the wide list
+constexpr int kListCap = 8;       // list entries available per face and view (bounds the workspace)
 constexpr float kCostBuild = 30.f, kCostTest = 40.f;   // thread-instructions per entry / test
 
 // ------------------------------------------------------------------ exact arithmetic
@@ -142,7 +143,7 @@ struct DeftetArgs {
   int* cell_start;     // [B][cells_cap]
   int* cell_count;     // [B][cells_cap]
   int* wide;           // [B][F]
-  int* list;           // [B][kWideCells * F]
+  int* list;           // [B][kListCap * F]
   int B, F, P, K, D, cells_cap, n2;
   float eps;
 };
@@ -242,7 +243,7 @@ __global__ void __launch_bounds__(256) deftet_levels_kernel(const DeftetArgs<T> 
 
 // one thread per view: the cheapest level (see the header), grid parameters stored
 __global__ void deftet_choose_kernel(const ViewStats* stats, CellGrid* grids, int B, int P,
-                                     int cells_cap) {
+                                     int F, int cells_cap) {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
   const ViewStats s = stats[b];
@@ -252,6 +253,7 @@ __global__ void deftet_choose_kernel(const ViewStats* stats, CellGrid* grids, in
   for (int l = 0; l < kLevels; l++) {
     const long long cells = 1ll << (2 * l);
     if (cells > cells_cap) break;
+    if (s.entries[l] > (unsigned long long)kListCap * F) continue;   // must fit the list area
     const float cost = (float)s.entries[l] * (kCostBuild + kCostTest * (float)P / (float)cells) +
                        kCostTest * (float)P * (float)s.wides[l];
     if (cost < best_cost) { best_cost = cost; best = l; }
@@ -271,7 +273,7 @@ __global__ void __launch_bounds__(256) deftet_bin_kernel(const DeftetArgs<T> a) 
   if (g.empty) return;
   int* cnt = a.cell_count + (long long)b * a.cells_cap;
   const int* start = a.cell_start + (long long)b * a.cells_cap;
-  int* list = a.list + (long long)b * kWideCells * a.F;
+  int* list = a.list + (long long)b * kListCap * a.F;
   for (int f = blockIdx.x * blockDim.x + threadIdx.x; f < a.F; f += gridDim.x * blockDim.x) {
     float fx0, fy0, fx1, fy1;
     if (!face_box_f(a, g, b, f, fx0, fy0, fx1, fy1)) continue;
@@ -281,12 +283,29 @@ __global__ void __launch_bounds__(256) deftet_bin_kernel(const DeftetArgs<T> a) 
       if (!FILL) a.wide[(long long)b * a.F + atomicAdd(&a.stats[b].wide, 1u)] = f;
       continue;
     }
-    for (int cy = cy0; cy <= cy1; cy++)
-      for (int cx = cx0; cx <= cx1; cx++) {
-        const int c = cy * g.g + cx;
-        if (FILL) list[start[c] + atomicAdd(cnt + c, 1)] = f;
-        else atomicAdd(cnt + c, 1);
+    const int nx = cx1 - cx0 + 1, tot = nx * (cy1 - cy0 + 1);
+    if (!FILL) {
+      for (int cy = cy0; cy <= cy1; cy++)
+        for (int cx = cx0; cx <= cx1; cx++) atomicAdd(cnt + cy * g.g + cx, 1);   // no return: RED
+      continue;
+    }
+    // four cells at a time: the cursor atomics (and the loads of the segment starts) of a
+    // group are issued back to back, the stores that need their results come after
+    for (int t = 0; t < tot; t += 4) {
+      int pos[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        pos[u] = -1;
+        if (t + u < tot) {
+          const int yy = (t + u) / nx;
+          const int c = (cy0 + yy) * g.g + cx0 + (t + u - yy * nx);
+          pos[u] = start[c] + atomicAdd(cnt + c, 1);
+        }
       }
+#pragma unroll
+      for (int u = 0; u < 4; u++)
+        if (pos[u] >= 0) list[pos[u]] = f;
+    }
   }
 }
 
@@ -302,9 +321,13 @@ __global__ void __launch_bounds__(1024) deftet_scan_kernel(const CellGrid* grids
   if (threadIdx.x == 0) carry = 0;
   __syncthreads();
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int base = 0; base < n; base += 1024) {
-    const int i = base + threadIdx.x;
-    const int v = i < n ? cnt[i] : 0;
+  // n is a power of four (or 1); cells_cap rows are 16-byte aligned: 4 cells per thread
+  for (int base = 0; base < n; base += 4096) {
+    const int i = base + 4 * threadIdx.x;
+    int4 v4 = make_int4(0, 0, 0, 0);
+    if (i + 3 < n) v4 = *reinterpret_cast<const int4*>(cnt + i);
+    else if (i < n) { v4.x = cnt[i]; if (i + 1 < n) v4.y = cnt[i + 1]; if (i + 2 < n) v4.z = cnt[i + 2]; }
+    const int v = v4.x + v4.y + v4.z + v4.w;
     int s = v;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
@@ -324,7 +347,15 @@ __global__ void __launch_bounds__(1024) deftet_scan_kernel(const CellGrid* grids
     }
     __syncthreads();
     const int prefix = carry + (warp ? warp_sum[warp - 1] : 0) + s - v;
-    if (i < n) { start[i] = prefix; cnt[i] = 0; }
+    if (i + 3 < n) {
+      *reinterpret_cast<int4*>(start + i) =
+          make_int4(prefix, prefix + v4.x, prefix + v4.x + v4.y, prefix + v4.x + v4.y + v4.z);
+      *reinterpret_cast<int4*>(cnt + i) = make_int4(0, 0, 0, 0);
+    } else if (i < n) {
+      start[i] = prefix; cnt[i] = 0;
+      if (i + 1 < n) { start[i + 1] = prefix + v4.x; cnt[i + 1] = 0; }
+      if (i + 2 < n) { start[i + 2] = prefix + v4.x + v4.y; cnt[i + 2] = 0; }
+    }
     __syncthreads();
     if (threadIdx.x == 1023) carry = prefix + v;
     __syncthreads();
@@ -399,7 +430,7 @@ __device__ __forceinline__ bool slot_before(const HitBuf<T>& h, int i, int j) {
 
 // one warp per sample point; blockIdx.y = view
 template <typename T, bool RAW>
-__global__ void __launch_bounds__(256) deftet_render_kernel(const DeftetArgs<T> a) {
+__global__ void __launch_bounds__(128) deftet_render_kernel(const DeftetArgs<T> a) {
   typedef typename Vec2<T>::type V2;
   extern __shared__ __align__(16) unsigned char smem[];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -425,7 +456,7 @@ __global__ void __launch_bounds__(256) deftet_render_kernel(const DeftetArgs<T> 
     if (pass == 0) {
       const int cell = cell_of(to_f(y0), g.loy, g.invy, g.g) * g.g +
                        cell_of(to_f(x0), g.lox, g.invx, g.g);
-      lst = a.list + face0 * kWideCells + a.cell_start[(long long)b * a.cells_cap + cell];
+      lst = a.list + face0 * kListCap + a.cell_start[(long long)b * a.cells_cap + cell];
       len = a.cell_count[(long long)b * a.cells_cap + cell];
     } else {
       lst = a.wide + face0;
@@ -486,9 +517,22 @@ __global__ void __launch_bounds__(256) deftet_render_kernel(const DeftetArgs<T> 
   }
   __syncwarp();
 
-  // order the held hits: bitonic network over slot numbers (padding = -1 goes last)
-  if (n > 1) {
-    int n2 = 2;
+  // order the held hits.  Up to 32: every lane ranks its own hit against the others
+  // (shuffles); beyond: bitonic network over slot numbers in shared memory (padding -1 last)
+  if (n > 1 && n <= 32) {
+    const bool mine = lane < n;
+    const T di = mine ? h.depth[lane] : (T)0;
+    const int fi = mine ? h.face[lane] : 0;
+    int rank = 0;
+    for (int j = 0; j < n; j++) {
+      const T dj = __shfl_sync(DIBR_FULL_MASK, di, j);
+      const int fj = __shfl_sync(DIBR_FULL_MASK, fi, j);
+      rank += RAW ? (fj < fi) : (dj > di || (dj == di && fj < fi));
+    }
+    if (mine) h.perm[rank] = lane;
+    __syncwarp();
+  } else if (n > 32) {
+    int n2 = 64;
     while (n2 < n) n2 <<= 1;
     for (int k = lane; k < n2; k += 32) h.perm[k] = k < n ? k : -1;
     __syncwarp();
@@ -512,33 +556,29 @@ __global__ void __launch_bounds__(256) deftet_render_kernel(const DeftetArgs<T> 
   const long long row = gp * K;
   const int D = a.D;
   for (int k = lane; k < K; k += 32) {
-    const int s = k < n ? (n > 1 ? h.perm[k] : 0) : -1;
+    const bool ok = k < n;
+    const int s = ok ? (n > 1 ? h.perm[k] : 0) : 0;
     const long long o = row + k;
-    if (s < 0) {
-      a.out_idx[o] = -1;
-      if (RAW) {
-        a.out_depth[o] = -(T)INFINITY; a.out_w0[o] = (T)0; a.out_w1[o] = (T)0;
-      } else {
-        a.out_w[o * 3] = (T)0; a.out_w[o * 3 + 1] = (T)0; a.out_w[o * 3 + 2] = (T)0;
-        for (int d = 0; d < D; d++) a.out_feat[o * D + d] = (T)0;
-      }
-      continue;
-    }
-    const int f = h.face[s];
-    const T w0 = h.w0[s], w1 = h.w1[s];
+    const int f = ok ? h.face[s] : -1;
+    const T w0 = ok ? h.w0[s] : (T)0, w1 = ok ? h.w1[s] : (T)0;
     a.out_idx[o] = f;
     if (RAW) {
-      a.out_depth[o] = h.depth[s]; a.out_w0[o] = w0; a.out_w1[o] = w1;
+      a.out_depth[o] = ok ? h.depth[s] : -(T)INFINITY; a.out_w0[o] = w0; a.out_w1[o] = w1;
       continue;
     }
     // deftet.py:307  w2 = (face_idx != -1) - (w0 + w1)
-    const T w2 = sub_rn((T)1, add_rn(w0, w1));
-    a.out_w[o * 3] = w0; a.out_w[o * 3 + 1] = w1; a.out_w[o * 3 + 2] = w2;
-    const T* fp = a.feat + (face0 + f) * 3 * D;
+    const T w2 = sub_rn(ok ? (T)1 : (T)0, add_rn(w0, w1));
+    T* ow = a.out_w + o * 3;
+    ow[0] = w0; ow[1] = w1; ow[2] = w2;
+    const T* fp = a.feat + (face0 + (ok ? f : 0)) * 3 * D;
+    T* of = a.out_feat + o * D;
     // deftet.py:315-317  sum over the three vertices of weight * feature
-    for (int d = 0; d < D; d++)
-      a.out_feat[o * D + d] = add_rn(add_rn(mul_rn(w0, __ldg(fp + d)), mul_rn(w1, __ldg(fp + D + d))),
-                                     mul_rn(w2, __ldg(fp + 2 * D + d)));
+    for (int d = 0; d < D; d++) {
+      T v = (T)0;
+      if (ok) v = add_rn(add_rn(mul_rn(w0, __ldg(fp + d)), mul_rn(w1, __ldg(fp + D + d))),
+                         mul_rn(w2, __ldg(fp + 2 * D + d)));
+      of[d] = v;
+    }
   }
 }
 
@@ -627,7 +667,7 @@ DeftetLayout deftet_layout(int B, int F, int P) {
   DeftetLayout L;
   int64_t cap = 4 * (int64_t)P + 16;      // no point in many more cells than samples
   if (cap > (1ll << (2 * (kLevels - 1)))) cap = 1ll << (2 * (kLevels - 1));
-  L.cells_cap = (int)cap;
+  L.cells_cap = (int)((cap + 3) / 4 * 4);      // rows stay 16-byte aligned
   int64_t off = 0;
   L.off_stats = off; off = up256(off + (int64_t)B * sizeof(ViewStats));
   L.off_count = off; off = up256(off + (int64_t)B * cap * 4);
@@ -635,7 +675,7 @@ DeftetLayout deftet_layout(int B, int F, int P) {
   L.off_grids = off; off = up256(off + (int64_t)B * sizeof(CellGrid));
   L.off_start = off; off = up256(off + (int64_t)B * cap * 4);
   L.off_wide = off; off = up256(off + (int64_t)B * F * 4);
-  L.off_list = off; off = up256(off + (int64_t)B * F * 4 * kWideCells);
+  L.off_list = off; off = up256(off + (int64_t)B * F * 4 * kListCap);
   L.bytes = off;
   return L;
 }
@@ -654,7 +694,7 @@ int deftet_forward(bool raw, int B, int F, int P, int K, int D, const void* z, c
                    int64_t ws_bytes, cudaStream_t st) {
   if (B < 0 || F < 0 || P < 0 || K < 0 || D < 0) return fail(DIBR_E_INVALID, "invalid sizes");
   if (B > 65535) return fail(DIBR_E_INVALID, "batch %d > 65535 not supported", B);
-  if ((int64_t)F * kWideCells > 0x7fffffff) return fail(DIBR_E_INVALID, "too many faces");
+  if ((int64_t)F * kListCap > 0x7fffffff) return fail(DIBR_E_INVALID, "too many faces");
   if (B == 0 || P == 0 || K == 0) return DIBR_OK;
   if (!pix || !range || !out_idx) return fail(DIBR_E_INVALID, "null pointer");
   if (F > 0 && (!z || !img)) return fail(DIBR_E_INVALID, "null input");
@@ -692,7 +732,7 @@ int deftet_forward(bool raw, int B, int F, int P, int K, int D, const void* z, c
       const int lb = (int)std::max<int64_t>(1, std::min<int64_t>((F + 1023) / 1024, (148 * 4 + B - 1) / B));
       deftet_levels_kernel<T><<<dim3(lb, B), 256, 0, st>>>(a);
     }
-    deftet_choose_kernel<<<(B + 127) / 128, 128, 0, st>>>(a.stats, a.grids, B, P, a.cells_cap);
+    deftet_choose_kernel<<<(B + 127) / 128, 128, 0, st>>>(a.stats, a.grids, B, P, F, a.cells_cap);
     if (F > 0) {
       deftet_bin_kernel<T, false><<<dim3(fb, B), 256, 0, st>>>(a);
       deftet_scan_kernel<<<B, 1024, 0, st>>>(a.grids, a.cell_start, a.cell_count, a.cells_cap);
@@ -703,7 +743,7 @@ int deftet_forward(bool raw, int B, int F, int P, int K, int D, const void* z, c
   // one warp per sample; warps per CTA limited by the staging of K hits per warp
   size_t per_warp = (size_t)K * (3 * sizeof(T) + sizeof(int)) + (size_t)n2 * sizeof(int);
   per_warp = (per_warp + 15) & ~(size_t)15;
-  int warps = (int)std::min<size_t>(8, (200 * 1024) / per_warp);
+  int warps = (int)std::min<size_t>(4, (200 * 1024) / per_warp);
   if (warps < 1) return fail(DIBR_E_INVALID, "knum %d needs %zu bytes of shared memory per sample, "
                              "more than an SM has", K, per_warp);
   const size_t smem = per_warp * warps;
