@@ -74,6 +74,12 @@ extern "C" {
 
 DIBR_API const char* dibr_last_error(void);
 DIBR_API int dibr_version(void);
+/* needed_host reports (protocol above) are normally a 16-byte device-to-host copy between two
+ * kernels.  If every needed_host the caller passes is pinned memory the device can address
+ * (cudaHostAlloc / cudaMallocHost under unified addressing -- torch's pin_memory() is), turn
+ * this on and the kernels store the report themselves: no copy node breaks the kernel chain.
+ * Process-wide; returns the previous setting. */
+DIBR_API int dibr_host_report_direct(int on);
 
 /* Measurement aid (used by bench.py only): between dibr_profile_begin() and
  * dibr_profile_end() every kernel launch of this library is bracketed by CUDA events on

@@ -22,6 +22,7 @@ _vp, _i, _f, _i64 = _c.c_void_p, _c.c_int, _c.c_float, _c.c_int64
 SIGNATURES = {
     "dibr_last_error": (_c.c_char_p, []),
     "dibr_version": (_i, []),
+    "dibr_host_report_direct": (_i, [_i]),
     "dibr_profile_begin": (_i, []),
     "dibr_profile_end": (_i, [_vp, _vp, _i]),
     "dibr_workspace_fixed_bytes": (_i64, [_i, _i, _i, _i]),
@@ -94,6 +95,9 @@ def lib():
                 fn = getattr(h, name)  # AttributeError if the library lacks a declared symbol
                 fn.restype = res
                 fn.argtypes = args
+            # every needed_host this package passes is a pin_memory() tensor: let the kernels
+            # store their reports directly (DIBR_B200_REPORT=copy keeps the copy nodes)
+            h.dibr_host_report_direct(0 if os.environ.get("DIBR_B200_REPORT") == "copy" else 1)
             _lib = h
     return _lib
 

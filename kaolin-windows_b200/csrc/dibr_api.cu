@@ -3,6 +3,7 @@
 // kernels of dibr_binning.cu / dibr_raster.cu / dibr_softmask.cu on the caller's stream.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -53,6 +54,21 @@ void prof_end(cudaStream_t st) {
 #ifdef DIBR_TRACE
 static unsigned long long* g_trace_ptr = nullptr;
 #endif
+
+// programmatic dependent launch between the kernels of the path (dibr_common.cuh):
+// measured to gain nothing under graph replay, so off unless DIBR_B200_PDL=1
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("DIBR_B200_PDL");
+    return e && e[0] == '1';
+  }();
+  return on;
+}
+
+// needed_host is device-visible pinned memory (cudaHostAlloc under UVA): the kernels store
+// the report themselves, no copy node between them (dibr_host_report_direct)
+static bool g_report_direct = false;   // process-wide, set once by the host binding
+
 
 static inline int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
 
@@ -174,8 +190,13 @@ static int run_binning(const Plan& p, const Workspace& w, BinJobs& jobs, const i
     DIBR_CUDA(cudaMemsetAsync(w.base + p.off_start[l], 0,
                               (l == 0 ? p.off_start[1] : p.off_order[0]) - p.off_start[l], st));
   }
+  const bool direct = needed_host && g_report_direct && p.B > 0 && p.F > 0;
+  jobs.totals = (const unsigned long long*)(w.base + p.off_total);
+  jobs.report = direct ? (unsigned long long*)needed_host : nullptr;
   if (p.B > 0) DIBR_CUDA(launch_binning_count(jobs, njobs, p, st));
-  if (needed_host) {
+  if (direct) {
+    // the fill kernel stores the totals into the host slot itself
+  } else if (needed_host) {
     DIBR_CUDA(cudaMemcpyAsync(needed_host, w.base + p.off_total, 16, cudaMemcpyDeviceToHost, st));
   } else {
     unsigned long long tot[2] = {0, 0};
@@ -213,6 +234,12 @@ extern "C" __attribute__((visibility("default"))) int dibr_trace_set(void* ptr) 
 
 extern "C" const char* dibr_last_error(void) { return g_err; }
 extern "C" int dibr_version(void) { return 100; }
+
+extern "C" int dibr_host_report_direct(int on) {
+  const int was = g_report_direct ? 1 : 0;
+  g_report_direct = on != 0;
+  return was;
+}
 
 extern "C" int dibr_profile_begin(void) {
   std::lock_guard<std::mutex> lk(g_prof_mu);
@@ -327,9 +354,11 @@ static int run_soft_forward(const SoftArgs& a, const Plan& p, int64_t* needed_ho
                             cudaStream_t st) {
   if (a.pairs.cap > 0) {
     DIBR_CUDA(launch_softmask(a, SOFT_GATHER, p, st));
-    if (needed_host)
+    SoftArgs e = a;
+    e.report = (needed_host && g_report_direct) ? (unsigned long long*)needed_host : nullptr;
+    if (needed_host && !e.report)
       DIBR_CUDA(cudaMemcpyAsync(needed_host + 2, a.pairs.cursor, 16, cudaMemcpyDeviceToHost, st));
-    DIBR_CUDA(launch_softmask_pairs_eval(a, p, st));
+    DIBR_CUDA(launch_softmask_pairs_eval(e, p, st));
   }
   DIBR_CUDA(launch_softmask(a, SOFT_FWD, p, st));
   return DIBR_OK;

@@ -44,6 +44,13 @@ __device__ __forceinline__ bool bin_rect(const Grid& g, const Face2D& f, int bin
 template <bool FILL>
 __global__ void __launch_bounds__(kBinWarps * 32)
 bin_walk_kernel(const BinJobs jobs, const Plan p) {
+  pdl_prologue();
+  if (FILL && jobs.report && (blockIdx.x | blockIdx.y | blockIdx.z | threadIdx.x) == 0) {
+    volatile unsigned long long* r = jobs.report;
+    r[0] = jobs.totals[0];
+    r[1] = jobs.totals[1];
+    __threadfence_system();
+  }
   extern __shared__ int s_hist[];  // [kBinWarps][NB]
   const BinJob& job = jobs.j[blockIdx.z];
   const int warp = threadIdx.x >> 5, lane = lane_id();
@@ -135,6 +142,7 @@ bin_walk_kernel(const BinJobs jobs, const Plan p) {
 
 // One warp per (view, bin); 8 warps per CTA share one cursor atomic.
 __global__ void __launch_bounds__(256) bin_scan_kernel(const BinJobs jobs, const Plan p) {
+  pdl_prologue();
   __shared__ int s_tot[8];
   __shared__ long long s_base;
   const BinJob& job = jobs.j[blockIdx.z];
@@ -184,13 +192,13 @@ cudaError_t launch_binning_count(const BinJobs& jobs, int njobs, const Plan& p, 
   if (p.nchunks > 0) {
     dim3 grid((p.nchunks + kBinWarps - 1) / kBinWarps, p.B, njobs);
     prof_begin(K_BIN_COUNT, st);
-    bin_walk_kernel<false><<<grid, kBinWarps * 32, smem, st>>>(jobs, p);
+    launch_k(bin_walk_kernel<false>, grid, kBinWarps * 32, smem, st, jobs, p);
     prof_end(st);
   }
   const long long nrows = (long long)p.B * p.NB;
   dim3 grid2((unsigned)((nrows + 7) / 8), 1, njobs);
   prof_begin(K_BIN_SCAN, st);
-  bin_scan_kernel<<<grid2, 256, 0, st>>>(jobs, p);
+  launch_k(bin_scan_kernel, grid2, 256, 0, st, jobs, p);
   prof_end(st);
   return cudaGetLastError();
 }
@@ -199,7 +207,7 @@ cudaError_t launch_binning_fill(const BinJobs& jobs, int njobs, const Plan& p, c
   const size_t smem = (size_t)kBinWarps * p.NB * sizeof(int);
   dim3 grid((p.nchunks + kBinWarps - 1) / kBinWarps, p.B, njobs);
   prof_begin(K_BIN_FILL, st);
-  bin_walk_kernel<true><<<grid, kBinWarps * 32, smem, st>>>(jobs, p);
+  launch_k(bin_walk_kernel<true>, grid, kBinWarps * 32, smem, st, jobs, p);
   prof_end(st);
   return cudaGetLastError();
 }

@@ -70,6 +70,10 @@ struct BinJob {
 // ------------------------------------------------------------- kernel argument packs
 struct BinJobs {
   BinJob j[2];
+  // list totals reported straight into device-visible pinned host memory by the fill
+  // kernel (dibr_host_report_direct), instead of a copy node between the kernels
+  const unsigned long long* totals;
+  unsigned long long* report;
 };
 
 struct RasterArgs {
@@ -140,6 +144,7 @@ struct SoftArgs {
   const float* mask_in;
   float* grad_img;         // (B, F, 3, 2) accumulated, unscaled coordinates
   PairBuf pairs;
+  unsigned long long* report;  // device-visible host slot for the pair-buffer needs, or null
 };
 
 struct SoftDenseBwdArgs {
@@ -438,6 +443,42 @@ __device__ __forceinline__ unsigned long long trace_now() {
 __device__ __forceinline__ void prefetch_l1(const void* p) {
   asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
 }
+
+// ------------------------------------------------------- programmatic dependent launch
+// Every kernel of the path starts with pdl_prologue(), which waits until the PREVIOUS kernel
+// of the stream has completed and flushed.  Without the launch attribute (launch_k, off by
+// default) it is a no-op.  Measured on the cfg-2 step inside a CUDA graph (B200): with the
+// attribute and an early griddepcontrol.launch_dependents the step got SLOWER (0.314 ->
+// 0.335 ms: the next kernel's parked CTAs take SM slots from the running one), with the
+// attribute and no early trigger it was unchanged (0.315 ms) -- graph replay already leaves
+// no launch gap worth hiding.  Kept as an experiment switch: DIBR_B200_PDL=1, and
+// -DDIBR_PDL_TRIGGER=1 at build time for the early trigger.
+#ifndef DIBR_PDL_TRIGGER
+#define DIBR_PDL_TRIGGER 0
+#endif
+__device__ __forceinline__ void pdl_prologue() {
+#if DIBR_PDL_TRIGGER
+  asm volatile("griddepcontrol.launch_dependents;");
+#endif
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
+#ifdef __CUDACC__
+bool pdl_enabled();   // dibr_api.cu: DIBR_B200_PDL=0 turns the attribute off
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem,
+                            cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+#endif
 
 // ------------------------------------------------------------------------------ misc
 __device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }

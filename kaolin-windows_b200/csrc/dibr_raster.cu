@@ -75,6 +75,7 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
   RasterSmem<BLK_LOG2>& sm = *reinterpret_cast<RasterSmem<BLK_LOG2>*>(s_raw);
   unsigned long long* zbuf = sm.zbuf;
 
+  pdl_prologue();
   DIBR_TRACE_BEGIN();
   // blocks are taken longest face list first (lpt_block)
   int b, bxi, byi;
@@ -379,7 +380,7 @@ cudaError_t launch_raster_forward(const RasterArgs& a, const Plan& p, cudaStream
   dim3 grid((unsigned)(((long long)p.B * p.NB) << (2 * shift)));
   prof_begin(K_RASTER_FWD, st);
   if (p.blk_log2 == 5) {
-    raster_forward_kernel<5><<<grid, kRasterThreads, sizeof(RasterSmem<5>), st>>>(a, p);
+    launch_k(raster_forward_kernel<5>, grid, kRasterThreads, sizeof(RasterSmem<5>), st, a, p);
   } else {
     const size_t smem = sizeof(RasterSmem<6>);  // above the 48 KB default: opt in
     static bool once = false;
@@ -389,7 +390,7 @@ cudaError_t launch_raster_forward(const RasterArgs& a, const Plan& p, cudaStream
       if (e != cudaSuccess) return e;
       once = true;
     }
-    raster_forward_kernel<6><<<grid, kRasterThreads, smem, st>>>(a, p);
+    launch_k(raster_forward_kernel<6>, grid, kRasterThreads, smem, st, a, p);
   }
   prof_end(st);
   return cudaGetLastError();
@@ -456,6 +457,7 @@ __device__ __forceinline__ void reduce_peers(unsigned peers, float (&v)[N], int 
 
 template <int DC>  // features handled per pass (D <= 4: one pass)
 __global__ void __launch_bounds__(256, 6) raster_backward_kernel(const RasterBwdArgs a) {
+  pdl_prologue();
   const int lane = lane_id(), warp = threadIdx.x >> 5;
   const int ix = (blockIdx.x << 4) + ((warp & 1) << 3) + (lane & 7);
   const int iy = (blockIdx.y << 4) + ((warp >> 1) << 2) + (lane >> 3);
@@ -562,6 +564,7 @@ __global__ void __launch_bounds__(256, 6) raster_backward_kernel(const RasterBwd
 
 // pass 2: moments -> gradients, one thread per (view, face)
 __global__ void __launch_bounds__(256) raster_backward_finish_kernel(const RasterBwdArgs a) {
+  pdl_prologue();
   const long long fbase = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (fbase >= (long long)a.B * a.F) return;
   float* gf = a.grad_feat + fbase * 3 * a.D;
@@ -615,10 +618,10 @@ cudaError_t launch_raster_backward_moments(const RasterBwdArgs& a, cudaStream_t 
   dim3 grid((a.W + 15) / 16, (a.H + 15) / 16, a.B);
   prof_begin(K_RASTER_BWD, st);
   switch (a.D >= 4 ? 4 : a.D) {
-    case 1: raster_backward_kernel<1><<<grid, 256, 0, st>>>(a); break;
-    case 2: raster_backward_kernel<2><<<grid, 256, 0, st>>>(a); break;
-    case 3: raster_backward_kernel<3><<<grid, 256, 0, st>>>(a); break;
-    default: raster_backward_kernel<4><<<grid, 256, 0, st>>>(a); break;
+    case 1: launch_k(raster_backward_kernel<1>, grid, 256, 0, st, a); break;
+    case 2: launch_k(raster_backward_kernel<2>, grid, 256, 0, st, a); break;
+    case 3: launch_k(raster_backward_kernel<3>, grid, 256, 0, st, a); break;
+    default: launch_k(raster_backward_kernel<4>, grid, 256, 0, st, a); break;
   }
   prof_end(st);
   return cudaGetLastError();
@@ -627,7 +630,7 @@ cudaError_t launch_raster_backward_moments(const RasterBwdArgs& a, cudaStream_t 
 cudaError_t launch_raster_backward_finish(const RasterBwdArgs& a, cudaStream_t st) {
   const long long nf = (long long)a.B * a.F;
   prof_begin(K_RASTER_BWD_FINISH, st);
-  raster_backward_finish_kernel<<<(unsigned)((nf + 255) / 256), 256, 0, st>>>(a);
+  launch_k(raster_backward_finish_kernel, (unsigned)((nf + 255) / 256), 256, 0, st, a);
   prof_end(st);
   return cudaGetLastError();
 }

@@ -62,6 +62,7 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
   extern __shared__ __align__(16) unsigned char s_raw[];
   Smem& sm = *reinterpret_cast<Smem*>(s_raw);
   const PairBuf& pb = a.pairs;
+  pdl_prologue();
 
   const int tid = threadIdx.x, lane = lane_id(), warp = tid >> 5;
 #ifdef DIBR_TRACE_GATHER
@@ -356,7 +357,7 @@ static cudaError_t launch_gather(const SoftArgs& a, const Plan& p, cudaStream_t 
     once = true;
   }
   dim3 grid((p.W + (1 << G_LOG2) - 1) >> G_LOG2, (p.H + (1 << G_LOG2) - 1) >> G_LOG2, p.B);
-  softmask_gather_kernel<G_LOG2><<<grid, kGThreads, smem, st>>>(a, p);
+  launch_k(softmask_gather_kernel<G_LOG2>, grid, kGThreads, smem, st, a, p);
   return cudaGetLastError();
 }
 

@@ -382,6 +382,7 @@ __global__ void __launch_bounds__(kSoftThreads)
 softmask_kernel(const SoftArgs a, const Plan p) {
   extern __shared__ __align__(16) unsigned char s_raw[];
   SoftSmem<BLK_LOG2, MODE>& sm = *reinterpret_cast<SoftSmem<BLK_LOG2, MODE>*>(s_raw);
+  pdl_prologue();
   if ((MODE == SOFT_FWD || MODE == SOFT_BWD) && a.pairs.cap > 0 && !pairs_overflowed(a.pairs))
     return;
   const int per_view = p.nkx * p.nky;
@@ -498,7 +499,14 @@ __device__ __forceinline__ bool pair_work(const PairBuf& pb, const Plan& p, unsi
 __global__ void __launch_bounds__(kPairWarps * 32, DIBR_EVAL_MINB)
 softmask_pairs_eval_kernel(const SoftArgs a, const Plan p) {
   __shared__ float sX[kPairWarps][6][kPairChunk];
+  pdl_prologue();
   const PairBuf& pb = a.pairs;
+  if (a.report && (blockIdx.x | threadIdx.x) == 0) {   // pair-buffer needs, see BinJobs::report
+    volatile unsigned long long* r = a.report;
+    r[2] = pb.cursor[0];
+    r[3] = pb.cursor[1];
+    __threadfence_system();
+  }
   if (pairs_overflowed(pb)) return;
   const int lane = lane_id();
   const unsigned nchunk = min(*pb.nchunk, 3u * (unsigned)pb.cap);
@@ -562,6 +570,7 @@ softmask_pairs_eval_kernel(const SoftArgs a, const Plan p) {
 // Rows are coalesced, eight independent loads at a time (a missing hit multiplies by
 // exactly 1).
 __global__ void __launch_bounds__(256) softmask_pairs_fold_kernel(const SoftArgs a, const Plan p) {
+  pdl_prologue();
   const PairBuf& pb = a.pairs;
   if (pairs_overflowed(pb)) return;
   const int lane = lane_id();
@@ -597,6 +606,7 @@ __global__ void __launch_bounds__(256) softmask_pairs_fold_kernel(const SoftArgs
 __global__ void __launch_bounds__(kPairWarps * 32, DIBR_GRAD_MINB)
 softmask_pairs_grad_kernel(const SoftArgs a, const Plan p) {
   __shared__ float sX[kPairWarps][6][kPairChunk];
+  pdl_prologue();
   const PairBuf& pb = a.pairs;
   if (pairs_overflowed(pb)) return;
   const int lane = lane_id();
@@ -673,6 +683,7 @@ softmask_pairs_grad_kernel(const SoftArgs a, const Plan p) {
 // ---------------------------------------------------------------------------
 
 __global__ void __launch_bounds__(256) softmask_dense_backward_kernel(const SoftDenseBwdArgs a) {
+  pdl_prologue();
   const long long npix = (long long)a.B * a.H * a.W;
   const Grid g = make_grid(a.mult, a.W, a.H);
   for (long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x; pix < npix;
@@ -721,7 +732,7 @@ static cudaError_t launch_soft_mode(const SoftArgs& a, const Plan& p, cudaStream
       attr5 = true;
     }
     prof_begin(MODE == SOFT_BWD ? K_SOFT_BWD : K_SOFT_FWD, st);
-    softmask_kernel<5, MODE><<<grid, kSoftThreads, smem, st>>>(a, p);
+    launch_k((softmask_kernel<5, MODE>), grid, kSoftThreads, smem, st, a, p);
   } else {
     const int smem = (int)sizeof(SoftSmem<6, MODE>);
     if (!attr6) {
@@ -731,7 +742,7 @@ static cudaError_t launch_soft_mode(const SoftArgs& a, const Plan& p, cudaStream
       attr6 = true;
     }
     prof_begin(MODE == SOFT_BWD ? K_SOFT_BWD : K_SOFT_FWD, st);
-    softmask_kernel<6, MODE><<<grid, kSoftThreads, smem, st>>>(a, p);
+    launch_k((softmask_kernel<6, MODE>), grid, kSoftThreads, smem, st, a, p);
   }
   prof_end(st);
   return cudaGetLastError();
@@ -748,11 +759,11 @@ static int pair_grid(const PairBuf& pb) {
 cudaError_t launch_softmask_pairs_eval(const SoftArgs& a, const Plan& p, cudaStream_t st) {
   if (a.pairs.cap <= 0) return cudaSuccess;
   prof_begin(K_SOFT_EVAL, st);
-  softmask_pairs_eval_kernel<<<pair_grid(a.pairs), kPairWarps * 32, 0, st>>>(a, p);
+  launch_k(softmask_pairs_eval_kernel, pair_grid(a.pairs), kPairWarps * 32, 0, st, a, p);
   prof_end(st);
   prof_begin(K_SOFT_FOLD, st);
   const long long regions = (a.pairs.cap + 7) / 8;
-  softmask_pairs_fold_kernel<<<(int)(regions < 148 * 8 ? regions : 148 * 8), 256, 0, st>>>(a, p);
+  launch_k(softmask_pairs_fold_kernel, (int)(regions < 148 * 8 ? regions : 148 * 8), 256, 0, st, a, p);
   prof_end(st);
   return cudaGetLastError();
 }
@@ -760,7 +771,7 @@ cudaError_t launch_softmask_pairs_eval(const SoftArgs& a, const Plan& p, cudaStr
 cudaError_t launch_softmask_pairs_grad(const SoftArgs& a, const Plan& p, cudaStream_t st) {
   if (a.pairs.cap <= 0) return cudaSuccess;
   prof_begin(K_SOFT_GRAD, st);
-  softmask_pairs_grad_kernel<<<pair_grid(a.pairs), kPairWarps * 32, 0, st>>>(a, p);
+  launch_k(softmask_pairs_grad_kernel, pair_grid(a.pairs), kPairWarps * 32, 0, st, a, p);
   prof_end(st);
   return cudaGetLastError();
 }
@@ -779,7 +790,7 @@ cudaError_t launch_softmask_dense_backward(const SoftDenseBwdArgs& a, cudaStream
   if (npix == 0) return cudaSuccess;
   const int blocks = (int)min((npix + 255) / 256, (long long)148 * 16);
   prof_begin(K_SOFT_BWD_DENSE, st);
-  softmask_dense_backward_kernel<<<blocks, 256, 0, st>>>(a);
+  launch_k(softmask_dense_backward_kernel, blocks, 256, 0, st, a);
   prof_end(st);
   return cudaGetLastError();
 }

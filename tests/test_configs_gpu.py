@@ -91,6 +91,15 @@ def test_cfg3_200k_1024_one_view(kal, ref):
     full_compare(kal, ref, inp, 1024, 1024, grads=False)
 
 
+def test_cfg4_1m_2048_one_view(kal, ref):
+    """BASELINE config 4 at full size (1 000 000 faces, 2048 x 2048), one of its 16 views,
+    forward and backward against the reference's kernels."""
+    inp = wl.make_config("cfg4_1m_16x2048", device=DEV, views=1)
+    assert inp["face_vertices_z"].shape[:2] == (1, 1000000)
+    s = full_compare(kal, ref, inp, 2048, 2048)
+    assert s["covered"] > 2000000 and s["soft"] > 1000
+
+
 @pytest.mark.parametrize("H,W", [(37, 53), (200, 333), (65, 64), (1, 1), (16, 700)])
 def test_odd_image_sizes(kal, ref, H, W):
     g = wl.fixture_geometry(batch_size=2)
