@@ -600,12 +600,11 @@ struct DeftetBwdArgs {
   float eps;
 };
 
+// the gradient of one valid slot s holding face f
 template <typename T>
-__global__ void __launch_bounds__(256) deftet_backward_kernel(const DeftetBwdArgs<T> a) {
-  for (long long s = (long long)blockIdx.x * blockDim.x + threadIdx.x; s < a.slots;
-       s += (long long)gridDim.x * blockDim.x) {
-    const long long f = a.idx[s];
-    if (f < 0) continue;
+__device__ __forceinline__ void deftet_backward_slot(const DeftetBwdArgs<T>& a, long long s,
+                                                     long long f) {
+  {
     const long long bf = (s / a.per_view) * a.F + f;
     const int D = a.D;
     const T* g = a.grad + s * D;
@@ -654,6 +653,44 @@ __global__ void __launch_bounds__(256) deftet_backward_kernel(const DeftetBwdArg
     atomicAdd(gi + 2, s_bx); atomicAdd(gi + 3, s_by);
     atomicAdd(gi + 4, s_cx); atomicAdd(gi + 5, s_cy);
   }
+}
+
+// Valid slots are few (a handful of layers out of knum per point) and sit at the front of
+// every point's row, so one thread per slot would leave ~90 % of the lanes idle in the heavy
+// part.  Each warp walks a contiguous range of slots 32 at a time (coalesced index reads),
+// queues the valid ones in shared memory (ballot compaction) and runs the gradient 32 valid
+// slots at a time with every lane busy.  No assumption on where the -1 entries are.
+constexpr int kBwdWarps = 8;
+template <typename T>
+__global__ void __launch_bounds__(kBwdWarps * 32) deftet_backward_kernel(const DeftetBwdArgs<T> a) {
+  __shared__ long long q_slot[kBwdWarps][64];
+  __shared__ int q_face[kBwdWarps][64];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const long long nwarps = (long long)gridDim.x * kBwdWarps;
+  const long long gw = (long long)blockIdx.x * kBwdWarps + warp;
+  // ranges in multiples of 32 slots
+  const long long tiles = (a.slots + 31) / 32;
+  const long long per = (tiles + nwarps - 1) / nwarps;
+  const long long t0 = gw * per, t1 = min(t0 + per, tiles);
+  int queued = 0;
+  for (long long t = t0; t < t1; t++) {
+    const long long s = t * 32 + lane;
+    const long long f = s < a.slots ? a.idx[s] : -1;
+    const unsigned m = __ballot_sync(DIBR_FULL_MASK, f >= 0);
+    if (f >= 0) {
+      const int q = queued + __popc(m & lanemask_lt());
+      q_slot[warp][q] = s;
+      q_face[warp][q] = (int)f;
+    }
+    queued += __popc(m);
+    __syncwarp();
+    if (queued >= 32) {
+      queued -= 32;
+      deftet_backward_slot(a, q_slot[warp][queued + lane], (long long)q_face[warp][queued + lane]);
+      __syncwarp();
+    }
+  }
+  if (lane < queued) deftet_backward_slot(a, q_slot[warp][lane], (long long)q_face[warp][lane]);
 }
 
 inline int64_t up256(int64_t v) { return (v + 255) / 256 * 256; }
@@ -772,8 +809,8 @@ int deftet_backward(int B, int F, int P, int K, int D, const void* grad, const i
   a.grad = (const T*)grad; a.idx = idx; a.weights = (const T*)weights; a.img = (const T*)img;
   a.feat = (const T*)feat; a.grad_img = (T*)grad_img; a.grad_feat = (T*)grad_feat;
   a.slots = slots; a.per_view = (long long)P * K; a.F = F; a.D = D; a.eps = eps;
-  const long long blocks = std::min<long long>((slots + 255) / 256, 148 * 32);
-  deftet_backward_kernel<T><<<(unsigned)blocks, 256, 0, st>>>(a);
+  const long long blocks = std::min<long long>((slots + 32 * kBwdWarps - 1) / (32 * kBwdWarps), 148 * 8);
+  deftet_backward_kernel<T><<<(unsigned)blocks, kBwdWarps * 32, 0, st>>>(a);
   DEF_CUDA(cudaGetLastError());
   return DIBR_OK;
 }
