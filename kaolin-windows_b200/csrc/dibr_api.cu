@@ -72,13 +72,15 @@ static bool g_report_direct = false;   // process-wide, set once by the host bin
 
 static inline int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
 
-static int make_plan(int B, int F, int H, int W, Plan& p) {
+static int make_plan(int B, int F, int H, int W, Plan& p, float mult = nanf("")) {
   if (B < 0 || F < 0 || H <= 0 || W <= 0)
     return fail(DIBR_E_INVALID, "invalid sizes B=%d F=%d H=%d W=%d", B, F, H, W);
   if (B > 65535) return fail(DIBR_E_INVALID, "batch %d > 65535 not supported", B);
   if (H > 32768 || W > 32768) return fail(DIBR_E_INVALID, "image %dx%d too large", H, W);
   memset(&p, 0, sizeof(p));
   p.B = B; p.F = F; p.H = H; p.W = W;
+  p.grid_mult = mult;
+  if (mult == mult) p.grid = make_grid(mult, W, H);
   int k = 5;
   while ((int64_t)((W + (1 << k) - 1) >> k) * ((H + (1 << k) - 1) >> k) > 1024) k++;
   p.bin_log2 = k;
@@ -298,7 +300,7 @@ extern "C" int dibr_rasterize_fwd(int B, int F, int H, int W, int D, const float
                                   void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   Plan p;
-  int rc = make_plan(B, F, H, W, p);
+  int rc = make_plan(B, F, H, W, p, multiplier);
   if (rc) return rc;
   if ((rc = check_common(multiplier))) return rc;
   if (D < 0) return fail(DIBR_E_INVALID, "feat_dim < 0");
@@ -367,7 +369,7 @@ static int run_soft_forward(const SoftArgs& a, const Plan& p, int64_t* needed_ho
 static int soft_common(int B, int F, int H, int W, const float* img, int prescaled,
                        const float* bboxes, const int64_t* sel, int K, float multiplier,
                        float box_margin, Plan& p, BinJob& job) {
-  int rc = make_plan(B, F, H, W, p);
+  int rc = make_plan(B, F, H, W, p, multiplier);
   if (rc) return rc;
   if ((rc = check_common(multiplier))) return rc;
   if (K < 0) return fail(DIBR_E_INVALID, "knum < 0");
@@ -508,7 +510,7 @@ extern "C" int dibr_render_fwd(int B, int F, int H, int W, int D, const float* z
                                int64_t cap_p, int64_t* needed_host, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   Plan p;
-  int rc = make_plan(B, F, H, W, p);
+  int rc = make_plan(B, F, H, W, p, multiplier);
   if (rc) return rc;
   if ((rc = check_common(multiplier))) return rc;
   if (D < 0 || K < 0) return fail(DIBR_E_INVALID, "feat_dim / knum < 0");
@@ -546,7 +548,7 @@ extern "C" int dibr_packed_rasterize_fwd_f64(
     int64_t ws_bytes, int64_t cap_r, int64_t* needed_host, void* stream) {
   cudaStream_t st = (cudaStream_t)stream;
   Plan p;
-  int rc = make_plan(B, F, H, W, p);
+  int rc = make_plan(B, F, H, W, p, multiplier);
   if (rc) return rc;
   if ((rc = check_common(multiplier))) return rc;
   if (D < 0) return fail(DIBR_E_INVALID, "feat_dim < 0");

@@ -58,7 +58,7 @@ bin_walk_kernel(const BinJobs jobs, const Plan p) {
   const int chunk = blockIdx.x * kBinWarps + warp;
   if (chunk >= p.nchunks) return;  // whole warp leaves; no block-wide barrier below
   int* hist = s_hist + warp * p.NB;
-  const Grid g = make_grid(job.mult, p.W, p.H);
+  const Grid g = plan_grid(p, job.mult);
   const long long row = (long long)b * p.NB;  // first bin row of this view in mat/start
 
   int lo_bin = p.NB, hi_bin = -1;

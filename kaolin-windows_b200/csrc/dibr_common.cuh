@@ -24,8 +24,32 @@ namespace dibr {
 // Screen hierarchy: bin (bin_px = 32 << k, <= 1024 bins per view, the binning
 // granularity) >= block (min(bin_px, 64): one CTA of the rasterizer / soft mask)
 // >= tile 16x16 (one warp of the soft mask) >= region 8x4 (one pixel per lane).
+struct Grid {
+  float xs, ys;        // fl(mult / W), fl(mult / H)       (rasterization_cuda.cu:85-86)
+  float inv_xs, inv_ys;
+  int W, H;
+};
+
+__host__ __device__ inline Grid make_grid(float mult, int W, int H) {
+  Grid g;
+  g.W = W;
+  g.H = H;
+#ifdef __CUDA_ARCH__
+  g.xs = __fdiv_rn(mult, (float)W);
+  g.ys = __fdiv_rn(mult, (float)H);
+#else
+  g.xs = mult / (float)W;
+  g.ys = mult / (float)H;
+#endif
+  g.inv_xs = 1.0f / g.xs;
+  g.inv_ys = 1.0f / g.ys;
+  return g;
+}
+
 struct Plan {
   int B, F, H, W;
+  Grid grid;               // make_grid(grid_mult, W, H), formed once on the host (IEEE
+  float grid_mult;         // divisions, bit-identical to the device's); NaN = not set
   int bin_log2, nbx, nby, NB;  // bins
   int blk_log2, nkx, nky;      // blocks (CTA footprint)
   int S, nchunks;              // faces per binning chunk (one warp), chunks per view
@@ -259,26 +283,10 @@ __device__ __forceinline__ bool lpt_block(const BinJob& j, const Plan& p, int su
 }
 
 // ------------------------------------------------------------------------ pixel grid
-struct Grid {
-  float xs, ys;        // fl(mult / W), fl(mult / H)       (rasterization_cuda.cu:85-86)
-  float inv_xs, inv_ys;
-  int W, H;
-};
-
-__host__ __device__ inline Grid make_grid(float mult, int W, int H) {
-  Grid g;
-  g.W = W;
-  g.H = H;
-#ifdef __CUDA_ARCH__
-  g.xs = __fdiv_rn(mult, (float)W);
-  g.ys = __fdiv_rn(mult, (float)H);
-#else
-  g.xs = mult / (float)W;
-  g.ys = mult / (float)H;
-#endif
-  g.inv_xs = 1.0f / g.xs;
-  g.inv_ys = 1.0f / g.ys;
-  return g;
+// the pixel grid of a kernel: the plan's if it was formed for this multiplier
+__device__ __forceinline__ Grid plan_grid(const Plan& p, float mult) {
+  if (p.grid_mult == mult) return p.grid;
+  return make_grid(mult, p.W, p.H);
 }
 
 __device__ __forceinline__ float pix_x(const Grid& g, int ix) {

@@ -31,7 +31,7 @@ raster_forward_f64_kernel(const RasterF64Args a, const Plan p) {
   const int tx0 = blockIdx.x * kTile, ty0 = blockIdx.y * kTile;
   const int ix = tx0 + (tid & (kTile - 1)), iy = ty0 + (tid / kTile);
   const bool inside = ix < p.W && iy < p.H;
-  const Grid g = make_grid(a.job.mult, p.W, p.H);
+  const Grid g = plan_grid(p, a.job.mult);
   // :85-86 float / int division and float * int product, widened afterwards
   const double x0 = (double)pix_x(g, min(ix, p.W - 1)), y0 = (double)pix_y(g, min(iy, p.H - 1));
   const long long row = (long long)b * p.NB + tile_bin(p, tx0, ty0);
@@ -156,7 +156,7 @@ softmask_forward_f64_kernel(const SoftF64Args a, const Plan p) {
   const int tx0 = blockIdx.x * kTile, ty0 = blockIdx.y * kTile;
   const int ix = tx0 + (tid & (kTile - 1)), iy = ty0 + (tid / kTile);
   const bool inside = ix < p.W && iy < p.H;
-  const Grid g = make_grid(a.job.mult, p.W, p.H);
+  const Grid g = plan_grid(p, a.job.mult);
   const double x0 = (double)pix_x(g, min(ix, p.W - 1)), y0 = (double)pix_y(g, min(iy, p.H - 1));
   const long long pix = ((long long)b * p.H + min(iy, p.H - 1)) * p.W + min(ix, p.W - 1);
   bool open = false;

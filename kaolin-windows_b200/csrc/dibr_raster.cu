@@ -82,7 +82,7 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
   if (!lpt_block(a.job, p, BLK_LOG2, blockIdx.x, b, bxi, byi)) return;
   const int bx0 = bxi << BLK_LOG2, by0 = byi << BLK_LOG2;
   const int bx1 = min(bx0 + BLK, p.W) - 1, by1 = min(by0 + BLK, p.H) - 1;
-  const Grid g = make_grid(a.job.mult, p.W, p.H);
+  const Grid g = plan_grid(p, a.job.mult);
   const int tid = threadIdx.x, lane = lane_id(), warp = tid >> 5;
   // local frame of the conservative span culling: origin = centre of the block's first
   // pixel, pixel (rx, ry) at (rx * pitch_x, -ry * pitch_y)

@@ -71,7 +71,7 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
   const int b = blockIdx.z;
   const int bx0 = blockIdx.x << BLK_LOG2, by0 = blockIdx.y << BLK_LOG2;
   const int bx1 = min(bx0 + BLK, p.W) - 1, by1 = min(by0 + BLK, p.H) - 1;
-  const Grid g = make_grid(a.job.mult, p.W, p.H);
+  const Grid g = plan_grid(p, a.job.mult);
   const int K = min(a.K, 0xfffe);
   const int lx = lane & 7, ly = lane >> 3;
   const int nrx = (p.W + 7) >> 3, nry = (p.H + 3) >> 2;  // regions of a view

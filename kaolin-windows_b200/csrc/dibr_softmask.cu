@@ -195,7 +195,7 @@ __device__ __forceinline__ void soft_block(const SoftArgs& a, const Plan& p,
   constexpr int CH = kSoftChunk;
   const int tid = threadIdx.x, lane = lane_id(), warp = tid >> 5;
   const int bx0 = bxi << BLK_LOG2, by0 = byi << BLK_LOG2;
-  const Grid g = make_grid(a.job.mult, p.W, p.H);
+  const Grid g = plan_grid(p, a.job.mult);
   const float mult = a.job.mult;
   const float four_mm = __fmul_rn(__fmul_rn(mult, 4.f), mult);
   const int K = min(a.K, 0xfffe);
@@ -510,7 +510,7 @@ softmask_pairs_eval_kernel(const SoftArgs a, const Plan p) {
   if (pairs_overflowed(pb)) return;
   const int lane = lane_id();
   const unsigned nchunk = min(*pb.nchunk, 3u * (unsigned)pb.cap);
-  const Grid g = make_grid(a.job.mult, p.W, p.H);
+  const Grid g = plan_grid(p, a.job.mult);
   const float mult = a.job.mult;
   const float four_mm = __fmul_rn(__fmul_rn(mult, 4.f), mult);
   for (unsigned w = blockIdx.x * kPairWarps + (threadIdx.x >> 5); w < nchunk;
@@ -611,7 +611,7 @@ softmask_pairs_grad_kernel(const SoftArgs a, const Plan p) {
   if (pairs_overflowed(pb)) return;
   const int lane = lane_id();
   const unsigned nchunk = min(*pb.nchunk, 3u * (unsigned)pb.cap);
-  const Grid g = make_grid(a.job.mult, p.W, p.H);
+  const Grid g = plan_grid(p, a.job.mult);
   const float mult = a.job.mult;
   for (unsigned w = blockIdx.x * kPairWarps + (threadIdx.x >> 5); w < nchunk;
        w += gridDim.x * kPairWarps) {
