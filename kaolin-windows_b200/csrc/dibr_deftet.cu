@@ -41,7 +41,7 @@ namespace {
 
 constexpr int kLevels = 10;       // G = 1 << level, level 0..9
 constexpr int kWideCells = 64;    // a face spanning more cells goes to the wide list
-constexpr int kListCap = 8;       // list entries available per face and view (bounds the workspace)
+constexpr int kListCap = 16;      // list entries available per face and view (bounds the workspace)
 constexpr float kCostBuild = 30.f, kCostTest = 40.f;   // thread-instructions per entry / test
 
 // ------------------------------------------------------------------ exact arithmetic
@@ -265,47 +265,68 @@ __global__ void deftet_choose_kernel(const ViewStats* stats, CellGrid* grids, in
 }
 
 // FILL = false: count entries per cell, wide faces go straight to the wide list;
-// FILL = true : write the face ids (cell_count doubles as the cursor, rebuilt to the count)
+// FILL = true : write the face ids (cell_count doubles as the cursor, rebuilt to the count).
+// Each CTA owns a contiguous run of a view's faces.  Grids of up to kSmemCells cells are
+// binned through a CTA-private histogram in shared memory: shared atomics per (face, cell),
+// then ONE global atomic per touched cell and CTA, issued for consecutive cells by
+// consecutive lanes (a warp's 32 atomics on one line travel as one transaction) -- scattered
+// global atomics on a few thousand counters were the whole cost of the direct form (6 %
+// issue-active).  In the fill the CTA reserves its share of every cell's segment the same
+// way and deals the slots out with shared cursors.  Finer grids have counters enough to
+// take the atomics directly.
+constexpr int kSmemCells = 16384;
 template <typename T, bool FILL>
 __global__ void __launch_bounds__(256) deftet_bin_kernel(const DeftetArgs<T> a) {
+  extern __shared__ int s_hist[];
   const int b = blockIdx.y;
   const CellGrid g = a.grids[b];
   if (g.empty) return;
   int* cnt = a.cell_count + (long long)b * a.cells_cap;
   const int* start = a.cell_start + (long long)b * a.cells_cap;
   int* list = a.list + (long long)b * kListCap * a.F;
-  for (int f = blockIdx.x * blockDim.x + threadIdx.x; f < a.F; f += gridDim.x * blockDim.x) {
-    float fx0, fy0, fx1, fy1;
-    if (!face_box_f(a, g, b, f, fx0, fy0, fx1, fy1)) continue;
-    const int cx0 = cell_of(fx0, g.lox, g.invx, g.g), cx1 = cell_of(fx1, g.lox, g.invx, g.g);
-    const int cy0 = cell_of(fy0, g.loy, g.invy, g.g), cy1 = cell_of(fy1, g.loy, g.invy, g.g);
-    if ((cx1 - cx0 + 1) * (cy1 - cy0 + 1) > kWideCells) {
-      if (!FILL) a.wide[(long long)b * a.F + atomicAdd(&a.stats[b].wide, 1u)] = f;
-      continue;
-    }
-    const int nx = cx1 - cx0 + 1, tot = nx * (cy1 - cy0 + 1);
-    if (!FILL) {
-      for (int cy = cy0; cy <= cy1; cy++)
-        for (int cx = cx0; cx <= cx1; cx++) atomicAdd(cnt + cy * g.g + cx, 1);   // no return: RED
-      continue;
-    }
-    // four cells at a time: the cursor atomics (and the loads of the segment starts) of a
-    // group are issued back to back, the stores that need their results come after
-    for (int t = 0; t < tot; t += 4) {
-      int pos[4];
-#pragma unroll
-      for (int u = 0; u < 4; u++) {
-        pos[u] = -1;
-        if (t + u < tot) {
-          const int yy = (t + u) / nx;
-          const int c = (cy0 + yy) * g.g + cx0 + (t + u - yy * nx);
-          pos[u] = start[c] + atomicAdd(cnt + c, 1);
-        }
+  const int ncell = g.g * g.g;
+  const bool priv = ncell <= kSmemCells;
+  const int per = (a.F + gridDim.x - 1) / gridDim.x;
+  const int f_lo = blockIdx.x * per, f_hi = min(f_lo + per, a.F);
+  if (f_lo >= f_hi) return;
+  if (priv) {
+    for (int c = threadIdx.x; c < ncell; c += blockDim.x) s_hist[c] = 0;
+    __syncthreads();
+  }
+  // pass 0 (both modes): count into the private histogram (or straight into the counters);
+  // pass 1 (fill, private form only): deal the reserved slots out
+  for (int pass = 0; pass < ((FILL && priv) ? 2 : 1); pass++) {
+    for (int f = f_lo + threadIdx.x; f < f_hi; f += blockDim.x) {
+      float fx0, fy0, fx1, fy1;
+      if (!face_box_f(a, g, b, f, fx0, fy0, fx1, fy1)) continue;
+      const int cx0 = cell_of(fx0, g.lox, g.invx, g.g), cx1 = cell_of(fx1, g.lox, g.invx, g.g);
+      const int cy0 = cell_of(fy0, g.loy, g.invy, g.g), cy1 = cell_of(fy1, g.loy, g.invy, g.g);
+      if ((cx1 - cx0 + 1) * (cy1 - cy0 + 1) > kWideCells) {
+        if (!FILL) a.wide[(long long)b * a.F + atomicAdd(&a.stats[b].wide, 1u)] = f;
+        continue;
       }
-#pragma unroll
-      for (int u = 0; u < 4; u++)
-        if (pos[u] >= 0) list[pos[u]] = f;
+      for (int cy = cy0; cy <= cy1; cy++)
+        for (int cx = cx0; cx <= cx1; cx++) {
+          const int c = cy * g.g + cx;
+          if (priv) {
+            if (pass == 0) atomicAdd(&s_hist[c], 1);
+            else list[atomicAdd(&s_hist[c], 1)] = f;
+          } else {
+            if (FILL) list[start[c] + atomicAdd(cnt + c, 1)] = f;
+            else atomicAdd(cnt + c, 1);
+          }
+        }
     }
+    if (!priv || pass == 1) break;
+    __syncthreads();
+    // flush: consecutive lanes, consecutive cells
+    for (int c = threadIdx.x; c < ncell; c += blockDim.x) {
+      const int h = s_hist[c];
+      if (h == 0) continue;
+      if (FILL) s_hist[c] = start[c] + atomicAdd(cnt + c, h);   // first slot of this CTA's share
+      else atomicAdd(cnt + c, h);
+    }
+    if (FILL) __syncthreads();
   }
 }
 
@@ -363,42 +384,55 @@ __global__ void __launch_bounds__(1024) deftet_scan_kernel(const CellGrid* grids
 }
 
 // ------------------------------------------------------------------ per-sample work
-// shared-memory staging of one warp's hits
+// shared-memory staging of one warp: the hits it keeps, and a queue of the candidates that
+// passed the box test and wait for the edge test (run 32 at a time, every lane busy)
+constexpr int kQueue = 64;
 template <typename T>
 struct HitBuf {
-  T* depth; T* w0; T* w1; int* face; int* perm;
+  T* depth; T* w0; T* w1; T* qv; int* face; int* perm; int* qf;
 };
 
 template <typename T>
+__host__ __device__ inline size_t hitbuf_bytes(int K, int n2) {
+  const size_t b = (size_t)K * (3 * sizeof(T) + sizeof(int)) + (size_t)n2 * sizeof(int) +
+                   (size_t)kQueue * (6 * sizeof(T) + sizeof(int));
+  return (b + 15) & ~(size_t)15;
+}
+
+template <typename T>
 __device__ __forceinline__ HitBuf<T> carve(unsigned char* base, int warp, int K, int n2) {
-  const size_t per_warp = (size_t)K * (3 * sizeof(T) + sizeof(int)) + (size_t)n2 * sizeof(int);
-  unsigned char* p = base + (size_t)warp * ((per_warp + 15) & ~(size_t)15);
+  unsigned char* p = base + (size_t)warp * hitbuf_bytes<T>(K, n2);
   HitBuf<T> h;
   h.depth = reinterpret_cast<T*>(p);
   h.w0 = h.depth + K;
   h.w1 = h.w0 + K;
-  h.face = reinterpret_cast<int*>(h.w1 + K);
+  h.qv = h.w1 + K;                       // [6][kQueue]
+  h.face = reinterpret_cast<int*>(h.qv + 6 * kQueue);
   h.perm = h.face + K;
+  h.qf = h.perm + n2;
   return h;
 }
 
-// the reference's test of one face against one sample (deftet_cuda.cu:120-163)
+// the reference's test of one face against one sample (deftet_cuda.cu:120-163), in two
+// parts: the half-open box test (:126) ...
 template <typename T>
-__device__ __forceinline__ bool deftet_test(const DeftetArgs<T>& a, long long bf, T x0, T y0,
-                                            T dmin, T dmax, T eps_t, T& w0, T& w1, T& depth) {
-  T v[6];
-  load_img6(a.img, bf, v);
+__device__ __forceinline__ bool deftet_box_test(const DeftetArgs<T>& a, long long bf,
+                                                const T (&v)[6], T x0, T y0) {
   if (a.bbox) {
     const T* q = a.bbox + bf * 4;
-    if (!(x0 >= __ldg(q) && x0 < __ldg(q + 2) && y0 >= __ldg(q + 1) && y0 < __ldg(q + 3)))
-      return false;
-  } else {
-    // min3 / max3 drop NaN where torch.min / torch.max keep it: a face with a NaN
-    // coordinate that slips through here gets NaN weights below and is rejected there
-    if (!(x0 >= min3(v[0], v[2], v[4]) && x0 < max3(v[0], v[2], v[4]) &&
-          y0 >= min3(v[1], v[3], v[5]) && y0 < max3(v[1], v[3], v[5])))
-      return false;
+    return x0 >= __ldg(q) && x0 < __ldg(q + 2) && y0 >= __ldg(q + 1) && y0 < __ldg(q + 3);
   }
+  // min3 / max3 drop NaN where torch.min / torch.max keep it: a face with a NaN coordinate
+  // that slips through here gets NaN weights in the edge test and is rejected there
+  return x0 >= min3(v[0], v[2], v[4]) && x0 < max3(v[0], v[2], v[4]) &&
+         y0 >= min3(v[1], v[3], v[5]) && y0 < max3(v[1], v[3], v[5]);
+}
+
+// ... and the edge functions, depth and range test (:131-163)
+template <typename T>
+__device__ __forceinline__ bool deftet_edge_test(const DeftetArgs<T>& a, long long bf,
+                                                 const T (&v)[6], T x0, T y0, T dmin, T dmax,
+                                                 T eps_t, T& w0, T& w1, T& depth) {
   const T aex = sub_rn(v[0], x0), aey = sub_rn(v[1], y0);
   const T bex = sub_rn(v[2], x0), bey = sub_rn(v[3], y0);
   const T cex = sub_rn(v[4], x0), cey = sub_rn(v[5], y0);
@@ -449,7 +483,66 @@ __global__ void __launch_bounds__(128) deftet_render_kernel(const DeftetArgs<T> 
 
   int n = 0;            // hits held (warp uniform)
   int maxf = -1, maxs = -1;   // largest held face id and its slot, valid once the buffer is full
+  int qn = 0;           // candidates queued for the edge test (warp uniform)
   const bool live = !g.empty && !(x0 != x0) && !(y0 != y0);
+
+  // edge test of `cnt` queued candidates starting at queue position q0, hits appended
+  auto drain = [&](int q0, int cnt) {
+    int f = -1;
+    T w0 = 0, w1 = 0, depth = 0;
+    bool hit = false;
+    if (lane < cnt) {
+      const int q = q0 + lane;
+      f = h.qf[q];
+      T v[6];
+#pragma unroll
+      for (int k = 0; k < 6; k++) v[k] = h.qv[k * kQueue + q];
+      hit = deftet_edge_test(a, face0 + f, v, x0, y0, dmin, dmax, eps_t, w0, w1, depth);
+    }
+    unsigned m = __ballot_sync(DIBR_FULL_MASK, hit);
+    if (m == 0u) return;
+    const int c = __popc(m);
+    if (n + c <= K) {
+      if (hit) {
+        const int s = n + __popc(m & lanemask_lt());
+        h.face[s] = f; h.depth[s] = depth; h.w0[s] = w0; h.w1[s] = w1;
+      }
+      n += c;
+      return;
+    }
+    // more hits than slots: keep the K smallest face ids (the reference keeps the first
+    // K in ascending face order)
+    while (m) {
+      const int src = __ffs(m) - 1;
+      m &= m - 1;
+      const int bf_ = __shfl_sync(DIBR_FULL_MASK, f, src);
+      const T bd = __shfl_sync(DIBR_FULL_MASK, depth, src);
+      const T b0 = __shfl_sync(DIBR_FULL_MASK, w0, src);
+      const T b1 = __shfl_sync(DIBR_FULL_MASK, w1, src);
+      int s = -1;
+      if (n < K) {
+        s = n++;
+        maxs = -1;
+      } else {
+        if (maxs < 0) {
+          __syncwarp();
+          int mf = -1, ms = -1;
+          for (int k = lane; k < K; k += 32) {
+            const int t = h.face[k];
+            if (t > mf) { mf = t; ms = k; }
+          }
+          const int top = __reduce_max_sync(DIBR_FULL_MASK, mf);
+          const unsigned who = __ballot_sync(DIBR_FULL_MASK, mf == top);
+          maxs = __shfl_sync(DIBR_FULL_MASK, ms, __ffs(who) - 1);
+          maxf = top;
+        }
+        if (bf_ < maxf) { s = maxs; maxs = -1; }
+      }
+      if (s >= 0 && lane == 0) { h.face[s] = bf_; h.depth[s] = bd; h.w0[s] = b0; h.w1[s] = b1; }
+      __syncwarp();
+    }
+  };
+
   for (int pass = 0; pass < 2 && live; pass++) {
     const int* lst;
     int len;
@@ -465,74 +558,51 @@ __global__ void __launch_bounds__(128) deftet_render_kernel(const DeftetArgs<T> 
     for (int base = 0; base < len; base += 32) {
       const int i = base + lane;
       int f = -1;
-      T w0 = 0, w1 = 0, depth = 0;
-      bool hit = false;
+      T v[6];
+      bool in_box = false;
       if (i < len) {
         f = __ldg(lst + i);
-        hit = deftet_test(a, face0 + f, x0, y0, dmin, dmax, eps_t, w0, w1, depth);
+        load_img6(a.img, face0 + f, v);
+        in_box = deftet_box_test(a, face0 + f, v, x0, y0);
       }
-      unsigned m = __ballot_sync(DIBR_FULL_MASK, hit);
+      const unsigned m = __ballot_sync(DIBR_FULL_MASK, in_box);
       if (m == 0u) continue;
-      const int cnt = __popc(m);
-      if (n + cnt <= K) {
-        if (hit) {
-          const int s = n + __popc(m & lanemask_lt());
-          h.face[s] = f; h.depth[s] = depth; h.w0[s] = w0; h.w1[s] = w1;
-        }
-        n += cnt;
-        continue;
+      if (in_box) {
+        const int q = qn + __popc(m & lanemask_lt());
+        h.qf[q] = f;
+#pragma unroll
+        for (int k = 0; k < 6; k++) h.qv[k * kQueue + q] = v[k];
       }
-      // more hits than slots: keep the K smallest face ids (the reference keeps the first
-      // K in ascending face order)
-      while (m) {
-        const int src = __ffs(m) - 1;
-        m &= m - 1;
-        const int bf_ = __shfl_sync(DIBR_FULL_MASK, f, src);
-        const T bd = __shfl_sync(DIBR_FULL_MASK, depth, src);
-        const T b0 = __shfl_sync(DIBR_FULL_MASK, w0, src);
-        const T b1 = __shfl_sync(DIBR_FULL_MASK, w1, src);
-        int s = -1;
-        if (n < K) {
-          s = n++;
-          maxs = -1;
-        } else {
-          if (maxs < 0) {
-            __syncwarp();
-            int mf = -1, ms = -1;
-            for (int k = lane; k < K; k += 32) {
-              const int t = h.face[k];
-              if (t > mf) { mf = t; ms = k; }
-            }
-            const int top = __reduce_max_sync(DIBR_FULL_MASK, mf);
-            const unsigned who = __ballot_sync(DIBR_FULL_MASK, mf == top);
-            maxs = __shfl_sync(DIBR_FULL_MASK, ms, __ffs(who) - 1);
-            maxf = top;
-          }
-          if (bf_ < maxf) { s = maxs; maxs = -1; }
-        }
-        if (s >= 0 && lane == 0) { h.face[s] = bf_; h.depth[s] = bd; h.w0[s] = b0; h.w1[s] = b1; }
+      qn += __popc(m);
+      __syncwarp();
+      if (qn >= 32) {
+        qn -= 32;
+        drain(qn, 32);
         __syncwarp();
       }
     }
   }
+  if (qn > 0) drain(0, qn);
   __syncwarp();
 
-  // order the held hits.  Up to 32: every lane ranks its own hit against the others
-  // (shuffles); beyond: bitonic network over slot numbers in shared memory (padding -1 last)
-  if (n > 1 && n <= 32) {
-    const bool mine = lane < n;
-    const T di = mine ? h.depth[lane] : (T)0;
-    const int fi = mine ? h.face[lane] : 0;
-    int rank = 0;
-    for (int j = 0; j < n; j++) {
-      const T dj = __shfl_sync(DIBR_FULL_MASK, di, j);
-      const int fj = __shfl_sync(DIBR_FULL_MASK, fi, j);
-      rank += RAW ? (fj < fi) : (dj > di || (dj == di && fj < fi));
+  // order the held hits.  Up to 128: every lane ranks its own hits against all the others
+  // (broadcast reads from shared memory, n compares per hit); beyond: bitonic network over
+  // slot numbers in shared memory (padding -1 last)
+  if (n > 1 && n <= 128) {
+    for (int i = lane; i < n; i += 32) {
+      const T di = h.depth[i];
+      const int fi = h.face[i];
+      int rank = 0;
+      for (int j = 0; j < n; j++) {
+        const T dj = h.depth[j];
+        const int fj = h.face[j];
+        rank += RAW ? (fj < fi) : (dj > di || (dj == di && fj < fi));
+      }
+      h.perm[rank] = i;
     }
-    if (mine) h.perm[rank] = lane;
     __syncwarp();
-  } else if (n > 32) {
-    int n2 = 64;
+  } else if (n > 128) {
+    int n2 = 256;
     while (n2 < n) n2 <<= 1;
     for (int k = lane; k < n2; k += 32) h.perm[k] = k < n ? k : -1;
     __syncwarp();
@@ -763,7 +833,6 @@ int deftet_forward(bool raw, int B, int F, int P, int K, int D, const void* z, c
   DEF_CUDA(cudaMemsetAsync(base, 0, (size_t)L.zero_bytes, st));
   {
     const int pb = (int)std::min<int64_t>((P + 255) / 256, 64);
-    const int fb = (int)std::max<int64_t>(1, std::min<int64_t>((F + 255) / 256, (148 * 8 + B - 1) / B));
     if (F > 0) {
       deftet_bounds_kernel<T><<<dim3(pb, B), 256, 0, st>>>(a);
       const int lb = (int)std::max<int64_t>(1, std::min<int64_t>((F + 1023) / 1024, (148 * 4 + B - 1) / B));
@@ -771,15 +840,22 @@ int deftet_forward(bool raw, int B, int F, int P, int K, int D, const void* z, c
     }
     deftet_choose_kernel<<<(B + 127) / 128, 128, 0, st>>>(a.stats, a.grids, B, P, F, a.cells_cap);
     if (F > 0) {
-      deftet_bin_kernel<T, false><<<dim3(fb, B), 256, 0, st>>>(a);
+      const size_t hist = (size_t)kSmemCells * sizeof(int);
+      // per device and cheap: set on every call
+      DEF_CUDA(cudaFuncSetAttribute(deftet_bin_kernel<T, false>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist));
+      DEF_CUDA(cudaFuncSetAttribute(deftet_bin_kernel<T, true>,
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)hist));
+      // three 64-KB CTAs per SM; a CTA's run of faces stays long enough to amortise its flush
+      const int bb = (int)std::max<int64_t>(1, std::min<int64_t>((F + 1023) / 1024, (148 * 3 + B - 1) / B));
+      deftet_bin_kernel<T, false><<<dim3(bb, B), 256, hist, st>>>(a);
       deftet_scan_kernel<<<B, 1024, 0, st>>>(a.grids, a.cell_start, a.cell_count, a.cells_cap);
-      deftet_bin_kernel<T, true><<<dim3(fb, B), 256, 0, st>>>(a);
+      deftet_bin_kernel<T, true><<<dim3(bb, B), 256, hist, st>>>(a);
     }
     DEF_CUDA(cudaGetLastError());
   }
   // one warp per sample; warps per CTA limited by the staging of K hits per warp
-  size_t per_warp = (size_t)K * (3 * sizeof(T) + sizeof(int)) + (size_t)n2 * sizeof(int);
-  per_warp = (per_warp + 15) & ~(size_t)15;
+  const size_t per_warp = hitbuf_bytes<T>(K, n2);
   int warps = (int)std::min<size_t>(4, (200 * 1024) / per_warp);
   if (warps < 1) return fail(DIBR_E_INVALID, "knum %d needs %zu bytes of shared memory per sample, "
                              "more than an SM has", K, per_warp);

@@ -191,9 +191,9 @@ def random_soup(F, B, dtype, seed, size=0.6):
 @pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
 @pytest.mark.parametrize("F,size,knum", [(12000, 0.6, 300), (3000, 0.6, 10), (3000, 0.6, 1),
                                          (20000, 0.05, 30), (500, 3.0, 8), (5000, 0.2, 33),
-                                         (12000, 0.6, 40)])
+                                         (12000, 0.6, 40), (40000, 0.6, 300)])
 def test_soup_vs_ref(kal, ref, dtype, F, size, knum):
-    """Hundreds of layers per point (bitonic network beyond one warp), more hits than knum
+    """Hundreds of layers per point (rank sort up to 128 hits, bitonic network beyond), more hits than knum
     (the first knum by face index must survive), faces larger than the sample domain (wide
     list), tiny faces (fine grid)."""
     B, P = 2, 777
@@ -206,7 +206,7 @@ def test_soup_vs_ref(kal, ref, dtype, F, size, knum):
     if knum in (10, 1, 8, 40):
         assert int(hits.max()) == knum        # the cut is exercised
     if knum == 300:
-        assert int(hits.max()) > 32
+        assert int(hits.max()) > (128 if F == 40000 else 32)   # bitonic network / rank sort
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.float64])

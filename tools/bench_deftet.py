@@ -69,12 +69,15 @@ def case(name, z, img, feat, P, knum, lo, hi):
 
 
 res = {}
-inp = wl.make_config("cfg2_70k_8x512", device=dev)
-n, r = case("cfg2 mesh, 16384 points/view, knum 30", inp["face_vertices_z"],
-            inp["face_vertices_image"], inp["face_features"], 16384, 30, -10., 0.)
-res[n] = r
-z, img, feat = random_soup(100000, 2, torch.float32, seed=0, size=0.15)
-n, r = case("soup 100k faces, 16384 points/view, knum 100", z, img, feat[..., :3].contiguous(),
-            16384, 100, -10., 0.)
-res[n] = r
+ONLY = sys.argv[1] if len(sys.argv) > 1 else ""      # "cfg2" | "soup" | "" (both)
+inp = wl.make_config("cfg2_70k_8x512", device=dev) if ONLY != "soup" else None
+if inp is not None:
+    n, r = case("cfg2 mesh, 16384 points/view, knum 30", inp["face_vertices_z"],
+                inp["face_vertices_image"], inp["face_features"], 16384, 30, -10., 0.)
+    res[n] = r
+if ONLY != "cfg2":
+    z, img, feat = random_soup(100000, 2, torch.float32, seed=0, size=0.15)
+    n, r = case("soup 100k faces, 16384 points/view, knum 100", z, img,
+                feat[..., :3].contiguous(), 16384, 100, -10., 0.)
+    res[n] = r
 print(json.dumps({"op": "deftet_sparse_render", "results": res}))
