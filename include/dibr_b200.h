@@ -349,7 +349,8 @@ DIBR_API int dibr_mask_iou_bwd(int batch, int64_t num_pixels, const float* lhs_m
  * grad_face_features (B, F, 3, D) (deftet.cpp:109-165).
  * The workspace (dibr_deftet_workspace_bytes, 256-byte aligned) holds the per-view cell grid
  * and face lists; its size is a bound, there is no capacity protocol and no host sync.
- * knum is limited by shared memory: knum * (4 + 3 * sizeof(T)) + 4 * pow2ceil(knum) <= 200 KiB.
+ * knum is limited by shared memory: knum * (4 + 3 * sizeof(T)) + 4 * pow2ceil(knum) + 64 * (4 + 6 * sizeof(T))
+ * <= 200 KiB.
  * ------------------------------------------------------------------------------------- */
 #define DIBR_F32 0
 #define DIBR_F64 1
