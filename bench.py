@@ -182,7 +182,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--e2e-chunks", type=int, default=2,
+    ap.add_argument("--e2e-chunks", type=int, default=1,
                     help="view chunks the e2e loop overlaps H2D copies and rendering with")
     ap.add_argument("--no-cuda-graph", action="store_true",
                     help="eager launches instead of dibr_rasterization(cuda_graph=True)")
@@ -298,8 +298,9 @@ def main():
 
     # The user-level loop a host-fed renderer runs, with the prefetch any data loader does:
     # device inputs are double buffered and step i+1's batch goes over on a copy stream while
-    # step i renders (the first step of the region has nothing to hide behind, so its batch
-    # goes over in view chunks and rendering starts on the first chunk).  Every step's H2D and
+    # step i renders (the first step of the region has nothing to hide behind; with
+    # --e2e-chunks > 1 its batch goes over in view chunks and rendering starts on the first
+    # chunk -- off by default, one odd step only adds captures).  Every step's H2D and
     # the D2H read of its loss are inside the timed region; the loss of step i is read before
     # step i+1 is issued, so at most one batch is in flight ahead of the compute.
     n_chunks = max(1, min(args.e2e_chunks, B))
@@ -356,9 +357,13 @@ def main():
         slot_free[slot] = done
         return total
 
+    e2e_trace = [] if os.environ.get("DIBR_BENCH_E2E_TRACE") else None
+
     def e2e_run(n):
-        ready = e2e_copy(0, True)
+        ready = e2e_copy(0, n_chunks > 1)
         for i in range(n):
+            if e2e_trace is not None:
+                e2e_trace.append(time.perf_counter())
             nxt = e2e_copy((i + 1) & 1, False) if i + 1 < n else None
             flush.zero_()                      # L2 flush, inside the timed span, not subtracted
             total = e2e_compute(i & 1, ready)
@@ -376,6 +381,9 @@ def main():
     if world > 1:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
     e2e_s = max(float(e2e_t.item()), 1e-9) / args.steps
+    if e2e_trace is not None and rank == 0:
+        ts = e2e_trace[-args.steps:]
+        print("e2e step starts (ms):", [round((t - ts[0]) * 1e3, 2) for t in ts], file=sys.stderr)
     e2e_val = world * B * P / e2e_s / 1e6
 
     if rank != 0:

@@ -373,6 +373,26 @@ DIBR_API int dibr_deftet_bwd(int dtype, int batch, int num_faces, int num_points
                     const void* face_vertices_image, const void* face_features, float eps,
                     void* grad_face_vertices_image, void* grad_face_features, void* stream);
 
+/* ---------------------------------------------------------------------------------------
+ * The path's only exchange: SUM all-reduce of the shared mesh's vertex-level
+ * gradient buffer across the GPUs of one NVSwitch box, as our own one-shot kernel over peer
+ * memory (csrc/dibr_peer.cu) instead of a collective-library call.  `buffers[r]` /
+ * `signal_pads[r]` (host arrays of `world` addresses) are rank r's buffer of a symmetric
+ * allocation and its pad of 32-bit flags as mapped into THIS process (the Python binding
+ * takes them from torch.distributed._symmetric_memory); flag rows 8 and 9 of the pads are
+ * used.  Per exchange: dibr_peer_signal(mode 1) waits until every peer has finished reading
+ * this rank's buffer of the previous exchange, the caller refills buffers[rank], and
+ * dibr_peer_allreduce writes out[i] = sum over r of buffers[r][i] (same order on every rank:
+ * bit-identical results) and tells the peers it is done reading.  dibr_peer_signal(mode 0)
+ * primes the "done" flags once after set-up.  `sync` = int[2] of zeros in local device
+ * memory.  Every rank must issue the same sequence of calls (as with any collective).
+ * ------------------------------------------------------------------------------------- */
+DIBR_API int dibr_peer_signal(int rank, int world, const int64_t* signal_pads, int mode,
+                     void* stream);
+DIBR_API int dibr_peer_allreduce(int rank, int world, const int64_t* buffers,
+                        const int64_t* signal_pads, int64_t num_floats, float* out, int* sync,
+                        void* stream);
+
 #ifdef __cplusplus
 }
 #endif

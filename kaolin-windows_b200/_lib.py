@@ -54,6 +54,8 @@ SIGNATURES = {
                                     _vp]),
     "dibr_softmask_fwd_f64": (_i, [_i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _i, _f, _vp, _vp,
                                    _vp, _vp, _vp, _i64, _i64, _vp, _vp]),
+    "dibr_peer_signal": (_i, [_i, _i, _vp, _i, _vp]),
+    "dibr_peer_allreduce": (_i, [_i, _i, _vp, _vp, _i64, _vp, _vp, _vp]),
     "dibr_deftet_workspace_bytes": (_i64, [_i, _i, _i]),
     "dibr_deftet_fwd": (_i, [_i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _vp, _vp, _vp,
                              _vp, _i64, _vp]),

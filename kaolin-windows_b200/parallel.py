@@ -73,6 +73,51 @@ def exchange_mesh_grads(faces, num_vertices, *face_grads, group=None):
     return flat
 
 
+class _PeerBuffers:
+    """This rank's part of a symmetric allocation for the one-shot peer all-reduce
+    (csrc/dibr_peer.cu): a float buffer every rank maps, its signal pad, a local result
+    buffer.  torch.distributed._symmetric_memory provides allocation and rendezvous."""
+
+    def __init__(self, numel, dev, group):
+        import ctypes
+        import torch.distributed._symmetric_memory as symm_mem
+        from . import _lib
+        self.n = (int(numel) + 3) // 4 * 4
+        self.buf = symm_mem.empty(self.n, dtype=torch.float32, device=dev)
+        hdl = symm_mem.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
+        self.hdl = hdl
+        self.rank, self.world = int(hdl.rank), int(hdl.world_size)
+        if (9 * self.world + self.world) * 4 > int(hdl.signal_pad_size):
+            raise RuntimeError("signal pad too small")
+        self.bufs = (ctypes.c_int64 * self.world)(*[int(p) for p in hdl.buffer_ptrs])
+        self.pads = (ctypes.c_int64 * self.world)(*[int(p) for p in hdl.signal_pad_ptrs])
+        self.out = torch.empty(self.n, dtype=torch.float32, device=dev)
+        self.sync = torch.zeros(2, dtype=torch.int32, device=dev)
+        self.buf.zero_()
+        with torch.cuda.device(dev):
+            st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+            _lib.check(_lib.lib().dibr_peer_signal(self.rank, self.world, self.pads, 0, st),
+                       "dibr_peer_signal")
+        torch.cuda.synchronize(dev)
+
+
+def _make_peer_buffers(numel, dev, group):
+    """_PeerBuffers, or None where symmetric memory is unavailable; all ranks agree."""
+    import os
+    if os.environ.get("DIBR_B200_EXCHANGE", "peer") == "nccl":
+        return None
+    peer, ok = None, 1
+    try:
+        peer = _PeerBuffers(numel, dev, group)
+    except Exception as e:      # no P2P mapping in this environment: NCCL does the exchange
+        import warnings
+        warnings.warn("kaolin-windows_b200: peer-memory exchange unavailable (%r), using NCCL" % (e,))
+        ok = 0
+    flag = torch.tensor([ok], device=dev, dtype=torch.int32)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+    return peer if int(flag.item()) == 1 else None
+
+
 class MeshGradExchange:
     """exchange_mesh_grads with its local part -- the buffer memset and the scatter kernels
     -- as ONE CUDA-graph launch, captured once per set of gradient addresses (a training
@@ -92,18 +137,43 @@ class MeshGradExchange:
         self.num_vertices = int(num_vertices)
         self.group = group
         self.flat = None
+        self.peer = None          # _PeerBuffers when the exchange runs over peer memory
+        self.mode = "local"
         self.graphs = {}
         self.seen = set()
+
+    def _setup(self, width, dev):
+        """The (num_vertices, width) buffer the scatter fills: in a symmetric allocation when
+        the exchange can run as our own peer-memory kernel, else plain memory + NCCL."""
+        self.graphs.clear()
+        self.peer = None
+        multi = (dist.is_available() and dist.is_initialized()
+                 and dist.get_world_size(self.group) > 1)
+        if multi:
+            self.peer = _make_peer_buffers(self.num_vertices * width, dev, self.group)
+        if self.peer is not None:
+            self.flat = self.peer.buf[:self.num_vertices * width].view(self.num_vertices, width)
+            self.result = self.peer.out[:self.num_vertices * width].view(self.num_vertices, width)
+            self.mode = "peer"
+        else:
+            self.flat = torch.empty((self.num_vertices, width), dtype=torch.float32, device=dev)
+            self.result = self.flat
+            self.mode = "nccl" if multi else "local"
 
     def _issue(self, face_grads):
         import ctypes
         from . import _lib
         lib = _lib.lib()
         dev = self.flat.device
-        self.flat.zero_()
+        st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        pb = self.peer
+        if pb is not None:      # peers may still be reading the previous exchange
+            _lib.check(lib.dibr_peer_signal(pb.rank, pb.world, pb.pads, 1, st), "dibr_peer_signal")
+            pb.buf.zero_()
+        else:
+            self.flat.zero_()
         width = self.flat.shape[1]
         col = 0
-        st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
         for g in face_grads:
             B, F, _, C = g.shape
             _lib.check(lib.dibr_scatter_face_grads(
@@ -111,6 +181,10 @@ class MeshGradExchange:
                 ctypes.c_void_p(self.faces.data_ptr()), ctypes.c_void_p(self.flat.data_ptr()),
                 width, col, st), "scatter_mesh_grads")
             col += C
+        if pb is not None:
+            _lib.check(lib.dibr_peer_allreduce(
+                pb.rank, pb.world, pb.bufs, pb.pads, pb.n, ctypes.c_void_p(pb.out.data_ptr()),
+                ctypes.c_void_p(pb.sync.data_ptr()), st), "dibr_peer_allreduce")
 
     def release(self):
         """Drop the captured graphs (required before destroy_process_group when the
@@ -119,9 +193,9 @@ class MeshGradExchange:
         self.seen.clear()
 
     def _reduce(self):
-        if dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1:
+        if self.mode == "nccl":
             dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group)
-        return self.flat
+        return self.result
 
     def __call__(self, *face_grads):
         face_grads = [g.contiguous() for g in face_grads]
@@ -130,14 +204,13 @@ class MeshGradExchange:
             raise RuntimeError("MeshGradExchange needs CUDA tensors (there is no CPU path)")
         width = sum(g.shape[-1] for g in face_grads)
         if self.flat is None or self.flat.shape[1] != width:
-            self.flat = torch.empty((self.num_vertices, width), dtype=torch.float32, device=dev)
-            self.graphs.clear()
+            self._setup(width, dev)
         key = tuple((g.data_ptr(), tuple(g.shape)) for g in face_grads)
         with torch.cuda.device(dev):
             graph = self.graphs.get(key)
             if graph is not None:
                 graph.replay()
-                return self.flat if self.capture_collective else self._reduce()
+                return self.result if self.capture_collective else self._reduce()
             self._issue(face_grads)
             if key in self.seen and len(self.graphs) < self.MAX_GRAPHS:
                 graph = torch.cuda.CUDAGraph()
@@ -147,7 +220,7 @@ class MeshGradExchange:
                     if self.capture_collective:
                         self._reduce()
                 self.graphs[key] = graph
-                return self.flat
+                return self.result
             else:
                 self.seen.add(key)
                 if len(self.seen) > 64:
