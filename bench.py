@@ -452,7 +452,11 @@ def main():
                                  "and reads back that loss",
                    "launch": "CUDA graphs (dibr_rasterization(cuda_graph=True))" if GRAPH
                              else "eager",
-                   "parallelism": "views sharded, %d per GPU" % B},
+                   "parallelism": "views sharded, %d per GPU" % B,
+                   "exchange": ("none (N = 1)" if world == 1 else
+                                {"peer": "own one-shot all-reduce kernel over NVLink peer memory",
+                                 "nccl": "NCCL all-reduce"}.get(
+                                     getattr(exchanger, "mode", "nccl"), "NCCL all-reduce"))},
         "clocks": sampler.summary(),
         "e2e": {"value": e2e_val, "unit": "Mpixels/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 8, "ms_per_step": e2e_s * 1e3,
