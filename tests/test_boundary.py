@@ -106,3 +106,35 @@ def test_shard_range_partitions_views():
         assert spans[0][0] == 0 and spans[-1][1] == n
         assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
         assert max(hi - lo for lo, hi in spans) - min(hi - lo for lo, hi in spans) <= 1
+
+
+def test_deftet_signature_and_planning_without_gpu():
+    """kaolin/render/mesh/deftet.py:342-343: names, order, defaults; the workspace bound and
+    the argument checks answer without a GPU; CPU tensors are refused (no CPU path)."""
+    sig = inspect.signature(kal.render.mesh.deftet_sparse_render)
+    assert list(sig.parameters) == ["pixel_coords", "render_ranges", "face_vertices_z",
+                                    "face_vertices_image", "face_features", "knum", "eps"]
+    assert sig.parameters["knum"].default == 300 and sig.parameters["eps"].default == 1e-8
+    h = _lib.lib()
+    n = h.dibr_deftet_workspace_bytes(8, 70000, 16384)
+    assert n > 0 and n % 256 == 0
+    # bound: 16 list entries + 1 wide-list entry per face and view, two ints per cell
+    assert n < 8 * 70000 * 4 * 17 + 8 * 2 * 4 * (4 * 16384 + 16) + (1 << 16)
+    assert h.dibr_deftet_workspace_bytes(-1, 1, 1) == _lib.DIBR_E_INVALID
+    assert h.dibr_deftet_fwd(7, 1, 1, 1, 1, 1, None, None, None, None, None, 1e-8, None, None,
+                             None, None, 0, None) == _lib.DIBR_E_INVALID
+    assert "dtype" in _lib.last_error()
+    z = torch.zeros(1, 2, 3)
+    with pytest.raises(RuntimeError):
+        kal.render.mesh.deftet_sparse_render(torch.zeros(1, 4, 2), torch.zeros(1, 4, 2), z,
+                                             torch.zeros(1, 2, 3, 2), torch.zeros(1, 2, 3, 1), 3)
+
+
+def test_peer_exchange_argument_checks_without_gpu():
+    import ctypes
+    h = _lib.lib()
+    pads = (ctypes.c_int64 * 2)(0, 0)
+    assert h.dibr_peer_signal(0, 0, pads, 0, None) == _lib.DIBR_E_INVALID       # world < 1
+    assert h.dibr_peer_signal(0, 2, pads, 0, None) == _lib.DIBR_E_INVALID       # null pads
+    assert "signal pad" in _lib.last_error()
+    assert h.dibr_peer_allreduce(3, 2, pads, pads, 8, None, None, None) == _lib.DIBR_E_INVALID
