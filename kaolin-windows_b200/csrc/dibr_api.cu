@@ -535,6 +535,7 @@ extern "C" int dibr_render_fwd(int B, int F, int H, int W, int D, const float* z
   memset(&s, 0, sizeof(s));
   s.job = jobs.j[1]; s.sel = out_idx; s.sigmainv = sigmainv; s.K = K; s.mask = mask;
   s.pairs = w.pairs;
+  s.block_uncovered = (const int*)(w.base + p.off_flags);
   return run_soft_forward(s, p, needed_host, st);
 }
 

@@ -169,6 +169,8 @@ struct SoftArgs {
   float* grad_img;         // (B, F, 3, 2) accumulated, unscaled coordinates
   PairBuf pairs;
   unsigned long long* report;  // device-visible host slot for the pair-buffer needs, or null
+  const int* block_uncovered;  // (B, nkx*nky) uncovered pixels per raster block (written by
+                               // the rasterizer of the same call), or null
 };
 
 struct SoftDenseBwdArgs {

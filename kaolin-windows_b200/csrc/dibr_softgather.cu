@@ -76,6 +76,18 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
   const int lx = lane & 7, ly = lane >> 3;
   const int nrx = (p.W + 7) >> 3, nry = (p.H + 3) >> 2;  // regions of a view
 
+  // a raster block without a single uncovered pixel (the rasterizer of the same call counted
+  // them): every pixel of this CTA is covered, soft_mask = 1, nothing to gather and no need
+  // to read selected_face_idx
+  if (a.block_uncovered &&
+      a.block_uncovered[(long long)b * p.nkx * p.nky + (by0 >> p.blk_log2) * p.nkx +
+                        (bx0 >> p.blk_log2)] == 0) {
+    for (int i = tid; i < NPX; i += kGThreads) {
+      const int ix = bx0 + (i & (BLK - 1)), iy = by0 + (i >> BLK_LOG2);
+      if (ix < p.W && iy < p.H) a.mask[((long long)b * p.H + iy) * p.W + ix] = 1.0f;
+    }
+    return;
+  }
   // ---- pixel state; covered pixels get their final value right away
   for (int i = tid; i < NPX; i += kGThreads) {
     const int ix = bx0 + (i & (BLK - 1)), iy = by0 + (i >> BLK_LOG2);
