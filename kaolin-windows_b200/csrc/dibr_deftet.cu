@@ -652,6 +652,155 @@ __global__ void __launch_bounds__(128) deftet_render_kernel(const DeftetArgs<T> 
   }
 }
 
+// ------------------------------------------------------------------ small knum
+// knum <= 32 (surface meshes: a few layers per point, short cell lists): a full warp per
+// point spends most of its instructions on per-point overhead executed by 32 lanes for a
+// handful of hits.  Here a warp takes TWO points, 16 lanes each; every warp-wide vote is
+// taken by all 32 lanes and split by half.  Same tests, same kept set, same order.
+constexpr int kHalfK = 32;
+template <typename T>
+struct HalfBuf {
+  T depth[kHalfK], w0[kHalfK], w1[kHalfK];
+  int face[kHalfK], perm[kHalfK];
+  T tdepth[16], tw0[16], tw1[16];     // a step's hits when they do not all fit any more
+  int tface[16];
+};
+
+template <typename T, bool RAW>
+__global__ void __launch_bounds__(128) deftet_render_half_kernel(const DeftetArgs<T> a) {
+  typedef typename Vec2<T>::type V2;
+  __shared__ HalfBuf<T> sbuf[8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int sub = lane >> 4, sl = lane & 15;
+  const int p0 = (blockIdx.x * 4 + warp) * 2;
+  if (p0 >= a.P) return;                       // whole warp
+  const int p = p0 + sub;
+  const bool exists = p < a.P;
+  const int b = blockIdx.y;
+  const long long gp = (long long)b * a.P + (exists ? p : p0);
+  const int K = a.K;
+  HalfBuf<T>& h = sbuf[warp * 2 + sub];
+  const V2 c = __ldg(reinterpret_cast<const V2*>(a.pix) + gp);
+  const V2 r = __ldg(reinterpret_cast<const V2*>(a.range) + gp);
+  const T x0 = c.x, y0 = c.y, dmin = r.x, dmax = r.y;
+  const T eps_t = (T)a.eps;
+  const CellGrid g = a.grids[b];
+  const long long face0 = (long long)b * a.F;
+  const unsigned below = (1u << sl) - 1u;
+
+  int n = 0;                  // hits held by this half's point (uniform within the half)
+  int maxf = -1, maxs = -1;   // lane sl == 0 only: largest held face id and its slot
+  const bool live = exists && !g.empty && !(x0 != x0) && !(y0 != y0);
+  for (int pass = 0; pass < 2; pass++) {
+    const int* lst = a.wide + face0;
+    int len = 0;
+    if (live) {
+      if (pass == 0) {
+        const int cell = cell_of(to_f(y0), g.loy, g.invy, g.g) * g.g +
+                         cell_of(to_f(x0), g.lox, g.invx, g.g);
+        lst = a.list + face0 * kListCap + a.cell_start[(long long)b * a.cells_cap + cell];
+        len = a.cell_count[(long long)b * a.cells_cap + cell];
+      } else {
+        len = (int)a.stats[b].wide;
+      }
+    }
+    const int maxlen = max(len, __shfl_xor_sync(DIBR_FULL_MASK, len, 16));
+    for (int base = 0; base < maxlen; base += 16) {
+      const int i = base + sl;
+      int f = -1;
+      T w0 = 0, w1 = 0, depth = 0;
+      bool hit = false;
+      if (i < len) {
+        f = __ldg(lst + i);
+        T v[6];
+        load_img6(a.img, face0 + f, v);
+        hit = deftet_box_test(a, face0 + f, v, x0, y0) &&
+              deftet_edge_test(a, face0 + f, v, x0, y0, dmin, dmax, eps_t, w0, w1, depth);
+      }
+      const unsigned m = (__ballot_sync(DIBR_FULL_MASK, hit) >> (16 * sub)) & 0xffffu;
+      const int cnt = __popc(m);
+      const bool fits = n + cnt <= K;
+      if (hit) {
+        const int t = __popc(m & below);
+        if (fits) {
+          h.face[n + t] = f; h.depth[n + t] = depth; h.w0[n + t] = w0; h.w1[n + t] = w1;
+        } else {
+          h.tface[t] = f; h.tdepth[t] = depth; h.tw0[t] = w0; h.tw1[t] = w1;
+        }
+      }
+      __syncwarp();
+      if (cnt && !fits && sl == 0) {
+        // more hits than slots: keep the K smallest face ids (the reference keeps the
+        // first K in ascending face order); one lane, K <= 32
+        int nn = n;
+        for (int t = 0; t < cnt; t++) {
+          const int tf = h.tface[t];
+          int s = -1;
+          if (nn < K) {
+            s = nn++;
+            maxs = -1;
+          } else {
+            if (maxs < 0) {
+              maxf = -1;
+              for (int k = 0; k < K; k++)
+                if (h.face[k] > maxf) { maxf = h.face[k]; maxs = k; }
+            }
+            if (tf < maxf) { s = maxs; maxs = -1; }
+          }
+          if (s >= 0) {
+            h.face[s] = tf; h.depth[s] = h.tdepth[t]; h.w0[s] = h.tw0[t]; h.w1[s] = h.tw1[t];
+          }
+        }
+      }
+      n = min(n + cnt, K);
+      __syncwarp();
+    }
+  }
+
+  // order: every lane ranks its hits against all others (n <= 32, broadcast reads)
+  if (n > 1) {
+    for (int i = sl; i < n; i += 16) {
+      const T di = h.depth[i];
+      const int fi = h.face[i];
+      int rank = 0;
+      for (int j = 0; j < n; j++) {
+        const T dj = h.depth[j];
+        const int fj = h.face[j];
+        rank += RAW ? (fj < fi) : (dj > di || (dj == di && fj < fi));
+      }
+      h.perm[rank] = i;
+    }
+  }
+  __syncwarp();
+  if (!exists) return;
+
+  const long long row = gp * K;
+  const int D = a.D;
+  for (int k = sl; k < K; k += 16) {
+    const bool ok = k < n;
+    const int s = ok ? (n > 1 ? h.perm[k] : 0) : 0;
+    const long long o = row + k;
+    const int f = ok ? h.face[s] : -1;
+    const T w0 = ok ? h.w0[s] : (T)0, w1 = ok ? h.w1[s] : (T)0;
+    a.out_idx[o] = f;
+    if (RAW) {
+      a.out_depth[o] = ok ? h.depth[s] : -(T)INFINITY; a.out_w0[o] = w0; a.out_w1[o] = w1;
+      continue;
+    }
+    const T w2 = sub_rn(ok ? (T)1 : (T)0, add_rn(w0, w1));     // deftet.py:307
+    T* ow = a.out_w + o * 3;
+    ow[0] = w0; ow[1] = w1; ow[2] = w2;
+    const T* fp = a.feat + (face0 + (ok ? f : 0)) * 3 * D;
+    T* of = a.out_feat + o * D;
+    for (int d = 0; d < D; d++) {                                // deftet.py:315-317
+      T v = (T)0;
+      if (ok) v = add_rn(add_rn(mul_rn(w0, __ldg(fp + d)), mul_rn(w1, __ldg(fp + D + d))),
+                         mul_rn(w2, __ldg(fp + 2 * D + d)));
+      of[d] = v;
+    }
+  }
+}
+
 // ------------------------------------------------------------------ backward
 // deftet_cuda.cu:239-401: one thread per (sample, layer) slot; the six image-coordinate
 // terms are summed over the features before the atomics (the reference issues 6 per feature).
@@ -853,6 +1002,12 @@ int deftet_forward(bool raw, int B, int F, int P, int K, int D, const void* z, c
       deftet_bin_kernel<T, true><<<dim3(bb, B), 256, hist, st>>>(a);
     }
     DEF_CUDA(cudaGetLastError());
+  }
+  if (K <= kHalfK) {            // two points per warp (deftet_render_half_kernel)
+    auto kern = raw ? deftet_render_half_kernel<T, true> : deftet_render_half_kernel<T, false>;
+    kern<<<dim3((P + 7) / 8, B), 128, 0, st>>>(a);
+    DEF_CUDA(cudaGetLastError());
+    return DIBR_OK;
   }
   // one warp per sample; warps per CTA limited by the staging of K hits per warp
   const size_t per_warp = hitbuf_bytes<T>(K, n2);
