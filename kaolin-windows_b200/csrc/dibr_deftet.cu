@@ -289,10 +289,13 @@ __global__ void __launch_bounds__(256) deftet_bin_kernel(const DeftetArgs<T> a) 
   const int per = (a.F + gridDim.x - 1) / gridDim.x;
   const int f_lo = blockIdx.x * per, f_hi = min(f_lo + per, a.F);
   if (f_lo >= f_hi) return;
+  __shared__ int s_lo, s_hi;       // range of cells this CTA touched (the flush walks only it)
   if (priv) {
     for (int c = threadIdx.x; c < ncell; c += blockDim.x) s_hist[c] = 0;
+    if (threadIdx.x == 0) { s_lo = ncell; s_hi = -1; }
     __syncthreads();
   }
+  int c_lo = ncell, c_hi = -1;
   // pass 0 (both modes): count into the private histogram (or straight into the counters);
   // pass 1 (fill, private form only): deal the reserved slots out
   for (int pass = 0; pass < ((FILL && priv) ? 2 : 1); pass++) {
@@ -305,6 +308,8 @@ __global__ void __launch_bounds__(256) deftet_bin_kernel(const DeftetArgs<T> a) 
         if (!FILL) a.wide[(long long)b * a.F + atomicAdd(&a.stats[b].wide, 1u)] = f;
         continue;
       }
+      c_lo = min(c_lo, cy0 * g.g + cx0);
+      c_hi = max(c_hi, cy1 * g.g + cx1);
       for (int cy = cy0; cy <= cy1; cy++)
         for (int cx = cx0; cx <= cx1; cx++) {
           const int c = cy * g.g + cx;
@@ -318,9 +323,12 @@ __global__ void __launch_bounds__(256) deftet_bin_kernel(const DeftetArgs<T> a) 
         }
     }
     if (!priv || pass == 1) break;
+    c_lo = __reduce_min_sync(DIBR_FULL_MASK, c_lo);
+    c_hi = __reduce_max_sync(DIBR_FULL_MASK, c_hi);
+    if ((threadIdx.x & 31) == 0 && c_hi >= 0) { atomicMin(&s_lo, c_lo); atomicMax(&s_hi, c_hi); }
     __syncthreads();
-    // flush: consecutive lanes, consecutive cells
-    for (int c = threadIdx.x; c < ncell; c += blockDim.x) {
+    // flush: consecutive lanes, consecutive cells, over the touched range only
+    for (int c = (s_lo & ~31) + threadIdx.x; c <= s_hi; c += blockDim.x) {
       const int h = s_hist[c];
       if (h == 0) continue;
       if (FILL) s_hist[c] = start[c] + atomicAdd(cnt + c, h);   // first slot of this CTA's share
