@@ -107,6 +107,27 @@ class ClockSampler(threading.Thread):
 
     def run(self):
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        # NVML answers in well under a millisecond (the timed regions last tens of
+        # milliseconds; one nvidia-smi call takes longer than that); nvidia-smi is the fallback
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            hd = pynvml.nvmlDeviceGetHandleByIndex(self.index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(hd, pynvml.NVML_CLOCK_SM))
+            get_reasons = getattr(pynvml, "nvmlDeviceGetCurrentClocksEventReasons", None) or \
+                pynvml.nvmlDeviceGetCurrentClocksThrottleReasons
+            bits = {"sw_power_cap": 0x4, "hw_slowdown": 0x8, "sw_thermal_slowdown": 0x20,
+                    "hw_thermal_slowdown": 0x40}
+            while not self.stop_flag:
+                self.samples.append(float(pynvml.nvmlDeviceGetClockInfo(hd, pynvml.NVML_CLOCK_SM)))
+                r = int(get_reasons(hd))
+                for n, bit in bits.items():
+                    if r & bit:
+                        self.reasons.add(n)
+                time.sleep(0.002)
+            return
+        except Exception:
+            pass
         while not self.stop_flag:
             try:
                 out = subprocess.run(
@@ -283,7 +304,6 @@ def main():
         step(img, feat)
         e1.record()
     barrier()
-    sampler.stop_flag = True
     step_ms = [e0.elapsed_time(e1) for e0, e1 in evs]
     total_ms = torch.tensor([sum(step_ms)], device=dev, dtype=torch.float64)
     if world > 1:
@@ -380,6 +400,7 @@ def main():
     e2e_t = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    sampler.stop_flag = True      # clocks sampled across both timed regions (device + e2e)
     e2e_s = max(float(e2e_t.item()), 1e-9) / args.steps
     if e2e_trace is not None and rank == 0:
         ts = e2e_trace[-args.steps:]
