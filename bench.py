@@ -149,52 +149,66 @@ class ClockSampler(threading.Thread):
                 "reasons": sorted(self.reasons), "samples": len(s)}
 
 
+def host_threads():
+    """Host threads this process may use (torchrun exports OMP_NUM_THREADS=1; the CPU legs
+    set their thread count explicitly instead of inheriting it)."""
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def cpu_reference_step(orc, H, W, z, img, feat, nz, g1, g2):
+    _, _, _, ctxs = orc.dibr_rasterization_forward(H, W, z, img, feat, nz, SIGMAINV, BOXLEN, KNUM)
+    orc.dibr_rasterization_backward(ctxs, g1, g2)
+
+
 def reference_arm(args, rank, world):
     """The reference's path on host cores: the CPU port (the reference has no CPU code for
-    this path: rasterization.cpp:100-102)."""
+    this path: rasterization.cpp:100-102), all host threads, one FULL view of the 8 per
+    step (no row band: the per-view fixed costs of the port are amortised as in a full run)."""
     if rank != 0:
         return
     import torch
     import workloads as wl
     from oracle import dibr_oracle as orc
-    inp = wl.make_config(CFG, views=1)
+    cores = host_threads()
+    orc.set_threads(cores)
+    orc.set_row_band()
+    views = wl.CONFIGS[CFG]["views"]
+    inp = wl.make_config(CFG, views=views, view_slice=(0, 1))
     H, W = inp["H"], inp["W"]
     z, img, feat, nz = (inp[k] for k in ("face_vertices_z", "face_vertices_image",
                                          "face_features", "face_normals_z"))
-    rows = 64
-    lo = (H - rows) // 2
-    orc.set_row_band(lo, lo + rows)
     g1 = torch.rand(1, H, W, feat.shape[-1])
     g2 = torch.rand(1, H, W)
-
-    def step():
-        _, _, _, ctxs = orc.dibr_rasterization_forward(H, W, z, img, feat, nz, SIGMAINV, BOXLEN,
-                                                       KNUM)
-        orc.dibr_rasterization_backward(ctxs, g1, g2)
-
-    for _ in range(args.warmup):
-        step()
+    for _ in range(min(args.warmup, 2)):
+        cpu_reference_step(orc, H, W, z, img, feat, nz, g1, g2)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        step()
+        cpu_reference_step(orc, H, W, z, img, feat, nz, g1, g2)
     dt = (time.perf_counter() - t0) / args.steps
-    orc.set_row_band()
-    val = rows * W / dt / 1e6
-    sample = "rows %d-%d of 1 view per step (%d px), extrapolated linearly in pixels" % (
-        lo, lo + rows, rows * W)
+    assert orc.get_threads() == cores
+    val = H * W / dt / 1e6
+    sample = "view 0 of %d in full (%d px) per step, %d host threads" % (views, H * W, cores)
     emit({
         "impl": "reference", "metric": METRIC, "value": val, "unit": "Mpixels/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": CFG, "views_per_gpu": 8, "faces": int(z.shape[1]), "H": H, "W": W,
-                   "D": int(feat.shape[-1]), "sigmainv": SIGMAINV, "boxlen": BOXLEN, "knum": KNUM},
-        "cpu_baseline": {"value": val, "unit": "Mpixels/s", "cores": orc.get_threads(),
+        "config": bench_config(views, int(z.shape[1]), H, W, int(feat.shape[-1])),
+        "cpu_baseline": {"value": val, "unit": "Mpixels/s", "cores": cores,
                          "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "Mpixels/s", "h2d_bytes_per_step": 0,
                 "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     })
+
+
+def bench_config(views_per_gpu, F, H, W, D):
+    """The workload, identical in both arms (prose lives in the line's `notes`)."""
+    return {"workload": CFG, "views_per_gpu": views_per_gpu, "faces": F, "H": H, "W": W, "D": D,
+            "sigmainv": SIGMAINV, "boxlen": BOXLEN, "knum": KNUM}
 
 
 def main():
@@ -290,6 +304,32 @@ def main():
     for _ in range(args.warmup):
         step(img, feat)
     barrier()
+
+    # ---- un-timed cross-check of the exchange (N > 1): the same gradients through our
+    # peer-memory all-reduce kernel and through scatter + NCCL all_reduce
+    exchange_check = None
+    if world > 1:
+        img_l = img.detach().requires_grad_(True)
+        feat_l = feat.detach().requires_grad_(True)
+        out, mask, idx = kal.render.mesh.dibr_rasterization(H, W, z, img_l, feat_l, nz,
+                                                            SIGMAINV, BOXLEN, KNUM)
+        torch.autograd.backward((out, mask), (g1, g2))
+        ex = exchanger if exchanger is not None else kal.parallel.MeshGradExchange(faces, V)
+        mine = ex(img_l.grad, feat_l.grad).clone()
+        want = kal.parallel.exchange_mesh_grads(faces, V, img_l.grad, feat_l.grad)
+        rel = (mine - want).abs().max() / want.abs().max().clamp_min(1e-30)
+        bits = mine.contiguous().view(torch.int32).to(torch.int64)
+        wts = torch.arange(bits.numel(), device=dev, dtype=torch.int64).view_as(bits) % 65521 + 1
+        digest = torch.stack([bits.sum(), (bits * wts).sum()])
+        every = [torch.zeros_like(digest) for _ in range(world)]
+        dist.all_gather(every, digest)
+        relmax = rel.clone()
+        dist.all_reduce(relmax, op=dist.ReduceOp.MAX)
+        exchange_check = {"mode": ex.mode, "max_rel_diff": float(relmax.item()),
+                          "bit_identical_across_ranks": all(torch.equal(e, every[0]) for e in every),
+                          "against": "dibr_scatter_face_grads + NCCL all_reduce on the same gradients"}
+        del out, mask, idx, img_l, feat_l, mine, want
+        barrier()
 
     # ---- timed: exactly K steps, one CUDA-event pair per step, L2 flushed in between
     sampler = ClockSampler(local_rank)
@@ -447,6 +487,38 @@ def main():
     except Exception:
         pass
 
+    # ---- secondary roofline: FP32 pipe.  N_pair = (pixel centre, valid face)
+    # pairs passing the reference's own box test, x 45 FP32-pipe ops per pair, over the
+    # rasterizer's time, against the FMA throughput measured on this GPU (tools/fma_peak.cu)
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        import fma_peak
+        fma_tf, _ = fma_peak.measure()
+        fma_kind = "measured (tools/fma_peak.cu)"
+    except Exception as e:
+        fma_tf, fma_kind = 148 * 128 * 2 * 1.965e9 / 1e12, "nominal (%r)" % (e,)
+    n_pair = wl.raster_pair_count(H, W, img, nz >= 0, 1000.0)
+    if "raster_fwd" in kernel_ms:
+        sec_ach = n_pair * 45 / (kernel_ms["raster_fwd"] * 1e-3) / 1e12
+        roofline["secondary"] = {
+            "bound": "fp32", "kernel": "raster_fwd", "n_pair": n_pair, "ops_per_pair": 45,
+            "achieved": sec_ach, "peak": fma_tf, "peak_kind": fma_kind, "unit": "TFLOP/s",
+            "frac": sec_ach / fma_tf}
+
+    # ---- the drop-in default: eager launches (no cuda_graph kwarg), same timing rules
+    ee = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+          for _ in range(args.steps)]
+    for _ in range(3):
+        step(img, feat, exchange=False, graph=False)
+    torch.cuda.synchronize(dev)
+    for e0, e1 in ee:
+        flush.zero_()
+        e0.record()
+        step(img, feat, exchange=False, graph=False)
+        e1.record()
+    torch.cuda.synchronize(dev)
+    eager_ms = sum(e0.elapsed_time(e1) for e0, e1 in ee) / args.steps
+
     # ---- forward only (SURVEY 8(d) asks for it beside fwd+bwd)
     fe = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
           for _ in range(args.steps)]
@@ -465,19 +537,18 @@ def main():
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": {"workload": CFG, "views_per_gpu": B, "faces": F, "H": H, "W": W, "D": D,
-                   "sigmainv": SIGMAINV, "boxlen": BOXLEN, "knum": KNUM,
-                   "l2": "flushed between steps (256 MiB memset outside the per-step event spans)",
-                   "cotangents": "fixed random G1, G2 fed to autograd directly (= backward of "
-                                 "(features*G1).sum() + (soft_mask*G2).sum()); e2e computes "
-                                 "and reads back that loss",
-                   "launch": "CUDA graphs (dibr_rasterization(cuda_graph=True))" if GRAPH
-                             else "eager",
-                   "parallelism": "views sharded, %d per GPU" % B,
-                   "exchange": ("none (N = 1)" if world == 1 else
-                                {"peer": "own one-shot all-reduce kernel over NVLink peer memory",
-                                 "nccl": "NCCL all-reduce"}.get(
-                                     getattr(exchanger, "mode", "nccl"), "NCCL all-reduce"))},
+        "config": bench_config(B, F, H, W, D),
+        "notes": {"l2": "flushed between steps (256 MiB memset outside the per-step event spans)",
+                  "cotangents": "fixed random G1, G2 fed to autograd directly (= backward of "
+                                "(features*G1).sum() + (soft_mask*G2).sum()); e2e computes "
+                                "and reads back that loss",
+                  "launch": "CUDA graphs (dibr_rasterization(cuda_graph=True))" if GRAPH
+                            else "eager",
+                  "parallelism": "views sharded, %d per GPU" % B,
+                  "exchange": ("none (N = 1)" if world == 1 else
+                               {"peer": "own one-shot all-reduce kernel over NVLink peer memory",
+                                "nccl": "NCCL all-reduce"}.get(
+                                    getattr(exchanger, "mode", "nccl"), "NCCL all-reduce"))},
         "clocks": sampler.summary(),
         "e2e": {"value": e2e_val, "unit": "Mpixels/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": 8, "ms_per_step": e2e_s * 1e3,
@@ -486,6 +557,8 @@ def main():
                             "step i's render; loss of step i read back before step i+1 is issued"},
         "gpu_launches": launches_per_step * args.steps,
         "fwd_only_ms_per_step": fwd_ms,
+        "eager_ms_per_step": eager_ms,
+        "exchange_check": exchange_check,
         "roofline": roofline,
     }
 
@@ -512,28 +585,25 @@ def main():
         except Exception as e:  # the strengthened checker is optional
             line["reference_kernels_on_this_gpu"] = {"unavailable": repr(e)[:200]}
 
-    # ---- CPU baseline: the oracle port on the host cores, bounded sample
+    # ---- CPU baseline: the oracle port on the host cores, bounded sample (view 0 in full)
     if not args.no_cpu_baseline and world == 1:
         from oracle import dibr_oracle as orc
-        rows = 128
-        lo_r = (H - rows) // 2
-        orc.set_row_band(lo_r, lo_r + rows)
+        cores = host_threads()
+        orc.set_threads(cores)
+        orc.set_row_band()
         cz, cimg, cfeat, cnz = (t[:1].cpu() for t in (z, img, feat, nz))
         cg1, cg2 = g1[:1].cpu(), g2[:1].cpu()
         t0 = time.perf_counter()
         reps = 0
         while reps < 2 or (time.perf_counter() - t0 < 10.0 and reps < 50):
-            _, _, _, ctxs = orc.dibr_rasterization_forward(H, W, cz, cimg, cfeat, cnz, SIGMAINV,
-                                                           BOXLEN, KNUM)
-            orc.dibr_rasterization_backward(ctxs, cg1, cg2)
+            cpu_reference_step(orc, H, W, cz, cimg, cfeat, cnz, cg1, cg2)
             reps += 1
         dt = (time.perf_counter() - t0) / reps
-        orc.set_row_band()
         line["cpu_baseline"] = {
-            "value": rows * W / dt / 1e6, "unit": "Mpixels/s", "cores": orc.get_threads(),
+            "value": P / dt / 1e6, "unit": "Mpixels/s", "cores": orc.get_threads(),
             "kind": "port",
-            "sample": "rows %d-%d of view 0 (%d px) x %d repeats, extrapolated linearly in pixels"
-                      % (lo_r, lo_r + rows, rows * W, reps)}
+            "sample": "view 0 of %d in full (%d px) x %d repeats, %d host threads"
+                      % (B, P, reps, cores)}
     emit(line)
     if world > 1:
         if exchanger is not None:

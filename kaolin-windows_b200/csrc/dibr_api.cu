@@ -65,6 +65,21 @@ bool pdl_enabled() {
   return on;
 }
 
+cudaError_t smem_optin(const void* kernel, int bytes) {
+  struct Done { const void* fn; int dev; int bytes; };
+  static std::mutex mu;
+  static std::vector<Done> done;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  std::lock_guard<std::mutex> lk(mu);
+  for (const Done& d : done)
+    if (d.fn == kernel && d.dev == dev && d.bytes >= bytes) return cudaSuccess;
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) done.push_back({kernel, dev, bytes});
+  return e;
+}
+
 // needed_host is device-visible pinned memory (cudaHostAlloc under UVA): the kernels store
 // the report themselves, no copy node between them (dibr_host_report_direct)
 static bool g_report_direct = false;   // process-wide, set once by the host binding
@@ -136,8 +151,8 @@ static int bind_workspace(const Plan& p, const void* ws, int64_t ws_bytes, int64
                           int64_t cap_s, Workspace& w, int64_t cap_p = 0, int K = 0) {
   if (cap_r < 0) cap_r = 0;
   if (cap_s < 0) cap_s = 0;
-  if (cap_r > 0x7fffffff || cap_s > 0x7fffffff)
-    return fail(DIBR_E_INVALID, "list capacity above 2^31-1 entries");
+  if (cap_r > kMaxListEntries || cap_s > kMaxListEntries)
+    return fail(DIBR_E_INVALID, "list capacity above 2^31 - 2^16 entries");
   if (cap_p > (1 << 23)) return fail(DIBR_E_INVALID, "pair capacity above 2^23 segments");
   const int64_t lists_end = align_up(p.fixed_bytes + 4 * (cap_r + cap_s), 256);
   const int64_t need = lists_end + pair_bytes(cap_p, K);

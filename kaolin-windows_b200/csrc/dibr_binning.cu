@@ -66,8 +66,11 @@ bin_walk_kernel(const BinJobs jobs, const Plan p) {
     const int2 r = job.range[(long long)b * p.nchunks + chunk];
     lo_bin = r.x;
     hi_bin = r.y;
+    // 64-bit sum clamped below 2^31: a segment beyond the capacity (an under-provisioned
+    // first attempt) must not wrap into a valid slot
     for (int i = lo_bin + lane; i <= hi_bin; i += 32)
-      hist[i] = job.start[row + i] + job.mat[(row + i) * p.nchunks + chunk];
+      hist[i] = (int)min((long long)job.start[row + i] + job.mat[(row + i) * p.nchunks + chunk],
+                         kMaxListEntries);
   } else {
     for (int i = lane; i < p.NB; i += 32) hist[i] = 0;
   }
@@ -92,7 +95,7 @@ bin_walk_kernel(const BinJobs jobs, const Plan p) {
           const int bin = cy * p.nbx + cx;
           const int slot = atomicAdd(&hist[bin], 1);
           if (FILL) {
-            if (slot < job.capacity) job.list[slot] = f;
+            if (slot >= 0 && slot < job.capacity) job.list[slot] = f;
           } else {
             lo_bin = min(lo_bin, bin);
             hi_bin = max(hi_bin, bin);

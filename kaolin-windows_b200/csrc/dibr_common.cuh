@@ -150,6 +150,9 @@ struct PairBuf {
   int* chunk;                 // [3 * cap]    act * 256 + chunk index within the region
 };
 constexpr int kPairChunk = 128;
+// list capacities stay this far below 2^31 so that the fill kernel's int slot counters
+// (segment start + up to S increments per chunk) cannot wrap
+constexpr long long kMaxListEntries = 0x7fffffffll - 65536;
 
 __device__ __forceinline__ bool pairs_overflowed(const PairBuf& pb) {
   return pb.cursor[0] > (unsigned long long)pb.cap || pb.cursor[1] > (unsigned long long)pb.cap;
@@ -474,6 +477,9 @@ __device__ __forceinline__ void pdl_prologue() {
 }
 
 #ifdef __CUDACC__
+// cudaFuncAttributeMaxDynamicSharedMemorySize is a per-DEVICE attribute of a kernel: opted
+// in once per (kernel, device) -- a process may render on several GPUs (dibr_api.cu)
+cudaError_t smem_optin(const void* kernel, int bytes);
 bool pdl_enabled();   // dibr_api.cu: DIBR_B200_PDL=0 turns the attribute off
 
 template <typename... KArgs, typename... Args>

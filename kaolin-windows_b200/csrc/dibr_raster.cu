@@ -222,7 +222,9 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
             }
             L = fminf(L, 1e6f);
             U = fmaxf(U, -1e6f);
-            xa = max(rxl, (int)ceilf(L - 0.01f));
+            // xa stays within the block (it is packed into 8 bits below): a left crossing
+            // beyond the rectangle means an empty span
+            xa = min(max(rxl, (int)ceilf(L - 0.01f)), rxh + 1);
             xb = min(rxh, (int)floorf(U + 0.01f));
           }
           const int len = max(xb - xa + 1, 0);
@@ -383,13 +385,8 @@ cudaError_t launch_raster_forward(const RasterArgs& a, const Plan& p, cudaStream
     launch_k(raster_forward_kernel<5>, grid, kRasterThreads, sizeof(RasterSmem<5>), st, a, p);
   } else {
     const size_t smem = sizeof(RasterSmem<6>);  // above the 48 KB default: opt in
-    static bool once = false;
-    if (!once) {
-      cudaError_t e = cudaFuncSetAttribute(raster_forward_kernel<6>,
-                                           cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      if (e != cudaSuccess) return e;
-      once = true;
-    }
+    cudaError_t e = smem_optin((const void*)raster_forward_kernel<6>, (int)smem);
+    if (e != cudaSuccess) return e;
     launch_k(raster_forward_kernel<6>, grid, kRasterThreads, smem, st, a, p);
   }
   prof_end(st);

@@ -360,14 +360,9 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
 
 template <int G_LOG2>
 static cudaError_t launch_gather(const SoftArgs& a, const Plan& p, cudaStream_t st) {
-  static bool once = false;
   const int smem = (int)sizeof(GatherSmem<G_LOG2>);
-  if (!once) {
-    cudaError_t e = cudaFuncSetAttribute(softmask_gather_kernel<G_LOG2>,
-                                         cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) return e;
-    once = true;
-  }
+  cudaError_t e = smem_optin((const void*)softmask_gather_kernel<G_LOG2>, smem);
+  if (e != cudaSuccess) return e;
   dim3 grid((p.W + (1 << G_LOG2) - 1) >> G_LOG2, (p.H + (1 << G_LOG2) - 1) >> G_LOG2, p.B);
   launch_k(softmask_gather_kernel<G_LOG2>, grid, kGThreads, smem, st, a, p);
   return cudaGetLastError();

@@ -721,26 +721,17 @@ static cudaError_t launch_soft_mode(const SoftArgs& a, const Plan& p, cudaStream
   const long long nblk = (long long)p.nkx * p.nky * p.B;
   const bool fallback = MODE != SOFT_FWD_DENSE && a.pairs.cap > 0;
   dim3 grid((unsigned)(fallback ? min(nblk, (long long)148 * 3) : nblk));
-  static bool attr5 = false, attr6 = false;
   cudaError_t e = cudaSuccess;
   if (p.blk_log2 == 5) {
     const int smem = (int)sizeof(SoftSmem<5, MODE>);
-    if (!attr5) {
-      e = cudaFuncSetAttribute(softmask_kernel<5, MODE>,
-                               cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-      if (e != cudaSuccess) return e;
-      attr5 = true;
-    }
+    e = smem_optin((const void*)softmask_kernel<5, MODE>, smem);
+    if (e != cudaSuccess) return e;
     prof_begin(MODE == SOFT_BWD ? K_SOFT_BWD : K_SOFT_FWD, st);
     launch_k((softmask_kernel<5, MODE>), grid, kSoftThreads, smem, st, a, p);
   } else {
     const int smem = (int)sizeof(SoftSmem<6, MODE>);
-    if (!attr6) {
-      e = cudaFuncSetAttribute(softmask_kernel<6, MODE>,
-                               cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-      if (e != cudaSuccess) return e;
-      attr6 = true;
-    }
+    e = smem_optin((const void*)softmask_kernel<6, MODE>, smem);
+    if (e != cudaSuccess) return e;
     prof_begin(MODE == SOFT_BWD ? K_SOFT_BWD : K_SOFT_FWD, st);
     launch_k((softmask_kernel<6, MODE>), grid, kSoftThreads, smem, st, a, p);
   }

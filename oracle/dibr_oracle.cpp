@@ -77,7 +77,7 @@ void packed_rasterize_forward(
     int batch_size, int height, int width, int num_features,
     float multiplier, float eps, int64_t* pair_count) {
   int64_t pairs = 0;
-#pragma omp parallel for collapse(2) schedule(dynamic, 4) num_threads(nthreads()) reduction(+ : pairs)
+#pragma omp parallel for collapse(2) schedule(dynamic, 1) num_threads(nthreads()) reduction(+ : pairs)
   for (int bidx = 0; bidx < batch_size; bidx++) {
     for (int heiidx = 0; heiidx < height; heiidx++) {
       if (row_skipped(heiidx)) continue;
@@ -200,7 +200,7 @@ void rasterize_backward(
       std::vector<double>& gf = acc_feat[tid];
       gi.assign(n_img, 0.0);
       gf.assign(n_feat, 0.0);
-#pragma omp for schedule(static)
+#pragma omp for schedule(dynamic, 1024)
       for (int64_t pixel_idx = 0; pixel_idx < num_pixels; pixel_idx++) {
         if (row_skipped((int)(pixel_idx / width))) continue;
         const int64_t true_pixel_idx = batch_idx * num_pixels + pixel_idx;
@@ -331,7 +331,7 @@ void dibr_soft_mask_forward(
     scalar_t* soft_mask,                  // (B, H, W)    pre-filled 0
     int batch_size, int height, int width, int num_faces, int knum,
     float sigmainv, float multiplier) {
-#pragma omp parallel for collapse(2) schedule(dynamic, 4) num_threads(nthreads())
+#pragma omp parallel for collapse(2) schedule(dynamic, 1) num_threads(nthreads())
   for (int bidx = 0; bidx < batch_size; bidx++) {
     for (int heiidx = 0; heiidx < height; heiidx++) {
       if (row_skipped(heiidx)) continue;
@@ -453,7 +453,7 @@ void dibr_soft_mask_backward(
 #endif
       std::vector<double>& g = acc[tid];
       g.assign(n_img, 0.0);
-#pragma omp for schedule(dynamic, 4)
+#pragma omp for schedule(dynamic, 1)
       for (int heiidx = 0; heiidx < height; heiidx++) {
         if (row_skipped(heiidx)) continue;
         for (int wididx = 0; wididx < width; wididx++) {

@@ -23,13 +23,19 @@ METRICS = [
     "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum",
     "smsp__thread_inst_executed_per_inst_executed.ratio",
     "sm__cycles_active.avg", "sm__cycles_active.max", "sm__cycles_elapsed.max",
-    "lts__t_sector_hit_rate.pct",
+    "lts__t_sector_hit_rate.pct", "lts__throughput.avg.pct_of_peak_sustained_elapsed",
+    # L2 atomic / reduction traffic of the backward kernels (north_star: "L2 atomic throughput")
+    "lts__t_sectors_op_atom.sum", "lts__t_sectors_op_red.sum",
+    "lts__t_sector_op_red_hit_rate.pct", "lts__t_sector_op_atom_hit_rate.pct",
+    "smsp__inst_executed_op_global_red.sum", "smsp__inst_executed_op_shared_atom.sum",
 ]
+# added to `ncu --set full` on the command line (not all are part of the full set)
+EXTRA_NCU_METRICS = ",".join(METRICS[-7:])
 # bench.py's kernel names by substring of the ncu kernel name (first match wins)
 BENCH_NAMES = [
     ("bin_walk_kernel<0>", "bin_count"), ("bin_walk_kernel<false>", "bin_count"),
     ("bin_scan", "bin_scan"), ("bin_walk_kernel", "bin_fill"),
-    ("raster_forward", "raster_fwd"), ("raster_backward_finish", None),
+    ("raster_forward", "raster_fwd"), ("raster_backward_finish", "raster_bwd_finish"),
     ("raster_backward", "raster_bwd"), ("softmask_gather", "softmask_gather"),
     ("softmask_pairs_eval", "softmask_eval"), ("softmask_pairs_grad", "softmask_grad"),
 ]
@@ -60,6 +66,18 @@ def main():
             print("%s = %s %s" % (m, r[j], units[j]))
             if m.startswith("dram__bytes"):
                 dram += float(r[j].replace(",", "")) * SCALE.get(units[j], 1)
+        if "gpu__time_duration.sum" in hdr:
+            # derived: L2 reduction/atomic sectors per microsecond of the launch
+            try:
+                j = hdr.index("gpu__time_duration.sum")
+                t_us = float(r[j].replace(",", "")) * {"ns": 1e-3, "us": 1.0, "ms": 1e3}.get(units[j], 1.0)
+                n = sum(float(r[hdr.index(m)].replace(",", "")) for m in
+                        ("lts__t_sectors_op_atom.sum", "lts__t_sectors_op_red.sum") if m in hdr)
+                if n:
+                    print("derived: L2 atom+red sectors per us = %.1f (32 B each: %.1f GB/s)"
+                          % (n / t_us, n * 32 / t_us / 1e3))
+            except (ValueError, ZeroDivisionError):
+                pass
         for sub, bname in BENCH_NAMES:
             if sub in name:
                 if bname:

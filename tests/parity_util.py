@@ -1,0 +1,81 @@
+"""Gradient parity bar shared by the GPU parity tests, and the PARITY log.
+
+north_star asks for gradients "within 1e-4 relative" of the reference.  A tensor-wide
+max-norm would let every small-magnitude face gradient be wrong by orders of magnitude, so
+the bar is PER FACE (the reference's own tests compare elementwise:
+tests/python/kaolin/render/mesh/test_rasterization.py:189-288):
+
+    e_f = |g_f - g64_f|_inf / max(|g64_f|_inf, 1e-3 * |g64|_inf)        must be <= 1e-4
+
+with g64 the reference's backward kernels run in fp64 on the state its fp32 forward saved
+(same discrete choices).  Where the reference's OWN fp32 result is further than that from
+its fp64 result (1 / k3^2 amplification on sub-pixel faces, 1 - soft_mask cancellation),
+a face may instead be no further from fp64 than 1.5x the reference's fp32 error -- capped
+at 1e-3 -- and the number of faces that needed this clause is counted and logged.
+
+Every comparison appends one JSON line to $DIBR_PARITY_LOG (default
+gpurun_out/r2_parity.jsonl when that directory exists); the committed copy is
+profiles/r2_parity.jsonl.
+"""
+import json
+import os
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+TOL = 1e-4          # north_star: gradients within 1e-4 relative
+FLOOR = 1e-3        # faces whose gradient is below 1e-3 of the tensor's largest: absolute bar
+ESCAPE_CAP = 1e-3   # hard cap of the "no worse than the reference's own fp32" clause
+
+
+def _log_path():
+    p = os.environ.get("DIBR_PARITY_LOG")
+    if p:
+        return p
+    d = os.path.join(ROOT, "gpurun_out")
+    return os.path.join(d, "r2_parity.jsonl") if os.path.isdir(d) else None
+
+
+def log(record):
+    p = _log_path()
+    if p:
+        with open(p, "a") as fh:
+            fh.write(json.dumps(record) + "\n")
+
+
+def per_face_err(g, g64):
+    """(B, F) tensor of e_f for gradients shaped (B, F, 3, C)."""
+    g, g64 = g.double(), g64.double()
+    B, F = g.shape[:2]
+    diff = (g - g64).abs().reshape(B, F, -1).amax(dim=2)
+    mag = g64.abs().reshape(B, F, -1).amax(dim=2)
+    floor = FLOOR * g64.abs().max().clamp_min(1e-300)
+    return diff / torch.maximum(mag, floor)
+
+
+def face_grad_check(name, mine, ref32, ref64):
+    """Per-face bar.  Returns a stats dict; `ok` says whether every face met it."""
+    e = per_face_err(mine, ref64)
+    r = per_face_err(ref32, ref64)
+    strict = e <= TOL
+    escape = (~strict) & (e <= torch.clamp(1.5 * r, max=ESCAPE_CAP))
+    bad = ~(strict | escape)
+    touched = ref64.abs().reshape(e.shape[0], e.shape[1], -1).amax(dim=2) > 0
+    n = e.numel()
+    st = {
+        "tensor": name, "faces": n, "faces_with_gradient": int(touched.sum()),
+        "max_e": float(e.max()) if n else 0.0,
+        "ref32_max_e": float(r.max()) if n else 0.0,
+        "over_1e-4": int((~strict).sum()),
+        "ref32_over_1e-4": int((r > TOL).sum()),
+        "escape_used": int(escape.sum()), "failed": int(bad.sum()),
+        "global_rel": float((mine.double() - ref64.double()).abs().max()
+                            / ref64.double().abs().max().clamp_min(1e-300)) if n else 0.0,
+    }
+    if n and bool(bad.any()):
+        w = int(torch.argmax(torch.where(bad, e, torch.zeros_like(e))))
+        st["worst_face"] = [w // e.shape[1], w % e.shape[1]]
+        st["worst_e"] = float(e.reshape(-1)[w])
+        st["worst_ref32_e"] = float(r.reshape(-1)[w])
+    st["ok"] = st["failed"] == 0
+    return st

@@ -184,3 +184,14 @@ def test_dibr_rasterization_composition():
     m2, _ = orc.dibr_soft_mask_forward_py(img, idx2)
     assert torch.equal(idx, idx2) and torch.equal(interp, i2) and torch.equal(mask, m2)
     assert (idx >= 0).sum() > 100 and ((mask > 0) & (mask < 1)).sum() > 10
+
+
+@pytest.mark.parametrize("H,W", [(35, 31), (64, 64), (200, 333)])
+def test_closed_form_pair_count_matches_oracle_counter(H, W):
+    """bench.py's secondary roofline counts N_pair with
+    workloads.raster_pair_count; the oracle counts the same pairs while it rasterizes."""
+    g = wl.fixture_geometry(batch_size=3)
+    z, img, feat, nz = (g[k] for k in ("face_vertices_z", "face_vertices_image", "face_uvs",
+                                       "face_normals_z"))
+    _, _, ctx = orc.rasterize_forward(H, W, z, img, feat, nz >= 0, return_pair_count=True)
+    assert ctx["pair_count"] == wl.raster_pair_count(H, W, img, nz >= 0) > 0

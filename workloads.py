@@ -252,3 +252,26 @@ def make_config(name, device="cpu", views=None, view_slice=None, seed=0):
                             view_slice=view_slice)
     out["H"], out["W"] = c["H"], c["W"]
     return out
+
+
+def raster_pair_count(H, W, face_vertices_image, valid_faces, multiplier=1000.0):
+    """N_pair of SURVEY 8(d): the number of (pixel centre, valid face) pairs that pass the
+    reference's half-open box test (rasterization_cuda.cu:115) -- tiling independent, the
+    unit of the secondary (FP32) roofline.  Closed form per face: the pixel-centre
+    coordinates are formed exactly as the kernel forms them (:85-86) and counted against the
+    float box of the x multiplier coordinates (rasterization.py:337-344) with searchsorted.
+    Checked against the oracle's own pair counter in tests/test_oracle_golden.py."""
+    img = face_vertices_image.detach().float() * multiplier
+    dev = img.device
+    mult = torch.tensor(float(multiplier), dtype=torch.float32, device=dev)
+    xs = (mult / W) * torch.arange(1 - W, W + 1, 2, device=dev, dtype=torch.int32).float()
+    ys = (mult / H) * torch.arange(1 - H, H + 1, 2, device=dev, dtype=torch.int32).float()  # ascending
+    lo = img.min(dim=2)[0]
+    hi = img.max(dim=2)[0]
+    # pixels with lo <= c < hi  ->  searchsorted(c, hi, left) - searchsorted(c, lo, left)
+    nx = torch.searchsorted(xs, hi[..., 0].contiguous()) - torch.searchsorted(xs, lo[..., 0].contiguous())
+    ny = torch.searchsorted(ys, hi[..., 1].contiguous()) - torch.searchsorted(ys, lo[..., 1].contiguous())
+    n = nx.clamp_min(0).long() * ny.clamp_min(0).long()
+    if valid_faces is not None:
+        n = n * valid_faces.to(n.dtype)
+    return int(n.sum().item())
