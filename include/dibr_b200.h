@@ -25,7 +25,8 @@
  *
  * Workspace protocol.  The face-binning pass builds per-bin face lists whose total
  * length is data dependent.  The caller passes `ws` of `ws_bytes` bytes laid out as
- *    [ fixed part | raster list: raster_capacity int32 | soft list: soft_capacity int32 ]
+ *    [ fixed part | raster list: raster_capacity entries | soft list: soft_capacity int32 ]
+ * (a raster entry is a 48-byte face record, or an int32 face id with DIBR_B200_RASTER_REC=0)
  * with ws_bytes >= dibr_workspace_bytes_for(..., raster_capacity, soft_capacity); a call
  * that does not build a list ignores that list's capacity.  The number of list entries
  * the call needed is written as int64[2] = {raster, soft} to `needed_host`:
@@ -262,6 +263,52 @@ DIBR_API int dibr_face_setup_bwd(int batch, int num_vertices, int num_faces,
                         const float* grad_face_vertices_camera,
                         const float* grad_face_vertices_image, const float* grad_face_normals,
                         float* grad_vertices_camera, float* grad_vertices_image, void* stream);
+
+/* ---------------------------------------------------------------------------------------
+ * Mesh-level entry points: dibr_rasterization straight from the mesh.
+ * The reference builds face_vertices_camera (B,F,3,3), face_vertices_image (B,F,3,2),
+ * face_normals (B,F,3) and face_features (B,F,3,D) in torch (prepare_vertices,
+ * kaolin/render/mesh/utils.py:128-175; index_vertices_by_faces, kaolin/ops/mesh/mesh.py:25-47;
+ * face_normals, kaolin/ops/mesh/trianglemesh.py:313-337) and hands them to
+ * dibr_rasterization (dibr.py:119-209).  Here every kernel of the path fetches the corners
+ * through `faces`, so those tensors never exist, and the backward adds straight into
+ * vertex-level gradients.
+ *   vertices_camera  (B, V, 3)   camera-space vertices: z = [..., 2], and the unit face normal
+ *                                whose z >= 0 selects the rasterized faces (dibr.py:190-199)
+ *   vertices_image   (B, V, 2)   NDC, not multiplied
+ *   faces            (F, 3)      int32 vertex ids (faces with an id outside [0, V) are skipped)
+ *   vertex_features  (B, V, D), or (1, V, D) shared by all views when features_shared != 0
+ *   valid_faces      (B, F) uint8 or NULL; when given it replaces the normal test
+ * Results are bit-identical to dibr_render_fwd on the face tensors dibr_face_setup_fwd /
+ * dibr_index_vertices_by_faces produce from the same arrays.  Workspace protocol and pair
+ * buffer as for dibr_render_fwd (same dibr_workspace_bytes_for).
+ * The backward zero-fills and then accumulates grad_vertices_image (B, V, 2) and
+ * grad_vertex_features (B or 1, V, D) -- with features_shared the views are summed, which
+ * makes it the vertex-level message of the multi-GPU all-reduce; vertices_camera receives
+ * no gradient (as face_vertices_z / face_normals_z in the reference, rasterization.py:387-388).
+ * `moment_scratch`: dibr_mesh_moment_bytes(B, F, D) bytes of device memory (contents
+ * irrelevant; the per-face moment accumulators of the two-pass backward).
+ * ------------------------------------------------------------------------------------- */
+DIBR_API int dibr_render_mesh_fwd(int batch, int num_vertices, int num_faces, int height,
+                         int width, int feat_dim, const float* vertices_camera,
+                         const float* vertices_image, const int32_t* faces,
+                         const float* vertex_features, int features_shared,
+                         const uint8_t* valid_faces, float sigmainv, float box_margin, int knum,
+                         float multiplier, float eps, int64_t* selected_face_idx,
+                         float* interpolated_features, float* soft_mask, void* ws,
+                         int64_t ws_bytes, int64_t raster_capacity, int64_t soft_capacity,
+                         int64_t pair_capacity, int64_t* needed_host, void* stream);
+DIBR_API int64_t dibr_mesh_moment_bytes(int batch, int num_faces, int feat_dim);
+DIBR_API int dibr_render_mesh_bwd(int batch, int num_vertices, int num_faces, int height,
+                         int width, int feat_dim, const float* grad_interpolated_features,
+                         const float* grad_soft_mask, const int64_t* selected_face_idx,
+                         const float* vertices_image, const int32_t* faces,
+                         const float* vertex_features, int features_shared,
+                         const float* soft_mask, float sigmainv, float box_margin, int knum,
+                         float multiplier, float eps, float* grad_vertices_image,
+                         float* grad_vertex_features, void* moment_scratch, const void* ws,
+                         int64_t ws_bytes, int64_t raster_capacity, int64_t soft_capacity,
+                         int64_t pair_capacity, void* stream);
 
 /* ---------------------------------------------------------------------------------------
  * Double precision: the reference dispatches float and double (rasterization_cuda.cu:30-39,

@@ -134,8 +134,24 @@ struct Workspace {
   char* base;
   int64_t cap[2];
   int* list[2];
+  float4* rec;     // the raster list area as records (same memory as list[0]) or nullptr
   PairBuf pairs;
 };
+
+// The rasterizer's list as 48-byte face records streamed with bulk async copies (default)
+// or as face ids gathered through the face tensors (DIBR_B200_RASTER_REC=0: the A/B
+// switch of the experiment recorded in DESIGN.md).  Process-wide, read once.
+static bool raster_rec_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("DIBR_B200_RASTER_REC");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+static int64_t raster_entry_bytes() { return raster_rec_enabled() ? kRecBytes : 4; }
+static int64_t lists_bytes(int64_t cap_r, int64_t cap_s) {
+  return align_up(cap_r * raster_entry_bytes(), 256) + align_up(cap_s * 4, 256);
+}
 
 // Pair area (compact soft-mask face lists kept for the backward) for `cap` segments.
 static int pair_nseg(int K) { return (K + kPairSegHits - 1) / kPairSegHits; }
@@ -154,7 +170,7 @@ static int bind_workspace(const Plan& p, const void* ws, int64_t ws_bytes, int64
   if (cap_r > kMaxListEntries || cap_s > kMaxListEntries)
     return fail(DIBR_E_INVALID, "list capacity above 2^31 - 2^16 entries");
   if (cap_p > (1 << 23)) return fail(DIBR_E_INVALID, "pair capacity above 2^23 segments");
-  const int64_t lists_end = align_up(p.fixed_bytes + 4 * (cap_r + cap_s), 256);
+  const int64_t lists_end = p.fixed_bytes + lists_bytes(cap_r, cap_s);
   const int64_t need = lists_end + pair_bytes(cap_p, K);
   if (!ws || ws_bytes < need)
     return fail(DIBR_E_WORKSPACE, "workspace of %lld bytes given, %lld needed",
@@ -164,7 +180,8 @@ static int bind_workspace(const Plan& p, const void* ws, int64_t ws_bytes, int64
   w.cap[0] = cap_r;
   w.cap[1] = cap_s;
   w.list[0] = (int*)(w.base + p.fixed_bytes);
-  w.list[1] = w.list[0] + cap_r;
+  w.list[1] = (int*)(w.base + p.fixed_bytes + align_up(cap_r * raster_entry_bytes(), 256));
+  w.rec = raster_rec_enabled() ? (float4*)w.list[0] : nullptr;
   memset(&w.pairs, 0, sizeof(w.pairs));
   if (pair_usable(cap_p, K)) {
     PairBuf& pb = w.pairs;
@@ -296,7 +313,7 @@ extern "C" int64_t dibr_workspace_bytes_for(int B, int F, int H, int W, int64_t 
   Plan p;
   int rc = make_plan(B, F, H, W, p);
   if (rc) return rc;
-  return align_up(p.fixed_bytes + 4 * ((cap_r > 0 ? cap_r : 0) + (cap_s > 0 ? cap_s : 0)), 256) +
+  return p.fixed_bytes + lists_bytes(cap_r > 0 ? cap_r : 0, cap_s > 0 ? cap_s : 0) +
          pair_bytes(cap_p, K);
 }
 
@@ -333,11 +350,13 @@ extern "C" int dibr_rasterize_fwd(int B, int F, int H, int W, int D, const float
   jobs.j[0] = face_source(img, bboxes, valid, normal_z, first, prescaled ? 0 : F, multiplier,
                           0.f, prescaled);
   attach(jobs.j[0], p, w, 0);
+  if (!prescaled) { jobs.j[0].rec = w.rec; jobs.j[0].z = z; }
   jobs.j[1] = jobs.j[0];
   const int kinds[1] = {0};
   if ((rc = run_binning(p, w, jobs, kinds, 1, needed_host, st))) return rc;
   RasterArgs a;
-  a.job = jobs.j[0]; a.z = z; a.feat = feat; a.D = D; a.eps_d = (double)eps;
+  memset(&a, 0, sizeof(a));
+  a.job = jobs.j[0]; a.rec = jobs.j[0].rec; a.z = z; a.feat = feat; a.D = D; a.eps_d = (double)eps;
   a.out_idx = out_idx; a.out_feat = out_feat; a.out_w = out_w;
   a.block_uncovered = (int*)(w.base + p.off_flags);
   DIBR_CUDA(launch_raster_forward(a, p, st));
@@ -356,11 +375,13 @@ extern "C" int dibr_rasterize_bwd(int B, int F, int H, int W, int D, const float
   if (!grad || !idx || !img || !feat || !grad_img || !grad_feat)
     return fail(DIBR_E_INVALID, "null pointer");
   RasterBwdArgs a;
+  memset(&a, 0, sizeof(a));
   a.grad = grad; a.idx = idx; a.weights = weights; a.img = img; a.feat = feat;
   a.grad_img = grad_img; a.grad_feat = grad_feat;
   a.B = B; a.F = F; a.H = H; a.W = W; a.D = D;
+  a.moments = grad_feat;
   a.mult = multiplier; a.eps_f = eps; a.eps_d = (double)eps;
-  a.inv_w = 1.0 / (double)W; a.inv_h = 1.0 / (double)H;
+  a.inv_mult = 1.0 / (double)multiplier; a.grid = make_grid(multiplier, W, H);
   DIBR_CUDA(launch_raster_backward(a, (cudaStream_t)stream));
   return DIBR_OK;
 }
@@ -479,12 +500,14 @@ extern "C" int dibr_render_bwd(int B, int F, int H, int W, int D, const float* g
   const bool do_raster = grad_feat_img && D > 0, do_soft = grad_mask && K > 0;
   if (do_soft && !mask) return fail(DIBR_E_INVALID, "null soft_mask");
   RasterBwdArgs ra;
+  memset(&ra, 0, sizeof(ra));
   if (do_raster) {
     ra.grad = grad_feat_img; ra.idx = idx; ra.weights = nullptr; ra.img = img; ra.feat = feat;
     ra.grad_img = grad_img; ra.grad_feat = grad_feat;
     ra.B = B; ra.F = F; ra.H = H; ra.W = W; ra.D = D;
+    ra.moments = grad_feat;
     ra.mult = multiplier; ra.eps_f = eps; ra.eps_d = (double)eps;
-    ra.inv_w = 1.0 / (double)W; ra.inv_h = 1.0 / (double)H;
+    ra.inv_mult = 1.0 / (double)multiplier; ra.grid = make_grid(multiplier, W, H);
     DIBR_CUDA(launch_raster_backward_moments(ra, st));
   }
   if (do_soft) {
@@ -539,10 +562,12 @@ extern "C" int dibr_render_fwd(int B, int F, int H, int W, int D, const float* z
   jobs.j[1] = face_source(img, nullptr, nullptr, nullptr, nullptr, F, multiplier, box_margin, 0);
   attach(jobs.j[0], p, w, 0);
   attach(jobs.j[1], p, w, 1);
+  jobs.j[0].rec = w.rec; jobs.j[0].z = z;
   const int kinds[2] = {0, 1};
   if ((rc = run_binning(p, w, jobs, kinds, 2, needed_host, st))) return rc;
   RasterArgs a;
-  a.job = jobs.j[0]; a.z = z; a.feat = feat; a.D = D; a.eps_d = (double)eps;
+  memset(&a, 0, sizeof(a));
+  a.job = jobs.j[0]; a.rec = jobs.j[0].rec; a.z = z; a.feat = feat; a.D = D; a.eps_d = (double)eps;
   a.out_idx = out_idx; a.out_feat = out_feat; a.out_w = nullptr;
   a.block_uncovered = (int*)(w.base + p.off_flags);
   DIBR_CUDA(launch_raster_forward(a, p, st));
@@ -647,5 +672,133 @@ extern "C" int dibr_softmask_bwd_dense_f64(int B, int F, int H, int W, int K,
   a.type = type; a.img = img_scaled; a.grad_img = grad_img;
   a.B = B; a.F = F; a.H = H; a.W = W; a.K = K; a.sigmainv = sigmainv; a.mult = multiplier;
   DIBR_CUDA(launch_softmask_backward_f64(a, (cudaStream_t)stream));
+  return DIBR_OK;
+}
+
+
+// ---------------------------------------------------------------- mesh-level entry points
+// the renderer reads the face corners THROUGH `faces` from the per-view
+// vertex arrays, so the (B, F, 3, .) face tensors of prepare_vertices
+// (kaolin/render/mesh/utils.py:128-175, ops/mesh/mesh.py:25-47, trianglemesh.py:313-337)
+// never exist, and the backward adds straight into vertex-level gradients.
+static BinJob mesh_source(const int* faces, const float* vimg, const float* vcam, int V, int F,
+                          const uint8_t* valid, int cull, float mult, float margin) {
+  BinJob j;
+  memset(&j, 0, sizeof(j));
+  j.faces = faces; j.vimg = vimg; j.vcam = vcam; j.V = V; j.mesh_cull = cull;
+  j.valid = valid; j.view_stride = F; j.mult = mult; j.margin = margin;
+  return j;
+}
+
+extern "C" int dibr_render_mesh_fwd(int B, int V, int F, int H, int W, int D,
+                                    const float* vertices_camera, const float* vertices_image,
+                                    const int32_t* faces, const float* vertex_features,
+                                    int features_shared, const uint8_t* valid_faces,
+                                    float sigmainv, float box_margin, int K, float multiplier,
+                                    float eps, int64_t* out_idx, float* out_feat, float* mask,
+                                    void* ws, int64_t ws_bytes, int64_t cap_r, int64_t cap_s,
+                                    int64_t cap_p, int64_t* needed_host, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  Plan p;
+  int rc = make_plan(B, F, H, W, p, multiplier);
+  if (rc) return rc;
+  if ((rc = check_common(multiplier))) return rc;
+  if (D < 0 || K < 0 || V < 0) return fail(DIBR_E_INVALID, "feat_dim / knum / num_vertices < 0");
+  if (B == 0) return DIBR_OK;
+  if (!out_idx || (!out_feat && D > 0) || !mask) return fail(DIBR_E_INVALID, "null output");
+  if (F > 0 && (!faces || !vertices_image || (!vertices_camera) || (!vertex_features && D > 0)))
+    return fail(DIBR_E_INVALID, "null input");
+  Workspace w;
+  if ((rc = bind_workspace(p, ws, ws_bytes, cap_r, cap_s, w, cap_p, K))) return rc;
+  BinJobs jobs;
+  // rasterizer: valid_faces if given, else normal_z >= 0 from the camera-space corners
+  // (dibr.py:190-199); soft mask: every face (dibr.py:201-203)
+  jobs.j[0] = mesh_source(faces, vertices_image, vertices_camera, V, F, valid_faces,
+                          valid_faces ? 0 : 1, multiplier, 0.f);
+  jobs.j[1] = mesh_source(faces, vertices_image, vertices_camera, V, F, nullptr, 0, multiplier,
+                          box_margin);
+  attach(jobs.j[0], p, w, 0);
+  attach(jobs.j[1], p, w, 1);
+  jobs.j[0].rec = w.rec; jobs.j[0].z = nullptr;
+  const int kinds[2] = {0, 1};
+  if ((rc = run_binning(p, w, jobs, kinds, 2, needed_host, st))) return rc;
+  RasterArgs a;
+  memset(&a, 0, sizeof(a));
+  a.job = jobs.j[0]; a.rec = jobs.j[0].rec; a.z = nullptr; a.feat = vertex_features;
+  a.feat_shared = features_shared; a.D = D; a.eps_d = (double)eps;
+  a.out_idx = out_idx; a.out_feat = out_feat; a.out_w = nullptr;
+  a.block_uncovered = (int*)(w.base + p.off_flags);
+  DIBR_CUDA(launch_raster_forward(a, p, st));
+  SoftArgs s;
+  memset(&s, 0, sizeof(s));
+  s.job = jobs.j[1]; s.sel = out_idx; s.sigmainv = sigmainv; s.K = K; s.mask = mask;
+  s.pairs = w.pairs;
+  s.block_uncovered = (const int*)(w.base + p.off_flags);
+  return run_soft_forward(s, p, needed_host, st);
+}
+
+extern "C" int64_t dibr_mesh_moment_bytes(int B, int F, int D) {
+  if (B < 0 || F < 0 || D < 0) return DIBR_E_INVALID;
+  return align_up((int64_t)B * F * 3 * D * 4, 256);
+}
+
+extern "C" int dibr_render_mesh_bwd(int B, int V, int F, int H, int W, int D,
+                                    const float* grad_feat_img, const float* grad_mask,
+                                    const int64_t* idx, const float* vertices_image,
+                                    const int32_t* faces, const float* vertex_features,
+                                    int features_shared, const float* mask, float sigmainv,
+                                    float box_margin, int K, float multiplier, float eps,
+                                    float* grad_vertices_image, float* grad_vertex_features,
+                                    void* moment_scratch, const void* ws, int64_t ws_bytes,
+                                    int64_t cap_r, int64_t cap_s, int64_t cap_p, void* stream) {
+  if (B < 0 || V < 0 || F < 0 || H <= 0 || W <= 0 || D < 0 || K < 0)
+    return fail(DIBR_E_INVALID, "invalid sizes");
+  int rc = check_common(multiplier);
+  if (rc) return rc;
+  if (B > 65535) return fail(DIBR_E_INVALID, "batch %d > 65535 not supported", B);
+  if (B == 0) return DIBR_OK;
+  if (!grad_vertices_image || (D > 0 && !grad_vertex_features))
+    return fail(DIBR_E_INVALID, "null gradient output");
+  cudaStream_t st = (cudaStream_t)stream;
+  DIBR_CUDA(cudaMemsetAsync(grad_vertices_image, 0, (size_t)B * V * 2 * sizeof(float), st));
+  if (D > 0)
+    DIBR_CUDA(cudaMemsetAsync(grad_vertex_features, 0,
+                              (size_t)(features_shared ? 1 : B) * V * D * sizeof(float), st));
+  if (F == 0 || V == 0) return DIBR_OK;
+  if (!idx || !vertices_image || !faces || (D > 0 && !vertex_features))
+    return fail(DIBR_E_INVALID, "null pointer");
+  const bool do_raster = grad_feat_img && D > 0, do_soft = grad_mask && K > 0;
+  if (do_soft && !mask) return fail(DIBR_E_INVALID, "null soft_mask");
+  if (do_raster && !moment_scratch) return fail(DIBR_E_INVALID, "null moment scratch");
+  RasterBwdArgs ra;
+  memset(&ra, 0, sizeof(ra));
+  if (do_raster) {
+    DIBR_CUDA(cudaMemsetAsync(moment_scratch, 0, (size_t)B * F * 3 * D * sizeof(float), st));
+    ra.grad = grad_feat_img; ra.idx = idx; ra.weights = nullptr; ra.img = vertices_image;
+    ra.feat = vertex_features; ra.grad_img = grad_vertices_image;
+    ra.grad_feat = grad_vertex_features; ra.moments = (float*)moment_scratch;
+    ra.faces = faces; ra.V = V; ra.feat_shared = features_shared;
+    ra.B = B; ra.F = F; ra.H = H; ra.W = W; ra.D = D;
+    ra.mult = multiplier; ra.eps_f = eps; ra.eps_d = (double)eps;
+    ra.inv_mult = 1.0 / (double)multiplier; ra.grid = make_grid(multiplier, W, H);
+    DIBR_CUDA(launch_raster_backward_moments(ra, st));
+  }
+  if (do_soft) {
+    Plan p;
+    if ((rc = make_plan(B, F, H, W, p, multiplier))) return rc;
+    Workspace w;
+    if ((rc = bind_workspace(p, ws, ws_bytes, cap_r, cap_s, w, cap_p, K))) return rc;
+    BinJob job = mesh_source(faces, vertices_image, nullptr, V, F, nullptr, 0, multiplier,
+                             box_margin);
+    attach(job, p, w, 1);
+    SoftArgs a;
+    memset(&a, 0, sizeof(a));
+    a.job = job; a.sel = idx; a.sigmainv = sigmainv; a.K = K;
+    a.grad_mask = grad_mask; a.mask_in = mask; a.grad_img = grad_vertices_image;
+    a.pairs = w.pairs;
+    DIBR_CUDA(launch_softmask_pairs_grad(a, p, st));
+    DIBR_CUDA(launch_softmask(a, SOFT_BWD, p, st));
+  }
+  if (do_raster) DIBR_CUDA(launch_raster_backward_finish(ra, st));
   return DIBR_OK;
 }

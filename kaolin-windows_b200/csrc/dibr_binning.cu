@@ -82,20 +82,35 @@ bin_walk_kernel(const BinJobs jobs, const Plan p) {
     const int f = f0 + lane;
     int bx0 = 0, bx1 = -1, by0 = 0, by1 = -1;
     bool act = false;
+    Face2D fc;
     if (f < f_end) {
-      Face2D fc;
       if (load_face2d(job, b, f, fc)) act = bin_rect(g, fc, p.bin_log2, bx0, bx1, by0, by1);
     }
     // Where the order inside a bin's list does not matter -- the counting pass, and the
     // fill of the rasterizer's list (its depth test is order independent) -- every lane
     // simply bumps the shared-memory counters of the bins of its rectangle.
     if (!FILL || !job.ordered) {
+      float4 q0, q1, q2;
+      if (FILL && job.rec && by0 <= by1) {
+        float za, zb, zc;
+        face_depths(job, job.z, b, f, za, zb, zc);
+        q0 = make_float4(fc.ax, fc.ay, fc.bx, fc.by);
+        q1 = make_float4(fc.cx, fc.cy, za, zb);
+        q2 = make_float4(zc, __int_as_float(f), 0.f, 0.f);
+      }
       for (int cy = by0; cy <= by1; cy++)
         for (int cx = bx0; cx <= bx1; cx++) {
           const int bin = cy * p.nbx + cx;
           const int slot = atomicAdd(&hist[bin], 1);
           if (FILL) {
-            if (slot >= 0 && slot < job.capacity) job.list[slot] = f;
+            if (slot >= 0 && slot < job.capacity) {
+              if (job.rec) {
+                float4* r = job.rec + (long long)slot * 3;
+                r[0] = q0; r[1] = q1; r[2] = q2;
+              } else {
+                job.list[slot] = f;
+              }
+            }
           } else {
             lo_bin = min(lo_bin, bin);
             hi_bin = max(hi_bin, bin);

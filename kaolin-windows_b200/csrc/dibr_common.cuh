@@ -69,6 +69,15 @@ struct Plan {
 
 // One binning job = one list kind.  Passed by value to the kernels.
 struct BinJob {
+  // Mesh mode (faces != nullptr): the face corners are fetched through `faces` from the
+  // per-view vertex arrays -- no (B, F, 3, .) face tensor exists; img / valid / normal_z /
+  // first / bbox are null and a face is valid iff the unit normal's z computed from vcam is
+  // >= 0 (mesh_cull) or always (soft list).
+  const int* faces;        // (F, 3) int32 vertex ids
+  const float* vimg;       // (B, V, 2) vertices_image
+  const float* vcam;       // (B, V, 3) vertices_camera (z = [..., 2])
+  int V;
+  int mesh_cull;           // raster list: keep faces whose normal z >= 0
   const float* img;        // (B or 1, F, 3, 2)
   const float* bbox;       // explicit boxes (., F, 4) or nullptr (computed)
   const uint8_t* valid;    // (B, F) or nullptr
@@ -84,6 +93,11 @@ struct BinJob {
   int* start;
   int* count;
   int* list;
+  // raster list as compact records instead of face ids (fused path): 3 x float4 per entry,
+  // {ax, ay, bx, by} {cx, cy, za, zb} {zc, face id bits, 0, 0} with scaled coordinates;
+  // written by the fill pass (which needs `z`), streamed by the rasterizer
+  float4* rec;
+  const float* z;          // (., F, 3), only read when rec != nullptr
   int* order;              // [16][B * NB] rows of each length bucket (filled by bin_scan)
   int* bucket;             // [16] rows per bucket
   unsigned long long* total;
@@ -102,8 +116,10 @@ struct BinJobs {
 
 struct RasterArgs {
   BinJob job;              // raster list + how to read faces
+  const float4* rec;       // = job.rec: the list as records, or nullptr (list of face ids)
   const float* z;          // (., F, 3)
-  const float* feat;       // (., F, 3, D)
+  const float* feat;       // (., F, 3, D); mesh mode: vertex features (B or 1, V, D)
+  int feat_shared;         // mesh mode: one (V, D) feature array for all views
   int D;
   double eps_d;
   int64_t* out_idx;        // (B, H, W)
@@ -120,11 +136,19 @@ struct RasterBwdArgs {
   const float* feat;       // (B, F, 3, D)
   float* grad_img;         // (B, F, 3, 2)
   float* grad_feat;        // (B, F, 3, D)
+  float* moments;          // (B, F, 3, D) accumulator of pass 1 (= grad_feat: in place)
+  // mesh mode (faces != nullptr): img = vertices_image (B, V, 2), feat = vertex features
+  // (B or 1, V, D), grad_img / grad_feat the vertex gradients of the same shapes (added to
+  // with atomics), moments a separate zero-filled scratch
+  const int* faces;        // (F, 3) int32 or nullptr
+  int V;
+  int feat_shared;
   int B, F, H, W, D;
   float mult;
   float eps_f;
   double eps_d;
-  double inv_w, inv_h;     // 1 / W, 1 / H
+  double inv_mult;         // 1 / multiplier
+  Grid grid;               // make_grid(mult, W, H): pixel centres as the forward forms them
 };
 
 // Compact per-pixel face lists of the soft mask ("pairs"), kept between forward and
@@ -153,6 +177,7 @@ constexpr int kPairChunk = 128;
 // list capacities stay this far below 2^31 so that the fill kernel's int slot counters
 // (segment start + up to S increments per chunk) cannot wrap
 constexpr long long kMaxListEntries = 0x7fffffffll - 65536;
+constexpr int kRecBytes = 48;   // one raster-list record (BinJob::rec)
 
 __device__ __forceinline__ bool pairs_overflowed(const PairBuf& pb) {
   return pb.cursor[0] > (unsigned long long)pb.cap || pb.cursor[1] > (unsigned long long)pb.cap;
@@ -345,6 +370,60 @@ struct Face2D {
 // part of the list (invalid, outside the packed range, or non-finite coordinates).
 // LISTED: `f` comes out of the job's own face list, which binning only fills with faces
 // that passed these checks -- consumers skip the (dependent) validity loads.
+// z component of the unit face normal as prepare_vertices forms it (face_normals(unit=True),
+// trianglemesh.py:328-335: cross of the edges from corner 0, divided by length + 1e-10);
+// ONE definition for the face-setup kernel (dibr_mesh.cu) and the mesh-mode validity test,
+// with explicit roundings so that both give the same bits
+__device__ __forceinline__ float3 unit_face_normal(const float* p0, const float* p1,
+                                                   const float* p2) {
+  const float e0x = __fsub_rn(p1[0], p0[0]), e0y = __fsub_rn(p1[1], p0[1]), e0z = __fsub_rn(p1[2], p0[2]);
+  const float e1x = __fsub_rn(p2[0], p0[0]), e1y = __fsub_rn(p2[1], p0[1]), e1z = __fsub_rn(p2[2], p0[2]);
+  const float nx = __fmaf_rn(e0y, e1z, -__fmul_rn(e0z, e1y));
+  const float ny = __fmaf_rn(e0z, e1x, -__fmul_rn(e0x, e1z));
+  const float nz = __fmaf_rn(e0x, e1y, -__fmul_rn(e0y, e1x));
+  const float len = __fadd_rn(__fsqrt_rn(__fmaf_rn(nz, nz, __fmaf_rn(ny, ny, __fmul_rn(nx, nx)))),
+                              1e-10f);
+  return make_float3(__fdiv_rn(nx, len), __fdiv_rn(ny, len), __fdiv_rn(nz, len));
+}
+
+// the three vertex ids of face f (mesh mode); false if any is out of range
+__device__ __forceinline__ bool mesh_face(const BinJob& j, int f, int (&v)[3]) {
+  const int* fp = j.faces + (long long)f * 3;
+  v[0] = __ldg(fp); v[1] = __ldg(fp + 1); v[2] = __ldg(fp + 2);
+  return (unsigned)v[0] < (unsigned)j.V && (unsigned)v[1] < (unsigned)j.V &&
+         (unsigned)v[2] < (unsigned)j.V;
+}
+
+// unscaled image coordinates of the three corners of face f of view b, either layout
+__device__ __forceinline__ bool face_corners(const BinJob& j, int b, int f, float2& a, float2& bb,
+                                             float2& c) {
+  if (j.faces) {
+    int v[3];
+    if (!mesh_face(j, f, v)) return false;
+    const float2* vp = reinterpret_cast<const float2*>(j.vimg) + (long long)b * j.V;
+    a = __ldg(vp + v[0]); bb = __ldg(vp + v[1]); c = __ldg(vp + v[2]);
+    return true;
+  }
+  const float2* p = reinterpret_cast<const float2*>(j.img + ((long long)b * j.view_stride + f) * 6);
+  a = __ldg(p); bb = __ldg(p + 1); c = __ldg(p + 2);
+  return true;
+}
+
+// depths of the three corners (rasterizer), either layout
+__device__ __forceinline__ void face_depths(const BinJob& j, const float* z, int b, int f,
+                                            float& za, float& zb, float& zc) {
+  if (j.faces) {
+    int v[3];
+    za = zb = zc = 0.f;
+    if (!mesh_face(j, f, v)) return;
+    const float* vp = j.vcam + (long long)b * j.V * 3;
+    za = __ldg(vp + v[0] * 3 + 2); zb = __ldg(vp + v[1] * 3 + 2); zc = __ldg(vp + v[2] * 3 + 2);
+    return;
+  }
+  const float* zp = z + ((long long)b * j.view_stride + f) * 3;
+  za = __ldg(zp); zb = __ldg(zp + 1); zc = __ldg(zp + 2);
+}
+
 template <bool LISTED = false>
 __device__ __forceinline__ bool load_face2d(const BinJob& j, int b, int f, Face2D& o) {
   const long long gi = (long long)b * j.view_stride + f;
@@ -354,9 +433,15 @@ __device__ __forceinline__ bool load_face2d(const BinJob& j, int b, int f, Face2
     }
     if (j.valid && !j.valid[gi]) return false;
     if (j.normal_z && !(j.normal_z[gi] >= 0.f)) return false;
+    if (j.faces && j.mesh_cull) {
+      int v[3];
+      if (!mesh_face(j, f, v)) return false;
+      const float* vp = j.vcam + (long long)b * j.V * 3;
+      if (!(unit_face_normal(vp + v[0] * 3, vp + v[1] * 3, vp + v[2] * 3).z >= 0.f)) return false;
+    }
   }
-  const float2* p = reinterpret_cast<const float2*>(j.img + gi * 6);
-  float2 a = __ldg(p), bb = __ldg(p + 1), c = __ldg(p + 2);
+  float2 a, bb, c;
+  if (!face_corners(j, b, f, a, bb, c)) return false;
   if (!j.prescaled) {
     a.x = __fmul_rn(a.x, j.mult); a.y = __fmul_rn(a.y, j.mult);
     bb.x = __fmul_rn(bb.x, j.mult); bb.y = __fmul_rn(bb.y, j.mult);

@@ -90,11 +90,11 @@ face_setup_forward_kernel(const float* __restrict__ vcam, const float* __restric
         s_img[t * 6 + c * 2 + 1] = ok ? __ldg(vimg + ((long long)b * V + v) * 2 + 1) : 0.f;
       }
     }
-    const Vec3 n = cross(sub(p[1], p[0]), sub(p[2], p[0]));
-    const float len = sqrtf(dot(n, n)) + 1e-10f;
-    s_n[t * 3 + 0] = n.x / len;
-    s_n[t * 3 + 1] = n.y / len;
-    s_n[t * 3 + 2] = n.z / len;
+    // one definition shared with the mesh-mode renderer's validity test (dibr_common.cuh)
+    const float3 n = unit_face_normal(&p[0].x, &p[1].x, &p[2].x);
+    s_n[t * 3 + 0] = n.x;
+    s_n[t * 3 + 1] = n.y;
+    s_n[t * 3 + 2] = n.z;
   }
   __syncthreads();
   const long long base = (long long)b * F + f0;

@@ -115,20 +115,37 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
     {
       const long long li = base + tid;
       if (li < n) {
-        const int f = a.job.list[start + li];
-        // the next chunk's entry now, its face record into L1 while this chunk is worked on
-        if (li + kRasterThreads < n) {
-          const long long gn = (long long)b * a.job.view_stride +
-                               a.job.list[start + li + kRasterThreads];
-          prefetch_l1(a.job.img + gn * 6);
-          prefetch_l1(a.z + gn * 3);
-        }
-        const long long gi = (long long)b * a.job.view_stride + f;
-        // depths requested together with the coordinates (one round trip, not two)
-        const float z_a = __ldg(a.z + gi * 3), z_b = __ldg(a.z + gi * 3 + 1);
-        const float z_c = __ldg(a.z + gi * 3 + 2);
+        int f;
+        float z_a, z_b, z_c;
         Face2D fc;
-        if (load_face2d<true>(a.job, b, f, fc) &&
+        bool have;
+        if (a.rec) {
+          // the list as compact records written by the binning pass: three 16-byte loads
+          // from consecutive addresses, no dependent gather through the face id
+          const float4* r = a.rec + (start + li) * 3;
+          const float4 q0 = __ldg(r), q1 = __ldg(r + 1), q2 = __ldg(r + 2);
+          if (li + kRasterThreads < n) prefetch_l1(r + 3 * kRasterThreads);
+          fc.ax = q0.x; fc.ay = q0.y; fc.bx = q0.z; fc.by = q0.w; fc.cx = q1.x; fc.cy = q1.y;
+          z_a = q1.z; z_b = q1.w; z_c = q2.x;
+          f = __float_as_int(q2.y);
+          // the box of the scaled coordinates (rasterization.py:342-344)
+          fc.xmin = fminf(fminf(fc.ax, fc.bx), fc.cx); fc.ymin = fminf(fminf(fc.ay, fc.by), fc.cy);
+          fc.xmax = fmaxf(fmaxf(fc.ax, fc.bx), fc.cx); fc.ymax = fmaxf(fmaxf(fc.ay, fc.by), fc.cy);
+          have = true;
+        } else {
+          f = a.job.list[start + li];
+          // the next chunk's entry now, its face record into L1 while this chunk is worked on
+          if (!a.job.faces && li + kRasterThreads < n) {
+            const long long gn = (long long)b * a.job.view_stride +
+                                 a.job.list[start + li + kRasterThreads];
+            prefetch_l1(a.job.img + gn * 6);
+            prefetch_l1(a.z + gn * 3);
+          }
+          // depths requested together with the coordinates (one round trip, not two)
+          face_depths(a.job, a.z, b, f, z_a, z_b, z_c);
+          have = load_face2d<true>(a.job, b, f, fc);
+        }
+        if (have &&
             pixel_range(g, fc.xmin, fc.ymin, fc.xmax, fc.ymax, x_lo, x_hi, y_lo, y_hi)) {
           x_lo = max(x_lo, bx0); x_hi = min(x_hi, bx1);
           y_lo = max(y_lo, by0); y_hi = min(y_hi, by1);
@@ -302,7 +319,7 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
   // not one per pixel and tensor.
   for (int i = tid; i < BLK * BLK; i += kRasterThreads) {
     const unsigned long long key = zbuf[i];
-    if (key) {
+    if (key && !a.job.faces) {
       const int face = key_face(key);
       const long long gi = (long long)b * a.job.view_stride +
                            (a.job.first ? face + (int)a.job.first[b] : face);
@@ -327,14 +344,25 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
     }
     const int face = key_face(key);
     const int f = a.job.first ? face + (int)a.job.first[b] : face;
-    const float* fp = a.feat + ((long long)b * a.job.view_stride + f) * 3 * a.D;
+    const float *fp0, *fp1, *fp2;   // features of the three corners
+    if (a.job.faces) {
+      int v[3];
+      mesh_face(a.job, f, v);   // listed faces have valid ids
+      const float* vb = a.feat + (a.feat_shared ? 0ll : (long long)b * a.job.V) * a.D;
+      fp0 = vb + (long long)v[0] * a.D; fp1 = vb + (long long)v[1] * a.D;
+      fp2 = vb + (long long)v[2] * a.D;
+    } else {
+      fp0 = a.feat + ((long long)b * a.job.view_stride + f) * 3 * a.D;
+      fp1 = fp0 + a.D;
+      fp2 = fp1 + a.D;
+    }
     // features before any store (the stores may alias them as far as the compiler knows)
     float r[3][4];
     const int dn = a.D < 4 ? a.D : 4;
 #pragma unroll
     for (int d = 0; d < 4; d++) {
       if (d < dn) {
-        r[0][d] = __ldg(fp + d); r[1][d] = __ldg(fp + a.D + d); r[2][d] = __ldg(fp + 2 * a.D + d);
+        r[0][d] = __ldg(fp0 + d); r[1][d] = __ldg(fp1 + d); r[2][d] = __ldg(fp2 + d);
       }
     }
     Face2D fc;
@@ -350,7 +378,7 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
         a.out_feat[pix * a.D + d] =
             __fmaf_rn(w2, r[2][d], __fmaf_rn(w0, r[0][d], __fmul_rn(w1, r[1][d])));
     for (int d = 4; d < a.D; d++) {
-      const float r0 = __ldg(fp + d), r1 = __ldg(fp + a.D + d), r2 = __ldg(fp + 2 * a.D + d);
+      const float r0 = __ldg(fp0 + d), r1 = __ldg(fp1 + d), r2 = __ldg(fp2 + d);
       a.out_feat[pix * a.D + d] = __fmaf_rn(w2, r2, __fmaf_rn(w0, r0, __fmul_rn(w1, r1)));
     }
   }
@@ -407,31 +435,71 @@ cudaError_t launch_raster_forward(const RasterArgs& a, const Plan& p, cudaStream
 //     grouped with __match_any_sync, their moments summed with shuffles, and ONE
 //     red.global.add per (face, moment) leaves the warp -- into grad_face_features, whose
 //     (3, D) slot per face is used as the moment accumulator;
-//   pass 2 (face-parallel): turns the moments of every touched face into grad_face_features
-//     (in place) and grad_face_vertices_image (added) with plain stores.
-// Faces for which the moment form would not stay within a few ulp of the per-pixel form
-// keep the reference's per-pixel arithmetic in pass 1 and are skipped by pass 2: slivers
-// and zero-area faces (|k3| < 1% of |m q| + |n p|) and faces smaller than two pixels
-// (|k3| < 4 pixel areas) -- the latter own one or two pixels, have the largest gradients
-// (~ 1 / k3^2) and gain nothing from the moments anyway.
+//   pass 2 (face-parallel, FP64): turns the moments of every touched face into
+//     grad_face_features (in place) and grad_face_vertices_image (added) with plain stores.
+// Precision.  The gradient is a function of the pixel CENTRE; the reference reconstructs the
+// centre from the fp32 weights its forward saved (:302-303), whose rounding -- and that of
+// fl32(v * multiplier) -- is a 1e-4 .. 1e-2 relative perturbation of (s, t) for sub-pixel
+// faces (it is the reference's fp32 noise against its own fp64 run).  Here (s, t) come from
+// the pixel centre itself, formed as the kernel forms it (:85-86) and differenced in double,
+// which is what the reference computes when run in double.  The eps of the forward's
+// normalisation (:140-142) scales all three weights by rho = |N| / (|N| + eps), N = the
+// face's area term in multiplied coordinates; the reconstructed centre is rho * X: both
+// are carried through (they matter for small multipliers).
+// Faces for which the fp32 moment sums would not stay within a few ulp -- slivers / zero
+// area (|k3| < 10% of |m q| + |n p|: k3 itself cancels) and faces under two pixels
+// (|k3| < 4 pixel areas; they own one or two pixels and gain nothing from moments) -- take
+// the reference's per-pixel formula in pass 1, evaluated in DOUBLE from the unrounded
+// inputs, and are skipped by pass 2.
 // ===========================================================================
 
 // face constants of the backward (unscaled coordinates); regular = moment form applies
 struct BwdFace {
-  float ax, ay, m, p, n, q, k3raw;
+  float ax, ay, bx, by, cx, cy;
+  float m, p, n, q, k3raw;
+  int v[3];        // mesh mode: vertex ids
   bool regular;
 };
-__device__ __forceinline__ BwdFace bwd_face(const float* img, long long fbase, float min_k3) {
-  const float2* ip = reinterpret_cast<const float2*>(img + fbase * 6);
-  const float2 A = __ldg(ip), Bv = __ldg(ip + 1), C = __ldg(ip + 2);
+__device__ __forceinline__ BwdFace bwd_face(const RasterBwdArgs& a, int b, int face, float min_k3) {
   BwdFace f;
-  f.ax = A.x; f.ay = A.y;
+  float2 A, Bv, C;
+  bool ok = true;
+  if (a.faces) {   // mesh mode: a.img is vertices_image (B, V, 2)
+    const int* fp = a.faces + (long long)face * 3;
+    f.v[0] = __ldg(fp); f.v[1] = __ldg(fp + 1); f.v[2] = __ldg(fp + 2);
+    ok = (unsigned)f.v[0] < (unsigned)a.V && (unsigned)f.v[1] < (unsigned)a.V &&
+         (unsigned)f.v[2] < (unsigned)a.V;
+    if (!ok) f.v[0] = f.v[1] = f.v[2] = 0;
+    const float2* vp = reinterpret_cast<const float2*>(a.img) + (long long)b * a.V;
+    A = __ldg(vp + f.v[0]); Bv = __ldg(vp + f.v[1]); C = __ldg(vp + f.v[2]);
+  } else {
+    f.v[0] = f.v[1] = f.v[2] = 0;
+    const float2* ip = reinterpret_cast<const float2*>(a.img + ((long long)b * a.F + face) * 6);
+    A = __ldg(ip); Bv = __ldg(ip + 1); C = __ldg(ip + 2);
+  }
+  f.ax = A.x; f.ay = A.y; f.bx = Bv.x; f.by = Bv.y; f.cx = C.x; f.cy = C.y;
   f.m = Bv.x - A.x; f.p = Bv.y - A.y; f.n = C.x - A.x; f.q = C.y - A.y;
   f.k3raw = f.m * f.q - f.n * f.p;
   // (false for NaN / Inf coordinates as well)
-  f.regular = fabsf(f.k3raw) >= 0.01f * (fabsf(f.m * f.q) + fabsf(f.n * f.p)) &&
+  f.regular = ok && fabsf(f.k3raw) >= 0.1f * (fabsf(f.m * f.q) + fabsf(f.n * f.p)) &&
               fabsf(f.k3raw) >= min_k3 && fabsf(f.k3raw) < 3e38f;
   return f;
+}
+// features / gradient slots of corner k of a face, either layout
+__device__ __forceinline__ const float* bwd_feat(const RasterBwdArgs& a, int b, int face,
+                                                 const BwdFace& f, int k) {
+  if (a.faces) return a.feat + ((a.feat_shared ? 0ll : (long long)b * a.V) + f.v[k]) * a.D;
+  return a.feat + (((long long)b * a.F + face) * 3 + k) * a.D;
+}
+__device__ __forceinline__ float* bwd_gfeat(const RasterBwdArgs& a, int b, int face,
+                                            const BwdFace& f, int k) {
+  if (a.faces) return a.grad_feat + ((a.feat_shared ? 0ll : (long long)b * a.V) + f.v[k]) * a.D;
+  return a.grad_feat + (((long long)b * a.F + face) * 3 + k) * a.D;
+}
+__device__ __forceinline__ float* bwd_gimg(const RasterBwdArgs& a, int b, int face,
+                                           const BwdFace& f, int k) {
+  if (a.faces) return a.grad_img + ((long long)b * a.V + f.v[k]) * 2;
+  return a.grad_img + (((long long)b * a.F + face) * 3 + k) * 2;
 }
 
 template <int N>
@@ -469,17 +537,20 @@ __global__ void __launch_bounds__(256, 6) raster_backward_kernel(const RasterBwd
 
   long long fbase = 0;
   float s = 0.f, t = 0.f;
+  double X = 0.0, Y = 0.0;
   bool regular = false;
   BwdFace fc;
   if (face >= 0) {
     fbase = (long long)b * a.F + face;
-    fc = bwd_face(a.img, fbase, 16.f / ((float)a.W * (float)a.H));
-    regular = fc.regular;
-    // pixel centre (what :302-303 reconstruct from the weights) minus vertex a, unscaled.
-    // The difference is taken in double: for faces much smaller than the image the float
-    // rounding of the centre itself (~6e-8) would be a visible fraction of (s, t).
-    s = (float)((double)(2 * ix + 1 - a.W) * a.inv_w - (double)fc.ax);
-    t = (float)((double)(a.H - 2 * iy - 1) * a.inv_h - (double)fc.ay);
+    fc = bwd_face(a, b, face, 16.f / ((float)a.W * (float)a.H));
+    regular = fc.regular && !a.weights;   // given weights (raw op): per pixel, as the reference
+    // pixel centre as the forward forms it (:85-86), back in unscaled coordinates; minus
+    // vertex a in double: for faces much smaller than the image the float rounding of the
+    // centre itself (~6e-8) would be a visible fraction of (s, t)
+    X = (double)pix_x(a.grid, ix) * a.inv_mult;
+    Y = (double)pix_y(a.grid, iy) * a.inv_mult;
+    s = (float)(X - (double)fc.ax);
+    t = (float)(Y - (double)fc.ay);
   }
   for (int d0 = 0; d0 < a.D; d0 += DC) {
     float mom[3 * DC];
@@ -498,7 +569,7 @@ __global__ void __launch_bounds__(256, 6) raster_backward_kernel(const RasterBwd
     }
     reduce_peers<3 * DC>(peers, mom, lane);
     if (leader && regular) {
-      float* gp = a.grad_feat + fbase * 3 * a.D;
+      float* gp = a.moments + fbase * 3 * a.D;
 #pragma unroll
       for (int dd = 0; dd < DC; dd++) {
         const int d = d0 + dd;
@@ -511,102 +582,151 @@ __global__ void __launch_bounds__(256, 6) raster_backward_kernel(const RasterBwd
     }
   }
 
-  // ---- thin faces: the reference's per-pixel arithmetic (:273-399), straight atomics
+  // ---- thin / tiny faces: the reference's per-pixel formula (:273-399) in double
   if (face >= 0 && !regular) {
-    const float2* ip = reinterpret_cast<const float2*>(a.img + fbase * 6);
-    const float2 A = __ldg(ip), Bv = __ldg(ip + 1), C = __ldg(ip + 2);
-    const float ax = A.x, ay = A.y, bx = Bv.x, by = Bv.y, cx = C.x, cy = C.y;
-    float w[3];
+    const double mult = (double)a.mult;
+    const double ax = fc.ax, ay = fc.ay, bx = fc.bx, by = fc.by, cx = fc.cx, cy = fc.cy;
+    // forward weights (:131-145) in multiplied coordinates, eps included.  Where the area
+    // term is eps-dominated or pure cancellation (collinear corners) the weights ARE the fp32
+    // rounding noise the reference's forward saved: those are recomputed bit-identically in
+    // float; everywhere else in double.
+    double w[3];
     if (a.weights) {
       w[0] = a.weights[pix * 3]; w[1] = a.weights[pix * 3 + 1]; w[2] = a.weights[pix * 3 + 2];
     } else {
-      const Grid g = make_grid(a.mult, a.W, a.H);
-      raster_weights(pix_x(g, ix), pix_y(g, iy), __fmul_rn(ax, a.mult), __fmul_rn(ay, a.mult),
-                     __fmul_rn(bx, a.mult), __fmul_rn(by, a.mult), __fmul_rn(cx, a.mult),
-                     __fmul_rn(cy, a.mult), a.eps_d, w[0], w[1], w[2]);
+      const double x0s = (double)pix_x(a.grid, ix), y0s = (double)pix_y(a.grid, iy);
+      const double aex = ax * mult - x0s, aey = ay * mult - y0s;
+      const double bex = bx * mult - x0s, bey = by * mult - y0s;
+      const double cex = cx * mult - x0s, cey = cy * mult - y0s;
+      w[0] = bex * cey - bey * cex; w[1] = cex * aey - cey * aex; w[2] = aex * bey - aey * bex;
+      double norm = w[0] + w[1] + w[2];
+      if (fabs(norm) > 1e-4 * (fabs(w[0]) + fabs(w[1]) + fabs(w[2])) && fabs(norm) > 4.0 * a.eps_d) {
+        norm += copysign(a.eps_d, norm);
+        w[0] /= norm; w[1] /= norm; w[2] /= norm;
+      } else {
+        float f0, f1, f2;
+        raster_weights(pix_x(a.grid, ix), pix_y(a.grid, iy), __fmul_rn(fc.ax, a.mult),
+                       __fmul_rn(fc.ay, a.mult), __fmul_rn(fc.bx, a.mult), __fmul_rn(fc.by, a.mult),
+                       __fmul_rn(fc.cx, a.mult), __fmul_rn(fc.cy, a.mult), a.eps_d, f0, f1, f2);
+        w[0] = f0; w[1] = f1; w[2] = f2;
+      }
     }
-    const float x0 = w[0] * ax + w[1] * bx + w[2] * cx;
-    const float y0 = w[0] * ay + w[1] * by + w[2] * cy;
-    const float m = bx - ax, pp = by - ay, n = cx - ax, q = cy - ay, ss = x0 - ax, tt = y0 - ay;
-    const float k1 = ss * q - n * tt;
-    const float k2 = m * tt - ss * pp;
-    float k3 = m * q - n * pp;
-    k3 = (float)((double)k3 + copysign(a.eps_d, (double)k3));
-    float dw1[6], dw2[6];
-    const float dw1dm = 0.f * k3 - q * k1, dw1dn = (-tt) * k3 - (-pp) * k1;
-    const float dw1dp = 0.f * k3 - (-n) * k1, dw1dq = ss * k3 - m * k1;
-    const float dw1ds = q * k3 - 0.f * k1, dw1dt = (-n) * k3 - 0.f * k1;
-    const float dw2dm = tt * k3 - q * k2, dw2dn = 0.f * k3 - (-pp) * k2;
-    const float dw2dp = (-ss) * k3 - (-n) * k2, dw2dq = 0.f * k3 - m * k2;
-    const float dw2ds = (-pp) * k3 - 0.f * k2, dw2dt = m * k3 - 0.f * k2;
+    const double x0 = w[0] * ax + w[1] * bx + w[2] * cx;   // :302-303
+    const double y0 = w[0] * ay + w[1] * by + w[2] * cy;
+    const double m = bx - ax, pp = by - ay, n = cx - ax, q = cy - ay, ss = x0 - ax, tt = y0 - ay;
+    const double k1 = ss * q - n * tt;
+    const double k2 = m * tt - ss * pp;
+    double k3 = m * q - n * pp;
+    k3 += copysign(a.eps_d, k3);
+    double dw1[6], dw2[6];
+    const double dw1dm = -q * k1, dw1dn = -tt * k3 + pp * k1;
+    const double dw1dp = n * k1, dw1dq = ss * k3 - m * k1;
+    const double dw1ds = q * k3, dw1dt = -n * k3;
+    const double dw2dm = tt * k3 - q * k2, dw2dn = pp * k2;
+    const double dw2dp = -ss * k3 + n * k2, dw2dq = -m * k2;
+    const double dw2ds = -pp * k3, dw2dt = m * k3;
     dw1[0] = -(dw1dm + dw1dn + dw1ds); dw1[1] = -(dw1dp + dw1dq + dw1dt);
     dw1[2] = dw1dm; dw1[3] = dw1dp; dw1[4] = dw1dn; dw1[5] = dw1dq;
     dw2[0] = -(dw2dm + dw2dn + dw2ds); dw2[1] = -(dw2dp + dw2dq + dw2dt);
     dw2[2] = dw2dm; dw2[3] = dw2dp; dw2[4] = dw2dn; dw2[5] = dw2dq;
-    const float* fp = a.feat + fbase * 3 * a.D;
-    float* gf = a.grad_feat + fbase * 3 * a.D;
-    float* gi = a.grad_img + fbase * 6;
+    const float *fp0 = bwd_feat(a, b, face, fc, 0), *fp1 = bwd_feat(a, b, face, fc, 1);
+    const float* fp2 = bwd_feat(a, b, face, fc, 2);
+    // face tensors: grad_face_features doubles as the moment accumulator, for these faces
+    // it receives the final gradient; mesh mode: the vertex gradients directly
+    float *gf0 = bwd_gfeat(a, b, face, fc, 0), *gf1 = bwd_gfeat(a, b, face, fc, 1);
+    float* gf2 = bwd_gfeat(a, b, face, fc, 2);
+    double e1 = 0.0, e2 = 0.0;                 // sum over d of g_d (c1 - c0), g_d (c2 - c0)
     for (int d = 0; d < a.D; d++) {
-      const float gd = a.grad[pix * a.D + d];
-      atomicAdd(gf + d, gd * w[0]);
-      atomicAdd(gf + a.D + d, gd * w[1]);
-      atomicAdd(gf + 2 * a.D + d, gd * w[2]);
-      const float c0 = __ldg(fp + d), c1 = __ldg(fp + a.D + d), c2 = __ldg(fp + 2 * a.D + d);
-      const float dldI = gd / (k3 * k3);
+      const double gd = (double)a.grad[pix * a.D + d];
+      atomicAdd(gf0 + d, (float)(gd * w[0]));
+      atomicAdd(gf1 + d, (float)(gd * w[1]));
+      atomicAdd(gf2 + d, (float)(gd * w[2]));
+      const double c0 = __ldg(fp0 + d), c1 = __ldg(fp1 + d), c2 = __ldg(fp2 + d);
+      e1 += gd * (c1 - c0);
+      e2 += gd * (c2 - c0);
+    }
+    const double r = 1.0 / (k3 * k3);
 #pragma unroll
-      for (int i = 0; i < 6; i++) atomicAdd(gi + i, dldI * ((c1 - c0) * dw1[i] + (c2 - c0) * dw2[i]));
+    for (int k = 0; k < 3; k++) {
+      float* gi = bwd_gimg(a, b, face, fc, k);
+      atomicAdd(gi, (float)((e1 * dw1[2 * k] + e2 * dw2[2 * k]) * r));
+      atomicAdd(gi + 1, (float)((e1 * dw1[2 * k + 1] + e2 * dw2[2 * k + 1]) * r));
     }
   }
 }
 
-// pass 2: moments -> gradients, one thread per (view, face)
+// pass 2: moments -> gradients, one thread per (view, face), in double
 __global__ void __launch_bounds__(256) raster_backward_finish_kernel(const RasterBwdArgs a) {
   pdl_prologue();
   const long long fbase = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (fbase >= (long long)a.B * a.F) return;
-  float* gf = a.grad_feat + fbase * 3 * a.D;
+  float* gf = a.moments + fbase * 3 * a.D;
   // untouched faces (most of them: back faces, hidden faces) hold zeros and keep them
   bool any = false;
   for (int i = 0; i < 3 * a.D; i++) any |= gf[i] != 0.f;
   if (!any) return;
-  const BwdFace fc = bwd_face(a.img, fbase, 16.f / ((float)a.W * (float)a.H));
+  const int b = (int)(fbase / a.F), face = (int)(fbase - (long long)b * a.F);
+  const BwdFace fc = bwd_face(a, b, face, 16.f / ((float)a.W * (float)a.H));
   if (!fc.regular) return;  // thin / tiny face: pass 1 wrote its gradients directly
-  const float m = fc.m, p = fc.p, n = fc.n, q = fc.q;
-  const float k3 = (float)((double)fc.k3raw + copysign(a.eps_d, (double)fc.k3raw));  // :321-322
-  const float inv_k3 = 1.0f / k3;
-  // the forward's weights carry eps only on the SCALED normalisation (negligible); the
-  // eps on the unscaled k3 belongs to the coordinate gradient alone (:321-322)
-  const float inv_k3raw = 1.0f / fc.k3raw;
-  const float* fp = a.feat + fbase * 3 * a.D;
-  float P0 = 0.f, Ps = 0.f, Pt = 0.f, Q0 = 0.f, Qs = 0.f, Qt = 0.f;
+  const double ax = fc.ax, ay = fc.ay;
+  const double m = (double)fc.bx - ax, p = (double)fc.by - ay;
+  const double n = (double)fc.cx - ax, q = (double)fc.cy - ay;
+  const double k3raw = m * q - n * p;
+  const double k3 = k3raw + copysign(a.eps_d, k3raw);       // :321-322
+  const double inv_k3raw = 1.0 / k3raw;
+  // eps of the forward's normalisation (:140-142), in multiplied coordinates
+  const double N = fabs(k3raw) * (double)a.mult * (double)a.mult;
+  const double rho = N / (N + a.eps_d);
+  const float *fp0 = bwd_feat(a, b, face, fc, 0), *fp1 = bwd_feat(a, b, face, fc, 1);
+  const float* fp2 = bwd_feat(a, b, face, fc, 2);
+  float *gf0 = bwd_gfeat(a, b, face, fc, 0), *gf1 = bwd_gfeat(a, b, face, fc, 1);
+  float* gf2 = bwd_gfeat(a, b, face, fc, 2);
+  double P0 = 0., Ps = 0., Pt = 0., Q0 = 0., Qs = 0., Qt = 0.;
   for (int d = 0; d < a.D; d++) {
-    const float M0 = gf[d], Ms = gf[a.D + d], Mt = gf[2 * a.D + d];
-    const float c0 = __ldg(fp + d), c1 = __ldg(fp + a.D + d), c2 = __ldg(fp + 2 * a.D + d);
-    const float e1 = c1 - c0, e2 = c2 - c0;
+    const double M0 = gf[d], Msl = gf[a.D + d], Mtl = gf[2 * a.D + d];
+    // moments of the reconstructed centre rho * X - a = rho (X - a) + (rho - 1) a
+    const double Ms = rho * Msl + (rho - 1.0) * ax * M0;
+    const double Mt = rho * Mtl + (rho - 1.0) * ay * M0;
+    const double c0 = __ldg(fp0 + d), c1 = __ldg(fp1 + d), c2 = __ldg(fp2 + d);
+    const double e1 = c1 - c0, e2 = c2 - c0;
     P0 += e1 * M0; Ps += e1 * Ms; Pt += e1 * Mt;
     Q0 += e2 * M0; Qs += e2 * Ms; Qt += e2 * Mt;
-    // grad_face_features: sum g w_k with w1 = k1 / k3, w2 = k2 / k3, w0 = 1 - w1 - w2
-    const float g1 = (Ms * q - n * Mt) * inv_k3raw;
-    const float g2 = (m * Mt - Ms * p) * inv_k3raw;
-    gf[d] = M0 - g1 - g2;
-    gf[a.D + d] = g1;
-    gf[2 * a.D + d] = g2;
+    // grad_face_features: sum g w_k with the forward's weights w1 = rho (sl q - n tl) / k3raw,
+    // w2 = rho (m tl - sl p) / k3raw, w0 = rho - w1 - w2
+    const double g1 = rho * (Msl * q - n * Mtl) * inv_k3raw;
+    const double g2 = rho * (m * Mtl - Msl * p) * inv_k3raw;
+    if (a.faces) {   // mesh mode: summed into the vertex gradients
+      atomicAdd(gf0 + d, (float)(rho * M0 - g1 - g2));
+      atomicAdd(gf1 + d, (float)g1);
+      atomicAdd(gf2 + d, (float)g2);
+    } else {         // in place: the moment slots become the gradient
+      gf0[d] = (float)(rho * M0 - g1 - g2);
+      gf1[d] = (float)g1;
+      gf2[d] = (float)g2;
+    }
   }
   // :324-374 with (1, s, t) replaced by their e1- / e2-weighted sums over the pixels
-  const float K1 = Ps * q - n * Pt, K2 = m * Qt - Qs * p;
-  const float dm = -q * K1 + (Qt * k3 - q * K2);
-  const float dn = (-Pt * k3 + p * K1) + p * K2;
-  const float dp = n * K1 + (-Qs * k3 + n * K2);
-  const float dq = (Ps * k3 - m * K1) - m * K2;
-  const float ds = q * k3 * P0 - p * k3 * Q0;
-  const float dt = -n * k3 * P0 + m * k3 * Q0;
-  const float r = inv_k3 * inv_k3;
-  float2* gi = reinterpret_cast<float2*>(a.grad_img + fbase * 6);
-  float2 ga = gi[0], gb = gi[1], gc = gi[2];
-  ga.x += -(dm + dn + ds) * r; ga.y += -(dp + dq + dt) * r;
-  gb.x += dm * r; gb.y += dp * r;
-  gc.x += dn * r; gc.y += dq * r;
-  gi[0] = ga; gi[1] = gb; gi[2] = gc;
+  const double K1 = Ps * q - n * Pt, K2 = m * Qt - Qs * p;
+  const double dm = -q * K1 + (Qt * k3 - q * K2);
+  const double dn = (-Pt * k3 + p * K1) + p * K2;
+  const double dp = n * K1 + (-Qs * k3 + n * K2);
+  const double dq = (Ps * k3 - m * K1) - m * K2;
+  const double ds = q * k3 * P0 - p * k3 * Q0;
+  const double dt = -n * k3 * P0 + m * k3 * Q0;
+  const double r = 1.0 / (k3 * k3);
+  const float2 da = make_float2((float)(-(dm + dn + ds) * r), (float)(-(dp + dq + dt) * r));
+  const float2 db = make_float2((float)(dm * r), (float)(dp * r));
+  const float2 dc = make_float2((float)(dn * r), (float)(dq * r));
+  if (a.faces) {
+    atomicAdd(reinterpret_cast<float2*>(bwd_gimg(a, b, face, fc, 0)), da);
+    atomicAdd(reinterpret_cast<float2*>(bwd_gimg(a, b, face, fc, 1)), db);
+    atomicAdd(reinterpret_cast<float2*>(bwd_gimg(a, b, face, fc, 2)), dc);
+  } else {
+    float2* gi = reinterpret_cast<float2*>(a.grad_img + fbase * 6);
+    float2 ga = gi[0], gb = gi[1], gc = gi[2];
+    ga.x += da.x; ga.y += da.y; gb.x += db.x; gb.y += db.y; gc.x += dc.x; gc.y += dc.y;
+    gi[0] = ga; gi[1] = gb; gi[2] = gc;
+  }
 }
 
 // Pass 1 (pixel-parallel moments).  The finish pass adds into grad_img with plain

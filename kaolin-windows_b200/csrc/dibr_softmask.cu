@@ -90,48 +90,51 @@ __device__ __forceinline__ double edge_inv(float x1, float y1, float x2, float y
 __device__ __forceinline__ float pick3(int v, float a, float b, float c) {
   return v == 0 ? a : (v == 1 ? b : c);
 }
+__device__ __forceinline__ int pick3i(int v, int a, int b, int c) {
+  return v == 0 ? a : (v == 1 ? b : c);
+}
 
 // dibr_soft_mask_cuda.cu:283-347: gradient of one (pixel, face) pair w.r.t. the face's
 // six UNscaled coordinates, added into g[6] (register array: static indices only).
 // Core: the gradient lands on vertex v1 (always) and v2 (edge case, else -1).
-__device__ __forceinline__ void soft_grad_core(float x0, float y0, const float (&X)[6], int edgeid,
+__device__ __forceinline__ void soft_grad_core(float x0f, float y0f, const float (&X)[6], int edgeid,
                                                float prob, float allprob, float dLdp,
                                                float sigmainv, float mult, double inv_e, int& v1,
                                                float& g1x, float& g1y, int& v2, float& g2x,
                                                float& g2y) {
-  const float dLdz = (float)(-1.0 * sigmainv * dLdp * (1.0 - allprob) /
-                             (1.0 - prob + DIBR_SOFT_EPS) * prob);
+  // Evaluated in double from the fp32 state (pixel centre, scaled coordinates, prob,
+  // soft_mask): what the reference's kernel computes when instantiated for double on that
+  // state.  Its float instantiation loses up to 1e-2 of a face's gradient to the float
+  // differences below; the pair count is small enough for FP64 not to show in the time.
+  (void)inv_e;
+  const double x0 = x0f, y0 = y0f, im = 1.0 / (double)mult;
+  const double dLdz = -1.0 * (double)sigmainv * (double)dLdp * (1.0 - (double)allprob) /
+                      (1.0 - (double)prob + DIBR_SOFT_EPS) * (double)prob;
   v2 = -1;
   g2x = 0.f;
   g2y = 0.f;
   if (edgeid >= 3) {
     v1 = edgeid - 3;
-    const float x1 = pick3(v1, X[0], X[2], X[4]), y1 = pick3(v1, X[1], X[3], X[5]);
-    const float dLdx1 = dLdz * 2 * (x1 - x0);
-    const float dLdy1 = dLdz * 2 * (y1 - y0);
-    g1x = dLdx1 / mult;
-    g1y = dLdy1 / mult;
+    const double x1 = pick3(v1, X[0], X[2], X[4]), y1 = pick3(v1, X[1], X[3], X[5]);
+    g1x = (float)(dLdz * 2.0 * (x1 - x0) * im);
+    g1y = (float)(dLdz * 2.0 * (y1 - y0) * im);
   } else {
     v1 = edgeid;
     v2 = (edgeid + 1) % 3;
-    const float x1 = pick3(v1, X[0], X[2], X[4]), y1 = pick3(v1, X[1], X[3], X[5]);
-    const float x2 = pick3(v2, X[0], X[2], X[4]), y2 = pick3(v2, X[1], X[3], X[5]);
-    const float A = y2 - y1, B = x1 - x2, C = x2 * y1 - x1 * y2;
-    const float up = A * x0 + B * y0 + C;
-    const float down = A * A + B * B;
-    const double dd = (double)down + DIBR_SOFT_EPS;   // the four "/ (down + EPS)" below
-    const float dissquare = (float)div_by((double)(up * up), dd, inv_e);
-    const float dzdA = (float)div_by((double)(2 * (x0 * up - dissquare * A)), dd, inv_e);
-    const float dzdB = (float)div_by((double)(2 * (y0 * up - dissquare * B)), dd, inv_e);
-    const float dzdC = (float)div_by((double)(2 * up), dd, inv_e);
-    const float dLdx1 = dLdz * (dzdB - y2 * dzdC);
-    const float dLdy1 = dLdz * (x2 * dzdC - dzdA);
-    const float dLdx2 = dLdz * (y1 * dzdC - dzdB);
-    const float dLdy2 = dLdz * (dzdA - x1 * dzdC);
-    g1x = dLdx1 / mult;
-    g1y = dLdy1 / mult;
-    g2x = dLdx2 / mult;
-    g2y = dLdy2 / mult;
+    const double x1 = pick3(v1, X[0], X[2], X[4]), y1 = pick3(v1, X[1], X[3], X[5]);
+    const double x2 = pick3(v2, X[0], X[2], X[4]), y2 = pick3(v2, X[1], X[3], X[5]);
+    const double A = y2 - y1, B = x1 - x2, C = x2 * y1 - x1 * y2;
+    const double up = A * x0 + B * y0 + C;
+    const double down = A * A + B * B;
+    const double id = 1.0 / (down + DIBR_SOFT_EPS);   // the four "/ (down + EPS)" (:318-330)
+    const double dissquare = up * up * id;
+    const double dzdA = 2.0 * (x0 * up - dissquare * A) * id;
+    const double dzdB = 2.0 * (y0 * up - dissquare * B) * id;
+    const double dzdC = 2.0 * up * id;
+    g1x = (float)(dLdz * (dzdB - y2 * dzdC) * im);
+    g1y = (float)(dLdz * (x2 * dzdC - dzdA) * im);
+    g2x = (float)(dLdz * (y1 * dzdC - dzdB) * im);
+    g2y = (float)(dLdz * (dzdA - x1 * dzdC) * im);
   }
 }
 
@@ -356,8 +359,15 @@ __device__ __forceinline__ void soft_block(const SoftArgs& a, const Plan& p,
       __syncthreads();
       for (int t = tid; t < nc * 6; t += kSoftThreads) {
         const float v = sm.acc[t / 6][t % 6];
-        if (v != 0.f)
+        if (v == 0.f) continue;
+        if (a.job.faces) {   // mesh mode: vertex gradients (B, V, 2)
+          int vid[3];
+          mesh_face(a.job, sm.face[t / 6], vid);
+          const int vv = pick3i((t % 6) >> 1, vid[0], vid[1], vid[2]);
+          atomicAdd(a.grad_img + ((long long)b * a.job.V + vv) * 2 + (t & 1), v);
+        } else {
           atomicAdd(a.grad_img + ((long long)b * a.job.view_stride + sm.face[t / 6]) * 6 + t % 6, v);
+        }
       }
     }
   }
@@ -407,9 +417,8 @@ softmask_kernel(const SoftArgs a, const Plan p) {
 constexpr int kPairWarps = DIBR_PAIR_WARPS;
 
 __device__ __forceinline__ void load_scaled_coords(const BinJob& j, int b, int f, float (&X)[6]) {
-  const long long gi = (long long)b * j.view_stride + f;
-  const float2* q = reinterpret_cast<const float2*>(j.img + gi * 6);
-  float2 v0 = __ldg(q), v1 = __ldg(q + 1), v2 = __ldg(q + 2);
+  float2 v0, v1, v2;
+  face_corners(j, b, f, v0, v1, v2);   // pair faces come out of the list: ids are valid
   if (!j.prescaled) {  // fl(v * mult), as torch does at dibr.py:32
     v0.x = __fmul_rn(v0.x, j.mult); v0.y = __fmul_rn(v0.y, j.mult);
     v1.x = __fmul_rn(v1.x, j.mult); v1.y = __fmul_rn(v1.y, j.mult);
@@ -668,10 +677,19 @@ softmask_pairs_grad_kernel(const SoftArgs a, const Plan p) {
                      v2, g2x, g2y);
       // one 8-byte vector reduction per touched vertex ((x, y) of a vertex are adjacent
       // and 8-byte aligned in grad_face_vertices_image) instead of up to four scalar ones
-      float2* gp = reinterpret_cast<float2*>(
-          a.grad_img + ((long long)k.b * a.job.view_stride + f[u]) * 6);
-      if (g1x != 0.f || g1y != 0.f) atomicAdd(gp + v1, make_float2(g1x, g1y));
-      if (v2 >= 0 && (g2x != 0.f || g2y != 0.f)) atomicAdd(gp + v2, make_float2(g2x, g2y));
+      if (a.job.faces) {   // mesh mode: straight into the vertex gradients (B, V, 2)
+        int vid[3];
+        mesh_face(a.job, f[u], vid);
+        float2* gv = reinterpret_cast<float2*>(a.grad_img) + (long long)k.b * a.job.V;
+        if (g1x != 0.f || g1y != 0.f) atomicAdd(gv + pick3i(v1, vid[0], vid[1], vid[2]), make_float2(g1x, g1y));
+        if (v2 >= 0 && (g2x != 0.f || g2y != 0.f))
+          atomicAdd(gv + pick3i(v2, vid[0], vid[1], vid[2]), make_float2(g2x, g2y));
+      } else {
+        float2* gp = reinterpret_cast<float2*>(
+            a.grad_img + ((long long)k.b * a.job.view_stride + f[u]) * 6);
+        if (g1x != 0.f || g1y != 0.f) atomicAdd(gp + v1, make_float2(g1x, g1y));
+        if (v2 >= 0 && (g2x != 0.f || g2y != 0.f)) atomicAdd(gp + v2, make_float2(g2x, g2y));
+      }
     }
   }
 }

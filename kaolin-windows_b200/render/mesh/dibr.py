@@ -12,7 +12,7 @@ from torch.autograd import Function
 from ... import _lib, _workspace
 from .rasterization import _prep, _ptr, _stream, rasterize
 
-__all__ = ["dibr_soft_mask", "dibr_rasterization"]
+__all__ = ["dibr_soft_mask", "dibr_rasterization", "dibr_rasterization_mesh"]
 
 
 def _margin(boxlen, multiplier):
@@ -213,5 +213,166 @@ def dibr_rasterization(height, width, face_vertices_z, face_vertices_image,
         for face_feature in face_features:
             _image_features.append(image_features[..., cur_idx:cur_idx + face_feature.shape[-1]])
             cur_idx += face_feature.shape[-1]
+        image_features = tuple(_image_features)
+    return image_features, soft_mask, face_idx
+
+
+# --------------------------------------------------------------------------- mesh level
+def _prep_faces(faces, num_vertices):
+    """(F, 3) int32 CUDA copy of the face list (cached on the tensor's storage address)."""
+    if faces.dim() != 2 or faces.shape[1] != 3:
+        raise RuntimeError("faces must be of shape (num_faces, 3)")
+    if not faces.is_cuda:
+        raise RuntimeError("faces must be a CUDA tensor (there is no CPU path)")
+    if faces.dtype == torch.int32 and faces.is_contiguous():
+        return faces
+    key = (faces.data_ptr(), faces._version, tuple(faces.shape), faces.dtype)
+    hit = _faces32_cache.get(key)
+    if hit is None:
+        if len(_faces32_cache) > 16:
+            _faces32_cache.clear()
+        hit = _faces32_cache[key] = (faces, faces.to(torch.int32).contiguous())
+    return hit[1]
+
+
+_faces32_cache = {}
+
+
+class DibrRasterizationMeshB200(Function):
+    """dibr_rasterization straight from the mesh: the kernels fetch the face corners through
+    `faces`, so prepare_vertices' (B, F, 3, .) face tensors (render/mesh/utils.py:128-175)
+    never exist, and the backward adds straight into vertex-level gradients."""
+
+    @staticmethod
+    def forward(ctx, height, width, vertices_camera, vertices_image, faces32, vertex_features,
+                valid_faces, sigmainv, boxlen, knum, multiplier, eps):
+        vcam = _prep(vertices_camera, "vertices_camera")
+        vimg = _prep(vertices_image, "vertices_image")
+        vfeat = _prep(vertex_features, "vertex_features")
+        B, V = vcam.shape[:2]
+        F = faces32.shape[0]
+        D = vfeat.shape[-1]
+        if (vcam.shape != (B, V, 3) or vimg.shape != (B, V, 2) or vfeat.dim() != 3
+                or vfeat.shape[1] != V or vfeat.shape[0] not in (1, B)):
+            raise RuntimeError("dibr_rasterization_mesh: expected vertices_camera (B,V,3), "
+                               "vertices_image (B,V,2), vertex_features (B or 1,V,D)")
+        shared = int(vfeat.shape[0] == 1)
+        dev = vcam.device
+        if any(t.device != dev for t in (vimg, vfeat, faces32)):
+            raise RuntimeError("dibr_rasterization_mesh: all tensors must be on the same GPU")
+        valid = None
+        if valid_faces is not None:
+            if valid_faces.shape != (B, F):
+                raise RuntimeError("valid_faces must be of shape (batch_size, num_faces)")
+            valid = valid_faces.to(device=dev, dtype=torch.bool).contiguous().view(torch.uint8)
+        H, W = int(height), int(width)
+        idx = torch.empty((B, H, W), dtype=torch.long, device=dev)
+        out = torch.empty((B, H, W, D), dtype=torch.float32, device=dev)
+        mask = torch.empty((B, H, W), dtype=torch.float32, device=dev)
+        margin = _margin(boxlen, multiplier)
+        lib = _lib.lib()
+        with torch.cuda.device(dev):
+            st = _stream(dev)
+
+            def call(ws, ws_bytes, cap_r, cap_s, cap_p, needed):
+                return lib.dibr_render_mesh_fwd(
+                    B, V, F, H, W, D, _ptr(vcam), _ptr(vimg), _ptr(faces32), _ptr(vfeat), shared,
+                    _ptr(valid), float(sigmainv), margin, int(knum), float(multiplier),
+                    float(eps), _ptr(idx), _ptr(out), _ptr(mask), ws, ws_bytes, cap_r, cap_s,
+                    cap_p, needed, st)
+
+            ws, cap_r, cap_s, cap_p = _workspace.run("mesh", dev, B, F, H, W, True, True, call,
+                                                     int(knum))
+        ctx.save_for_backward(idx, vimg, vfeat, faces32, mask, ws)
+        ctx.mark_non_differentiable(idx)
+        ctx.set_materialize_grads(False)
+        ctx.args = (float(sigmainv), margin, int(knum), float(multiplier), float(eps), cap_r, cap_s,
+                    cap_p, shared)
+        return out, mask, idx
+
+    @staticmethod
+    def backward(ctx, grad_features, grad_soft_mask, grad_face_idx):
+        idx, vimg, vfeat, faces32, mask, ws = ctx.saved_tensors
+        sigmainv, margin, knum, multiplier, eps, cap_r, cap_s, cap_p, shared = ctx.args
+        B, V = vimg.shape[:2]
+        F = faces32.shape[0]
+        H, W = idx.shape[1:]
+        D = vfeat.shape[-1]
+        if grad_features is None and grad_soft_mask is None:
+            return (None,) * 12
+        lib = _lib.lib()
+        grad_vimg = torch.empty_like(vimg)      # zero-filled by the call
+        grad_vfeat = torch.empty_like(vfeat)
+        scratch = torch.empty(int(lib.dibr_mesh_moment_bytes(B, F, D)), dtype=torch.uint8,
+                              device=vimg.device)
+        g = None if grad_features is None else _prep(grad_features, "grad_interpolated_features")
+        gm = None if grad_soft_mask is None else _prep(grad_soft_mask, "grad_soft_mask")
+        with torch.cuda.device(vimg.device):
+            rc = lib.dibr_render_mesh_bwd(
+                B, V, F, H, W, D, _ptr(g), _ptr(gm), _ptr(idx), _ptr(vimg), _ptr(faces32),
+                _ptr(vfeat), shared, _ptr(mask), sigmainv, margin, knum, multiplier, eps,
+                _ptr(grad_vimg), _ptr(grad_vfeat), _ptr(scratch), _ptr(ws), ws.numel(), cap_r,
+                cap_s, cap_p, _stream(vimg.device))
+        _lib.check(rc, "dibr_render_mesh_bwd")
+        return (None, None, None, grad_vimg, None, grad_vfeat, None, None, None, None, None, None)
+
+
+def dibr_rasterization_mesh(height, width, vertices_camera, vertices_image, faces,
+                            vertex_features, valid_faces=None, sigmainv=7000, boxlen=0.02,
+                            knum=30, multiplier=None, eps=None, cuda_graph=False):
+    r"""dibr_rasterization fed by the mesh itself (extension; not in the reference).
+
+    Equivalent -- bit for bit in the forward -- to
+
+        face_vertices_camera, face_vertices_image, face_normals = prepare_vertices(...)
+        face_features = index_vertices_by_faces(vertex_features, faces)
+        dibr_rasterization(height, width, face_vertices_camera[..., 2], face_vertices_image,
+                           face_features, face_normals[..., 2], ...)
+
+    (kaolin/render/mesh/utils.py:128-175, kaolin/render/mesh/dibr.py:119-209) without ever
+    building the (batch_size, num_faces, 3, .) tensors: the kernels read the corners through
+    ``faces`` and the backward accumulates vertex-level gradients.
+
+    Args:
+        height, width (int): size of the rendered images.
+        vertices_camera (torch.FloatTensor): (batch_size, num_vertices, 3), camera space (the
+            output of ``rotate_translate_points``); supplies depth and the normal test.
+        vertices_image (torch.FloatTensor): (batch_size, num_vertices, 2), NDC in [-1, 1].
+        faces (torch.IntTensor or LongTensor): (num_faces, 3).
+        vertex_features (torch.FloatTensor or list): (batch_size, num_vertices, feature_dim),
+            or (1, num_vertices, feature_dim) shared by all views (its gradient is then the
+            sum over the views).
+        valid_faces (torch.BoolTensor): (batch_size, num_faces); default: faces whose unit
+            normal has z >= 0 in camera space, as dibr_rasterization uses.
+        sigmainv, boxlen, knum, multiplier, eps: as dibr_rasterization.
+
+    Returns:
+        (torch.Tensor or tuple, torch.Tensor, torch.LongTensor): as dibr_rasterization.
+    """
+    _multiplier = 1000. if multiplier is None else multiplier
+    _eps = 1e-8 if eps is None else eps
+    _features = torch.cat(vertex_features, dim=-1) \
+        if isinstance(vertex_features, (list, tuple)) else vertex_features
+    if vertices_camera.dtype != torch.float32:
+        raise TypeError("dibr_rasterization_mesh takes float32 tensors")
+    faces32 = _prep_faces(faces, vertices_camera.shape[1])
+    res = None
+    if cuda_graph:
+        from .dibr_graph import graphed_dibr_rasterization_mesh
+        res = graphed_dibr_rasterization_mesh(
+            height, width, vertices_camera, vertices_image, faces32, _features, valid_faces,
+            (float(sigmainv), _margin(boxlen, _multiplier), int(knum), float(_multiplier),
+             float(_eps)))
+    if res is None:
+        res = DibrRasterizationMeshB200.apply(
+            height, width, vertices_camera, vertices_image, faces32, _features, valid_faces,
+            sigmainv, boxlen, knum, _multiplier, _eps)
+    image_features, soft_mask, face_idx = res
+    if isinstance(vertex_features, (list, tuple)):
+        _image_features = []
+        cur_idx = 0
+        for f in vertex_features:
+            _image_features.append(image_features[..., cur_idx:cur_idx + f.shape[-1]])
+            cur_idx += f.shape[-1]
         image_features = tuple(_image_features)
     return image_features, soft_mask, face_idx

@@ -11,7 +11,8 @@ Semantics that differ from the eager call (hence opt-in):
   * the returned tensors are views of the entry's static buffers: the next graphed call on
     the same inputs overwrites them (as with torch.cuda.make_graphed_callables);
   * backward must run before the next forward of the same entry (checked: raises);
-  * gradients come back as views of static buffers (autograd copies them into ``.grad``).
+  * gradients come back as copies of the static buffers (a view could be adopted as a leaf's
+    ``.grad`` and then be rewritten by the next replay).
 Correctness is kept as in the eager path: the list-size report of every replay is checked
 before the call returns; an overflow grows the workspace, re-issues the call eagerly and
 re-captures.  A first sighting of a problem runs eagerly; it is captured when seen again.
@@ -213,8 +214,10 @@ class DibrRasterizationGraphed(Function):
         g = None if grad_features is None else _prep(grad_features, "grad_interpolated_features")
         gm = None if grad_soft_mask is None else _prep(grad_soft_mask, "grad_soft_mask")
         entry.backward(g, gm)
-        return (None, None, None, entry.grad_img.view_as(entry.grad_img),
-                entry.grad_feat.view_as(entry.grad_feat))
+        # clones: AccumulateGrad may adopt a returned tensor as a leaf's .grad without copying
+        # it (it looks at the tensor's use count, not at storage sharing); a view of the
+        # entry's static buffer would then be rewritten by the next replay
+        return (None, None, None, entry.grad_img.clone(), entry.grad_feat.clone())
 
 
 def graphed_dibr_rasterization(H, W, face_vertices_z, face_vertices_image, face_features,
@@ -239,3 +242,130 @@ def graphed_dibr_rasterization(H, W, face_vertices_z, face_vertices_image, face_
         return None
     return DibrRasterizationGraphed.apply(entry, img.detach(), feat.detach(),
                                           face_vertices_image, face_features)
+
+
+# --------------------------------------------------------------------------- mesh level
+class _MeshEntry(_Entry):
+    """Graph entry of dibr_rasterization_mesh: same replay / overflow / re-capture logic, the
+    mesh-level C calls (dibr_render_mesh_fwd / _bwd) and vertex-level gradient buffers."""
+
+    def __init__(self, H, W, vcam, vimg, faces32, vfeat, valid, params):
+        self.H, self.W = H, W
+        self.vcamp, self.vimgp, self.facesp, self.vfeatp = (
+            t.data_ptr() for t in (vcam, vimg, faces32, vfeat))
+        self.validp = None if valid is None else valid.data_ptr()
+        self.params = params
+        self.B, self.V = vcam.shape[:2]
+        self.F = faces32.shape[0]
+        self.D = vfeat.shape[-1]
+        self.shared = int(vfeat.shape[0] == 1)
+        dev = self.dev = vcam.device
+        B, D = self.B, self.D
+        self.idx = torch.empty((B, H, W), dtype=torch.long, device=dev)
+        self.out = torch.empty((B, H, W, D), dtype=torch.float32, device=dev)
+        self.mask = torch.empty((B, H, W), dtype=torch.float32, device=dev)
+        self.grad_img = torch.empty(tuple(vimg.shape), dtype=torch.float32, device=dev)
+        self.grad_feat = torch.empty(tuple(vfeat.shape), dtype=torch.float32, device=dev)
+        self.scratch = torch.empty(int(_lib.lib().dibr_mesh_moment_bytes(B, self.F, D)),
+                                   dtype=torch.uint8, device=dev)
+        self.caps = _workspace.initial_caps(B, self.F, H, W, params[2])
+        if not (_workspace.USE_PAIRS and 0 < params[2] <= _workspace.PAIR_MAX_K):
+            self.caps[2] = 0
+        self.slot = torch.full((4,), -1, dtype=torch.int64).pin_memory()
+        self.ws = None
+        self.graph = None
+        self.bwd_graphs = collections.OrderedDict()
+        self.bwd_seen = set()
+        self.generation = 0
+        self._alloc_ws()
+
+    def _issue_forward(self):
+        sigmainv, margin, knum, multiplier, eps = self.params
+        cap_r, cap_s, cap_p = self.caps
+        rc = _lib.lib().dibr_render_mesh_fwd(
+            self.B, self.V, self.F, self.H, self.W, self.D, self.vcamp, self.vimgp, self.facesp,
+            self.vfeatp, self.shared, self.validp, sigmainv, margin, knum, multiplier, eps,
+            _ptr(self.idx), _ptr(self.out), _ptr(self.mask), self.ws.data_ptr(), self.ws_bytes,
+            cap_r, cap_s, cap_p, self.slot.data_ptr(), _stream(self.dev))
+        _lib.check(rc, "dibr_render_mesh_fwd")
+
+    def _issue_backward(self, g_out, g_mask):
+        sigmainv, margin, knum, multiplier, eps = self.params
+        cap_r, cap_s, cap_p = self.caps
+        rc = _lib.lib().dibr_render_mesh_bwd(
+            self.B, self.V, self.F, self.H, self.W, self.D, _ptr(g_out), _ptr(g_mask),
+            _ptr(self.idx), self.vimgp, self.facesp, self.vfeatp, self.shared, _ptr(self.mask),
+            sigmainv, margin, knum, multiplier, eps, _ptr(self.grad_img), _ptr(self.grad_feat),
+            _ptr(self.scratch), self.ws.data_ptr(), self.ws_bytes, cap_r, cap_s, cap_p,
+            _stream(self.dev))
+        _lib.check(rc, "dibr_render_mesh_bwd")
+
+
+class DibrRasterizationMeshGraphed(Function):
+    @staticmethod
+    def forward(ctx, entry, keep, vertices_image, vertex_features):
+        entry.forward(capture_ok=True)
+        ctx.entry = entry
+        ctx.keep = keep                    # inputs the backward reads: keep them alive
+        ctx.generation = entry.generation
+        ctx.set_materialize_grads(False)
+        idx = entry.idx.view_as(entry.idx)
+        ctx.mark_non_differentiable(idx)
+        return entry.out.view_as(entry.out), entry.mask.view_as(entry.mask), idx
+
+    @staticmethod
+    def backward(ctx, grad_features, grad_soft_mask, grad_face_idx):
+        entry = ctx.entry
+        if ctx.generation != entry.generation:
+            raise RuntimeError("dibr_rasterization_mesh(cuda_graph=True): backward of a call "
+                               "whose static buffers were overwritten by a later forward")
+        if grad_features is None and grad_soft_mask is None:
+            return None, None, None, None
+        g = None if grad_features is None else _prep(grad_features, "grad_interpolated_features")
+        gm = None if grad_soft_mask is None else _prep(grad_soft_mask, "grad_soft_mask")
+        entry.backward(g, gm)
+        # clones: autograd may adopt a returned tensor as .grad without copying it, and the
+        # next replay rewrites the entry's buffers (V-sized: the copy is cheap)
+        return None, None, entry.grad_img.clone(), entry.grad_feat.clone()
+
+
+def graphed_dibr_rasterization_mesh(H, W, vertices_camera, vertices_image, faces32,
+                                    vertex_features, valid_faces, params):
+    """(features, soft_mask, face_idx) from a graph entry, or None on the first sighting of
+    this problem (the caller then takes the eager path)."""
+    vcam = _prep(vertices_camera, "vertices_camera")
+    vimg = _prep(vertices_image, "vertices_image")
+    vfeat = _prep(vertex_features, "vertex_features")
+    B, V = vcam.shape[:2]
+    if (vcam.shape != (B, V, 3) or vimg.shape != (B, V, 2) or vfeat.dim() != 3
+            or vfeat.shape[1] != V or vfeat.shape[0] not in (1, B)):
+        raise RuntimeError("dibr_rasterization_mesh: expected vertices_camera (B,V,3), "
+                           "vertices_image (B,V,2), vertex_features (B or 1,V,D)")
+    F = faces32.shape[0]
+    valid = None
+    if valid_faces is not None:
+        if valid_faces.dtype != torch.bool or not valid_faces.is_contiguous():
+            return None                      # needs a converted copy: eager path
+        valid = valid_faces.view(torch.uint8)
+    if B == 0 or F == 0 or V == 0:
+        return None
+    key = ("mesh", vcam.device.index, int(H), int(W), tuple(vcam.shape), F, tuple(vfeat.shape),
+           params, vcam.data_ptr(), vimg.data_ptr(), faces32.data_ptr(), vfeat.data_ptr(),
+           None if valid is None else valid.data_ptr())
+    e = _entries.get(key)
+    if e is None:
+        n = _sightings.get(key, 0) + 1
+        _sightings[key] = n
+        _sightings.move_to_end(key)
+        while len(_sightings) > 64:
+            _sightings.popitem(last=False)
+        if n < 2:
+            return None
+        while len(_entries) >= MAX_ENTRIES:
+            _entries.popitem(last=False)
+        e = _entries[key] = _MeshEntry(int(H), int(W), vcam, vimg, faces32, vfeat, valid, params)
+        del _sightings[key]
+    else:
+        _entries.move_to_end(key)
+    return DibrRasterizationMeshGraphed.apply(e, (vcam, vimg, vfeat, faces32, valid),
+                                              vertices_image, vertex_features)

@@ -7,9 +7,19 @@ tests/python/kaolin/render/mesh/test_rasterization.py:189-288):
 
     e_f = |g_f - g64_f|_inf / max(|g64_f|_inf, 1e-3 * |g64|_inf)        must be <= 1e-4
 
-with g64 the reference's backward kernels run in fp64 on the state its fp32 forward saved
-(same discrete choices).  Where the reference's OWN fp32 result is further than that from
-its fp64 result (1 / k3^2 amplification on sub-pixel faces, 1 - soft_mask cancellation),
+with g64 the reference's backward kernels run in fp64 for the discrete choices of the fp32
+forward (selected faces, kept faces and nearest-feature types of the soft mask, and the fp32
+soft-mask state, which is the backward op's input), and with the barycentric weights a
+fp64 run of the reference's forward computes for those faces at those pixel centres
+(`exact_weights64`, restating rasterization_cuda.cu:85-86,131-145 in double) -- i.e. "the
+reference run in fp64"  without the pixels changing hands.  The fp32
+weights the fp32 forward saves are NOT used for g64: the backward only needs them to
+reconstruct the pixel centre (:302-303), and their rounding moves that centre by up to 1e-2
+of a sub-pixel face -- that is the reference's own fp32 noise (`ref32_*` columns), not the
+target.  The comparison against the fp64 backward on the saved fp32 weights (round 1's
+reference) is logged beside it as `vs_saved_w`.
+
+Where the reference's OWN fp32 result is further than 1e-4 from its fp64 result (1 / k3^2 amplification on sub-pixel faces, 1 - soft_mask cancellation),
 a face may instead be no further from fp64 than 1.5x the reference's fp32 error -- capped
 at 1e-3 -- and the number of faces that needed this clause is counted and logged.
 
@@ -79,3 +89,40 @@ def face_grad_check(name, mine, ref32, ref64):
         st["worst_ref32_e"] = float(r.reshape(-1)[w])
     st["ok"] = st["failed"] == 0
     return st
+
+
+def exact_weights64(height, width, face_vertices_image, face_idx, multiplier, eps,
+                    saved_weights=None):
+    """(B, H, W, 3) float64: the weights the reference's forward kernel instantiated for
+    double (rasterization_cuda.cu:85-86, 131-145) gives the face `face_idx` holds at each
+    pixel; zeros for background.  The pixel centre is the FLOAT product the kernel forms
+    (`multiplier / width * (2 * wididx + 1 - width)`, float x int), coordinates are
+    double(fp32 input) * multiplier as RasterizeCuda.forward scales them (:337).
+    Degenerate faces -- area term N = w0 + w1 + w2 below 1e-4 of |w0| + |w1| + |w2| (collinear
+    corners: N is pure cancellation) or below 4 eps (the weights are w_k / +-eps, the sign
+    decided by rounding) -- have no meaningful fp64 weights: there the fp32 forward's
+    `saved_weights` (B, H, W, 3) are kept, as the reference's backward would see them."""
+    dev = face_vertices_image.device
+    B, H, W = face_idx.shape
+    mult32 = torch.tensor(float(multiplier), dtype=torch.float32, device=dev)
+    xs = ((mult32 / width) * torch.arange(1 - width, width + 1, 2, device=dev,
+                                          dtype=torch.int32).float()).double()
+    ys = ((mult32 / height) * torch.arange(height - 1, -height - 1, -2, device=dev,
+                                           dtype=torch.int32).float()).double()
+    out = torch.zeros((B, H, W, 3), dtype=torch.float64, device=dev)
+    b, y, x = torch.nonzero(face_idx >= 0, as_tuple=True)
+    v = face_vertices_image.double()[b, face_idx[b, y, x]] * float(multiplier)   # (n, 3, 2)
+    x0, y0 = xs[x], ys[y]
+    ex = v[..., 0] - x0[:, None]
+    ey = v[..., 1] - y0[:, None]
+    w0 = ex[:, 1] * ey[:, 2] - ey[:, 1] * ex[:, 2]
+    w1 = ex[:, 2] * ey[:, 0] - ey[:, 2] * ex[:, 0]
+    w2 = ex[:, 0] * ey[:, 1] - ey[:, 0] * ex[:, 1]
+    norm = w0 + w1 + w2
+    healthy = (norm.abs() > 1e-4 * (w0.abs() + w1.abs() + w2.abs())) & (norm.abs() > 4.0 * float(eps))
+    norm = norm + torch.copysign(torch.full_like(norm, float(eps)), norm)
+    w = torch.stack([w0 / norm, w1 / norm, w2 / norm], dim=-1)
+    if saved_weights is not None:
+        w = torch.where(healthy[:, None], w, saved_weights.double()[b, y, x])
+    out[b, y, x] = w
+    return out

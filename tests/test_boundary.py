@@ -22,7 +22,7 @@ def _declared_symbols():
 
 def test_library_exports_every_declared_symbol():
     names = _declared_symbols()
-    assert len(names) == 32 and "dibr_deftet_fwd" in names and "dibr_render_fwd" in names and "dibr_face_setup_fwd" in names
+    assert len(names) == 35 and "dibr_deftet_fwd" in names and "dibr_render_fwd" in names and "dibr_face_setup_fwd" in names
     h = _lib.lib()
     for n in names:
         assert hasattr(h, n), n
@@ -44,7 +44,11 @@ def test_workspace_planning_without_gpu():
     h = _lib.lib()
     fixed = h.dibr_workspace_fixed_bytes(8, 70000, 512, 512)
     assert fixed > 0 and fixed % 256 == 0
-    assert h.dibr_workspace_bytes_for(8, 70000, 512, 512, 10, 20, 0, 0) == (fixed + 4 * 30 + 255) // 256 * 256
+    # raster entries are 48-byte face records (4-byte ids with DIBR_B200_RASTER_REC=0), soft
+    # entries 4-byte face ids; each list area is 256-byte aligned
+    rb = 4 if os.environ.get("DIBR_B200_RASTER_REC", "1")[:1] == "0" else 48
+    up = lambda v: (v + 255) // 256 * 256
+    assert h.dibr_workspace_bytes_for(8, 70000, 512, 512, 10, 20, 0, 0) == fixed + up(rb * 10) + up(4 * 20)
     assert h.dibr_workspace_fixed_bytes(1, 10, 0, 16) == _lib.DIBR_E_INVALID
     assert "invalid sizes" in _lib.last_error()
     # larger images use larger bins, never more than 1024 per view

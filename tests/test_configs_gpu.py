@@ -50,13 +50,24 @@ def full_compare(kal, ref, inp, H, W, grads=True, label=None, **kw):
         g1 = torch.rand(out.shape, device=DEV, generator=gen)
         g2 = torch.rand(mask.shape, device=DEV, generator=gen)
         ((out * g1).sum() + (mask * g2).sum()).backward()
-        # low-noise reference: the reference's backward kernels in fp64 on the state its
-        # fp32 forward saved, i.e. for the same discrete choices (selected faces, kept
-        # faces and nearest-feature types of the soft mask)
-        gi, gf = orc.dibr_rasterization_backward(orc.ctxs_to_double(ctxs), g1.double(),
-                                                 g2.double(), ops=ref)
-        # and in fp32: the same arithmetic as ours up to the order of the atomic adds
+        # low-noise reference: the reference's backward kernels in fp64 for the discrete
+        # choices of its fp32 forward (selected faces, kept faces / nearest-feature types and
+        # fp32 state of the soft mask) with the weights of a fp64 forward (parity_util)
+        ctx64 = orc.ctxs_to_double(ctxs)
+        gi_saved, gf_saved = orc.dibr_rasterization_backward(ctx64, g1.double(), g2.double(),
+                                                             ops=ref)
+        ctx64[0]["weights"] = pu.exact_weights64(
+            H, W, img, r_idx, 1000. if kw.get("multiplier") is None else kw["multiplier"],
+            1e-8 if kw.get("eps") is None else kw["eps"], saved_weights=ctxs[0]["weights"])
+        gi, gf = orc.dibr_rasterization_backward(ctx64, g1.double(), g2.double(), ops=ref)
+        # and in fp32: the reference's own output (atomics in arbitrary order)
         gi32, gf32 = orc.dibr_rasterization_backward(ctxs, g1, g2, ops=ref)
+        vs_saved = {"grad_face_vertices_image": pu.face_grad_check("", img_p.grad, gi32, gi_saved),
+                    "grad_face_features": pu.face_grad_check("", feat_p.grad, gf32, gf_saved)}
+        stats["vs_saved_w"] = {k: {q: v[q] for q in ("max_e", "ref32_max_e", "over_1e-4",
+                                                     "ref32_over_1e-4")}
+                               for k, v in vs_saved.items()}
+        del gi_saved, gf_saved, ctx64
         stats["grad_face_vertices_image"] = pu.face_grad_check("grad_face_vertices_image",
                                                                img_p.grad, gi32, gi)
         stats["grad_face_features"] = pu.face_grad_check("grad_face_features", feat_p.grad,

@@ -195,3 +195,18 @@ def test_closed_form_pair_count_matches_oracle_counter(H, W):
                                        "face_normals_z"))
     _, _, ctx = orc.rasterize_forward(H, W, z, img, feat, nz >= 0, return_pair_count=True)
     assert ctx["pair_count"] == wl.raster_pair_count(H, W, img, nz >= 0) > 0
+
+
+def test_exact_weights64_is_the_fp64_forward_of_the_oracle():
+    """tests/parity_util.exact_weights64 (the weights of the low-noise gradient reference)
+    against the weights the oracle's forward kernel saves when instantiated for double."""
+    import parity_util as pu
+    g = wl.fixture_geometry(batch_size=2)
+    z, img, feat, nz = (g[k] for k in ("face_vertices_z", "face_vertices_image", "face_uvs",
+                                       "face_normals_z"))
+    for mult, eps in ((1000, 1e-8), (1, 1e-8), (100, 1e-6)):
+        _, idx, ctx = orc.rasterize_forward(64, 48, z.double(), img.double(), feat.double(),
+                                            nz >= 0, multiplier=mult, eps=eps)
+        w = pu.exact_weights64(64, 48, img, idx, mult, eps)
+        assert (idx >= 0).sum() > 200
+        assert float((w - ctx["weights"]).abs().max()) <= 1e-12

@@ -211,11 +211,16 @@ def render_inputs(vertices, faces, n_views, vertex_features=None, seed=0, device
         v, rot, trans, vf = v[lo:hi], rot[lo:hi], trans[lo:hi], vf[lo:hi]
     v, f, rot, trans, proj, vf = (t.to(device) for t in (v, f, rot, trans, proj, vf))
     fvc, fvi, fn = prepare_vertices(v, f, proj, rot, trans)
+    vcam = rotate_translate_points(v, rot, trans)
     return dict(face_vertices_z=fvc[..., 2].contiguous(),
                 face_vertices_image=fvi.contiguous(),
                 face_features=index_vertices_by_faces(vf, f).contiguous(),
                 face_normals_z=fn[..., 2].contiguous(),
-                faces=f, vertices=v, vertex_features=vf)
+                faces=f, vertices=v, vertex_features=vf,
+                # mesh-level inputs (dibr_rasterization_mesh): the same camera pipeline
+                vertices_camera=vcam.contiguous(),
+                vertices_image=perspective_camera(vcam, proj).contiguous(),
+                camera=(rot, trans, proj))
 
 
 # BASELINE.json configs.  F is what the generator actually produces.
