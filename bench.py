@@ -4,26 +4,31 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
     torchrun --nproc-per-node N ... bench.py --gpus N ...
 
-A step = one pass of the hot path over one batch: dibr_rasterization forward, then the
-backward driven by fixed random cotangents on both outputs
-(loss = (features*G1).sum() + (soft_mask*G2).sum()).
-
 Workload at every N: BASELINE.json configs[1] per GPU (synthetic 69,938-face sphere with
 radial noise, 8 views, 512x512, D=3 vertex colours, sigmainv=7000 boxlen=0.02 knum=30).
-Weak scaling: rank r renders views [8r, 8r+8) of an 8N-view job over the shared mesh; for
-N > 1 the step adds the path's only exchange, a NCCL SUM all-reduce of the shared mesh's
-vertex-position/feature gradients (after the local face->vertex scatter-add).
+Weak scaling: rank r renders views [8r, 8r+8) of an 8N-view job over the shared mesh.
+
+A step = one pass of the hot path over one batch, from the MESH: camera transform +
+projection, dibr_rasterization forward (rasterize + soft mask), then the backward driven by
+fixed random cotangents on both outputs (loss = (features*G1).sum() + (soft_mask*G2).sum(),
+SURVEY 8(d)) down to the gradients of the shared mesh's vertices (V,3) and vertex features
+(V,D) -- `render.mesh.dibr_rasterization_vertices`, whose kernels read the face corners
+through `faces` (no (B,F,3,.) face tensors).  For N > 1 the step adds the path's only
+exchange: a SUM all-reduce of those vertex-level gradients.  The same work through the
+reference-shaped API on pre-built face tensors (`dibr_rasterization`, graph and eager) is
+reported beside it as `dropin`.
 
 Prints ONE JSON line (rank 0).  `value` = device-resident throughput (CUDA events, max
-over ranks, L2 flushed between steps outside the timed spans); `e2e` = the same metric
-through the public API from pinned HOST buffers (H2D of every step's inputs and D2H of its
-loss inside the timed region; inputs double buffered, the next step's batch prefetched on a
-copy stream while this step renders, L2 flush inside the span); `roofline` = dominant kernel vs the measured HBM peak;
-`cpu_baseline` = the CPU oracle (a port of the reference kernels; the reference has no CPU
-implementation of this path) on a bounded sample, rank 0, N = 1 only.
+over ranks, L2 flushed between steps outside the timed spans); `e2e` = the same step from
+pinned HOST buffers: H2D of the step's inputs (vertices, vertex features, cameras) and D2H
+of its results (both gradients and the loss) inside the timed region, L2 flush inside the
+span; `roofline` = dominant kernel vs the measured HBM peak, `roofline.secondary` = the
+rasterizer's FP32 work vs the measured FMA peak; `cpu_baseline` = the CPU oracle (a port of
+the reference kernels; the reference has no CPU implementation of this path) on a bounded
+sample, rank 0, N = 1 only.
 
---impl reference: times that CPU port with all host threads on the same config
-(each step = a 64-row band of one view; throughput in pixels/s is band-independent).
+--impl reference: times that CPU port with all host threads on the same config (each step
+= one full view of the 8).
 """
 import argparse
 import ctypes
@@ -217,12 +222,12 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--e2e-chunks", type=int, default=1,
-                    help="view chunks the e2e loop overlaps H2D copies and rendering with")
     ap.add_argument("--no-cuda-graph", action="store_true",
-                    help="eager launches instead of dibr_rasterization(cuda_graph=True)")
+                    help="eager launches instead of cuda_graph=True")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-ref-gpu", action="store_true")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the un-timed cfg 3 / cfg 5 sharding runs (`extra`)")
     args = ap.parse_args()
     # stdout carries the ONE JSON line: whatever libraries print (NCCL's version banner)
     # goes to stderr -- fd 1 points at stderr until the line is written
@@ -251,219 +256,212 @@ def main():
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries the JSON line only
         import datetime
         dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=120))
+    mesh_api = kal.render.mesh.dibr_rasterization_vertices
+    GRAPH = not args.no_cuda_graph
+    K, Wm = args.steps, args.warmup
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def barrier(coll=True):
+        if world > 1 and coll:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def make_mesh_job(cfg, n_views, lo, hi, shared=True):
+        """This rank's views [lo, hi) of an n_views job: the mesh (shared by all views, or one
+        mesh per view), its cameras, fixed cotangents."""
+        inp = wl.make_config(cfg, device=dev, views=n_views, view_slice=(lo, hi))
+        rot, trans, proj = inp["camera"]
+        verts, vfeat = inp["vertices"].contiguous(), inp["vertex_features"].contiguous()
+        if shared:
+            verts, vfeat = verts[:1].contiguous(), vfeat[:1].contiguous()
+        B = rot.shape[0]
+        gen = torch.Generator(device=dev).manual_seed(1234 + rank)
+        return dict(inp=inp, H=inp["H"], W=inp["W"], B=B, verts=verts, vfeat=vfeat,
+                    faces32=inp["faces"].int().contiguous(), rot=rot.contiguous(),
+                    trans=trans.contiguous(), proj=proj.contiguous(),
+                    g1=torch.rand((B, inp["H"], inp["W"], vfeat.shape[-1]), device=dev, generator=gen),
+                    g2=torch.rand((B, inp["H"], inp["W"]), device=dev, generator=gen))
+
+    def mesh_step(job, exchanger=None, graph=GRAPH, verts=None, vfeat=None):
+        """One step from the mesh; returns (loss terms' outputs, vertex grad, feature grad)."""
+        v = (job["verts"] if verts is None else verts).detach().requires_grad_(True)
+        f = (job["vfeat"] if vfeat is None else vfeat).detach().requires_grad_(True)
+        out, mask, idx = mesh_api(job["H"], job["W"], v, job["faces32"], f, job["proj"],
+                                  job["rot"], job["trans"], sigmainv=SIGMAINV, boxlen=BOXLEN,
+                                  knum=KNUM, cuda_graph=graph)
+        # d loss / d out = G1, d loss / d mask = G2: the backward of the loss without timing
+        # torch's multiply / reduce kernels, which are not part of the path
+        torch.autograd.backward((out, mask), (job["g1"], job["g2"]))
+        gv, gf = v.grad, f.grad
+        if exchanger is not None:
+            gv, gf = exchanger(gv, gf)       # the path's only exchange (N > 1)
+        return out, mask, gv, gf
+
+    def time_steps(fn, steps, warm, coll=True):
+        """ms per step: CUDA events per step, L2 flushed in between, max over ranks
+        (coll=False: this rank alone, no collective call)."""
+        for _ in range(warm):
+            fn()
+        barrier(coll)
+        evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+               for _ in range(steps)]
+        for e0, e1 in evs:
+            flush.zero_()
+            e0.record()
+            fn()
+            e1.record()
+        barrier(coll)
+        tot = torch.tensor([sum(e0.elapsed_time(e1) for e0, e1 in evs)], device=dev,
+                           dtype=torch.float64)
+        if world > 1 and coll:
+            dist.all_reduce(tot, op=dist.ReduceOp.MAX)
+        return float(tot.item()) / steps
 
     # ---- workload: this rank's 8 views of the 8N-view job over the shared mesh
     views_per_gpu = wl.CONFIGS[CFG]["views"]
     lo, hi = kal.parallel.shard_range(views_per_gpu * world, rank, world)
-    inp = wl.make_config(CFG, device=dev, views=views_per_gpu * world, view_slice=(lo, hi))
-    H, W = inp["H"], inp["W"]
+    job = make_mesh_job(CFG, views_per_gpu * world, lo, hi)
+    inp = job["inp"]
+    H, W, B = job["H"], job["W"], job["B"]
     z, img, feat, nz = (inp[k] for k in ("face_vertices_z", "face_vertices_image",
                                          "face_features", "face_normals_z"))
     faces = inp["faces"]
-    B, F, D = z.shape[0], z.shape[1], feat.shape[-1]
-    V = inp["vertices"].shape[1]
+    F, D = z.shape[1], feat.shape[-1]
+    V = job["verts"].shape[1]
     P = H * W
-    gen = torch.Generator(device=dev).manual_seed(1234 + rank)
-    g1 = torch.rand((B, H, W, D), device=dev, generator=gen)
-    g2 = torch.rand((B, H, W), device=dev, generator=gen)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
-
-    GRAPH = not args.no_cuda_graph
-    # (capture_collective=True was measured: 4 % faster at N=2, 45 % slower at N=8)
-    exchanger = kal.parallel.MeshGradExchange(inp["faces"], inp["vertices"].shape[1]) \
-        if GRAPH else None
-
-    def step(img_in, feat_in, z_in=z, nz_in=nz, exchange=True, with_loss=False, graph=GRAPH):
-        img_l = img_in.detach().requires_grad_(True)
-        feat_l = feat_in.detach().requires_grad_(True)
-        out, mask, idx = kal.render.mesh.dibr_rasterization(H, W, z_in, img_l, feat_l, nz_in,
-                                                            SIGMAINV, BOXLEN, KNUM,
-                                                            cuda_graph=graph)
-        if with_loss:
-            loss = (out * g1).sum() + (mask * g2).sum()
-            loss.backward()
-        else:
-            # d loss / d out = g1, d loss / d mask = g2: the same backward without timing
-            # torch's multiply/reduce kernels, which are not part of the path
-            loss = None
-            torch.autograd.backward((out, mask), (g1, g2))
-        if world > 1 and exchange:
-            # local face -> vertex scatter-add (one kernel per gradient into one flat
-            # (V, 2+D) buffer), then ONE all-reduce of the shared mesh's gradients
-            if exchanger is not None:
-                exchanger(img_l.grad, feat_l.grad)
-            else:
-                kal.parallel.exchange_mesh_grads(faces, V, img_l.grad, feat_l.grad)
-        return loss
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
-
-    for _ in range(args.warmup):
-        step(img, feat)
-    barrier()
+    g1, g2 = job["g1"], job["g2"]
+    exchanger = kal.parallel.VertexGradExchange() if world > 1 else None
 
     # ---- un-timed cross-check of the exchange (N > 1): the same gradients through our
-    # peer-memory all-reduce kernel and through scatter + NCCL all_reduce
+    # peer-memory all-reduce kernel and through one flat NCCL all_reduce
     exchange_check = None
     if world > 1:
-        img_l = img.detach().requires_grad_(True)
-        feat_l = feat.detach().requires_grad_(True)
-        out, mask, idx = kal.render.mesh.dibr_rasterization(H, W, z, img_l, feat_l, nz,
-                                                            SIGMAINV, BOXLEN, KNUM)
-        torch.autograd.backward((out, mask), (g1, g2))
-        ex = exchanger if exchanger is not None else kal.parallel.MeshGradExchange(faces, V)
-        mine = ex(img_l.grad, feat_l.grad).clone()
-        want = kal.parallel.exchange_mesh_grads(faces, V, img_l.grad, feat_l.grad)
+        _, _, gv, gf = mesh_step(job, None, graph=False)
+        mine = torch.cat([t.reshape(-1) for t in exchanger(gv, gf)]).clone()
+        want = torch.cat([gv.reshape(-1), gf.reshape(-1)]).clone()
+        dist.all_reduce(want, op=dist.ReduceOp.SUM)
         rel = (mine - want).abs().max() / want.abs().max().clamp_min(1e-30)
         bits = mine.contiguous().view(torch.int32).to(torch.int64)
-        wts = torch.arange(bits.numel(), device=dev, dtype=torch.int64).view_as(bits) % 65521 + 1
+        wts = torch.arange(bits.numel(), device=dev, dtype=torch.int64) % 65521 + 1
         digest = torch.stack([bits.sum(), (bits * wts).sum()])
         every = [torch.zeros_like(digest) for _ in range(world)]
         dist.all_gather(every, digest)
-        relmax = rel.clone()
-        dist.all_reduce(relmax, op=dist.ReduceOp.MAX)
-        exchange_check = {"mode": ex.mode, "max_rel_diff": float(relmax.item()),
+        dist.all_reduce(rel, op=dist.ReduceOp.MAX)
+        exchange_check = {"mode": exchanger.mode, "max_rel_diff": float(rel.item()),
                           "bit_identical_across_ranks": all(torch.equal(e, every[0]) for e in every),
-                          "against": "dibr_scatter_face_grads + NCCL all_reduce on the same gradients"}
-        del out, mask, idx, img_l, feat_l, mine, want
+                          "floats": int(mine.numel()),
+                          "against": "one flat NCCL all_reduce(SUM) of the same gradients"}
+        del mine, want, gv, gf
         barrier()
 
     # ---- timed: exactly K steps, one CUDA-event pair per step, L2 flushed in between
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
-           for _ in range(args.steps)]
-    barrier()
-    for e0, e1 in evs:
-        flush.zero_()
-        e0.record()
-        step(img, feat)
-        e1.record()
-    barrier()
-    step_ms = [e0.elapsed_time(e1) for e0, e1 in evs]
-    total_ms = torch.tensor([sum(step_ms)], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
-    ms_per_step = float(total_ms.item()) / args.steps
+    ms_per_step = time_steps(lambda: mesh_step(job, exchanger), K, Wm)
     value = world * B * P / (ms_per_step * 1e-3) / 1e6
 
-    # ---- e2e: public API from pinned host buffers, H2D of inputs + D2H of the loss per step
-    h_in = [t.detach().cpu().pin_memory() for t in (z, img, feat, nz)]
-    d_in = [torch.empty_like(t, device=dev) for t in h_in]
-    h2d = sum(t.numel() * t.element_size() for t in h_in)
+    # ---- e2e: the same step from pinned HOST buffers.  Per step, inside the timed region:
+    # ONE H2D copy of the step's inputs (vertices, vertex features, cameras, packed in one
+    # pinned buffer), the step, the loss, and D2H copies of both gradients and the loss into
+    # pinned host buffers.  The host reads step i's results while step i + 1 is in flight
+    # (two result slots); every step's copies and the final read are inside the region.
+    names = ("verts", "vfeat", "rot", "trans", "proj")
+    sizes = [job[k].numel() for k in names]
+    h_pack = torch.cat([job[k].detach().reshape(-1).cpu() for k in names]).pin_memory()
+    d_pack = torch.empty_like(h_pack, device=dev)
+    d_in, off = {}, 0
+    for k, n_k in zip(names, sizes):
+        d_in[k] = d_pack[off:off + n_k].view(job[k].shape)
+        off += n_k
+    e2e_job = dict(job, rot=d_in["rot"], trans=d_in["trans"], proj=d_in["proj"])
+    nv, nf = job["verts"].numel(), job["vfeat"].numel()
+    h_res = [torch.empty(nv + nf + 1, dtype=torch.float32).pin_memory() for _ in range(2)]
+    res_ev = [None, None]
+    h2d = h_pack.numel() * 4
+    d2h_grads = (nv + nf + 1) * 4
+    l2_small = flush[:160 << 20]              # 160 MiB > the 126 MB L2
 
-    # The user-level loop a host-fed renderer runs, with the prefetch any data loader does:
-    # device inputs are double buffered and step i+1's batch goes over on a copy stream while
-    # step i renders (the first step of the region has nothing to hide behind; with
-    # --e2e-chunks > 1 its batch goes over in view chunks and rendering starts on the first
-    # chunk -- off by default, one odd step only adds captures).  Every step's H2D and
-    # the D2H read of its loss are inside the timed region; the loss of step i is read before
-    # step i+1 is issued, so at most one batch is in flight ahead of the compute.
-    n_chunks = max(1, min(args.e2e_chunks, B))
-    bounds = [kal.parallel.shard_range(B, c, n_chunks) for c in range(n_chunks)]
-    copy_stream = torch.cuda.Stream(dev)
-    slots = [d_in, [torch.empty_like(t) for t in d_in]]
-    slot_free = [None, None]                   # event: the slot's last readers are done
+    def e2e_step(i, read_grads=True):
+        l2_small.zero_()                       # L2 flush, inside the timed span, not subtracted
+        d_pack.copy_(h_pack, non_blocking=True)
+        out, mask, gv, gf = mesh_step(e2e_job, exchanger, verts=d_in["verts"], vfeat=d_in["vfeat"])
+        with torch.no_grad():
+            loss = (out * g1).sum() + (mask * g2).sum()
+        h = h_res[i & 1]
+        if read_grads:
+            h[:nv].copy_(gv.reshape(-1), non_blocking=True)
+            h[nv:nv + nf].copy_(gf.reshape(-1), non_blocking=True)
+        h[nv + nf:].copy_(loss.reshape(1), non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        res_ev[i & 1] = ev
+        # the previous step's results are on the host by now: read them
+        prev = res_ev[(i + 1) & 1]
+        if prev is not None:
+            prev.synchronize()
+            return float(h_res[(i + 1) & 1][nv + nf])
+        return None
 
-    def e2e_copy(slot, chunked):
-        """H2D of one batch into `slot` on the copy stream; returns [(lo, hi, event)]."""
-        if slot_free[slot] is not None:
-            copy_stream.wait_event(slot_free[slot])
-        ready = []
-        with torch.cuda.stream(copy_stream):
-            for lo, hi in (bounds if chunked else [(0, B)]):
-                for d, h in zip(slots[slot], h_in):
-                    d[lo:hi].copy_(h[lo:hi], non_blocking=True)
-                ev = torch.cuda.Event()
-                ev.record(copy_stream)
-                ready.append((lo, hi, ev))
-        return ready
-
-    def e2e_compute(slot, ready):
-        main = torch.cuda.current_stream(dev)
-        d = slots[slot]
-        total = None
-        gi_out = gf_out = None
-        for lo, hi, ev in ready:
-            main.wait_event(ev)
-            img_l = d[1][lo:hi].requires_grad_(True)
-            feat_l = d[2][lo:hi].requires_grad_(True)
-            out, mask, idx = kal.render.mesh.dibr_rasterization(
-                H, W, d[0][lo:hi], img_l, feat_l, d[3][lo:hi], SIGMAINV, BOXLEN, KNUM,
-                cuda_graph=GRAPH)
-            # backward of the chunk's loss terms (d loss / d out = G1, d loss / d mask = G2)
-            torch.autograd.backward((out, mask), (g1[lo:hi], g2[lo:hi]))
-            with torch.no_grad():
-                loss = (out * g1[lo:hi]).sum() + (mask * g2[lo:hi]).sum()
-                total = loss if total is None else total + loss
-            if len(ready) == 1:
-                gi_out, gf_out = img_l.grad, feat_l.grad
-            else:
-                if gi_out is None:
-                    gi_out, gf_out = torch.empty_like(d[1]), torch.empty_like(d[2])
-                gi_out[lo:hi] = img_l.grad
-                gf_out[lo:hi] = feat_l.grad
+    def e2e_time(read_grads):
+        for i in range(6):
+            e2e_step(i, read_grads)
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(K):
+            e2e_step(i, read_grads)
+        res_ev[(K - 1) & 1].synchronize()
+        float(h_res[(K - 1) & 1][nv + nf])     # the last step's results
+        torch.cuda.synchronize(dev)
+        t = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
         if world > 1:
-            if exchanger is not None:
-                exchanger(gi_out, gf_out)
-            else:
-                kal.parallel.exchange_mesh_grads(faces, V, gi_out, gf_out)
-        done = torch.cuda.Event()
-        done.record(main)
-        slot_free[slot] = done
-        return total
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return max(float(t.item()), 1e-9) / K
 
-    e2e_trace = [] if os.environ.get("DIBR_BENCH_E2E_TRACE") else None
-
-    def e2e_run(n):
-        ready = e2e_copy(0, n_chunks > 1)
-        for i in range(n):
-            if e2e_trace is not None:
-                e2e_trace.append(time.perf_counter())
-            nxt = e2e_copy((i + 1) & 1, False) if i + 1 < n else None
-            flush.zero_()                      # L2 flush, inside the timed span, not subtracted
-            total = e2e_compute(i & 1, ready)
-            float(total.item())                # D2H read of this step's loss
-            ready = nxt
-
-    e2e_run(6)
-    e2e_run(6)
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(1):
-        e2e_run(args.steps)
-    torch.cuda.synchronize(dev)
-    e2e_t = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    e2e_s = e2e_time(True)
+    e2e_loss_s = e2e_time(False)
     sampler.stop_flag = True      # clocks sampled across both timed regions (device + e2e)
-    e2e_s = max(float(e2e_t.item()), 1e-9) / args.steps
-    if e2e_trace is not None and rank == 0:
-        ts = e2e_trace[-args.steps:]
-        print("e2e step starts (ms):", [round((t - ts[0]) * 1e3, 2) for t in ts], file=sys.stderr)
     e2e_val = world * B * P / e2e_s / 1e6
+
+    # ---- un-timed by the driver: the sharded configs BASELINE.json names for multi-GPU
+    extra = {}
+    if not args.no_extras:
+        # cfg 3: ONE 200k-face mesh, 64 views at 1024^2, views sharded 64/N per rank (strong
+        # scaling) + the vertex-gradient all-reduce
+        lo3, hi3 = kal.parallel.shard_range(64, rank, world)
+        j3 = make_mesh_job("cfg3_200k_64x1024", 64, lo3, hi3)
+        ms3 = time_steps(lambda: mesh_step(j3, exchanger), 5, 3)
+        extra["cfg3_strong"] = {"views_total": 64, "views_per_rank": hi3 - lo3, "H": 1024, "W": 1024,
+                                "faces": int(j3["faces32"].shape[0]), "ms_per_step": ms3,
+                                "Mpixels_per_s": 64 * 1024 * 1024 / (ms3 * 1e-3) / 1e6,
+                                "exchange_floats": int(j3["verts"].numel() + j3["vfeat"].numel())}
+        del j3
+        # cfg 5: 256 distinct 2k-face meshes at 128^2, 256/N per rank, no collective
+        lo5, hi5 = kal.parallel.shard_range(256, rank, world)
+        j5 = make_mesh_job("cfg5_256x2k_128", 256, lo5, hi5, shared=False)
+        ms5 = time_steps(lambda: mesh_step(j5, None), 5, 3)
+        extra["cfg5_dp"] = {"meshes_total": 256, "meshes_per_rank": hi5 - lo5, "H": 128, "W": 128,
+                            "faces": int(j5["faces32"].shape[0]), "ms_per_step": ms5,
+                            "Mpixels_per_s": 256 * 128 * 128 / (ms5 * 1e-3) / 1e6,
+                            "collective": "none"}
+        del j5
+        torch.cuda.empty_cache()
 
     if rank != 0:
         if world > 1:
-            if exchanger is not None:
-                exchanger.release()
+            exchanger.release()
             torch.cuda.synchronize(dev)
             _teardown(dist)
         return
 
-    # ---- per-kernel times (CUDA events on the launching stream, a separate pass of K steps)
+    # ---- rank 0 only from here (no collective): per-kernel times, CUDA events on the
+    # launching stream around every kernel; eager launches (a graph replay has no events)
     lib = _lib.lib()
     lib.dibr_profile_begin()
-    for _ in range(args.steps):
+    for _ in range(K):
         flush.zero_()
-        # rank 0 only: no collective in this pass; eager launches so that the library's
-        # per-kernel CUDA events bracket each kernel (a graph replay has none)
-        step(img, feat, exchange=False, graph=False)
-    cap = 64 * args.steps
+        mesh_step(job, None, graph=False)
+    cap = 64 * K
     ids = (ctypes.c_int * cap)()
     ms = (ctypes.c_float * cap)()
     n = lib.dibr_profile_end(ids, ms, cap)
@@ -471,16 +469,19 @@ def main():
     for i in range(n):
         per_kernel.setdefault(KERNELS[ids[i]], []).append(ms[i])
     kernel_ms = {k: sum(v) / len(v) for k, v in per_kernel.items()}
-    launches_per_step = n // max(args.steps, 1)
+    launches_per_step = n // max(K, 1) + 2          # + the two vertex-transform kernels
     top = max(kernel_ms, key=kernel_ms.get)
     peak, peak_kind = hbm_peak()
     achieved = algorithmic_bytes(top, B, F, P, D) / (kernel_ms[top] * 1e-3) / 1e9
+    total_bytes = total_algorithmic_bytes(B, F, P, D)
     roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak,
                 "peak_kind": peak_kind, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                 "kernel_ms": {k: round(v, 4) for k, v in kernel_ms.items()},
                 "kernel_share_of_step": kernel_ms[top] / ms_per_step,
-                "path_achieved_gbs": total_algorithmic_bytes(B, F, P, D) / (ms_per_step * 1e-3) / 1e9,
-                "path_frac": total_algorithmic_bytes(B, F, P, D) / (ms_per_step * 1e-3) / 1e9 / peak}
+                "path_achieved_gbs": total_bytes / (ms_per_step * 1e-3) / 1e9,
+                "path_frac": total_bytes / (ms_per_step * 1e-3) / 1e9 / peak,
+                "path_bytes": "SURVEY 8(d) face-tensor formula (56 B/px + 196 B/face-view); the "
+                              "mesh path's own compulsory traffic is smaller"}
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as fh:
             roofline["traffic"] = json.load(fh).get(top)
@@ -505,60 +506,62 @@ def main():
             "achieved": sec_ach, "peak": fma_tf, "peak_kind": fma_kind, "unit": "TFLOP/s",
             "frac": sec_ach / fma_tf}
 
-    # ---- the drop-in default: eager launches (no cuda_graph kwarg), same timing rules
-    ee = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
-          for _ in range(args.steps)]
-    for _ in range(3):
-        step(img, feat, exchange=False, graph=False)
-    torch.cuda.synchronize(dev)
-    for e0, e1 in ee:
-        flush.zero_()
-        e0.record()
-        step(img, feat, exchange=False, graph=False)
-        e1.record()
-    torch.cuda.synchronize(dev)
-    eager_ms = sum(e0.elapsed_time(e1) for e0, e1 in ee) / args.steps
+    # ---- the same step eagerly launched, and forward only
+    eager_ms = time_steps(lambda: mesh_step(job, None, graph=False), K, 3, coll=False)
 
-    # ---- forward only (SURVEY 8(d) asks for it beside fwd+bwd)
-    fe = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
-          for _ in range(args.steps)]
-    with torch.no_grad():
-        for e0, e1 in fe:
-            flush.zero_()
-            e0.record()
-            kal.render.mesh.dibr_rasterization(H, W, z, img, feat, nz, SIGMAINV, BOXLEN, KNUM,
-                                               cuda_graph=GRAPH)
-            e1.record()
-    torch.cuda.synchronize(dev)
-    fwd_ms = sum(e0.elapsed_time(e1) for e0, e1 in fe) / args.steps
+    def fwd_only():
+        with torch.no_grad():
+            mesh_api(H, W, job["verts"], job["faces32"], job["vfeat"], job["proj"], job["rot"],
+                     job["trans"], sigmainv=SIGMAINV, boxlen=BOXLEN, knum=KNUM, cuda_graph=GRAPH)
+    fwd_ms = time_steps(fwd_only, K, 3, coll=False)
+
+    # ---- drop-in API on pre-built face tensors (the reference's call, same pixels)
+    def dropin_step(graph):
+        img_l = img.detach().requires_grad_(True)
+        feat_l = feat.detach().requires_grad_(True)
+        out, mask, idx = kal.render.mesh.dibr_rasterization(H, W, z, img_l, feat_l, nz, SIGMAINV,
+                                                            BOXLEN, KNUM, cuda_graph=graph)
+        torch.autograd.backward((out, mask), (g1, g2))
+    dropin = {"api": "dibr_rasterization(face tensors): gradients w.r.t. face_vertices_image "
+                     "(B,F,3,2) and face_features (B,F,3,D)",
+              "graph_ms_per_step": time_steps(lambda: dropin_step(True), K, 3, coll=False),
+              "eager_ms_per_step": time_steps(lambda: dropin_step(False), K, 3, coll=False)}
+    dropin["Mpixels_per_s"] = B * P / (dropin["graph_ms_per_step"] * 1e-3) / 1e6
 
     line = {
         "metric": METRIC, "value": value, "unit": "Mpixels/s", "n_gpus": world,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step,
+        "steps": K, "warmup": Wm, "ms_per_step": ms_per_step,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": bench_config(B, F, H, W, D),
-        "notes": {"l2": "flushed between steps (256 MiB memset outside the per-step event spans)",
+        "notes": {"api": "render.mesh.dibr_rasterization_vertices: world-space vertices (V,3), "
+                         "faces (F,3), vertex features (V,D), cameras in; features / soft mask / "
+                         "face index out; gradients w.r.t. vertices and vertex features back",
+                  "l2": "flushed between steps (256 MiB memset outside the per-step event spans)",
                   "cotangents": "fixed random G1, G2 fed to autograd directly (= backward of "
                                 "(features*G1).sum() + (soft_mask*G2).sum()); e2e computes "
                                 "and reads back that loss",
-                  "launch": "CUDA graphs (dibr_rasterization(cuda_graph=True))" if GRAPH
+                  "launch": "CUDA graphs (cuda_graph=True): one launch each way" if GRAPH
                             else "eager",
                   "parallelism": "views sharded, %d per GPU" % B,
                   "exchange": ("none (N = 1)" if world == 1 else
                                {"peer": "own one-shot all-reduce kernel over NVLink peer memory",
-                                "nccl": "NCCL all-reduce"}.get(
-                                    getattr(exchanger, "mode", "nccl"), "NCCL all-reduce"))},
+                                "nccl": "NCCL all-reduce"}.get(exchanger.mode, "NCCL all-reduce")
+                               + " of the vertex-level gradients (V x (3 + D) floats)")},
         "clocks": sampler.summary(),
         "e2e": {"value": e2e_val, "unit": "Mpixels/s", "h2d_bytes_per_step": h2d,
-                "d2h_bytes_per_step": 8, "ms_per_step": e2e_s * 1e3,
-                "view_chunks": n_chunks,
-                "pipeline": "double-buffered inputs: step i+1's H2D on a copy stream during "
-                            "step i's render; loss of step i read back before step i+1 is issued"},
-        "gpu_launches": launches_per_step * args.steps,
+                "d2h_bytes_per_step": d2h_grads, "ms_per_step": e2e_s * 1e3,
+                "what": "per step: one H2D copy of vertices, vertex features and cameras from a "
+                        "pinned buffer; the step; the loss; D2H of both gradients and the loss "
+                        "into pinned buffers, read by the host while the next step runs",
+                "loss_only": {"ms_per_step": e2e_loss_s * 1e3, "d2h_bytes_per_step": 4,
+                              "value": world * B * P / e2e_loss_s / 1e6}},
+        "gpu_launches": launches_per_step * K,
         "fwd_only_ms_per_step": fwd_ms,
         "eager_ms_per_step": eager_ms,
+        "dropin": dropin,
         "exchange_check": exchange_check,
+        "extra": extra,
         "roofline": roofline,
     }
 
@@ -581,7 +584,7 @@ def main():
             rms = e0.elapsed_time(e1) / reps
             line["reference_kernels_on_this_gpu"] = {
                 "ms_per_step": rms, "value": B * P / (rms * 1e-3) / 1e6, "unit": "Mpixels/s",
-                "what": "reference's unmodified CUDA kernels + torch prep, same inputs"}
+                "what": "reference's unmodified CUDA kernels + torch prep on face tensors, same pixels"}
         except Exception as e:  # the strengthened checker is optional
             line["reference_kernels_on_this_gpu"] = {"unavailable": repr(e)[:200]}
 
@@ -606,8 +609,7 @@ def main():
                       % (B, P, reps, cores)}
     emit(line)
     if world > 1:
-        if exchanger is not None:
-            exchanger.release()
+        exchanger.release()
         torch.cuda.synchronize(dev)
         _teardown(dist)
 

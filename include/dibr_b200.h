@@ -310,6 +310,28 @@ DIBR_API int dibr_render_mesh_bwd(int batch, int num_vertices, int num_faces, in
                          int64_t ws_bytes, int64_t raster_capacity, int64_t soft_capacity,
                          int64_t pair_capacity, void* stream);
 
+/* The V-sized head of prepare_vertices (kaolin/render/mesh/utils.py:158-170):
+ * rotate_translate_points (camera/legacy.py:22-37: (v - trans) @ rot^T) or the 4x3
+ * camera_transform ([v, 1] @ T), then perspective_camera (legacy.py:120-139:
+ * (xy * proj.xy) / (z * proj.z)).  vertices (B, V, 3), or (V, 3) used by every view when
+ * vertices_shared != 0; camera_rot (B,3,3) + camera_trans (B,3), or camera_transform (B,4,3)
+ * (the others NULL); camera_proj 3 floats.  Outputs vertices_camera (B,V,3), vertices_image
+ * (B,V,2) -- the inputs of dibr_render_mesh_fwd.  The backward takes the cotangents of both
+ * outputs (either may be NULL) and WRITES grad_vertices of the shape of `vertices` (summed
+ * over the views when shared).  Camera parameters get no gradient here (they do through the
+ * torch form, render.mesh.prepare_vertices). */
+DIBR_API int dibr_vertex_transform_fwd(int batch, int num_vertices, int vertices_shared,
+                              const float* vertices, const float* camera_rot,
+                              const float* camera_trans, const float* camera_transform,
+                              const float* camera_proj, float* vertices_camera,
+                              float* vertices_image, void* stream);
+DIBR_API int dibr_vertex_transform_bwd(int batch, int num_vertices, int vertices_shared,
+                              const float* vertices_camera, const float* camera_rot,
+                              const float* camera_transform, const float* camera_proj,
+                              const float* grad_vertices_camera,
+                              const float* grad_vertices_image, float* grad_vertices,
+                              void* stream);
+
 /* ---------------------------------------------------------------------------------------
  * Double precision: the reference dispatches float and double (rasterization_cuda.cu:30-39,
  * dibr_soft_mask_cuda.cu:211,382) and tests both.  These are its four raw ops

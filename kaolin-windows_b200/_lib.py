@@ -46,6 +46,8 @@ SIGNATURES = {
     "dibr_render_mesh_bwd": (_i, [_i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp,
                                   _f, _f, _i, _f, _f, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64,
                                   _vp]),
+    "dibr_vertex_transform_fwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    "dibr_vertex_transform_bwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "dibr_index_vertices_by_faces": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "dibr_scatter_face_grads": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _i, _i, _vp]),
     "dibr_face_setup_fwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

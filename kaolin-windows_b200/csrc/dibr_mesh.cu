@@ -171,6 +171,85 @@ inline int grid_for(long long n, int threads) {
   return (int)(g < 1 ? 1 : (g > 148 * 64 ? 148 * 64 : g));
 }
 
+
+// ---- camera transform + perspective projection (prepare_vertices before the gathers:
+// kaolin/render/mesh/utils.py:158-170, camera/legacy.py:22-37,120-139), V-sized.
+//   mode 0: vcam = (v - trans_b) @ rot_b^T        (rotate_translate_points)
+//   mode 1: vcam = [v, 1] @ transform_b (4 x 3)   (camera_transform)
+//   vimg = (vcam.xy * proj.xy) / (vcam.z * proj.z)
+// One thread per (view, vertex); `shared`: one (V, 3) vertex array for all views.
+__global__ void __launch_bounds__(kThreads)
+vertex_transform_forward_kernel(const float* __restrict__ vertices, int shared,
+                                const float* __restrict__ mat, const float* __restrict__ trans,
+                                const float* __restrict__ proj, int mode,
+                                float* __restrict__ vcam, float* __restrict__ vimg, int V) {
+  const int b = blockIdx.y;
+  const int v = blockIdx.x * kThreads + threadIdx.x;
+  if (v >= V) return;
+  const float* p = vertices + ((shared ? 0ll : (long long)b * V) + v) * 3;
+  float x = __ldg(p), y = __ldg(p + 1), z = __ldg(p + 2);
+  float cx, cy, cz;
+  if (mode == 0) {
+    const float* R = mat + (long long)b * 9;
+    const float* t = trans + (long long)b * 3;
+    x -= __ldg(t); y -= __ldg(t + 1); z -= __ldg(t + 2);
+    cx = x * __ldg(R) + y * __ldg(R + 1) + z * __ldg(R + 2);
+    cy = x * __ldg(R + 3) + y * __ldg(R + 4) + z * __ldg(R + 5);
+    cz = x * __ldg(R + 6) + y * __ldg(R + 7) + z * __ldg(R + 8);
+  } else {
+    const float* T = mat + (long long)b * 12;
+    cx = x * __ldg(T) + y * __ldg(T + 3) + z * __ldg(T + 6) + __ldg(T + 9);
+    cy = x * __ldg(T + 1) + y * __ldg(T + 4) + z * __ldg(T + 7) + __ldg(T + 10);
+    cz = x * __ldg(T + 2) + y * __ldg(T + 5) + z * __ldg(T + 8) + __ldg(T + 11);
+  }
+  const long long o = (long long)b * V + v;
+  vcam[o * 3] = cx; vcam[o * 3 + 1] = cy; vcam[o * 3 + 2] = cz;
+  const float den = cz * __ldg(proj + 2);
+  vimg[o * 2] = cx * __ldg(proj) / den;
+  vimg[o * 2 + 1] = cy * __ldg(proj + 1) / den;
+}
+
+// Backward: cotangents of vcam (may be null) and vimg -> grad_vertices.  `shared`: one
+// thread per vertex sums its views (no atomics); else one thread per (view, vertex).
+__global__ void __launch_bounds__(kThreads)
+vertex_transform_backward_kernel(const float* __restrict__ vcam, const float* __restrict__ mat,
+                                 const float* __restrict__ proj, int mode,
+                                 const float* __restrict__ g_vcam,
+                                 const float* __restrict__ g_vimg, float* __restrict__ g_vertices,
+                                 int B, int V, int shared) {
+  const int v = blockIdx.x * kThreads + threadIdx.x;
+  if (v >= V) return;
+  const int b0 = shared ? 0 : blockIdx.y, b1 = shared ? B : blockIdx.y + 1;
+  const float p0 = __ldg(proj), p1 = __ldg(proj + 1), p2 = __ldg(proj + 2);
+  float gx = 0.f, gy = 0.f, gz = 0.f;
+  for (int b = b0; b < b1; b++) {
+    const long long o = (long long)b * V + v;
+    const float X = __ldg(vcam + o * 3), Y = __ldg(vcam + o * 3 + 1), Z = __ldg(vcam + o * 3 + 2);
+    float cx = 0.f, cy = 0.f, cz = 0.f;
+    if (g_vimg) {
+      const float gu = __ldg(g_vimg + o * 2), gv = __ldg(g_vimg + o * 2 + 1);
+      const float inv = 1.0f / (Z * p2);
+      cx = gu * p0 * inv;
+      cy = gv * p1 * inv;
+      cz = -(gu * X * p0 + gv * Y * p1) * inv / Z;
+    }
+    if (g_vcam) { cx += __ldg(g_vcam + o * 3); cy += __ldg(g_vcam + o * 3 + 1); cz += __ldg(g_vcam + o * 3 + 2); }
+    if (mode == 0) {
+      const float* R = mat + (long long)b * 9;
+      gx += cx * __ldg(R) + cy * __ldg(R + 3) + cz * __ldg(R + 6);
+      gy += cx * __ldg(R + 1) + cy * __ldg(R + 4) + cz * __ldg(R + 7);
+      gz += cx * __ldg(R + 2) + cy * __ldg(R + 5) + cz * __ldg(R + 8);
+    } else {
+      const float* T = mat + (long long)b * 12;
+      gx += cx * __ldg(T) + cy * __ldg(T + 1) + cz * __ldg(T + 2);
+      gy += cx * __ldg(T + 3) + cy * __ldg(T + 4) + cz * __ldg(T + 5);
+      gz += cx * __ldg(T + 6) + cy * __ldg(T + 7) + cz * __ldg(T + 8);
+    }
+  }
+  float* g = g_vertices + ((shared ? 0ll : (long long)b0 * V) + v) * 3;
+  g[0] = gx; g[1] = gy; g[2] = gz;
+}
+
 }  // namespace
 }  // namespace dibr
 
@@ -261,6 +340,57 @@ DIBR_API int dibr_face_setup_bwd(int batch, int num_vertices, int num_faces,
                                (cudaStream_t)stream>>>(
       vertices_camera, faces, grad_face_vertices_camera, grad_face_vertices_image,
       grad_face_normals, grad_vertices_camera, grad_vertices_image, num_vertices, num_faces);
+  MESH_CUDA(cudaGetLastError());
+  return DIBR_OK;
+}
+
+DIBR_API int dibr_vertex_transform_fwd(int batch, int num_vertices, int vertices_shared,
+                                       const float* vertices, const float* camera_rot,
+                                       const float* camera_trans, const float* camera_transform,
+                                       const float* camera_proj, float* vertices_camera,
+                                       float* vertices_image, void* stream) {
+  if (batch < 0 || num_vertices < 0) return fail(DIBR_E_INVALID, "invalid sizes");
+  if (batch > 65535) return fail(DIBR_E_INVALID, "batch %d > 65535 not supported", batch);
+  if (batch == 0 || num_vertices == 0) return DIBR_OK;
+  const bool rt = camera_rot && camera_trans && !camera_transform;
+  const bool tf = camera_transform && !camera_rot && !camera_trans;
+  if (!rt && !tf)
+    return fail(DIBR_E_INVALID, "camera_transform or camera_trans and camera_rot must be defined");
+  if (!vertices || !camera_proj || !vertices_camera || !vertices_image)
+    return fail(DIBR_E_INVALID, "null pointer");
+  vertex_transform_forward_kernel<<<dim3((num_vertices + kThreads - 1) / kThreads, batch),
+                                    kThreads, 0, (cudaStream_t)stream>>>(
+      vertices, vertices_shared, rt ? camera_rot : camera_transform, camera_trans, camera_proj,
+      rt ? 0 : 1, vertices_camera, vertices_image, num_vertices);
+  MESH_CUDA(cudaGetLastError());
+  return DIBR_OK;
+}
+
+DIBR_API int dibr_vertex_transform_bwd(int batch, int num_vertices, int vertices_shared,
+                                       const float* vertices_camera, const float* camera_rot,
+                                       const float* camera_transform, const float* camera_proj,
+                                       const float* grad_vertices_camera,
+                                       const float* grad_vertices_image, float* grad_vertices,
+                                       void* stream) {
+  if (batch < 0 || num_vertices < 0) return fail(DIBR_E_INVALID, "invalid sizes");
+  if (batch > 65535) return fail(DIBR_E_INVALID, "batch %d > 65535 not supported", batch);
+  if (num_vertices == 0) return DIBR_OK;
+  if ((camera_rot != nullptr) == (camera_transform != nullptr))
+    return fail(DIBR_E_INVALID, "exactly one of camera_rot / camera_transform");
+  if (!vertices_camera || !camera_proj || !grad_vertices)
+    return fail(DIBR_E_INVALID, "null pointer");
+  if (batch == 0) {
+    if (vertices_shared)
+      MESH_CUDA(cudaMemsetAsync(grad_vertices, 0, (size_t)num_vertices * 3 * sizeof(float),
+                                (cudaStream_t)stream));
+    return DIBR_OK;
+  }
+  vertex_transform_backward_kernel<<<dim3((num_vertices + kThreads - 1) / kThreads,
+                                          vertices_shared ? 1 : batch),
+                                     kThreads, 0, (cudaStream_t)stream>>>(
+      vertices_camera, camera_rot ? camera_rot : camera_transform, camera_proj,
+      camera_rot ? 0 : 1, grad_vertices_camera, grad_vertices_image, grad_vertices, batch,
+      num_vertices, vertices_shared);
   MESH_CUDA(cudaGetLastError());
   return DIBR_OK;
 }

@@ -68,8 +68,11 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
 #ifdef DIBR_TRACE_GATHER
   DIBR_TRACE_BEGIN();
 #endif
-  const int b = blockIdx.z;
-  const int bx0 = blockIdx.x << BLK_LOG2, by0 = blockIdx.y << BLK_LOG2;
+  // CTAs are taken longest face list first, as the rasterizer's (lpt_block): the few
+  // silhouette CTAs that walk a long list start early, the many that leave at once fill in
+  int b, bxi, byi;
+  if (!lpt_block(a.job, p, BLK_LOG2, blockIdx.x, b, bxi, byi)) return;
+  const int bx0 = bxi << BLK_LOG2, by0 = byi << BLK_LOG2;
   const int bx1 = min(bx0 + BLK, p.W) - 1, by1 = min(by0 + BLK, p.H) - 1;
   const Grid g = plan_grid(p, a.job.mult);
   const int K = min(a.K, 0xfffe);
@@ -363,7 +366,8 @@ static cudaError_t launch_gather(const SoftArgs& a, const Plan& p, cudaStream_t 
   const int smem = (int)sizeof(GatherSmem<G_LOG2>);
   cudaError_t e = smem_optin((const void*)softmask_gather_kernel<G_LOG2>, smem);
   if (e != cudaSuccess) return e;
-  dim3 grid((p.W + (1 << G_LOG2) - 1) >> G_LOG2, (p.H + (1 << G_LOG2) - 1) >> G_LOG2, p.B);
+  const int shift = p.bin_log2 - G_LOG2;
+  dim3 grid((unsigned)(((long long)p.B * p.NB) << (2 * shift)));
   launch_k(softmask_gather_kernel<G_LOG2>, grid, kGThreads, smem, st, a, p);
   return cudaGetLastError();
 }

@@ -226,3 +226,101 @@ class MeshGradExchange:
                 if len(self.seen) > 64:
                     self.seen.clear()
             return self._reduce()
+
+
+class VertexGradExchange:
+    """SUM all-reduce of the shared mesh's VERTEX-level gradients -- what the mesh-level
+    backward (render.mesh.dibr_rasterization_vertices / _mesh) produces directly, so there is
+    no face -> vertex scatter in front of the exchange any more.  The gradients (e.g.
+    vertices.grad (1, V, 3) and vertex_features.grad (1, V, D)) travel as ONE flat message:
+    copied into this rank's buffer of a symmetric allocation and reduced by our own one-shot
+    kernel over NVLink peer memory (csrc/dibr_peer.cu), NCCL where peer memory cannot be
+    mapped (or DIBR_B200_EXCHANGE=nccl).  Copies + kernel replay as one CUDA graph once the
+    same gradient addresses are seen again.  Returns views of a static result buffer."""
+
+    MAX_GRAPHS = 4
+
+    def __init__(self, group=None):
+        self.group = group
+        self.peer = None
+        self.flat = None
+        self.result = None
+        self.mode = "local"
+        self.n = 0
+        self.graphs = {}
+        self.seen = set()
+
+    def _setup(self, n, dev):
+        self.graphs.clear()
+        self.n = n
+        multi = (dist.is_available() and dist.is_initialized()
+                 and dist.get_world_size(self.group) > 1)
+        self.peer = _make_peer_buffers(n, dev, self.group) if multi else None
+        if self.peer is not None:
+            self.flat, self.result, self.mode = self.peer.buf, self.peer.out, "peer"
+        else:
+            self.flat = torch.empty(n, dtype=torch.float32, device=dev)
+            self.result, self.mode = self.flat, ("nccl" if multi else "local")
+
+    def _issue(self, grads):
+        import ctypes
+        from . import _lib
+        lib = _lib.lib()
+        pb = self.peer
+        dev = self.flat.device
+        st = ctypes.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        if pb is not None:      # peers may still be reading the previous exchange
+            _lib.check(lib.dibr_peer_signal(pb.rank, pb.world, pb.pads, 1, st), "dibr_peer_signal")
+        off = 0
+        for g in grads:
+            k = g.numel()
+            self.flat[off:off + k].copy_(g.reshape(-1))
+            off += k
+        if pb is not None:      # (the padding behind `off` was zeroed at set-up and stays so)
+            _lib.check(lib.dibr_peer_allreduce(
+                pb.rank, pb.world, pb.bufs, pb.pads, pb.n, ctypes.c_void_p(pb.out.data_ptr()),
+                ctypes.c_void_p(pb.sync.data_ptr()), st), "dibr_peer_allreduce")
+
+    def _reduce(self):
+        if self.mode == "nccl":
+            dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=self.group)
+
+    def release(self):
+        self.graphs.clear()
+        self.seen.clear()
+
+    def __call__(self, *grads):
+        grads = [g.contiguous() for g in grads]
+        if not grads[0].is_cuda:
+            raise RuntimeError("VertexGradExchange needs CUDA tensors (there is no CPU path)")
+        dev = grads[0].device
+        n = sum(g.numel() for g in grads)
+        if self.flat is None or self.n != n:
+            self._setup(n, dev)
+        key = tuple((g.data_ptr(), tuple(g.shape)) for g in grads)
+        with torch.cuda.device(dev):
+            graph = self.graphs.get(key)
+            if graph is not None:
+                graph.replay()
+            else:
+                self._issue(grads)
+                if key in self.seen and len(self.graphs) < self.MAX_GRAPHS:
+                    self._reduce()
+                    graph = torch.cuda.CUDAGraph()
+                    with torch.cuda.graph(graph, capture_error_mode="thread_local"):
+                        self._issue(grads)
+                    self.graphs[key] = graph
+                    return self._views(grads)
+                self.seen.add(key)
+                if len(self.seen) > 64:
+                    self.seen.clear()
+            self._reduce()
+        return self._views(grads)
+
+    def _views(self, grads):
+        out, off = [], 0
+        for g in grads:
+            k = g.numel()
+            out.append(self.result[off:off + k].view_as(g))
+            off += k
+        return out

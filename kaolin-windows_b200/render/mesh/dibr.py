@@ -12,7 +12,8 @@ from torch.autograd import Function
 from ... import _lib, _workspace
 from .rasterization import _prep, _ptr, _stream, rasterize
 
-__all__ = ["dibr_soft_mask", "dibr_rasterization", "dibr_rasterization_mesh"]
+__all__ = ["dibr_soft_mask", "dibr_rasterization", "dibr_rasterization_mesh",
+           "dibr_rasterization_vertices"]
 
 
 def _margin(boxlen, multiplier):
@@ -367,6 +368,116 @@ def dibr_rasterization_mesh(height, width, vertices_camera, vertices_image, face
         res = DibrRasterizationMeshB200.apply(
             height, width, vertices_camera, vertices_image, faces32, _features, valid_faces,
             sigmainv, boxlen, knum, _multiplier, _eps)
+    image_features, soft_mask, face_idx = res
+    if isinstance(vertex_features, (list, tuple)):
+        _image_features = []
+        cur_idx = 0
+        for f in vertex_features:
+            _image_features.append(image_features[..., cur_idx:cur_idx + f.shape[-1]])
+            cur_idx += f.shape[-1]
+        image_features = tuple(_image_features)
+    return image_features, soft_mask, face_idx
+
+
+class VertexTransformB200(Function):
+    """The V-sized head of prepare_vertices (render/mesh/utils.py:158-170) as one kernel each
+    way: camera transform + perspective projection.  Gradients reach the vertices only."""
+
+    @staticmethod
+    def forward(ctx, vertices, camera_proj, camera_rot, camera_trans, camera_transform, batch):
+        v = _prep(vertices, "vertices")
+        proj = _prep(camera_proj.reshape(-1), "camera_proj")
+        rot = None if camera_rot is None else _prep(camera_rot, "camera_rot")
+        trans = None if camera_trans is None else _prep(camera_trans.reshape(-1, 3), "camera_trans")
+        tf = None if camera_transform is None else _prep(camera_transform, "camera_transform")
+        if v.dim() != 3 or v.shape[-1] != 3 or v.shape[0] not in (1, batch) or proj.numel() != 3:
+            raise RuntimeError("expected vertices (batch_size or 1, num_vertices, 3) and "
+                               "camera_proj of 3 elements")
+        if (rot is not None and rot.shape != (batch, 3, 3)) or \
+                (trans is not None and trans.shape != (batch, 3)) or \
+                (tf is not None and tf.shape != (batch, 4, 3)):
+            raise RuntimeError("camera_rot (B,3,3), camera_trans (B,3) or camera_transform (B,4,3)")
+        V = v.shape[1]
+        shared = int(v.shape[0] == 1)
+        dev = v.device
+        vcam = torch.empty((batch, V, 3), dtype=torch.float32, device=dev)
+        vimg = torch.empty((batch, V, 2), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            _lib.check(_lib.lib().dibr_vertex_transform_fwd(
+                batch, V, shared, _ptr(v), _ptr(rot), _ptr(trans), _ptr(tf), _ptr(proj),
+                _ptr(vcam), _ptr(vimg), _stream(dev)), "dibr_vertex_transform_fwd")
+        ctx.save_for_backward(vcam, proj, rot if rot is not None else tf)
+        ctx.meta = (batch, V, shared, rot is not None, tuple(v.shape))
+        ctx.set_materialize_grads(False)
+        return vcam, vimg
+
+    @staticmethod
+    def backward(ctx, g_vcam, g_vimg):
+        vcam, proj, mat = ctx.saved_tensors
+        batch, V, shared, is_rot, vshape = ctx.meta
+        if g_vcam is None and g_vimg is None:
+            return (None,) * 6
+        g_vcam = None if g_vcam is None else _prep(g_vcam, "grad_vertices_camera")
+        g_vimg = None if g_vimg is None else _prep(g_vimg, "grad_vertices_image")
+        gv = torch.empty(vshape, dtype=torch.float32, device=vcam.device)
+        with torch.cuda.device(vcam.device):
+            _lib.check(_lib.lib().dibr_vertex_transform_bwd(
+                batch, V, shared, _ptr(vcam), _ptr(mat) if is_rot else None,
+                None if is_rot else _ptr(mat), _ptr(proj), _ptr(g_vcam), _ptr(g_vimg), _ptr(gv),
+                _stream(vcam.device)), "dibr_vertex_transform_bwd")
+        return gv, None, None, None, None, None
+
+
+def _camera_batch(camera_rot, camera_trans, camera_transform):
+    if camera_transform is None:
+        assert camera_trans is not None and camera_rot is not None, \
+            "camera_transform or camera_trans and camera_rot must be defined"
+        return camera_rot.shape[0]
+    assert camera_trans is None and camera_rot is None, \
+        "camera_trans and camera_rot must be None when camera_transform is defined"
+    return camera_transform.shape[0]
+
+
+def dibr_rasterization_vertices(height, width, vertices, faces, vertex_features, camera_proj,
+                                camera_rot=None, camera_trans=None, camera_transform=None,
+                                valid_faces=None, sigmainv=7000, boxlen=0.02, knum=30,
+                                multiplier=None, eps=None, cuda_graph=False):
+    r"""prepare_vertices + dibr_rasterization in one call (extension; not in the reference):
+    world-space vertices and cameras in, images out, vertex-level gradients back.
+
+    The camera arguments are prepare_vertices' (kaolin/render/mesh/utils.py:128-175); the
+    camera transform and the projection run as one V-sized kernel, the renderer reads the
+    corners through ``faces`` (see :func:`dibr_rasterization_mesh`).  ``vertices`` and
+    ``vertex_features`` may have a leading dimension of 1: one mesh seen by all cameras, whose
+    gradients are summed over the views.  Camera parameters receive no gradient (use
+    ``prepare_vertices`` + ``dibr_rasterization_mesh`` for that).  ``cuda_graph=True`` replays
+    the whole forward and the whole backward as one graph launch each.
+
+    Returns:
+        (torch.Tensor or tuple, torch.Tensor, torch.LongTensor): as dibr_rasterization.
+    """
+    batch = _camera_batch(camera_rot, camera_trans, camera_transform)
+    _multiplier = 1000. if multiplier is None else multiplier
+    _eps = 1e-8 if eps is None else eps
+    _features = torch.cat(vertex_features, dim=-1) \
+        if isinstance(vertex_features, (list, tuple)) else vertex_features
+    if vertices.dtype != torch.float32:
+        raise TypeError("dibr_rasterization_vertices takes float32 tensors")
+    faces32 = _prep_faces(faces, vertices.shape[1])
+    res = None
+    if cuda_graph:
+        from .dibr_graph import graphed_dibr_rasterization_vertices
+        res = graphed_dibr_rasterization_vertices(
+            height, width, vertices, faces32, _features, camera_proj, camera_rot, camera_trans,
+            camera_transform, valid_faces, batch,
+            (float(sigmainv), _margin(boxlen, _multiplier), int(knum), float(_multiplier),
+             float(_eps)))
+    if res is None:
+        vcam, vimg = VertexTransformB200.apply(vertices, camera_proj, camera_rot, camera_trans,
+                                               camera_transform, batch)
+        res = DibrRasterizationMeshB200.apply(
+            height, width, vcam, vimg, faces32, _features, valid_faces, sigmainv, boxlen, knum,
+            _multiplier, _eps)
     image_features, soft_mask, face_idx = res
     if isinstance(vertex_features, (list, tuple)):
         _image_features = []

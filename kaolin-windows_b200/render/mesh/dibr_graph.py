@@ -369,3 +369,113 @@ def graphed_dibr_rasterization_mesh(H, W, vertices_camera, vertices_image, faces
         _entries.move_to_end(key)
     return DibrRasterizationMeshGraphed.apply(e, (vcam, vimg, vfeat, faces32, valid),
                                               vertices_image, vertex_features)
+
+
+# ----------------------------------------------------------------- vertices + cameras in
+class _VertexEntry(_MeshEntry):
+    """Graph entry of dibr_rasterization_vertices: the camera transform / projection kernel
+    in front of the mesh-level forward, its backward behind the mesh-level backward -- one
+    graph launch each way for the whole step."""
+
+    def __init__(self, H, W, vertices, faces32, vfeat, proj, rot, trans, tf, valid, batch,
+                 params):
+        dev = vertices.device
+        V = vertices.shape[1]
+        self.vertsp, self.projp = vertices.data_ptr(), proj.data_ptr()
+        self.rotp = None if rot is None else rot.data_ptr()
+        self.transp = None if trans is None else trans.data_ptr()
+        self.tfp = None if tf is None else tf.data_ptr()
+        self.verts_shared = int(vertices.shape[0] == 1)
+        self.vcam = torch.empty((batch, V, 3), dtype=torch.float32, device=dev)
+        self.vimg = torch.empty((batch, V, 2), dtype=torch.float32, device=dev)
+        self.grad_verts = torch.empty(tuple(vertices.shape), dtype=torch.float32, device=dev)
+        super().__init__(H, W, self.vcam, self.vimg, faces32, vfeat, valid, params)
+
+    def _issue_forward(self):
+        _lib.check(_lib.lib().dibr_vertex_transform_fwd(
+            self.B, self.V, self.verts_shared, self.vertsp, self.rotp, self.transp, self.tfp,
+            self.projp, _ptr(self.vcam), _ptr(self.vimg), _stream(self.dev)),
+            "dibr_vertex_transform_fwd")
+        super()._issue_forward()
+
+    def _issue_backward(self, g_out, g_mask):
+        super()._issue_backward(g_out, g_mask)
+        _lib.check(_lib.lib().dibr_vertex_transform_bwd(
+            self.B, self.V, self.verts_shared, _ptr(self.vcam), self.rotp, self.tfp, self.projp,
+            None, _ptr(self.grad_img), _ptr(self.grad_verts), _stream(self.dev)),
+            "dibr_vertex_transform_bwd")
+
+
+class DibrRasterizationVerticesGraphed(Function):
+    @staticmethod
+    def forward(ctx, entry, keep, vertices, vertex_features):
+        entry.forward(capture_ok=True)
+        ctx.entry = entry
+        ctx.keep = keep
+        ctx.generation = entry.generation
+        ctx.set_materialize_grads(False)
+        idx = entry.idx.view_as(entry.idx)
+        ctx.mark_non_differentiable(idx)
+        return entry.out.view_as(entry.out), entry.mask.view_as(entry.mask), idx
+
+    @staticmethod
+    def backward(ctx, grad_features, grad_soft_mask, grad_face_idx):
+        entry = ctx.entry
+        if ctx.generation != entry.generation:
+            raise RuntimeError("dibr_rasterization_vertices(cuda_graph=True): backward of a call "
+                               "whose static buffers were overwritten by a later forward")
+        if grad_features is None and grad_soft_mask is None:
+            return None, None, None, None
+        g = None if grad_features is None else _prep(grad_features, "grad_interpolated_features")
+        gm = None if grad_soft_mask is None else _prep(grad_soft_mask, "grad_soft_mask")
+        entry.backward(g, gm)
+        return None, None, entry.grad_verts.clone(), entry.grad_feat.clone()
+
+
+def graphed_dibr_rasterization_vertices(H, W, vertices, faces32, vertex_features, camera_proj,
+                                        camera_rot, camera_trans, camera_transform, valid_faces,
+                                        batch, params):
+    """(features, soft_mask, face_idx) from a graph entry, or None on the first sighting."""
+    v = _prep(vertices, "vertices")
+    vfeat = _prep(vertex_features, "vertex_features")
+    proj = _prep(camera_proj.reshape(-1), "camera_proj")
+    rot = None if camera_rot is None else _prep(camera_rot, "camera_rot")
+    trans = None if camera_trans is None else _prep(camera_trans.reshape(-1, 3), "camera_trans")
+    tf = None if camera_transform is None else _prep(camera_transform, "camera_transform")
+    V = v.shape[1] if v.dim() == 3 else -1
+    if (v.dim() != 3 or v.shape[-1] != 3 or v.shape[0] not in (1, batch) or proj.numel() != 3
+            or vfeat.dim() != 3 or vfeat.shape[1] != V or vfeat.shape[0] not in (1, batch)
+            or (rot is not None and rot.shape != (batch, 3, 3))
+            or (trans is not None and trans.shape != (batch, 3))
+            or (tf is not None and tf.shape != (batch, 4, 3))):
+        raise RuntimeError("dibr_rasterization_vertices: inconsistent input shapes")
+    F = faces32.shape[0]
+    valid = None
+    if valid_faces is not None:
+        if valid_faces.dtype != torch.bool or not valid_faces.is_contiguous():
+            return None
+        valid = valid_faces.view(torch.uint8)
+    if batch == 0 or F == 0 or V == 0:
+        return None
+    cams = tuple(None if t is None else t.data_ptr() for t in (proj, rot, trans, tf))
+    key = ("vertices", v.device.index, int(H), int(W), batch, tuple(v.shape), F,
+           tuple(vfeat.shape), params, v.data_ptr(), faces32.data_ptr(), vfeat.data_ptr(), cams,
+           None if valid is None else valid.data_ptr())
+    e = _entries.get(key)
+    if e is None:
+        n = _sightings.get(key, 0) + 1
+        _sightings[key] = n
+        _sightings.move_to_end(key)
+        while len(_sightings) > 64:
+            _sightings.popitem(last=False)
+        if n < 2:
+            return None
+        while len(_entries) >= MAX_ENTRIES:
+            _entries.popitem(last=False)
+        e = _entries[key] = _VertexEntry(int(H), int(W), v, faces32, vfeat, proj, rot, trans, tf,
+                                         valid, batch, params)
+        del _sightings[key]
+    else:
+        _entries.move_to_end(key)
+    return DibrRasterizationVerticesGraphed.apply(e, (v, vfeat, faces32, proj, rot, trans, tf,
+                                                      valid), vertices, vertex_features)

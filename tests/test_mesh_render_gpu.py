@@ -189,3 +189,87 @@ def test_graph_replay_matches_eager(kal):
             assert torch.equal(x, y)
         for x, y in zip(got[3:], want[3:]):
             assert float((x - y).abs().max()) <= 1e-5 * float(y.abs().max())
+
+
+# ------------------------------------------------- vertices + cameras in (one call)
+def camera_inputs(cfg="cfg5_256x2k_128", views=8, shared=False):
+    inp = wl.make_config(cfg, device=DEV, views=views)
+    rot, trans, proj = inp["camera"]
+    verts = inp["vertices"].contiguous()
+    vfeat = inp["vertex_features"].contiguous()
+    if shared:
+        verts, vfeat = verts[:1].contiguous(), vfeat[:1].contiguous()
+    return inp, verts, vfeat, rot.contiguous(), trans.contiguous(), proj.contiguous()
+
+
+@pytest.mark.parametrize("shared", [False, True])
+@pytest.mark.parametrize("mode", ["rot_trans", "transform"])
+def test_vertex_transform_matches_torch(kal, shared, mode):
+    """camera transform + projection kernel against the torch restatement of
+    rotate_translate_points / perspective_camera (camera/legacy.py:22-37,120-139), forward
+    and gradient."""
+    from kaolin_windows_b200.render.mesh.dibr import VertexTransformB200
+    _, verts, _, rot, trans, proj = camera_inputs(shared=shared)
+    B = rot.shape[0]
+    tf = None
+    if mode == "transform":
+        tf = torch.cat([rot.permute(0, 2, 1), (-trans.unsqueeze(1) @ rot.permute(0, 2, 1))], dim=1)
+        tf = tf.contiguous()
+    v1 = verts.clone().requires_grad_(True)
+    if tf is None:
+        vcam, vimg = VertexTransformB200.apply(v1, proj, rot, trans, None, B)
+    else:
+        vcam, vimg = VertexTransformB200.apply(v1, proj, None, None, tf, B)
+    v2 = verts.clone().double().requires_grad_(True)
+    ve = v2.expand(B, -1, -1)
+    if tf is None:
+        rcam = wl.rotate_translate_points(ve, rot.double(), trans.double())
+    else:
+        rcam = torch.nn.functional.pad(ve, (0, 1), value=1.) @ tf.double()
+    rimg = wl.perspective_camera(rcam, proj.double())
+    assert torch.allclose(vcam.double(), rcam, rtol=1e-5, atol=1e-5)
+    assert torch.allclose(vimg.double(), rimg, rtol=1e-5, atol=1e-5)
+    gc, gi = torch.rand_like(vcam), torch.rand_like(vimg)
+    torch.autograd.backward((vcam, vimg), (gc, gi))
+    torch.autograd.backward((rcam, rimg), (gc.double(), gi.double()))
+    assert v1.grad.shape == verts.shape
+    assert float((v1.grad.double() - v2.grad).abs().max()) <= 1e-5 * float(v2.grad.abs().max())
+
+
+@pytest.mark.parametrize("shared", [False, True])
+def test_vertices_call_equals_mesh_call(kal, shared):
+    """dibr_rasterization_vertices == VertexTransform + dibr_rasterization_mesh (bit for bit),
+    eager and replayed from CUDA graphs; gradients reach vertices and vertex features."""
+    from kaolin_windows_b200.render.mesh.dibr import VertexTransformB200
+    inp, verts, vfeat, rot, trans, proj = camera_inputs(shared=shared)
+    faces = inp["faces"].int()
+    B = rot.shape[0]
+    g1 = torch.rand((B, 128, 128, 3), device=DEV)
+    g2 = torch.rand((B, 128, 128), device=DEV)
+    v1 = verts.clone().requires_grad_(True)
+    f1 = vfeat.clone().requires_grad_(True)
+    vcam, vimg = VertexTransformB200.apply(v1, proj, rot, trans, None, B)
+    o_m, m_m, i_m = kal.render.mesh.dibr_rasterization_mesh(128, 128, vcam, vimg, faces, f1)
+    torch.autograd.backward((o_m, m_m), (g1, g2))
+    # the torch camera chain lands within rounding of the kernel's: same image up to a few
+    # boundary pixels
+    t_cam = wl.rotate_translate_points(verts.expand(B, -1, -1), rot, trans)
+    o_t, m_t, i_t = kal.render.mesh.dibr_rasterization_mesh(
+        128, 128, t_cam.contiguous(), wl.perspective_camera(t_cam, proj).contiguous(), faces,
+        vfeat.expand(B, -1, -1).contiguous())
+    assert float((i_t != i_m).float().mean()) < 1e-4
+    for graph in (False, True, True, True):
+        v2 = verts.clone().requires_grad_(True) if not graph else v_static
+        f2 = vfeat.clone().requires_grad_(True) if not graph else f_static
+        if graph:
+            v2.grad = f2.grad = None
+        o, m, i = kal.render.mesh.dibr_rasterization_vertices(
+            128, 128, v2, faces, f2, proj, rot, trans, cuda_graph=graph)
+        torch.autograd.backward((o, m), (g1, g2))
+        assert torch.equal(i, i_m) and torch.equal(o, o_m) and torch.equal(m, m_m)
+        for a, b in ((v2.grad, v1.grad), (f2.grad, f1.grad)):
+            assert a.shape == b.shape
+            assert float((a - b).abs().max()) <= 1e-5 * float(b.abs().max())
+        if not graph:
+            v_static = verts.clone().requires_grad_(True)
+            f_static = vfeat.clone().requires_grad_(True)
