@@ -133,10 +133,10 @@ DIBR_API int dibr_rasterize_fwd(int batch, int num_faces, int height, int width,
  * rasterization_cuda.cu:238-402).  face_vertices_image is UNscaled (B, F, 3, 2).
  * output_weights may be NULL: the weights are then recomputed bit-identically from
  * (face_vertices_image * multiplier, pixel centre, eps) as the forward did.
- * grad_face_vertices_image (B,F,3,2) is ACCUMULATED into; grad_face_features (B,F,3,D)
- * MUST be zero-filled by the caller (at::zeros_like at rasterization.cpp:156-157): it
- * doubles as the per-face moment accumulator of the two-pass backward and is rewritten
- * in place.
+ * Both gradients are ACCUMULATED into (the caller zero-fills them, as at::zeros_like at
+ * rasterization.cpp:156-157 does).  With output_weights the per-pixel formula of the
+ * reference is evaluated (in double) on exactly those weights; without, the pixel-centre
+ * form (DESIGN.md "Backward").
  * face_vertices_z receives no gradient (rasterization.py:387-388).
  */
 DIBR_API int dibr_rasterize_bwd(int batch, int num_faces, int height, int width, int feat_dim,
@@ -286,8 +286,6 @@ DIBR_API int dibr_face_setup_bwd(int batch, int num_vertices, int num_faces,
  * grad_vertex_features (B or 1, V, D) -- with features_shared the views are summed, which
  * makes it the vertex-level message of the multi-GPU all-reduce; vertices_camera receives
  * no gradient (as face_vertices_z / face_normals_z in the reference, rasterization.py:387-388).
- * `moment_scratch`: dibr_mesh_moment_bytes(B, F, D) bytes of device memory (contents
- * irrelevant; the per-face moment accumulators of the two-pass backward).
  * ------------------------------------------------------------------------------------- */
 DIBR_API int dibr_render_mesh_fwd(int batch, int num_vertices, int num_faces, int height,
                          int width, int feat_dim, const float* vertices_camera,
@@ -298,7 +296,6 @@ DIBR_API int dibr_render_mesh_fwd(int batch, int num_vertices, int num_faces, in
                          float* interpolated_features, float* soft_mask, void* ws,
                          int64_t ws_bytes, int64_t raster_capacity, int64_t soft_capacity,
                          int64_t pair_capacity, int64_t* needed_host, void* stream);
-DIBR_API int64_t dibr_mesh_moment_bytes(int batch, int num_faces, int feat_dim);
 DIBR_API int dibr_render_mesh_bwd(int batch, int num_vertices, int num_faces, int height,
                          int width, int feat_dim, const float* grad_interpolated_features,
                          const float* grad_soft_mask, const int64_t* selected_face_idx,
@@ -306,9 +303,9 @@ DIBR_API int dibr_render_mesh_bwd(int batch, int num_vertices, int num_faces, in
                          const float* vertex_features, int features_shared,
                          const float* soft_mask, float sigmainv, float box_margin, int knum,
                          float multiplier, float eps, float* grad_vertices_image,
-                         float* grad_vertex_features, void* moment_scratch, const void* ws,
-                         int64_t ws_bytes, int64_t raster_capacity, int64_t soft_capacity,
-                         int64_t pair_capacity, void* stream);
+                         float* grad_vertex_features, const void* ws, int64_t ws_bytes,
+                         int64_t raster_capacity, int64_t soft_capacity, int64_t pair_capacity,
+                         void* stream);
 
 /* The V-sized head of prepare_vertices (kaolin/render/mesh/utils.py:158-170):
  * rotate_translate_points (camera/legacy.py:22-37: (v - trans) @ rot^T) or the 4x3

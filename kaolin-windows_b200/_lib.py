@@ -42,9 +42,8 @@ SIGNATURES = {
                              _vp, _vp, _vp, _i64, _i64, _i64, _i64, _vp]),
     "dibr_render_mesh_fwd": (_i, [_i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _i, _vp, _f, _f, _i,
                                   _f, _f, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _vp, _vp]),
-    "dibr_mesh_moment_bytes": (_i64, [_i, _i, _i]),
     "dibr_render_mesh_bwd": (_i, [_i, _i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp,
-                                  _f, _f, _i, _f, _f, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64,
+                                  _f, _f, _i, _f, _f, _vp, _vp, _vp, _i64, _i64, _i64, _i64,
                                   _vp]),
     "dibr_vertex_transform_fwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "dibr_vertex_transform_bwd": (_i, [_i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),

@@ -379,7 +379,6 @@ extern "C" int dibr_rasterize_bwd(int B, int F, int H, int W, int D, const float
   a.grad = grad; a.idx = idx; a.weights = weights; a.img = img; a.feat = feat;
   a.grad_img = grad_img; a.grad_feat = grad_feat;
   a.B = B; a.F = F; a.H = H; a.W = W; a.D = D;
-  a.moments = grad_feat;
   a.mult = multiplier; a.eps_f = eps; a.eps_d = (double)eps;
   a.inv_mult = 1.0 / (double)multiplier; a.grid = make_grid(multiplier, W, H);
   DIBR_CUDA(launch_raster_backward(a, (cudaStream_t)stream));
@@ -505,19 +504,17 @@ extern "C" int dibr_render_bwd(int B, int F, int H, int W, int D, const float* g
     ra.grad = grad_feat_img; ra.idx = idx; ra.weights = nullptr; ra.img = img; ra.feat = feat;
     ra.grad_img = grad_img; ra.grad_feat = grad_feat;
     ra.B = B; ra.F = F; ra.H = H; ra.W = W; ra.D = D;
-    ra.moments = grad_feat;
     ra.mult = multiplier; ra.eps_f = eps; ra.eps_d = (double)eps;
     ra.inv_mult = 1.0 / (double)multiplier; ra.grid = make_grid(multiplier, W, H);
-    DIBR_CUDA(launch_raster_backward_moments(ra, st));
+    DIBR_CUDA(launch_raster_backward(ra, st));
   }
   if (do_soft) {
-    // (running this on a second stream beside the moments pass was measured: both kernels
-    // fill the SMs, the overlap gained nothing)
+    // (running this on a second stream beside the rasterizer's backward was measured: both
+    // kernels fill the SMs, the overlap gained nothing)
     rc = dibr_softmask_bwd(B, F, H, W, img, 0, nullptr, idx, sigmainv, box_margin, K, multiplier,
                            grad_mask, mask, grad_img, ws, ws_bytes, cap_r, cap_s, cap_p, st);
     if (rc) return rc;
   }
-  if (do_raster) DIBR_CUDA(launch_raster_backward_finish(ra, st));
   return DIBR_OK;
 }
 
@@ -618,6 +615,7 @@ extern "C" int dibr_rasterize_bwd_f64(int B, int F, int H, int W, int D, const d
                                       double* grad_img, double* grad_feat, void* stream) {
   if (B < 0 || F < 0 || H <= 0 || W <= 0 || D < 0) return fail(DIBR_E_INVALID, "invalid sizes");
   if (B == 0 || F == 0 || D == 0) return DIBR_OK;
+  if (B > 65535) return fail(DIBR_E_INVALID, "batch %d > 65535 not supported", B);
   if (!grad || !idx || !weights || !img || !feat || !grad_img || !grad_feat)
     return fail(DIBR_E_INVALID, "null pointer");
   RasterBwdF64Args a;
@@ -737,11 +735,6 @@ extern "C" int dibr_render_mesh_fwd(int B, int V, int F, int H, int W, int D,
   return run_soft_forward(s, p, needed_host, st);
 }
 
-extern "C" int64_t dibr_mesh_moment_bytes(int B, int F, int D) {
-  if (B < 0 || F < 0 || D < 0) return DIBR_E_INVALID;
-  return align_up((int64_t)B * F * 3 * D * 4, 256);
-}
-
 extern "C" int dibr_render_mesh_bwd(int B, int V, int F, int H, int W, int D,
                                     const float* grad_feat_img, const float* grad_mask,
                                     const int64_t* idx, const float* vertices_image,
@@ -749,7 +742,7 @@ extern "C" int dibr_render_mesh_bwd(int B, int V, int F, int H, int W, int D,
                                     int features_shared, const float* mask, float sigmainv,
                                     float box_margin, int K, float multiplier, float eps,
                                     float* grad_vertices_image, float* grad_vertex_features,
-                                    void* moment_scratch, const void* ws, int64_t ws_bytes,
+                                    const void* ws, int64_t ws_bytes,
                                     int64_t cap_r, int64_t cap_s, int64_t cap_p, void* stream) {
   if (B < 0 || V < 0 || F < 0 || H <= 0 || W <= 0 || D < 0 || K < 0)
     return fail(DIBR_E_INVALID, "invalid sizes");
@@ -769,19 +762,17 @@ extern "C" int dibr_render_mesh_bwd(int B, int V, int F, int H, int W, int D,
     return fail(DIBR_E_INVALID, "null pointer");
   const bool do_raster = grad_feat_img && D > 0, do_soft = grad_mask && K > 0;
   if (do_soft && !mask) return fail(DIBR_E_INVALID, "null soft_mask");
-  if (do_raster && !moment_scratch) return fail(DIBR_E_INVALID, "null moment scratch");
   RasterBwdArgs ra;
   memset(&ra, 0, sizeof(ra));
   if (do_raster) {
-    DIBR_CUDA(cudaMemsetAsync(moment_scratch, 0, (size_t)B * F * 3 * D * sizeof(float), st));
     ra.grad = grad_feat_img; ra.idx = idx; ra.weights = nullptr; ra.img = vertices_image;
     ra.feat = vertex_features; ra.grad_img = grad_vertices_image;
-    ra.grad_feat = grad_vertex_features; ra.moments = (float*)moment_scratch;
+    ra.grad_feat = grad_vertex_features;
     ra.faces = faces; ra.V = V; ra.feat_shared = features_shared;
     ra.B = B; ra.F = F; ra.H = H; ra.W = W; ra.D = D;
     ra.mult = multiplier; ra.eps_f = eps; ra.eps_d = (double)eps;
     ra.inv_mult = 1.0 / (double)multiplier; ra.grid = make_grid(multiplier, W, H);
-    DIBR_CUDA(launch_raster_backward_moments(ra, st));
+    DIBR_CUDA(launch_raster_backward(ra, st));
   }
   if (do_soft) {
     Plan p;
@@ -799,6 +790,5 @@ extern "C" int dibr_render_mesh_bwd(int B, int V, int F, int H, int W, int D,
     DIBR_CUDA(launch_softmask_pairs_grad(a, p, st));
     DIBR_CUDA(launch_softmask(a, SOFT_BWD, p, st));
   }
-  if (do_raster) DIBR_CUDA(launch_raster_backward_finish(ra, st));
   return DIBR_OK;
 }

@@ -136,10 +136,8 @@ struct RasterBwdArgs {
   const float* feat;       // (B, F, 3, D)
   float* grad_img;         // (B, F, 3, 2)
   float* grad_feat;        // (B, F, 3, D)
-  float* moments;          // (B, F, 3, D) accumulator of pass 1 (= grad_feat: in place)
   // mesh mode (faces != nullptr): img = vertices_image (B, V, 2), feat = vertex features
-  // (B or 1, V, D), grad_img / grad_feat the vertex gradients of the same shapes (added to
-  // with atomics), moments a separate zero-filled scratch
+  // (B or 1, V, D), grad_img / grad_feat the vertex gradients of the same shapes
   const int* faces;        // (F, 3) int32 or nullptr
   int V;
   int feat_shared;
@@ -201,18 +199,22 @@ struct SoftArgs {
                                // the rasterizer of the same call), or null
 };
 
-struct SoftDenseBwdArgs {
-  const float* grad_mask;
-  const float* mask;
+// dense-state backward of the raw _C op, float and double
+template <typename T>
+struct SoftDenseBwdArgsT {
+  const T* grad_mask;
+  const T* mask;
   const int64_t* sel;
-  const float* prob;
+  const T* prob;
   const int64_t* cidx;
   const uint8_t* type;
-  const float* img;  // (B, F, 3, 2) scaled
-  float* grad_img;
+  const T* img;  // (B, F, 3, 2) scaled
+  T* grad_img;
   int B, F, H, W, K;
   float sigmainv, mult;
 };
+using SoftDenseBwdArgs = SoftDenseBwdArgsT<float>;
+using SoftBwdF64Args = SoftDenseBwdArgsT<double>;
 
 // ---- double-precision instantiation (dibr_f64.cu): the reference's raw-op layouts --
 // packed faces + boxes + first index for the rasterizer, scaled coordinates + enlarged boxes
@@ -242,14 +244,6 @@ struct SoftF64Args {
   int64_t* cidx;
   uint8_t* type;
 };
-struct SoftBwdF64Args {
-  const double *grad_mask, *mask, *prob, *img;
-  const int64_t *sel, *cidx;
-  const uint8_t* type;
-  double* grad_img;
-  int B, F, H, W, K;
-  float sigmainv, mult;
-};
 
 // SOFT_FWD / SOFT_BWD: self-contained kernels (gather + evaluate per block); when a pair
 // buffer is attached they only run if it overflowed.  SOFT_GATHER: gather only, fills the
@@ -267,8 +261,6 @@ cudaError_t launch_binning_count(const BinJobs&, int njobs, const Plan&, cudaStr
 cudaError_t launch_binning_fill(const BinJobs&, int njobs, const Plan&, cudaStream_t);
 cudaError_t launch_raster_forward(const RasterArgs&, const Plan&, cudaStream_t);
 cudaError_t launch_raster_backward(const RasterBwdArgs&, cudaStream_t);
-cudaError_t launch_raster_backward_moments(const RasterBwdArgs&, cudaStream_t);
-cudaError_t launch_raster_backward_finish(const RasterBwdArgs&, cudaStream_t);
 cudaError_t launch_softmask(const SoftArgs&, int mode, const Plan&, cudaStream_t);
 cudaError_t launch_softmask_dense_backward(const SoftDenseBwdArgs&, cudaStream_t);
 cudaError_t launch_softmask_gather(const SoftArgs&, const Plan&, cudaStream_t);

@@ -1,8 +1,12 @@
-// dibr_f64.cu -- the double-precision instantiation of the four reference kernels
-// (AT_DISPATCH_FLOATING_TYPES at rasterization_cuda.cu:30-39, dibr_soft_mask_cuda.cu:211,382;
-// the reference's tests run both dtypes).  Test-sized workloads: plain one-pixel-per-thread
-// kernels, but over the same binned face lists as the float path instead of the
-// reference's loop over every face -- the lists come from the float binning run on float
+// dibr_f64.cu -- the two FORWARD kernels of the reference's double dispatch
+// (AT_DISPATCH_FLOATING_TYPES at rasterization_cuda.cu:30-39, dibr_soft_mask_cuda.cu:211;
+// the reference's tests run both dtypes).  The two backward kernels for double are the
+// double instantiations of the float path's designs: raster_backward_f64_kernel
+// (dibr_raster.cu: warp-grouped sums, group-level conversion) and
+// softmask_dense_backward_kernel<double> (dibr_softmask.cu: pairs dealt over the lanes,
+// (face, vertex)-grouped atomics).  Test-sized workloads: one pixel per thread, but over
+// the same binned face lists as the float path instead of the reference's loop over every
+// face -- the lists come from the float binning run on float
 // copies of the coordinates (a conservative superset: its pixel ranges carry 1e-3 pixel of
 // slack, the float rounding of a coordinate is < 1e-4 pixel), every listed face then takes
 // the exact double test below.
@@ -96,53 +100,6 @@ raster_forward_f64_kernel(const RasterF64Args a, const Plan p) {
   }
 }
 
-// ------------------------------------------------------------------ rasterize backward
-// rasterization_cuda.cu:238-402; unscaled coordinates, saved weights.
-__global__ void __launch_bounds__(256) raster_backward_f64_kernel(const RasterBwdF64Args a) {
-  const long long npix = (long long)a.B * a.H * a.W;
-  for (long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x; pix < npix;
-       pix += (long long)gridDim.x * blockDim.x) {
-    const int face = (int)a.idx[pix];
-    if (face < 0) continue;
-    const int b = (int)(pix / ((long long)a.H * a.W));
-    const long long gi = (long long)b * a.F + face;
-    const double* g = a.grad + pix * a.D;
-    const double aw = a.weights[pix * 3], bw = a.weights[pix * 3 + 1], cw = a.weights[pix * 3 + 2];
-    double* gf = a.grad_feat + gi * 3 * a.D;
-    for (int d = 0; d < a.D; d++) {      // :273-285
-      atomicAdd(gf + d, g[d] * aw);
-      atomicAdd(gf + a.D + d, g[d] * bw);
-      atomicAdd(gf + 2 * a.D + d, g[d] * cw);
-    }
-    const double* v = a.img + gi * 6;
-    const double ax = v[0], ay = v[1], bx = v[2], by = v[3], cx = v[4], cy = v[5];
-    const double x0 = aw * ax + bw * bx + cw * cx, y0 = aw * ay + bw * by + cw * cy;  // :302-303
-    const double m = bx - ax, pp = by - ay, n = cx - ax, q = cy - ay, s = x0 - ax, t = y0 - ay;
-    const double k1 = s * q - n * t, k2 = m * t - s * pp;
-    double k3 = m * q - n * pp;
-    k3 = k3 + copysign(a.eps_d, k3);                                                  // :319-322
-    // dw1 = d(k1/k3) * k3^2, dw2 = d(k2/k3) * k3^2 w.r.t. m, n, p, q, s, t (:324-360)
-    const double dw1dm = -q * k1, dw1dn = -t * k3 + pp * k1, dw1dp = n * k1;
-    const double dw1dq = s * k3 - m * k1, dw1ds = q * k3, dw1dt = -n * k3;
-    const double dw2dm = t * k3 - q * k2, dw2dn = pp * k2, dw2dp = -s * k3 + n * k2;
-    const double dw2dq = -m * k2, dw2ds = -pp * k3, dw2dt = m * k3;
-    const double dw1dax = -(dw1dm + dw1dn + dw1ds), dw1day = -(dw1dp + dw1dq + dw1dt);
-    const double dw2dax = -(dw2dm + dw2dn + dw2ds), dw2day = -(dw2dp + dw2dq + dw2dt);
-    const double* fp = a.feat + gi * 3 * a.D;
-    double* gv = a.grad_img + gi * 6;
-    for (int d = 0; d < a.D; d++) {      // :376-399
-      const double c0 = fp[d], e1 = fp[a.D + d] - c0, e2 = fp[2 * a.D + d] - c0;
-      const double dldI = g[d] / (k3 * k3);
-      atomicAdd(gv + 0, dldI * (e1 * dw1dax + e2 * dw2dax));
-      atomicAdd(gv + 1, dldI * (e1 * dw1day + e2 * dw2day));
-      atomicAdd(gv + 2, dldI * (e1 * dw1dm + e2 * dw2dm));
-      atomicAdd(gv + 3, dldI * (e1 * dw1dp + e2 * dw2dp));
-      atomicAdd(gv + 4, dldI * (e1 * dw1dn + e2 * dw2dn));
-      atomicAdd(gv + 5, dldI * (e1 * dw1dq + e2 * dw2dq));
-    }
-  }
-}
-
 // ------------------------------------------------------------------ soft mask forward
 // dibr_soft_mask_cuda.cu:27-184; scaled coordinates, enlarged boxes, dense per-pixel state
 // (pre-filled by the caller as dibr_soft_mask.cpp:84-97 does).
@@ -228,51 +185,6 @@ softmask_forward_f64_kernel(const SoftF64Args a, const Plan p) {
   }
 }
 
-// ------------------------------------------------------------------ soft mask backward
-// dibr_soft_mask_cuda.cu:230-353 over the dense state the forward stored.
-__global__ void __launch_bounds__(256) softmask_backward_f64_kernel(const SoftBwdF64Args a) {
-  const long long npix = (long long)a.B * a.H * a.W;
-  const Grid g = make_grid(a.mult, a.W, a.H);
-  const double mult = (double)a.mult;
-  for (long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x; pix < npix;
-       pix += (long long)gridDim.x * blockDim.x) {
-    if (a.sel[pix] >= 0) continue;
-    const int ix = (int)(pix % a.W), iy = (int)((pix / a.W) % a.H);
-    const int b = (int)(pix / ((long long)a.W * a.H));
-    const double x0 = (double)pix_x(g, ix), y0 = (double)pix_y(g, iy);
-    const double dLdp = a.grad_mask[pix], allprob = a.mask[pix];
-    for (int kid = 0; kid < a.K; kid++) {
-      const long long o = pix * a.K + kid;
-      const int f = (int)a.cidx[o];
-      if (f < 0) break;
-      const double* v = a.img + ((long long)b * a.F + f) * 6;
-      double* gv = a.grad_img + ((long long)b * a.F + f) * 6;
-      const double prob = a.prob[o];
-      const double dLdz = -1.0 * (double)a.sigmainv * dLdp * (1.0 - allprob) /
-                          (1.0 - prob + DIBR_F64_EPS) * prob;                      // :283-284
-      const int edgeid = (int)a.type[o] - 1;
-      if (edgeid >= 3) {                 // :287-302 nearest feature is a vertex
-        const int pl = (edgeid - 3) * 2;
-        atomicAdd(gv + pl, dLdz * 2 * (v[pl] - x0) / mult);
-        atomicAdd(gv + pl + 1, dLdz * 2 * (v[pl + 1] - y0) / mult);
-      } else {                           // :304-347 nearest feature is an edge
-        const int pl = edgeid * 2, pl2 = ((edgeid + 1) % 3) * 2;
-        const double x1 = v[pl], y1 = v[pl + 1], x2 = v[pl2], y2 = v[pl2 + 1];
-        const double A = y2 - y1, B = x1 - x2, C = x2 * y1 - x1 * y2;
-        const double up = A * x0 + B * y0 + C, down = A * A + B * B;
-        const double dis = up * up / (down + DIBR_F64_EPS);
-        const double dzdA = 2 * (x0 * up - dis * A) / (down + DIBR_F64_EPS);
-        const double dzdB = 2 * (y0 * up - dis * B) / (down + DIBR_F64_EPS);
-        const double dzdC = 2 * up / (down + DIBR_F64_EPS);
-        atomicAdd(gv + pl, dLdz * (dzdB - y2 * dzdC) / mult);
-        atomicAdd(gv + pl + 1, dLdz * (x2 * dzdC - dzdA) / mult);
-        atomicAdd(gv + pl2, dLdz * (y1 * dzdC - dzdB) / mult);
-        atomicAdd(gv + pl2 + 1, dLdz * (dzdA - x1 * dzdC) / mult);
-      }
-    }
-  }
-}
-
 }  // namespace
 
 cudaError_t launch_raster_forward_f64(const RasterF64Args& a, const Plan& p, cudaStream_t st) {
@@ -281,23 +193,9 @@ cudaError_t launch_raster_forward_f64(const RasterF64Args& a, const Plan& p, cud
   return cudaGetLastError();
 }
 
-cudaError_t launch_raster_backward_f64(const RasterBwdF64Args& a, cudaStream_t st) {
-  const long long npix = (long long)a.B * a.H * a.W;
-  if (npix == 0) return cudaSuccess;
-  raster_backward_f64_kernel<<<(int)min((npix + 255) / 256, (long long)148 * 16), 256, 0, st>>>(a);
-  return cudaGetLastError();
-}
-
 cudaError_t launch_softmask_forward_f64(const SoftF64Args& a, const Plan& p, cudaStream_t st) {
   dim3 grid((p.W + kTile - 1) / kTile, (p.H + kTile - 1) / kTile, p.B);
   softmask_forward_f64_kernel<<<grid, kTile * kTile, 0, st>>>(a, p);
-  return cudaGetLastError();
-}
-
-cudaError_t launch_softmask_backward_f64(const SoftBwdF64Args& a, cudaStream_t st) {
-  const long long npix = (long long)a.B * a.H * a.W;
-  if (npix == 0) return cudaSuccess;
-  softmask_backward_f64_kernel<<<(int)min((npix + 255) / 256, (long long)148 * 16), 256, 0, st>>>(a);
   return cudaGetLastError();
 }
 

@@ -430,13 +430,14 @@ cudaError_t launch_raster_forward(const RasterArgs& a, const Plan& p, cudaStream
 //     w1 = (s q - n t) / k3,  w2 = (m t - s p) / k3,  w0 = 1 - w1 - w2,
 // and every d(w1|w2)/d(vertex) (:324-374) is (const + const s + const t) / k3^2.  So all a
 // face needs from its pixels are the 3*D MOMENTS  M0_d = sum g_d, Ms_d = sum g_d s,
-// Mt_d = sum g_d t  of the incoming gradient g over the pixels that selected it:
-//   pass 1 (pixel-parallel): a warp owns an 8x4 region; lanes with the same face are
-//     grouped with __match_any_sync, their moments summed with shuffles, and ONE
-//     red.global.add per (face, moment) leaves the warp -- into grad_face_features, whose
-//     (3, D) slot per face is used as the moment accumulator;
-//   pass 2 (face-parallel, FP64): turns the moments of every touched face into
-//     grad_face_features (in place) and grad_face_vertices_image (added) with plain stores.
+// Mt_d = sum g_d t  of the incoming gradient g over the pixels that selected it -- and the
+// map from moments to both gradients is LINEAR, so it can be applied to partial sums.
+// One pass, pixel-parallel: a warp owns an 8x4 region; lanes with the same face are grouped
+// with __match_any_sync, their moments summed with shuffles, and the group's first lane
+// turns the partial moments into gradient contributions and issues ONE
+// red.global.add per output element: 3*D + 6 per (warp, face) instead of 9*D per pixel, no
+// per-face accumulator, no second pass.  In mesh mode the contributions go straight to the
+// vertex gradients through `faces`.
 // Precision.  The gradient is a function of the pixel CENTRE; the reference reconstructs the
 // centre from the fp32 weights its forward saved (:302-303), whose rounding -- and that of
 // fl32(v * multiplier) -- is a 1e-4 .. 1e-2 relative perturbation of (s, t) for sub-pixel
@@ -446,11 +447,14 @@ cudaError_t launch_raster_forward(const RasterArgs& a, const Plan& p, cudaStream
 // normalisation (:140-142) scales all three weights by rho = |N| / (|N| + eps), N = the
 // face's area term in multiplied coordinates; the reconstructed centre is rho * X: both
 // are carried through (they matter for small multipliers).
-// Faces for which the fp32 moment sums would not stay within a few ulp -- slivers / zero
-// area (|k3| < 10% of |m q| + |n p|: k3 itself cancels) and faces under two pixels
-// (|k3| < 4 pixel areas; they own one or two pixels and gain nothing from moments) -- take
-// the reference's per-pixel formula in pass 1, evaluated in DOUBLE from the unrounded
-// inputs, and are skipped by pass 2.
+// Faces for which fp32 moment sums would not stay within a few ulp -- slivers / zero area
+// (|k3| < 10% of |m q| + |n p|: k3 itself cancels) and faces under two pixels
+// (|k3| < 4 pixel areas; they own one or two pixels and gain nothing from grouping) -- take
+// the reference's per-pixel formula, evaluated in DOUBLE from the unrounded inputs; so does
+// every face when the caller hands the forward's weights (the raw _C op).
+// The same kernel instantiated for double serves the reference's double dispatch
+// (rasterization_cuda.cu:30-39): moments and sums in double, pixel centre from the saved
+// double weights (that entry point has no image geometry).
 // ===========================================================================
 
 // face constants of the backward (unscaled coordinates); regular = moment form applies
@@ -502,8 +506,49 @@ __device__ __forceinline__ float* bwd_gimg(const RasterBwdArgs& a, int b, int fa
   return a.grad_img + (((long long)b * a.F + face) * 3 + k) * 2;
 }
 
-template <int N>
-__device__ __forceinline__ void reduce_peers(unsigned peers, float (&v)[N], int lane) {
+// The reference's per-pixel backward (:273-399) for one pixel, in double, from the weights w:
+// grad_face_features += g w_k, grad_face_vertices_image += (sum over d) dldI d w_{1,2} / d v.
+// T = storage type of the tensors (float, or double for the reference's double dispatch).
+template <typename T>
+__device__ __forceinline__ void per_pixel_backward(const T* g, const double (&w)[3], double ax,
+                                                   double ay, double bx, double by, double cx,
+                                                   double cy, double eps_d, int D, const T* fp0,
+                                                   const T* fp1, const T* fp2, T* gf0, T* gf1,
+                                                   T* gf2, T* gi0, T* gi1, T* gi2) {
+  const double x0 = w[0] * ax + w[1] * bx + w[2] * cx;   // :302-303
+  const double y0 = w[0] * ay + w[1] * by + w[2] * cy;
+  const double m = bx - ax, pp = by - ay, n = cx - ax, q = cy - ay, ss = x0 - ax, tt = y0 - ay;
+  const double k1 = ss * q - n * tt;
+  const double k2 = m * tt - ss * pp;
+  double k3 = m * q - n * pp;
+  k3 += copysign(eps_d, k3);
+  const double dw1dm = -q * k1, dw1dn = -tt * k3 + pp * k1;
+  const double dw1dp = n * k1, dw1dq = ss * k3 - m * k1;
+  const double dw1ds = q * k3, dw1dt = -n * k3;
+  const double dw2dm = tt * k3 - q * k2, dw2dn = pp * k2;
+  const double dw2dp = -ss * k3 + n * k2, dw2dq = -m * k2;
+  const double dw2ds = -pp * k3, dw2dt = m * k3;
+  double e1 = 0.0, e2 = 0.0;                 // sum over d of g_d (c1 - c0), g_d (c2 - c0)
+  for (int d = 0; d < D; d++) {
+    const double gd = (double)g[d];
+    atomicAdd(gf0 + d, (T)(gd * w[0]));
+    atomicAdd(gf1 + d, (T)(gd * w[1]));
+    atomicAdd(gf2 + d, (T)(gd * w[2]));
+    const double c0 = (double)fp0[d], c1 = (double)fp1[d], c2 = (double)fp2[d];
+    e1 += gd * (c1 - c0);
+    e2 += gd * (c2 - c0);
+  }
+  const double r = 1.0 / (k3 * k3);
+  atomicAdd(gi0, (T)((e1 * -(dw1dm + dw1dn + dw1ds) + e2 * -(dw2dm + dw2dn + dw2ds)) * r));
+  atomicAdd(gi0 + 1, (T)((e1 * -(dw1dp + dw1dq + dw1dt) + e2 * -(dw2dp + dw2dq + dw2dt)) * r));
+  atomicAdd(gi1, (T)((e1 * dw1dm + e2 * dw2dm) * r));
+  atomicAdd(gi1 + 1, (T)((e1 * dw1dp + e2 * dw2dp) * r));
+  atomicAdd(gi2, (T)((e1 * dw1dn + e2 * dw2dn) * r));
+  atomicAdd(gi2 + 1, (T)((e1 * dw1dq + e2 * dw2dq) * r));
+}
+
+template <typename T, int N>
+__device__ __forceinline__ void reduce_peers(unsigned peers, T (&v)[N], int lane) {
   int rel_pos = __popc(peers & lanemask_lt());
   unsigned rem = peers & ~(lanemask_lt() | (1u << lane));  // peers with a higher lane id
   while (__any_sync(DIBR_FULL_MASK, rem != 0)) {
@@ -511,7 +556,7 @@ __device__ __forceinline__ void reduce_peers(unsigned peers, float (&v)[N], int 
     const int src = next ? next - 1 : lane;
 #pragma unroll
     for (int i = 0; i < N; i++) {
-      const float t = __shfl_sync(DIBR_FULL_MASK, v[i], src);
+      const T t = __shfl_sync(DIBR_FULL_MASK, v[i], src);
       if (next) v[i] += t;
     }
     const bool done = rel_pos & 1;
@@ -520,8 +565,70 @@ __device__ __forceinline__ void reduce_peers(unsigned peers, float (&v)[N], int 
   }
 }
 
+// moments of a (warp, face) group -> gradient contributions (:324-374 with (1, s, t) replaced
+// by their sums; all in double) and one atomic per output element.  M[0..D) = sum g_d,
+// M[DC..) = sum g_d s, M[2 DC..) = sum g_d t with (s, t) measured from vertex a WITHOUT the
+// eps scaling (sl, tl); rho folds it in.
+template <int DC>
+__device__ __forceinline__ void emit_group(const RasterBwdArgs& a, int b, int face,
+                                           const BwdFace& fc, const float (&M)[3 * DC], int d0) {
+  // Regular faces only (|k3| >= 10% of |m q| + |n p|, >= 4 pixel areas): every quotient below
+  // is well conditioned, so float carries it (the cancellation inside the K and d terms
+  // amplifies float rounding by at most ~1e2: 1e-5 relative).  Face constants in float from
+  // the float inputs; only k3's eps and rho, which differ from 1 by ~1e-8, go through double.
+  // (edge vectors and k3 differenced in double first: a float difference of two coordinates
+  // near 1 would already cost 1e-5 of a two-pixel face at 2048^2)
+  const double md = (double)fc.bx - (double)fc.ax, pd = (double)fc.by - (double)fc.ay;
+  const double nd = (double)fc.cx - (double)fc.ax, qd = (double)fc.cy - (double)fc.ay;
+  const double k3d = md * qd - nd * pd;
+  const float m = (float)md, p = (float)pd, n = (float)nd, q = (float)qd, k3raw = (float)k3d;
+  const float k3 = (float)(k3d + copysign(a.eps_d, k3d));                          // :321-322
+  const float inv_k3raw = 1.0f / k3raw;
+  // eps of the forward's normalisation (:140-142), in multiplied coordinates:
+  // rho = N / (N + eps), N = |k3raw| mult^2; rho - 1 = -eps / (N + eps) kept separately
+  const double N = fabs(k3d) * (double)a.mult * (double)a.mult;
+  const float rho = (float)(N / (N + a.eps_d)), rho1 = (float)(-a.eps_d / (N + a.eps_d));
+  const float *fp0 = bwd_feat(a, b, face, fc, 0), *fp1 = bwd_feat(a, b, face, fc, 1);
+  const float* fp2 = bwd_feat(a, b, face, fc, 2);
+  float *gf0 = bwd_gfeat(a, b, face, fc, 0), *gf1 = bwd_gfeat(a, b, face, fc, 1);
+  float* gf2 = bwd_gfeat(a, b, face, fc, 2);
+  float P0 = 0.f, Ps = 0.f, Pt = 0.f, Q0 = 0.f, Qs = 0.f, Qt = 0.f;
+#pragma unroll
+  for (int dd = 0; dd < DC; dd++) {
+    const int d = d0 + dd;
+    if (d >= a.D) break;
+    const float M0 = M[dd], Msl = M[DC + dd], Mtl = M[2 * DC + dd];
+    // moments of the reconstructed centre rho * X - a = rho (X - a) + (rho - 1) a
+    const float Ms = rho * Msl + rho1 * fc.ax * M0;
+    const float Mt = rho * Mtl + rho1 * fc.ay * M0;
+    const float c0 = __ldg(fp0 + d), c1 = __ldg(fp1 + d), c2 = __ldg(fp2 + d);
+    const float e1 = c1 - c0, e2 = c2 - c0;
+    P0 += e1 * M0; Ps += e1 * Ms; Pt += e1 * Mt;
+    Q0 += e2 * M0; Qs += e2 * Ms; Qt += e2 * Mt;
+    // grad_face_features: sum g w_k with the forward's weights w1 = rho (sl q - n tl) / k3raw,
+    // w2 = rho (m tl - sl p) / k3raw, w0 = rho - w1 - w2
+    const float g1 = rho * (Msl * q - n * Mtl) * inv_k3raw;
+    const float g2 = rho * (m * Mtl - Msl * p) * inv_k3raw;
+    atomicAdd(gf0 + d, rho * M0 - g1 - g2);
+    atomicAdd(gf1 + d, g1);
+    atomicAdd(gf2 + d, g2);
+  }
+  const float K1 = Ps * q - n * Pt, K2 = m * Qt - Qs * p;
+  const float dm = -q * K1 + (Qt * k3 - q * K2);
+  const float dn = (-Pt * k3 + p * K1) + p * K2;
+  const float dp = n * K1 + (-Qs * k3 + n * K2);
+  const float dq = (Ps * k3 - m * K1) - m * K2;
+  const float ds = q * k3 * P0 - p * k3 * Q0;
+  const float dt = -n * k3 * P0 + m * k3 * Q0;
+  const float r = 1.0f / (k3 * k3);
+  atomicAdd(reinterpret_cast<float2*>(bwd_gimg(a, b, face, fc, 0)),
+            make_float2(-(dm + dn + ds) * r, -(dp + dq + dt) * r));
+  atomicAdd(reinterpret_cast<float2*>(bwd_gimg(a, b, face, fc, 1)), make_float2(dm * r, dp * r));
+  atomicAdd(reinterpret_cast<float2*>(bwd_gimg(a, b, face, fc, 2)), make_float2(dn * r, dq * r));
+}
+
 template <int DC>  // features handled per pass (D <= 4: one pass)
-__global__ void __launch_bounds__(256, 6) raster_backward_kernel(const RasterBwdArgs a) {
+__global__ void __launch_bounds__(256, 4) raster_backward_kernel(const RasterBwdArgs a) {
   pdl_prologue();
   const int lane = lane_id(), warp = threadIdx.x >> 5;
   const int ix = (blockIdx.x << 4) + ((warp & 1) << 3) + (lane & 7);
@@ -535,22 +642,17 @@ __global__ void __launch_bounds__(256, 6) raster_backward_kernel(const RasterBwd
   const unsigned peers = __match_any_sync(DIBR_FULL_MASK, face);
   const bool leader = (peers & lanemask_lt()) == 0;
 
-  long long fbase = 0;
   float s = 0.f, t = 0.f;
-  double X = 0.0, Y = 0.0;
   bool regular = false;
   BwdFace fc;
   if (face >= 0) {
-    fbase = (long long)b * a.F + face;
     fc = bwd_face(a, b, face, 16.f / ((float)a.W * (float)a.H));
     regular = fc.regular && !a.weights;   // given weights (raw op): per pixel, as the reference
     // pixel centre as the forward forms it (:85-86), back in unscaled coordinates; minus
     // vertex a in double: for faces much smaller than the image the float rounding of the
     // centre itself (~6e-8) would be a visible fraction of (s, t)
-    X = (double)pix_x(a.grid, ix) * a.inv_mult;
-    Y = (double)pix_y(a.grid, iy) * a.inv_mult;
-    s = (float)(X - (double)fc.ax);
-    t = (float)(Y - (double)fc.ay);
+    s = (float)((double)pix_x(a.grid, ix) * a.inv_mult - (double)fc.ax);
+    t = (float)((double)pix_y(a.grid, iy) * a.inv_mult - (double)fc.ay);
   }
   for (int d0 = 0; d0 < a.D; d0 += DC) {
     float mom[3 * DC];
@@ -567,19 +669,8 @@ __global__ void __launch_bounds__(256, 6) raster_backward_kernel(const RasterBwd
         }
       }
     }
-    reduce_peers<3 * DC>(peers, mom, lane);
-    if (leader && regular) {
-      float* gp = a.moments + fbase * 3 * a.D;
-#pragma unroll
-      for (int dd = 0; dd < DC; dd++) {
-        const int d = d0 + dd;
-        if (d < a.D) {
-          atomicAdd(gp + d, mom[dd]);
-          atomicAdd(gp + a.D + d, mom[DC + dd]);
-          atomicAdd(gp + 2 * a.D + d, mom[2 * DC + dd]);
-        }
-      }
-    }
+    reduce_peers<float, 3 * DC>(peers, mom, lane);
+    if (leader && regular) emit_group<DC>(a, b, face, fc, mom, d0);
   }
 
   // ---- thin / tiny faces: the reference's per-pixel formula (:273-399) in double
@@ -611,127 +702,116 @@ __global__ void __launch_bounds__(256, 6) raster_backward_kernel(const RasterBwd
         w[0] = f0; w[1] = f1; w[2] = f2;
       }
     }
-    const double x0 = w[0] * ax + w[1] * bx + w[2] * cx;   // :302-303
-    const double y0 = w[0] * ay + w[1] * by + w[2] * cy;
-    const double m = bx - ax, pp = by - ay, n = cx - ax, q = cy - ay, ss = x0 - ax, tt = y0 - ay;
-    const double k1 = ss * q - n * tt;
-    const double k2 = m * tt - ss * pp;
-    double k3 = m * q - n * pp;
-    k3 += copysign(a.eps_d, k3);
-    double dw1[6], dw2[6];
-    const double dw1dm = -q * k1, dw1dn = -tt * k3 + pp * k1;
-    const double dw1dp = n * k1, dw1dq = ss * k3 - m * k1;
-    const double dw1ds = q * k3, dw1dt = -n * k3;
-    const double dw2dm = tt * k3 - q * k2, dw2dn = pp * k2;
-    const double dw2dp = -ss * k3 + n * k2, dw2dq = -m * k2;
-    const double dw2ds = -pp * k3, dw2dt = m * k3;
-    dw1[0] = -(dw1dm + dw1dn + dw1ds); dw1[1] = -(dw1dp + dw1dq + dw1dt);
-    dw1[2] = dw1dm; dw1[3] = dw1dp; dw1[4] = dw1dn; dw1[5] = dw1dq;
-    dw2[0] = -(dw2dm + dw2dn + dw2ds); dw2[1] = -(dw2dp + dw2dq + dw2dt);
-    dw2[2] = dw2dm; dw2[3] = dw2dp; dw2[4] = dw2dn; dw2[5] = dw2dq;
-    const float *fp0 = bwd_feat(a, b, face, fc, 0), *fp1 = bwd_feat(a, b, face, fc, 1);
-    const float* fp2 = bwd_feat(a, b, face, fc, 2);
-    // face tensors: grad_face_features doubles as the moment accumulator, for these faces
-    // it receives the final gradient; mesh mode: the vertex gradients directly
-    float *gf0 = bwd_gfeat(a, b, face, fc, 0), *gf1 = bwd_gfeat(a, b, face, fc, 1);
-    float* gf2 = bwd_gfeat(a, b, face, fc, 2);
-    double e1 = 0.0, e2 = 0.0;                 // sum over d of g_d (c1 - c0), g_d (c2 - c0)
-    for (int d = 0; d < a.D; d++) {
-      const double gd = (double)a.grad[pix * a.D + d];
-      atomicAdd(gf0 + d, (float)(gd * w[0]));
-      atomicAdd(gf1 + d, (float)(gd * w[1]));
-      atomicAdd(gf2 + d, (float)(gd * w[2]));
-      const double c0 = __ldg(fp0 + d), c1 = __ldg(fp1 + d), c2 = __ldg(fp2 + d);
-      e1 += gd * (c1 - c0);
-      e2 += gd * (c2 - c0);
-    }
-    const double r = 1.0 / (k3 * k3);
+    per_pixel_backward<float>(a.grad + pix * a.D, w, ax, ay, bx, by, cx, cy, a.eps_d, a.D,
+                              bwd_feat(a, b, face, fc, 0), bwd_feat(a, b, face, fc, 1),
+                              bwd_feat(a, b, face, fc, 2), bwd_gfeat(a, b, face, fc, 0),
+                              bwd_gfeat(a, b, face, fc, 1), bwd_gfeat(a, b, face, fc, 2),
+                              bwd_gimg(a, b, face, fc, 0), bwd_gimg(a, b, face, fc, 1),
+                              bwd_gimg(a, b, face, fc, 2));
+  }
+}
+
+// ---- double dispatch of the raw op (rasterization_cuda.cu:30-39 with scalar_t = double):
+// unscaled double coordinates and the forward's saved double weights, no image geometry.
+// Same design as above with everything in double: per pixel the centre (s, t) is rebuilt
+// from the weights (:302-303, exact to 1e-16 in double); lanes of a warp that hold the same
+// face sum 6 numbers -- E1 = sum_d g_d (c1 - c0) and E2 = sum_d g_d (c2 - c0), each times
+// (1, s, t) -- and 3 * D feature-gradient terms g_d w_k with shuffles; the group's first
+// lane converts the six sums into the coordinate gradient (the formula is affine in (s, t))
+// and issues one atomicAdd(double) per output element.
+constexpr int kF64Chunk = 4;   // feature channels reduced per round
+
+__global__ void __launch_bounds__(256) raster_backward_f64_kernel(const RasterBwdF64Args a) {
+  const int lane = lane_id(), warp = threadIdx.x >> 5;
+  const int ix = (blockIdx.x << 4) + ((warp & 1) << 3) + (lane & 7);
+  const int iy = (blockIdx.y << 4) + ((warp >> 1) << 2) + (lane >> 3);
+  const int b = blockIdx.z;
+  const bool inimg = ix < a.W && iy < a.H;
+  const long long pix = ((long long)b * a.H + iy) * a.W + ix;
+  int face = -1;
+  if (inimg) face = (int)a.idx[pix];
+  if (!__any_sync(DIBR_FULL_MASK, face >= 0)) return;
+  const unsigned peers = __match_any_sync(DIBR_FULL_MASK, face);
+  const bool leader = (peers & lanemask_lt()) == 0 && face >= 0;
+  const long long gi = (long long)b * a.F + max(face, 0);
+  const double* v = a.img + gi * 6;
+  const double* fp = a.feat + gi * 3 * a.D;
+  const double ax = v[0], ay = v[1], bx = v[2], by = v[3], cx = v[4], cy = v[5];
+  double w[3] = {0., 0., 0.}, ss = 0., tt = 0.;
+  if (face >= 0) {
+    w[0] = a.weights[pix * 3]; w[1] = a.weights[pix * 3 + 1]; w[2] = a.weights[pix * 3 + 2];
+    ss = w[0] * ax + w[1] * bx + w[2] * cx - ax;   // :302-303, :311-312
+    tt = w[0] * ay + w[1] * by + w[2] * cy - ay;
+  }
+  // ---- feature gradient: sum over the group's pixels of g_d w_k, kF64Chunk channels a round
+  double E1 = 0., E2 = 0.;
+  for (int d0 = 0; d0 < a.D; d0 += kF64Chunk) {
+    double acc[3 * kF64Chunk];
 #pragma unroll
-    for (int k = 0; k < 3; k++) {
-      float* gi = bwd_gimg(a, b, face, fc, k);
-      atomicAdd(gi, (float)((e1 * dw1[2 * k] + e2 * dw2[2 * k]) * r));
-      atomicAdd(gi + 1, (float)((e1 * dw1[2 * k + 1] + e2 * dw2[2 * k + 1]) * r));
+    for (int i = 0; i < 3 * kF64Chunk; i++) acc[i] = 0.;
+    if (face >= 0) {
+#pragma unroll
+      for (int dd = 0; dd < kF64Chunk; dd++) {
+        const int d = d0 + dd;
+        if (d < a.D) {
+          const double gd = a.grad[pix * a.D + d];
+          acc[dd] = gd * w[0];
+          acc[kF64Chunk + dd] = gd * w[1];
+          acc[2 * kF64Chunk + dd] = gd * w[2];
+          const double c0 = fp[d];
+          E1 += gd * (fp[a.D + d] - c0);
+          E2 += gd * (fp[2 * a.D + d] - c0);
+        }
+      }
     }
+    reduce_peers<double, 3 * kF64Chunk>(peers, acc, lane);
+    if (leader) {
+      double* gf = a.grad_feat + gi * 3 * a.D;
+#pragma unroll
+      for (int dd = 0; dd < kF64Chunk; dd++) {
+        const int d = d0 + dd;
+        if (d < a.D) {
+          atomicAdd(gf + d, acc[dd]);
+          atomicAdd(gf + a.D + d, acc[kF64Chunk + dd]);
+          atomicAdd(gf + 2 * a.D + d, acc[2 * kF64Chunk + dd]);
+        }
+      }
+    }
+  }
+  // ---- coordinate gradient from the six sums
+  double S[6] = {E1, E1 * ss, E1 * tt, E2, E2 * ss, E2 * tt};
+  reduce_peers<double, 6>(peers, S, lane);
+  if (leader) {
+    const double m = bx - ax, p = by - ay, n = cx - ax, q = cy - ay;
+    double k3 = m * q - n * p;
+    k3 += copysign(a.eps_d, k3);                                            // :319-322
+    const double P0 = S[0], Ps = S[1], Pt = S[2], Q0 = S[3], Qs = S[4], Qt = S[5];
+    const double K1 = Ps * q - n * Pt, K2 = m * Qt - Qs * p;               // sums of e k1, e k2
+    const double dm = -q * K1 + (Qt * k3 - q * K2);
+    const double dn = (-Pt * k3 + p * K1) + p * K2;
+    const double dp = n * K1 + (-Qs * k3 + n * K2);
+    const double dq = (Ps * k3 - m * K1) - m * K2;
+    const double ds = q * k3 * P0 - p * k3 * Q0;
+    const double dt = -n * k3 * P0 + m * k3 * Q0;
+    const double r = 1.0 / (k3 * k3);
+    double* gv = a.grad_img + gi * 6;
+    atomicAdd(gv + 0, -(dm + dn + ds) * r);
+    atomicAdd(gv + 1, -(dp + dq + dt) * r);
+    atomicAdd(gv + 2, dm * r);
+    atomicAdd(gv + 3, dp * r);
+    atomicAdd(gv + 4, dn * r);
+    atomicAdd(gv + 5, dq * r);
   }
 }
 
-// pass 2: moments -> gradients, one thread per (view, face), in double
-__global__ void __launch_bounds__(256) raster_backward_finish_kernel(const RasterBwdArgs a) {
-  pdl_prologue();
-  const long long fbase = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (fbase >= (long long)a.B * a.F) return;
-  float* gf = a.moments + fbase * 3 * a.D;
-  // untouched faces (most of them: back faces, hidden faces) hold zeros and keep them
-  bool any = false;
-  for (int i = 0; i < 3 * a.D; i++) any |= gf[i] != 0.f;
-  if (!any) return;
-  const int b = (int)(fbase / a.F), face = (int)(fbase - (long long)b * a.F);
-  const BwdFace fc = bwd_face(a, b, face, 16.f / ((float)a.W * (float)a.H));
-  if (!fc.regular) return;  // thin / tiny face: pass 1 wrote its gradients directly
-  const double ax = fc.ax, ay = fc.ay;
-  const double m = (double)fc.bx - ax, p = (double)fc.by - ay;
-  const double n = (double)fc.cx - ax, q = (double)fc.cy - ay;
-  const double k3raw = m * q - n * p;
-  const double k3 = k3raw + copysign(a.eps_d, k3raw);       // :321-322
-  const double inv_k3raw = 1.0 / k3raw;
-  // eps of the forward's normalisation (:140-142), in multiplied coordinates
-  const double N = fabs(k3raw) * (double)a.mult * (double)a.mult;
-  const double rho = N / (N + a.eps_d);
-  const float *fp0 = bwd_feat(a, b, face, fc, 0), *fp1 = bwd_feat(a, b, face, fc, 1);
-  const float* fp2 = bwd_feat(a, b, face, fc, 2);
-  float *gf0 = bwd_gfeat(a, b, face, fc, 0), *gf1 = bwd_gfeat(a, b, face, fc, 1);
-  float* gf2 = bwd_gfeat(a, b, face, fc, 2);
-  double P0 = 0., Ps = 0., Pt = 0., Q0 = 0., Qs = 0., Qt = 0.;
-  for (int d = 0; d < a.D; d++) {
-    const double M0 = gf[d], Msl = gf[a.D + d], Mtl = gf[2 * a.D + d];
-    // moments of the reconstructed centre rho * X - a = rho (X - a) + (rho - 1) a
-    const double Ms = rho * Msl + (rho - 1.0) * ax * M0;
-    const double Mt = rho * Mtl + (rho - 1.0) * ay * M0;
-    const double c0 = __ldg(fp0 + d), c1 = __ldg(fp1 + d), c2 = __ldg(fp2 + d);
-    const double e1 = c1 - c0, e2 = c2 - c0;
-    P0 += e1 * M0; Ps += e1 * Ms; Pt += e1 * Mt;
-    Q0 += e2 * M0; Qs += e2 * Ms; Qt += e2 * Mt;
-    // grad_face_features: sum g w_k with the forward's weights w1 = rho (sl q - n tl) / k3raw,
-    // w2 = rho (m tl - sl p) / k3raw, w0 = rho - w1 - w2
-    const double g1 = rho * (Msl * q - n * Mtl) * inv_k3raw;
-    const double g2 = rho * (m * Mtl - Msl * p) * inv_k3raw;
-    if (a.faces) {   // mesh mode: summed into the vertex gradients
-      atomicAdd(gf0 + d, (float)(rho * M0 - g1 - g2));
-      atomicAdd(gf1 + d, (float)g1);
-      atomicAdd(gf2 + d, (float)g2);
-    } else {         // in place: the moment slots become the gradient
-      gf0[d] = (float)(rho * M0 - g1 - g2);
-      gf1[d] = (float)g1;
-      gf2[d] = (float)g2;
-    }
-  }
-  // :324-374 with (1, s, t) replaced by their e1- / e2-weighted sums over the pixels
-  const double K1 = Ps * q - n * Pt, K2 = m * Qt - Qs * p;
-  const double dm = -q * K1 + (Qt * k3 - q * K2);
-  const double dn = (-Pt * k3 + p * K1) + p * K2;
-  const double dp = n * K1 + (-Qs * k3 + n * K2);
-  const double dq = (Ps * k3 - m * K1) - m * K2;
-  const double ds = q * k3 * P0 - p * k3 * Q0;
-  const double dt = -n * k3 * P0 + m * k3 * Q0;
-  const double r = 1.0 / (k3 * k3);
-  const float2 da = make_float2((float)(-(dm + dn + ds) * r), (float)(-(dp + dq + dt) * r));
-  const float2 db = make_float2((float)(dm * r), (float)(dp * r));
-  const float2 dc = make_float2((float)(dn * r), (float)(dq * r));
-  if (a.faces) {
-    atomicAdd(reinterpret_cast<float2*>(bwd_gimg(a, b, face, fc, 0)), da);
-    atomicAdd(reinterpret_cast<float2*>(bwd_gimg(a, b, face, fc, 1)), db);
-    atomicAdd(reinterpret_cast<float2*>(bwd_gimg(a, b, face, fc, 2)), dc);
-  } else {
-    float2* gi = reinterpret_cast<float2*>(a.grad_img + fbase * 6);
-    float2 ga = gi[0], gb = gi[1], gc = gi[2];
-    ga.x += da.x; ga.y += da.y; gb.x += db.x; gb.y += db.y; gc.x += dc.x; gc.y += dc.y;
-    gi[0] = ga; gi[1] = gb; gi[2] = gc;
-  }
+cudaError_t launch_raster_backward_f64(const RasterBwdF64Args& a, cudaStream_t st) {
+  if ((long long)a.B * a.H * a.W == 0) return cudaSuccess;
+  dim3 grid((a.W + 15) / 16, (a.H + 15) / 16, a.B);
+  raster_backward_f64_kernel<<<grid, 256, 0, st>>>(a);
+  return cudaGetLastError();
 }
 
-// Pass 1 (pixel-parallel moments).  The finish pass adds into grad_img with plain
-// read-modify-writes, so it must not overlap another writer of grad_img.
-cudaError_t launch_raster_backward_moments(const RasterBwdArgs& a, cudaStream_t st) {
+cudaError_t launch_raster_backward(const RasterBwdArgs& a, cudaStream_t st) {
   dim3 grid((a.W + 15) / 16, (a.H + 15) / 16, a.B);
   prof_begin(K_RASTER_BWD, st);
   switch (a.D >= 4 ? 4 : a.D) {
@@ -742,19 +822,6 @@ cudaError_t launch_raster_backward_moments(const RasterBwdArgs& a, cudaStream_t 
   }
   prof_end(st);
   return cudaGetLastError();
-}
-
-cudaError_t launch_raster_backward_finish(const RasterBwdArgs& a, cudaStream_t st) {
-  const long long nf = (long long)a.B * a.F;
-  prof_begin(K_RASTER_BWD_FINISH, st);
-  launch_k(raster_backward_finish_kernel, (unsigned)((nf + 255) / 256), 256, 0, st, a);
-  prof_end(st);
-  return cudaGetLastError();
-}
-
-cudaError_t launch_raster_backward(const RasterBwdArgs& a, cudaStream_t st) {
-  cudaError_t e = launch_raster_backward_moments(a, st);
-  return e != cudaSuccess ? e : launch_raster_backward_finish(a, st);
 }
 
 }  // namespace dibr

@@ -93,36 +93,37 @@ __device__ __forceinline__ float pick3(int v, float a, float b, float c) {
 __device__ __forceinline__ int pick3i(int v, int a, int b, int c) {
   return v == 0 ? a : (v == 1 ? b : c);
 }
+__device__ __forceinline__ double pick3d(int v, double a, double b, double c) {
+  return v == 0 ? a : (v == 1 ? b : c);
+}
 
 // dibr_soft_mask_cuda.cu:283-347: gradient of one (pixel, face) pair w.r.t. the face's
 // six UNscaled coordinates, added into g[6] (register array: static indices only).
 // Core: the gradient lands on vertex v1 (always) and v2 (edge case, else -1).
-__device__ __forceinline__ void soft_grad_core(float x0f, float y0f, const float (&X)[6], int edgeid,
-                                               float prob, float allprob, float dLdp,
-                                               float sigmainv, float mult, double inv_e, int& v1,
-                                               float& g1x, float& g1y, int& v2, float& g2x,
-                                               float& g2y) {
-  // Evaluated in double from the fp32 state (pixel centre, scaled coordinates, prob,
-  // soft_mask): what the reference's kernel computes when instantiated for double on that
-  // state.  Its float instantiation loses up to 1e-2 of a face's gradient to the float
-  // differences below; the pair count is small enough for FP64 not to show in the time.
-  (void)inv_e;
-  const double x0 = x0f, y0 = y0f, im = 1.0 / (double)mult;
-  const double dLdz = -1.0 * (double)sigmainv * (double)dLdp * (1.0 - (double)allprob) /
-                      (1.0 - (double)prob + DIBR_SOFT_EPS) * (double)prob;
+// Evaluated in double from the saved state (pixel centre, scaled coordinates, prob,
+// soft_mask): what the reference's kernel computes when instantiated for double on that
+// state.  Its float instantiation loses up to 1e-2 of a face's gradient to float
+// differences; the pair count is small enough for FP64 not to show in the time.
+__device__ __forceinline__ void soft_grad_core_sel(double x0, double y0, const double (&X)[6],
+                                                 int edgeid, double prob, double allprob,
+                                                 double dLdp, double sigmainv, double mult,
+                                                 int& v1, double& g1x, double& g1y, int& v2,
+                                                 double& g2x, double& g2y) {
+  const double im = 1.0 / mult;
+  const double dLdz = -1.0 * sigmainv * dLdp * (1.0 - allprob) / (1.0 - prob + DIBR_SOFT_EPS) * prob;
   v2 = -1;
-  g2x = 0.f;
-  g2y = 0.f;
+  g2x = 0.0;
+  g2y = 0.0;
   if (edgeid >= 3) {
     v1 = edgeid - 3;
-    const double x1 = pick3(v1, X[0], X[2], X[4]), y1 = pick3(v1, X[1], X[3], X[5]);
-    g1x = (float)(dLdz * 2.0 * (x1 - x0) * im);
-    g1y = (float)(dLdz * 2.0 * (y1 - y0) * im);
+    const double x1 = pick3d(v1, X[0], X[2], X[4]), y1 = pick3d(v1, X[1], X[3], X[5]);
+    g1x = dLdz * 2.0 * (x1 - x0) * im;
+    g1y = dLdz * 2.0 * (y1 - y0) * im;
   } else {
     v1 = edgeid;
     v2 = (edgeid + 1) % 3;
-    const double x1 = pick3(v1, X[0], X[2], X[4]), y1 = pick3(v1, X[1], X[3], X[5]);
-    const double x2 = pick3(v2, X[0], X[2], X[4]), y2 = pick3(v2, X[1], X[3], X[5]);
+    const double x1 = pick3d(v1, X[0], X[2], X[4]), y1 = pick3d(v1, X[1], X[3], X[5]);
+    const double x2 = pick3d(v2, X[0], X[2], X[4]), y2 = pick3d(v2, X[1], X[3], X[5]);
     const double A = y2 - y1, B = x1 - x2, C = x2 * y1 - x1 * y2;
     const double up = A * x0 + B * y0 + C;
     const double down = A * A + B * B;
@@ -131,11 +132,24 @@ __device__ __forceinline__ void soft_grad_core(float x0f, float y0f, const float
     const double dzdA = 2.0 * (x0 * up - dissquare * A) * id;
     const double dzdB = 2.0 * (y0 * up - dissquare * B) * id;
     const double dzdC = 2.0 * up * id;
-    g1x = (float)(dLdz * (dzdB - y2 * dzdC) * im);
-    g1y = (float)(dLdz * (x2 * dzdC - dzdA) * im);
-    g2x = (float)(dLdz * (y1 * dzdC - dzdB) * im);
-    g2y = (float)(dLdz * (dzdA - x1 * dzdC) * im);
+    g1x = dLdz * (dzdB - y2 * dzdC) * im;
+    g1y = dLdz * (x2 * dzdC - dzdA) * im;
+    g2x = dLdz * (y1 * dzdC - dzdB) * im;
+    g2y = dLdz * (dzdA - x1 * dzdC) * im;
   }
+}
+
+__device__ __forceinline__ void soft_grad_core(float x0f, float y0f, const float (&X)[6], int edgeid,
+                                               float prob, float allprob, float dLdp,
+                                               float sigmainv, float mult, double inv_e, int& v1,
+                                               float& g1x, float& g1y, int& v2, float& g2x,
+                                               float& g2y) {
+  (void)inv_e;
+  // X[2 * v] with a runtime v would push the array to local memory: select instead
+  const double Xd[6] = {X[0], X[1], X[2], X[3], X[4], X[5]};
+  double a1, b1, a2, b2;
+  soft_grad_core_sel(x0f, y0f, Xd, edgeid, prob, allprob, dLdp, sigmainv, mult, v1, a1, b1, v2, a2, b2);
+  g1x = (float)a1; g1y = (float)b1; g2x = (float)a2; g2y = (float)b2;
 }
 
 __device__ __forceinline__ void soft_grad(float x0, float y0, const float (&X)[6], int edgeid,
@@ -695,40 +709,95 @@ softmask_pairs_grad_kernel(const SoftArgs a, const Plan p) {
 }
 
 // ---------------------------------------------------------------------------
-// Dense-state backward: the raw _C op (dibr_soft_mask_cuda.cu:230-353), one thread per
-// pixel reading the per-pixel lists the dense forward stored.  Only the reference-shaped
-// shim uses it; the autograd path uses the recompute form above.
+// Dense-state backward: the raw _C op (dibr_soft_mask_cuda.cu:230-353) on the per-pixel
+// lists (B, H, W, K) the dense forward stored; float and double (the reference dispatches
+// both).  Only the reference-shaped shim uses it; the autograd path runs over the pair
+// buffer.  Mapping: one warp per 8x4-pixel region; the region's (pixel, slot) pairs are
+// dealt out evenly over the lanes whatever pixel they belong to (an exclusive scan of the
+// per-pixel slot counts, owner found by a search over the lanes), each pair takes the
+// gradient arithmetic in double, and lanes that hit the same (face, vertex) are grouped with
+// __match_any_sync and summed with shuffles, so that ONE atomic per (face, vertex) and step
+// leaves the warp.
 // ---------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ void add_grouped(T* base, long long key, bool has, T gx, T gy,
+                                            int lane) {
+  // lanes with the same key (the same (face, vertex) slot) sum their (gx, gy); lanes
+  // without a contribution get unique keys
+  const long long k = has ? key : -1ll - lane;
+  const unsigned peers = __match_any_sync(DIBR_FULL_MASK, k);
+  T sx = gx, sy = gy;
+  unsigned rest = peers & ~(1u << lane);
+  // at most a handful of lanes share a key: walk the peer set (all lanes iterate together)
+  while (__any_sync(DIBR_FULL_MASK, rest != 0)) {
+    const int src = rest ? __ffs(rest) - 1 : lane;
+    const T ox = __shfl_sync(DIBR_FULL_MASK, gx, src), oy = __shfl_sync(DIBR_FULL_MASK, gy, src);
+    if (rest) { sx += ox; sy += oy; rest &= rest - 1; }
+  }
+  if (has && (peers & lanemask_lt()) == 0 && (sx != (T)0 || sy != (T)0)) {
+    atomicAdd(base + key * 2, sx);
+    atomicAdd(base + key * 2 + 1, sy);
+  }
+}
 
-__global__ void __launch_bounds__(256) softmask_dense_backward_kernel(const SoftDenseBwdArgs a) {
+template <typename T>
+__global__ void __launch_bounds__(256) softmask_dense_backward_kernel(const SoftDenseBwdArgsT<T> a) {
   pdl_prologue();
-  const long long npix = (long long)a.B * a.H * a.W;
+  const int lane = lane_id();
+  const int nrx = (a.W + 7) >> 3, nry = (a.H + 3) >> 2;
+  const long long nreg = (long long)a.B * nrx * nry;
   const Grid g = make_grid(a.mult, a.W, a.H);
-  for (long long pix = (long long)blockIdx.x * blockDim.x + threadIdx.x; pix < npix;
-       pix += (long long)gridDim.x * blockDim.x) {
-    if (a.sel[pix] >= 0) continue;
-    const int ix = (int)(pix % a.W), iy = (int)((pix / a.W) % a.H), b = (int)(pix / ((long long)a.W * a.H));
-    const float x0 = pix_x(g, ix), y0 = pix_y(g, iy);
-    const float dLdp = a.grad_mask[pix], allprob = a.mask[pix];
-    for (int kid = 0; kid < a.K; kid++) {
-      const long long o = pix * a.K + kid;
-      const int f = (int)a.cidx[o];
-      if (f < 0) break;
-      const float* ip = a.img + ((long long)b * a.F + f) * 6;
-      const float X[6] = {ip[0], ip[1], ip[2], ip[3], ip[4], ip[5]};
-      float gv[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      const int eid = (int)a.type[o] - 1;
-      double inv_e = 0.0;
-      if (eid < 3) {
-        const int v2 = (eid + 1) % 3;
-        inv_e = edge_inv(pick3(eid, X[0], X[2], X[4]), pick3(eid, X[1], X[3], X[5]),
-                         pick3(v2, X[0], X[2], X[4]), pick3(v2, X[1], X[3], X[5]));
-      }
-      soft_grad(x0, y0, X, eid, a.prob[o], allprob, dLdp, a.sigmainv, a.mult, inv_e, gv);
-      float* gp = a.grad_img + ((long long)b * a.F + f) * 6;
+  for (long long reg = (long long)blockIdx.x * 8 + (threadIdx.x >> 5); reg < nreg;
+       reg += (long long)gridDim.x * 8) {
+    const int b = (int)(reg / (nrx * nry)), rr = (int)(reg - (long long)b * nrx * nry);
+    const int ix = (rr % nrx) * 8 + (lane & 7), iy = (rr / nrx) * 4 + (lane >> 3);
+    const bool inimg = ix < a.W && iy < a.H;
+    const long long pix = ((long long)b * a.H + min(iy, a.H - 1)) * a.W + min(ix, a.W - 1);
+    int cnt = 0;
+    double dLdp = 0.0, allprob = 0.0;
+    if (inimg && a.sel[pix] < 0) {
+      while (cnt < a.K && a.cidx[pix * a.K + cnt] >= 0) cnt++;   // slots are filled in order (:271-276)
+      dLdp = (double)a.grad_mask[pix];
+      allprob = (double)a.mask[pix];
+    }
+    int total;
+    int incl = cnt;
 #pragma unroll
-      for (int i = 0; i < 6; i++)
-        if (gv[i] != 0.f) atomicAdd(gp + i, gv[i]);
+    for (int d = 1; d < 32; d <<= 1) {
+      const int t = __shfl_up_sync(DIBR_FULL_MASK, incl, d);
+      if (lane >= d) incl += t;
+    }
+    const int off = incl - cnt;
+    total = __shfl_sync(DIBR_FULL_MASK, incl, 31);
+    const double x0 = (double)pix_x(g, ix), y0 = (double)pix_y(g, iy);   // float products (:262-263)
+    for (int i0 = 0; i0 < total; i0 += 32) {
+      const int i = i0 + lane;
+      const bool act = i < total;
+      int l = 0;   // owner pixel lane: the largest l with off[l] <= i
+#pragma unroll
+      for (int st = 16; st > 0; st >>= 1) {
+        const int o = __shfl_sync(DIBR_FULL_MASK, off, l + st);
+        if (o <= i) l += st;
+      }
+      const int h = i - __shfl_sync(DIBR_FULL_MASK, off, l);
+      const long long opix = __shfl_sync(DIBR_FULL_MASK, pix, l);
+      const double ox0 = __shfl_sync(DIBR_FULL_MASK, x0, l), oy0 = __shfl_sync(DIBR_FULL_MASK, y0, l);
+      const double odL = __shfl_sync(DIBR_FULL_MASK, dLdp, l), oap = __shfl_sync(DIBR_FULL_MASK, allprob, l);
+      int v1 = 0, v2 = -1;
+      double g1x = 0., g1y = 0., g2x = 0., g2y = 0.;
+      long long fb = 0;
+      if (act) {
+        const long long o = opix * a.K + h;
+        const int f = (int)a.cidx[o];
+        fb = (long long)b * a.F + f;
+        const T* ip = a.img + fb * 6;
+        const double X[6] = {(double)ip[0], (double)ip[1], (double)ip[2], (double)ip[3],
+                             (double)ip[4], (double)ip[5]};
+        soft_grad_core_sel(ox0, oy0, X, (int)a.type[o] - 1, (double)a.prob[o], oap, odL,
+                           (double)a.sigmainv, (double)a.mult, v1, g1x, g1y, v2, g2x, g2y);
+      }
+      add_grouped<T>(a.grad_img, fb * 3 + v1, act, (T)g1x, (T)g1y, lane);
+      add_grouped<T>(a.grad_img, fb * 3 + max(v2, 0), act && v2 >= 0, (T)g2x, (T)g2y, lane);
     }
   }
 }
@@ -794,14 +863,21 @@ cudaError_t launch_softmask(const SoftArgs& a, int mode, const Plan& p, cudaStre
   }
 }
 
-cudaError_t launch_softmask_dense_backward(const SoftDenseBwdArgs& a, cudaStream_t st) {
-  const long long npix = (long long)a.B * a.H * a.W;
-  if (npix == 0) return cudaSuccess;
-  const int blocks = (int)min((npix + 255) / 256, (long long)148 * 16);
+template <typename T>
+static cudaError_t launch_dense_backward_t(const SoftDenseBwdArgsT<T>& a, cudaStream_t st) {
+  const long long nreg = (long long)a.B * ((a.W + 7) >> 3) * ((a.H + 3) >> 2);
+  if (nreg == 0) return cudaSuccess;
+  const int blocks = (int)min((nreg + 7) / 8, (long long)148 * 16);
   prof_begin(K_SOFT_BWD_DENSE, st);
-  launch_k(softmask_dense_backward_kernel, blocks, 256, 0, st, a);
+  launch_k(softmask_dense_backward_kernel<T>, blocks, 256, 0, st, a);
   prof_end(st);
   return cudaGetLastError();
+}
+cudaError_t launch_softmask_dense_backward(const SoftDenseBwdArgs& a, cudaStream_t st) {
+  return launch_dense_backward_t<float>(a, st);
+}
+cudaError_t launch_softmask_backward_f64(const SoftBwdF64Args& a, cudaStream_t st) {
+  return launch_dense_backward_t<double>(a, st);
 }
 
 }  // namespace dibr

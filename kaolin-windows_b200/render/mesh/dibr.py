@@ -304,15 +304,13 @@ class DibrRasterizationMeshB200(Function):
         lib = _lib.lib()
         grad_vimg = torch.empty_like(vimg)      # zero-filled by the call
         grad_vfeat = torch.empty_like(vfeat)
-        scratch = torch.empty(int(lib.dibr_mesh_moment_bytes(B, F, D)), dtype=torch.uint8,
-                              device=vimg.device)
         g = None if grad_features is None else _prep(grad_features, "grad_interpolated_features")
         gm = None if grad_soft_mask is None else _prep(grad_soft_mask, "grad_soft_mask")
         with torch.cuda.device(vimg.device):
             rc = lib.dibr_render_mesh_bwd(
                 B, V, F, H, W, D, _ptr(g), _ptr(gm), _ptr(idx), _ptr(vimg), _ptr(faces32),
                 _ptr(vfeat), shared, _ptr(mask), sigmainv, margin, knum, multiplier, eps,
-                _ptr(grad_vimg), _ptr(grad_vfeat), _ptr(scratch), _ptr(ws), ws.numel(), cap_r,
+                _ptr(grad_vimg), _ptr(grad_vfeat), _ptr(ws), ws.numel(), cap_r,
                 cap_s, cap_p, _stream(vimg.device))
         _lib.check(rc, "dibr_render_mesh_bwd")
         return (None, None, None, grad_vimg, None, grad_vfeat, None, None, None, None, None, None)

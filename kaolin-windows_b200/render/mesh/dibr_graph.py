@@ -60,6 +60,7 @@ class _Entry:
         if not (_workspace.USE_PAIRS and 0 < params[2] <= _workspace.PAIR_MAX_K):
             self.caps[2] = 0
         self.slot = torch.full((4,), -1, dtype=torch.int64).pin_memory()
+        self.slot_np = self.slot.numpy()      # same memory: the host polls without torch overhead
         self.ws = None
         self.graph = None
         self.bwd_graphs = collections.OrderedDict()
@@ -92,28 +93,33 @@ class _Entry:
         _lib.check(rc, "dibr_render_fwd")
 
     def _poll(self):
-        slot = self.slot
-        t0 = time.perf_counter()
+        slot = self.slot_np
+        spins = 0
+        t0 = None
         while True:
             nr, ns = int(slot[0]), int(slot[1])
             if nr >= 0 and ns >= 0:
                 return nr, ns
-            if time.perf_counter() - t0 > 120.0:
-                torch.cuda.synchronize(self.dev)
-                nr, ns = int(slot[0]), int(slot[1])
-                if nr < 0 or ns < 0:
-                    raise RuntimeError("libdibr_b200: list-size report never arrived")
-                return nr, ns
+            spins += 1
+            if spins & 0xfff == 0:
+                if t0 is None:
+                    t0 = time.perf_counter()
+                elif time.perf_counter() - t0 > 120.0:
+                    torch.cuda.synchronize(self.dev)
+                    nr, ns = int(slot[0]), int(slot[1])
+                    if nr < 0 or ns < 0:
+                        raise RuntimeError("libdibr_b200: list-size report never arrived")
+                    return nr, ns
 
     def forward(self, capture_ok):
         # pair buffer: what the previous call of this entry wanted (long arrived)
-        want = max(int(self.slot[2]), int(self.slot[3]))
+        want = max(int(self.slot_np[2]), int(self.slot_np[3]))
         if self.caps[2] > 0 and want > self.caps[2]:
             self.caps[2] = min(int(want * 1.25) + 1024, 1 << 23)
             self._alloc_ws()
         with torch.cuda.device(self.dev):
             for _attempt in range(4):
-                self.slot.fill_(-1)
+                self.slot_np[:] = -1
                 if self.graph is not None:
                     self.graph.replay()
                 else:
@@ -266,12 +272,11 @@ class _MeshEntry(_Entry):
         self.mask = torch.empty((B, H, W), dtype=torch.float32, device=dev)
         self.grad_img = torch.empty(tuple(vimg.shape), dtype=torch.float32, device=dev)
         self.grad_feat = torch.empty(tuple(vfeat.shape), dtype=torch.float32, device=dev)
-        self.scratch = torch.empty(int(_lib.lib().dibr_mesh_moment_bytes(B, self.F, D)),
-                                   dtype=torch.uint8, device=dev)
         self.caps = _workspace.initial_caps(B, self.F, H, W, params[2])
         if not (_workspace.USE_PAIRS and 0 < params[2] <= _workspace.PAIR_MAX_K):
             self.caps[2] = 0
         self.slot = torch.full((4,), -1, dtype=torch.int64).pin_memory()
+        self.slot_np = self.slot.numpy()
         self.ws = None
         self.graph = None
         self.bwd_graphs = collections.OrderedDict()
@@ -296,7 +301,7 @@ class _MeshEntry(_Entry):
             self.B, self.V, self.F, self.H, self.W, self.D, _ptr(g_out), _ptr(g_mask),
             _ptr(self.idx), self.vimgp, self.facesp, self.vfeatp, self.shared, _ptr(self.mask),
             sigmainv, margin, knum, multiplier, eps, _ptr(self.grad_img), _ptr(self.grad_feat),
-            _ptr(self.scratch), self.ws.data_ptr(), self.ws_bytes, cap_r, cap_s, cap_p,
+            self.ws.data_ptr(), self.ws_bytes, cap_r, cap_s, cap_p,
             _stream(self.dev))
         _lib.check(rc, "dibr_render_mesh_bwd")
 
