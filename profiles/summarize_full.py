@@ -35,7 +35,7 @@ EXTRA_NCU_METRICS = ",".join(METRICS[-7:])
 BENCH_NAMES = [
     ("bin_walk_kernel<0>", "bin_count"), ("bin_walk_kernel<false>", "bin_count"),
     ("bin_scan", "bin_scan"), ("bin_walk_kernel", "bin_fill"),
-    ("raster_forward", "raster_fwd"), ("raster_backward_finish", "raster_bwd_finish"),
+    ("raster_forward", "raster_fwd"),
     ("raster_backward", "raster_bwd"), ("softmask_gather", "softmask_gather"),
     ("softmask_pairs_eval", "softmask_eval"), ("softmask_pairs_grad", "softmask_grad"),
 ]
