@@ -238,7 +238,7 @@ class VertexGradExchange:
     mapped (or DIBR_B200_EXCHANGE=nccl).  Copies + kernel replay as one CUDA graph once the
     same gradient addresses are seen again.  Returns views of a static result buffer."""
 
-    MAX_GRAPHS = 4
+    MAX_GRAPHS = 16      # gradient tensors come out of the caching allocator: a few address sets
 
     def __init__(self, group=None):
         self.group = group
