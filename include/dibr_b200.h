@@ -129,6 +129,38 @@ DIBR_API int dibr_rasterize_fwd(int batch, int num_faces, int height, int width,
                        int64_t raster_capacity, int64_t* needed_host, void* stream);
 
 /*
+ * rasterize forward WITHOUT any allocation.  No counterpart in the reference: added
+ * for callers that cannot allocate device memory (code under
+ * CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc).  Same inputs,
+ * outputs and arithmetic as dibr_rasterize_fwd in its plain mode (unscaled
+ * face_vertices_image, boxes computed; valid_faces / face_normals_z optional), but the
+ * scratch workspace lives in a file-scope device array of DIBR_STATIC_SCRATCH_BYTES inside
+ * the library (every GPU that loads the library holds it until exit); the call makes no
+ * cudaMalloc / cudaFree and no allocating library call.  The caller still passes inputs and
+ * outputs.
+ *  - Sizes whose tables plus 2 list entries per face-view (+ 4096) do not fit are rejected
+ *    with DIBR_E_INVALID (the message names the bytes needed and the maximum): use
+ *    dibr_rasterize_fwd with a caller-allocated workspace for those.
+ *  - The list capacity is everything that fits: (DIBR_STATIC_SCRATCH_BYTES - 512 -
+ *    dibr_workspace_fixed_bytes(batch, num_faces, height, width)) / 48 entries (4-byte entries
+ *    with DIBR_B200_RASTER_REC=0).  needed_host as in the workspace protocol: NULL = one
+ *    internal stream synchronisation and DIBR_E_WORKSPACE if the data needed more entries;
+ *    else int64[2] pinned memory written asynchronously, needed_host[0] > capacity means the
+ *    outputs are invalid.
+ *  - ALL calls share the one array, which keeps the previous call's contents: each call
+ *    clears what must start at zero itself, but calls that overlap on the same GPU (two
+ *    streams, two threads) race -- serialise them.
+ */
+#define DIBR_STATIC_SCRATCH_BYTES (16 * 1024 * 1024)
+DIBR_API int dibr_rasterize_fwd_static(int batch, int num_faces, int height, int width,
+                              int feat_dim, const float* face_vertices_z,
+                              const float* face_vertices_image, const float* face_features,
+                              const uint8_t* valid_faces, const float* face_normals_z,
+                              float multiplier, float eps, int64_t* selected_face_idx,
+                              float* interpolated_features, float* output_weights,
+                              int64_t* needed_host, void* stream);
+
+/*
  * rasterize backward.  Replaces rasterize_backward_cuda (rasterization.cpp:106-168,
  * rasterization_cuda.cu:238-402).  face_vertices_image is UNscaled (B, F, 3, 2).
  * output_weights may be NULL: the weights are then recomputed bit-identically from

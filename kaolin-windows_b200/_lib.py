@@ -29,6 +29,8 @@ SIGNATURES = {
     "dibr_workspace_bytes_for": (_i64, [_i, _i, _i, _i, _i64, _i64, _i64, _i]),
     "dibr_rasterize_fwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp, _f, _f,
                                 _vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp]),
+    "dibr_rasterize_fwd_static": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp,
+                                       _vp, _vp, _vp]),
     "dibr_rasterize_bwd": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _f, _f, _vp, _vp, _vp]),
     "dibr_softmask_fwd": (_i, [_i, _i, _i, _i, _vp, _i, _vp, _vp, _f, _f, _i, _f, _vp, _vp, _vp, _vp,
                                _vp, _i64, _i64, _i64, _i64, _vp, _vp]),

@@ -792,3 +792,83 @@ extern "C" int dibr_render_mesh_bwd(int B, int V, int F, int H, int W, int D,
   }
   return DIBR_OK;
 }
+
+// ------------------------------------------------------------- no-allocation variant
+// dibr_rasterize_fwd with its scratch workspace (binning tables + the per-bin face lists) in
+// a file-scope device array instead of caller memory, for callers that cannot allocate
+// (CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc);
+// it has no counterpart in the reference.  Every GPU that
+// loads the library holds DIBR_STATIC_SCRATCH_BYTES of it until exit.  All calls share the
+// array (overlapping calls on one GPU race); each call re-zeroes the parts that must start
+// at zero (run_binning's memsets), the rest is overwritten before it is read.
+static __device__ __align__(256) unsigned char g_static_scratch[DIBR_STATIC_SCRATCH_BYTES];
+
+// Device address of the array on the CURRENT device.  In host code `g_static_scratch` is
+// only a stand-in for the symbol, never a device address: the address comes from
+// cudaGetSymbolAddress, once per device, with that device current.
+static int static_scratch_ptr(void** out) {
+  constexpr int kMaxDevices = 64;
+  static void* ptrs[kMaxDevices] = {};
+  static std::mutex mu;
+  int dev = 0;
+  DIBR_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxDevices) return fail(DIBR_E_INVALID, "device index %d not supported", dev);
+  std::lock_guard<std::mutex> lk(mu);
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    DIBR_CUDA(cudaGetSymbolAddress(&p, g_static_scratch));
+    if (!p || ((uintptr_t)p & 255) != 0)
+      return fail(DIBR_E_CUDA, "static scratch array has no usable device address");
+    ptrs[dev] = p;
+  }
+  *out = ptrs[dev];
+  return DIBR_OK;
+}
+
+extern "C" int dibr_rasterize_fwd_static(int B, int F, int H, int W, int D, const float* z,
+                                         const float* img, const float* feat,
+                                         const uint8_t* valid, const float* normal_z,
+                                         float multiplier, float eps, int64_t* out_idx,
+                                         float* out_feat, float* out_w, int64_t* needed_host,
+                                         void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  Plan p;
+  int rc = make_plan(B, F, H, W, p, multiplier);
+  if (rc) return rc;
+  // sizes first: the fixed tables plus room for 2 list entries per face-view (+ 4096) must
+  // fit into the array; whatever is left beyond that is list capacity as well
+  const int64_t want = 2 * (int64_t)B * F + 4096;
+  const int64_t room = ((int64_t)DIBR_STATIC_SCRATCH_BYTES - p.fixed_bytes - 512) / raster_entry_bytes();
+  if (room < want)
+    return fail(DIBR_E_INVALID,
+                "dibr_rasterize_fwd_static: batch %d x %d faces at %dx%d needs %lld bytes of "
+                "scratch, the static array holds DIBR_STATIC_SCRATCH_BYTES = %lld; use "
+                "dibr_rasterize_fwd with a caller-allocated workspace",
+                B, F, H, W, (long long)(p.fixed_bytes + 512 + want * raster_entry_bytes()),
+                (long long)DIBR_STATIC_SCRATCH_BYTES);
+  if ((rc = check_common(multiplier))) return rc;
+  if (D < 0) return fail(DIBR_E_INVALID, "feat_dim < 0");
+  if (B == 0) return DIBR_OK;
+  if (!out_idx || (!out_feat && D > 0)) return fail(DIBR_E_INVALID, "null output");
+  if (F > 0 && (!z || !img || (!feat && D > 0))) return fail(DIBR_E_INVALID, "null input");
+  if (valid && normal_z) return fail(DIBR_E_INVALID, "valid_faces and face_normals_z both given");
+  void* ws = nullptr;
+  if ((rc = static_scratch_ptr(&ws))) return rc;
+  const int64_t cap_r = room < kMaxListEntries ? room : kMaxListEntries;
+  Workspace w;
+  if ((rc = bind_workspace(p, ws, DIBR_STATIC_SCRATCH_BYTES, cap_r, 0, w))) return rc;
+  BinJobs jobs;
+  jobs.j[0] = face_source(img, nullptr, valid, normal_z, nullptr, F, multiplier, 0.f, 0);
+  attach(jobs.j[0], p, w, 0);
+  jobs.j[0].rec = w.rec; jobs.j[0].z = z;
+  jobs.j[1] = jobs.j[0];
+  const int kinds[1] = {0};
+  if ((rc = run_binning(p, w, jobs, kinds, 1, needed_host, st))) return rc;
+  RasterArgs a;
+  memset(&a, 0, sizeof(a));
+  a.job = jobs.j[0]; a.rec = jobs.j[0].rec; a.z = z; a.feat = feat; a.D = D; a.eps_d = (double)eps;
+  a.out_idx = out_idx; a.out_feat = out_feat; a.out_w = out_w;
+  a.block_uncovered = (int*)(w.base + p.off_flags);
+  DIBR_CUDA(launch_raster_forward(a, p, st));
+  return DIBR_OK;
+}
