@@ -286,16 +286,15 @@ def main():
         """One step from the mesh; returns (loss terms' outputs, vertex grad, feature grad)."""
         v = (job["verts"] if verts is None else verts).detach().requires_grad_(True)
         f = (job["vfeat"] if vfeat is None else vfeat).detach().requires_grad_(True)
+        # exchange=: the gradients come back summed over all ranks -- the path's only exchange
+        # (N > 1); with graphs it is the last node of the backward graph
         out, mask, idx = mesh_api(job["H"], job["W"], v, job["faces32"], f, job["proj"],
                                   job["rot"], job["trans"], sigmainv=SIGMAINV, boxlen=BOXLEN,
-                                  knum=KNUM, cuda_graph=graph)
+                                  knum=KNUM, cuda_graph=graph, exchange=exchanger)
         # d loss / d out = G1, d loss / d mask = G2: the backward of the loss without timing
         # torch's multiply / reduce kernels, which are not part of the path
         torch.autograd.backward((out, mask), (job["g1"], job["g2"]))
-        gv, gf = v.grad, f.grad
-        if exchanger is not None:
-            gv, gf = exchanger(gv, gf)       # the path's only exchange (N > 1)
-        return out, mask, gv, gf
+        return out, mask, v.grad, f.grad
 
     def time_steps(fn, steps, warm, coll=True):
         """ms per step: CUDA events per step, L2 flushed in between, max over ranks
@@ -337,9 +336,11 @@ def main():
     exchange_check = None
     if world > 1:
         _, _, gv, gf = mesh_step(job, None, graph=False)
-        mine = torch.cat([t.reshape(-1) for t in exchanger(gv, gf)]).clone()
         want = torch.cat([gv.reshape(-1), gf.reshape(-1)]).clone()
         dist.all_reduce(want, op=dist.ReduceOp.SUM)
+        for _ in range(3):       # eager first, then captured, then replayed: the timed form
+            _, _, xv, xf = mesh_step(job, exchanger)
+        mine = torch.cat([xv.reshape(-1), xf.reshape(-1)]).clone()
         rel = (mine - want).abs().max() / want.abs().max().clamp_min(1e-30)
         bits = mine.contiguous().view(torch.int32).to(torch.int64)
         wts = torch.arange(bits.numel(), device=dev, dtype=torch.int64) % 65521 + 1
@@ -350,8 +351,10 @@ def main():
         exchange_check = {"mode": exchanger.mode, "max_rel_diff": float(rel.item()),
                           "bit_identical_across_ranks": all(torch.equal(e, every[0]) for e in every),
                           "floats": int(mine.numel()),
-                          "against": "one flat NCCL all_reduce(SUM) of the same gradients"}
-        del mine, want, gv, gf
+                          "folded_into_backward_graph": bool(GRAPH and exchanger.mode == "peer"),
+                          "against": "one flat NCCL all_reduce(SUM) of this rank's un-exchanged "
+                                     "gradients (eager run of the same step)"}
+        del mine, want, gv, gf, xv, xf
         barrier()
 
     # ---- timed: exactly K steps, one CUDA-event pair per step, L2 flushed in between
@@ -468,12 +471,15 @@ def main():
         # scaling) + the vertex-gradient all-reduce
         lo3, hi3 = kal.parallel.shard_range(64, rank, world)
         j3 = make_mesh_job("cfg3_200k_64x1024", 64, lo3, hi3)
-        ms3 = time_steps(lambda: mesh_step(j3, exchanger), 5, 3)
+        ex3 = kal.parallel.VertexGradExchange() if world > 1 else None   # its own buffers
+        ms3 = time_steps(lambda: mesh_step(j3, ex3), 5, 3)
         extra["cfg3_strong"] = {"views_total": 64, "views_per_rank": hi3 - lo3, "H": 1024, "W": 1024,
                                 "faces": int(j3["faces32"].shape[0]), "ms_per_step": ms3,
                                 "Mpixels_per_s": 64 * 1024 * 1024 / (ms3 * 1e-3) / 1e6,
                                 "exchange_floats": int(j3["verts"].numel() + j3["vfeat"].numel())}
-        del j3
+        if ex3 is not None:
+            ex3.release()
+        del j3, ex3
         # cfg 5: 256 distinct 2k-face meshes at 128^2, 256/N per rank, no collective
         lo5, hi5 = kal.parallel.shard_range(256, rank, world)
         j5 = make_mesh_job("cfg5_256x2k_128", 256, lo5, hi5, shared=False)

@@ -289,14 +289,44 @@ class VertexGradExchange:
         self.graphs.clear()
         self.seen.clear()
 
+    # ---- folding the exchange into the producer's own CUDA graph (render.mesh.dibr_graph):
+    # the backward kernels write the gradients straight into this rank's buffer of the
+    # symmetric allocation -- no copy -- and the all-reduce kernel is the graph's last node.
+    def prepare(self, n, dev):
+        """Set up for messages of n floats; returns True when the exchange can be captured
+        (peer-memory mode).  Every rank must call it at the same point."""
+        n = (int(n) + 3) // 4 * 4
+        if self.flat is None or self.n < n:
+            self._setup(n, dev)
+        return self.mode == "peer"
+
+    def issue_wait(self):
+        """(capturable) wait until every peer has read this rank's buffer of the previous
+        exchange; the buffer may be overwritten afterwards."""
+        import ctypes
+        from . import _lib
+        pb = self.peer
+        st = ctypes.c_void_p(torch.cuda.current_stream(self.flat.device).cuda_stream)
+        _lib.check(_lib.lib().dibr_peer_signal(pb.rank, pb.world, pb.pads, 1, st), "dibr_peer_signal")
+
+    def issue_allreduce(self):
+        """(capturable) result = sum over ranks of their buffers."""
+        import ctypes
+        from . import _lib
+        pb = self.peer
+        st = ctypes.c_void_p(torch.cuda.current_stream(self.flat.device).cuda_stream)
+        _lib.check(_lib.lib().dibr_peer_allreduce(
+            pb.rank, pb.world, pb.bufs, pb.pads, pb.n, ctypes.c_void_p(pb.out.data_ptr()),
+            ctypes.c_void_p(pb.sync.data_ptr()), st), "dibr_peer_allreduce")
+
     def __call__(self, *grads):
         grads = [g.contiguous() for g in grads]
         if not grads[0].is_cuda:
             raise RuntimeError("VertexGradExchange needs CUDA tensors (there is no CPU path)")
         dev = grads[0].device
         n = sum(g.numel() for g in grads)
-        if self.flat is None or self.n != n:
-            self._setup(n, dev)
+        if self.flat is None or self.n < n:      # (a larger buffer is reused: the padding is
+            self._setup(n, dev)                  #  reduced along, nobody reads it)
         key = tuple((g.data_ptr(), tuple(g.shape)) for g in grads)
         with torch.cuda.device(dev):
             graph = self.graphs.get(key)
@@ -324,3 +354,21 @@ class VertexGradExchange:
             out.append(self.result[off:off + k].view_as(g))
             off += k
         return out
+
+
+class SumGradsAcrossRanks(torch.autograd.Function):
+    """Identity on (vertices, vertex_features) whose backward SUM-all-reduces both gradients
+    through a VertexGradExchange: the shared mesh's gradients come back already summed over
+    all ranks."""
+
+    @staticmethod
+    def forward(ctx, exchange, vertices, vertex_features):
+        ctx.exchange = exchange
+        return vertices.view_as(vertices), vertex_features.view_as(vertex_features)
+
+    @staticmethod
+    def backward(ctx, gv, gf):
+        if gv is None or gf is None:
+            raise RuntimeError("SumGradsAcrossRanks: both gradients are exchanged together")
+        rv, rf = ctx.exchange(gv, gf)
+        return None, rv.clone(), rf.clone()

@@ -439,7 +439,7 @@ def _camera_batch(camera_rot, camera_trans, camera_transform):
 def dibr_rasterization_vertices(height, width, vertices, faces, vertex_features, camera_proj,
                                 camera_rot=None, camera_trans=None, camera_transform=None,
                                 valid_faces=None, sigmainv=7000, boxlen=0.02, knum=30,
-                                multiplier=None, eps=None, cuda_graph=False):
+                                multiplier=None, eps=None, cuda_graph=False, exchange=None):
     r"""prepare_vertices + dibr_rasterization in one call (extension; not in the reference):
     world-space vertices and cameras in, images out, vertex-level gradients back.
 
@@ -450,6 +450,13 @@ def dibr_rasterization_vertices(height, width, vertices, faces, vertex_features,
     gradients are summed over the views.  Camera parameters receive no gradient (use
     ``prepare_vertices`` + ``dibr_rasterization_mesh`` for that).  ``cuda_graph=True`` replays
     the whole forward and the whole backward as one graph launch each.
+
+    ``exchange`` (a ``parallel.VertexGradExchange``; multi-GPU, one process per GPU, each
+    rendering its shard of the views of ONE shared mesh): the gradients of ``vertices`` and
+    ``vertex_features`` -- both with a leading dimension of 1 -- come back already summed
+    over all ranks, the path's only exchange.  With ``cuda_graph=True`` and peer-memory mode
+    the backward kernels write straight into the exchange buffer and the all-reduce kernel is
+    the last node of the backward graph: no copy, no extra launch.
 
     Returns:
         (torch.Tensor or tuple, torch.Tensor, torch.LongTensor): as dibr_rasterization.
@@ -463,13 +470,29 @@ def dibr_rasterization_vertices(height, width, vertices, faces, vertex_features,
         raise TypeError("dibr_rasterization_vertices takes float32 tensors")
     faces32 = _prep_faces(faces, vertices.shape[1])
     res = None
+    fold = False
+    if exchange is not None:
+        if vertices.shape[0] != 1 or _features.shape[0] != 1:
+            raise RuntimeError("exchange= needs ONE shared mesh: vertices (1, V, 3) and "
+                               "vertex_features (1, V, D)")
+        # every rank decides the same way (same shapes, same mode)
+        pad = (vertices.numel() + 63) // 64 * 64
+        fold = cuda_graph and exchange.prepare(pad + _features.numel(), vertices.device)
+    if exchange is not None and not fold:
+        # not folded into a graph: an identity node whose backward sums both gradients
+        from ...parallel import SumGradsAcrossRanks
+        vertices, _features = SumGradsAcrossRanks.apply(exchange, vertices, _features)
     if cuda_graph:
         from .dibr_graph import graphed_dibr_rasterization_vertices
         res = graphed_dibr_rasterization_vertices(
             height, width, vertices, faces32, _features, camera_proj, camera_rot, camera_trans,
             camera_transform, valid_faces, batch,
             (float(sigmainv), _margin(boxlen, _multiplier), int(knum), float(_multiplier),
-             float(_eps)))
+             float(_eps)), exchange if fold else None)
+    if res is None and fold:
+        # first sighting of a problem whose graph will hold the exchange: eager this once
+        from ...parallel import SumGradsAcrossRanks
+        vertices, _features = SumGradsAcrossRanks.apply(exchange, vertices, _features)
     if res is None:
         vcam, vimg = VertexTransformB200.apply(vertices, camera_proj, camera_rot, camera_trans,
                                                camera_transform, batch)

@@ -383,8 +383,9 @@ class _VertexEntry(_MeshEntry):
     graph launch each way for the whole step."""
 
     def __init__(self, H, W, vertices, faces32, vfeat, proj, rot, trans, tf, valid, batch,
-                 params):
+                 params, exchange=None):
         dev = vertices.device
+        self.exchange = exchange      # VertexGradExchange in peer mode, or None
         V = vertices.shape[1]
         self.vertsp, self.projp = vertices.data_ptr(), proj.data_ptr()
         self.rotp = None if rot is None else rot.data_ptr()
@@ -395,6 +396,14 @@ class _VertexEntry(_MeshEntry):
         self.vimg = torch.empty((batch, V, 2), dtype=torch.float32, device=dev)
         self.grad_verts = torch.empty(tuple(vertices.shape), dtype=torch.float32, device=dev)
         super().__init__(H, W, self.vcam, self.vimg, faces32, vfeat, valid, params)
+        if exchange is not None:
+            # the gradients are written straight into this rank's buffer of the exchange's
+            # symmetric allocation; the all-reduce is the last node of the backward graph
+            nv, nf = self.grad_verts.numel(), self.grad_feat.numel()
+            self.nv, self.nf = nv, nf
+            self.off_f = (nv + 63) // 64 * 64
+            self.grad_verts = exchange.flat[:nv].view(self.grad_verts.shape)
+            self.grad_feat = exchange.flat[self.off_f:self.off_f + nf].view(self.grad_feat.shape)
 
     def _issue_forward(self):
         _lib.check(_lib.lib().dibr_vertex_transform_fwd(
@@ -404,11 +413,23 @@ class _VertexEntry(_MeshEntry):
         super()._issue_forward()
 
     def _issue_backward(self, g_out, g_mask):
+        if self.exchange is not None:
+            self.exchange.issue_wait()        # peers have read the previous step's gradients
         super()._issue_backward(g_out, g_mask)
         _lib.check(_lib.lib().dibr_vertex_transform_bwd(
             self.B, self.V, self.verts_shared, _ptr(self.vcam), self.rotp, self.tfp, self.projp,
             None, _ptr(self.grad_img), _ptr(self.grad_verts), _stream(self.dev)),
             "dibr_vertex_transform_bwd")
+        if self.exchange is not None:
+            self.exchange.issue_allreduce()   # result = sum over ranks
+
+    def result_grads(self):
+        """Copies of the two gradients (summed over ranks when an exchange is folded in)."""
+        if self.exchange is None:
+            return self.grad_verts.clone(), self.grad_feat.clone()
+        flat = self.exchange.result.clone()    # one copy, both gradients are views of it
+        return (flat[:self.nv].view(self.grad_verts.shape),
+                flat[self.off_f:self.off_f + self.nf].view(self.grad_feat.shape))
 
 
 class DibrRasterizationVerticesGraphed(Function):
@@ -434,12 +455,13 @@ class DibrRasterizationVerticesGraphed(Function):
         g = None if grad_features is None else _prep(grad_features, "grad_interpolated_features")
         gm = None if grad_soft_mask is None else _prep(grad_soft_mask, "grad_soft_mask")
         entry.backward(g, gm)
-        return None, None, entry.grad_verts.clone(), entry.grad_feat.clone()
+        gv, gf = entry.result_grads()
+        return None, None, gv, gf
 
 
 def graphed_dibr_rasterization_vertices(H, W, vertices, faces32, vertex_features, camera_proj,
                                         camera_rot, camera_trans, camera_transform, valid_faces,
-                                        batch, params):
+                                        batch, params, exchange=None):
     """(features, soft_mask, face_idx) from a graph entry, or None on the first sighting."""
     v = _prep(vertices, "vertices")
     vfeat = _prep(vertex_features, "vertex_features")
@@ -465,7 +487,7 @@ def graphed_dibr_rasterization_vertices(H, W, vertices, faces32, vertex_features
     cams = tuple(None if t is None else t.data_ptr() for t in (proj, rot, trans, tf))
     key = ("vertices", v.device.index, int(H), int(W), batch, tuple(v.shape), F,
            tuple(vfeat.shape), params, v.data_ptr(), faces32.data_ptr(), vfeat.data_ptr(), cams,
-           None if valid is None else valid.data_ptr())
+           None if valid is None else valid.data_ptr(), None if exchange is None else id(exchange))
     e = _entries.get(key)
     if e is None:
         n = _sightings.get(key, 0) + 1
@@ -478,7 +500,7 @@ def graphed_dibr_rasterization_vertices(H, W, vertices, faces32, vertex_features
         while len(_entries) >= MAX_ENTRIES:
             _entries.popitem(last=False)
         e = _entries[key] = _VertexEntry(int(H), int(W), v, faces32, vfeat, proj, rot, trans, tf,
-                                         valid, batch, params)
+                                         valid, batch, params, exchange)
         del _sightings[key]
     else:
         _entries.move_to_end(key)
