@@ -20,3 +20,12 @@ print("%-72s %6s %12s %7s" % ("kernel", "n", "total_us", "share"))
 for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1]):
     print("%-72s %6d %12.1f %6.1f%%" % (k, v[0], v[1], 100 * v[1] / tot))
 print("%-72s %6s %12.1f" % ("TOTAL", "", tot))
+# the library's own kernels only (bench.py also runs torch fills, the reference kernels and
+# its FMA-peak micro-kernel, all outside the timed step)
+own = {k: v for k, v in agg.items() if k.startswith("dibr::")}
+tot_own = sum(v[1] for v in own.values()) or 1.0
+print()
+print("# libdibr_b200 kernels only: share of the step's own kernel time")
+print("%-72s %6s %12s %10s %7s" % ("kernel", "n", "total_us", "us/launch", "share"))
+for k, v in sorted(own.items(), key=lambda kv: -kv[1][1]):
+    print("%-72s %6d %12.1f %10.1f %6.1f%%" % (k, v[0], v[1], v[1] / v[0], 100 * v[1] / tot_own))
