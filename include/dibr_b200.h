@@ -86,7 +86,8 @@ DIBR_API int dibr_host_report_direct(int on);
  * dibr_profile_end() every kernel launch of this library is bracketed by CUDA events on
  * its launching stream.  dibr_profile_end synchronises those events and returns the number
  * of records written: kernel_ids[i] in {0 bin_count, 1 bin_scan, 2 bin_fill, 3 raster_fwd,
- * 4 softmask_fwd, 5 raster_bwd, 6 softmask_bwd, 7 softmask_bwd_dense}, ms[i] its duration. */
+ * 4 softmask_fwd (fallback), 5 raster_bwd, 6 softmask_bwd (fallback), 7 softmask_bwd_dense,
+ * 8 softmask_gather, 9 softmask_eval, 10 softmask_grad, 11 softmask_fold}, ms[i] its duration. */
 DIBR_API int dibr_profile_begin(void);
 DIBR_API int dibr_profile_end(int* kernel_ids, float* ms, int capacity);
 
