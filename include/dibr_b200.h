@@ -426,6 +426,9 @@ DIBR_API int dibr_texture_mapping_bwd(int batch, int64_t num_points, int channel
                              void* stream);
 DIBR_API int dibr_mask_iou_sums(int batch, int64_t num_pixels, const float* lhs_mask,
                        const float* rhs_mask, float* sums, void* stream);
+/* loss[0] = 1 - mean_b sums[b][0] / (sums[b][1] + 1e-10): the B-sized tail of mask_iou
+ * (kaolin/metrics/render.py:37-40) on the device, so that the metric is two launches. */
+DIBR_API int dibr_mask_iou_loss(int batch, const float* sums, float* loss, void* stream);
 DIBR_API int dibr_mask_iou_bwd(int batch, int64_t num_pixels, const float* lhs_mask,
                       const float* rhs_mask, const float* sums, const float* grad_loss,
                       float* grad_lhs, float* grad_rhs, void* stream);

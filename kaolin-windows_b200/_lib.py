@@ -56,6 +56,7 @@ SIGNATURES = {
     "dibr_texture_mapping_fwd": (_i, [_i, _i64, _i, _i, _i, _i, _vp, _vp, _vp, _vp]),
     "dibr_texture_mapping_bwd": (_i, [_i, _i64, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     "dibr_mask_iou_sums": (_i, [_i, _i64, _vp, _vp, _vp, _vp]),
+    "dibr_mask_iou_loss": (_i, [_i, _vp, _vp, _vp]),
     "dibr_mask_iou_bwd": (_i, [_i, _i64, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
     "dibr_packed_rasterize_fwd_f64": (_i, [_i, _i, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp,
                                            _f, _f, _vp, _vp, _vp, _vp, _i64, _i64, _vp, _vp]),

@@ -191,6 +191,15 @@ mask_iou_backward_kernel(const float* __restrict__ lhs, const float* __restrict_
   }
 }
 
+// the B-sized tail of mask_iou (render.py:37-40) on the device: 1 - mean_b up_b / (down_b + 1e-10)
+__global__ void mask_iou_loss_kernel(const float* __restrict__ sums, float* __restrict__ loss, int B) {
+  float acc = 0.f;
+  for (int b = threadIdx.x; b < B; b += 32) acc += sums[2 * b] / (sums[2 * b + 1] + 1e-10f);
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(DIBR_FULL_MASK, acc, d);
+  if (threadIdx.x == 0) loss[0] = 1.0f - acc / (float)B;
+}
+
 inline int blocks_for(long long n, int cap) {
   long long g = (n + 255) / 256;
   return (int)(g < 1 ? 1 : (g > cap ? cap : g));
@@ -265,6 +274,14 @@ DIBR_API int dibr_mask_iou_sums(int batch, int64_t num_pixels, const float* lhs_
   const int per_view = blocks_for(num_pixels, (148 * 8 + batch - 1) / batch);
   mask_iou_sums_kernel<<<dim3(per_view, batch), 256, 0, (cudaStream_t)stream>>>(
       lhs_mask, rhs_mask, sums, num_pixels);
+  EPI_CUDA(cudaGetLastError());
+  return DIBR_OK;
+}
+
+DIBR_API int dibr_mask_iou_loss(int batch, const float* sums, float* loss, void* stream) {
+  if (batch <= 0) return fail(DIBR_E_INVALID, "mask_iou of an empty batch");
+  if (!sums || !loss) return fail(DIBR_E_INVALID, "null pointer");
+  mask_iou_loss_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(sums, loss, batch);
   EPI_CUDA(cudaGetLastError());
   return DIBR_OK;
 }

@@ -209,45 +209,58 @@ vertex_transform_forward_kernel(const float* __restrict__ vertices, int shared,
   vimg[o * 2 + 1] = cy * __ldg(proj + 1) / den;
 }
 
-// Backward: cotangents of vcam (may be null) and vimg -> grad_vertices.  `shared`: one
-// thread per vertex sums its views (no atomics); else one thread per (view, vertex).
+// Backward: cotangents of vcam (may be null) and vimg -> grad_vertices.  64 vertices x 4
+// view lanes per CTA; `shared`: the view lanes stride over all views and their partial sums
+// meet in shared memory (no atomics); else blockIdx.y selects the view and lane 0 works.
 __global__ void __launch_bounds__(kThreads)
 vertex_transform_backward_kernel(const float* __restrict__ vcam, const float* __restrict__ mat,
                                  const float* __restrict__ proj, int mode,
                                  const float* __restrict__ g_vcam,
                                  const float* __restrict__ g_vimg, float* __restrict__ g_vertices,
                                  int B, int V, int shared) {
-  const int v = blockIdx.x * kThreads + threadIdx.x;
-  if (v >= V) return;
-  const int b0 = shared ? 0 : blockIdx.y, b1 = shared ? B : blockIdx.y + 1;
+  __shared__ float s_part[4][64][3];
+  const int vl = threadIdx.x & 63, ty = threadIdx.x >> 6;
+  const int v = blockIdx.x * 64 + vl;
+  const int b0 = shared ? ty : blockIdx.y, b1 = shared ? B : blockIdx.y + 1;
+  const int bstep = shared ? 4 : 1;
   const float p0 = __ldg(proj), p1 = __ldg(proj + 1), p2 = __ldg(proj + 2);
   float gx = 0.f, gy = 0.f, gz = 0.f;
-  for (int b = b0; b < b1; b++) {
-    const long long o = (long long)b * V + v;
-    const float X = __ldg(vcam + o * 3), Y = __ldg(vcam + o * 3 + 1), Z = __ldg(vcam + o * 3 + 2);
-    float cx = 0.f, cy = 0.f, cz = 0.f;
-    if (g_vimg) {
-      const float gu = __ldg(g_vimg + o * 2), gv = __ldg(g_vimg + o * 2 + 1);
-      const float inv = 1.0f / (Z * p2);
-      cx = gu * p0 * inv;
-      cy = gv * p1 * inv;
-      cz = -(gu * X * p0 + gv * Y * p1) * inv / Z;
-    }
-    if (g_vcam) { cx += __ldg(g_vcam + o * 3); cy += __ldg(g_vcam + o * 3 + 1); cz += __ldg(g_vcam + o * 3 + 2); }
-    if (mode == 0) {
-      const float* R = mat + (long long)b * 9;
-      gx += cx * __ldg(R) + cy * __ldg(R + 3) + cz * __ldg(R + 6);
-      gy += cx * __ldg(R + 1) + cy * __ldg(R + 4) + cz * __ldg(R + 7);
-      gz += cx * __ldg(R + 2) + cy * __ldg(R + 5) + cz * __ldg(R + 8);
-    } else {
-      const float* T = mat + (long long)b * 12;
-      gx += cx * __ldg(T) + cy * __ldg(T + 1) + cz * __ldg(T + 2);
-      gy += cx * __ldg(T + 3) + cy * __ldg(T + 4) + cz * __ldg(T + 5);
-      gz += cx * __ldg(T + 6) + cy * __ldg(T + 7) + cz * __ldg(T + 8);
+  if (v < V && (shared || ty == 0)) {
+    for (int b = b0; b < b1; b += bstep) {
+      const long long o = (long long)b * V + v;
+      const float X = __ldg(vcam + o * 3), Y = __ldg(vcam + o * 3 + 1), Z = __ldg(vcam + o * 3 + 2);
+      float cx = 0.f, cy = 0.f, cz = 0.f;
+      if (g_vimg) {
+        const float gu = __ldg(g_vimg + o * 2), gv = __ldg(g_vimg + o * 2 + 1);
+        const float inv = 1.0f / (Z * p2);
+        cx = gu * p0 * inv;
+        cy = gv * p1 * inv;
+        cz = -(gu * X * p0 + gv * Y * p1) * inv / Z;
+      }
+      if (g_vcam) { cx += __ldg(g_vcam + o * 3); cy += __ldg(g_vcam + o * 3 + 1); cz += __ldg(g_vcam + o * 3 + 2); }
+      if (mode == 0) {
+        const float* R = mat + (long long)b * 9;
+        gx += cx * __ldg(R) + cy * __ldg(R + 3) + cz * __ldg(R + 6);
+        gy += cx * __ldg(R + 1) + cy * __ldg(R + 4) + cz * __ldg(R + 7);
+        gz += cx * __ldg(R + 2) + cy * __ldg(R + 5) + cz * __ldg(R + 8);
+      } else {
+        const float* T = mat + (long long)b * 12;
+        gx += cx * __ldg(T) + cy * __ldg(T + 1) + cz * __ldg(T + 2);
+        gy += cx * __ldg(T + 3) + cy * __ldg(T + 4) + cz * __ldg(T + 5);
+        gz += cx * __ldg(T + 6) + cy * __ldg(T + 7) + cz * __ldg(T + 8);
+      }
     }
   }
-  float* g = g_vertices + ((shared ? 0ll : (long long)b0 * V) + v) * 3;
-  g[0] = gx; g[1] = gy; g[2] = gz;
+  s_part[ty][vl][0] = gx; s_part[ty][vl][1] = gy; s_part[ty][vl][2] = gz;
+  __syncthreads();
+  if (ty == 0 && v < V) {
+    if (shared) {
+#pragma unroll
+      for (int k = 1; k < 4; k++) { gx += s_part[k][vl][0]; gy += s_part[k][vl][1]; gz += s_part[k][vl][2]; }
+    }
+    float* g = g_vertices + ((shared ? 0ll : (long long)blockIdx.y * V) + v) * 3;
+    g[0] = gx; g[1] = gy; g[2] = gz;
+  }
 }
 
 }  // namespace
@@ -385,7 +398,7 @@ DIBR_API int dibr_vertex_transform_bwd(int batch, int num_vertices, int vertices
                                 (cudaStream_t)stream));
     return DIBR_OK;
   }
-  vertex_transform_backward_kernel<<<dim3((num_vertices + kThreads - 1) / kThreads,
+  vertex_transform_backward_kernel<<<dim3((num_vertices + 63) / 64,
                                           vertices_shared ? 1 : batch),
                                      kThreads, 0, (cudaStream_t)stream>>>(
       vertices_camera, camera_rot ? camera_rot : camera_transform, camera_proj,

@@ -586,8 +586,9 @@ __device__ __forceinline__ void emit_group(const RasterBwdArgs& a, int b, int fa
   const float inv_k3raw = 1.0f / k3raw;
   // eps of the forward's normalisation (:140-142), in multiplied coordinates:
   // rho = N / (N + eps), N = |k3raw| mult^2; rho - 1 = -eps / (N + eps) kept separately
-  const double N = fabs(k3d) * (double)a.mult * (double)a.mult;
-  const float rho = (float)(N / (N + a.eps_d)), rho1 = (float)(-a.eps_d / (N + a.eps_d));
+  // (rho differs from 1 by eps / N ~ 1e-8 .. 1e-4: a float quotient carries it)
+  const float Nf = fabsf(k3raw) * a.mult * a.mult;
+  const float rho1 = -a.eps_f / (Nf + a.eps_f), rho = 1.0f + rho1;
   const float *fp0 = bwd_feat(a, b, face, fc, 0), *fp1 = bwd_feat(a, b, face, fc, 1);
   const float* fp2 = bwd_feat(a, b, face, fc, 2);
   float *gf0 = bwd_gfeat(a, b, face, fc, 0), *gf1 = bwd_gfeat(a, b, face, fc, 1);
@@ -627,8 +628,29 @@ __device__ __forceinline__ void emit_group(const RasterBwdArgs& a, int b, int fa
   atomicAdd(reinterpret_cast<float2*>(bwd_gimg(a, b, face, fc, 2)), make_float2(dn * r, dq * r));
 }
 
+// DIBR_BWD_CTA=1 (experiment, off): the (warp, face) groups of a CTA are merged per face in a
+// shared-memory table and converted one face per thread with dense lanes.  Measured on cfg 2:
+// 98.6 us against 71.0 us for the default (every group leader converts its own partial
+// moments): three barriers and a conversion phase with one or two busy warps per CTA cost
+// more than the saved instructions.
+#ifndef DIBR_BWD_CTA
+#define DIBR_BWD_CTA 0
+#endif
+constexpr int kBwdSlots = 512;   // >= 2 x the pixels of a CTA: at most 256 distinct faces
+
+#ifndef DIBR_BWD_MINB
+#define DIBR_BWD_MINB 4
+#endif
 template <int DC>  // features handled per pass (D <= 4: one pass)
-__global__ void __launch_bounds__(256, 4) raster_backward_kernel(const RasterBwdArgs a) {
+__global__ void __launch_bounds__(256, DIBR_BWD_MINB) raster_backward_kernel(const RasterBwdArgs a) {
+#if DIBR_BWD_CTA
+  // per-CTA face table: open addressing on the face id; `s_list` holds the claimed slots in
+  // claim order so that the conversion runs one face per THREAD with dense lanes
+  __shared__ int s_key[kBwdSlots];
+  __shared__ float s_mom[kBwdSlots * 3 * DC];
+  __shared__ int s_list[256];
+  __shared__ int s_count;
+#endif
   pdl_prologue();
   const int lane = lane_id(), warp = threadIdx.x >> 5;
   const int ix = (blockIdx.x << 4) + ((warp & 1) << 3) + (lane & 7);
@@ -638,7 +660,11 @@ __global__ void __launch_bounds__(256, 4) raster_backward_kernel(const RasterBwd
   const long long pix = ((long long)b * a.H + iy) * a.W + ix;
   int face = -1;
   if (inimg) face = (int)a.idx[pix];
+#if DIBR_BWD_CTA
+  if (!__syncthreads_or(face >= 0)) return;   // nothing covered in this 16 x 16 block
+#else
   if (!__any_sync(DIBR_FULL_MASK, face >= 0)) return;
+#endif
   const unsigned peers = __match_any_sync(DIBR_FULL_MASK, face);
   const bool leader = (peers & lanemask_lt()) == 0;
 
@@ -670,7 +696,38 @@ __global__ void __launch_bounds__(256, 4) raster_backward_kernel(const RasterBwd
       }
     }
     reduce_peers<float, 3 * DC>(peers, mom, lane);
+#if DIBR_BWD_CTA
+    // ---- merge the CTA's groups per face: leaders add their partial moments into the
+    // face's slot (shared-memory atomics), then one thread per distinct face converts
+    for (int i = threadIdx.x; i < kBwdSlots; i += 256) s_key[i] = -1;
+    for (int i = threadIdx.x; i < kBwdSlots * 3 * DC; i += 256) s_mom[i] = 0.f;
+    if (threadIdx.x == 0) s_count = 0;
+    __syncthreads();
+    if (leader && regular) {
+      unsigned h = ((unsigned)face * 2654435761u) >> 23;   // 9 bits
+      while (true) {
+        const int prev = atomicCAS(&s_key[h], -1, face);
+        if (prev == -1) { s_list[atomicAdd(&s_count, 1)] = (int)h; break; }
+        if (prev == face) break;
+        h = (h + 1) & (kBwdSlots - 1);
+      }
+#pragma unroll
+      for (int i = 0; i < 3 * DC; i++)
+        if (mom[i] != 0.f) atomicAdd(&s_mom[h * 3 * DC + i], mom[i]);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < s_count; i += 256) {
+      const int slot = s_list[i], f2 = s_key[slot];
+      const BwdFace fc2 = bwd_face(a, b, f2, 16.f / ((float)a.W * (float)a.H));
+      float M[3 * DC];
+#pragma unroll
+      for (int j = 0; j < 3 * DC; j++) M[j] = s_mom[slot * 3 * DC + j];
+      emit_group<DC>(a, b, f2, fc2, M, d0);
+    }
+    __syncthreads();   // table free for the next feature chunk
+#else
     if (leader && regular) emit_group<DC>(a, b, face, fc, mom, d0);
+#endif
   }
 
   // ---- thin / tiny faces: the reference's per-pixel formula (:273-399) in double

@@ -1,7 +1,7 @@
 """kaolin.metrics.render.mask_iou on B200 (kaolin/metrics/render.py:18-40): the loss the
 DIB-R loop puts on the soft mask.  Both per-view sums come from ONE pass over the two
 masks (the reference materialises their product and sum and reduces each), the backward is
-one elementwise kernel; the B-sized tail (ratio, mean) stays in torch."""
+one elementwise kernel; the B-sized tail (ratio, mean) is a one-warp kernel."""
 import ctypes
 
 import torch
@@ -26,12 +26,17 @@ class _MaskIoU(Function):
         B = lhs.shape[0]
         npix = lhs.numel() // B if B > 0 else 0
         sums = torch.empty((B, 2), dtype=torch.float32, device=lhs.device)
+        if B == 0:                       # the reference's mean over no views
+            ctx.save_for_backward(lhs, rhs, sums)
+            return torch.full((), float("nan"), dtype=torch.float32, device=lhs.device)
         with torch.cuda.device(lhs.device):
             _lib.check(_lib.lib().dibr_mask_iou_sums(B, npix, _ptr(lhs), _ptr(rhs), _ptr(sums),
                                                      _stream(lhs.device)), "mask_iou")
+            loss = torch.empty((), dtype=torch.float32, device=lhs.device)
+            _lib.check(_lib.lib().dibr_mask_iou_loss(B, _ptr(sums), _ptr(loss),
+                                                     _stream(lhs.device)), "mask_iou")  # render.py:37-40
         ctx.save_for_backward(lhs, rhs, sums)
-        iou = sums[:, 0] / (sums[:, 1] + 1e-10)          # render.py:37-38
-        return 1.0 - iou.mean()
+        return loss
 
     @staticmethod
     def backward(ctx, grad_loss):

@@ -22,7 +22,7 @@ def _declared_symbols():
 
 def test_library_exports_every_declared_symbol():
     names = _declared_symbols()
-    assert len(names) == 37 and "dibr_deftet_fwd" in names and "dibr_render_fwd" in names and "dibr_face_setup_fwd" in names
+    assert len(names) == 38 and "dibr_deftet_fwd" in names and "dibr_render_fwd" in names and "dibr_face_setup_fwd" in names
     h = _lib.lib()
     for n in names:
         assert hasattr(h, n), n

@@ -61,7 +61,42 @@ for bw in (False, True):
                                    kal.ops.mesh.index_vertices_by_faces, bw)),
         "torch": timed(lambda: prep(mo.prepare_vertices, mo.index_vertices_by_faces, bw))}
 
+# ---- SURVEY 8(f) rank 1 as a whole: vertices + cameras -> images -> vertex gradients.
+# (a) the reference's chain with its torch code around our drop-in dibr_rasterization,
+# (b) the same chain on our face-tensor kernels (round 1), (c) the mesh-level call (round 2)
 H = W = 512
+g1 = torch.rand((B, H, W, 3), device=dev)
+g2 = torch.rand((B, H, W), device=dev)
+verts1, colors1 = verts[:1].contiguous(), colors[:1].contiguous()
+faces32 = faces.int().contiguous()
+
+
+def chain(mod_prepare, mod_gather, graph):
+    v = verts1.detach().requires_grad_(True)
+    c = colors1.detach().requires_grad_(True)
+    fvc, fvi, fn = mod_prepare(v.expand(B, -1, -1), faces, proj, camera_rot=rot, camera_trans=trans)
+    ff = mod_gather(c.expand(B, -1, -1), faces)
+    out, mask, _ = kal.render.mesh.dibr_rasterization(H, W, fvc[..., 2].contiguous(), fvi, ff,
+                                                      fn[..., 2].contiguous(), cuda_graph=graph)
+    torch.autograd.backward((out, mask), (g1, g2))
+
+
+def mesh_level(graph):
+    v = verts1.detach().requires_grad_(True)
+    c = colors1.detach().requires_grad_(True)
+    out, mask, _ = kal.render.mesh.dibr_rasterization_vertices(H, W, v, faces32, c, proj, rot, trans,
+                                                               cuda_graph=graph)
+    torch.autograd.backward((out, mask), (g1, g2))
+
+
+res["vertices+cameras -> dibr_rasterization -> vertex gradients, fwd+bwd (us)"] = {
+    "torch prepare_vertices/index + b200 dibr_rasterization (eager)":
+        timed(lambda: chain(mo.prepare_vertices, mo.index_vertices_by_faces, False)),
+    "b200 face-tensor kernels: prepare_vertices/index + dibr_rasterization (eager)":
+        timed(lambda: chain(kal.render.mesh.prepare_vertices, kal.ops.mesh.index_vertices_by_faces, False)),
+    "b200 mesh-level dibr_rasterization_vertices (eager)": timed(lambda: mesh_level(False)),
+    "b200 mesh-level dibr_rasterization_vertices (cuda_graph)": timed(lambda: mesh_level(True))}
+
 uv = torch.rand((B, H, W, 2), device=dev)
 tex = torch.rand((B, 3, 512, 512), device=dev)
 cot_tex = torch.randn((B, H, W, 3), device=dev)
@@ -85,5 +120,39 @@ def iou(fn):
 
 res["mask_iou fwd+bwd (us)"] = {"b200": timed(lambda: iou(kal.metrics.render.mask_iou)),
                                 "torch": timed(lambda: iou(mo.mask_iou))}
+# ---- the same two consumer ops as bare C-ABI calls on preallocated buffers (device time:
+# the public calls above are bound by Python / autograd-engine overhead per iteration)
+import ctypes                           # noqa: E402
+from kaolin_windows_b200 import _lib    # noqa: E402
+lib = _lib.lib()
+P = ctypes.c_void_p
+st = P(torch.cuda.current_stream(dev).cuda_stream)
+sums = torch.empty((B, 2), device=dev)
+loss = torch.empty((), device=dev)
+gl = torch.ones((), device=dev)
+g_m1 = torch.empty_like(m1)
+
+
+def iou_raw():
+    lib.dibr_mask_iou_sums(B, H * W, P(m1.data_ptr()), P(m2.data_ptr()), P(sums.data_ptr()), st)
+    lib.dibr_mask_iou_loss(B, P(sums.data_ptr()), P(loss.data_ptr()), st)
+    lib.dibr_mask_iou_bwd(B, H * W, P(m1.data_ptr()), P(m2.data_ptr()), P(sums.data_ptr()),
+                          P(gl.data_ptr()), P(g_m1.data_ptr()), None, st)
+
+
+res["mask_iou fwd+bwd (us)"]["b200 kernels only (C ABI)"] = timed(iou_raw, 50)
+out_t = torch.empty((B, H, W, 3), device=dev)
+g_tex = torch.empty_like(tex)
+g_uv = torch.empty_like(uv)
+for mode_i, mode in enumerate(("nearest", "bilinear")):
+    def tex_raw():
+        lib.dibr_texture_mapping_fwd(B, H * W, 3, 512, 512, mode_i, P(uv.data_ptr()),
+                                     P(tex.data_ptr()), P(out_t.data_ptr()), st)
+        g_tex.zero_()
+        lib.dibr_texture_mapping_bwd(B, H * W, 3, 512, 512, mode_i, P(uv.data_ptr()),
+                                     P(tex.data_ptr()), P(cot_tex.data_ptr()), P(g_tex.data_ptr()),
+                                     P(g_uv.data_ptr()) if mode_i else None, st)
+    res["texture_mapping %s fwd+bwd (us)" % mode]["b200 kernels only (C ABI)"] = timed(tex_raw, 50)
+
 res = {k: {a: round(b, 1) for a, b in v.items()} for k, v in res.items()}
 print(json.dumps({"config": "cfg2_70k_8x512 sizes (8 views, 69938 faces, 512x512)", "results": res}))
