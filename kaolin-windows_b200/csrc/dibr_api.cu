@@ -123,6 +123,7 @@ static int make_plan(int B, int F, int H, int W, Plan& p, float mult = nanf(""))
   for (int l = 0; l < 2; l++) {  // not memset: only the bucket sizes in the header are
     p.off_order[l] = off; off = align_up(off + (int64_t)kOrderBuckets * B * p.NB * 4, 256);
   }
+  p.off_rect = off; off = align_up(off + (int64_t)B * F * 8, 256);   // (never memset)
   p.fixed_bytes = off;
 #ifdef DIBR_TRACE
   p.trace = g_trace_ptr;
@@ -213,6 +214,7 @@ static void attach(BinJob& j, const Plan& p, const Workspace& w, int l) {
   j.total = (unsigned long long*)(w.base + p.off_total) + l;
   j.capacity = w.cap[l];
   j.ordered = l == 1;
+  j.rect = l == 1 ? (ushort4*)(w.base + p.off_rect) : nullptr;
 }
 
 // memset + count + scan + (capacity check) + fill for the given jobs (kinds[i] = 0/1).

@@ -84,7 +84,28 @@ bin_walk_kernel(const BinJobs jobs, const Plan p) {
     bool act = false;
     Face2D fc;
     if (f < f_end) {
-      if (load_face2d(job, b, f, fc)) act = bin_rect(g, fc, p.bin_log2, bx0, bx1, by0, by1);
+      if (job.rect) {
+        // soft list: the exact pixel rectangle, computed once (counting pass) and kept
+        ushort4* rp = job.rect + (long long)b * p.F + f;
+        int x_lo = 1, x_hi = 0, y_lo = 1, y_hi = 0;
+        if (FILL) {
+          const ushort4 r = *rp;
+          x_lo = r.x; x_hi = r.y; y_lo = r.z; y_hi = r.w;
+          act = x_lo <= x_hi;
+        } else {
+          act = load_face2d(job, b, f, fc) &&
+                exact_pixel_rect(g, fc.xmin, fc.ymin, fc.xmax, fc.ymax, x_lo, x_hi, y_lo, y_hi);
+          *rp = act ? make_ushort4((unsigned short)x_lo, (unsigned short)x_hi,
+                                   (unsigned short)y_lo, (unsigned short)y_hi)
+                    : make_ushort4(1, 0, 1, 0);
+        }
+        if (act) {
+          bx0 = x_lo >> p.bin_log2; bx1 = x_hi >> p.bin_log2;
+          by0 = y_lo >> p.bin_log2; by1 = y_hi >> p.bin_log2;
+        }
+      } else if (load_face2d(job, b, f, fc)) {
+        act = bin_rect(g, fc, p.bin_log2, bx0, bx1, by0, by1);
+      }
     }
     // Where the order inside a bin's list does not matter -- the counting pass, and the
     // fill of the rasterizer's list (its depth test is order independent) -- every lane

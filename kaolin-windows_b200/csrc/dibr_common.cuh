@@ -63,6 +63,7 @@ struct Plan {
                           // then int [2][16] bucket sizes of the heaviest-first order
   int64_t off_order[2];   // int [16][B * NB]    (view, bin) rows bucketed by list length
   int64_t off_flags;      // int [B][nkx*nky]      uncovered-pixel count per block
+  int64_t off_rect;       // ushort4 [B][F]        exact pixel rectangle of each face's soft box
   int64_t fixed_bytes;    // everything above
   unsigned long long* trace;  // -DDIBR_TRACE builds only, else null
 };
@@ -93,6 +94,11 @@ struct BinJob {
   int* start;
   int* count;
   int* list;
+  // soft list only: the EXACT pixel rectangle {x_lo, x_hi, y_lo, y_hi} of every face's
+  // (enlarged) box -- the pixel centres passing the reference's half-open box test
+  // (dibr_soft_mask_cuda.cu:89-97), x_lo > x_hi = none.  Written once per (view, face) by the
+  // counting pass; the fill pass and the gather read it instead of redoing the geometry.
+  ushort4* rect;
   // raster list as compact records instead of face ids (fused path): 3 x float4 per entry,
   // {ax, ay, bx, by} {cx, cy, za, zb} {zc, face id bits, 0, 0} with scaled coordinates;
   // written by the fill pass (which needs `z`), streamed by the rasterizer
@@ -347,6 +353,19 @@ __device__ __forceinline__ bool pixel_range(const Grid& g, float xmin, float ymi
   //    y0 >= ymin <=> iy <= fy_hi  ->  iy in [floor(fy_lo) + 1, floor(fy_hi)]
   y_lo = max((int)floorf(fy_lo - dy) + 1, 0);
   y_hi = min((int)floorf(fy_hi + dy), g.H - 1);
+  return x_lo <= x_hi && y_lo <= y_hi;
+}
+
+// The exact rectangle: the conservative range trimmed with the reference's own float
+// comparisons (pix_x / pix_y are monotone in ix / iy).  Returns false when empty.
+__device__ __forceinline__ bool exact_pixel_rect(const Grid& g, float xmin, float ymin, float xmax,
+                                                 float ymax, int& x_lo, int& x_hi, int& y_lo,
+                                                 int& y_hi) {
+  if (!pixel_range(g, xmin, ymin, xmax, ymax, x_lo, x_hi, y_lo, y_hi)) return false;
+  while (x_lo <= x_hi && pix_x(g, x_lo) < xmin) x_lo++;
+  while (x_lo <= x_hi && pix_x(g, x_hi) >= xmax) x_hi--;
+  while (y_lo <= y_hi && pix_y(g, y_lo) >= ymax) y_lo++;
+  while (y_lo <= y_hi && pix_y(g, y_hi) < ymin) y_hi--;
   return x_lo <= x_hi && y_lo <= y_hi;
 }
 

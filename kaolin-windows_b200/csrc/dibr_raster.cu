@@ -636,7 +636,9 @@ __device__ __forceinline__ void emit_group(const RasterBwdArgs& a, int b, int fa
 #ifndef DIBR_BWD_CTA
 #define DIBR_BWD_CTA 0
 #endif
+#if DIBR_BWD_CTA
 constexpr int kBwdSlots = 512;   // >= 2 x the pixels of a CTA: at most 256 distinct faces
+#endif
 
 #ifndef DIBR_BWD_MINB
 #define DIBR_BWD_MINB 4

@@ -146,17 +146,13 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
       for (int w = 0; w < NW; w++) rmask[w] = 0u;
       if (t < nc) {
         const int f = a.job.list[start + base + t];
-        Face2D fc;
-        int x_lo, x_hi, y_lo, y_hi;
-        if (load_face2d(a.job, b, f, fc) &&
-            pixel_range(g, fc.xmin, fc.ymin, fc.xmax, fc.ymax, x_lo, x_hi, y_lo, y_hi)) {
+        // the face's exact pixel rectangle (the reference's half-open test, :89-97), kept by
+        // the binning pass: 8 bytes instead of the corner loads and the float geometry
+        const ushort4 r = __ldg(a.job.rect + (long long)b * p.F + f);
+        int x_lo = r.x, x_hi = r.y, y_lo = r.z, y_hi = r.w;
+        {
           x_lo = max(x_lo, bx0); x_hi = min(x_hi, bx1);
           y_lo = max(y_lo, by0); y_hi = min(y_hi, by1);
-          // exact half-open test of the reference (:89-97) on the range ends
-          while (x_lo <= x_hi && pix_x(g, x_lo) < fc.xmin) x_lo++;
-          while (x_lo <= x_hi && pix_x(g, x_hi) >= fc.xmax) x_hi--;
-          while (y_lo <= y_hi && pix_y(g, y_lo) >= fc.ymax) y_lo++;
-          while (y_lo <= y_hi && pix_y(g, y_hi) < fc.ymin) y_hi--;
           if (x_lo <= x_hi && y_lo <= y_hi) {
             const int xl = x_lo - bx0, xh = x_hi - bx0, yl = y_lo - by0, yh = y_hi - by0;
             sm.rect[t] = (unsigned)xl | ((unsigned)xh << 8) | ((unsigned)yl << 16) |
