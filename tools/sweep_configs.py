@@ -51,6 +51,9 @@ for spec in (sys.argv[1:] or DEFAULT):
     e1.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / n
+    for _ in range(3):            # eager calls of this shape first: capacities settle
+        step(False)
+    torch.cuda.synchronize()
     lib.dibr_profile_begin()
     for _ in range(3):
         step(False)
