@@ -30,6 +30,7 @@ profiles/r2_parity.jsonl.
 import json
 import os
 
+import numpy as np
 import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -104,11 +105,18 @@ def exact_weights64(height, width, face_vertices_image, face_idx, multiplier, ep
     `saved_weights` (B, H, W, 3) are kept, as the reference's backward would see them."""
     dev = face_vertices_image.device
     B, H, W = face_idx.shape
-    mult32 = torch.tensor(float(multiplier), dtype=torch.float32, device=dev)
-    xs = ((mult32 / width) * torch.arange(1 - width, width + 1, 2, device=dev,
-                                          dtype=torch.int32).float()).double()
-    ys = ((mult32 / height) * torch.arange(height - 1, -height - 1, -2, device=dev,
-                                           dtype=torch.int32).float()).double()
+    # fl32(multiplier / width) as an IEEE float DIVISION, formed with numpy: torch divides a
+    # tensor by a host scalar as a multiplication by fl32(1 / width), which is 1 ulp off for
+    # sizes that are not powers of two (520, 600: the centre moves by 3e-5 multiplied units,
+    # 1e-4 of a sub-pixel face)
+    xstep = torch.tensor(float(np.float32(multiplier) / np.float32(width)), dtype=torch.float32,
+                         device=dev)
+    ystep = torch.tensor(float(np.float32(multiplier) / np.float32(height)), dtype=torch.float32,
+                         device=dev)
+    xs = (xstep * torch.arange(1 - width, width + 1, 2, device=dev,
+                               dtype=torch.int32).float()).double()
+    ys = (ystep * torch.arange(height - 1, -height - 1, -2, device=dev,
+                               dtype=torch.int32).float()).double()
     out = torch.zeros((B, H, W, 3), dtype=torch.float64, device=dev)
     b, y, x = torch.nonzero(face_idx >= 0, as_tuple=True)
     v = face_vertices_image.double()[b, face_idx[b, y, x]] * float(multiplier)   # (n, 3, 2)

@@ -187,6 +187,41 @@ def test_large_faces_and_ties(kal, ref):
     assert s["covered"] > 50000
 
 
+@pytest.mark.parametrize("reverse", [False, True])
+def test_wide_slanted_triangles_among_small_faces(kal, ref, reverse):
+    """Screen-sized triangles whose slanted left edge crosses block rows hundreds of pixels to
+    the right of the block origin, listed together with thousands of small faces in the same
+    blocks, at an image size with a partial-height last block row; both face orders.  (Round 1
+    packed a span's left end into 8 bits without clamping it: such rows got a phantom length
+    and real candidates of the following faces were never tested.)"""
+    H, W = 600, 520                                   # 600 = 18 * 32 + 24: partial block row
+    gen = torch.Generator(device=DEV).manual_seed(11)
+    big = torch.tensor([[[-0.95, -0.9], [0.95, -0.2], [0.9, 0.95]],     # slanted, screen-sized
+                        [[-0.9, 0.9], [0.2, -0.95], [0.95, 0.9]],
+                        [[-0.99, -0.99], [0.99, -0.97], [0.97, 0.99]],
+                        [[0.99, 0.99], [-0.99, 0.97], [-0.97, -0.99]],
+                        [[-0.2, -0.99], [0.99, 0.99], [-0.99, 0.3]]], device=DEV)
+    n_small = 6000
+    c = torch.rand((n_small, 1, 2), device=DEV, generator=gen) * 1.9 - 0.95
+    small = c + (torch.rand((n_small, 3, 2), device=DEV, generator=gen) - 0.5) * 0.03
+    tris = torch.cat([big[:2], small[:3000], big[2:4], small[3000:], big[4:]], dim=0)
+    if reverse:
+        tris = tris.flip(0)
+    F = tris.shape[0]
+    img = tris.unsqueeze(0).repeat(2, 1, 1, 1).contiguous()
+    img[1] = img[1].flip(-1)                          # second view: transposed geometry
+    z = -(1.0 + torch.rand((2, F, 3), device=DEV, generator=gen))
+    feat = torch.rand((2, F, 3, 3), device=DEV, generator=gen)
+    nz = torch.ones((2, F), device=DEV)
+    inp = dict(face_vertices_z=z, face_vertices_image=img, face_features=feat, face_normals_z=nz)
+    s = full_compare(kal, ref, inp, H, W, label="wide+small rev=%d" % reverse)
+    assert s["covered"] > 300000
+    # and the rasterizer alone with the weights output (the raw-op route)
+    o1, i1 = kal.render.mesh.rasterize(H, W, z, img, feat)
+    r_out, r_idx, _ = orc.rasterize_forward(H, W, z, img, feat, None, ops=ref)
+    assert torch.equal(i1, r_idx) and torch.equal(o1, r_out)
+
+
 def test_empty_and_all_invalid(kal):
     z = torch.zeros(2, 0, 3, device=DEV)
     img = torch.zeros(2, 0, 3, 2, device=DEV)
