@@ -268,9 +268,12 @@ def raster_pair_count(H, W, face_vertices_image, valid_faces, multiplier=1000.0)
     Checked against the oracle's own pair counter in tests/test_oracle_golden.py."""
     img = face_vertices_image.detach().float() * multiplier
     dev = img.device
-    mult = torch.tensor(float(multiplier), dtype=torch.float32, device=dev)
-    xs = (mult / W) * torch.arange(1 - W, W + 1, 2, device=dev, dtype=torch.int32).float()
-    ys = (mult / H) * torch.arange(1 - H, H + 1, 2, device=dev, dtype=torch.int32).float()  # ascending
+    # (the step as an IEEE float division, with numpy: torch divides a tensor by a host
+    # scalar as a multiplication by the rounded reciprocal, 1 ulp off when W is not 2^k)
+    xstep = float(np.float32(multiplier) / np.float32(W))
+    ystep = float(np.float32(multiplier) / np.float32(H))
+    xs = torch.arange(1 - W, W + 1, 2, device=dev, dtype=torch.int32).float() * xstep
+    ys = torch.arange(1 - H, H + 1, 2, device=dev, dtype=torch.int32).float() * ystep  # ascending
     lo = img.min(dim=2)[0]
     hi = img.max(dim=2)[0]
     # pixels with lo <= c < hi  ->  searchsorted(c, hi, left) - searchsorted(c, lo, left)
