@@ -111,6 +111,7 @@ static int make_plan(int B, int F, int H, int W, Plan& p, float mult = nanf(""))
   if (s > 4096) s = 4096;
   p.S = (int)align_up(s, 32);
   p.nchunks = F > 0 ? (F + p.S - 1) / p.S : 0;
+  p.mstride = (int)align_up(p.nchunks, 4);
   int64_t off = 0;
   p.off_total = off; off += 256;
   p.off_flags = off; off = align_up(off + (int64_t)B * p.nkx * p.nky * 4, 256);
@@ -118,7 +119,7 @@ static int make_plan(int B, int F, int H, int W, Plan& p, float mult = nanf(""))
     p.off_start[l] = off; off = align_up(off + (int64_t)B * p.NB * 4, 256);
     p.off_count[l] = off; off = align_up(off + (int64_t)B * p.NB * 4, 256);
     p.off_range[l] = off; off = align_up(off + (int64_t)B * p.nchunks * 8, 256);
-    p.off_mat[l] = off; off = align_up(off + (int64_t)B * p.NB * p.nchunks * 4, 256);
+    p.off_mat[l] = off; off = align_up(off + (int64_t)B * p.NB * p.mstride * 4, 256);
   }
   for (int l = 0; l < 2; l++) {  // not memset: only the bucket sizes in the header are
     p.off_order[l] = off; off = align_up(off + (int64_t)kOrderBuckets * B * p.NB * 4, 256);

@@ -11,12 +11,14 @@
 //              private shared-memory histogram (native integer shared atomics; the order
 //              is irrelevant for counting).  Non-zero counts go to mat[view][bin][chunk].
 //   bin_scan   one warp per (view, bin): exclusive scan of mat[view][bin][:] over chunks
-//              (coalesced, shuffle scan), then one list segment per bin is reserved from
-//              a global cursor (one atomic per CTA of 8 bins).
-//   bin_fill   soft-mask list (ordered): the warp walks the distinct bins its 32 faces
-//              touch in ascending bin id (warp min-reduce); the faces touching the current
-//              bin are found with __ballot_sync and ranked with __popc(mask & lanemask_lt),
-//              so every bin's list comes out sorted by face index.
+//              (rows padded to int4, four independent 16-byte loads per lane in flight, then
+//              shuffle scans), then one list segment per bin is reserved from a global
+//              cursor (one atomic per CTA of 8 bins).
+//   bin_fill   soft-mask list (ordered): per step of 32 faces every lane ORs its lane bit
+//              into a per-warp shared-memory mask word of each bin of its rectangle; a
+//              lane's slot in a bin is then the bin's counter + __popc(mask & lanemask_lt),
+//              so every bin's list comes out sorted by face index with all lanes working in
+//              parallel; the lowest lane of each mask advances the counter and clears it.
 //              rasterizer list (order free, its depth test is order independent): slots
 //              are taken with shared-memory atomics on the same per-warp counters.
 //
@@ -51,13 +53,14 @@ bin_walk_kernel(const BinJobs jobs, const Plan p) {
     r[1] = jobs.totals[1];
     __threadfence_system();
   }
-  extern __shared__ int s_hist[];  // [kBinWarps][NB]
+  extern __shared__ int s_hist[];  // [kBinWarps][NB] counters (+ [kBinWarps][NB] lane masks: fill)
   const BinJob& job = jobs.j[blockIdx.z];
   const int warp = threadIdx.x >> 5, lane = lane_id();
   const int b = blockIdx.y;
   const int chunk = blockIdx.x * kBinWarps + warp;
   if (chunk >= p.nchunks) return;  // whole warp leaves; no block-wide barrier below
   int* hist = s_hist + warp * p.NB;
+  unsigned* lmask = reinterpret_cast<unsigned*>(s_hist + (kBinWarps + warp) * p.NB);  // FILL only
   const Grid g = plan_grid(p, job.mult);
   const long long row = (long long)b * p.NB;  // first bin row of this view in mat/start
 
@@ -69,8 +72,10 @@ bin_walk_kernel(const BinJobs jobs, const Plan p) {
     // 64-bit sum clamped below 2^31: a segment beyond the capacity (an under-provisioned
     // first attempt) must not wrap into a valid slot
     for (int i = lo_bin + lane; i <= hi_bin; i += 32)
-      hist[i] = (int)min((long long)job.start[row + i] + job.mat[(row + i) * p.nchunks + chunk],
-                         kMaxListEntries);
+      hist[i] = (int)min((long long)job.start[row + i] +
+                             job.mat[(row + i) * p.mstride + chunk], kMaxListEntries);
+    if (job.ordered)
+      for (int i = lo_bin + lane; i <= hi_bin; i += 32) lmask[i] = 0u;
   } else {
     for (int i = lane; i < p.NB; i += 32) hist[i] = 0;
   }
@@ -139,31 +144,36 @@ bin_walk_kernel(const BinJobs jobs, const Plan p) {
         }
       continue;
     }
-    int cx = bx0, cy = by0;
-    // Ordered emission (soft-mask list): each lane walks its rectangle row-major (ascending bin id); the
-    // warp repeatedly takes the smallest pending bin id, so all faces touching that bin
-    // are handled together, in lane (= face) order.
-    while (true) {
-      const int cur = act ? cy * p.nbx + cx : 0x7fffffff;
-      const int m = __reduce_min_sync(DIBR_FULL_MASK, cur);
-      if (m == 0x7fffffff) break;
-      const bool hit = (cur == m);
-      const unsigned mask = __ballot_sync(DIBR_FULL_MASK, hit);
-      const int base = hist[m];
+    // Ordered emission (soft-mask list, fill pass only: the counting pass took the branch
+    // above).  Three lane-parallel sweeps over the lane's own bin rectangle:
+    //   mark   OR the lane bit into the mask word of every bin of the rectangle
+    //   place  slot = bin counter + number of lower lanes (= lower face ids) in the mask
+    //   close  the lowest lane of a mask adds its population to the counter and clears it
+    // (a lane that reads an already cleared mask in `close` sees 0 and is not its lowest
+    // lane; counters only move in `close`, masks only in `mark` and `close`)
+    if (FILL) {
+      if (act)
+        for (int cy = by0; cy <= by1; cy++)
+          for (int cx = bx0; cx <= bx1; cx++) atomicOr(&lmask[cy * p.nbx + cx], 1u << lane);
       __syncwarp();
-      if (lane == 0) hist[m] = base + __popc(mask);
-      if (FILL) {
-        if (hit) {
-          const long long slot = (long long)base + __popc(mask & lanemask_lt());
-          if (slot < job.capacity) job.list[slot] = f;
-        }
-      }
-      if (hit) {
-        if (++cx > bx1) {
-          cx = bx0;
-          if (++cy > by1) act = false;
-        }
-      }
+      if (act)
+        for (int cy = by0; cy <= by1; cy++)
+          for (int cx = bx0; cx <= bx1; cx++) {
+            const int bin = cy * p.nbx + cx;
+            const long long slot = (long long)hist[bin] + __popc(lmask[bin] & lanemask_lt());
+            if (slot < job.capacity) job.list[slot] = f;
+          }
+      __syncwarp();
+      if (act)
+        for (int cy = by0; cy <= by1; cy++)
+          for (int cx = bx0; cx <= bx1; cx++) {
+            const int bin = cy * p.nbx + cx;
+            const unsigned mk = lmask[bin];
+            if ((mk & ((2u << lane) - 1u)) == (1u << lane)) {   // own bit is the lowest set
+              hist[bin] += __popc(mk);
+              lmask[bin] = 0u;
+            }
+          }
       __syncwarp();
     }
   }
@@ -173,7 +183,7 @@ bin_walk_kernel(const BinJobs jobs, const Plan p) {
     __syncwarp();
     for (int i = lo_bin + lane; i <= hi_bin; i += 32) {
       const int c = hist[i];
-      if (c) job.mat[(row + i) * p.nchunks + chunk] = c;
+      if (c) job.mat[(row + i) * p.mstride + chunk] = c;
     }
     if (lane == 0) job.range[(long long)b * p.nchunks + chunk] = make_int2(lo_bin, hi_bin);
   }
@@ -190,18 +200,35 @@ __global__ void __launch_bounds__(256) bin_scan_kernel(const BinJobs jobs, const
   const long long rowi = (long long)blockIdx.x * 8 + warp;
   int carry = 0;
   if (rowi < nrows) {
-    int* m = job.mat + rowi * p.nchunks;
-    for (int i = 0; i < p.nchunks; i += 32) {
-      const int idx = i + lane;
-      const int v = idx < p.nchunks ? m[idx] : 0;
-      int incl = v;
+    // rows are mstride = 4 n4 ints, 16-byte aligned, zero beyond nchunks: each lane scans
+    // int4 groups; four groups per lane are loaded before the first shuffle scan so that one
+    // L2 round trip covers 512 chunks
+    int4* m4 = reinterpret_cast<int4*>(job.mat + rowi * p.mstride);
+    const int n4 = p.mstride >> 2;
+    constexpr int U = 4;
+    for (int i0 = 0; i0 < n4; i0 += 32 * U) {
+      int4 v[U];
 #pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const int t = __shfl_up_sync(DIBR_FULL_MASK, incl, d);
-        if (lane >= d) incl += t;
+      for (int u = 0; u < U; u++) {
+        const int idx = i0 + u * 32 + lane;
+        v[u] = idx < n4 ? m4[idx] : make_int4(0, 0, 0, 0);
       }
-      if (idx < p.nchunks) m[idx] = carry + incl - v;
-      carry += __shfl_sync(DIBR_FULL_MASK, incl, 31);
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        if (i0 + u * 32 >= n4) break;   // warp-uniform
+        const int idx = i0 + u * 32 + lane;
+        const int sum = v[u].x + v[u].y + v[u].z + v[u].w;
+        int incl = sum;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          const int t = __shfl_up_sync(DIBR_FULL_MASK, incl, d);
+          if (lane >= d) incl += t;
+        }
+        const int e = carry + incl - sum;
+        if (idx < n4)
+          m4[idx] = make_int4(e, e + v[u].x, e + v[u].x + v[u].y, e + v[u].x + v[u].y + v[u].z);
+        carry += __shfl_sync(DIBR_FULL_MASK, incl, 31);
+      }
     }
   }
   if (lane == 0) s_tot[warp] = carry;
@@ -243,7 +270,7 @@ cudaError_t launch_binning_count(const BinJobs& jobs, int njobs, const Plan& p, 
 }
 
 cudaError_t launch_binning_fill(const BinJobs& jobs, int njobs, const Plan& p, cudaStream_t st) {
-  const size_t smem = (size_t)kBinWarps * p.NB * sizeof(int);
+  const size_t smem = (size_t)2 * kBinWarps * p.NB * sizeof(int);   // counters + lane masks
   dim3 grid((p.nchunks + kBinWarps - 1) / kBinWarps, p.B, njobs);
   prof_begin(K_BIN_FILL, st);
   launch_k(bin_walk_kernel<true>, grid, kBinWarps * 32, smem, st, jobs, p);

@@ -53,9 +53,10 @@ struct Plan {
   int bin_log2, nbx, nby, NB;  // bins
   int blk_log2, nkx, nky;      // blocks (CTA footprint)
   int S, nchunks;              // faces per binning chunk (one warp), chunks per view
+  int mstride;                 // row stride of the count matrix: nchunks rounded up to 4 (int4 rows)
   int lists;
   // byte offsets inside the workspace (per list kind l = 0 raster, 1 soft)
-  int64_t off_mat[2];     // int [B][NB][nchunks]  chunk counts -> exclusive offsets
+  int64_t off_mat[2];     // int [B][NB][mstride]  chunk counts -> exclusive offsets
   int64_t off_range[2];   // int2 [B][nchunks]     touched bin range of each chunk
   int64_t off_start[2];   // int [B][NB]           list segment start of each bin
   int64_t off_count[2];   // int [B][NB]           list segment length
