@@ -283,31 +283,42 @@ cudaError_t launch_softmask_backward_f64(const SoftBwdF64Args&, cudaStream_t);
 // CTA cost grows with the list length take their block through this order, longest lists
 // first, so the long CTAs start early and the short ones fill the tail (LPT scheduling).
 constexpr int kOrderBuckets = 16;
-__device__ __forceinline__ long long lpt_row(const BinJob& j, long long nrows, long long i) {
-  int c[kOrderBuckets];
+// Warp-cooperative (every lane of a converged warp calls it with the same i): lane k holds
+// bucket k's size, a suffix sum over the 16 buckets finds the bucket that position i of the
+// heaviest-first order falls into.  ~20 instructions per warp; the per-thread version (16
+// loads and 64-bit compares in every thread) was a third of the gather kernel's instructions.
+// nrows = B * NB < 2^27.
+__device__ __forceinline__ int lpt_row(const BinJob& j, int nrows, int i) {
+  const int lane = threadIdx.x & 31;
+  const int c = lane < kOrderBuckets ? j.bucket[lane] : 0;
+  int incl = c;                       // -> sum of the sizes of buckets >= lane
 #pragma unroll
-  for (int k = 0; k < kOrderBuckets; k++) c[k] = j.bucket[k];
-  long long acc = 0;
-#pragma unroll
-  for (int k = kOrderBuckets - 1; k >= 0; k--) {
-    if (i < acc + c[k]) return j.order[(long long)k * nrows + (i - acc)];
-    acc += c[k];
+  for (int d = 1; d < kOrderBuckets; d <<= 1) {
+    const int t = __shfl_down_sync(DIBR_FULL_MASK, incl, d);
+    if (lane + d < 32) incl += t;
   }
-  return -1;
+  const int before = incl - c;        // rows in heavier buckets
+  const unsigned hit = __ballot_sync(DIBR_FULL_MASK, c > 0 && i >= before && i < incl);
+  if (!hit) return -1;
+  const int k = __ffs(hit) - 1;
+  const int acc = __shfl_sync(DIBR_FULL_MASK, before, k);
+  return j.order[(long long)k * nrows + (i - acc)];
 }
 
 // CTA `id` of a 1-D grid of B * NB * 4^(bin_log2 - sub_log2) CTAs -> (view, block x, block y)
-// in units of 2^sub_log2 pixels.  Returns false for blocks outside the image.
+// in units of 2^sub_log2 pixels.  Returns false for blocks outside the image.  Called by all
+// threads of the CTA at kernel start (see lpt_row).
 __device__ __forceinline__ bool lpt_block(const BinJob& j, const Plan& p, int sub_log2,
-                                          long long id, int& b, int& bxi, int& byi) {
+                                          unsigned id, int& b, int& bxi, int& byi) {
   const int shift = p.bin_log2 - sub_log2;
-  const long long row = lpt_row(j, (long long)p.B * p.NB, id >> (2 * shift));
+  const int row = lpt_row(j, p.B * p.NB, (int)(id >> (2 * shift)));
   if (row < 0) return false;
-  const int sub = (int)(id & ((1ll << (2 * shift)) - 1));
-  b = (int)(row / p.NB);
-  const int bin = (int)(row - (long long)b * p.NB);
-  bxi = ((bin % p.nbx) << shift) + (sub & ((1 << shift) - 1));
-  byi = ((bin / p.nbx) << shift) + (sub >> shift);
+  const int sub = (int)(id & ((1u << (2 * shift)) - 1u));
+  b = row / p.NB;
+  const int bin = row - b * p.NB;
+  const int by = bin / p.nbx;
+  bxi = ((bin - by * p.nbx) << shift) + (sub & ((1 << shift) - 1));
+  byi = (by << shift) + (sub >> shift);
   return (bxi << sub_log2) < p.W && (byi << sub_log2) < p.H;
 }
 
