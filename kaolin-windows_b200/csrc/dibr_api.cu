@@ -125,6 +125,7 @@ static int make_plan(int B, int F, int H, int W, Plan& p, float mult = nanf(""))
     p.off_order[l] = off; off = align_up(off + (int64_t)kOrderBuckets * B * p.NB * 4, 256);
   }
   p.off_rect = off; off = align_up(off + (int64_t)B * F * 8, 256);   // (never memset)
+  p.off_work = off; off = align_up(off + (int64_t)B * p.nkx * p.nky * 4 * 8, 256);   // (never memset)
   p.fixed_bytes = off;
 #ifdef DIBR_TRACE
   p.trace = g_trace_ptr;
@@ -216,6 +217,26 @@ static void attach(BinJob& j, const Plan& p, const Workspace& w, int l) {
   j.capacity = w.cap[l];
   j.ordered = l == 1;
   j.rect = l == 1 ? (ushort4*)(w.base + p.off_rect) : nullptr;
+}
+
+// DIBR_B200_GATHER_WORK=0: the gather takes every block of the screen in list-length order,
+// as the stand-alone soft mask does (A/B switch)
+static bool gather_handoff_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("DIBR_B200_GATHER_WORK");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+
+// gather work list of the fused forward (rasterizer -> gather); header words 200 / 204
+static GatherWork gather_work(const Plan& p, const Workspace& w) {
+  GatherWork g;
+  g.item = (int2*)(w.base + p.off_work);
+  g.count = (unsigned*)(w.base + p.off_total + 200);
+  g.next = (unsigned*)(w.base + p.off_total + 204);
+  g.cap = (unsigned)((int64_t)p.B * p.nkx * p.nky * 4);
+  return g;
 }
 
 // memset + count + scan + (capacity check) + fill for the given jobs (kinds[i] = 0/1).
@@ -570,12 +591,17 @@ extern "C" int dibr_render_fwd(int B, int F, int H, int W, int D, const float* z
   a.job = jobs.j[0]; a.rec = jobs.j[0].rec; a.z = z; a.feat = feat; a.D = D; a.eps_d = (double)eps;
   a.out_idx = out_idx; a.out_feat = out_feat; a.out_w = nullptr;
   a.block_uncovered = (int*)(w.base + p.off_flags);
+  const bool handoff = gather_handoff_enabled() && w.pairs.cap > 0 && K > 0;
+  if (handoff) {   // the rasterizer writes soft_mask's base value and the gather's work list
+    a.mask = mask; a.soft_count = jobs.j[1].count; a.work = gather_work(p, w);
+  }
   DIBR_CUDA(launch_raster_forward(a, p, st));
   SoftArgs s;
   memset(&s, 0, sizeof(s));
   s.job = jobs.j[1]; s.sel = out_idx; s.sigmainv = sigmainv; s.K = K; s.mask = mask;
   s.pairs = w.pairs;
   s.block_uncovered = (const int*)(w.base + p.off_flags);
+  if (handoff) s.work = a.work;
   return run_soft_forward(s, p, needed_host, st);
 }
 
@@ -729,12 +755,17 @@ extern "C" int dibr_render_mesh_fwd(int B, int V, int F, int H, int W, int D,
   a.feat_shared = features_shared; a.D = D; a.eps_d = (double)eps;
   a.out_idx = out_idx; a.out_feat = out_feat; a.out_w = nullptr;
   a.block_uncovered = (int*)(w.base + p.off_flags);
+  const bool handoff = gather_handoff_enabled() && w.pairs.cap > 0 && K > 0;
+  if (handoff) {   // the rasterizer writes soft_mask's base value and the gather's work list
+    a.mask = mask; a.soft_count = jobs.j[1].count; a.work = gather_work(p, w);
+  }
   DIBR_CUDA(launch_raster_forward(a, p, st));
   SoftArgs s;
   memset(&s, 0, sizeof(s));
   s.job = jobs.j[1]; s.sel = out_idx; s.sigmainv = sigmainv; s.K = K; s.mask = mask;
   s.pairs = w.pairs;
   s.block_uncovered = (const int*)(w.base + p.off_flags);
+  if (handoff) s.work = a.work;
   return run_soft_forward(s, p, needed_host, st);
 }
 

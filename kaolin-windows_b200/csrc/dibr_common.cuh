@@ -56,6 +56,7 @@ struct Plan {
   int mstride;                 // row stride of the count matrix: nchunks rounded up to 4 (int4 rows)
   int lists;
   // byte offsets inside the workspace (per list kind l = 0 raster, 1 soft)
+  int64_t off_work;       // int2 [B * nkx * nky * 4]  gather work list (rasterizer -> gather)
   int64_t off_mat[2];     // int [B][NB][mstride]  chunk counts -> exclusive offsets
   int64_t off_range[2];   // int2 [B][nchunks]     touched bin range of each chunk
   int64_t off_start[2];   // int [B][NB]           list segment start of each bin
@@ -121,6 +122,17 @@ struct BinJobs {
   unsigned long long* report;
 };
 
+// Work list of the gather kernel, filled by the rasterizer of the same call: one entry per
+// quarter block (the gather's CTA footprint) with uncovered pixels whose bin has a non-empty
+// soft list.  x = view, y = block x | block y << 16 (gather-block units).  `count` and the
+// queue cursor `next` live in the workspace header (zeroed with it at the start of a call).
+struct GatherWork {
+  int2* item;
+  unsigned* count;
+  unsigned* next;
+  unsigned cap;
+};
+
 struct RasterArgs {
   BinJob job;              // raster list + how to read faces
   const float4* rec;       // = job.rec: the list as records, or nullptr (list of face ids)
@@ -133,6 +145,10 @@ struct RasterArgs {
   float* out_feat;         // (B, H, W, D)
   float* out_w;            // (B, H, W, 3) or nullptr
   int* block_uncovered;    // (B, nkx*nky) or nullptr
+  // fused forward only (else null): the rasterizer hands the soft mask its work
+  float* mask;             // (B, H, W): base value of soft_mask, 1 covered / 0 uncovered
+  const int* soft_count;   // soft list length per (view, bin)
+  GatherWork work;         // quarter blocks that hold uncovered pixels and have a soft list
 };
 
 struct RasterBwdArgs {
@@ -204,6 +220,8 @@ struct SoftArgs {
   unsigned long long* report;  // device-visible host slot for the pair-buffer needs, or null
   const int* block_uncovered;  // (B, nkx*nky) uncovered pixels per raster block (written by
                                // the rasterizer of the same call), or null
+  GatherWork work;             // item != null: persistent gather over the rasterizer's work
+                               // list; soft_mask's base value is already written
 };
 
 // dense-state backward of the raw _C op, float and double

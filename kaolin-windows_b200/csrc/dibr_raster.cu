@@ -38,7 +38,7 @@ struct RasterSmem {
   int wsum[kRasterWarps];
   unsigned span[ROWS];          // slot | ry << 8 | xa << 16 | len << 24 (len <= 64 -> 7 bits)
   int spre[ROWS + 1];           // exclusive prefix of the span lengths within the batch
-  int uncovered;
+  int unc4[4];   // uncovered pixels per quarter block (the gather's CTA footprint)
 };
 
 // block-wide exclusive scan of one int per thread; returns the exclusive prefix, total in
@@ -90,7 +90,7 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
   const float pitch_x = 2.f * g.xs, pitch_y = 2.f * g.ys;
 
   for (int i = tid; i < BLK * BLK; i += kRasterThreads) zbuf[i] = 0ull;
-  if (tid == 0) sm.uncovered = 0;
+  if (tid < 4) sm.unc4[tid] = 0;
 
   // parent bin of this block
   const int shift = p.bin_log2 - BLK_LOG2;
@@ -329,7 +329,10 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
       if (a.D > 2) prefetch_l1(fp + 3 * a.D - 1);
     }
   }
-  int uncovered = 0;
+  // uncovered pixels by quarter row; the quarter COLUMN of a thread's pixels is fixed
+  // (i = tid + k * kRasterThreads and BLK divides kRasterThreads)
+  static_assert(kRasterThreads % BLK == 0, "quarter column must be fixed per thread");
+  int unc_top = 0, unc_bot = 0;
   for (int i = tid; i < BLK * BLK; i += kRasterThreads) {
     const int ix = bx0 + (i & (BLK - 1)), iy = by0 + (i >> BLK_LOG2);
     if (ix >= p.W || iy >= p.H) continue;
@@ -339,7 +342,8 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
       a.out_idx[pix] = -1;
       for (int d = 0; d < a.D; d++) a.out_feat[pix * a.D + d] = 0.f;
       if (a.out_w) { a.out_w[pix * 3] = 0.f; a.out_w[pix * 3 + 1] = 0.f; a.out_w[pix * 3 + 2] = 0.f; }
-      uncovered++;
+      if (a.mask) a.mask[pix] = 0.f;   // 1 - 1 (dibr_soft_mask_cuda.cu:181-182 with no face held)
+      if ((i >> BLK_LOG2) >> (BLK_LOG2 - 1)) unc_bot++; else unc_top++;
       continue;
     }
     const int face = key_face(key);
@@ -371,6 +375,7 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
     raster_weights(pix_x(g, ix), pix_y(g, iy), fc.ax, fc.ay, fc.bx, fc.by, fc.cx, fc.cy, a.eps_d,
                    w0, w1, w2);
     a.out_idx[pix] = face;
+    if (a.mask) a.mask[pix] = 1.f;     // covered (dibr_soft_mask_cuda.cu:68-70)
     if (a.out_w) { a.out_w[pix * 3] = w0; a.out_w[pix * 3 + 1] = w1; a.out_w[pix * 3 + 2] = w2; }
 #pragma unroll
     for (int d = 0; d < 4; d++)
@@ -383,12 +388,33 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
     }
   }
   if (a.block_uncovered) {
-    uncovered = __reduce_add_sync(DIBR_FULL_MASK, uncovered);
-    if (lane == 0 && uncovered) atomicAdd(&sm.uncovered, uncovered);
+    const int qx = (tid & (BLK - 1)) >> (BLK_LOG2 - 1);
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+      const int u = __reduce_add_sync(DIBR_FULL_MASK, qx == (q & 1) ? ((q >> 1) ? unc_bot : unc_top) : 0);
+      if (lane == 0 && u) atomicAdd(&sm.unc4[q], u);
+    }
     __syncthreads();
-    if (tid == 0)
-      a.block_uncovered[(long long)b * p.nkx * p.nky + byi * p.nkx + bxi] =
-          sm.uncovered;
+    if (tid == 0) {
+      const int total = sm.unc4[0] + sm.unc4[1] + sm.unc4[2] + sm.unc4[3];
+      a.block_uncovered[(long long)b * p.nkx * p.nky + byi * p.nkx + bxi] = total;
+      // hand the quarters that hold uncovered pixels to the soft mask's gather -- unless no
+      // face box reaches this bin: those pixels keep the 0 written above
+      if (a.work.item && total > 0 && a.soft_count[row] > 0) {
+        int nq = 0;
+#pragma unroll
+        for (int q = 0; q < 4; q++) nq += sm.unc4[q] > 0;
+        unsigned slot = atomicAdd(a.work.count, (unsigned)nq);
+#pragma unroll
+        for (int q = 0; q < 4; q++)
+          if (sm.unc4[q] > 0) {
+            if (slot < a.work.cap)
+              a.work.item[slot] =
+                  make_int2(b, (bxi * 2 + (q & 1)) | ((byi * 2 + (q >> 1)) << 16));
+            slot++;
+          }
+      }
+    }
   }
 #ifdef DIBR_TRACE_PHASES
   {
@@ -400,7 +426,7 @@ raster_forward_kernel(const RasterArgs a, const Plan p) {
                                  (unsigned long long)min(ph_r >> 6, 16383ll);
     DIBR_TRACE_END(u);
   }
-#else
+#elif !defined(DIBR_TRACE_GATHER)   // (the gather's trace shares the buffer: one kernel at a time)
   DIBR_TRACE_END(n);
 #endif
 }

@@ -51,27 +51,28 @@ struct GatherSmem {
   int tile[kGWarps][kGTileK][32];       // hits of the region a warp works on: [hit][pixel]
   unsigned short clist[kGWarps][kGChunk];  // the region's candidates of the chunk, compacted
   int next;
+  unsigned item_next;                   // persistent mode: the CTA's next work item
 };
 
+// One block (b, bxi, byi) of 2^BLK_LOG2 pixels, by the whole CTA.  prefilled: the rasterizer
+// of the same call has written soft_mask's base value (1 covered / 0 uncovered) and only
+// hands over blocks that hold uncovered pixels.
 template <int BLK_LOG2>
-__global__ void __launch_bounds__(kGThreads)
-softmask_gather_kernel(const SoftArgs a, const Plan p) {
+__device__ __forceinline__ void gather_block(const SoftArgs& a, const Plan& p,
+                                             GatherSmem<BLK_LOG2>& sm, int b, int bxi, int byi,
+                                             bool prefilled) {
   using Smem = GatherSmem<BLK_LOG2>;
   constexpr int BLK = Smem::BLK, NPX = Smem::NPX, NR = Smem::NR, RX = Smem::RX, NW = Smem::NW;
   constexpr int NRW = Smem::NRW;
-  extern __shared__ __align__(16) unsigned char s_raw[];
-  Smem& sm = *reinterpret_cast<Smem*>(s_raw);
   const PairBuf& pb = a.pairs;
-  pdl_prologue();
-
   const int tid = threadIdx.x, lane = lane_id(), warp = tid >> 5;
 #ifdef DIBR_TRACE_GATHER
   DIBR_TRACE_BEGIN();
+  long long ph_t = clock64(), ph_init = 0, ph_stage = 0, ph_gather = 0;   // thread 0's wall clock
+#define GATHER_PHASE(acc) do { const long long now_ = clock64(); acc += now_ - ph_t; ph_t = now_; } while (0)
+#else
+#define GATHER_PHASE(acc)
 #endif
-  // CTAs are taken longest face list first, as the rasterizer's (lpt_block): the few
-  // silhouette CTAs that walk a long list start early, the many that leave at once fill in
-  int b, bxi, byi;
-  if (!lpt_block(a.job, p, BLK_LOG2, blockIdx.x, b, bxi, byi)) return;
   const int bx0 = bxi << BLK_LOG2, by0 = byi << BLK_LOG2;
   const int bx1 = min(bx0 + BLK, p.W) - 1, by1 = min(by0 + BLK, p.H) - 1;
   const Grid g = plan_grid(p, a.job.mult);
@@ -82,13 +83,16 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
   // a raster block without a single uncovered pixel (the rasterizer of the same call counted
   // them): every pixel of this CTA is covered, soft_mask = 1, nothing to gather and no need
   // to read selected_face_idx
-  if (a.block_uncovered &&
+  if (!prefilled && a.block_uncovered &&
       a.block_uncovered[(long long)b * p.nkx * p.nky + (by0 >> p.blk_log2) * p.nkx +
                         (bx0 >> p.blk_log2)] == 0) {
     for (int i = tid; i < NPX; i += kGThreads) {
       const int ix = bx0 + (i & (BLK - 1)), iy = by0 + (i >> BLK_LOG2);
       if (ix < p.W && iy < p.H) a.mask[((long long)b * p.H + iy) * p.W + ix] = 1.0f;
     }
+#ifdef DIBR_TRACE_GATHER
+    DIBR_TRACE_END(-1);
+#endif
     return;
   }
   // ---- pixel state; covered pixels get their final value right away
@@ -100,7 +104,7 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
       uncovered = a.sel[pix] < 0;
       // 1 for covered pixels (:68-70); 1 - 1 = 0 for uncovered ones until the pair
       // evaluation overwrites those that hold faces
-      a.mask[pix] = uncovered ? 0.0f : 1.0f;
+      if (!prefilled) a.mask[pix] = uncovered ? 0.0f : 1.0f;
     }
     sm.cnt[i] = uncovered ? 0 : 0xffff;
   }
@@ -131,8 +135,10 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
   long long n = a.job.count[row];
   if (start + n > a.job.capacity) n = max(0ll, a.job.capacity - start);
 
+  GATHER_PHASE(ph_init);
   for (long long base = 0; base < n; base += kGChunk) {
     __syncthreads();
+    GATHER_PHASE(ph_gather);
     bool mine = false;
     for (int r = tid; r < NR; r += kGThreads) mine |= sm.ropen[r] != 0;
     if (tid == 0) sm.next = 0;
@@ -183,6 +189,7 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
       }
     }
     __syncthreads();
+    GATHER_PHASE(ph_stage);
 
     // ---- gather
     while (true) {
@@ -336,6 +343,7 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
 
   // ---- per-pixel hit counts of the regions that became active
   __syncthreads();
+  GATHER_PHASE(ph_gather);
   for (int r = warp; r < NR; r += kGWarps) {
     const int aidx = sm.ract[r];
     if (aidx >= 0 && aidx < pb.cap) {
@@ -353,8 +361,53 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
     }
   }
 #ifdef DIBR_TRACE_GATHER
-  DIBR_TRACE_END(n);
+  {
+    __syncthreads();
+    const long long ph_tail = clock64() - ph_t;
+    DIBR_TRACE_END(((unsigned long long)min(ph_init >> 6, 16383ll) << 42) |
+                   ((unsigned long long)min(ph_stage >> 6, 16383ll) << 28) |
+                   ((unsigned long long)min(ph_gather >> 6, 16383ll) << 14) |
+                   (unsigned long long)min(ph_tail >> 6, 16383ll));
+  }
 #endif
+}
+
+#undef GATHER_PHASE
+
+constexpr int kGPersistentCtas = 148 * 4;   // 4 CTAs per SM fit (shared memory)
+
+template <int BLK_LOG2>
+__global__ void __launch_bounds__(kGThreads)
+softmask_gather_kernel(const SoftArgs a, const Plan p) {
+  using Smem = GatherSmem<BLK_LOG2>;
+  extern __shared__ __align__(16) unsigned char s_raw[];
+  Smem& sm = *reinterpret_cast<Smem*>(s_raw);
+  pdl_prologue();
+  if (a.work.item) {
+    // Persistent CTAs over the rasterizer's work list: only blocks that hold uncovered
+    // pixels and have a soft list (the silhouette band) reach this kernel, and all of them
+    // start at once instead of queueing behind thousands of CTAs that leave immediately.
+    // First item = CTA id; further ones from a queue cursor, fetched while the current
+    // block is being worked on (the result is only read afterwards).
+    const unsigned nwork = min(*a.work.count, a.work.cap);
+    unsigned item = blockIdx.x;
+    while (item < nwork) {
+      unsigned fetched = 0;
+      if (threadIdx.x == 0) fetched = atomicAdd(a.work.next, 1u);
+      const int2 wk = a.work.item[item];
+      gather_block<BLK_LOG2>(a, p, sm, wk.x, wk.y & 0xffff, wk.y >> 16, true);
+      __syncthreads();   // the block's shared state is free; item_next is not being read
+      if (threadIdx.x == 0) sm.item_next = gridDim.x + fetched;
+      __syncthreads();
+      item = sm.item_next;
+    }
+    return;
+  }
+  // CTAs are taken longest face list first, as the rasterizer's (lpt_block): the few
+  // silhouette CTAs that walk a long list start early, the many that leave at once fill in
+  int b, bxi, byi;
+  if (!lpt_block(a.job, p, BLK_LOG2, blockIdx.x, b, bxi, byi)) return;
+  gather_block<BLK_LOG2>(a, p, sm, b, bxi, byi, false);
 }
 
 template <int G_LOG2>
@@ -363,7 +416,9 @@ static cudaError_t launch_gather(const SoftArgs& a, const Plan& p, cudaStream_t 
   cudaError_t e = smem_optin((const void*)softmask_gather_kernel<G_LOG2>, smem);
   if (e != cudaSuccess) return e;
   const int shift = p.bin_log2 - G_LOG2;
-  dim3 grid((unsigned)(((long long)p.B * p.NB) << (2 * shift)));
+  long long nblk = ((long long)p.B * p.NB) << (2 * shift);
+  if (a.work.item && nblk > kGPersistentCtas) nblk = kGPersistentCtas;
+  dim3 grid((unsigned)nblk);
   launch_k(softmask_gather_kernel<G_LOG2>, grid, kGThreads, smem, st, a, p);
   return cudaGetLastError();
 }

@@ -62,6 +62,9 @@ if len(sys.argv) > 2 and sys.argv[2] == "phases":   # -DDIBR_TRACE_PHASES build 
     ph = np.stack([(u >> np.uint64(42)) & np.uint64(16383), (u >> np.uint64(28)) & np.uint64(16383),
                    (u >> np.uint64(14)) & np.uint64(16383), u & np.uint64(16383)], 1).astype(np.float64) * 64 / 1.965e3
     tot = dur.sum()
+    heavy = dur > 10
+    print("phases, CTAs over 10 us only (%d): mean us per CTA %s of %.1f" % (
+        heavy.sum(), np.round(ph[heavy].mean(0), 2), dur[heavy].mean()))
     print("phase time summed over CTAs (us): A %.0f  A2 %.0f  B %.0f  resolve(+tail) %.0f  | all %.0f" % (
         ph[:, 0].sum(), ph[:, 1].sum(), ph[:, 2].sum(), ph[:, 3].sum(), tot))
     print("  shares: A %.2f A2 %.2f B %.2f resolve %.2f other %.2f" % tuple(
@@ -74,3 +77,11 @@ print("per-SM summed CTA time / span: mean %.2f max %.2f (resident CTAs per SM o
 # time by which X% of the CTA work is done
 end = np.sort((d[:, 1] - t0) / 1e3)
 print("CTA end-time percentiles 50/90/99/100: ", np.percentile(end, [50, 90, 99, 100]))
+# when CTAs start, and how long the ones started in each window live
+st = (d[:, 0] - t0) / 1e3
+edges = np.arange(0, span + 5, 5)
+for lo, hi in zip(edges[:-1], edges[1:]):
+    m = (st >= lo) & (st < hi)
+    if m.any():
+        print("  started in [%2.0f, %2.0f) us: %5d CTAs, mean dur %.2f us, of them > 5 us: %d" % (
+            lo, hi, m.sum(), dur[m].mean(), (dur[m] > 5).sum()))
