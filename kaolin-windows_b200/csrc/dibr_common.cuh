@@ -563,20 +563,22 @@ __device__ __forceinline__ unsigned long long trace_now() {
   return t;
 }
 #define DIBR_TRACE_BEGIN() const unsigned long long trace_t0_ = trace_now()
-#define DIBR_TRACE_END(user)                                                               \
+#define DIBR_TRACE_END_AT(slot, user)                                                      \
   do {                                                                                     \
     __syncthreads();                                                                       \
     if (p.trace && threadIdx.x == 0) {                                                        \
       unsigned smid_;                                                                      \
       asm volatile("mov.u32 %0, %%smid;" : "=r"(smid_));                                   \
-      unsigned long long* o_ =                                                             \
-          p.trace + 4ull * ((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x); \
+      unsigned long long* o_ = p.trace + 4ull * (slot);                                    \
       o_[0] = trace_t0_; o_[1] = trace_now(); o_[2] = smid_; o_[3] = (unsigned long long)(user); \
     }                                                                                      \
   } while (0)
+#define DIBR_TRACE_END(user) \
+  DIBR_TRACE_END_AT((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x, user)
 #else
 #define DIBR_TRACE_BEGIN()
 #define DIBR_TRACE_END(user)
+#define DIBR_TRACE_END_AT(slot, user)
 #endif
 
 __device__ __forceinline__ void prefetch_l1(const void* p) {

@@ -60,7 +60,7 @@ struct GatherSmem {
 template <int BLK_LOG2>
 __device__ __forceinline__ void gather_block(const SoftArgs& a, const Plan& p,
                                              GatherSmem<BLK_LOG2>& sm, int b, int bxi, int byi,
-                                             bool prefilled) {
+                                             bool prefilled, unsigned trace_slot) {
   using Smem = GatherSmem<BLK_LOG2>;
   constexpr int BLK = Smem::BLK, NPX = Smem::NPX, NR = Smem::NR, RX = Smem::RX, NW = Smem::NW;
   constexpr int NRW = Smem::NRW;
@@ -91,7 +91,7 @@ __device__ __forceinline__ void gather_block(const SoftArgs& a, const Plan& p,
       if (ix < p.W && iy < p.H) a.mask[((long long)b * p.H + iy) * p.W + ix] = 1.0f;
     }
 #ifdef DIBR_TRACE_GATHER
-    DIBR_TRACE_END(-1);
+    DIBR_TRACE_END_AT(trace_slot, -1);
 #endif
     return;
   }
@@ -122,7 +122,7 @@ __device__ __forceinline__ void gather_block(const SoftArgs& a, const Plan& p,
   }
   if (!__syncthreads_or(any_open)) {
 #ifdef DIBR_TRACE_GATHER
-    DIBR_TRACE_END(0);
+    DIBR_TRACE_END_AT(trace_slot, 0);
 #endif
     return;
   }
@@ -135,6 +135,17 @@ __device__ __forceinline__ void gather_block(const SoftArgs& a, const Plan& p,
   long long n = a.job.count[row];
   if (start + n > a.job.capacity) n = max(0ll, a.job.capacity - start);
 
+  // The list entries of the NEXT chunk are loaded (coalesced, independent of everything) when
+  // a chunk starts and stay in flight through its stage and gather phases; within a chunk all
+  // rectangle loads (the dependent gather through the face id) are issued before the first
+  // is used.  Leaves one exposed global round trip per chunk instead of four.
+  constexpr int NIT = kGChunk / kGThreads;
+  int fpre[NIT];
+#pragma unroll
+  for (int k = 0; k < NIT; k++) {
+    const long long e = (long long)k * kGThreads + tid;
+    fpre[k] = e < n ? a.job.list[start + e] : -1;
+  }
   GATHER_PHASE(ph_init);
   for (long long base = 0; base < n; base += kGChunk) {
     __syncthreads();
@@ -143,18 +154,32 @@ __device__ __forceinline__ void gather_block(const SoftArgs& a, const Plan& p,
     for (int r = tid; r < NR; r += kGThreads) mine |= sm.ropen[r] != 0;
     if (tid == 0) sm.next = 0;
     if (!__syncthreads_or(mine)) break;
-    const int nc = (int)min((long long)kGChunk, n - base);
 
     // ---- stage + transpose (t / 32 is warp-uniform)
-    for (int t = tid; t < kGChunk; t += kGThreads) {
+    // the face's exact pixel rectangle (the reference's half-open test, :89-97), kept by the
+    // binning pass: 8 bytes instead of the corner loads and the float geometry
+    int fcur[NIT];
+    ushort4 rcur[NIT];
+#pragma unroll
+    for (int k = 0; k < NIT; k++) {
+      fcur[k] = fpre[k];
+      rcur[k] = fcur[k] >= 0 ? __ldg(a.job.rect + (long long)b * p.F + fcur[k])
+                             : make_ushort4(1, 0, 1, 0);
+    }
+#pragma unroll
+    for (int k = 0; k < NIT; k++) {
+      const long long e = base + kGChunk + (long long)k * kGThreads + tid;
+      fpre[k] = e < n ? a.job.list[start + e] : -1;
+    }
+#pragma unroll
+    for (int k = 0; k < NIT; k++) {
+      const int t = k * kGThreads + tid;
       unsigned rmask[NW];
 #pragma unroll
       for (int w = 0; w < NW; w++) rmask[w] = 0u;
-      if (t < nc) {
-        const int f = a.job.list[start + base + t];
-        // the face's exact pixel rectangle (the reference's half-open test, :89-97), kept by
-        // the binning pass: 8 bytes instead of the corner loads and the float geometry
-        const ushort4 r = __ldg(a.job.rect + (long long)b * p.F + f);
+      if (fcur[k] >= 0) {
+        const int f = fcur[k];
+        const ushort4 r = rcur[k];
         int x_lo = r.x, x_hi = r.y, y_lo = r.z, y_hi = r.w;
         {
           x_lo = max(x_lo, bx0); x_hi = min(x_hi, bx1);
@@ -364,7 +389,7 @@ __device__ __forceinline__ void gather_block(const SoftArgs& a, const Plan& p,
   {
     __syncthreads();
     const long long ph_tail = clock64() - ph_t;
-    DIBR_TRACE_END(((unsigned long long)min(ph_init >> 6, 16383ll) << 42) |
+    DIBR_TRACE_END_AT(trace_slot, ((unsigned long long)min(ph_init >> 6, 16383ll) << 42) |
                    ((unsigned long long)min(ph_stage >> 6, 16383ll) << 28) |
                    ((unsigned long long)min(ph_gather >> 6, 16383ll) << 14) |
                    (unsigned long long)min(ph_tail >> 6, 16383ll));
@@ -395,7 +420,7 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
       unsigned fetched = 0;
       if (threadIdx.x == 0) fetched = atomicAdd(a.work.next, 1u);
       const int2 wk = a.work.item[item];
-      gather_block<BLK_LOG2>(a, p, sm, wk.x, wk.y & 0xffff, wk.y >> 16, true);
+      gather_block<BLK_LOG2>(a, p, sm, wk.x, wk.y & 0xffff, wk.y >> 16, true, item);
       __syncthreads();   // the block's shared state is free; item_next is not being read
       if (threadIdx.x == 0) sm.item_next = gridDim.x + fetched;
       __syncthreads();
@@ -407,7 +432,7 @@ softmask_gather_kernel(const SoftArgs a, const Plan p) {
   // silhouette CTAs that walk a long list start early, the many that leave at once fill in
   int b, bxi, byi;
   if (!lpt_block(a.job, p, BLK_LOG2, blockIdx.x, b, bxi, byi)) return;
-  gather_block<BLK_LOG2>(a, p, sm, b, bxi, byi, false);
+  gather_block<BLK_LOG2>(a, p, sm, b, bxi, byi, false, blockIdx.x);
 }
 
 template <int G_LOG2>
