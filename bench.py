@@ -210,6 +210,33 @@ def reference_arm(args, rank, world):
     })
 
 
+L2_BYTES = 126 * 1000 * 1000     # B200 L2 (B200_PROFILING.md)
+
+
+def step_footprint_bytes(job, B, H, W, D, F):
+    """Lower bound of the device bytes ONE mesh-level step touches: the API-level tensors
+    (inputs, the three images, both cotangents, both gradients), the per-view vertex images,
+    and the workspace parts whose sizes the kernels report (raster records, soft list, pair
+    buffer) or that are sized by the problem (exact soft rectangles).  The count matrix, the
+    order tables and every re-read are left out."""
+    from kaolin_windows_b200.render.mesh import dibr_graph
+    V = job["verts"].shape[-2]
+    api = sum(job[k].numel() * 4 for k in ("verts", "vfeat", "rot", "trans", "proj"))
+    api += job["faces32"].numel() * 4 if "faces32" in job else F * 3 * 4
+    images = B * H * W * (D * 4 + 4 + 8)              # features, soft mask, face index
+    cot = B * H * W * (D + 1) * 4                     # G1, G2
+    grads = (job["verts"].numel() + job["vfeat"].numel()) * 4
+    vertex_images = B * V * (2 + 3) * 4
+    rect = B * F * 8
+    lists = 0
+    ents = [e for e in dibr_graph._entries.values() if isinstance(e, dibr_graph._VertexEntry)]
+    if ents:
+        need = [int(x) for x in ents[-1].slot_np[:4]]     # raster entries, soft entries, pair
+        if min(need) >= 0:                                # segments, active regions
+            lists = need[0] * 48 + need[1] * 4 + need[2] * 256 * 9 + need[3] * (64 + 4 + 16)
+    return int(api + images + cot + grads + vertex_images + rect + lists)
+
+
 def bench_config(views_per_gpu, F, H, W, D):
     """The workload, identical in both arms (prose lives in the line's `notes`)."""
     return {"workload": CFG, "views_per_gpu": views_per_gpu, "faces": F, "H": H, "W": W, "D": D,
@@ -406,13 +433,15 @@ def main():
             ev.record(copy_stream)
         in_ready[slot] = ev
 
-    def e2e_step(i, with_loss, last):
+    def e2e_step(i, with_loss, last, flush_l2):
         main = torch.cuda.current_stream(dev)
         slot = i & 1
-        l2_small.zero_()                       # L2 flush, inside the timed span, not subtracted
+        if flush_l2:
+            l2_small.zero_()                   # L2 flush, inside the timed span, not subtracted
         main.wait_event(in_ready[slot])
-        if res_ev[slot ^ 1] is not None:       # the previous results have left the device
-            main.wait_event(res_ev[slot ^ 1])  # (before an exchange may rewrite its buffer)
+        # (the previous step's D2H reads private copies of its gradients -- result_grads()
+        # clones, also when the exchange is folded in -- held in keep[] until that copy has
+        # been synchronised: this step does not wait for it)
         j = e2e_jobs[slot]
         out, mask, gv, gf = mesh_step(j, exchanger, verts=j["verts"], vfeat=j["vfeat"])
         if not last:
@@ -442,7 +471,7 @@ def main():
             return float(h_res[slot ^ 1][0])
         return None
 
-    def e2e_time(with_loss):
+    def e2e_time(with_loss, flush_l2):
         for n_run in (12, K):
             if n_run == K:
                 barrier()
@@ -450,7 +479,7 @@ def main():
             res_ev[0] = res_ev[1] = None
             e2e_h2d(0)
             for i in range(n_run):
-                e2e_step(i, with_loss, i == n_run - 1)
+                e2e_step(i, with_loss, i == n_run - 1, flush_l2)
             res_ev[(n_run - 1) & 1].synchronize()
             float(h_res[(n_run - 1) & 1][0])   # the last step's results
             torch.cuda.synchronize(dev)
@@ -459,8 +488,30 @@ def main():
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return max(float(t.item()), 1e-9) / K
 
-    e2e_s = e2e_time(False)
-    e2e_loss_s = e2e_time(True)
+    # L2 between e2e steps.  The two input slots are two CUDA-graph entries (graphs are keyed
+    # by input addresses), each with its OWN workspace, outputs and gradient buffers, so
+    # consecutive steps touch disjoint buffer sets: a buffer is touched again after two steps'
+    # worth of other data has gone through the cache.  When one step's footprint alone
+    # (counted below from the sizes the kernels report: a lower bound) exceeds the 126 MB L2,
+    # that is the timing rules' "inputs larger than L2" and the e2e loop runs no explicit
+    # flush; otherwise it keeps the 160 MiB memset inside its timed region.  The flushed
+    # variant is always reported beside it (`with_l2_flush`).
+    e2e_time(False, True)                      # (settles both slots' graph entries)
+    if os.environ.get("DIBR_BENCH_PROFILE") == "1" and rank == 0:   # dev aid: host cost of the loop
+        import cProfile
+        import pstats
+        pr = cProfile.Profile()
+        K_keep, K = K, 300
+        pr.enable()
+        e2e_time(False, False)
+        pr.disable()
+        K = K_keep
+        pstats.Stats(pr, stream=sys.stderr).sort_stats("tottime").print_stats(28)
+    footprint = step_footprint_bytes(job, B, H, W, D, F)
+    e2e_flush = footprint <= L2_BYTES
+    e2e_s = e2e_time(False, e2e_flush)
+    e2e_loss_s = e2e_time(True, e2e_flush)
+    e2e_flushed_s = e2e_s if e2e_flush else e2e_time(False, True)
     sampler.stop_flag = True      # clocks sampled across both timed regions (device + e2e)
     e2e_val = world * B * P / e2e_s / 1e6
 
@@ -599,6 +650,15 @@ def main():
                         "pinned buffer; the step; D2H of its results (both gradients) into "
                         "pinned buffers. Inputs double buffered: step i+1's H2D and step i's D2H "
                         "on a copy stream; the host reads step i's results while step i+1 runs",
+                "l2": ("160 MiB memset inside every timed step" if e2e_flush else
+                       "no explicit flush: the two input slots own disjoint workspaces / outputs "
+                       "(two graph entries) and one step touches >= %.0f MB > the %d MB L2"
+                       % (footprint / 1e6, L2_BYTES // 1000000)),
+                "step_footprint_bytes": footprint,
+                "with_l2_flush": {"ms_per_step": e2e_flushed_s * 1e3,
+                                  "value": world * B * P / e2e_flushed_s / 1e6,
+                                  "what": "the same loop with a 160 MiB memset inside every "
+                                          "timed step (not subtracted)"},
                 "with_loss": {"ms_per_step": e2e_loss_s * 1e3, "d2h_bytes_per_step": d2h_grads + 4,
                               "value": world * B * P / e2e_loss_s / 1e6,
                               "what": "the same + (features*G1).sum() + (soft_mask*G2).sum() "
