@@ -14,11 +14,15 @@
 //              (rows padded to int4, four independent 16-byte loads per lane in flight, then
 //              shuffle scans), then one list segment per bin is reserved from a global
 //              cursor (one atomic per CTA of 8 bins).
-//   bin_fill   soft-mask list (ordered): per step of 32 faces every lane ORs its lane bit
-//              into a per-warp shared-memory mask word of each bin of its rectangle; a
-//              lane's slot in a bin is then the bin's counter + __popc(mask & lanemask_lt),
-//              so every bin's list comes out sorted by face index with all lanes working in
-//              parallel; the lowest lane of each mask advances the counter and clears it.
+//   bin_fill   soft-mask list (ordered), up to kMaskBins bins: per step of 32 faces every lane
+//              ORs its lane bit into a per-warp shared-memory mask word of each bin of its
+//              rectangle; a lane's slot in a bin is then the bin's counter +
+//              __popc(mask & lanemask_lt), so every bin's list comes out sorted by face index
+//              with all lanes working in parallel; the lowest lane of each mask advances the
+//              counter and clears it.  More bins (the mask words would double the shared
+//              memory per warp and halve the resident warps: measured slower at 1024 bins):
+//              the warp walks the distinct bins its 32 faces touch in ascending bin id (warp
+//              min-reduce) and ranks the faces touching the current bin with a ballot.
 //              rasterizer list (order free, its depth test is order independent): slots
 //              are taken with shared-memory atomics on the same per-warp counters.
 //
@@ -30,6 +34,7 @@ namespace dibr {
 
 
 constexpr int kBinWarps = 4;  // warps (= chunks) per CTA of bin_count / bin_fill
+constexpr int kMaskBins = 256; // ordered fill: lane masks up to this many bins, else the bin walk
 
 // Bin rectangle of a face box; false if it touches no pixel.
 __device__ __forceinline__ bool bin_rect(const Grid& g, const Face2D& f, int bin_log2, int& bx0,
@@ -74,7 +79,7 @@ bin_walk_kernel(const BinJobs jobs, const Plan p) {
     for (int i = lo_bin + lane; i <= hi_bin; i += 32)
       hist[i] = (int)min((long long)job.start[row + i] +
                              job.mat[(row + i) * p.mstride + chunk], kMaxListEntries);
-    if (job.ordered)
+    if (job.ordered && p.NB <= kMaskBins)
       for (int i = lo_bin + lane; i <= hi_bin; i += 32) lmask[i] = 0u;
   } else {
     for (int i = lane; i < p.NB; i += 32) hist[i] = 0;
@@ -145,13 +150,14 @@ bin_walk_kernel(const BinJobs jobs, const Plan p) {
       continue;
     }
     // Ordered emission (soft-mask list, fill pass only: the counting pass took the branch
-    // above).  Three lane-parallel sweeps over the lane's own bin rectangle:
-    //   mark   OR the lane bit into the mask word of every bin of the rectangle
-    //   place  slot = bin counter + number of lower lanes (= lower face ids) in the mask
-    //   close  the lowest lane of a mask adds its population to the counter and clears it
-    // (a lane that reads an already cleared mask in `close` sees 0 and is not its lowest
-    // lane; counters only move in `close`, masks only in `mark` and `close`)
-    if (FILL) {
+    // above).
+    if (FILL && p.NB <= kMaskBins) {
+      // Three lane-parallel sweeps over the lane's own bin rectangle:
+      //   mark   OR the lane bit into the mask word of every bin of the rectangle
+      //   place  slot = bin counter + number of lower lanes (= lower face ids) in the mask
+      //   close  the lowest lane of a mask adds its population to the counter and clears it
+      // (a lane that reads an already cleared mask in `close` sees 0 and is not its lowest
+      // lane; counters only move in `close`, masks only in `mark` and `close`)
       if (act)
         for (int cy = by0; cy <= by1; cy++)
           for (int cx = bx0; cx <= bx1; cx++) atomicOr(&lmask[cy * p.nbx + cx], 1u << lane);
@@ -175,6 +181,30 @@ bin_walk_kernel(const BinJobs jobs, const Plan p) {
             }
           }
       __syncwarp();
+    } else if (FILL) {
+      // Each lane walks its rectangle row-major (ascending bin id); the warp repeatedly takes
+      // the smallest pending bin id, so all faces touching that bin are handled together, in
+      // lane (= face) order.
+      int cx = bx0, cy = by0;
+      while (true) {
+        const int cur = act ? cy * p.nbx + cx : 0x7fffffff;
+        const int m = __reduce_min_sync(DIBR_FULL_MASK, cur);
+        if (m == 0x7fffffff) break;
+        const bool hit = (cur == m);
+        const unsigned mask = __ballot_sync(DIBR_FULL_MASK, hit);
+        const int base = hist[m];
+        __syncwarp();
+        if (lane == 0) hist[m] = base + __popc(mask);
+        if (hit) {
+          const long long slot = (long long)base + __popc(mask & lanemask_lt());
+          if (slot < job.capacity) job.list[slot] = f;
+          if (++cx > bx1) {
+            cx = bx0;
+            if (++cy > by1) act = false;
+          }
+        }
+        __syncwarp();
+      }
     }
   }
   if (!FILL) {
@@ -270,7 +300,8 @@ cudaError_t launch_binning_count(const BinJobs& jobs, int njobs, const Plan& p, 
 }
 
 cudaError_t launch_binning_fill(const BinJobs& jobs, int njobs, const Plan& p, cudaStream_t st) {
-  const size_t smem = (size_t)2 * kBinWarps * p.NB * sizeof(int);   // counters + lane masks
+  // counters (+ lane masks of the ordered fill up to kMaskBins bins)
+  const size_t smem = (size_t)(p.NB <= kMaskBins ? 2 : 1) * kBinWarps * p.NB * sizeof(int);
   dim3 grid((p.nchunks + kBinWarps - 1) / kBinWarps, p.B, njobs);
   prof_begin(K_BIN_FILL, st);
   launch_k(bin_walk_kernel<true>, grid, kBinWarps * 32, smem, st, jobs, p);
