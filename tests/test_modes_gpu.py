@@ -1,7 +1,9 @@
 """The library's launch / report switches give the same results as the defaults:
 DIBR_B200_REPORT=copy (list-size reports as copy nodes -- what a C caller handing pageable
-memory gets) and DIBR_B200_PDL=1 (programmatic dependent launch).  Both are read once per
-process, so each combination runs the oracle-checked smoke in its own interpreter."""
+memory gets), DIBR_B200_PDL=1 (programmatic dependent launch), DIBR_B200_RASTER_REC=0 (raster
+lists of face ids instead of records) and DIBR_B200_GATHER_WORK=0 (the fused forward's gather
+over every block of the screen instead of the rasterizer's work list).  All are read once
+per process, so each combination runs the oracle-checked smoke in its own interpreter."""
 import os
 import subprocess
 import sys
@@ -15,7 +17,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 @pytest.mark.parametrize("env", [{"DIBR_B200_REPORT": "copy"}, {"DIBR_B200_PDL": "1"},
                                  {"DIBR_B200_REPORT": "copy", "DIBR_B200_PDL": "1"},
                                  {"DIBR_B200_WORKSPACE": "poll"}, {"DIBR_B200_WORKSPACE": "sync"},
-                                 {"DIBR_B200_RASTER_REC": "0"}])
+                                 {"DIBR_B200_RASTER_REC": "0"}, {"DIBR_B200_GATHER_WORK": "0"}])
 def test_smoke_under_switch(env):
     e = dict(os.environ)
     e.update(env)
