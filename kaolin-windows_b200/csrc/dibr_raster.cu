@@ -515,21 +515,27 @@ __device__ __forceinline__ BwdFace bwd_face(const RasterBwdArgs& a, int b, int f
               fabsf(f.k3raw) >= min_k3 && fabsf(f.k3raw) < 3e38f;
   return f;
 }
-// features / gradient slots of corner k of a face, either layout
+// features / gradient slots of corner k of a face, either layout.  The view's base (uniform
+// over the CTA: b = blockIdx.z) is kept apart from the per-corner offset, a 32 x 32 -> 64 bit
+// product: the nine pointers of a face were 15 % of the kernel's instructions as 64-bit
+// multiplies of (view offset + vertex id).
 __device__ __forceinline__ const float* bwd_feat(const RasterBwdArgs& a, int b, int face,
                                                  const BwdFace& f, int k) {
-  if (a.faces) return a.feat + ((a.feat_shared ? 0ll : (long long)b * a.V) + f.v[k]) * a.D;
-  return a.feat + (((long long)b * a.F + face) * 3 + k) * a.D;
+  if (a.faces)
+    return a.feat + (a.feat_shared ? 0ll : (long long)b * a.V * a.D) + (long long)f.v[k] * a.D;
+  return a.feat + (long long)b * a.F * 3 * a.D + (long long)(face * 3 + k) * a.D;
 }
 __device__ __forceinline__ float* bwd_gfeat(const RasterBwdArgs& a, int b, int face,
                                             const BwdFace& f, int k) {
-  if (a.faces) return a.grad_feat + ((a.feat_shared ? 0ll : (long long)b * a.V) + f.v[k]) * a.D;
-  return a.grad_feat + (((long long)b * a.F + face) * 3 + k) * a.D;
+  if (a.faces)
+    return a.grad_feat + (a.feat_shared ? 0ll : (long long)b * a.V * a.D) +
+           (long long)f.v[k] * a.D;
+  return a.grad_feat + (long long)b * a.F * 3 * a.D + (long long)(face * 3 + k) * a.D;
 }
 __device__ __forceinline__ float* bwd_gimg(const RasterBwdArgs& a, int b, int face,
                                            const BwdFace& f, int k) {
-  if (a.faces) return a.grad_img + ((long long)b * a.V + f.v[k]) * 2;
-  return a.grad_img + (((long long)b * a.F + face) * 3 + k) * 2;
+  if (a.faces) return a.grad_img + (long long)b * a.V * 2 + f.v[k] * 2ll;
+  return a.grad_img + (long long)b * a.F * 6 + (face * 3 + k) * 2ll;
 }
 
 // The reference's per-pixel backward (:273-399) for one pixel, in double, from the weights w:
