@@ -229,6 +229,18 @@ static bool gather_handoff_enabled() {
   return on;
 }
 
+// Zero-fill of the two gradient outputs of a backward call: one memset when the second
+// starts exactly where the first ends (the Python graph entries allocate them that way: one
+// node less in the launch chain), else two.  Exact adjacency only -- no byte that is not part
+// of either output is ever written.
+static cudaError_t zero_gradients(float* g0, size_t bytes0, float* g1, size_t bytes1,
+                                  cudaStream_t st) {
+  if (g1 && (char*)g1 == (char*)g0 + bytes0) return cudaMemsetAsync(g0, 0, bytes0 + bytes1, st);
+  cudaError_t e = cudaMemsetAsync(g0, 0, bytes0, st);
+  if (e == cudaSuccess && g1) e = cudaMemsetAsync(g1, 0, bytes1, st);
+  return e;
+}
+
 // gather work list of the fused forward (rasterizer -> gather); header words 200 / 204
 static GatherWork gather_work(const Plan& p, const Workspace& w) {
   GatherWork g;
@@ -242,11 +254,17 @@ static GatherWork gather_work(const Plan& p, const Workspace& w) {
 // memset + count + scan + (capacity check) + fill for the given jobs (kinds[i] = 0/1).
 static int run_binning(const Plan& p, const Workspace& w, BinJobs& jobs, const int* kinds,
                        int njobs, int64_t* needed_host, cudaStream_t st) {
-  DIBR_CUDA(cudaMemsetAsync(w.base, 0, p.off_start[0], st));  // totals + block flags
-  for (int i = 0; i < njobs; i++) {
-    const int l = kinds[i];
-    DIBR_CUDA(cudaMemsetAsync(w.base + p.off_start[l], 0,
-                              (l == 0 ? p.off_start[1] : p.off_order[0]) - p.off_start[l], st));
+  if (njobs == 2) {
+    // header + block flags + both lists' start / count / range / count matrix are one
+    // contiguous range: one memset node instead of three in the launch chain
+    DIBR_CUDA(cudaMemsetAsync(w.base, 0, p.off_order[0], st));
+  } else {
+    DIBR_CUDA(cudaMemsetAsync(w.base, 0, p.off_start[0], st));  // totals + block flags
+    for (int i = 0; i < njobs; i++) {
+      const int l = kinds[i];
+      DIBR_CUDA(cudaMemsetAsync(w.base + p.off_start[l], 0,
+                                (l == 0 ? p.off_start[1] : p.off_order[0]) - p.off_start[l], st));
+    }
   }
   const bool direct = needed_host && g_report_direct && p.B > 0 && p.F > 0;
   jobs.totals = (const unsigned long long*)(w.base + p.off_total);
@@ -518,8 +536,8 @@ extern "C" int dibr_render_bwd(int B, int F, int H, int W, int D, const float* g
     return fail(DIBR_E_INVALID, "null pointer");
   cudaStream_t st = (cudaStream_t)stream;
   const size_t nfv = (size_t)B * F * 3;
-  DIBR_CUDA(cudaMemsetAsync(grad_img, 0, nfv * 2 * sizeof(float), st));
-  if (D > 0) DIBR_CUDA(cudaMemsetAsync(grad_feat, 0, nfv * D * sizeof(float), st));
+  DIBR_CUDA(zero_gradients(grad_img, nfv * 2 * sizeof(float), D > 0 ? grad_feat : nullptr,
+                           nfv * D * sizeof(float), st));
   const bool do_raster = grad_feat_img && D > 0, do_soft = grad_mask && K > 0;
   if (do_soft && !mask) return fail(DIBR_E_INVALID, "null soft_mask");
   RasterBwdArgs ra;
@@ -787,10 +805,9 @@ extern "C" int dibr_render_mesh_bwd(int B, int V, int F, int H, int W, int D,
   if (!grad_vertices_image || (D > 0 && !grad_vertex_features))
     return fail(DIBR_E_INVALID, "null gradient output");
   cudaStream_t st = (cudaStream_t)stream;
-  DIBR_CUDA(cudaMemsetAsync(grad_vertices_image, 0, (size_t)B * V * 2 * sizeof(float), st));
-  if (D > 0)
-    DIBR_CUDA(cudaMemsetAsync(grad_vertex_features, 0,
-                              (size_t)(features_shared ? 1 : B) * V * D * sizeof(float), st));
+  DIBR_CUDA(zero_gradients(grad_vertices_image, (size_t)B * V * 2 * sizeof(float),
+                           D > 0 ? grad_vertex_features : nullptr,
+                           (size_t)(features_shared ? 1 : B) * V * D * sizeof(float), st));
   if (F == 0 || V == 0) return DIBR_OK;
   if (!idx || !vertices_image || !faces || (D > 0 && !vertex_features))
     return fail(DIBR_E_INVALID, "null pointer");

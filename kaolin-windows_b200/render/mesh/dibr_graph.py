@@ -54,8 +54,12 @@ class _Entry:
         self.idx = torch.empty((B, H, W), dtype=torch.long, device=dev)
         self.out = torch.empty((B, H, W, D), dtype=torch.float32, device=dev)
         self.mask = torch.empty((B, H, W), dtype=torch.float32, device=dev)
-        self.grad_img = torch.empty(tuple(img.shape), dtype=torch.float32, device=dev)
-        self.grad_feat = torch.empty(tuple(feat.shape), dtype=torch.float32, device=dev)
+        # both gradients in ONE buffer, exactly adjacent: the backward call zero-fills them with
+        # one memset node and the result leaves as one clone (fewer nodes in the launch chain)
+        self._n_img = img.numel()
+        self._gpool = torch.empty(self._n_img + feat.numel(), dtype=torch.float32, device=dev)
+        self.grad_img = self._gpool[:self._n_img].view(tuple(img.shape))
+        self.grad_feat = self._gpool[self._n_img:].view(tuple(feat.shape))
         self.caps = _workspace.initial_caps(B, self.F, H, W, params[2])
         if not (_workspace.USE_PAIRS and 0 < params[2] <= _workspace.PAIR_MAX_K):
             self.caps[2] = 0
@@ -223,7 +227,9 @@ class DibrRasterizationGraphed(Function):
         # clones: AccumulateGrad may adopt a returned tensor as a leaf's .grad without copying
         # it (it looks at the tensor's use count, not at storage sharing); a view of the
         # entry's static buffer would then be rewritten by the next replay
-        return (None, None, None, entry.grad_img.clone(), entry.grad_feat.clone())
+        flat = entry._gpool.clone()
+        return (None, None, None, flat[:entry._n_img].view(entry.grad_img.shape),
+                flat[entry._n_img:].view(entry.grad_feat.shape))
 
 
 def graphed_dibr_rasterization(H, W, face_vertices_z, face_vertices_image, face_features,
@@ -270,8 +276,13 @@ class _MeshEntry(_Entry):
         self.idx = torch.empty((B, H, W), dtype=torch.long, device=dev)
         self.out = torch.empty((B, H, W, D), dtype=torch.float32, device=dev)
         self.mask = torch.empty((B, H, W), dtype=torch.float32, device=dev)
-        self.grad_img = torch.empty(tuple(vimg.shape), dtype=torch.float32, device=dev)
-        self.grad_feat = torch.empty(tuple(vfeat.shape), dtype=torch.float32, device=dev)
+        # [grad_img | grad_feat | tail] in one buffer (see _Entry); the vertex entry keeps its
+        # world-space vertex gradient in the tail so that both results leave as one clone
+        self._n_img, self._n_feat = vimg.numel(), vfeat.numel()
+        self._gpool = torch.empty(self._n_img + self._n_feat + getattr(self, "_pool_tail", 0),
+                                  dtype=torch.float32, device=dev)
+        self.grad_img = self._gpool[:self._n_img].view(tuple(vimg.shape))
+        self.grad_feat = self._gpool[self._n_img:self._n_img + self._n_feat].view(tuple(vfeat.shape))
         self.caps = _workspace.initial_caps(B, self.F, H, W, params[2])
         if not (_workspace.USE_PAIRS and 0 < params[2] <= _workspace.PAIR_MAX_K):
             self.caps[2] = 0
@@ -331,7 +342,10 @@ class DibrRasterizationMeshGraphed(Function):
         entry.backward(g, gm)
         # clones: autograd may adopt a returned tensor as .grad without copying it, and the
         # next replay rewrites the entry's buffers (V-sized: the copy is cheap)
-        return None, None, entry.grad_img.clone(), entry.grad_feat.clone()
+        n_img, n_feat = entry._n_img, entry._n_feat
+        flat = entry._gpool[:n_img + n_feat].clone()
+        return (None, None, flat[:n_img].view(entry.grad_img.shape),
+                flat[n_img:].view(entry.grad_feat.shape))
 
 
 def graphed_dibr_rasterization_mesh(H, W, vertices_camera, vertices_image, faces32,
@@ -394,8 +408,9 @@ class _VertexEntry(_MeshEntry):
         self.verts_shared = int(vertices.shape[0] == 1)
         self.vcam = torch.empty((batch, V, 3), dtype=torch.float32, device=dev)
         self.vimg = torch.empty((batch, V, 2), dtype=torch.float32, device=dev)
-        self.grad_verts = torch.empty(tuple(vertices.shape), dtype=torch.float32, device=dev)
+        self._pool_tail = vertices.numel()
         super().__init__(H, W, self.vcam, self.vimg, faces32, vfeat, valid, params)
+        self.grad_verts = self._gpool[self._n_img + self._n_feat:].view(tuple(vertices.shape))
         if exchange is not None:
             # the gradients are written straight into this rank's buffer of the exchange's
             # symmetric allocation; the all-reduce is the last node of the backward graph
@@ -426,7 +441,9 @@ class _VertexEntry(_MeshEntry):
     def result_grads(self):
         """Copies of the two gradients (summed over ranks when an exchange is folded in)."""
         if self.exchange is None:
-            return self.grad_verts.clone(), self.grad_feat.clone()
+            flat = self._gpool[self._n_img:].clone()     # [grad_feat | grad_verts], one copy
+            return (flat[self._n_feat:].view(self.grad_verts.shape),
+                    flat[:self._n_feat].view(self.grad_feat.shape))
         flat = self.exchange.result.clone()    # one copy, both gradients are views of it
         return (flat[:self.nv].view(self.grad_verts.shape),
                 flat[self.off_f:self.off_f + self.nf].view(self.grad_feat.shape))
