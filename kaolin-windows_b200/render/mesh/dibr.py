@@ -145,8 +145,10 @@ class DibrRasterizationB200(Function):
         D = feat.shape[-1]
         if grad_features is None and grad_soft_mask is None:
             return (None,) * 11
-        grad_img = torch.empty_like(img)      # zero-filled by the call
-        grad_feat = torch.empty_like(feat)
+        # zero-filled by the call -- with ONE memset, the two being exactly adjacent
+        pool = torch.empty(img.numel() + feat.numel(), dtype=torch.float32, device=img.device)
+        grad_img = pool[:img.numel()].view(img.shape)
+        grad_feat = pool[img.numel():].view(feat.shape)
         g = None if grad_features is None else _prep(grad_features, "grad_interpolated_features")
         gm = None if grad_soft_mask is None else _prep(grad_soft_mask, "grad_soft_mask")
         with torch.cuda.device(img.device):
@@ -302,8 +304,10 @@ class DibrRasterizationMeshB200(Function):
         if grad_features is None and grad_soft_mask is None:
             return (None,) * 12
         lib = _lib.lib()
-        grad_vimg = torch.empty_like(vimg)      # zero-filled by the call
-        grad_vfeat = torch.empty_like(vfeat)
+        # zero-filled by the call -- with ONE memset, the two being exactly adjacent
+        pool = torch.empty(vimg.numel() + vfeat.numel(), dtype=torch.float32, device=vimg.device)
+        grad_vimg = pool[:vimg.numel()].view(vimg.shape)
+        grad_vfeat = pool[vimg.numel():].view(vfeat.shape)
         g = None if grad_features is None else _prep(grad_features, "grad_interpolated_features")
         gm = None if grad_soft_mask is None else _prep(grad_soft_mask, "grad_soft_mask")
         with torch.cuda.device(vimg.device):
