@@ -420,6 +420,7 @@ def main():
     in_free = [None, None]                     # the step that read the slot has finished
     keep = [None, None]                        # tensors a pending D2H still reads
     copy_stream = torch.cuda.Stream(dev)
+    on_copy_stream = torch.cuda.stream(copy_stream)   # one context object, entered per step
     h2d = h_pack.numel() * 4
     d2h_grads = (nv + nf) * 4
     l2_small = flush[:160 << 20]              # 160 MiB > the 126 MB L2
@@ -427,7 +428,7 @@ def main():
     def e2e_h2d(slot):
         if in_free[slot] is not None:
             copy_stream.wait_event(in_free[slot])
-        with torch.cuda.stream(copy_stream):
+        with on_copy_stream:
             d_packs[slot].copy_(h_pack, non_blocking=True)
             ev = torch.cuda.Event()
             ev.record(copy_stream)
@@ -456,7 +457,7 @@ def main():
         keep[slot] = (gv, gf, loss)
         copy_stream.wait_event(done)
         h = h_res[slot]
-        with torch.cuda.stream(copy_stream):
+        with on_copy_stream:
             h[:nv].copy_(gv.reshape(-1), non_blocking=True)          # the step's results: both
             h[nv:nv + nf].copy_(gf.reshape(-1), non_blocking=True)   # gradients of the mesh
             if with_loss:
@@ -506,7 +507,7 @@ def main():
         e2e_time(False, False)
         pr.disable()
         K = K_keep
-        pstats.Stats(pr, stream=sys.stderr).sort_stats("tottime").print_stats(28)
+        pstats.Stats(pr, stream=sys.stderr).sort_stats(os.environ.get("DIBR_BENCH_PROFILE_SORT", "tottime")).print_stats(45)
     footprint = step_footprint_bytes(job, B, H, W, D, F)
     e2e_flush = footprint <= L2_BYTES
     e2e_s = e2e_time(False, e2e_flush)

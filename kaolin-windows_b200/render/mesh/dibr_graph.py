@@ -50,6 +50,7 @@ class _Entry:
         self.B, self.F = z.shape[:2]
         self.D = feat.shape[-1]
         dev = self.dev = z.device
+        self._devctx = torch.cuda.device(dev)   # reused: constructing one costs ~10 us of Python
         B, D = self.B, self.D
         self.idx = torch.empty((B, H, W), dtype=torch.long, device=dev)
         self.out = torch.empty((B, H, W, D), dtype=torch.float32, device=dev)
@@ -121,7 +122,7 @@ class _Entry:
         if self.caps[2] > 0 and want > self.caps[2]:
             self.caps[2] = min(int(want * 1.25) + 1024, 1 << 23)
             self._alloc_ws()
-        with torch.cuda.device(self.dev):
+        with self._devctx:
             for _attempt in range(4):
                 self.slot_np[:] = -1
                 if self.graph is not None:
@@ -159,7 +160,7 @@ class _Entry:
     def backward(self, g_out, g_mask):
         key = (None if g_out is None else g_out.data_ptr(),
                None if g_mask is None else g_mask.data_ptr())
-        with torch.cuda.device(self.dev):
+        with self._devctx:
             g = self.bwd_graphs.get(key)
             if g is not None:
                 g.replay()
@@ -272,6 +273,7 @@ class _MeshEntry(_Entry):
         self.D = vfeat.shape[-1]
         self.shared = int(vfeat.shape[0] == 1)
         dev = self.dev = vcam.device
+        self._devctx = torch.cuda.device(dev)   # reused: constructing one costs ~10 us of Python
         B, D = self.B, self.D
         self.idx = torch.empty((B, H, W), dtype=torch.long, device=dev)
         self.out = torch.empty((B, H, W, D), dtype=torch.float32, device=dev)
